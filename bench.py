@@ -1,0 +1,329 @@
+"""bench.py -- IIT train-step throughput (pairs/s) on the configuration BASELINE.json quotes:
+MNIST-PVR, ResNet-18 LL, IIT + behaviour + strict-IIT losses, bf16 activations, batch 4096 pairs
+per GPU (configs[1]); one "step" = one StrictIITModelPair.run_train_step over one batch of
+synthetic (base, source) pairs = 5 LL forwards, 3 backwards, 3 clip+Adam updates.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--batch B]
+                    [--dtype bf16|f32]
+
+N>1 is launched by torchrun (one rank per GPU, NCCL gradient all-reduce, weak scaling).
+Prints ONE JSON line on rank 0. `--impl reference` times the oracle's CPU restatement of the
+reference step (oracle/restate.py; the Python reference itself needs /root/reference and
+transformer_lens, neither of which exists on the GPU box) on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+HOOK = "mod.layer3.mod.1.mod.conv2.hook_point"
+F56 = 258_162_688            # ResNet-18 forward FLOPs per 56x56 image
+METRIC = "iit_train_pairs_per_sec"
+UNIT = "pairs/s"
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return {"hbm_gbs": p["hbm_gbs"], "tflops": p.get("bf16_tflops_sustained", p["bf16_tflops"]), "src": "measured"}
+    return {"hbm_gbs": 6650.0, "tflops": 1400.0, "src": "fallback"}
+
+
+def workload_config(args, world):
+    return {
+        "workload": f"MNIST-PVR IIT+behaviour+strict train step, ResNet-18 LL, synthetic 56x56 4-digit grids, "
+                    f"batch {args.batch} pairs/GPU ({'bf16' if args.dtype == 'bf16' else 'f32'} activations, "
+                    f"fp32 master weights/accumulation)",
+        "baseline_config": "configs[1]",
+        "batch_pairs_per_gpu": args.batch,
+        "global_batch_pairs": args.batch * world,
+        "image": "3x56x56",
+        "hook_point": HOOK,
+        "mode": "q",
+        "losses": ["iit", "strict", "behaviour"],
+        "optimizer": "Adam lr 1e-3, clip_grad_norm 1.0, one update per loss term",
+        "parallelism": f"dp{world}",
+        "l2": "no flush needed: per-step activation working set is several GB (>> 126 MB L2)",
+    }
+
+
+# --------------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the oracle's CPU restatement of the same step
+# --------------------------------------------------------------------------------------------------
+def cpu_step_factory(batch):
+    from oracle import restate as R
+    torch.set_num_threads(os.cpu_count() or 1)
+    oll = R.ResNet18Oracle(R.resnet18_state_dict(0))
+    strict = [(n, None) for n in R.ResNet18Oracle.conv_hook_points() if n != HOOK]
+    pair = R.OraclePair(oll, "pvr", R.pvr_corr("q", HOOK, 256, 4), lr=1e-3, weights=(1.0, 1.0, 1.0), strict_nodes=strict)
+    base, src = R.synthetic_pvr(batch, 11), R.synthetic_pvr(batch, 12)
+
+    def step():
+        return pair.train_step(base, src, strict=True)
+
+    return step
+
+
+def cpu_baseline(budget_s=20.0):
+    """Bounded sample of the same workload on the host cores (oracle port)."""
+    batch = 32
+    step = cpu_step_factory(batch)
+    step()  # warm-up
+    t0 = time.perf_counter()
+    n = 0
+    while True:
+        step()
+        n += 1
+        if time.perf_counter() - t0 > budget_s or n >= 50:
+            break
+    dt = time.perf_counter() - t0
+    return {"value": batch * n / dt, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"{n} steps of {batch} pairs (same step: IIT+strict+behaviour, fp32, torch-CPU eager restatement "
+                      f"oracle/restate.py), {dt:.1f} s"}
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    total = max(args.steps + args.warmup, 1)
+    # size the per-step sample so the whole run stays within ~2 minutes
+    probe = cpu_step_factory(16)
+    probe()
+    t0 = time.perf_counter()
+    probe()
+    per_pair = (time.perf_counter() - t0) / 16
+    batch = int(max(8, min(256, 120.0 / (total * per_pair))))
+    step = cpu_step_factory(batch)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    value = batch * args.steps / dt
+    cfg = workload_config(args, world)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(args.steps, 1), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                         "sample": f"{args.steps} steps of {batch} pairs each on the host cores (oracle/restate.py)"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------------
+# our arm
+# --------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop_evt = threading.Event()
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {
+                getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+                getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+                getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+                getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+            }
+            get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons")
+            while not self._stop_evt.is_set():
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                r = get_reasons(h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+                time.sleep(0.1)
+        except Exception as e:  # clocks are evidence, not a dependency
+            self.reasons.add(f"sampler_error:{type(e).__name__}")
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+class KernelTimer:
+    """CUDA-event timing of chosen C-ABI entry points inside the timed region (on the launching stream)."""
+
+    def __init__(self, names):
+        self.names = set(names)
+        self.records = {n: [] for n in names}
+        self.enabled = False
+
+    def install(self):
+        from iit_b200 import ops
+        inner = ops.call
+
+        def timed_call(name, *a):
+            if self.enabled and name in self.names:
+                s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                s.record()
+                inner(name, *a)
+                e.record()
+                self.records[name].append((s, e, conv_flops(a)))
+            else:
+                inner(name, *a)
+
+        ops.call = timed_call
+
+    def summary(self):
+        out = {}
+        for n, recs in self.records.items():
+            if recs:
+                ms = [s.elapsed_time(e) for s, e, _ in recs]
+                fl = [f for _, _, f in recs]
+                out[n] = {"launches": len(recs), "total_ms": float(sum(ms)), "avg_ms": float(np.mean(ms)),
+                          "tflops": float(sum(fl) / (sum(ms) * 1e-3) / 1e12)}
+        return out
+
+
+def conv_flops(call_args):
+    """Algorithmic FLOPs (2*MAC) of one convolution launch from its iit_conv_t descriptor."""
+    from iit_b200._lib import Conv
+    for a in call_args:
+        d = getattr(a, "_obj", None)
+        if isinstance(d, Conv):
+            return 2.0 * d.n * d.p * d.q * d.k * d.r * d.s * d.c
+    return 0.0
+
+
+def run_ours(args, rank, world, local):
+    from iit_b200 import _lib, dist as idist
+    from iit_b200.model_pairs import StrictIITModelPair
+    from iit_b200.tasks.mnist_pvr.get_alignment import get_alignment
+    from oracle import restate as R  # synthetic pair generators only (shared with the CPU arm)
+
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
+    B = args.batch
+    ll, hl, corr = get_alignment("mnist_pvr", {"input_shape": (1, 3, 56, 56)}, device=dev, dtype=dtype)
+    ll.load_state_dict(R.resnet18_state_dict(0))
+    pair = StrictIITModelPair(hl, ll, corr, training_args={"lr": 1e-3})
+    dp = idist.DataParallel()
+    if world > 1:
+        pair.dp = dp
+    opt = pair.make_optimizer()
+    ll.train()
+    # synthetic pairs: generated in chunks on the host, one shard per rank (different seeds per rank)
+    def gen(seed):
+        parts = [R.synthetic_pvr(min(512, B - i), seed * 1000 + i) for i in range(0, B, 512)]
+        return tuple(torch.cat([p[j] for p in parts]).pin_memory() for j in range(3))
+    base_h, src_h = gen(1 + 2 * rank), gen(2 + 2 * rank)
+    base_d = tuple(t.to(dev) for t in base_h)
+    src_d = tuple(t.to(dev) for t in src_h)
+    h2d = 2 * sum(t.numel() * t.element_size() for t in base_h)
+
+    def step_resident():
+        return pair.run_train_step(base_d, src_d, pair.loss_fn, opt)
+
+    def step_e2e():
+        b = tuple(t.to(dev, non_blocking=True) for t in base_h)
+        s = tuple(t.to(dev, non_blocking=True) for t in src_h)
+        return pair.run_train_step(b, s, pair.loss_fn, opt)  # returns host floats: the D2H read of the losses
+
+    timer = KernelTimer(["iit_conv2d_fprop", "iit_conv2d_dgrad", "iit_conv2d_wgrad"])
+    timer.install()
+
+    def timed(fn, steps):
+        dp.barrier()
+        torch.cuda.synchronize()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(steps):
+            m = fn()
+        e.record()
+        torch.cuda.synchronize()
+        dp.barrier()
+        return dp.max_over_ranks(s.elapsed_time(e) * 1e-3, dev), m
+
+    for _ in range(args.warmup):
+        step_resident()
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches0 = _lib.launch_count()
+    timer.enabled = True
+    sec, metrics = timed(step_resident, args.steps)
+    timer.enabled = False
+    launches = _lib.launch_count() - launches0
+    clocks = sampler.stop()
+    step_e2e()  # warm the copy path
+    sec_e2e, _ = timed(step_e2e, args.steps)
+
+    if rank != 0:
+        return
+    pk = peaks()
+    ks = timer.summary()
+    roof = None
+    if ks:
+        top = max(ks, key=lambda n: ks[n]["total_ms"])
+        k = ks[top]
+        roof = {"kernel": top, "bound": "tensor", "achieved": k["tflops"], "peak": pk["tflops"], "unit": "TFLOP/s",
+                "frac": k["tflops"] / pk["tflops"], "traffic": None, "peak_source": pk["src"] + " bf16 sustained",
+                "share_of_step": k["total_ms"] / (sec * 1e3), "launches": k["launches"], "avg_ms": k["avg_ms"]}
+    value = B * world * args.steps / sec
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * sec / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": args.dtype, "data": "synthetic", "config": workload_config(args, world),
+        "e2e": {"value": B * world * args.steps / sec_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": 3 * 4},
+        "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "kernels": ks,
+        "step_tflops": 11 * F56 * B * args.steps / sec / 1e12,
+        "last_step_metrics": metrics,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline()
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=4096)
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    from iit_b200 import dist as idist
+    rank, world, local = idist.init_from_env()
+    try:
+        run_ours(args, rank, world, local)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

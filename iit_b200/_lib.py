@@ -1,0 +1,109 @@
+"""ctypes binding of libiit_b200.so (the C-ABI declared in include/iit_b200.h).
+
+There is no fallback: if the shared library is missing or a symbol is absent, importing this module
+raises. Every entry point returns an int status; non-zero raises RuntimeError(iit_last_error()).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libiit_b200.so")
+
+IIT_MAX_RANK = 6
+IIT_F32, IIT_BF16 = 0, 1
+IOI_NODE_IDS = {None: 0, "all_nodes_hook": 1, "hook_duplicate": 2, "hook_s_inhibition": 3, "hook_name_mover": 4}
+
+
+class Box(C.Structure):
+    _fields_ = [
+        ("rank", C.c_int32),
+        ("elem_bytes", C.c_int32),
+        ("start", C.c_int64 * IIT_MAX_RANK),
+        ("extent", C.c_int64 * IIT_MAX_RANK),
+        ("dst_stride", C.c_int64 * IIT_MAX_RANK),
+        ("src_stride", C.c_int64 * IIT_MAX_RANK),
+    ]
+
+
+class Conv(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("n", "h", "w", "c", "k", "r", "s", "stride", "pad", "p", "q")]
+
+
+_vp, _i, _i64, _f, _d, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_double, C.c_size_t
+_BoxP, _ConvP = C.POINTER(Box), C.POINTER(Conv)
+
+# name -> argtypes (restype is int unless listed in _RESTYPES). Mirrors include/iit_b200.h one to one.
+SIGNATURES = {
+    "iit_patch_fwd": [_vp, _vp, _BoxP, _vp],
+    "iit_patch_bwd": [_vp, _BoxP, _vp],
+    "iit_capture_box": [_vp, _vp, _BoxP, _vp],
+    "iit_hl_pvr": [_vp, _vp, _i, _i64, _vp, _vp],
+    "iit_hl_ioi_last_argmax": [_vp, _vp, _i, _vp, _i, _i64, _i, _i64, _vp, _vp],
+    "iit_hl_ioi_dense": [_vp, _vp, _i, _vp, _i, _i64, _i, _i64, _vp, _vp],
+    "iit_ce_index_fwd": [_vp, _i, _i64, _i64, _i64, _vp, _vp, _vp, _vp],
+    "iit_ce_index_bwd": [_vp, _i, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _i64, _vp],
+    "iit_ce_prob_fwd": [_vp, _i, _i64, _i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp],
+    "iit_ce_prob_bwd": [_vp, _i, _i64, _i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _i64, _vp],
+    "iit_iia_count": [_vp, _i, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp],
+    "iit_conv2d_fprop": [_vp, _vp, _vp, _ConvP, _i, _vp, _vp, _vp],
+    "iit_conv2d_dgrad": [_vp, _vp, _vp, _ConvP, _i, _vp],
+    "iit_conv2d_wgrad_scratch_bytes": [_ConvP],
+    "iit_conv2d_wgrad": [_vp, _vp, _vp, _ConvP, _i, _vp, _sz, _vp],
+    "iit_filter_relayout": [_vp, C.POINTER(C.c_int64), _vp, _i, _i, _i, _i, _i, _i, _vp],
+    "iit_bn_stats": [_vp, _i, _i64, _i, _vp, _vp, _vp],
+    "iit_bn_finalize": [_vp, _vp, _i64, _i, _f, _f, _vp, _vp, _vp, _vp, _vp],
+    "iit_bn_eval_invstd": [_vp, _i, _f, _vp, _vp],
+    "iit_bn_act_fwd": [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _i, _vp],
+    "iit_bn_act_bwd_reduce": [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _i, _vp, _vp, _vp],
+    "iit_bn_act_bwd_apply": [_vp, _vp, _vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp],
+    "iit_relu_fwd": [_vp, _vp, _i, _i64, _vp],
+    "iit_relu_bwd": [_vp, _vp, _vp, _i, _i64, _vp],
+    "iit_add_relu_fwd": [_vp, _vp, _vp, _i, _i64, _i, _vp],
+    "iit_maxpool3x3s2_fwd": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp],
+    "iit_maxpool3x3s2_bwd": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp],
+    "iit_avgpool_fwd": [_vp, _vp, _i, _i, _i, _i, _vp],
+    "iit_avgpool_bwd": [_vp, _vp, _i, _i, _i, _i, _vp],
+    "iit_linear_fwd": [_vp, _vp, _vp, _vp, _i, _i, _i, _vp],
+    "iit_linear_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
+    "iit_sqnorm": [_vp, _i64, _vp, _vp],
+    "iit_adam_step": [_vp, _vp, _vp, _vp, _i64, _d, _d, _d, _d, _i64, _vp, _d, _vp],
+    "iit_last_error": [],
+    "iit_version": [],
+    "iit_launch_count": [],
+}
+_RESTYPES = {"iit_last_error": C.c_char_p, "iit_launch_count": C.c_ulonglong,
+             "iit_conv2d_wgrad_scratch_bytes": C.c_size_t}
+_NO_STATUS = set(_RESTYPES) | {"iit_version"}
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: the CUDA extension was not built. Run `python -m iit_b200.build` "
+            "(or __graft_entry__.build()). There is no CPU or PyTorch fallback for these kernels.")
+    lib = C.CDLL(LIB_PATH)
+    for name, argtypes in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the .so does not export a declared symbol
+        fn.argtypes = argtypes
+        fn.restype = _RESTYPES.get(name, C.c_int)
+    return lib
+
+
+lib = _load()
+
+
+def last_error() -> str:
+    return lib.iit_last_error().decode()
+
+
+def call(name: str, *args):
+    """Invoke a status-returning entry point; raise on failure."""
+    rc = getattr(lib, name)(*args)
+    if rc != 0:
+        raise RuntimeError(f"{name} failed (status {rc}): {last_error()}")
+
+
+def launch_count() -> int:
+    return int(lib.iit_launch_count())

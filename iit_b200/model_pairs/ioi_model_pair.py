@@ -1,0 +1,159 @@
+"""IOI pair: last-token loss, HL argmax -> one-hot target, per-token accuracy
+(API mirror of the reference's iit/model_pairs/ioi_model_pair.py:12-171).
+
+The reference materialises [B,S,V] tensors three times per loss (HL logits, one-hot HL target,
+one-hot labels) although only position -1 is ever consumed (ioi_model_pair.py:20,35). Here the
+training losses use (i) the sparse HL kernel that returns argmax(hl[:, -1]) directly, (ii) class-index
+cross-entropy on the last-position logits -- identical in value to cross-entropy against the
+one-hot probability target -- and (iii) labels reduced once per batch to their last-position ids.
+`do_intervention` still returns the dense tensors for callers that want them."""
+from __future__ import annotations
+
+import numpy as np
+import torch as t
+
+from iit_b200 import ops
+from iit_b200.model_pairs.iit_model_pair import _f32_ratio
+from iit_b200.model_pairs.strict_iit_model_pair import StrictIITModelPair
+from iit_b200.utils import index
+from iit_b200.utils.metric import MetricStore, MetricStoreCollection, MetricType, PerTokenMetricStore
+
+
+class IOI_ModelPair(StrictIITModelPair):
+    def __init__(self, hl_model, ll_model, corr, training_args=None):
+        super().__init__(hl_model, ll_model, corr, training_args=training_args)
+        defaults = {"next_token": False, "non_ioi_thresh": 0.65, "use_per_token_check": False,
+                    "labels_are_one_hot": True}
+        self.training_args = {**defaults, **self.training_args}
+        # the reference reads this from the DEFAULTS, not the merged args (ioi_model_pair.py:20): always False
+        self.next_token = defaults["next_token"]
+        self._label_cache = (None, None)
+
+    @property
+    def loss_fn(self):
+        def per_token_weighted_cross_entropy(output, target):
+            if output.dim() == 2:
+                return ops.cross_entropy(output, target)
+            if self.next_token:
+                raise NotImplementedError("next_token=True is unreachable in the reference (ioi_model_pair.py:20)")
+            tgt = target[:, -1] if target.dim() == 2 else target[:, -1, :]
+            return ops.cross_entropy(output[:, -1, :], tgt)
+
+        return per_token_weighted_cross_entropy
+
+    @staticmethod
+    def get_label_idxs():
+        return index.Ix[:, -1]
+
+    @staticmethod
+    def make_test_metrics():
+        return MetricStoreCollection([
+            MetricStore("val/iit_loss", MetricType.LOSS),
+            MetricStore("val/IIA", MetricType.ACCURACY),
+            MetricStore("val/accuracy", MetricType.ACCURACY),
+            PerTokenMetricStore("val/per_token_accuracy"),
+        ])
+
+    # ---- label handling ------------------------------------------------------------------------
+    def label_ids(self, base_y: t.Tensor) -> t.Tensor:
+        """[B,S] int64 ids from one-hot [B,S,V] labels (one argmax pass per batch tensor, memoised)."""
+        if base_y.dtype == t.int64:
+            return base_y
+        key = (base_y.data_ptr(), tuple(base_y.shape), base_y._version)
+        if self._label_cache[0] != key:
+            ids = ops.argmax_rows(base_y.reshape(-1, base_y.shape[-1])).view(base_y.shape[:-1])
+            self._label_cache = (key, ids)
+        return self._label_cache[1]
+
+    def _last_logits(self, fwd_hooks, x):
+        """LL run returning last-position logits [B,V] (unembeds one position when the model can)."""
+        if getattr(self.ll_model, "supports_last_pos", False):
+            return self.ll_model.run_with_hooks(x, fwd_hooks=fwd_hooks, last_pos_only=True)
+        return self.ll_model.run_with_hooks(x, fwd_hooks=fwd_hooks)[:, -1, :]
+
+    def _label_loss(self, logits_last, base_y):
+        if self.training_args["labels_are_one_hot"] or base_y.dtype == t.int64:
+            return ops.cross_entropy(logits_last, self.label_ids(base_y)[:, -1].contiguous())
+        return ops.cross_entropy(logits_last, base_y[:, -1, :])
+
+    # ---- losses ------------------------------------------------------------------------------
+    def get_IIT_loss_over_batch(self, base_input, ablation_input, hl_node, loss_fn):
+        hl_node = self._resolve_hl_node(hl_node)
+        ll_nodes = self.corr[hl_node]
+        if hasattr(self.hl_model, "interchange_last_argmax"):
+            hl_argmax = self.hl_model.interchange_last_argmax(base_input, ablation_input, hl_node)
+        else:
+            hl_output = self.hl_intervention(base_input, ablation_input, hl_node)
+            hl_argmax = ops.argmax_rows(hl_output[:, -1, :])
+        self.ll_source_run(ablation_input[0], ll_nodes)
+        last = self._last_logits([(n.name, self.make_ll_ablation_hook(n)) for n in ll_nodes], base_input[0])
+        # CE against one_hot(argmax).float() == CE against the index (reference :64-68)
+        return ops.cross_entropy(last, hl_argmax)
+
+    def get_strict_loss_over_batch(self, base_input, ablation_input, ll_node, loss_fn):
+        self.ll_source_run(ablation_input[0], [ll_node])
+        last = self._last_logits([(ll_node.name, self.make_ll_ablation_hook(ll_node))], base_input[0])
+        return self._label_loss(last, base_input[1])
+
+    def get_behaviour_loss_over_batch(self, base_input, loss_fn):
+        last = self._last_logits([], base_input[0])
+        return self._label_loss(last, base_input[1])
+
+    def run_eval_step(self, base_input, ablation_input, loss_fn):
+        hl_node = self._resolve_hl_node(self.sample_hl_name())
+        ll_nodes = self.corr[hl_node]
+        if hasattr(self.hl_model, "interchange_last_argmax"):
+            hl_argmax = self.hl_model.interchange_last_argmax(base_input, ablation_input, hl_node)
+        else:
+            hl_argmax = ops.argmax_rows(self.hl_intervention(base_input, ablation_input, hl_node)[:, -1, :])
+        self.ll_source_run(ablation_input[0], ll_nodes)
+        last = self._last_logits([(n.name, self.make_ll_ablation_hook(n)) for n in ll_nodes], base_input[0])
+        assert self.hl_model.is_categorical()
+        loss = ops.cross_entropy(last, hl_argmax)
+        counts, _ = ops.iia_count(last, hl_argmax)
+        # behavioural accuracy at every position (reference :94-102)
+        base_x, base_y, _ = base_input
+        output = self.ll_model(base_x)
+        b, s, v = output.shape
+        top1 = ops.argmax_rows(output.reshape(b * s, v)).view(b, s)
+        per_tok = (top1 == self.label_ids(base_y)).sum(dim=0)
+        host = t.cat([counts, per_tok]).tolist()
+        hits, n = host[0], host[1]
+        per_token_accuracy = (np.asarray(host[2:], dtype=np.float32) / np.float32(b)).astype(np.float32)
+        return {
+            "val/iit_loss": loss.item(),
+            "val/IIA": _f32_ratio(hits, n),
+            "val/accuracy": per_token_accuracy.mean().item() if self.next_token else per_token_accuracy[-1],
+            "val/per_token_accuracy": per_token_accuracy,
+        }
+
+    @staticmethod
+    def _check_early_stop_fn(test_metrics, verbose=False, non_ioi_thresh=0.65, use_per_token_check=False):
+        """Early stopping for IOI (reference :114-157)."""
+        say = print if verbose else (lambda *_: None)
+        for metric in test_metrics:
+            if metric.get_name() == "val/IIA" and metric.get_value() < 100:
+                say(f"IIA is not enough: {metric.get_value()}")
+                return False
+            if metric.get_name() == "val/per_token_accuracy":
+                acc = metric.get_value()
+                if acc[-1] < 1:
+                    say(f"per_token_acc at IOI index is not enough: {acc[-1]}")
+                    return False
+                if np.mean(acc) < non_ioi_thresh:
+                    say(f"mean per_token_acc is not enough: {np.mean(acc)}")
+                    return False
+                if use_per_token_check:
+                    for i in range(len(acc)):
+                        if i in [2, 4, 5, 8, 10, 13]:
+                            continue
+                        if acc[i] < non_ioi_thresh:
+                            say(f"per_token_acc at {i} is not enough: {acc[i]}")
+                            return False
+        return True
+
+    def _check_early_stop_condition(self, *args, **kwargs):
+        if not self.training_args["next_token"]:
+            return super()._check_early_stop_condition(*args, **kwargs)
+        return self._check_early_stop_fn(*args, **kwargs, non_ioi_thresh=self.training_args["non_ioi_thresh"],
+                                         use_per_token_check=self.training_args["use_per_token_check"])

@@ -1,0 +1,540 @@
+"""Torch-facing operators over the C-ABI (iit_b200/_lib.py -> libiit_b200.so).
+
+PyTorch is plumbing here: it owns device memory, streams and the autograd tape; every operator's
+arithmetic runs in the hand-written sm_100a kernels. There is no CPU / eager fallback: tensors that
+are not on a CUDA device raise.
+
+Layout convention for image activations: logical shape [N, C, H, W] with channels-last strides
+(physical NHWC), so the reference-facing view is NCHW while C is the contiguous dim in memory.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import Box, Conv, call
+
+_DT = {torch.float32: _lib.IIT_F32, torch.bfloat16: _lib.IIT_BF16}
+
+
+def _require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("iit_b200 kernels need CUDA tensors (no CPU fallback exists); got a tensor on "
+                               f"{t.device}")
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _dt(t: torch.Tensor) -> int:
+    try:
+        return _DT[t.dtype]
+    except KeyError:
+        raise TypeError(f"unsupported dtype {t.dtype}; expected float32 or bfloat16") from None
+
+
+def _is_cl(t: torch.Tensor) -> bool:
+    return t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last)
+
+
+def _cl(t: torch.Tensor) -> torch.Tensor:
+    """channels-last contiguous (no copy when already so)."""
+    return t if _is_cl(t) else t.contiguous(memory_format=torch.channels_last)
+
+
+def empty_cl(n, c, h, w, dtype, device):
+    return torch.empty((n, c, h, w), dtype=dtype, device=device, memory_format=torch.channels_last)
+
+
+# =================================================================================================
+# (a) patch
+# =================================================================================================
+def make_box(index, dst: torch.Tensor, src: Optional[torch.Tensor]) -> Optional[Box]:
+    """Box descriptor for `dst[index] = src[index]` from a TorchIndex and the tensors' strides."""
+    spans = index.box(tuple(dst.shape))
+    if spans is None:
+        return None
+    if dst.dim() > _lib.IIT_MAX_RANK:
+        raise ValueError(f"rank {dst.dim()} exceeds {_lib.IIT_MAX_RANK}")
+    b = Box()
+    b.rank = dst.dim()
+    b.elem_bytes = dst.element_size()
+    for d, (start, extent) in enumerate(spans):
+        b.start[d], b.extent[d] = start, extent
+        b.dst_stride[d] = dst.stride(d)
+        b.src_stride[d] = src.stride(d) if src is not None else dst.stride(d)
+    return b
+
+
+def box_bytes(index, t: torch.Tensor) -> int:
+    spans = index.box(tuple(t.shape))
+    n = 1
+    for _, e in spans:
+        n *= e
+    return n * t.element_size()
+
+
+def patch_(dst: torch.Tensor, src: torch.Tensor, index) -> torch.Tensor:
+    """In place, no autograd: dst[index] = src[index]."""
+    _require_cuda(dst, src)
+    if dst.shape != src.shape or dst.dtype != src.dtype:
+        raise ValueError(f"patch: shape/dtype mismatch {tuple(dst.shape)} {dst.dtype} vs {tuple(src.shape)} {src.dtype}")
+    box = make_box(index, dst, src)
+    if box is None:  # list-of-ints index: no box form -> advanced-indexing gather/scatter by torch
+        dst[index.as_index] = src[index.as_index]
+        return dst
+    call("iit_patch_fwd", _p(dst), _p(src), C.byref(box), _stream())
+    return dst
+
+
+def zero_box_(grad: torch.Tensor, index) -> torch.Tensor:
+    _require_cuda(grad)
+    box = make_box(index, grad, None)
+    if box is None:
+        grad[index.as_index] = 0
+        return grad
+    call("iit_patch_bwd", _p(grad), C.byref(box), _stream())
+    return grad
+
+
+def capture_box(src: torch.Tensor, index) -> torch.Tensor:
+    """Compact copy of src[index] (box order), for caches that must outlive the source tensor."""
+    _require_cuda(src)
+    spans = index.box(tuple(src.shape))
+    if spans is None:
+        return src[index.as_index].contiguous()
+    out = torch.empty([e for _, e in spans], dtype=src.dtype, device=src.device)
+    box = make_box(index, src, src)
+    call("iit_capture_box", _p(out), _p(src), C.byref(box), _stream())
+    return out
+
+
+class _PatchFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, act, cached, index, inplace):
+        ctx.index = index
+        ctx.whole = index.is_whole()
+        if inplace and not (act.is_leaf and act.requires_grad):
+            out = act
+            ctx.mark_dirty(act)
+        else:
+            out = act.clone(memory_format=torch.preserve_format)
+        patch_(out, cached, index)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        if ctx.whole:
+            return None, None, None, None  # every element was overwritten by a constant
+        g = g.clone(memory_format=torch.preserve_format)
+        zero_box_(g, ctx.index)
+        return g, None, None, None
+
+
+def patch(act: torch.Tensor, cached: torch.Tensor, index, inplace: bool = True) -> torch.Tensor:
+    """`out = act.clone(); out[index] = cached[index]` with the CopySlices gradient (zero inside the
+    box, identity outside). With inplace=True `act` itself is overwritten (legal for a hook-point
+    value that no earlier op saved for backward)."""
+    return _PatchFn.apply(act, cached.detach(), index, inplace)
+
+
+# =================================================================================================
+# (c) high-level models + losses
+# =================================================================================================
+def hl_pvr(base_vars: torch.Tensor, src_vars: Optional[torch.Tensor], var: int) -> torch.Tensor:
+    _require_cuda(base_vars, src_vars)
+    bv = base_vars.contiguous()
+    sv = src_vars.contiguous() if src_vars is not None else None
+    if bv.dtype != torch.int64 or bv.dim() != 2 or bv.shape[1] != 4:
+        raise ValueError("hl_pvr: intermediate vars must be int64 [B,4]")
+    out = torch.empty(bv.shape[0], dtype=torch.int64, device=bv.device)
+    call("iit_hl_pvr", _p(bv), _p(sv), int(var), bv.shape[0], _p(out), _stream())
+    return out
+
+
+def hl_ioi_last_argmax(base_tok, src_tok, node: Optional[str], names, d_vocab: int) -> torch.Tensor:
+    _require_cuda(base_tok, src_tok, names)
+    bt = base_tok.contiguous()
+    st = src_tok.contiguous() if src_tok is not None else None
+    out = torch.empty(bt.shape[0], dtype=torch.int64, device=bt.device)
+    call("iit_hl_ioi_last_argmax", _p(bt), _p(st), _lib.IOI_NODE_IDS[node], _p(names), int(names.numel()),
+         bt.shape[0], bt.shape[1], int(d_vocab), _p(out), _stream())
+    return out
+
+
+def hl_ioi_dense(base_tok, src_tok, node: Optional[str], names, d_vocab: int) -> torch.Tensor:
+    _require_cuda(base_tok, src_tok, names)
+    bt = base_tok.contiguous()
+    st = src_tok.contiguous() if src_tok is not None else None
+    out = torch.empty((bt.shape[0], bt.shape[1], d_vocab), dtype=torch.float32, device=bt.device)
+    call("iit_hl_ioi_dense", _p(bt), _p(st), _lib.IOI_NODE_IDS[node], _p(names), int(names.numel()),
+         bt.shape[0], bt.shape[1], int(d_vocab), _p(out), _stream())
+    return out
+
+
+def _rows_view(logits: torch.Tensor):
+    """[rows, classes] with unit class stride and a single row stride, without copying if possible."""
+    if logits.dim() != 2:
+        raise ValueError("expected 2-D logits [rows, classes]")
+    if logits.stride(1) != 1:
+        logits = logits.contiguous()
+    return logits, logits.stride(0)
+
+
+class _CEIndexFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, target):
+        _require_cuda(logits, target)
+        lg, rs = _rows_view(logits)
+        tgt = target.contiguous()
+        rows, classes = lg.shape
+        lse = torch.empty(rows, dtype=torch.float32, device=lg.device)
+        loss = torch.zeros((), dtype=torch.float32, device=lg.device)
+        call("iit_ce_index_fwd", _p(lg), _dt(lg), rows, classes, rs, _p(tgt), _p(lse), _p(loss), _stream())
+        ctx.save_for_backward(lg, tgt, lse)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        lg, tgt, lse = ctx.saved_tensors
+        rows, classes = lg.shape
+        d = torch.empty((rows, classes), dtype=lg.dtype, device=lg.device)
+        g = g.to(torch.float32).contiguous()
+        call("iit_ce_index_bwd", _p(lg), _dt(lg), rows, classes, lg.stride(0), _p(tgt), _p(lse), _p(g), _p(d), classes,
+             _stream())
+        return d, None
+
+
+class _CEProbFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, prob):
+        _require_cuda(logits, prob)
+        lg, rs = _rows_view(logits)
+        pr = prob if (prob.dtype == torch.float32 and prob.stride(1) == 1) else prob.float().contiguous()
+        rows, classes = lg.shape
+        lse = torch.empty(rows, dtype=torch.float32, device=lg.device)
+        psum = torch.empty(2 * rows, dtype=torch.float32, device=lg.device)  # [psum | per-row nll]
+        loss = torch.zeros((), dtype=torch.float32, device=lg.device)
+        call("iit_ce_prob_fwd", _p(lg), _dt(lg), rows, classes, rs, _p(pr), pr.stride(0), _p(lse), _p(psum), _p(loss),
+             _stream())
+        ctx.save_for_backward(lg, pr, lse, psum)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        lg, pr, lse, psum = ctx.saved_tensors
+        rows, classes = lg.shape
+        d = torch.empty((rows, classes), dtype=lg.dtype, device=lg.device)
+        g = g.to(torch.float32).contiguous()
+        call("iit_ce_prob_bwd", _p(lg), _dt(lg), rows, classes, lg.stride(0), _p(pr), pr.stride(0), _p(lse), _p(psum),
+             _p(g), _p(d), classes, _stream())
+        return d, None
+
+
+def cross_entropy(logits: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+    """F.cross_entropy(logits, target) with mean reduction for 2-D logits; `target` is class indices
+    (int64 [rows]) or probabilities (float [rows, classes])."""
+    if target.dtype == torch.int64 and target.dim() == 1:
+        return _CEIndexFn.apply(logits, target)
+    if target.is_floating_point() and target.shape == logits.shape:
+        return _CEProbFn.apply(logits, target)
+    raise ValueError(f"cross_entropy: unsupported target {target.dtype} {tuple(target.shape)} for logits "
+                     f"{tuple(logits.shape)}")
+
+
+# =================================================================================================
+# (d) IIA
+# =================================================================================================
+def iia_count(logits: torch.Tensor, hl: Optional[torch.Tensor], changed: Optional[torch.Tensor] = None,
+              counts: Optional[torch.Tensor] = None, want_top1: bool = False):
+    """Accumulates (hits, denominator) into `counts` (int64[2], created if None); optionally returns
+    top-1 indices. No host sync."""
+    _require_cuda(logits, hl, changed, counts)
+    lg, rs = _rows_view(logits.detach())
+    rows, classes = lg.shape
+    if counts is None and hl is not None:
+        counts = torch.zeros(2, dtype=torch.int64, device=lg.device)
+    top1 = torch.empty(rows, dtype=torch.int64, device=lg.device) if want_top1 else None
+    hl_c = hl.contiguous() if hl is not None else None
+    if hl_c is not None and (hl_c.dtype != torch.int64 or hl_c.numel() != rows):
+        raise ValueError("iia_count: hl must be int64 with one entry per row")
+    ch = None
+    if changed is not None:
+        ch = changed.to(torch.uint8).contiguous() if changed.dtype != torch.uint8 else changed.contiguous()
+    call("iit_iia_count", _p(lg), _dt(lg), rows, classes, rs, _p(hl_c), _p(ch), _p(top1), _p(counts), _stream())
+    return counts, top1
+
+
+def argmax_rows(logits: torch.Tensor) -> torch.Tensor:
+    return iia_count(logits, None, want_top1=True)[1]
+
+
+# =================================================================================================
+# (b) ResNet layers
+# =================================================================================================
+def _conv_desc(x, k, r, s, stride, pad) -> Conv:
+    n, c, h, w = x.shape
+    d = Conv()
+    d.n, d.h, d.w, d.c, d.k, d.r, d.s, d.stride, d.pad = n, h, w, c, k, r, s, stride, pad
+    d.p = (h + 2 * pad - r) // stride + 1
+    d.q = (w + 2 * pad - s) // stride + 1
+    return d
+
+
+def filter_relayout(weight: torch.Tensor, to_crsk: bool, dtype) -> torch.Tensor:
+    """fp32 master filter [K,C,R,S] (any strides) -> dense KRSC or CRSK buffer in `dtype`."""
+    _require_cuda(weight)
+    k, c, r, s = weight.shape
+    out = torch.empty(k * c * r * s, dtype=dtype, device=weight.device)
+    strides = (C.c_int64 * 4)(*weight.stride())
+    call("iit_filter_relayout", _p(weight), strides, _p(out), k, c, r, s, int(to_crsk), _DT[dtype], _stream())
+    return out
+
+
+class _ConvFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums):
+        _require_cuda(x, weight)
+        x = _cl(x)
+        k, c, r, s = weight.shape
+        d = _conv_desc(x, k, r, s, stride, pad)
+        y = empty_cl(d.n, k, d.p, d.q, x.dtype, x.device)
+        s0 = s1 = None
+        if bn_sums is not None:
+            s0, s1 = bn_sums[0], bn_sums[1]
+        call("iit_conv2d_fprop", _p(x), _p(w_krsc), _p(y), C.byref(d), _dt(x), _p(s0), _p(s1), _stream())
+        ctx.save_for_backward(x, weight)
+        ctx.d, ctx.w_crsk_fn = d, w_crsk_fn
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        d = ctx.d
+        dy = _cl(dy)
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = empty_cl(d.n, d.c, d.h, d.w, x.dtype, x.device)
+            call("iit_conv2d_dgrad", _p(dy), _p(ctx.w_crsk_fn()), _p(dx), C.byref(d), _dt(x), _stream())
+        if ctx.needs_input_grad[1]:
+            dwb = torch.empty((d.k, d.r, d.s, d.c), dtype=torch.float32, device=x.device)
+            need = int(_lib.lib.iit_conv2d_wgrad_scratch_bytes(C.byref(d)))
+            scratch = torch.empty(need, dtype=torch.uint8, device=x.device) if need else None
+            call("iit_conv2d_wgrad", _p(dy), _p(x), _p(dwb), C.byref(d), _dt(x), _p(scratch), need, _stream())
+            dw = dwb.permute(0, 3, 1, 2)  # [K,C,R,S] view with channels-last strides, like the parameter
+        return dx, dw, None, None, None, None, None
+
+
+def conv2d(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums=None):
+    return _ConvFn.apply(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums)
+
+
+def new_bn_sums(c: int, device) -> torch.Tensor:
+    return torch.zeros((2, c), dtype=torch.float64, device=device)
+
+
+class _BNActFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums):
+        _require_cuda(x, gamma, beta, residual)
+        x = _cl(x)
+        n, c, h, w = x.shape
+        rows = n * h * w
+        st = _stream()
+        if residual is not None:
+            residual = _cl(residual)
+        if training:
+            if sums is None:
+                sums = new_bn_sums(c, x.device)
+                call("iit_bn_stats", _p(x), _dt(x), rows, c, _p(sums[0]), _p(sums[1]), st)
+            mean = torch.empty(c, dtype=torch.float32, device=x.device)
+            invstd = torch.empty(c, dtype=torch.float32, device=x.device)
+            call("iit_bn_finalize", _p(sums[0]), _p(sums[1]), rows, c, float(eps), float(momentum), _p(mean), _p(invstd),
+                 _p(running_mean), _p(running_var), st)
+        else:
+            mean = running_mean
+            invstd = torch.empty(c, dtype=torch.float32, device=x.device)
+            call("iit_bn_eval_invstd", _p(running_var), c, float(eps), _p(invstd), st)
+        y = torch.empty_like(x)
+        call("iit_bn_act_fwd", _p(x), _p(residual), _p(y), _dt(x), rows, c, _p(mean), _p(invstd), _p(gamma), _p(beta),
+             int(relu), st)
+        ctx.save_for_backward(x, y if relu else None, gamma, mean, invstd)
+        ctx.relu, ctx.training, ctx.has_res = relu, training, residual is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y, gamma, mean, invstd = ctx.saved_tensors
+        dy = _cl(dy)
+        n, c, h, w = x.shape
+        rows = n * h * w
+        st = _stream()
+        red = torch.zeros((2, c), dtype=torch.float64, device=x.device)
+        call("iit_bn_act_bwd_reduce", _p(dy), _p(y), _p(x), _dt(x), rows, c, _p(mean), _p(invstd), int(ctx.relu),
+             _p(red[0]), _p(red[1]), st)
+        dx = torch.empty_like(x)
+        dres = torch.empty_like(x) if ctx.has_res else None
+        # eval mode: statistics are constants, so the two correction terms vanish
+        corr = red if ctx.training else torch.zeros_like(red)
+        call("iit_bn_act_bwd_apply", _p(dy), _p(y), _p(x), _p(dx), _p(dres), _dt(x), rows, c, _p(mean), _p(invstd),
+             _p(gamma), _p(corr[0]), _p(corr[1]), int(ctx.relu), st)
+        return dx, red[0].float(), red[1].float(), dres, None, None, None, None, None, None, None
+
+
+def bn_act(x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums=None):
+    return _BNActFn.apply(x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums)
+
+
+class _ReluFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        _require_cuda(x)
+        xc = x if (x.is_contiguous() or _is_cl(x)) else x.contiguous()
+        y = torch.empty_like(xc)
+        call("iit_relu_fwd", _p(xc), _p(y), _dt(xc), xc.numel(), _stream())
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        dy = dy.contiguous(memory_format=torch.channels_last) if _is_cl(y) else dy.contiguous()
+        dx = torch.empty_like(y)
+        call("iit_relu_bwd", _p(dy), _p(y), _p(dx), _dt(y), y.numel(), _stream())
+        return dx
+
+
+def relu(x):
+    return _ReluFn.apply(x)
+
+
+class _AddReluFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, a, b, do_relu):
+        _require_cuda(a, b)
+        a, b = _cl(a), _cl(b)
+        y = torch.empty_like(a)
+        call("iit_add_relu_fwd", _p(a), _p(b), _p(y), _dt(a), a.numel(), int(do_relu), _stream())
+        ctx.do_relu = do_relu
+        ctx.save_for_backward(y if do_relu else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        if not ctx.do_relu:
+            return dy, dy, None
+        dy = _cl(dy)
+        dx = torch.empty_like(y)
+        call("iit_relu_bwd", _p(dy), _p(y), _p(dx), _dt(y), y.numel(), _stream())
+        return dx, dx, None
+
+
+def add_relu(a, b, do_relu=True):
+    return _AddReluFn.apply(a, b, do_relu)
+
+
+class _MaxPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        _require_cuda(x)
+        x = _cl(x)
+        n, c, h, w = x.shape
+        p, q = (h + 2 - 3) // 2 + 1, (w + 2 - 3) // 2 + 1
+        y = empty_cl(n, c, p, q, x.dtype, x.device)
+        idx = torch.empty((n, p, q, c), dtype=torch.int8, device=x.device)
+        call("iit_maxpool3x3s2_fwd", _p(x), _p(y), _p(idx), _dt(x), n, h, w, c, _stream())
+        ctx.save_for_backward(idx)
+        ctx.shape = (n, c, h, w)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        n, c, h, w = ctx.shape
+        dy = _cl(dy)
+        dx = empty_cl(n, c, h, w, dy.dtype, dy.device)
+        call("iit_maxpool3x3s2_bwd", _p(dy), _p(idx), _p(dx), _dt(dy), n, h, w, c, _stream())
+        return dx
+
+
+def maxpool3x3s2(x):
+    return _MaxPoolFn.apply(x)
+
+
+class _AvgPoolFn(torch.autograd.Function):
+    """AdaptiveAvgPool2d(1): [N,C,H,W] -> fp32 [N,C,1,1]."""
+
+    @staticmethod
+    def forward(ctx, x):
+        _require_cuda(x)
+        x = _cl(x)
+        n, c, h, w = x.shape
+        y = torch.empty((n, c), dtype=torch.float32, device=x.device)
+        call("iit_avgpool_fwd", _p(x), _p(y), _dt(x), n, h * w, c, _stream())
+        ctx.shape, ctx.dtype = (n, c, h, w), x.dtype
+        return y.view(n, c, 1, 1)
+
+    @staticmethod
+    def backward(ctx, dy):
+        n, c, h, w = ctx.shape
+        dy = dy.reshape(n, c).float().contiguous()
+        dx = empty_cl(n, c, h, w, ctx.dtype, dy.device)
+        call("iit_avgpool_bwd", _p(dy), _p(dx), _DT[ctx.dtype], n, h * w, c, _stream())
+        return dx
+
+
+def avgpool(x):
+    return _AvgPoolFn.apply(x)
+
+
+class _LinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b):
+        _require_cuda(x, w, b)
+        x = x.float().contiguous()
+        wc = w.contiguous()
+        n, i = x.shape
+        o = wc.shape[0]
+        y = torch.empty((n, o), dtype=torch.float32, device=x.device)
+        call("iit_linear_fwd", _p(x), _p(wc), _p(b), _p(y), n, i, o, _stream())
+        ctx.save_for_backward(x, wc)
+        ctx.has_bias = b is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        dy = dy.float().contiguous()
+        n, i = x.shape
+        o = w.shape[0]
+        dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        dw = torch.empty_like(w)
+        db = torch.empty(o, dtype=torch.float32, device=x.device) if ctx.has_bias else None
+        call("iit_linear_bwd", _p(x), _p(w), _p(dy), _p(dx), _p(dw), _p(db), n, i, o, _stream())
+        return dx, dw, db
+
+
+def linear(x, w, b):
+    return _LinearFn.apply(x, w, b)
+
+
+# =================================================================================================
+# optimiser pieces
+# =================================================================================================
+def sqnorm_(g_flat: torch.Tensor, out: torch.Tensor):
+    call("iit_sqnorm", _p(g_flat), g_flat.numel(), _p(out), _stream())
+
+
+def adam_step_(p, g, m, v, lr, beta1, beta2, eps, step, sqnorm, max_norm):
+    call("iit_adam_step", _p(p), _p(g), _p(m), _p(v), p.numel(), float(lr), float(beta1), float(beta2), float(eps),
+         int(step), _p(sqnorm), float(max_norm or 0.0), _stream())

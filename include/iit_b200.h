@@ -1,0 +1,208 @@
+/*
+ * iit_b200 -- C-ABI of the B200 (sm_100a) kernels behind the interchange-intervention step.
+ *
+ * Plain `extern "C"`: raw device pointers, POD descriptors, a cudaStream_t passed as void*.
+ * No torch types. Every entry point returns 0 on success; on failure it returns non-zero and
+ * iit_last_error() holds a message (thread-local). Unless a comment says otherwise, no entry
+ * point allocates, frees, retains pointers or synchronises: the caller owns every buffer
+ * (inputs, outputs, workspaces) and the kernels are enqueued on the given stream.
+ *
+ * The reference (tkwa/iit) is pure Python over PyTorch eager ops and has no FFI of its own; each
+ * entry point below names the reference lines whose arithmetic it replaces (paths relative to
+ * the reference root). INTEGRATION.md shows the ctypes binding a maintainer would add.
+ */
+#ifndef IIT_B200_H
+#define IIT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IIT_MAX_RANK 6
+
+enum { IIT_F32 = 0, IIT_BF16 = 1 };
+
+/* ------------------------------------------------------------------------------------------ */
+/* library                                                                                     */
+/* ------------------------------------------------------------------------------------------ */
+const char* iit_last_error(void);
+int iit_version(void);
+/* number of kernels this library has enqueued since load (bench.py's gpu_launches) */
+unsigned long long iit_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------ */
+/* (a) patch: TorchIndex box gather/scatter                                                     */
+/* A box is what `TorchIndex.as_index` (iit/utils/index.py:36-38) selects when every entry is   */
+/* None, an int or a step-less slice: per dim a [start, start+extent) range. Strides are in     */
+/* elements, so NCHW-shaped views of channels-last memory patch with contiguous C runs.          */
+/* ------------------------------------------------------------------------------------------ */
+typedef struct {
+  int32_t rank;
+  int32_t elem_bytes;               /* 2, 4 or 8 */
+  int64_t start[IIT_MAX_RANK];
+  int64_t extent[IIT_MAX_RANK];
+  int64_t dst_stride[IIT_MAX_RANK];
+  int64_t src_stride[IIT_MAX_RANK];
+} iit_box_t;
+
+/* dst[box] = src[box], in place on dst.
+ * Replaces `out = hook_point_out.clone(); out[idx] = cache[name][idx]`
+ * (iit/model_pairs/base_model_pair.py:157-161, and the HL twin at :125-137). */
+int iit_patch_fwd(void* dst, const void* src, const iit_box_t* box, void* stream);
+
+/* grad[box] = 0, in place: the autograd CopySlices backward of the assignment above
+ * (the patched values are constants; base_model_pair.py:160 under autograd). */
+int iit_patch_bwd(void* grad, const iit_box_t* box, void* stream);
+
+/* dst_compact = src[box] packed densely in box order (source-run capture of only the
+ * Correspondence's slice; replaces caching every hook point, base_model_pair.py:86). */
+int iit_capture_box(void* dst_compact, const void* src, const iit_box_t* box, void* stream);
+
+/* ------------------------------------------------------------------------------------------ */
+/* (c) high-level models and losses                                                             */
+/* ------------------------------------------------------------------------------------------ */
+/* MNIST-PVR HL with one variable interchanged: v = base_vars; v[:, var] = src_vars[:, var]
+ * (var < 0: no interchange); hl_out[b] = (tr,bl,br)[class_map[tl]-1].
+ * Replaces MNIST_PVR_HL.forward + hl_ablation_hook (iit/tasks/mnist_pvr/pvr_hl.py:44-56,
+ * base_model_pair.py:80,89-91,120-142) and the leaky variant (pvr_check_leaky_hl.py:45-66). */
+int iit_hl_pvr(const int64_t* base_vars, const int64_t* src_vars, int var, int64_t batch,
+               int64_t* hl_out, void* stream);
+
+enum { IIT_IOI_NONE = 0, IIT_IOI_ALL_NODES = 1, IIT_IOI_DUPLICATE = 2, IIT_IOI_S_INHIBITION = 3,
+       IIT_IOI_NAME_MOVER = 4 };
+
+/* IOI HL with one hook interchanged, evaluated sparsely at the LAST position:
+ * out_argmax[b] = argmax_v logits[b, S-1, v] with first-index tie-breaking (torch.argmax).
+ * Replaces IOI_HL.forward + heads (iit/tasks/ioi/ioi_hl.py:16-24,37-46,54-68,102-130) and the
+ * argmax at ioi_model_pair.py:64,82 without materialising [B,S,V]. names must be sorted. */
+int iit_hl_ioi_last_argmax(const int64_t* base_tok, const int64_t* src_tok, int node,
+                           const int64_t* names, int n_names, int64_t batch, int seq, int64_t d_vocab,
+                           int64_t* out_argmax, void* stream);
+
+/* Dense IOI HL output [B,S,V] fp32 (API compatibility for do_intervention's hl_output). */
+int iit_hl_ioi_dense(const int64_t* base_tok, const int64_t* src_tok, int node,
+                     const int64_t* names, int n_names, int64_t batch, int seq, int64_t d_vocab,
+                     float* out, void* stream);
+
+/* Cross-entropy over rows with a class-index target, mean over rows:
+ *   row_lse[r] = logsumexp(logits[r,:]);  loss += (row_lse[r] - logits[r,target[r]]) / rows
+ * loss must be zeroed by the caller (one float). Replaces t.nn.CrossEntropyLoss()(ll, hl)
+ * (iit_behavior_model_pair.py:20-30, base_model_pair.py:173) and, with target = argmax of the
+ * one-hot, CE with a probability target (ioi_model_pair.py:27-35,64-68). */
+int iit_ce_index_fwd(const void* logits, int dtype, int64_t rows, int64_t classes, int64_t row_stride,
+                     const int64_t* target, float* row_lse, float* loss, void* stream);
+
+/* dlogits[r,c] = (exp(logits[r,c]-row_lse[r]) - [c==target[r]]) * (*grad_out) / rows */
+int iit_ce_index_bwd(const void* logits, int dtype, int64_t rows, int64_t classes, int64_t row_stride,
+                     const int64_t* target, const float* row_lse, const float* grad_out,
+                     void* dlogits, int64_t d_row_stride, void* stream);
+
+/* Same with a dense probability target prob[r,c] (fp32), as F.cross_entropy does for float
+ * targets (ioi_model_pair.py:29,35): loss_r = lse_r * sum_c p - sum_c p*l. */
+int iit_ce_prob_fwd(const void* logits, int dtype, int64_t rows, int64_t classes, int64_t row_stride,
+                    const float* prob, int64_t p_row_stride, float* row_lse, float* row_psum,
+                    float* loss, void* stream);
+int iit_ce_prob_bwd(const void* logits, int dtype, int64_t rows, int64_t classes, int64_t row_stride,
+                    const float* prob, int64_t p_row_stride, const float* row_lse, const float* row_psum,
+                    const float* grad_out, void* dlogits, int64_t d_row_stride, void* stream);
+
+/* ------------------------------------------------------------------------------------------ */
+/* (d) interchange-intervention accuracy                                                        */
+/* ------------------------------------------------------------------------------------------ */
+/* top1[r] = argmax_c logits[r,c] (first maximal index; NaN counts as maximal, as torch.argmax);
+ * counts[0] += #{r : top1[r]==hl[r] and (changed==NULL or changed[r])}
+ * counts[1] += #{r : changed==NULL or changed[r]}
+ * top1 may be NULL; hl may be NULL (then only top1 is written). counts is accumulated, not
+ * cleared. Replaces argmax/eq/float().mean() (iit_behavior_model_pair.py:118-120,
+ * ioi_model_pair.py:90-92) and the masked reduction of eval_causality.py:74-83. */
+int iit_iia_count(const void* logits, int dtype, int64_t rows, int64_t classes, int64_t row_stride,
+                  const int64_t* hl, const uint8_t* changed, int64_t* top1,
+                  unsigned long long* counts, void* stream);
+
+/* ------------------------------------------------------------------------------------------ */
+/* (b) low-level ResNet-18 layers, NHWC ("channels-last") activations                           */
+/* ------------------------------------------------------------------------------------------ */
+typedef struct {
+  int32_t n, h, w, c;      /* input  [n,h,w,c]            */
+  int32_t k, r, s;         /* filter [k,r,s,c] (KRSC)     */
+  int32_t stride, pad;
+  int32_t p, q;            /* output [n,p,q,k]            */
+} iit_conv_t;
+
+/* y = conv(x, w). Replaces torch's cuDNN conv for every Conv2d of torchvision resnet18
+ * (iit/tasks/mnist_pvr/get_alignment.py:11-15). If bn_sum/bn_sqsum are non-NULL (fp64 [k],
+ * zeroed by the caller) the epilogue also accumulates per-channel sum and sum of squares of y
+ * for the BatchNorm that follows. */
+int iit_conv2d_fprop(const void* x, const void* w, void* y, const iit_conv_t* d, int dtype,
+                     double* bn_sum, double* bn_sqsum, void* stream);
+/* dx = conv_transpose(dy, w);  w_crsk is the filter re-laid out as [c,r,s,k]. */
+int iit_conv2d_dgrad(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, int dtype,
+                     void* stream);
+/* dw[k,r,s,c] (fp32) = sum over pixels dy * x. scratch: iit_conv2d_wgrad_scratch_bytes(). */
+size_t iit_conv2d_wgrad_scratch_bytes(const iit_conv_t* d);
+int iit_conv2d_wgrad(const void* dy, const void* x, float* dw, const iit_conv_t* d, int dtype,
+                     void* scratch, size_t scratch_bytes, void* stream);
+/* filter re-layout: fp32 master filter addressed as [k,c,r,s] through the 4 element strides given
+ * (any memory format) -> dense KRSC (to_crsk=0) or CRSK (to_crsk=1) in `dtype`. */
+int iit_filter_relayout(const float* w, const int64_t* strides_kcrs, void* w_out, int k, int c, int r,
+                        int s, int to_crsk, int dtype, void* stream);
+
+/* BatchNorm2d (training): per-channel statistics over n*h*w rows of an NHWC tensor.
+ * sum/sqsum fp64 [c] zeroed by caller. Replaces F.batch_norm's statistics pass. */
+int iit_bn_stats(const void* x, int dtype, int64_t rows, int c, double* sum, double* sqsum, void* stream);
+/* From sums: mean, invstd (biased var + eps), and running-stat update with momentum and the
+ * unbiased variance (torch.nn.BatchNorm2d semantics). running_* may be NULL (no update). */
+int iit_bn_finalize(const double* sum, const double* sqsum, int64_t rows, int c, float eps, float momentum,
+                    float* mean, float* invstd, float* running_mean, float* running_var, void* stream);
+/* y = act((x-mean)*invstd*gamma+beta (+ residual)); act = relu if relu!=0. In eval mode pass
+ * mean=running_mean and invstd=1/sqrt(running_var+eps) (iit_bn_eval_invstd). */
+int iit_bn_eval_invstd(const float* running_var, int c, float eps, float* invstd, void* stream);
+int iit_bn_act_fwd(const void* x, const void* residual, void* y, int dtype, int64_t rows, int c,
+                   const float* mean, const float* invstd, const float* gamma, const float* beta,
+                   int relu, void* stream);
+/* Backward of the above in training mode. Pass 1 reduces dgamma = sum(g*xhat), dbeta = sum(g)
+ * with g = dy * [y>0 if relu]; pass 2 writes dx (and dresidual = g when dres != NULL).
+ * dgamma/dbeta fp64 [c] zeroed by the caller. */
+int iit_bn_act_bwd_reduce(const void* dy, const void* y, const void* x, int dtype, int64_t rows, int c,
+                          const float* mean, const float* invstd, int relu,
+                          double* dgamma, double* dbeta, void* stream);
+int iit_bn_act_bwd_apply(const void* dy, const void* y, const void* x, void* dx, void* dres, int dtype,
+                         int64_t rows, int c, const float* mean, const float* invstd, const float* gamma,
+                         const double* dgamma, const double* dbeta, int relu, void* stream);
+int iit_relu_fwd(const void* x, void* y, int dtype, int64_t n, void* stream);
+int iit_relu_bwd(const void* dy, const void* y, void* dx, int dtype, int64_t n, void* stream);
+int iit_add_relu_fwd(const void* a, const void* b, void* y, int dtype, int64_t n, int relu, void* stream);
+
+/* MaxPool2d(3, stride 2, pad 1), NHWC. idx (int8, window slot) is saved for the backward. */
+int iit_maxpool3x3s2_fwd(const void* x, void* y, int8_t* idx, int dtype, int n, int h, int w, int c,
+                         void* stream);
+int iit_maxpool3x3s2_bwd(const void* dy, const int8_t* idx, void* dx, int dtype, int n, int h, int w,
+                         int c, void* stream);
+/* AdaptiveAvgPool2d(1) + flatten: [n,hw,c] -> fp32 [n,c]; and its backward. */
+int iit_avgpool_fwd(const void* x, float* y, int dtype, int n, int hw, int c, void* stream);
+int iit_avgpool_bwd(const float* dy, void* dx, int dtype, int n, int hw, int c, void* stream);
+/* Linear: y[n,o] = x[n,i] @ w[o,i]^T + b (fp32), and its three gradients. */
+int iit_linear_fwd(const float* x, const float* w, const float* b, float* y, int n, int in, int out,
+                   void* stream);
+int iit_linear_bwd(const float* x, const float* w, const float* dy, float* dx, float* dw, float* db,
+                   int n, int in, int out, void* stream);
+
+/* ------------------------------------------------------------------------------------------ */
+/* optimiser step pieces (iit_behavior_model_pair.py:60-64, base_model_pair.py:176-180,229)     */
+/* ------------------------------------------------------------------------------------------ */
+/* sqnorm[0] += sum(g^2) over a flat fp32 buffer (clip_grad_norm_'s total norm) */
+int iit_sqnorm(const float* g, int64_t n, double* sqnorm, void* stream);
+/* Adam (torch.optim.Adam defaults: no weight decay, no amsgrad) on a flat fp32 buffer with the
+ * clip factor min(1, max_norm/(sqrt(*sqnorm)+1e-6)) applied to g on the fly (max_norm<=0: none).
+ * step is the 1-based step count (host value). */
+int iit_adam_step(float* p, const float* g, float* m, float* v, int64_t n, double lr, double beta1,
+                  double beta2, double eps, int64_t step, const double* sqnorm, double max_norm,
+                  void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IIT_B200_H */

@@ -1,0 +1,356 @@
+"""GPU parity of each kernel, called through the C-ABI (iit_b200.ops -> libiit_b200.so), against
+the oracle (oracle/restate.py) for the integer / index work -- bit-exact -- and against a plain
+PyTorch fp32 CPU evaluation of the same op for the floating-point kernels (tolerances stated inline)."""
+import math
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from oracle import restate as R  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from iit_b200 import ops
+    return ops
+
+
+@pytest.fixture(scope="module")
+def Ix():
+    from iit_b200.utils.index import Ix
+    return Ix
+
+
+DEV = "cuda"
+
+
+# ------------------------------------------------------------------------------------------ patch
+def _patch_cases(Ix):
+    return [
+        ((8, 256, 4, 4), Ix[None, None, :2, :2], "q tl"),
+        ((8, 256, 4, 4), Ix[None, None, 2:4, 2:4], "q br"),
+        ((8, 256, 6, 6), Ix[None, None, :3, 3:6], "q 84px"),
+        ((8, 256, 4, 4), Ix[None, 64:128, None, None], "c mode"),
+        ((8, 256, 4, 4), Ix[[None]], "whole"),
+        ((4, 16, 4, 16), Ix[:, :, 2, :], "one head"),
+        ((4, 16, 4, 16), Ix[:, -1], "negative int"),
+        ((4, 16, 3072), Ix[[None]], "mlp whole"),
+        ((5, 7, 3), Ix[1:4, :, 2], "odd sizes"),
+        ((3, 5), Ix[:, 2:2], "empty box"),
+        ((6,), Ix[2:5], "rank 1"),
+    ]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.int64])
+@pytest.mark.parametrize("layout", ["contiguous", "channels_last", "mixed"])
+def test_patch_bit_exact(ops, Ix, dtype, layout):
+    g = torch.Generator().manual_seed(0)
+    for shape, idx, name in _patch_cases(Ix):
+        def mk():
+            v = torch.randn(shape, generator=g) * 100
+            return v.to(dtype)
+        act, src = mk(), mk()
+        want = R.patch(act, src, idx.as_index)           # reference semantics on CPU
+        a, s = act.to(DEV), src.to(DEV)
+        if len(shape) == 4 and layout != "contiguous":
+            a = a.contiguous(memory_format=torch.channels_last)
+            if layout == "channels_last":
+                s = s.contiguous(memory_format=torch.channels_last)
+        out = ops.patch(a, s, idx, inplace=True)
+        assert out.data_ptr() == a.data_ptr(), name
+        assert torch.equal(out.cpu(), want), f"{name} {dtype} {layout}"
+        cap = ops.capture_box(s, idx)
+        assert torch.equal(cap.cpu().reshape(-1), src[idx.as_index].reshape(-1)), f"capture {name}"
+
+
+def test_patch_list_index_falls_back(ops, Ix):
+    act, src = torch.randn(4, 6, 5), torch.randn(4, 6, 5)
+    idx = Ix[:, [0, 3], :]
+    out = ops.patch(act.to(DEV), src.to(DEV), idx, inplace=False)
+    assert torch.equal(out.cpu(), R.patch(act, src, idx.as_index))
+
+
+def test_patch_gradient_is_copyslices(ops, Ix):
+    for shape, idx, name in _patch_cases(Ix):
+        x = torch.randn(shape, requires_grad=True)
+        src = torch.randn(shape)
+        w = torch.randn(shape)
+        (R.patch(x * 2, src, idx.as_index) * w).sum().backward()
+        xg = x.detach().to(DEV).requires_grad_(True)
+        out = ops.patch(xg * 2, src.to(DEV), idx, inplace=True)
+        (out * w.to(DEV)).sum().backward()
+        assert torch.equal(xg.grad.cpu(), x.grad), name
+
+
+def test_patch_rejects_cpu_tensors(ops, Ix):
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.patch_(torch.zeros(4, 4), torch.zeros(4, 4), Ix[[None]])
+
+
+# --------------------------------------------------------------------------------------------- HL
+def test_hl_pvr_bit_exact(ops):
+    g = torch.Generator().manual_seed(1)
+    for batch in (1, 7, 4096):
+        bv = torch.randint(0, 10, (batch, 4), generator=g)
+        sv = torch.randint(0, 10, (batch, 4), generator=g)
+        assert torch.equal(ops.hl_pvr(bv.to(DEV), None, -1).cpu(), R.pvr_hl_forward(bv))
+        for i, h in enumerate(R.PVR_HOOKS):
+            got = ops.hl_pvr(bv.to(DEV), sv.to(DEV), i).cpu()
+            assert torch.equal(got, R.pvr_hl_intervened(bv, sv, h)), h
+
+
+def _rand_tokens(batch, seq, vocab, names, g):
+    tok = torch.randint(0, vocab, (batch, seq), generator=g)
+    # plenty of names and duplicates
+    m = torch.rand(batch, seq, generator=g) < 0.5
+    tok[m] = names[torch.randint(0, len(names), (int(m.sum()),), generator=g)]
+    return tok
+
+
+@pytest.mark.parametrize("vocab,seq", [(21, 9), (101, 16), (50257, 16)])
+def test_hl_ioi_bit_exact(ops, vocab, seq):
+    g = torch.Generator().manual_seed(2)
+    names = torch.tensor([10, 20, 30]) if vocab == 21 else torch.randperm(vocab - 1, generator=g)[:20].sort().values
+    batch = 64 if vocab < 1000 else 8
+    base = _rand_tokens(batch, seq, vocab, names, g)
+    src = _rand_tokens(batch, seq, vocab, names, g)
+    # reference's own vector (iit/tasks/ioi/test_ioi.py:34-45)
+    if vocab == 21:
+        base[0] = torch.tensor([3, 10, 4, 10, 5, 9, 2, 6, 5])
+    nd, bd, sd = names.to(DEV), base.to(DEV), src.to(DEV)
+    dense = ops.hl_ioi_dense(bd, None, None, nd, vocab).cpu()
+    want = R.ioi_hl_forward(base, names, vocab)
+    assert torch.equal(dense, want)
+    assert torch.equal(ops.hl_ioi_last_argmax(bd, None, None, nd, vocab).cpu(), torch.argmax(want[:, -1, :], dim=-1))
+    for node in R.IOI_HL_HOOKS:
+        want = R.ioi_hl_intervened(base, src, names, vocab, node)
+        assert torch.equal(ops.hl_ioi_dense(bd, sd, node, nd, vocab).cpu(), want), node
+        assert torch.equal(ops.hl_ioi_last_argmax(bd, sd, node, nd, vocab).cpu(),
+                           torch.argmax(want[:, -1, :], dim=-1)), node
+
+
+# ------------------------------------------------------------------------------------- CE and IIA
+@pytest.mark.parametrize("rows,classes", [(8, 10), (4096, 10), (5, 101), (6, 50257)])
+def test_ce_index_and_prob(ops, rows, classes):
+    g = torch.Generator().manual_seed(3)
+    logits = (torch.randn(rows, classes, generator=g) * 3).requires_grad_(True)
+    tgt = torch.randint(0, classes, (rows,), generator=g)
+    want = F.cross_entropy(logits, tgt)
+    (want * 0.4).backward()
+    lg = logits.detach().to(DEV).requires_grad_(True)
+    got = ops.cross_entropy(lg, tgt.to(DEV))
+    (got * 0.4).backward()
+    # fp32: relative 1e-5 on the loss, 1e-5 absolute on gradients of magnitude <= 1/rows
+    assert math.isclose(got.item(), want.item(), rel_tol=1e-5)
+    torch.testing.assert_close(lg.grad.cpu(), logits.grad, rtol=1e-4, atol=1e-7)
+    # probability target: one-hot must equal the index form; soft targets must match torch
+    onehot = F.one_hot(tgt, classes).float()
+    soft = torch.softmax(torch.randn(rows, classes, generator=g), -1)
+    for prob in (onehot, soft):
+        l2 = logits.detach().clone().requires_grad_(True)
+        w2 = F.cross_entropy(l2, prob)
+        w2.backward()
+        lg2 = logits.detach().to(DEV).requires_grad_(True)
+        g2 = ops.cross_entropy(lg2, prob.to(DEV))
+        g2.backward()
+        assert math.isclose(g2.item(), w2.item(), rel_tol=1e-5)
+        torch.testing.assert_close(lg2.grad.cpu(), l2.grad, rtol=1e-4, atol=1e-7)
+
+
+def test_ce_strided_rows(ops):
+    """last-position rows of a [B,S,V] tensor are read in place (row stride S*V)."""
+    g = torch.Generator().manual_seed(4)
+    full = torch.randn(6, 16, 101, generator=g)
+    tgt = torch.randint(0, 101, (6,), generator=g)
+    want = F.cross_entropy(full[:, -1, :], tgt)
+    got = ops.cross_entropy(full.to(DEV)[:, -1, :], tgt.to(DEV))
+    assert math.isclose(got.item(), want.item(), rel_tol=1e-5)
+
+
+@pytest.mark.parametrize("rows,classes", [(9, 10), (4096, 10), (7, 1025), (5, 50257)])
+def test_iia_count_bit_exact(ops, rows, classes):
+    g = torch.Generator().manual_seed(5)
+    logits = torch.randn(rows, classes, generator=g)
+    logits[0, :] = 0.0                       # all tied -> first index
+    logits[1, -1] = logits[1, 3] = 50.0      # two-way tie -> lower index
+    if rows > 2:
+        logits[2, 5] = float("nan")          # NaN is maximal in torch.argmax
+    hl = torch.randint(0, classes, (rows,), generator=g)
+    hl[::2] = torch.argmax(logits, -1)[::2]
+    changed = torch.rand(rows, generator=g) < 0.6
+    top1_want = torch.argmax(logits, dim=-1)
+    counts, top1 = ops.iia_count(logits.to(DEV), hl.to(DEV), want_top1=True)
+    assert torch.equal(top1.cpu(), top1_want)
+    assert counts.tolist() == [int((top1_want == hl).sum()), rows]
+    counts, _ = ops.iia_count(logits.to(DEV), hl.to(DEV), changed=changed.to(DEV))
+    assert counts.tolist() == [int(((top1_want == hl) & changed).sum()), int(changed.sum())]
+    # accumulation across calls
+    counts, _ = ops.iia_count(logits.to(DEV), hl.to(DEV), counts=counts)
+    assert counts.tolist() == [int(((top1_want == hl) & changed).sum()) + int((top1_want == hl).sum()),
+                               int(changed.sum()) + rows]
+    # bf16 logits
+    lb = logits.to(torch.bfloat16)
+    _, t2 = ops.iia_count(lb.to(DEV), None, want_top1=True)
+    assert torch.equal(t2.cpu(), torch.argmax(lb.float(), dim=-1))
+
+
+# ------------------------------------------------------------------------------- ResNet layers
+RESNET_CONVS = [  # (cin, cout, k, stride, pad, hw)
+    (3, 64, 7, 2, 3, 56), (64, 64, 3, 1, 1, 14), (64, 128, 3, 2, 1, 14), (64, 128, 1, 2, 0, 14),
+    (128, 128, 3, 1, 1, 7), (128, 256, 3, 2, 1, 7), (256, 256, 3, 1, 1, 4), (256, 512, 3, 2, 1, 4),
+    (512, 512, 3, 1, 1, 2), (256, 512, 1, 2, 0, 4), (64, 64, 3, 1, 1, 21),
+]
+
+
+@pytest.mark.parametrize("cfg", RESNET_CONVS)
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_conv_fprop_dgrad_wgrad(ops, cfg, dtype):
+    from iit_b200.nn.resnet import Conv2d
+    cin, cout, k, stride, pad, hw = cfg
+    g = torch.Generator().manual_seed(6)
+    n = 5
+    x = torch.randn(n, cin, hw, hw, generator=g)
+    w = torch.randn(cout, cin, k, k, generator=g) / math.sqrt(cin * k * k)
+    if dtype == torch.bfloat16:  # compare against fp32 math on the bf16-rounded operands
+        x, w = x.bfloat16().float(), w.bfloat16().float()
+    x.requires_grad_(True)
+    w.requires_grad_(True)
+    y = F.conv2d(x, w, None, stride, pad)
+    gy = torch.randn(y.shape, generator=g)
+    if dtype == torch.bfloat16:
+        gy = gy.bfloat16().float()
+    y.backward(gy)
+    conv = Conv2d(cin, cout, k, stride, pad).to(DEV)
+    with torch.no_grad():
+        conv.weight.copy_(w)
+    xd = x.detach().to(DEV).to(dtype).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    sums = ops.new_bn_sums(cout, DEV)
+    yd = conv(xd, sums)
+    assert yd.shape == y.shape and yd.is_contiguous(memory_format=torch.channels_last)
+    yd.backward(gy.to(DEV).to(dtype))
+    # fp32 path: FFMA accumulation order differs from the CPU's -> 2e-4 of the output scale.
+    # bf16 path: operands identical, outputs rounded to bf16 -> 1e-2 of the output scale.
+    tol = 2e-4 if dtype == torch.float32 else 1e-2
+    def close(a, b, what):
+        scale = b.abs().max().item() + 1e-12
+        err = (a.float().cpu() - b).abs().max().item()
+        assert err <= tol * scale, f"{what}: err {err:.3e} scale {scale:.3e} cfg {cfg} {dtype}"
+    close(yd, y.detach(), "fprop")
+    close(xd.grad, x.grad, "dgrad")
+    close(conv.weight.grad, w.grad, "wgrad")
+    # fused BN statistics of the stored output
+    ys = yd.detach().float().cpu()
+    rows = ys.numel() // cout
+    torch.testing.assert_close(sums[0].cpu().float() / rows, ys.mean(dim=(0, 2, 3)), rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(sums[1].cpu().float() / rows, (ys * ys).mean(dim=(0, 2, 3)), rtol=1e-3, atol=1e-4)
+
+
+@pytest.mark.parametrize("c,hw", [(64, 28), (128, 7), (512, 2)])
+@pytest.mark.parametrize("relu,res", [(False, False), (True, False), (True, True)])
+@pytest.mark.parametrize("training", [True, False])
+def test_bn_act_fwd_bwd(ops, c, hw, relu, res, training):
+    from iit_b200.nn.resnet import BatchNorm2d
+    g = torch.Generator().manual_seed(7)
+    n = 6
+    x = (torch.randn(n, c, hw, hw, generator=g) * 2 + 0.5).requires_grad_(True)
+    r = torch.randn(n, c, hw, hw, generator=g).requires_grad_(True) if res else None
+    gamma = (torch.rand(c, generator=g) + 0.5).requires_grad_(True)
+    beta = torch.randn(c, generator=g).requires_grad_(True)
+    rm, rv = torch.randn(c, generator=g), torch.rand(c, generator=g) + 0.5
+    rm0, rv0 = rm.clone(), rv.clone()
+    y = F.batch_norm(x, rm, rv, gamma, beta, training, 0.1, 1e-5)
+    if res:
+        y = y + r
+    if relu:
+        y = F.relu(y)
+    gy = torch.randn(y.shape, generator=g)
+    y.backward(gy)
+    bn = BatchNorm2d(c).to(DEV)
+    bn.train(training)
+    with torch.no_grad():
+        bn.weight.copy_(gamma); bn.bias.copy_(beta); bn.running_mean.copy_(rm0); bn.running_var.copy_(rv0)
+    xd = x.detach().to(DEV).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    rd = r.detach().to(DEV).contiguous(memory_format=torch.channels_last).requires_grad_(True) if res else None
+    yd = bn(xd, residual=rd, relu=relu)
+    yd.backward(gy.to(DEV))
+    # fp32 elementwise + reductions: 1e-4 relative / 1e-5 absolute
+    kw = dict(rtol=1e-4, atol=2e-5)
+    torch.testing.assert_close(yd.cpu(), y.detach(), **kw)
+    torch.testing.assert_close(xd.grad.cpu(), x.grad, **kw)
+    torch.testing.assert_close(bn.weight.grad.cpu(), gamma.grad, rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(bn.bias.grad.cpu(), beta.grad, rtol=1e-4, atol=1e-4)
+    if res:
+        torch.testing.assert_close(rd.grad.cpu(), r.grad, **kw)
+    torch.testing.assert_close(bn.running_mean.cpu(), rm, **kw)
+    torch.testing.assert_close(bn.running_var.cpu(), rv, **kw)
+    assert int(bn.num_batches_tracked) == (1 if training else 0)
+
+
+def test_pool_linear_relu(ops):
+    g = torch.Generator().manual_seed(8)
+    x = torch.randn(5, 64, 28, 28, generator=g).requires_grad_(True)
+    y = F.max_pool2d(x, 3, 2, 1)
+    gy = torch.randn(y.shape, generator=g)
+    y.backward(gy)
+    xd = x.detach().to(DEV).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    yd = ops.maxpool3x3s2(xd)
+    yd.backward(gy.to(DEV))
+    assert torch.equal(yd.cpu(), y.detach())
+    torch.testing.assert_close(xd.grad.cpu(), x.grad, rtol=0, atol=1e-6)
+
+    x = torch.randn(7, 512, 2, 2, generator=g).requires_grad_(True)
+    w = torch.randn(10, 512, generator=g).requires_grad_(True)
+    b = torch.randn(10, generator=g).requires_grad_(True)
+    out = F.linear(torch.flatten(F.adaptive_avg_pool2d(x, 1), 1), w, b)
+    go = torch.randn(out.shape, generator=g)
+    out.backward(go)
+    xd = x.detach().to(DEV).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    wd, bd = w.detach().to(DEV).requires_grad_(True), b.detach().to(DEV).requires_grad_(True)
+    od = ops.linear(torch.flatten(ops.avgpool(xd), 1), wd, bd)
+    od.backward(go.to(DEV))
+    kw = dict(rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(od.cpu(), out.detach(), **kw)
+    torch.testing.assert_close(xd.grad.cpu(), x.grad, **kw)
+    torch.testing.assert_close(wd.grad.cpu(), w.grad, **kw)
+    torch.testing.assert_close(bd.grad.cpu(), b.grad, **kw)
+
+    a = torch.randn(4, 64, 7, 7, generator=g).requires_grad_(True)
+    c = torch.randn(4, 64, 7, 7, generator=g).requires_grad_(True)
+    z = F.relu(F.relu(a) + c)
+    gz = torch.randn(z.shape, generator=g)
+    z.backward(gz)
+    ad = a.detach().to(DEV).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    cd = c.detach().to(DEV).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    zd = ops.add_relu(ops.relu(ad), cd, True)
+    zd.backward(gz.to(DEV))
+    assert torch.equal(zd.cpu(), z.detach())
+    assert torch.equal(ad.grad.cpu(), a.grad) and torch.equal(cd.grad.cpu(), c.grad)
+
+
+def test_flat_adam_matches_torch_adam_with_clip(ops):
+    from iit_b200.nn.optim import FlatAdam
+    g = torch.Generator().manual_seed(9)
+    shapes = [(64, 3, 7, 7), (64,), (10, 512), (7,)]
+    ps = [torch.randn(s, generator=g) for s in shapes]
+    ref = [p.clone().requires_grad_(True) for p in ps]
+    ropt = torch.optim.Adam(ref, lr=1e-3)
+    mine = [torch.nn.Parameter(p.clone().to(DEV)) for p in ps]
+    mine[0].data = mine[0].data.contiguous(memory_format=torch.channels_last)
+    opt = FlatAdam(mine, lr=1e-3)
+    for step in range(4):
+        grads = [torch.randn(s, generator=g) * (10.0 if step % 2 == 0 else 0.01) for s in shapes]
+        ropt.zero_grad()
+        opt.zero_grad()
+        for p, gr in zip(ref, grads):
+            p.grad = gr.clone()
+        for p, gr in zip(mine, grads):
+            p.grad.add_(gr.to(DEV))
+        torch.nn.utils.clip_grad_norm_(ref, 1.0)
+        ropt.step()
+        opt.step(max_norm=1.0)
+        for p, q in zip(ref, mine):
+            torch.testing.assert_close(q.detach().cpu(), p.detach(), rtol=1e-5, atol=1e-7)

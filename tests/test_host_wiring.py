@@ -1,0 +1,139 @@
+"""CPU tests of the host side: API mirrors (index / nodes / correspondence / node picker / hooks),
+the C-ABI library's exported symbols, and a dry run of the model-pair wiring (no kernel executes)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from iit_b200 import _lib
+from iit_b200.model_pairs import HLNode, IITBehaviorModelPair, LLNode, StrictIITModelPair
+from iit_b200.utils.correspondence import Correspondence
+from iit_b200.utils.index import Ix, TorchIndex
+from iit_b200.utils import node_picker
+
+from dryrun import dry_run
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_header_symbols_exported():
+    """Every function declared in include/iit_b200.h is exported by the .so and bound in _lib."""
+    hdr = open(os.path.join(ROOT, "include", "iit_b200.h")).read()
+    declared = set(re.findall(r"\b(iit_[a-z0-9_]+)\s*\(", hdr))
+    assert declared, "no declarations parsed"
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in the header but not exported"
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+    assert _lib.lib.iit_version() >= 100
+
+
+def test_index_reference_cases():  # reference tests/test_index.py
+    assert Ix[:, :, :, :] == Ix[:, :, :, :]
+    assert Ix[:, :, 0, :] != Ix[:, :, 1, :]
+    assert Ix[:, :] != Ix[:, :, 1, :]
+    assert hash(Ix[:, :, 0, :]) == hash(Ix[:, :, 0, :])
+    assert hash(Ix[:, :, 0, :]) != hash(Ix[:, :, 1, :])
+    assert Ix[:, :, :, :].intersects(Ix[:, :, 0, :])
+    assert not Ix[:, :, 0, :].intersects(Ix[:, :, 2:3, :])
+    assert not Ix[:, :, 2, :].intersects(Ix[:, :, 1, :])
+    with pytest.raises(ValueError):
+        Ix[:, :, 1].intersects(Ix[:, :, :, :])
+    assert repr(Ix[:, :, 1, :]) == "[:, :, 1, :]"
+    assert repr(Ix[[None]]) == "[:]"
+
+
+def test_index_box():
+    assert Ix[None, None, :2, 2:4].box((8, 256, 4, 4)) == [(0, 8), (0, 256), (0, 2), (2, 2)]
+    assert Ix[:, :, 3, :].box((8, 16, 4, 16)) == [(0, 8), (0, 16), (3, 1), (0, 16)]
+    assert Ix[[None]].box((5, 6)) == [(0, 5), (0, 6)]
+    assert Ix[:, -1].box((5, 6)) == [(0, 5), (5, 1)]
+    assert Ix[:, [0, 2]].box((5, 6)) is None
+    t = torch.arange(8 * 6 * 4 * 4).reshape(8, 6, 4, 4)
+    idx = Ix[None, 1:3, :2, 2:4]
+    spans = idx.box(t.shape)
+    ref = t[idx.as_index]
+    assert list(ref.shape) == [e for _, e in spans]
+
+
+def test_nodes_and_correspondence():  # reference tests/test_corr.py
+    corr = Correspondence()
+    hl, ll = HLNode("hl", -1), LLNode("ll", None)
+    corr[hl] = ll
+    assert corr[hl] == ll and corr["hl"] == ll
+    assert corr.get_suffixes() == {"attn": "attn.hook_result", "mlp": "mlp.hook_post"}
+    assert ll.index == Ix[[None]]
+    c = Correspondence.make_corr_from_dict({"a": ["blocks.0.attn.hook_z"], "b": ["blocks.1.mlp.hook_post"]},
+                                           make_suffixes_from_corr=True)
+    assert c.get_suffixes() == {"attn": "attn.hook_z", "mlp": "mlp.hook_post"}
+    assert {n.name for n in c["a"]} == {"blocks.0.attn.hook_z"}
+
+
+def test_node_picker_transformer():  # reference tests/test_node_picker.py:6-29
+    class M:
+        class cfg:
+            n_layers, n_heads = 2, 4
+    want = []
+    for l in range(2):
+        want += [LLNode(f"blocks.{l}.attn.hook_result", Ix[:, :, h, :]) for h in range(4)]
+        want.append(LLNode(f"blocks.{l}.mlp.hook_post", Ix[[None]]))
+    assert node_picker.get_all_nodes(M) == want
+
+
+def test_ioi_nodes_not_in_circuit_matches_golden():
+    from iit_b200.tasks.ioi import corr
+    gold = np.load(os.path.join(ROOT, "tests", "golden", "ioi.npz"))
+
+    class M:
+        class cfg:
+            n_layers, n_heads = 6, 4
+    got = [f"{n.name}|{n.index}" for n in node_picker.get_nodes_not_in_circuit(M, corr)]
+    assert got == gold["nodes_not_in_circuit"].tolist()
+
+
+def test_resnet_names_match_reference_golden():
+    from iit_b200.nn.resnet import ResNet18LL
+    from iit_b200.utils.wrapper import get_hook_points
+    gold = np.load(os.path.join(ROOT, "tests", "golden", "pvr.npz"))
+    m = ResNet18LL()
+    assert set(m.hook_dict.keys()) == set(gold["hook_points"].tolist())
+    assert get_hook_points(m) == gold["conv_hook_points"].tolist()
+    assert set(m.state_dict().keys()) == set(gold["state_dict_keys"].tolist())
+    from oracle import restate
+    missing = m.load_state_dict(restate.resnet18_state_dict(0))
+    assert not missing.missing_keys and not missing.unexpected_keys
+
+
+def test_node_sampling_matches_reference_sequence():
+    """Same numpy stream and call order as the reference => same nodes (golden from the reference run)."""
+    from iit_b200.tasks.mnist_pvr.pvr_hl import MNIST_PVR_HL, hl_nodes
+    gold = np.load(os.path.join(ROOT, "tests", "golden", "pvr.npz"))
+    corr = {hl_nodes[h]: {LLNode("x", Ix[[None]])} for h in ["hook_tl", "hook_tr", "hook_bl", "hook_br"]}
+    pair = IITBehaviorModelPair(MNIST_PVR_HL(), None, corr)
+    assert [str(pair.sample_hl_name()) for _ in range(4)] == gold["q/nodes"].tolist()
+
+
+def test_dry_run_pvr_train_and_eval_steps():
+    from iit_b200.tasks.mnist_pvr.get_alignment import get_alignment
+    from oracle import restate
+    with dry_run() as calls:
+        ll, hl, corr = get_alignment("mnist_pvr", {"input_shape": (1, 3, 56, 56)}, device="cpu")
+        assert all(isinstance(k, HLNode) for k in corr)
+        pair = StrictIITModelPair(hl, ll, corr, training_args={"lr": 1e-3})
+        assert len(pair.nodes_not_in_circuit) == 16
+        opt = torch.optim.Adam(ll.parameters(), lr=1e-3)
+        base, src = restate.synthetic_pvr(4, 0), restate.synthetic_pvr(4, 1)
+        ll.train()
+        m = pair.run_train_step(base, src, pair.loss_fn, opt)
+        assert set(m) == {"train/iit_loss", "train/behavior_loss", "train/strict_loss"}
+        assert all(p.grad is not None and p.grad.shape == p.shape for p in ll.parameters())
+        ll.eval()
+        with torch.no_grad():
+            e = pair.run_eval_step(base, src, pair.loss_fn)
+        assert set(e) == {"val/iit_loss", "val/IIA", "val/accuracy"}
+        hl_o, ll_o = pair.do_intervention(base, src, "hook_tr")
+        assert hl_o.shape == (4,) and ll_o.shape == (4, 10)
+    assert "iit_patch_fwd" in calls and "iit_conv2d_wgrad" in calls and "iit_hl_pvr" in calls
