@@ -166,6 +166,8 @@ static int launch(void* dst, const void* src, const iit_box_t* box, bool compact
   IIT_REQUIRE(box && box->rank >= 0 && box->rank <= IIT_MAX_RANK, "%s: rank must be in [0,%d]", name, IIT_MAX_RANK);
   IIT_REQUIRE(box->elem_bytes == 2 || box->elem_bytes == 4 || box->elem_bytes == 8 || box->elem_bytes == 1,
               "%s: elem_bytes must be 1, 2, 4 or 8", name);
+  for (int i = 0; i < box->rank; ++i)
+    if (box->extent[i] <= 0) return 0;  // empty box: nothing to do (pointers may be null)
   IIT_REQUIRE(dst != nullptr && (MODE == MODE_ZERO || src != nullptr), "%s: null pointer", name);
   PatchDesc pd;
   int64_t db, sb;

@@ -42,9 +42,11 @@ def golden_pvr():
     from iit.utils.wrapper import HookedModuleWrapper, get_hook_points
     from iit.model_pairs.nodes import HLNode
 
-    B, size = 8, 56
+    # B=64: with batch-statistic BatchNorm + ReLU + Adam a single fp32 rounding flip of one ReLU mask moves a
+    # whole channel's gradient by O(1/rows); at B=8 that alone exceeds the 1e-3 loss bar after one Adam update
+    B, size = 64, 56
     hook = "mod.layer3.mod.1.mod.conv2.hook_point"  # task_loader.py:41
-    res = {}
+    res = {"B": B}
     for mode in ("q", "c"):
         torch.manual_seed(0)
         net = torchvision.models.resnet18()
@@ -74,7 +76,7 @@ def golden_pvr():
                     res[f"{mode}/di/{k.name}/hl"] = hl_o
                     res[f"{mode}/di/{k.name}/ll"] = ll_o
                     if mode == "q" and k.name == "hook_tr":
-                        res["q/di/hook_tr/cache_hook"] = pair.ll_cache[hook]
+                        res["q/di/hook_tr/cache_hook"] = pair.ll_cache[hook][:4]
                 ll.load_state_dict(sd0)  # undo the BN running-stat updates of the probe runs
             before = pair.rng.bit_generator.state["state"]["state"]
             m = pair.run_train_step(base, src, pair.loss_fn, opt)
