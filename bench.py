@@ -245,7 +245,8 @@ def run_ours(args, rank, world, local):
         s = tuple(t.to(dev, non_blocking=True) for t in src_h)
         return pair.run_train_step(b, s, pair.loss_fn, opt)  # returns host floats: the D2H read of the losses
 
-    timer = KernelTimer(["iit_conv2d_fprop", "iit_conv2d_dgrad", "iit_conv2d_wgrad"])
+    timer = KernelTimer(["iit_conv2d_fprop", "iit_conv2d_dgrad", "iit_conv2d_wgrad", "iit_conv2d_fprop_tc",
+                         "iit_conv2d_dgrad_tc", "iit_conv2d_wgrad_tc"])
     timer.install()
 
     def timed(fn, steps):

@@ -49,6 +49,11 @@ SIGNATURES = {
     "iit_iia_count": [_vp, _i, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp],
     "iit_conv2d_fprop": [_vp, _vp, _vp, _ConvP, _i, _vp, _vp, _vp],
     "iit_conv2d_dgrad": [_vp, _vp, _vp, _ConvP, _i, _vp],
+    "iit_conv2d_tc_supported": [_ConvP, _i],
+    "iit_conv2d_fprop_tc": [_vp, _vp, _vp, _ConvP, _vp],
+    "iit_conv2d_dgrad_tc": [_vp, _vp, _vp, _ConvP, _vp],
+    "iit_conv2d_wgrad_tc_scratch_bytes": [_ConvP],
+    "iit_conv2d_wgrad_tc": [_vp, _vp, _vp, _ConvP, _vp, _sz, _vp],
     "iit_conv2d_wgrad_scratch_bytes": [_ConvP],
     "iit_conv2d_wgrad": [_vp, _vp, _vp, _ConvP, _i, _vp, _sz, _vp],
     "iit_filter_relayout": [_vp, C.POINTER(C.c_int64), _vp, _i, _i, _i, _i, _i, _i, _vp],
@@ -74,8 +79,8 @@ SIGNATURES = {
     "iit_launch_count": [],
 }
 _RESTYPES = {"iit_last_error": C.c_char_p, "iit_launch_count": C.c_ulonglong,
-             "iit_conv2d_wgrad_scratch_bytes": C.c_size_t}
-_NO_STATUS = set(_RESTYPES) | {"iit_version"}
+             "iit_conv2d_wgrad_scratch_bytes": C.c_size_t, "iit_conv2d_wgrad_tc_scratch_bytes": C.c_size_t}
+_NO_STATUS = set(_RESTYPES) | {"iit_version", "iit_conv2d_tc_supported"}
 
 
 def _load():

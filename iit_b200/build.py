@@ -47,7 +47,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         failed |= p.returncode != 0
     if failed:
         raise RuntimeError("nvcc failed")
-    cmd = [NVCC, "-shared", "-o", LIB, *objs, "-lcuda"]
+    cmd = [NVCC, "-shared", "-o", LIB, *objs]
     subprocess.check_call(cmd)
     return LIB
 

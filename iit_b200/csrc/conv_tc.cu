@@ -1,0 +1,573 @@
+// (b) ResNet-18 3x3 stride-1 convolutions (fprop and dgrad) on the 5th-generation tensor cores:
+// TMA-fed, warp-specialised implicit GEMM with tcgen05.mma and a TMEM accumulator (bf16 in, fp32 acc).
+//
+//   D[128 pixels, BN filters] = sum over 9 taps, sum over C/64 chunks:  A_tap[128, 64] * W_tap[BN, 64]^T
+//
+// * A tile = a box of BW x BH x BNI output pixels (BW*BH*BNI = 128) of BNI images. For tap (r,s) the
+//   operand is the SAME box of the NHWC input shifted by (r-pad, s-pad): one 4-D TMA load
+//   (cp.async.bulk.tensor.4d, SWIZZLE_128B) whose out-of-bounds rows/columns - the padding halo - are
+//   zero-filled by the TMA unit. No im2col buffer, no index arithmetic in the SM.
+// * B tile = BN filters x 64 reduction elements of the KRSC (fprop) / CRSK (dgrad) filter matrix: one
+//   2-D TMA load. Both land in the canonical K-major SWIZZLE_128B layout that the UMMA shared-memory
+//   descriptors address directly.
+// * Warp 0: TMA producer (one elected lane). Warp 1: TMEM allocator + MMA issuer (one elected lane,
+//   tcgen05.mma.cta_group::1.kind::f16, 128 x BN x 16 per instruction, completion via tcgen05.commit ->
+//   mbarrier). Warps 2-5: epilogue; each owns the 32 TMEM lanes it is allowed to read, pulls 32 fp32
+//   columns per tcgen05.ld, converts to bf16 and stores 64 B runs of one output pixel's channels.
+// * STAGES-deep full/empty mbarrier ring between producer and MMA; several CTAs per SM (<= 113 KB smem
+//   and <= 128 TMEM columns each) so one tile's epilogue overlaps another tile's main loop.
+//
+// Every mbarrier wait is bounded: a protocol bug traps (CUDA error) instead of hanging the GPU.
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace iit {
+
+constexpr int TC_BM = 128;      // pixels per tile (UMMA M)
+constexpr int TC_BK = 64;       // bf16 elements per 128-byte swizzle row
+constexpr int TC_UK = 16;       // UMMA K for 16-bit inputs
+constexpr int TC_THREADS = 192;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  uint32_t done = 0;
+  for (uint32_t spins = 0; !done; ++spins) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    if (!done && spins > (1u << 24)) __trap();  // protocol bug: fail loudly, never hang the GPU
+  }
+}
+__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+// K-major, SWIZZLE_128B operand descriptor: 128-byte rows, 8-row (1024 B) swizzle atoms stacked along M/N
+__device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr >> 4) & 0x3FFF) | (1ull << 16) /* LBO (unused) */ | ((uint64_t)(1024 >> 4) << 32) /* SBO */ |
+         (1ull << 46) /* descriptor version: Blackwell */ | (2ull << 61) /* SWIZZLE_128B */;
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+struct TcParams {
+  int N, P, Q;          // output pixel grid (== input grid: stride 1, "same" padding)
+  int Cin, Cout;        // reduction channels per tap / produced channels
+  int R, S;
+  int off_h, off_w;     // input row = p + sign*r + off_h   (fprop: sign=+1, off=-pad; dgrad: sign=-1, off=+pad)
+  int sign;
+  int BW, BH, BNI;      // pixel box
+  int tiles_w, tiles_h; // boxes per image row / column
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_constant__ CUtensorMap map_a,
+                                                                const __grid_constant__ CUtensorMap map_b,
+                                                                __nv_bfloat16* __restrict__ out, TcParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  // SWIZZLE_128B operands need 1024-byte aligned tiles
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2, B_BYTES = BN * TC_BK * 2;
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + STAGES * A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * B_BYTES);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tmem_full = empty + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // tile -> (image block, row block, column block); blockIdx.y -> filter block
+  int t = blockIdx.x;
+  const int tw = t % p.tiles_w; t /= p.tiles_w;
+  const int th = t % p.tiles_h; t /= p.tiles_h;
+  const int n0 = t * p.BNI, p0 = th * p.BH, q0 = tw * p.BW;
+  const int co0 = blockIdx.y * BN;
+  const int kchunks = p.Cin / TC_BK;
+  const int nk = p.R * p.S * kchunks;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(tmem_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {  // TMEM allocation is warp-collective; this warp also frees it
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(BN));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < nk; ++kb) {
+        const int tap = kb / kchunks, kc = kb - tap * kchunks;
+        const int r = tap / p.S, s = tap - r * p.S;
+        mbar_wait(&empty[stage], phase ^ 1);
+        mbar_expect_tx(&full[stage], A_BYTES + B_BYTES);
+        tma_load_4d(sA + stage * A_BYTES, &map_a, &full[stage], kc * TC_BK, q0 + p.sign * s + p.off_w,
+                    p0 + p.sign * r + p.off_h, n0);
+        tma_load_2d(sB + stage * B_BYTES, &map_b, &full[stage], tap * p.Cin + kc * TC_BK, co0);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // instruction descriptor: D=f32, A=B=bf16, both K-major, N at [17,23), M at [24,29)
+      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < nk; ++kb) {
+        mbar_wait(&full[stage], phase);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t a0 = smem_u32(sA + stage * A_BYTES), b0 = smem_u32(sB + stage * B_BYTES);
+#pragma unroll
+        for (int k = 0; k < TC_BK / TC_UK; ++k) {
+          umma_bf16(tmem_base, umma_desc_k_sw128(a0 + k * TC_UK * 2), umma_desc_k_sw128(b0 + k * TC_UK * 2), idesc,
+                    (uint32_t)((kb | k) != 0));
+        }
+        umma_commit(&empty[stage]);  // frees this smem stage once the MMAs above have read it
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      umma_commit(tmem_full);        // accumulator complete
+    }
+  } else {
+    // epilogue: warp w may read TMEM lanes [32*(w%4), 32*(w%4)+32)
+    const int quarter = warp & 3;
+    const int m = quarter * 32 + lane;  // accumulator row == pixel of the box
+    const int wl = m % p.BW;
+    const int hl = (m / p.BW) % p.BH;
+    const int nl = m / (p.BW * p.BH);
+    const int n = n0 + nl, pp = p0 + hl, qq = q0 + wl;
+    const bool ok = n < p.N && pp < p.P && qq < p.Q;
+    __nv_bfloat16* dst = out + (((int64_t)n * p.P + pp) * p.Q + qq) * p.Cout + co0;
+    mbar_wait(tmem_full, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+    for (int c = 0; c < BN; c += 32) {
+      uint32_t v[32];
+      tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c, v);
+      if (ok) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+          uint4 o;
+          __nv_bfloat162 h0 = __floats2bfloat162_rn(__uint_as_float(v[j + 0]), __uint_as_float(v[j + 1]));
+          __nv_bfloat162 h1 = __floats2bfloat162_rn(__uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+          __nv_bfloat162 h2 = __floats2bfloat162_rn(__uint_as_float(v[j + 4]), __uint_as_float(v[j + 5]));
+          __nv_bfloat162 h3 = __floats2bfloat162_rn(__uint_as_float(v[j + 6]), __uint_as_float(v[j + 7]));
+          o.x = *reinterpret_cast<uint32_t*>(&h0); o.y = *reinterpret_cast<uint32_t*>(&h1);
+          o.z = *reinterpret_cast<uint32_t*>(&h2); o.w = *reinterpret_cast<uint32_t*>(&h3);
+          *reinterpret_cast<uint4*>(dst + c + j) = o;
+        }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(BN));
+  }
+}
+
+// ---- host side -----------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+static int pow2_ge(int v) { int r = 1; while (r < v) r <<= 1; return r; }
+
+template <int BN>
+static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16* out, const TcParams& p, dim3 grid,
+                     cudaStream_t st) {
+  constexpr int STAGES = BN == 64 ? 4 : 4;
+  constexpr size_t smem = STAGES * (TC_BM * TC_BK * 2 + BN * TC_BK * 2) + (2 * STAGES + 1) * 8 + 16 + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    IIT_CUDA(cudaFuncSetAttribute(conv3x3_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = true;
+  }
+  conv3x3_tc_kernel<BN, STAGES><<<grid, TC_THREADS, smem, st>>>(ma, mb, out, p);
+  return 0;
+}
+
+// in: [N,P,Q,Cin] bf16 NHWC;  wmat: [Cout][R*S*Cin] bf16;  out: [N,P,Q,Cout] bf16
+static int conv_tc(const void* in, const void* wmat, void* out, int N, int P, int Q, int Cin, int Cout, int R, int S, int pad,
+                   bool dgrad, cudaStream_t st, const char* name) {
+  EncodeTiledFn enc = get_encode();
+  IIT_REQUIRE(enc != nullptr, "%s: cuTensorMapEncodeTiled is unavailable in this driver", name);
+  IIT_REQUIRE(Cin % TC_BK == 0 && Cout % 64 == 0, "%s: channels must be multiples of 64", name);
+  IIT_REQUIRE((reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(wmat) & 15) == 0 &&
+                  (reinterpret_cast<uintptr_t>(out) & 15) == 0, "%s: pointers must be 16-byte aligned", name);
+  TcParams p{};
+  p.N = N; p.P = P; p.Q = Q; p.Cin = Cin; p.Cout = Cout; p.R = R; p.S = S;
+  p.sign = dgrad ? -1 : 1;
+  p.off_h = dgrad ? pad : -pad;
+  p.off_w = dgrad ? pad : -pad;
+  p.BW = pow2_ge(Q) < 16 ? pow2_ge(Q) : 16;
+  int rem = TC_BM / p.BW;
+  p.BH = pow2_ge(P) < rem ? pow2_ge(P) : rem;
+  p.BNI = rem / p.BH;
+  p.tiles_w = (Q + p.BW - 1) / p.BW;
+  p.tiles_h = (P + p.BH - 1) / p.BH;
+  const int tiles_n = (N + p.BNI - 1) / p.BNI;
+  const int BN = (Cout % 128 == 0) ? 128 : 64;
+
+  CUtensorMap ma, mb;
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)Cin, (cuuint64_t)Q, (cuuint64_t)P, (cuuint64_t)N};
+    cuuint64_t strides[3] = {(cuuint64_t)Cin * 2, (cuuint64_t)Q * Cin * 2, (cuuint64_t)P * Q * Cin * 2};
+    cuuint32_t box[4] = {(cuuint32_t)TC_BK, (cuuint32_t)p.BW, (cuuint32_t)p.BH, (cuuint32_t)p.BNI};
+    cuuint32_t es[4] = {1, 1, 1, 1};
+    CUresult r = enc(&ma, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(in), dims, strides, box, es,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    IIT_REQUIRE(r == CUDA_SUCCESS, "%s: activation tensor map rejected (CUresult %d)", name, (int)r);
+  }
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)R * S * Cin, (cuuint64_t)Cout};
+    cuuint64_t strides[1] = {(cuuint64_t)R * S * Cin * 2};
+    cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)BN};
+    cuuint32_t es[2] = {1, 1};
+    CUresult r = enc(&mb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(wmat), dims, strides, box, es,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    IIT_REQUIRE(r == CUDA_SUCCESS, "%s: filter tensor map rejected (CUresult %d)", name, (int)r);
+  }
+  dim3 grid((unsigned)(p.tiles_w * p.tiles_h * tiles_n), (unsigned)(Cout / BN));
+  int rc = BN == 128 ? launch_tc<128>(ma, mb, (__nv_bfloat16*)out, p, grid, st)
+                     : launch_tc<64>(ma, mb, (__nv_bfloat16*)out, p, grid, st);
+  if (rc) return rc;
+  IIT_LAUNCH_CHECK(name);
+  return 0;
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// wgrad for 3x3 stride-1 convolutions on the tensor cores.
+//   dW[k, r, s, c] = sum over pixels  dy[pix, k] * x[pix shifted by (r-pad, s-pad), c]
+// Per filter row r one CTA accumulates the three taps s=0..2 of a [128 filters x CB channels] block in
+// TMEM (3*CB fp32 columns) while streaming boxes of 64 pixels (the GEMM K dimension):
+//   A = dy box  [64 pixels x 128 filters]   (two 64-channel TMA boxes; the second is out of bounds and
+//                                             therefore zero-filled when the layer has only 64 filters)
+//   B = x box shifted by the tap [64 pixels x CB channels], three of them per stage
+// Both operands are "MN-major" (channels contiguous, pixels strided): exactly how NHWC rows land in
+// shared memory, so no transpose is needed; the UMMA descriptors say so (a_major = b_major = MN).
+// Pixels are split across gridDim.x CTAs; partial sums go to fp32 scratch and are reduced in fixed order.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return (uint64_t)((smem_addr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
+         ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+
+struct TcWgradParams {
+  int N, P, Q, Cin, Cout, pad;
+  int BW, BH, BNI, tiles_w, tiles_h, tiles_n;
+  int chunks_per_split, total_chunks;
+  int ncblk;
+};
+
+template <int CB, int STAGES>
+__global__ void __launch_bounds__(TC_THREADS) wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap map_dy,
+                                                                 const __grid_constant__ CUtensorMap map_x,
+                                                                 float* __restrict__ part, TcWgradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr uint32_t BOX = 64 * 64 * 2;                 // one TMA box: 64 pixels x 64 channels bf16
+  constexpr uint32_t A_BYTES = 2 * BOX;                 // 128 filters
+  constexpr uint32_t B_TAP = (CB / 64) * BOX;           // CB channels
+  constexpr uint32_t STAGE_BYTES = A_BYTES + 3 * B_TAP;
+  constexpr uint32_t TMEM_COLS = (3 * CB <= 256) ? 256 : 512;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tmem_full = empty + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int split = blockIdx.x, r = blockIdx.y;
+  const int kblk = blockIdx.z / p.ncblk, cblk = blockIdx.z - kblk * p.ncblk;
+  const int chunk_lo = split * p.chunks_per_split;
+  int chunk_hi = chunk_lo + p.chunks_per_split;
+  if (chunk_hi > p.total_chunks) chunk_hi = p.total_chunks;
+  const int nchunks = chunk_hi > chunk_lo ? chunk_hi - chunk_lo : 0;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(tmem_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TMEM_COLS));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_dy)) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_x)) : "memory");
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int ch = chunk_lo; ch < chunk_hi; ++ch) {
+        int t = ch;
+        const int tw = t % p.tiles_w; t /= p.tiles_w;
+        const int th = t % p.tiles_h; t /= p.tiles_h;
+        const int n0 = t * p.BNI, p0 = th * p.BH, q0 = tw * p.BW;
+        uint8_t* st = smem + stage * STAGE_BYTES;
+        mbar_wait(&empty[stage], phase ^ 1);
+        mbar_expect_tx(&full[stage], STAGE_BYTES);
+        tma_load_4d(st, &map_dy, &full[stage], kblk * 128, q0, p0, n0);
+        tma_load_4d(st + BOX, &map_dy, &full[stage], kblk * 128 + 64, q0, p0, n0);
+#pragma unroll
+        for (int s = 0; s < 3; ++s)
+#pragma unroll
+          for (int j = 0; j < CB / 64; ++j)
+            tma_load_4d(st + A_BYTES + s * B_TAP + j * BOX, &map_x, &full[stage], cblk * CB + j * 64, q0 + s - p.pad,
+                        p0 + r - p.pad, n0);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && nchunks > 0) {
+      // D=f32, A=B=bf16, A and B MN-major (bits 15, 16), N = CB, M = 128
+      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(CB >> 3) << 17) |
+                                 ((uint32_t)(128 >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int i = 0; i < nchunks; ++i) {
+        mbar_wait(&full[stage], phase);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t a0 = smem_u32(smem + stage * STAGE_BYTES);
+        const uint32_t b0 = a0 + A_BYTES;
+#pragma unroll
+        for (int s = 0; s < 3; ++s) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {   // 64 pixels = 4 x UMMA_K(16); 16 pixel rows = 2048 bytes
+            umma_bf16(tmem_base + s * CB, umma_desc_mn_sw128(a0 + k * 2048, BOX), umma_desc_mn_sw128(b0 + s * B_TAP + k * 2048, BOX),
+                      idesc, (uint32_t)((i | k) != 0));
+          }
+        }
+        umma_commit(&empty[stage]);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      umma_commit(tmem_full);
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int m = quarter * 32 + lane;
+    const int k = kblk * 128 + m;
+    const int64_t rsc = (int64_t)9 * p.Cin;
+    float* dst = part + ((int64_t)split * p.Cout + k) * rsc + (int64_t)(r * 3) * p.Cin + cblk * CB;
+    if (nchunks > 0) {
+      mbar_wait(tmem_full, 0);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+#pragma unroll
+      for (int c = 0; c < CB; c += 32) {
+        uint32_t v[32];
+        if (nchunks > 0) {
+          tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(s * CB + c), v);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0u;
+        }
+        if (k < p.Cout) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<uint4*>(dst + (int64_t)s * p.Cin + c + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS));
+  }
+}
+
+__global__ void __launch_bounds__(256) tc_splitk_reduce_kernel(const float* __restrict__ part, float* __restrict__ out,
+                                                               int64_t n, int splits) {
+  const int64_t n4 = n >> 2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int z = 0; z < splits; ++z) {  // fixed order: deterministic
+      float4 v = reinterpret_cast<const float4*>(part + (int64_t)z * n)[i];
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    reinterpret_cast<float4*>(out)[i] = s;
+  }
+}
+
+static void wgrad_tc_plan(const iit_conv_t* d, TcWgradParams* p, int* splits, int* CB) {
+  p->N = d->n; p->P = d->p; p->Q = d->q; p->Cin = d->c; p->Cout = d->k; p->pad = d->pad;
+  p->BW = pow2_ge(d->q) < 16 ? pow2_ge(d->q) : 16;
+  int rem = 64 / p->BW;
+  p->BH = pow2_ge(d->p) < rem ? pow2_ge(d->p) : rem;
+  p->BNI = rem / p->BH;
+  p->tiles_w = (d->q + p->BW - 1) / p->BW;
+  p->tiles_h = (d->p + p->BH - 1) / p->BH;
+  p->tiles_n = (d->n + p->BNI - 1) / p->BNI;
+  p->total_chunks = p->tiles_w * p->tiles_h * p->tiles_n;
+  *CB = d->c >= 128 ? 128 : 64;
+  p->ncblk = d->c / *CB;
+  int groups = 3 * ((d->k + 127) / 128) * p->ncblk;
+  int want = (kNumSMs + groups - 1) / groups;
+  int maxs = (p->total_chunks + 7) / 8;   // at least 8 chunks (512 pixels) per CTA
+  if (want > maxs) want = maxs;
+  if (want < 1) want = 1;
+  p->chunks_per_split = (p->total_chunks + want - 1) / want;
+  *splits = (p->total_chunks + p->chunks_per_split - 1) / p->chunks_per_split;
+}
+
+template <int CB>
+static int launch_wgrad_tc(const CUtensorMap& mdy, const CUtensorMap& mx, float* part, const TcWgradParams& p, dim3 grid,
+                           cudaStream_t st) {
+  constexpr int STAGES = CB == 64 ? 4 : 3;
+  constexpr size_t smem = STAGES * (2 + 3 * (CB / 64)) * 8192 + (2 * STAGES + 1) * 8 + 16 + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    IIT_CUDA(cudaFuncSetAttribute(wgrad3x3_tc_kernel<CB, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = true;
+  }
+  wgrad3x3_tc_kernel<CB, STAGES><<<grid, TC_THREADS, smem, st>>>(mdy, mx, part, p);
+  return 0;
+}
+
+static int encode_nhwc(CUtensorMap* m, const void* ptr, int C, int W, int H, int N, int bw, int bh, int bn, const char* name) {
+  EncodeTiledFn enc = get_encode();
+  IIT_REQUIRE(enc != nullptr, "%s: cuTensorMapEncodeTiled is unavailable in this driver", name);
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn};
+  cuuint32_t es[4] = {1, 1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  IIT_REQUIRE(r == CUDA_SUCCESS, "%s: tensor map rejected (CUresult %d)", name, (int)r);
+  return 0;
+}
+
+}  // namespace iit
+
+using namespace iit;
+
+extern "C" int iit_conv2d_tc_supported(const iit_conv_t* d, int dtype) {
+  if (!d || dtype != IIT_BF16) return 0;
+  return d->r == 3 && d->s == 3 && d->stride == 1 && d->pad == 1 && d->c % 64 == 0 && d->k % 64 == 0 && d->p == d->h &&
+         d->q == d->w;
+}
+
+extern "C" int iit_conv2d_fprop_tc(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, void* stream) {
+  IIT_REQUIRE(x && w_krsc && y && d, "iit_conv2d_fprop_tc: null pointer");
+  IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "iit_conv2d_fprop_tc: only bf16 3x3 stride-1 pad-1 convolutions with "
+              "channel counts that are multiples of 64");
+  return conv_tc(x, w_krsc, y, d->n, d->p, d->q, d->c, d->k, d->r, d->s, d->pad, false, as_stream(stream), "iit_conv2d_fprop_tc");
+}
+
+extern "C" int iit_conv2d_dgrad_tc(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream) {
+  IIT_REQUIRE(dy && w_crsk && dx && d, "iit_conv2d_dgrad_tc: null pointer");
+  IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "iit_conv2d_dgrad_tc: only bf16 3x3 stride-1 pad-1 convolutions with "
+              "channel counts that are multiples of 64");
+  // gathered tensor = dy [n,p,q,k]; produced = dx [n,h,w,c]; reduction over (r,s,k)
+  return conv_tc(dy, w_crsk, dx, d->n, d->h, d->w, d->k, d->c, d->r, d->s, d->pad, true, as_stream(stream), "iit_conv2d_dgrad_tc");
+}
+
+extern "C" size_t iit_conv2d_wgrad_tc_scratch_bytes(const iit_conv_t* d) {
+  if (!d || !iit_conv2d_tc_supported(d, IIT_BF16)) return 0;
+  TcWgradParams p;
+  int splits, CB;
+  wgrad_tc_plan(d, &p, &splits, &CB);
+  return (size_t)splits * d->k * 9 * d->c * sizeof(float);
+}
+
+extern "C" int iit_conv2d_wgrad_tc(const void* dy, const void* x, float* dw, const iit_conv_t* d, void* scratch,
+                                   size_t scratch_bytes, void* stream) {
+  IIT_REQUIRE(dy && x && dw && d, "iit_conv2d_wgrad_tc: null pointer");
+  IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "iit_conv2d_wgrad_tc: only bf16 3x3 stride-1 pad-1 convolutions with "
+              "channel counts that are multiples of 64");
+  TcWgradParams p;
+  int splits, CB;
+  wgrad_tc_plan(d, &p, &splits, &CB);
+  size_t need = (size_t)splits * d->k * 9 * d->c * sizeof(float);
+  IIT_REQUIRE(scratch && scratch_bytes >= need, "iit_conv2d_wgrad_tc: scratch too small: need %zu bytes, got %zu", need, scratch_bytes);
+  IIT_REQUIRE((reinterpret_cast<uintptr_t>(scratch) & 15) == 0 && (reinterpret_cast<uintptr_t>(dw) & 15) == 0,
+              "iit_conv2d_wgrad_tc: scratch and dw must be 16-byte aligned");
+  CUtensorMap mdy, mx;
+  if (encode_nhwc(&mdy, dy, d->k, d->q, d->p, d->n, p.BW, p.BH, p.BNI, "iit_conv2d_wgrad_tc(dy)")) return 1;
+  if (encode_nhwc(&mx, x, d->c, d->w, d->h, d->n, p.BW, p.BH, p.BNI, "iit_conv2d_wgrad_tc(x)")) return 1;
+  cudaStream_t st = as_stream(stream);
+  dim3 grid((unsigned)splits, 3, (unsigned)(((d->k + 127) / 128) * p.ncblk));
+  int rc = CB == 128 ? launch_wgrad_tc<128>(mdy, mx, (float*)scratch, p, grid, st)
+                     : launch_wgrad_tc<64>(mdy, mx, (float*)scratch, p, grid, st);
+  if (rc) return rc;
+  IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc");
+  int64_t n = (int64_t)d->k * 9 * d->c;
+  tc_splitk_reduce_kernel<<<grid_for(n / 4, 256), 256, 0, st>>>((const float*)scratch, dw, n, splits);
+  IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc(reduce)");
+  return 0;
+}

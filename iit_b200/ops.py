@@ -18,6 +18,9 @@ from . import _lib
 from ._lib import Box, Conv, call
 
 _DT = {torch.float32: _lib.IIT_F32, torch.bfloat16: _lib.IIT_BF16}
+# bf16 convolutions that qualify run on the tcgen05 tensor-core kernels; the CUDA-core kernels remain the
+# exact-fp32 path and the catch-all. (A switch for A/B measurements, not a fallback: both are this library.)
+USE_TENSOR_CORES = True
 
 
 def _require_cuda(*tensors):
@@ -311,9 +314,15 @@ class _ConvFn(torch.autograd.Function):
         s0 = s1 = None
         if bn_sums is not None:
             s0, s1 = bn_sums[0], bn_sums[1]
-        call("iit_conv2d_fprop", _p(x), _p(w_krsc), _p(y), C.byref(d), _dt(x), _p(s0), _p(s1), _stream())
+        tc = USE_TENSOR_CORES and bool(_lib.lib.iit_conv2d_tc_supported(C.byref(d), _dt(x)))
+        if tc:  # tcgen05 + TMA implicit GEMM; BN statistics (if wanted) by the statistics kernel
+            call("iit_conv2d_fprop_tc", _p(x), _p(w_krsc), _p(y), C.byref(d), _stream())
+            if s0 is not None:
+                call("iit_bn_stats", _p(y), _dt(y), d.n * d.p * d.q, k, _p(s0), _p(s1), _stream())
+        else:
+            call("iit_conv2d_fprop", _p(x), _p(w_krsc), _p(y), C.byref(d), _dt(x), _p(s0), _p(s1), _stream())
         ctx.save_for_backward(x, weight)
-        ctx.d, ctx.w_crsk_fn = d, w_crsk_fn
+        ctx.d, ctx.w_crsk_fn, ctx.tc = d, w_crsk_fn, tc
         return y
 
     @staticmethod
@@ -324,12 +333,20 @@ class _ConvFn(torch.autograd.Function):
         dx = dw = None
         if ctx.needs_input_grad[0]:
             dx = empty_cl(d.n, d.c, d.h, d.w, x.dtype, x.device)
-            call("iit_conv2d_dgrad", _p(dy), _p(ctx.w_crsk_fn()), _p(dx), C.byref(d), _dt(x), _stream())
+            if ctx.tc:
+                call("iit_conv2d_dgrad_tc", _p(dy), _p(ctx.w_crsk_fn()), _p(dx), C.byref(d), _stream())
+            else:
+                call("iit_conv2d_dgrad", _p(dy), _p(ctx.w_crsk_fn()), _p(dx), C.byref(d), _dt(x), _stream())
         if ctx.needs_input_grad[1]:
             dwb = torch.empty((d.k, d.r, d.s, d.c), dtype=torch.float32, device=x.device)
-            need = int(_lib.lib.iit_conv2d_wgrad_scratch_bytes(C.byref(d)))
-            scratch = torch.empty(need, dtype=torch.uint8, device=x.device) if need else None
-            call("iit_conv2d_wgrad", _p(dy), _p(x), _p(dwb), C.byref(d), _dt(x), _p(scratch), need, _stream())
+            if ctx.tc:
+                need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
+                scratch = torch.empty(need, dtype=torch.uint8, device=x.device)
+                call("iit_conv2d_wgrad_tc", _p(dy), _p(x), _p(dwb), C.byref(d), _p(scratch), need, _stream())
+            else:
+                need = int(_lib.lib.iit_conv2d_wgrad_scratch_bytes(C.byref(d)))
+                scratch = torch.empty(need, dtype=torch.uint8, device=x.device) if need else None
+                call("iit_conv2d_wgrad", _p(dy), _p(x), _p(dwb), C.byref(d), _dt(x), _p(scratch), need, _stream())
             dw = dwb.permute(0, 3, 1, 2)  # [K,C,R,S] view with channels-last strides, like the parameter
         return dx, dw, None, None, None, None, None
 

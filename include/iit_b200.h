@@ -145,6 +145,19 @@ int iit_conv2d_dgrad(const void* dy, const void* w_crsk, void* dx, const iit_con
 size_t iit_conv2d_wgrad_scratch_bytes(const iit_conv_t* d);
 int iit_conv2d_wgrad(const void* dy, const void* x, float* dw, const iit_conv_t* d, int dtype,
                      void* scratch, size_t scratch_bytes, void* stream);
+/* Tensor-core path (tcgen05.mma + TMA + TMEM accumulator) for bf16 3x3 stride-1 pad-1 convolutions whose
+ * channel counts are multiples of 64 -- 80 % of ResNet-18's FLOPs. Same results contract as
+ * iit_conv2d_fprop / iit_conv2d_dgrad (fp32 accumulation, bf16 output); w_krsc / w_crsk are bf16.
+ * iit_conv2d_tc_supported() returns 1 when a descriptor qualifies. */
+int iit_conv2d_tc_supported(const iit_conv_t* d, int dtype);
+int iit_conv2d_fprop_tc(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, void* stream);
+int iit_conv2d_dgrad_tc(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream);
+/* dw[k,r,s,c] fp32: pixels are the GEMM K dimension (MN-major operands straight from NHWC), split across
+ * CTAs; scratch holds the per-split partial sums (iit_conv2d_wgrad_tc_scratch_bytes), reduced in fixed order. */
+size_t iit_conv2d_wgrad_tc_scratch_bytes(const iit_conv_t* d);
+int iit_conv2d_wgrad_tc(const void* dy, const void* x, float* dw, const iit_conv_t* d, void* scratch,
+                        size_t scratch_bytes, void* stream);
+
 /* filter re-layout: fp32 master filter addressed as [k,c,r,s] through the 4 element strides given
  * (any memory format) -> dense KRSC (to_crsk=0) or CRSK (to_crsk=1) in `dtype`. */
 int iit_filter_relayout(const float* w, const int64_t* strides_kcrs, void* w_out, int k, int c, int r,

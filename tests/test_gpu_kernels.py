@@ -356,3 +356,36 @@ def test_flat_adam_matches_torch_adam_with_clip(ops):
         opt.step(max_norm=1.0)
         for p, q in zip(ref, mine):
             torch.testing.assert_close(q.detach().cpu(), p.detach(), rtol=1e-5, atol=1e-7)
+
+
+def test_tensor_core_path_is_taken_and_matches_cuda_core_path(ops):
+    """bf16 3x3 stride-1 convolutions go through the tcgen05/TMA kernels; results must agree with the
+    CUDA-core kernels of the same library on identical bf16 operands (both accumulate in fp32; only the
+    summation order differs): 2 bf16 ulps of the output scale."""
+    from iit_b200.nn.resnet import Conv2d
+    g = torch.Generator().manual_seed(11)
+    for (c, k, hw, n) in [(64, 64, 14, 9), (128, 128, 7, 5), (256, 256, 4, 11), (512, 512, 2, 37), (64, 64, 21, 3),
+                          (64, 128, 14, 4)]:
+        conv = Conv2d(c, k, 3, 1, 1).to(DEV)
+        x = torch.randn(n, c, hw, hw, generator=g).to(DEV).bfloat16().contiguous(memory_format=torch.channels_last)
+        gy = torch.randn(n, k, hw, hw, generator=g).to(DEV).bfloat16().contiguous(memory_format=torch.channels_last)
+        outs = {}
+        for use_tc in (True, False):
+            ops.USE_TENSOR_CORES = use_tc
+            seen = []
+            inner = ops.call
+            ops.call = lambda name, *a, inner=inner, seen=seen: (seen.append(name), inner(name, *a))[1]
+            try:
+                xd = x.clone().requires_grad_(True)
+                conv.weight.grad = None
+                y = conv(xd)
+                y.backward(gy)
+            finally:
+                ops.call = inner
+                ops.USE_TENSOR_CORES = True
+            assert ("iit_conv2d_fprop_tc" in seen) == use_tc and ("iit_conv2d_dgrad_tc" in seen) == use_tc, seen
+            assert ("iit_conv2d_wgrad_tc" in seen) == use_tc, seen
+            outs[use_tc] = (y.detach().float(), xd.grad.float(), conv.weight.grad.detach().float().clone())
+        for a, b, what in zip(outs[True], outs[False], ("fprop", "dgrad", "wgrad")):
+            scale = b.abs().max().item()
+            assert (a - b).abs().max().item() <= 2 * 2 ** -8 * scale, (what, c, k, hw)
