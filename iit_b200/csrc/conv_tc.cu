@@ -92,13 +92,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 }
 
 struct TcParams {
-  int N, P, Q;          // output pixel grid (== input grid: stride 1, "same" padding)
-  int Cin, Cout;        // reduction channels per tap / produced channels
-  int R, S;
-  int off_h, off_w;     // input row = p + sign*r + off_h   (fprop: sign=+1, off=-pad; dgrad: sign=-1, off=+pad)
-  int sign;
-  int BW, BH, BNI;      // pixel box
-  int tiles_w, tiles_h; // boxes per image row / column
+  int N, P, Q;            // pixel grid enumerated by the tiles (a parity class of the output for strided dgrad)
+  int OH, OW;             // full spatial size of the produced tensor
+  int out_mul, out_oh, out_ow;  // produced pixel = (p*out_mul + out_oh, q*out_mul + out_ow)
+  int in_mul;             // gathered row = p*in_mul + dh[tap] (the tensor map strides by in_mul too)
+  int Cin, Cout;          // reduction channels per tap / produced channels
+  int ntaps;              // 0 => the class receives no contribution: zeros are written
+  int8_t dh[9], dw[9];    // per-tap offset into the gathered tensor
+  int8_t wk[9];           // per-tap block index in the filter matrix (reduction offset = wk*Cin)
+  int BW, BH, BNI;        // pixel box
+  int tiles_w, tiles_h;   // boxes per image row / column
 };
 
 template <int BN, int STAGES>
@@ -124,7 +127,7 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
   const int n0 = t * p.BNI, p0 = th * p.BH, q0 = tw * p.BW;
   const int co0 = blockIdx.y * BN;
   const int kchunks = p.Cin / TC_BK;
-  const int nk = p.R * p.S * kchunks;
+  const int nk = p.ntaps * kchunks;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
@@ -148,12 +151,11 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
       uint32_t phase = 0;
       for (int kb = 0; kb < nk; ++kb) {
         const int tap = kb / kchunks, kc = kb - tap * kchunks;
-        const int r = tap / p.S, s = tap - r * p.S;
         mbar_wait(&empty[stage], phase ^ 1);
         mbar_expect_tx(&full[stage], A_BYTES + B_BYTES);
-        tma_load_4d(sA + stage * A_BYTES, &map_a, &full[stage], kc * TC_BK, q0 + p.sign * s + p.off_w,
-                    p0 + p.sign * r + p.off_h, n0);
-        tma_load_2d(sB + stage * B_BYTES, &map_b, &full[stage], tap * p.Cin + kc * TC_BK, co0);
+        tma_load_4d(sA + stage * A_BYTES, &map_a, &full[stage], kc * TC_BK, q0 * p.in_mul + p.dw[tap],
+                    p0 * p.in_mul + p.dh[tap], n0);
+        tma_load_2d(sB + stage * B_BYTES, &map_b, &full[stage], p.wk[tap] * p.Cin + kc * TC_BK, co0);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
@@ -175,7 +177,7 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
         umma_commit(&empty[stage]);  // frees this smem stage once the MMAs above have read it
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
-      umma_commit(tmem_full);        // accumulator complete
+      if (nk > 0) umma_commit(tmem_full);  // accumulator complete
     }
   } else {
     // epilogue: warp w may read TMEM lanes [32*(w%4), 32*(w%4)+32)
@@ -186,13 +188,20 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
     const int nl = m / (p.BW * p.BH);
     const int n = n0 + nl, pp = p0 + hl, qq = q0 + wl;
     const bool ok = n < p.N && pp < p.P && qq < p.Q;
-    __nv_bfloat16* dst = out + (((int64_t)n * p.P + pp) * p.Q + qq) * p.Cout + co0;
-    mbar_wait(tmem_full, 0);
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    __nv_bfloat16* dst = out + (((int64_t)n * p.OH + (pp * p.out_mul + p.out_oh)) * p.OW + (qq * p.out_mul + p.out_ow)) * p.Cout + co0;
+    if (nk > 0) {
+      mbar_wait(tmem_full, 0);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
 #pragma unroll
     for (int c = 0; c < BN; c += 32) {
       uint32_t v[32];
-      tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c, v);
+      if (nk > 0) {
+        tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c, v);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = 0u;
+      }
       if (ok) {
 #pragma unroll
         for (int j = 0; j < 32; j += 8) {
@@ -249,57 +258,116 @@ static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16
   return 0;
 }
 
-// in: [N,P,Q,Cin] bf16 NHWC;  wmat: [Cout][R*S*Cin] bf16;  out: [N,P,Q,Cout] bf16
-static int conv_tc(const void* in, const void* wmat, void* out, int N, int P, int Q, int Cin, int Cout, int R, int S, int pad,
-                   bool dgrad, cudaStream_t st, const char* name) {
+static void plan_box(int P, int Q, int pixels, int* BW, int* BH, int* BNI) {
+  *BW = pow2_ge(Q) < 16 ? pow2_ge(Q) : 16;
+  int rem = pixels / *BW;
+  *BH = pow2_ge(P) < rem ? pow2_ge(P) : rem;
+  *BNI = rem / *BH;
+}
+
+static int encode_nhwc_strided(CUtensorMap* m, const void* ptr, int C, int W, int H, int N, int bw, int bh, int bn, int es_hw,
+                               const char* name) {
   EncodeTiledFn enc = get_encode();
   IIT_REQUIRE(enc != nullptr, "%s: cuTensorMapEncodeTiled is unavailable in this driver", name);
-  IIT_REQUIRE(Cin % TC_BK == 0 && Cout % 64 == 0, "%s: channels must be multiples of 64", name);
-  IIT_REQUIRE((reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(wmat) & 15) == 0 &&
-                  (reinterpret_cast<uintptr_t>(out) & 15) == 0, "%s: pointers must be 16-byte aligned", name);
-  TcParams p{};
-  p.N = N; p.P = P; p.Q = Q; p.Cin = Cin; p.Cout = Cout; p.R = R; p.S = S;
-  p.sign = dgrad ? -1 : 1;
-  p.off_h = dgrad ? pad : -pad;
-  p.off_w = dgrad ? pad : -pad;
-  p.BW = pow2_ge(Q) < 16 ? pow2_ge(Q) : 16;
-  int rem = TC_BM / p.BW;
-  p.BH = pow2_ge(P) < rem ? pow2_ge(P) : rem;
-  p.BNI = rem / p.BH;
-  p.tiles_w = (Q + p.BW - 1) / p.BW;
-  p.tiles_h = (P + p.BH - 1) / p.BH;
-  const int tiles_n = (N + p.BNI - 1) / p.BNI;
-  const int BN = (Cout % 128 == 0) ? 128 : 64;
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  // with an element stride e the box is given in traversed elements: e*n to load n
+  cuuint32_t box[4] = {64, (cuuint32_t)(bw * es_hw), (cuuint32_t)(bh * es_hw), (cuuint32_t)bn};
+  cuuint32_t es[4] = {1, (cuuint32_t)es_hw, (cuuint32_t)es_hw, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  IIT_REQUIRE(r == CUDA_SUCCESS, "%s: tensor map rejected (CUresult %d)", name, (int)r);
+  return 0;
+}
 
+static int encode_filter(CUtensorMap* m, const void* wmat, int Kg, int rows, int BN, const char* name) {
+  EncodeTiledFn enc = get_encode();
+  IIT_REQUIRE(enc != nullptr, "%s: cuTensorMapEncodeTiled is unavailable in this driver", name);
+  cuuint64_t dims[2] = {(cuuint64_t)Kg, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)Kg * 2};
+  cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)BN};
+  cuuint32_t es[2] = {1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(wmat), dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  IIT_REQUIRE(r == CUDA_SUCCESS, "%s: filter tensor map rejected (CUresult %d)", name, (int)r);
+  return 0;
+}
+
+// One launch: the produced pixels (p*out_mul+out_oh, q*out_mul+out_ow), p<P, q<Q, from the taps listed in `tp`.
+static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const void* wmat, int Kg, void* out, TcParams tp,
+                          cudaStream_t st, const char* name) {
+  plan_box(tp.P, tp.Q, TC_BM, &tp.BW, &tp.BH, &tp.BNI);
+  tp.tiles_w = (tp.Q + tp.BW - 1) / tp.BW;
+  tp.tiles_h = (tp.P + tp.BH - 1) / tp.BH;
+  const int tiles_n = (tp.N + tp.BNI - 1) / tp.BNI;
+  const int BN = (tp.Cout % 128 == 0) ? 128 : 64;
   CUtensorMap ma, mb;
-  {
-    cuuint64_t dims[4] = {(cuuint64_t)Cin, (cuuint64_t)Q, (cuuint64_t)P, (cuuint64_t)N};
-    cuuint64_t strides[3] = {(cuuint64_t)Cin * 2, (cuuint64_t)Q * Cin * 2, (cuuint64_t)P * Q * Cin * 2};
-    cuuint32_t box[4] = {(cuuint32_t)TC_BK, (cuuint32_t)p.BW, (cuuint32_t)p.BH, (cuuint32_t)p.BNI};
-    cuuint32_t es[4] = {1, 1, 1, 1};
-    CUresult r = enc(&ma, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(in), dims, strides, box, es,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    IIT_REQUIRE(r == CUDA_SUCCESS, "%s: activation tensor map rejected (CUresult %d)", name, (int)r);
-  }
-  {
-    cuuint64_t dims[2] = {(cuuint64_t)R * S * Cin, (cuuint64_t)Cout};
-    cuuint64_t strides[1] = {(cuuint64_t)R * S * Cin * 2};
-    cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)BN};
-    cuuint32_t es[2] = {1, 1};
-    CUresult r = enc(&mb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(wmat), dims, strides, box, es,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    IIT_REQUIRE(r == CUDA_SUCCESS, "%s: filter tensor map rejected (CUresult %d)", name, (int)r);
-  }
-  dim3 grid((unsigned)(p.tiles_w * p.tiles_h * tiles_n), (unsigned)(Cout / BN));
-  int rc = BN == 128 ? launch_tc<128>(ma, mb, (__nv_bfloat16*)out, p, grid, st)
-                     : launch_tc<64>(ma, mb, (__nv_bfloat16*)out, p, grid, st);
+  if (encode_nhwc_strided(&ma, gathered, gC, gW, gH, tp.N, tp.BW, tp.BH, tp.BNI, tp.in_mul, name)) return 1;
+  if (encode_filter(&mb, wmat, Kg, tp.Cout, BN, name)) return 1;
+  dim3 grid((unsigned)(tp.tiles_w * tp.tiles_h * tiles_n), (unsigned)(tp.Cout / BN));
+  int rc = BN == 128 ? launch_tc<128>(ma, mb, (__nv_bfloat16*)out, tp, grid, st)
+                     : launch_tc<64>(ma, mb, (__nv_bfloat16*)out, tp, grid, st);
   if (rc) return rc;
   IIT_LAUNCH_CHECK(name);
   return 0;
 }
 
+static int check_tc_ptrs(const void* a, const void* b, const void* c, const char* name) {
+  IIT_REQUIRE(((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(c)) & 15) == 0,
+              "%s: pointers must be 16-byte aligned", name);
+  return 0;
+}
+
+// y[n,p,q,k] = sum_{r,s,c} x[n, p*stride - pad + r, q*stride - pad + s, c] * w[k,r,s,c]
+static int conv_tc_fprop(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, cudaStream_t st) {
+  const char* name = "iit_conv2d_fprop_tc";
+  if (check_tc_ptrs(x, w_krsc, y, name)) return 1;
+  TcParams tp{};
+  tp.N = d->n; tp.P = d->p; tp.Q = d->q; tp.OH = d->p; tp.OW = d->q;
+  tp.out_mul = 1; tp.out_oh = 0; tp.out_ow = 0; tp.in_mul = d->stride;
+  tp.Cin = d->c; tp.Cout = d->k;
+  tp.ntaps = d->r * d->s;
+  for (int r = 0; r < d->r; ++r)
+    for (int s = 0; s < d->s; ++s) {
+      int t = r * d->s + s;
+      tp.dh[t] = (int8_t)(r - d->pad); tp.dw[t] = (int8_t)(s - d->pad); tp.wk[t] = (int8_t)t;
+    }
+  return conv_tc_launch(x, d->c, d->w, d->h, w_krsc, d->r * d->s * d->c, y, tp, st, name);
+}
+
+// dx[n,h,w,c] = sum_{r,s,k} dy[n,(h+pad-r)/stride,(w+pad-s)/stride,k] * w[k,r,s,c]  over exact divisions.
+// For stride 2 the output splits into four parity classes, each a stride-1 gather of dy with its own taps.
+static int conv_tc_dgrad(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, cudaStream_t st) {
+  const char* name = "iit_conv2d_dgrad_tc";
+  if (check_tc_ptrs(dy, w_crsk, dx, name)) return 1;
+  const int st_ = d->stride;
+  for (int a = 0; a < st_; ++a)
+    for (int b = 0; b < st_; ++b) {
+      TcParams tp{};
+      tp.N = d->n; tp.OH = d->h; tp.OW = d->w;
+      tp.P = (d->h - a + st_ - 1) / st_; tp.Q = (d->w - b + st_ - 1) / st_;
+      if (tp.P <= 0 || tp.Q <= 0) continue;
+      tp.out_mul = st_; tp.out_oh = a; tp.out_ow = b; tp.in_mul = 1;
+      tp.Cin = d->k; tp.Cout = d->c;
+      int nt = 0;
+      for (int r = 0; r < d->r; ++r) {
+        if ((a + d->pad - r) % st_ != 0) continue;
+        for (int s = 0; s < d->s; ++s) {
+          if ((b + d->pad - s) % st_ != 0) continue;
+          // floor division is exact here; negative numerators stay exact multiples
+          tp.dh[nt] = (int8_t)((a + d->pad - r) / st_); tp.dw[nt] = (int8_t)((b + d->pad - s) / st_);
+          tp.wk[nt] = (int8_t)(r * d->s + s);
+          ++nt;
+        }
+      }
+      tp.ntaps = nt;
+      int rc = conv_tc_launch(dy, d->k, d->q, d->p, w_crsk, d->r * d->s * d->k, dx, tp, st, name);
+      if (rc) return rc;
+    }
+  return 0;
+}
 
 // ------------------------------------------------------------------------------------------------
 // wgrad for 3x3 stride-1 convolutions on the tensor cores.
@@ -319,13 +387,13 @@ __device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint3
 }
 
 struct TcWgradParams {
-  int N, P, Q, Cin, Cout, pad;
+  int N, P, Q, Cin, Cout, pad, stride, R, S;
   int BW, BH, BNI, tiles_w, tiles_h, tiles_n;
   int chunks_per_split, total_chunks;
   int ncblk;
 };
 
-template <int CB, int STAGES>
+template <int CB, int S, int STAGES>
 __global__ void __launch_bounds__(TC_THREADS) wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap map_dy,
                                                                  const __grid_constant__ CUtensorMap map_x,
                                                                  float* __restrict__ part, TcWgradParams p) {
@@ -334,8 +402,8 @@ __global__ void __launch_bounds__(TC_THREADS) wgrad3x3_tc_kernel(const __grid_co
   constexpr uint32_t BOX = 64 * 64 * 2;                 // one TMA box: 64 pixels x 64 channels bf16
   constexpr uint32_t A_BYTES = 2 * BOX;                 // 128 filters
   constexpr uint32_t B_TAP = (CB / 64) * BOX;           // CB channels
-  constexpr uint32_t STAGE_BYTES = A_BYTES + 3 * B_TAP;
-  constexpr uint32_t TMEM_COLS = (3 * CB <= 256) ? 256 : 512;
+  constexpr uint32_t STAGE_BYTES = A_BYTES + S * B_TAP;
+  constexpr uint32_t TMEM_COLS = (S * CB <= 64) ? 64 : (S * CB <= 128) ? 128 : (S * CB <= 256) ? 256 : 512;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
   uint64_t* empty = full + STAGES;
   uint64_t* tmem_full = empty + STAGES;
@@ -380,11 +448,11 @@ __global__ void __launch_bounds__(TC_THREADS) wgrad3x3_tc_kernel(const __grid_co
         tma_load_4d(st, &map_dy, &full[stage], kblk * 128, q0, p0, n0);
         tma_load_4d(st + BOX, &map_dy, &full[stage], kblk * 128 + 64, q0, p0, n0);
 #pragma unroll
-        for (int s = 0; s < 3; ++s)
+        for (int s = 0; s < S; ++s)
 #pragma unroll
           for (int j = 0; j < CB / 64; ++j)
-            tma_load_4d(st + A_BYTES + s * B_TAP + j * BOX, &map_x, &full[stage], cblk * CB + j * 64, q0 + s - p.pad,
-                        p0 + r - p.pad, n0);
+            tma_load_4d(st + A_BYTES + s * B_TAP + j * BOX, &map_x, &full[stage], cblk * CB + j * 64,
+                        q0 * p.stride + s - p.pad, p0 * p.stride + r - p.pad, n0);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
@@ -401,7 +469,7 @@ __global__ void __launch_bounds__(TC_THREADS) wgrad3x3_tc_kernel(const __grid_co
         const uint32_t a0 = smem_u32(smem + stage * STAGE_BYTES);
         const uint32_t b0 = a0 + A_BYTES;
 #pragma unroll
-        for (int s = 0; s < 3; ++s) {
+        for (int s = 0; s < S; ++s) {
 #pragma unroll
           for (int k = 0; k < 4; ++k) {   // 64 pixels = 4 x UMMA_K(16); 16 pixel rows = 2048 bytes
             umma_bf16(tmem_base + s * CB, umma_desc_mn_sw128(a0 + k * 2048, BOX), umma_desc_mn_sw128(b0 + s * B_TAP + k * 2048, BOX),
@@ -417,14 +485,14 @@ __global__ void __launch_bounds__(TC_THREADS) wgrad3x3_tc_kernel(const __grid_co
     const int quarter = warp & 3;
     const int m = quarter * 32 + lane;
     const int k = kblk * 128 + m;
-    const int64_t rsc = (int64_t)9 * p.Cin;
-    float* dst = part + ((int64_t)split * p.Cout + k) * rsc + (int64_t)(r * 3) * p.Cin + cblk * CB;
+    const int64_t rsc = (int64_t)p.R * S * p.Cin;
+    float* dst = part + ((int64_t)split * p.Cout + k) * rsc + (int64_t)(r * S) * p.Cin + cblk * CB;
     if (nchunks > 0) {
       mbar_wait(tmem_full, 0);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     }
 #pragma unroll
-    for (int s = 0; s < 3; ++s) {
+    for (int s = 0; s < S; ++s) {
 #pragma unroll
       for (int c = 0; c < CB; c += 32) {
         uint32_t v[32];
@@ -465,17 +533,15 @@ __global__ void __launch_bounds__(256) tc_splitk_reduce_kernel(const float* __re
 
 static void wgrad_tc_plan(const iit_conv_t* d, TcWgradParams* p, int* splits, int* CB) {
   p->N = d->n; p->P = d->p; p->Q = d->q; p->Cin = d->c; p->Cout = d->k; p->pad = d->pad;
-  p->BW = pow2_ge(d->q) < 16 ? pow2_ge(d->q) : 16;
-  int rem = 64 / p->BW;
-  p->BH = pow2_ge(d->p) < rem ? pow2_ge(d->p) : rem;
-  p->BNI = rem / p->BH;
+  p->stride = d->stride; p->R = d->r; p->S = d->s;
+  plan_box(d->p, d->q, 64, &p->BW, &p->BH, &p->BNI);
   p->tiles_w = (d->q + p->BW - 1) / p->BW;
   p->tiles_h = (d->p + p->BH - 1) / p->BH;
   p->tiles_n = (d->n + p->BNI - 1) / p->BNI;
   p->total_chunks = p->tiles_w * p->tiles_h * p->tiles_n;
   *CB = d->c >= 128 ? 128 : 64;
   p->ncblk = d->c / *CB;
-  int groups = 3 * ((d->k + 127) / 128) * p->ncblk;
+  int groups = d->r * ((d->k + 127) / 128) * p->ncblk;
   int want = (kNumSMs + groups - 1) / groups;
   int maxs = (p->total_chunks + 7) / 8;   // at least 8 chunks (512 pixels) per CTA
   if (want > maxs) want = maxs;
@@ -484,31 +550,17 @@ static void wgrad_tc_plan(const iit_conv_t* d, TcWgradParams* p, int* splits, in
   *splits = (p->total_chunks + p->chunks_per_split - 1) / p->chunks_per_split;
 }
 
-template <int CB>
+template <int CB, int S>
 static int launch_wgrad_tc(const CUtensorMap& mdy, const CUtensorMap& mx, float* part, const TcWgradParams& p, dim3 grid,
                            cudaStream_t st) {
-  constexpr int STAGES = CB == 64 ? 4 : 3;
-  constexpr size_t smem = STAGES * (2 + 3 * (CB / 64)) * 8192 + (2 * STAGES + 1) * 8 + 16 + 1024;
+  constexpr int STAGES = (S == 3 && CB == 128) ? 3 : 4;
+  constexpr size_t smem = STAGES * (2 + S * (CB / 64)) * 8192 + (2 * STAGES + 1) * 8 + 16 + 1024;
   static bool attr_set = false;
   if (!attr_set) {
-    IIT_CUDA(cudaFuncSetAttribute(wgrad3x3_tc_kernel<CB, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    IIT_CUDA(cudaFuncSetAttribute(wgrad3x3_tc_kernel<CB, S, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
-  wgrad3x3_tc_kernel<CB, STAGES><<<grid, TC_THREADS, smem, st>>>(mdy, mx, part, p);
-  return 0;
-}
-
-static int encode_nhwc(CUtensorMap* m, const void* ptr, int C, int W, int H, int N, int bw, int bh, int bn, const char* name) {
-  EncodeTiledFn enc = get_encode();
-  IIT_REQUIRE(enc != nullptr, "%s: cuTensorMapEncodeTiled is unavailable in this driver", name);
-  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
-  cuuint32_t box[4] = {64, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn};
-  cuuint32_t es[4] = {1, 1, 1, 1};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, es,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  IIT_REQUIRE(r == CUDA_SUCCESS, "%s: tensor map rejected (CUresult %d)", name, (int)r);
+  wgrad3x3_tc_kernel<CB, S, STAGES><<<grid, TC_THREADS, smem, st>>>(mdy, mx, part, p);
   return 0;
 }
 
@@ -518,23 +570,23 @@ using namespace iit;
 
 extern "C" int iit_conv2d_tc_supported(const iit_conv_t* d, int dtype) {
   if (!d || dtype != IIT_BF16) return 0;
-  return d->r == 3 && d->s == 3 && d->stride == 1 && d->pad == 1 && d->c % 64 == 0 && d->k % 64 == 0 && d->p == d->h &&
-         d->q == d->w;
+  const bool k3 = d->r == 3 && d->s == 3 && d->pad == 1;
+  const bool k1 = d->r == 1 && d->s == 1 && d->pad == 0;
+  return (k3 || k1) && (d->stride == 1 || d->stride == 2) && d->c % 64 == 0 && d->k % 64 == 0;
 }
 
 extern "C" int iit_conv2d_fprop_tc(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, void* stream) {
   IIT_REQUIRE(x && w_krsc && y && d, "iit_conv2d_fprop_tc: null pointer");
-  IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "iit_conv2d_fprop_tc: only bf16 3x3 stride-1 pad-1 convolutions with "
-              "channel counts that are multiples of 64");
-  return conv_tc(x, w_krsc, y, d->n, d->p, d->q, d->c, d->k, d->r, d->s, d->pad, false, as_stream(stream), "iit_conv2d_fprop_tc");
+  IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "iit_conv2d_fprop_tc: only bf16 3x3/pad-1 or 1x1/pad-0 convolutions, stride 1 "
+              "or 2, with channel counts that are multiples of 64");
+  return conv_tc_fprop(x, w_krsc, y, d, as_stream(stream));
 }
 
 extern "C" int iit_conv2d_dgrad_tc(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream) {
   IIT_REQUIRE(dy && w_crsk && dx && d, "iit_conv2d_dgrad_tc: null pointer");
-  IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "iit_conv2d_dgrad_tc: only bf16 3x3 stride-1 pad-1 convolutions with "
-              "channel counts that are multiples of 64");
-  // gathered tensor = dy [n,p,q,k]; produced = dx [n,h,w,c]; reduction over (r,s,k)
-  return conv_tc(dy, w_crsk, dx, d->n, d->h, d->w, d->k, d->c, d->r, d->s, d->pad, true, as_stream(stream), "iit_conv2d_dgrad_tc");
+  IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "iit_conv2d_dgrad_tc: only bf16 3x3/pad-1 or 1x1/pad-0 convolutions, stride 1 "
+              "or 2, with channel counts that are multiples of 64");
+  return conv_tc_dgrad(dy, w_crsk, dx, d, as_stream(stream));
 }
 
 extern "C" size_t iit_conv2d_wgrad_tc_scratch_bytes(const iit_conv_t* d) {
@@ -542,31 +594,34 @@ extern "C" size_t iit_conv2d_wgrad_tc_scratch_bytes(const iit_conv_t* d) {
   TcWgradParams p;
   int splits, CB;
   wgrad_tc_plan(d, &p, &splits, &CB);
-  return (size_t)splits * d->k * 9 * d->c * sizeof(float);
+  return (size_t)splits * d->k * d->r * d->s * d->c * sizeof(float);
 }
 
 extern "C" int iit_conv2d_wgrad_tc(const void* dy, const void* x, float* dw, const iit_conv_t* d, void* scratch,
                                    size_t scratch_bytes, void* stream) {
   IIT_REQUIRE(dy && x && dw && d, "iit_conv2d_wgrad_tc: null pointer");
-  IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "iit_conv2d_wgrad_tc: only bf16 3x3 stride-1 pad-1 convolutions with "
-              "channel counts that are multiples of 64");
+  IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "iit_conv2d_wgrad_tc: only bf16 3x3/pad-1 or 1x1/pad-0 convolutions, stride 1 "
+              "or 2, with channel counts that are multiples of 64");
   TcWgradParams p;
   int splits, CB;
   wgrad_tc_plan(d, &p, &splits, &CB);
-  size_t need = (size_t)splits * d->k * 9 * d->c * sizeof(float);
+  size_t need = (size_t)splits * d->k * d->r * d->s * d->c * sizeof(float);
   IIT_REQUIRE(scratch && scratch_bytes >= need, "iit_conv2d_wgrad_tc: scratch too small: need %zu bytes, got %zu", need, scratch_bytes);
   IIT_REQUIRE((reinterpret_cast<uintptr_t>(scratch) & 15) == 0 && (reinterpret_cast<uintptr_t>(dw) & 15) == 0,
               "iit_conv2d_wgrad_tc: scratch and dw must be 16-byte aligned");
   CUtensorMap mdy, mx;
-  if (encode_nhwc(&mdy, dy, d->k, d->q, d->p, d->n, p.BW, p.BH, p.BNI, "iit_conv2d_wgrad_tc(dy)")) return 1;
-  if (encode_nhwc(&mx, x, d->c, d->w, d->h, d->n, p.BW, p.BH, p.BNI, "iit_conv2d_wgrad_tc(x)")) return 1;
+  if (encode_nhwc_strided(&mdy, dy, d->k, d->q, d->p, d->n, p.BW, p.BH, p.BNI, 1, "iit_conv2d_wgrad_tc(dy)")) return 1;
+  if (encode_nhwc_strided(&mx, x, d->c, d->w, d->h, d->n, p.BW, p.BH, p.BNI, d->stride, "iit_conv2d_wgrad_tc(x)")) return 1;
   cudaStream_t st = as_stream(stream);
-  dim3 grid((unsigned)splits, 3, (unsigned)(((d->k + 127) / 128) * p.ncblk));
-  int rc = CB == 128 ? launch_wgrad_tc<128>(mdy, mx, (float*)scratch, p, grid, st)
-                     : launch_wgrad_tc<64>(mdy, mx, (float*)scratch, p, grid, st);
+  dim3 grid((unsigned)splits, (unsigned)d->r, (unsigned)(((d->k + 127) / 128) * p.ncblk));
+  int rc;
+  if (d->s == 3) rc = CB == 128 ? launch_wgrad_tc<128, 3>(mdy, mx, (float*)scratch, p, grid, st)
+                                : launch_wgrad_tc<64, 3>(mdy, mx, (float*)scratch, p, grid, st);
+  else rc = CB == 128 ? launch_wgrad_tc<128, 1>(mdy, mx, (float*)scratch, p, grid, st)
+                      : launch_wgrad_tc<64, 1>(mdy, mx, (float*)scratch, p, grid, st);
   if (rc) return rc;
   IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc");
-  int64_t n = (int64_t)d->k * 9 * d->c;
+  int64_t n = (int64_t)d->k * d->r * d->s * d->c;
   tc_splitk_reduce_kernel<<<grid_for(n / 4, 256), 256, 0, st>>>((const float*)scratch, dw, n, splits);
   IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc(reduce)");
   return 0;

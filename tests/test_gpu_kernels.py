@@ -364,11 +364,16 @@ def test_tensor_core_path_is_taken_and_matches_cuda_core_path(ops):
     summation order differs): 2 bf16 ulps of the output scale."""
     from iit_b200.nn.resnet import Conv2d
     g = torch.Generator().manual_seed(11)
-    for (c, k, hw, n) in [(64, 64, 14, 9), (128, 128, 7, 5), (256, 256, 4, 11), (512, 512, 2, 37), (64, 64, 21, 3),
-                          (64, 128, 14, 4)]:
-        conv = Conv2d(c, k, 3, 1, 1).to(DEV)
+    for (c, k, hw, n, ks, stride, pad) in [
+            (64, 64, 14, 9, 3, 1, 1), (128, 128, 7, 5, 3, 1, 1), (256, 256, 4, 11, 3, 1, 1), (512, 512, 2, 37, 3, 1, 1),
+            (64, 64, 21, 3, 3, 1, 1), (64, 128, 14, 4, 3, 1, 1),
+            (64, 128, 14, 9, 3, 2, 1), (128, 256, 7, 5, 3, 2, 1), (256, 512, 4, 11, 3, 2, 1),      # strided 3x3
+            (64, 128, 14, 9, 1, 2, 0), (128, 256, 7, 5, 1, 2, 0), (256, 512, 4, 11, 1, 2, 0),      # downsample 1x1
+            (64, 128, 21, 2, 3, 2, 1), (64, 128, 21, 2, 1, 2, 0)]:                                  # odd sizes (84 px)
+        conv = Conv2d(c, k, ks, stride, pad).to(DEV)
+        ohw = (hw + 2 * pad - ks) // stride + 1
         x = torch.randn(n, c, hw, hw, generator=g).to(DEV).bfloat16().contiguous(memory_format=torch.channels_last)
-        gy = torch.randn(n, k, hw, hw, generator=g).to(DEV).bfloat16().contiguous(memory_format=torch.channels_last)
+        gy = torch.randn(n, k, ohw, ohw, generator=g).to(DEV).bfloat16().contiguous(memory_format=torch.channels_last)
         outs = {}
         for use_tc in (True, False):
             ops.USE_TENSOR_CORES = use_tc
@@ -388,4 +393,4 @@ def test_tensor_core_path_is_taken_and_matches_cuda_core_path(ops):
             outs[use_tc] = (y.detach().float(), xd.grad.float(), conv.weight.grad.detach().float().clone())
         for a, b, what in zip(outs[True], outs[False], ("fprop", "dgrad", "wgrad")):
             scale = b.abs().max().item()
-            assert (a - b).abs().max().item() <= 2 * 2 ** -8 * scale, (what, c, k, hw)
+            assert (a - b).abs().max().item() <= 2 * 2 ** -8 * scale, (what, c, k, hw, ks, stride)
