@@ -539,7 +539,7 @@ static void wgrad_tc_plan(const iit_conv_t* d, TcWgradParams* p, int* splits, in
   p->tiles_h = (d->p + p->BH - 1) / p->BH;
   p->tiles_n = (d->n + p->BNI - 1) / p->BNI;
   p->total_chunks = p->tiles_w * p->tiles_h * p->tiles_n;
-  *CB = d->c >= 128 ? 128 : 64;
+  *CB = (d->c % 128 == 0) ? 128 : 64;
   p->ncblk = d->c / *CB;
   int groups = d->r * ((d->k + 127) / 128) * p->ncblk;
   int want = (kNumSMs + groups - 1) / groups;

@@ -51,7 +51,24 @@ class Conv2d(nn.Module):
 
         return ent[1], crsk
 
-    def forward(self, x, bn_sums=None):
+    def is_stem(self):
+        return tuple(self.weight.shape[1:]) == (3, 7, 7) and self.stride == 2 and self.pad == 3
+
+    def stem_filter(self):
+        """[K,192] bf16: the KRSC filter rows (147 values) zero-padded to three 128-byte rows; cached per version."""
+        w = self.weight
+        key = (w._version, w.data_ptr())
+        ent = self._prep.get("stem")
+        if ent is None or ent[0] != key:
+            w192 = torch.zeros((w.shape[0], ops.STEM_K), dtype=torch.bfloat16, device=w.device)
+            w192[:, :147] = w.detach().permute(0, 2, 3, 1).reshape(w.shape[0], 147)
+            ent = (key, w192)
+            self._prep["stem"] = ent
+        return ent[1]
+
+    def forward(self, x, bn_sums=None, act_dtype=None):
+        if act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES and self.is_stem():
+            return ops.stem_conv(x, self.weight, self.stem_filter(), bn_sums)
         krsc, crsk = self.prepared(x.dtype)
         return ops.conv2d(x, self.weight, krsc, crsk, self.stride, self.pad, bn_sums)
 
@@ -135,14 +152,14 @@ class BasicBlock(nn.Module):
             self.downsample = Wrapped(_Seq(Wrapped(Conv2d(cin, cout, 1, stride, 0)), Wrapped(BatchNorm2d(cout))))
 
 
-def _conv_bn(conv: Wrapped, bn: Wrapped, x, residual=None, relu=False, fuse_stats=True):
+def _conv_bn(conv: Wrapped, bn: Wrapped, x, residual=None, relu=False, fuse_stats=True, act_dtype=None):
     """conv -> hook -> bn(+residual)(+relu). BN statistics come from the conv epilogue unless a hook
     can modify the conv output first (the patch site): then they are taken from the hooked tensor."""
     bnm = bn.mod
     sums = None
     if bnm.training and fuse_stats and not conv.hook_point.has_hooks():
         sums = ops.new_bn_sums(bnm.c, x.device)
-    y = conv.hook_point(conv.mod(x, sums))
+    y = conv.hook_point(conv.mod(x, sums) if act_dtype is None else conv.mod(x, sums, act_dtype))
     return bnm(y, residual=residual, relu=relu, sums=sums)
 
 
@@ -198,13 +215,15 @@ class ResNet18LL(HookedRootModule):
 
     def forward(self, x):
         m = self.mod
-        if x.dtype != self.act_dtype or not ops._is_cl(x):
+        stem_tc = self.act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES and m.conv1.mod.is_stem()
+        if not stem_tc and (x.dtype != self.act_dtype or not ops._is_cl(x)):
+            # the tensor-core stem reads the caller's tensor (fp32 NCHW included) directly; otherwise convert
             x = x.to(self.act_dtype).contiguous(memory_format=torch.channels_last)
         if m.bn1.hook_point.has_hooks():
-            x = m.bn1.hook_point(_conv_bn(m.conv1, m.bn1, x))
+            x = m.bn1.hook_point(_conv_bn(m.conv1, m.bn1, x, act_dtype=self.act_dtype))
             x = m.relu.hook_point(m.relu.mod(x))
         else:
-            x = m.relu.hook_point(_conv_bn(m.conv1, m.bn1, x, relu=True))
+            x = m.relu.hook_point(_conv_bn(m.conv1, m.bn1, x, relu=True, act_dtype=self.act_dtype))
         x = m.maxpool.hook_point(m.maxpool.mod(x))
         for i in range(1, 5):
             layer: Wrapped = getattr(m, f"layer{i}")

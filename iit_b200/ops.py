@@ -355,6 +355,60 @@ def conv2d(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums=None):
     return _ConvFn.apply(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums)
 
 
+STEM_K = 192
+
+
+def stem_im2col(x: torch.Tensor) -> torch.Tensor:
+    """[N,3,H,W] image (fp32 or bf16, any strides) -> bf16 [N,192,P,Q] channels-last im2col tensor of the stem."""
+    _require_cuda(x)
+    n, c, h, w = x.shape
+    if c != 3:
+        raise ValueError("stem_im2col expects 3 input channels")
+    p, q = (h + 6 - 7) // 2 + 1, (w + 6 - 7) // 2 + 1
+    col = empty_cl(n, STEM_K, p, q, torch.bfloat16, x.device)
+    strides = (C.c_int64 * 4)(*x.stride())
+    call("iit_stem_im2col", _p(x), _dt(x), strides, _p(col), n, h, w, _stream())
+    return col
+
+
+class _StemConvFn(torch.autograd.Function):
+    """7x7/2 stem on the tensor cores: im2col (HBM-bound) + a 1x1 convolution with 192 input channels."""
+
+    @staticmethod
+    def forward(ctx, x, weight, w192, bn_sums):
+        _require_cuda(x, weight)
+        col = stem_im2col(x)
+        n, _, p, q = col.shape
+        k = weight.shape[0]
+        d = _conv_desc(col, k, 1, 1, 1, 0)
+        y = empty_cl(n, k, p, q, torch.bfloat16, x.device)
+        call("iit_conv2d_fprop_tc", _p(col), _p(w192), _p(y), C.byref(d), _stream())
+        if bn_sums is not None:
+            call("iit_bn_stats", _p(y), _dt(y), n * p * q, k, _p(bn_sums[0]), _p(bn_sums[1]), _stream())
+        ctx.save_for_backward(x, weight)
+        ctx.d = d
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        d = ctx.d
+        dw = None
+        if ctx.needs_input_grad[1]:
+            dy = _cl(dy)
+            col = stem_im2col(x)  # recomputed (0.3 ms) rather than kept alive (1.2 GB at batch 4096)
+            dw192 = torch.empty((d.k, STEM_K), dtype=torch.float32, device=x.device)
+            need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
+            scratch = torch.empty(need, dtype=torch.uint8, device=x.device)
+            call("iit_conv2d_wgrad_tc", _p(dy), _p(col), _p(dw192), C.byref(d), _p(scratch), need, _stream())
+            dw = dw192[:, :147].reshape(d.k, 7, 7, 3).permute(0, 3, 1, 2)
+        return None, dw, None, None
+
+
+def stem_conv(x, weight, w192, bn_sums=None):
+    return _StemConvFn.apply(x, weight, w192, bn_sums)
+
+
 def new_bn_sums(c: int, device) -> torch.Tensor:
     return torch.zeros((2, c), dtype=torch.float64, device=device)
 

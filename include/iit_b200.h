@@ -158,6 +158,13 @@ size_t iit_conv2d_wgrad_tc_scratch_bytes(const iit_conv_t* d);
 int iit_conv2d_wgrad_tc(const void* dy, const void* x, float* dw, const iit_conv_t* d, void* scratch,
                         size_t scratch_bytes, void* stream);
 
+/* Stem (7x7 stride-2 pad-3, 3 input channels): im2col matrix col[n*p*q][192] in bf16 (147 columns in
+ * (r,s,c) order + zero padding) gathered from an image tensor addressed as [n,c,h,w] through the given
+ * element strides (fp32 or bf16, any memory format); the stem then runs as a 1x1 convolution with 192
+ * input channels on iit_conv2d_fprop_tc / iit_conv2d_wgrad_tc. */
+int iit_stem_im2col(const void* x, int dtype, const int64_t* strides_nchw, void* col, int n, int h, int w,
+                    void* stream);
+
 /* filter re-layout: fp32 master filter addressed as [k,c,r,s] through the 4 element strides given
  * (any memory format) -> dense KRSC (to_crsk=0) or CRSK (to_crsk=1) in `dtype`. */
 int iit_filter_relayout(const float* w, const int64_t* strides_kcrs, void* w_out, int k, int c, int r,

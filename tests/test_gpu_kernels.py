@@ -394,3 +394,38 @@ def test_tensor_core_path_is_taken_and_matches_cuda_core_path(ops):
         for a, b, what in zip(outs[True], outs[False], ("fprop", "dgrad", "wgrad")):
             scale = b.abs().max().item()
             assert (a - b).abs().max().item() <= 2 * 2 ** -8 * scale, (what, c, k, hw, ks, stride)
+
+
+@pytest.mark.parametrize("hw,layout", [(56, "nchw_f32"), (84, "nchw_f32"), (56, "cl_bf16")])
+def test_stem_tensor_core_path(ops, hw, layout):
+    """7x7/2 stem = im2col (from the caller's own tensor layout/dtype) + tcgen05 1x1 conv with 192 channels."""
+    from iit_b200.nn.resnet import Conv2d
+    g = torch.Generator().manual_seed(12)
+    n = 6
+    x = torch.rand(n, 3, hw, hw, generator=g).bfloat16().float()
+    w = (torch.randn(64, 3, 7, 7, generator=g) / math.sqrt(147)).bfloat16().float().requires_grad_(True)
+    y = F.conv2d(x, w, None, 2, 3)
+    gy = torch.randn(y.shape, generator=g).bfloat16().float()
+    y.backward(gy)
+    conv = Conv2d(3, 64, 7, 2, 3).to(DEV)
+    with torch.no_grad():
+        conv.weight.copy_(w)
+    xd = x.to(DEV)
+    if layout == "cl_bf16":
+        xd = xd.bfloat16().contiguous(memory_format=torch.channels_last)
+    seen = []
+    inner = ops.call
+    ops.call = lambda name, *a: (seen.append(name), inner(name, *a))[1]
+    try:
+        sums = ops.new_bn_sums(64, DEV)
+        yd = conv(xd, sums, torch.bfloat16)
+        yd.backward(gy.to(DEV).bfloat16())
+    finally:
+        ops.call = inner
+    assert "iit_stem_im2col" in seen and "iit_conv2d_fprop_tc" in seen and "iit_conv2d_wgrad_tc" in seen
+    assert "iit_conv2d_fprop" not in seen and "iit_conv2d_wgrad" not in seen
+    for a, b, what in ((yd.float().cpu(), y.detach(), "fprop"), (conv.weight.grad.cpu(), w.grad, "wgrad")):
+        scale = b.abs().max().item()
+        assert (a - b).abs().max().item() <= 1e-2 * scale, (what, hw, layout)
+    rows = yd.numel() // 64
+    torch.testing.assert_close(sums[0].cpu().float() / rows, yd.float().cpu().mean(dim=(0, 2, 3)), rtol=1e-3, atol=1e-4)
