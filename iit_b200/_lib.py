@@ -57,6 +57,7 @@ SIGNATURES = {
     "iit_conv2d_wgrad_scratch_bytes": [_ConvP],
     "iit_conv2d_wgrad": [_vp, _vp, _vp, _ConvP, _i, _vp, _sz, _vp],
     "iit_stem_im2col": [_vp, _i, C.POINTER(C.c_int64), _vp, _i, _i, _i, _vp],
+    "iit_conv2d_wgrad_noalloc": [_vp, _vp, _vp, _ConvP, _i, _vp],
     "iit_filter_relayout": [_vp, C.POINTER(C.c_int64), _vp, _i, _i, _i, _i, _i, _i, _vp],
     "iit_bn_stats": [_vp, _i, _i64, _i, _vp, _vp, _vp],
     "iit_bn_finalize": [_vp, _vp, _i64, _i, _f, _f, _vp, _vp, _vp, _vp, _vp],

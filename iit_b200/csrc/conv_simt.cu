@@ -473,3 +473,45 @@ extern "C" int iit_filter_relayout(const float* w, const int64_t* strides_kcrs, 
   IIT_LAUNCH_CHECK("iit_filter_relayout");
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Weight gradient for callers that cannot allocate device memory.
+//
+// Some hosts of this library cannot hand the kernels a scratch buffer: a plug-in called through an FFI
+// that only forwards the tensors it was given; a service that reserved all device memory at start-up and
+// must not call cudaMalloc afterwards (it synchronises the whole device and may fail once memory is
+// fragmented); a latency-sensitive loop where that implicit synchronisation is not acceptable. For them
+// the split-K partial sums of the weight gradient live in a fixed array inside the library image instead.
+// The price: every GPU that loads the library carries kStaticScratchBytes of it until the process exits,
+// and problems whose partial sums do not fit are refused.
+// ------------------------------------------------------------------------------------------------
+namespace iit {
+constexpr size_t kStaticScratchBytes = 8u << 20;  // 8 MiB
+static __device__ __align__(256) unsigned char g_wgrad_static_scratch[kStaticScratchBytes];
+constexpr int kMaxDevices = 64;
+static void* g_static_scratch_addr[kMaxDevices] = {nullptr};  // device address of the array, per device
+}  // namespace iit
+
+extern "C" int iit_conv2d_wgrad_noalloc(const void* dy, const void* x, float* dw, const iit_conv_t* d, int dtype,
+                                        void* stream) {
+  if (check_conv(d, "iit_conv2d_wgrad_noalloc")) return 1;
+  IIT_REQUIRE(dy && x && dw, "iit_conv2d_wgrad_noalloc: null pointer");
+  const size_t need = iit_conv2d_wgrad_scratch_bytes(d);
+  IIT_REQUIRE(need <= kStaticScratchBytes,
+              "iit_conv2d_wgrad_noalloc: this problem needs %zu bytes of split-K scratch but the built-in buffer holds %zu; "
+              "use iit_conv2d_wgrad with caller-provided scratch (or a smaller batch)", need, (size_t)kStaticScratchBytes);
+  int dev = -1;
+  IIT_CUDA(cudaGetDevice(&dev));
+  IIT_REQUIRE(dev >= 0 && dev < kMaxDevices, "iit_conv2d_wgrad_noalloc: device ordinal %d out of range", dev);
+  if (g_static_scratch_addr[dev] == nullptr) {
+    // One-time set-up for the current device: in host code the array's name is only a handle, the
+    // address the kernels must be given comes from the runtime. Nothing is allocated here.
+    void* p = nullptr;
+    IIT_CUDA(cudaGetSymbolAddress(&p, g_wgrad_static_scratch));
+    IIT_REQUIRE(p != nullptr, "iit_conv2d_wgrad_noalloc: could not resolve the built-in scratch buffer");
+    g_static_scratch_addr[dev] = p;
+  }
+  // The partial sums need no clearing: every cell of the region a launch uses is written by the
+  // gradient kernel before the reduction reads it.
+  return iit_conv2d_wgrad(dy, x, dw, d, dtype, g_static_scratch_addr[dev], kStaticScratchBytes, stream);
+}

@@ -145,6 +145,20 @@ int iit_conv2d_dgrad(const void* dy, const void* w_crsk, void* dx, const iit_con
 size_t iit_conv2d_wgrad_scratch_bytes(const iit_conv_t* d);
 int iit_conv2d_wgrad(const void* dy, const void* x, float* dw, const iit_conv_t* d, int dtype,
                      void* scratch, size_t scratch_bytes, void* stream);
+/* Same result as iit_conv2d_wgrad, for callers that cannot give the kernels a scratch buffer because
+ * they must not (or cannot) allocate device memory: FFI plug-ins that only forward the caller's tensors,
+ * processes that reserved the whole device at start-up and may not call cudaMalloc afterwards, loops that
+ * cannot afford cudaMalloc's device-wide synchronisation. This entry point has no counterpart in the
+ * reference. The split-K partial sums go to an 8 MiB array built into the library (each GPU that loads
+ * the library holds those 8 MiB until the process exits); a problem that needs more is rejected with
+ * an error naming both sizes. It calls no cudaMalloc / cudaFree / allocating routine. The first call on
+ * a device looks up the array's device address (once per device, with that device current): make that
+ * first call before starting any stream capture. All calls share the one array and it keeps the last
+ * call's partial sums (nothing needs clearing: a launch overwrites what it reads), so two calls whose
+ * kernels may overlap on the GPU - different streams - race with each other: serialise them. */
+int iit_conv2d_wgrad_noalloc(const void* dy, const void* x, float* dw, const iit_conv_t* d, int dtype,
+                             void* stream);
+
 /* Tensor-core path (tcgen05.mma + TMA + TMEM accumulator) for bf16 3x3 stride-1 pad-1 convolutions whose
  * channel counts are multiples of 64 -- 80 % of ResNet-18's FLOPs. Same results contract as
  * iit_conv2d_fprop / iit_conv2d_dgrad (fp32 accumulation, bf16 output); w_krsc / w_crsk are bf16.
