@@ -222,7 +222,7 @@ def run_ours(args, rank, world, local):
     B = args.batch
     ll, hl, corr = get_alignment("mnist_pvr", {"input_shape": (1, 3, 56, 56)}, device=dev, dtype=dtype)
     ll.load_state_dict(R.resnet18_state_dict(0))
-    pair = StrictIITModelPair(hl, ll, corr, training_args={"lr": 1e-3})
+    pair = StrictIITModelPair(hl, ll, corr, training_args={"lr": 1e-3, "cuda_graphs": bool(args.graphs)})
     dp = idist.DataParallel()
     if world > 1:
         pair.dp = dp
@@ -245,6 +245,8 @@ def run_ours(args, rank, world, local):
         s = tuple(t.to(dev, non_blocking=True) for t in src_h)
         return pair.run_train_step(b, s, pair.loss_fn, opt)  # returns host floats: the D2H read of the losses
 
+    if args.graphs:  # capture all 21 (term, node) variants before anything is timed; leaves state untouched
+        pair.prepare_graphs(base_d, src_d, pair.loss_fn, opt)
     timer = KernelTimer(["iit_conv2d_fprop", "iit_conv2d_dgrad", "iit_conv2d_wgrad", "iit_conv2d_fprop_tc",
                          "iit_conv2d_dgrad_tc", "iit_conv2d_wgrad_tc"])
     timer.install()
@@ -266,13 +268,25 @@ def run_ours(args, rank, world, local):
     sampler = ClockSampler(local)
     sampler.start()
     launches0 = _lib.launch_count()
-    timer.enabled = True
+    timer.enabled = not args.graphs
     sec, metrics = timed(step_resident, args.steps)
     timer.enabled = False
     launches = _lib.launch_count() - launches0
     clocks = sampler.stop()
     step_e2e()  # warm the copy path
     sec_e2e, _ = timed(step_e2e, args.steps)
+    sec_eager = None
+    if args.graphs:
+        # Graph replays cannot be bracketed kernel by kernel: the per-kernel CUDA-event timings (roofline, kernels)
+        # come from an eager pass of the same steps, whose launches also give the per-step launch count.
+        pair.training_args["cuda_graphs"] = False
+        step_resident()
+        launches0 = _lib.launch_count()
+        timer.enabled = True
+        sec_eager, _ = timed(step_resident, args.steps)
+        timer.enabled = False
+        launches = _lib.launch_count() - launches0
+        pair.training_args["cuda_graphs"] = True
 
     if rank != 0:
         return
@@ -284,7 +298,8 @@ def run_ours(args, rank, world, local):
         k = ks[top]
         roof = {"kernel": top, "bound": "tensor", "achieved": k["tflops"], "peak": pk["tflops"], "unit": "TFLOP/s",
                 "frac": k["tflops"] / pk["tflops"], "traffic": None, "peak_source": pk["src"] + " bf16 sustained",
-                "share_of_step": k["total_ms"] / (sec * 1e3), "launches": k["launches"], "avg_ms": k["avg_ms"]}
+                "share_of_step": k["total_ms"] / ((sec_eager or sec) * 1e3), "launches": k["launches"], "avg_ms": k["avg_ms"],
+                "timed_in": "eager pass of the same steps (CUDA events around each launch)" if sec_eager else "timed region"}
     value = B * world * args.steps / sec
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -294,6 +309,7 @@ def run_ours(args, rank, world, local):
                 "d2h_bytes_per_step": 3 * 4},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "kernels": ks,
         "step_tflops": 11 * F56 * B * args.steps / sec / 1e12,
+        "cuda_graphs": bool(args.graphs), "ms_per_step_eager": (1e3 * sec_eager / args.steps) if sec_eager else None,
         "last_step_metrics": metrics,
     }
     if world == 1 and not args.no_cpu_baseline:
@@ -302,6 +318,8 @@ def run_ours(args, rank, world, local):
 
 
 def main():
+    if os.environ.get("NCCL_DEBUG", "VERSION") == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -310,6 +328,7 @@ def main():
     ap.add_argument("--batch", type=int, default=4096)
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--graphs", type=int, default=1, help="1: replay each (loss term, node) variant from a CUDA graph")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -50,7 +50,7 @@ SIGNATURES = {
     "iit_conv2d_fprop": [_vp, _vp, _vp, _ConvP, _i, _vp, _vp, _vp],
     "iit_conv2d_dgrad": [_vp, _vp, _vp, _ConvP, _i, _vp],
     "iit_conv2d_tc_supported": [_ConvP, _i],
-    "iit_conv2d_fprop_tc": [_vp, _vp, _vp, _ConvP, _vp],
+    "iit_conv2d_fprop_tc": [_vp, _vp, _vp, _ConvP, _vp, _vp, _vp],
     "iit_conv2d_dgrad_tc": [_vp, _vp, _vp, _ConvP, _vp],
     "iit_conv2d_wgrad_tc_scratch_bytes": [_ConvP],
     "iit_conv2d_wgrad_tc": [_vp, _vp, _vp, _ConvP, _vp, _sz, _vp],
@@ -76,6 +76,7 @@ SIGNATURES = {
     "iit_linear_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
     "iit_sqnorm": [_vp, _i64, _vp, _vp],
     "iit_adam_step": [_vp, _vp, _vp, _vp, _i64, _d, _d, _d, _d, _i64, _vp, _d, _vp],
+    "iit_adam_step_dev": [_vp, _vp, _vp, _vp, _i64, _vp, _d, _d, _d, _vp, _vp, _d, _vp],
     "iit_last_error": [],
     "iit_version": [],
     "iit_launch_count": [],

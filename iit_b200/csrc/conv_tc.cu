@@ -107,7 +107,8 @@ struct TcParams {
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_constant__ CUtensorMap map_a,
                                                                 const __grid_constant__ CUtensorMap map_b,
-                                                                __nv_bfloat16* __restrict__ out, TcParams p) {
+                                                                __nv_bfloat16* __restrict__ out, TcParams p,
+                                                                double* __restrict__ bn_sum, double* __restrict__ bn_sq) {
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operands need 1024-byte aligned tiles
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -118,6 +119,8 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
   uint64_t* empty = full + STAGES;
   uint64_t* tmem_full = empty + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [2][BN] per-channel sum / sum of squares of this tile
+  if (bn_sum != nullptr && threadIdx.x < 2 * BN / 2) { s_stat[threadIdx.x] = 0.f; s_stat[threadIdx.x + BN] = 0.f; }
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // tile -> (image block, row block, column block); blockIdx.y -> filter block
@@ -215,6 +218,38 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
           *reinterpret_cast<uint4*>(dst + c + j) = o;
         }
       }
+      if (bn_sum != nullptr) {
+        // BatchNorm statistics of the values as stored (bf16-rounded), for the BN that follows this conv.
+        // Each lane holds one pixel x 32 channels; a butterfly that halves the channel set per step leaves
+        // lane l with the warp total of channel c+l after 31 shuffles (instead of 32 x 5).
+        float a[32], b[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float f = ok ? __bfloat162float(__float2bfloat16_rn(__uint_as_float(v[j]))) : 0.f;
+          a[j] = f; b[j] = f * f;
+        }
+#pragma unroll
+        for (int h = 16; h >= 1; h >>= 1) {
+          const bool up = (lane & h) != 0;
+#pragma unroll
+          for (int i = 0; i < h; ++i) {
+            float sa = up ? a[i] : a[i + h], ka = up ? a[i + h] : a[i];
+            float sb = up ? b[i] : b[i + h], kb = up ? b[i + h] : b[i];
+            a[i] = ka + __shfl_xor_sync(0xffffffffu, sa, h);
+            b[i] = kb + __shfl_xor_sync(0xffffffffu, sb, h);
+          }
+        }
+        atomicAdd(&s_stat[c + lane], a[0]);
+        atomicAdd(&s_stat[BN + c + lane], b[0]);
+      }
+    }
+    if (bn_sum != nullptr) {
+      asm volatile("bar.sync 1, 128;" ::: "memory");   // the four epilogue warps only
+      const int e = threadIdx.x - 64;                  // 0..127
+      if (e < BN) {
+        atomicAdd(&bn_sum[co0 + e], (double)s_stat[e]);
+        atomicAdd(&bn_sq[co0 + e], (double)s_stat[BN + e]);
+      }
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -246,15 +281,15 @@ static int pow2_ge(int v) { int r = 1; while (r < v) r <<= 1; return r; }
 
 template <int BN>
 static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16* out, const TcParams& p, dim3 grid,
-                     cudaStream_t st) {
+                     cudaStream_t st, double* bn_sum, double* bn_sq) {
   constexpr int STAGES = BN == 64 ? 4 : 4;
-  constexpr size_t smem = STAGES * (TC_BM * TC_BK * 2 + BN * TC_BK * 2) + (2 * STAGES + 1) * 8 + 16 + 1024;
+  constexpr size_t smem = STAGES * (TC_BM * TC_BK * 2 + BN * TC_BK * 2) + (2 * STAGES + 1) * 8 + 16 + 2 * BN * 4 + 1024;
   static bool attr_set = false;
   if (!attr_set) {
     IIT_CUDA(cudaFuncSetAttribute(conv3x3_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
-  conv3x3_tc_kernel<BN, STAGES><<<grid, TC_THREADS, smem, st>>>(ma, mb, out, p);
+  conv3x3_tc_kernel<BN, STAGES><<<grid, TC_THREADS, smem, st>>>(ma, mb, out, p, bn_sum, bn_sq);
   return 0;
 }
 
@@ -297,7 +332,7 @@ static int encode_filter(CUtensorMap* m, const void* wmat, int Kg, int rows, int
 
 // One launch: the produced pixels (p*out_mul+out_oh, q*out_mul+out_ow), p<P, q<Q, from the taps listed in `tp`.
 static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const void* wmat, int Kg, void* out, TcParams tp,
-                          cudaStream_t st, const char* name) {
+                          cudaStream_t st, const char* name, double* bn_sum = nullptr, double* bn_sq = nullptr) {
   plan_box(tp.P, tp.Q, TC_BM, &tp.BW, &tp.BH, &tp.BNI);
   tp.tiles_w = (tp.Q + tp.BW - 1) / tp.BW;
   tp.tiles_h = (tp.P + tp.BH - 1) / tp.BH;
@@ -307,8 +342,8 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
   if (encode_nhwc_strided(&ma, gathered, gC, gW, gH, tp.N, tp.BW, tp.BH, tp.BNI, tp.in_mul, name)) return 1;
   if (encode_filter(&mb, wmat, Kg, tp.Cout, BN, name)) return 1;
   dim3 grid((unsigned)(tp.tiles_w * tp.tiles_h * tiles_n), (unsigned)(tp.Cout / BN));
-  int rc = BN == 128 ? launch_tc<128>(ma, mb, (__nv_bfloat16*)out, tp, grid, st)
-                     : launch_tc<64>(ma, mb, (__nv_bfloat16*)out, tp, grid, st);
+  int rc = BN == 128 ? launch_tc<128>(ma, mb, (__nv_bfloat16*)out, tp, grid, st, bn_sum, bn_sq)
+                     : launch_tc<64>(ma, mb, (__nv_bfloat16*)out, tp, grid, st, bn_sum, bn_sq);
   if (rc) return rc;
   IIT_LAUNCH_CHECK(name);
   return 0;
@@ -321,7 +356,8 @@ static int check_tc_ptrs(const void* a, const void* b, const void* c, const char
 }
 
 // y[n,p,q,k] = sum_{r,s,c} x[n, p*stride - pad + r, q*stride - pad + s, c] * w[k,r,s,c]
-static int conv_tc_fprop(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, cudaStream_t st) {
+static int conv_tc_fprop(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, cudaStream_t st, double* bn_sum,
+                         double* bn_sq) {
   const char* name = "iit_conv2d_fprop_tc";
   if (check_tc_ptrs(x, w_krsc, y, name)) return 1;
   TcParams tp{};
@@ -334,7 +370,7 @@ static int conv_tc_fprop(const void* x, const void* w_krsc, void* y, const iit_c
       int t = r * d->s + s;
       tp.dh[t] = (int8_t)(r - d->pad); tp.dw[t] = (int8_t)(s - d->pad); tp.wk[t] = (int8_t)t;
     }
-  return conv_tc_launch(x, d->c, d->w, d->h, w_krsc, d->r * d->s * d->c, y, tp, st, name);
+  return conv_tc_launch(x, d->c, d->w, d->h, w_krsc, d->r * d->s * d->c, y, tp, st, name, bn_sum, bn_sq);
 }
 
 // dx[n,h,w,c] = sum_{r,s,k} dy[n,(h+pad-r)/stride,(w+pad-s)/stride,k] * w[k,r,s,c]  over exact divisions.
@@ -575,11 +611,13 @@ extern "C" int iit_conv2d_tc_supported(const iit_conv_t* d, int dtype) {
   return (k3 || k1) && (d->stride == 1 || d->stride == 2) && d->c % 64 == 0 && d->k % 64 == 0;
 }
 
-extern "C" int iit_conv2d_fprop_tc(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, void* stream) {
+extern "C" int iit_conv2d_fprop_tc(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, double* bn_sum,
+                                   double* bn_sqsum, void* stream) {
   IIT_REQUIRE(x && w_krsc && y && d, "iit_conv2d_fprop_tc: null pointer");
+  IIT_REQUIRE((bn_sum == nullptr) == (bn_sqsum == nullptr), "iit_conv2d_fprop_tc: bn_sum and bn_sqsum go together");
   IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "iit_conv2d_fprop_tc: only bf16 3x3/pad-1 or 1x1/pad-0 convolutions, stride 1 "
               "or 2, with channel counts that are multiples of 64");
-  return conv_tc_fprop(x, w_krsc, y, d, as_stream(stream));
+  return conv_tc_fprop(x, w_krsc, y, d, as_stream(stream), bn_sum, bn_sqsum);
 }
 
 extern "C" int iit_conv2d_dgrad_tc(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream) {

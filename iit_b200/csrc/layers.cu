@@ -417,6 +417,35 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
   }
 }
 
+// Device-resident step counter and learning rate: nothing about the update is baked into the launch
+// arguments, so the launch can sit inside a captured CUDA graph and still follow the schedule.
+__global__ void adam_tick_kernel(long long* step) { *step += 1; }
+
+__global__ void __launch_bounds__(256) adam_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                                       float* __restrict__ v, int64_t n, const float* __restrict__ lr_dev, double b1d,
+                                                       double b2d, float eps, const long long* __restrict__ step_dev,
+                                                       const double* __restrict__ sqnorm, float max_norm) {
+  // bias corrections in double, as torch.optim.Adam computes them in Python floats
+  const double step = (double)*step_dev;
+  const double bc1 = 1.0 - pow(b1d, step), bc2 = 1.0 - pow(b2d, step);
+  const float step_size = (float)((double)*lr_dev / bc1), bc2_sqrt = (float)sqrt(bc2);
+  const float b1 = (float)b1d, b2 = (float)b2d;
+  float clip = 1.f;
+  if (sqnorm && max_norm > 0.f) {
+    float total = (float)sqrt(*sqnorm);
+    float coef = max_norm / (total + 1e-6f);
+    clip = coef < 1.f ? coef : 1.f;
+  }
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float gi = g[i] * clip;
+    float mi = m[i] + (gi - m[i]) * (1.f - b1);
+    float vi = v[i] * b2 + gi * gi * (1.f - b2);
+    m[i] = mi; v[i] = vi;
+    float denom = sqrtf(vi) / bc2_sqrt + eps;
+    p[i] = p[i] - step_size * (mi / denom);
+  }
+}
+
 }  // namespace iit
 
 using namespace iit;
@@ -605,5 +634,18 @@ extern "C" int iit_adam_step(float* p, const float* g, float* m, float* v, int64
   adam_kernel<<<grid_for(n, 256 * 4), 256, 0, as_stream(stream)>>>(p, g, m, v, n, (float)(lr / bc1), (float)beta1, (float)beta2,
                                                                  (float)eps, (float)sqrt(bc2), sqnorm, (float)max_norm);
   IIT_LAUNCH_CHECK("iit_adam_step");
+  return 0;
+}
+
+extern "C" int iit_adam_step_dev(float* p, const float* g, float* m, float* v, int64_t n, const float* lr_dev, double beta1,
+                                 double beta2, double eps, long long* step_dev, const double* sqnorm, double max_norm,
+                                 void* stream) {
+  IIT_REQUIRE(p && g && m && v && lr_dev && step_dev, "iit_adam_step_dev: null pointer");
+  cudaStream_t st = as_stream(stream);
+  adam_tick_kernel<<<1, 1, 0, st>>>(step_dev);
+  IIT_LAUNCH_CHECK("iit_adam_step_dev(tick)");
+  adam_dev_kernel<<<grid_for(n, 256 * 4), 256, 0, st>>>(p, g, m, v, n, lr_dev, beta1, beta2, (float)eps, step_dev, sqnorm,
+                                                       (float)max_norm);
+  IIT_LAUNCH_CHECK("iit_adam_step_dev");
   return 0;
 }

@@ -144,6 +144,55 @@ class BaseModelPair(ABC):
         hl_output, ll_output = self.do_intervention(base_input, ablation_input, hl_node)
         return loss_fn(ll_output, hl_output)
 
+    # ---- CUDA graphs -------------------------------------------------------------------------
+    # One loss term of a train step (loss -> zero_grad -> backward -> [all-reduce] -> clip -> Adam) is a fixed
+    # sequence of ~300 kernel launches once the interchanged node is chosen. With training_args["cuda_graphs"]
+    # each (term, node) variant is captured once into a CUDA graph and replayed afterwards: the host only copies
+    # the batch into static buffers, draws the nodes and replays. Requires FlatAdam (device-side step / lr) and
+    # fixed batch shapes; all variants share one memory pool.
+    def _static_inputs(self, base_input, ablation_input):
+        key = tuple((tuple(t.shape), t.dtype) for t in (*base_input, *ablation_input))
+        st = getattr(self, "_static", None)
+        if st is None or st[0] != key:
+            st = (key, tuple(t.clone() for t in base_input), tuple(t.clone() for t in ablation_input))
+            self._static = st
+            self._graphs = {}
+        for dst, src in zip((*st[1], *st[2]), (*base_input, *ablation_input)):
+            if dst is not src:
+                dst.copy_(src, non_blocking=True)
+        return st[1], st[2]
+
+    def _graphed_term(self, key, optimizer, build_loss):
+        graphs = self.__dict__.setdefault("_graphs", {})
+        ent = graphs.get(key)
+        if ent is None:
+            ent = graphs[key] = self._capture_term(optimizer, build_loss)
+        ent[0].replay()
+        return ent[1]
+
+    def _capture_term(self, optimizer, build_loss):
+        if not hasattr(self, "_graph_pool"):
+            self._graph_pool = t.cuda.graph_pool_handle()
+        buffers = list(self.ll_model.buffers())
+        snap_opt = optimizer.state_snapshot()
+        snap_buf = [b.clone() for b in buffers]
+        cur = t.cuda.current_stream()
+        side = t.cuda.Stream()
+        side.wait_stream(cur)
+        with t.cuda.stream(side):  # eager warm-up: first-launch attribute set-up, autograd worker thread
+            self.step_on_loss(build_loss(), optimizer)
+        cur.wait_stream(side)
+        optimizer.state_restore(snap_opt)  # the warm-up was a real update: undo it
+        with t.no_grad():
+            for b, s in zip(buffers, snap_buf):
+                b.copy_(s)
+        graph = t.cuda.CUDAGraph()
+        with t.cuda.graph(graph, pool=self._graph_pool):
+            loss = build_loss()
+            self.step_on_loss(loss, optimizer)
+            out = loss.detach().clone()
+        return graph, out
+
     # ---- optimisation ------------------------------------------------------------------------
     def clip_grad_fn(self):
         if self.training_args["clip_grad_norm"]:

@@ -63,7 +63,27 @@ class IITBehaviorModelPair(IITModelPair):
             self.clip_grad_fn()
             optimizer.step()
 
+    def _use_graphs(self, optimizer) -> bool:
+        return (bool(self.training_args.get("cuda_graphs")) and isinstance(optimizer, FlatAdam)
+                and not self.training_args["use_single_loss"])
+
+    def _graphed_iit(self, sb, ss, hl_node, loss_fn, optimizer):
+        return self._graphed_term(("iit", str(hl_node)), optimizer, lambda: (
+            self.get_IIT_loss_over_batch(sb, ss, hl_node, loss_fn) * self.training_args["iit_weight"]))
+
+    def _graphed_behavior(self, sb, loss_fn, optimizer):
+        return self._graphed_term(("behavior",), optimizer, lambda: (
+            self.get_behaviour_loss_over_batch(sb, loss_fn) * self.training_args["behavior_weight"]))
+
     def run_train_step(self, base_input, ablation_input, loss_fn, optimizer):
+        if self._use_graphs(optimizer):
+            sb, ss = self._static_inputs(base_input, ablation_input)
+            optimizer.sync_lr()
+            hl_node = self.sample_hl_name()
+            iit_loss = self._graphed_iit(sb, ss, hl_node, loss_fn, optimizer)
+            behavior_loss = self._graphed_behavior(sb, loss_fn, optimizer)
+            vals = t.stack([iit_loss, behavior_loss]).tolist()
+            return {"train/iit_loss": vals[0], "train/behavior_loss": vals[1]}
         single = self.training_args["use_single_loss"]
         hl_node = self.sample_hl_name()
         iit_loss = (self.get_IIT_loss_over_batch(base_input, ablation_input, hl_node, loss_fn)

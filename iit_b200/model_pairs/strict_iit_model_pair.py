@@ -51,7 +51,39 @@ class StrictIITModelPair(IITBehaviorModelPair):
             out = out.squeeze()
         return loss_fn(out, base_y)
 
+    def _graphed_strict(self, sb, ss, ll_node, loss_fn, optimizer):
+        return self._graphed_term(("strict", ll_node.name, repr(ll_node.index)), optimizer, lambda: (
+            self.get_strict_loss_over_batch(sb, ss, ll_node, loss_fn) * self.training_args["strict_weight"]))
+
+    def prepare_graphs(self, base_input, ablation_input, loss_fn, optimizer):
+        """Capture every (term, node) variant up front so that no capture happens inside a timed / training
+        loop. Model and optimizer state are left exactly as found."""
+        sb, ss = self._static_inputs(base_input, ablation_input)
+        for hl_node in self.corr.keys():
+            self._graphed_capture_only(("iit", str(hl_node)), optimizer, lambda n=hl_node: (
+                self.get_IIT_loss_over_batch(sb, ss, n, loss_fn) * self.training_args["iit_weight"]))
+        for ll_node in self.nodes_not_in_circuit:
+            self._graphed_capture_only(("strict", ll_node.name, repr(ll_node.index)), optimizer, lambda n=ll_node: (
+                self.get_strict_loss_over_batch(sb, ss, n, loss_fn) * self.training_args["strict_weight"]))
+        self._graphed_capture_only(("behavior",), optimizer, lambda: (
+            self.get_behaviour_loss_over_batch(sb, loss_fn) * self.training_args["behavior_weight"]))
+
+    def _graphed_capture_only(self, key, optimizer, build_loss):
+        graphs = self.__dict__.setdefault("_graphs", {})
+        if key not in graphs:
+            graphs[key] = self._capture_term(optimizer, build_loss)
+
     def run_train_step(self, base_input, ablation_input, loss_fn, optimizer):
+        if self._use_graphs(optimizer):
+            sb, ss = self._static_inputs(base_input, ablation_input)
+            optimizer.sync_lr()
+            hl_node = self.sample_hl_name()
+            iit_loss = self._graphed_iit(sb, ss, hl_node, loss_fn, optimizer)
+            ll_node = self.sample_ll_node()
+            ll_loss = self._graphed_strict(sb, ss, ll_node, loss_fn, optimizer)
+            behavior_loss = self._graphed_behavior(sb, loss_fn, optimizer)
+            vals = t.stack([iit_loss, behavior_loss, ll_loss]).tolist()
+            return {"train/iit_loss": vals[0], "train/behavior_loss": vals[1], "train/strict_loss": vals[2]}
         single = self.training_args["use_single_loss"]
         hl_node = self.sample_hl_name()
         iit_loss = (self.get_IIT_loss_over_batch(base_input, ablation_input, hl_node, loss_fn)

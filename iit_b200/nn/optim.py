@@ -35,7 +35,10 @@ class FlatAdam(torch.optim.Optimizer):
         self.flat_m = torch.zeros(total, dtype=torch.float32, device=dev)
         self.flat_v = torch.zeros(total, dtype=torch.float32, device=dev)
         self._sq = torch.zeros(1, dtype=torch.float64, device=dev)
-        self.step_count = 0
+        # step count and learning rate live on the device so that a captured CUDA graph of step() stays valid
+        self.step_dev = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.lr_dev = torch.full((1,), float(lr), dtype=torch.float32, device=dev)
+        self._lr_host = float(lr)
         with torch.no_grad():
             for p, o in zip(params, offs):
                 pv = self._view_like(self.flat_p, o, p)
@@ -56,13 +59,35 @@ class FlatAdam(torch.optim.Optimizer):
         ops.sqnorm_(self.flat_g, self._sq)
         return self._sq
 
+    @property
+    def step_count(self) -> int:
+        return int(self.step_dev.item())
+
+    def sync_lr(self):
+        """Push a host-side learning-rate change (e.g. from a scheduler) to the device scalar. Call outside
+        graph capture; step() calls it when not capturing."""
+        lr = float(self.param_groups[0]["lr"])
+        if lr != self._lr_host:
+            self.lr_dev.fill_(lr)
+            self._lr_host = lr
+
+    def state_snapshot(self):
+        return [t.clone() for t in (self.flat_p, self.flat_m, self.flat_v, self.step_dev)]
+
+    def state_restore(self, snap):
+        for t, s in zip((self.flat_p, self.flat_m, self.flat_v, self.step_dev), snap):
+            t.copy_(s)
+        for p in self._params:
+            torch.autograd.graph.increment_version(p)
+
     @torch.no_grad()
     def step(self, closure=None, max_norm=None):
         g = self.param_groups[0]
-        self.step_count += 1
+        if not ops.capturing():
+            self.sync_lr()
         sq = self.grad_sqnorm() if max_norm else None
-        ops.adam_step_(self.flat_p, self.flat_g, self.flat_m, self.flat_v, g["lr"], g["betas"][0], g["betas"][1],
-                       g["eps"], self.step_count, sq, max_norm)
+        ops.adam_step_dev_(self.flat_p, self.flat_g, self.flat_m, self.flat_v, self.lr_dev, g["betas"][0], g["betas"][1],
+                           g["eps"], self.step_dev, sq, max_norm)
         for p in self._params:  # the kernel wrote through raw pointers: tell autograd / filter caches
             torch.autograd.graph.increment_version(p)
 

@@ -38,7 +38,8 @@ class Conv2d(nn.Module):
         w = self.weight
         key = (w._version, w.data_ptr(), dtype)
         ent = self._prep.get("ent")
-        if ent is None or ent[0] != key:
+        # under CUDA-graph capture the re-layout must be part of the graph (replays see new weights)
+        if ent is None or ent[0] != key or ops.capturing():
             direct = dtype == torch.float32 and w.dim() == 4 and w.permute(0, 2, 3, 1).is_contiguous()
             krsc = w.detach() if direct else ops.filter_relayout(w.detach(), False, dtype)
             ent = [key, krsc, None]
@@ -48,6 +49,9 @@ class Conv2d(nn.Module):
             if ent[2] is None:
                 ent[2] = ops.filter_relayout(w.detach(), True, dtype)
             return ent[2]
+
+        if ops.capturing():
+            crsk()  # the backward of this forward is captured too: make the copy while weights are current
 
         return ent[1], crsk
 
@@ -59,7 +63,7 @@ class Conv2d(nn.Module):
         w = self.weight
         key = (w._version, w.data_ptr())
         ent = self._prep.get("stem")
-        if ent is None or ent[0] != key:
+        if ent is None or ent[0] != key or ops.capturing():
             w192 = torch.zeros((w.shape[0], ops.STEM_K), dtype=torch.bfloat16, device=w.device)
             w192[:, :147] = w.detach().permute(0, 2, 3, 1).reshape(w.shape[0], 147)
             ent = (key, w192)

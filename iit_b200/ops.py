@@ -23,6 +23,11 @@ _DT = {torch.float32: _lib.IIT_F32, torch.bfloat16: _lib.IIT_BF16}
 USE_TENSOR_CORES = True
 
 
+def capturing() -> bool:
+    """True while the current CUDA stream is being captured into a graph."""
+    return torch.cuda.is_available() and torch.cuda.is_current_stream_capturing()
+
+
 def _require_cuda(*tensors):
     for t in tensors:
         if t is not None and not t.is_cuda:
@@ -316,9 +321,7 @@ class _ConvFn(torch.autograd.Function):
             s0, s1 = bn_sums[0], bn_sums[1]
         tc = USE_TENSOR_CORES and bool(_lib.lib.iit_conv2d_tc_supported(C.byref(d), _dt(x)))
         if tc:  # tcgen05 + TMA implicit GEMM; BN statistics (if wanted) by the statistics kernel
-            call("iit_conv2d_fprop_tc", _p(x), _p(w_krsc), _p(y), C.byref(d), _stream())
-            if s0 is not None:
-                call("iit_bn_stats", _p(y), _dt(y), d.n * d.p * d.q, k, _p(s0), _p(s1), _stream())
+            call("iit_conv2d_fprop_tc", _p(x), _p(w_krsc), _p(y), C.byref(d), _p(s0), _p(s1), _stream())
         else:
             call("iit_conv2d_fprop", _p(x), _p(w_krsc), _p(y), C.byref(d), _dt(x), _p(s0), _p(s1), _stream())
         ctx.save_for_backward(x, weight)
@@ -382,24 +385,24 @@ class _StemConvFn(torch.autograd.Function):
         k = weight.shape[0]
         d = _conv_desc(col, k, 1, 1, 1, 0)
         y = empty_cl(n, k, p, q, torch.bfloat16, x.device)
-        call("iit_conv2d_fprop_tc", _p(col), _p(w192), _p(y), C.byref(d), _stream())
+        s0 = s1 = None
         if bn_sums is not None:
-            call("iit_bn_stats", _p(y), _dt(y), n * p * q, k, _p(bn_sums[0]), _p(bn_sums[1]), _stream())
-        ctx.save_for_backward(x, weight)
+            s0, s1 = bn_sums[0], bn_sums[1]
+        call("iit_conv2d_fprop_tc", _p(col), _p(w192), _p(y), C.byref(d), _p(s0), _p(s1), _stream())
+        ctx.save_for_backward(col, weight)   # kept for the weight gradient (1.2 GB at batch 4096, bf16)
         ctx.d = d
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, weight = ctx.saved_tensors
+        col, weight = ctx.saved_tensors
         d = ctx.d
         dw = None
         if ctx.needs_input_grad[1]:
             dy = _cl(dy)
-            col = stem_im2col(x)  # recomputed (0.3 ms) rather than kept alive (1.2 GB at batch 4096)
-            dw192 = torch.empty((d.k, STEM_K), dtype=torch.float32, device=x.device)
+            dw192 = torch.empty((d.k, STEM_K), dtype=torch.float32, device=col.device)
             need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
-            scratch = torch.empty(need, dtype=torch.uint8, device=x.device)
+            scratch = torch.empty(need, dtype=torch.uint8, device=col.device)
             call("iit_conv2d_wgrad_tc", _p(dy), _p(col), _p(dw192), C.byref(d), _p(scratch), need, _stream())
             dw = dw192[:, :147].reshape(d.k, 7, 7, 3).permute(0, 3, 1, 2)
         return None, dw, None, None
@@ -604,6 +607,11 @@ def linear(x, w, b):
 # =================================================================================================
 def sqnorm_(g_flat: torch.Tensor, out: torch.Tensor):
     call("iit_sqnorm", _p(g_flat), g_flat.numel(), _p(out), _stream())
+
+
+def adam_step_dev_(p, g, m, v, lr_dev, beta1, beta2, eps, step_dev, sqnorm, max_norm):
+    call("iit_adam_step_dev", _p(p), _p(g), _p(m), _p(v), p.numel(), _p(lr_dev), float(beta1), float(beta2), float(eps),
+         _p(step_dev), _p(sqnorm), float(max_norm or 0.0), _stream())
 
 
 def adam_step_(p, g, m, v, lr, beta1, beta2, eps, step, sqnorm, max_norm):

@@ -164,7 +164,8 @@ int iit_conv2d_wgrad_noalloc(const void* dy, const void* x, float* dw, const iit
  * iit_conv2d_fprop / iit_conv2d_dgrad (fp32 accumulation, bf16 output); w_krsc / w_crsk are bf16.
  * iit_conv2d_tc_supported() returns 1 when a descriptor qualifies. */
 int iit_conv2d_tc_supported(const iit_conv_t* d, int dtype);
-int iit_conv2d_fprop_tc(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, void* stream);
+int iit_conv2d_fprop_tc(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, double* bn_sum,
+                        double* bn_sqsum, void* stream);
 int iit_conv2d_dgrad_tc(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream);
 /* dw[k,r,s,c] fp32: pixels are the GEMM K dimension (MN-major operands straight from NHWC), split across
  * CTAs; scratch holds the per-split partial sums (iit_conv2d_wgrad_tc_scratch_bytes), reduced in fixed order. */
@@ -235,6 +236,13 @@ int iit_sqnorm(const float* g, int64_t n, double* sqnorm, void* stream);
 int iit_adam_step(float* p, const float* g, float* m, float* v, int64_t n, double lr, double beta1,
                   double beta2, double eps, int64_t step, const double* sqnorm, double max_norm,
                   void* stream);
+
+/* Same update with the 1-based step count and the learning rate read from device memory (the call
+ * first increments *step_dev): no schedule value is baked into the launch, so it can be replayed from a
+ * captured CUDA graph. */
+int iit_adam_step_dev(float* p, const float* g, float* m, float* v, int64_t n, const float* lr_dev,
+                      double beta1, double beta2, double eps, long long* step_dev, const double* sqnorm,
+                      double max_norm, void* stream);
 
 #ifdef __cplusplus
 }
