@@ -1,0 +1,411 @@
+// (b) Low-level HookedTransformer (IOI task: 6 layers, 4 heads, d_model 64, d_head 16, d_mlp 3072, 16 tokens):
+// the non-GEMM pieces. Dense contractions (QKV, O, MLP in/out, unembed) run on the convolution GEMM kernels
+// (a linear layer is a 1x1 convolution over tokens); here are embedding gather / scatter-add, LayerNormPre,
+// bias (+GELU) (+residual) epilogues, column sums for bias gradients and the causal attention core.
+// With d_model = 64 every one of these is HBM/latency bound: rows are short, so one warp owns one row
+// (coalesced 256-byte row accesses), and attention keeps a whole (sequence, head) in shared memory.
+#include "common.cuh"
+
+namespace iit {
+
+// ---------------------------------------------------------------------------------------------- embedding
+template <typename T>
+__global__ void __launch_bounds__(256) embed_fwd_kernel(const int64_t* __restrict__ tok, const float* __restrict__ WE,
+                                                        const float* __restrict__ Wpos, T* __restrict__ out, int64_t ntok,
+                                                        int S, int D, int64_t V) {
+  const int64_t total = ntok * (D / 4);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t t = i / (D / 4);
+    const int d4 = (int)(i - t * (D / 4)) * 4;
+    int64_t id = tok[t];
+    if (id < 0) id += V;
+    const int pos = (int)(t % S);
+    float4 e = *reinterpret_cast<const float4*>(WE + id * D + d4);
+    float4 p = *reinterpret_cast<const float4*>(Wpos + (int64_t)pos * D + d4);
+    float v[4] = {e.x + p.x, e.y + p.y, e.z + p.z, e.w + p.w};
+    Vec4<T>::store(out + t * D + d4, v);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) embed_bwd_kernel(const int64_t* __restrict__ tok, const T* __restrict__ dres,
+                                                        float* __restrict__ dWE, float* __restrict__ dWpos, int64_t ntok,
+                                                        int S, int D, int64_t V) {
+  const int64_t total = ntok * D;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t t = i / D;
+    const int d = (int)(i - t * D);
+    int64_t id = tok[t];
+    if (id < 0) id += V;
+    const float g = to_f<T>(dres[i]);
+    atomicAdd(dWE + id * D + d, g);
+    atomicAdd(dWpos + (int64_t)(t % S) * D + d, g);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- LayerNormPre
+// y = (x - mean) / sqrt(mean((x-mean)^2) + eps); one warp per row, D a multiple of 32 (<= 1024)
+template <typename T, int PER>
+__global__ void __launch_bounds__(256) lnpre_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, float* __restrict__ rstd,
+                                                        int64_t rows, int D, float eps) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp; r < rows; r += nw) {
+    float v[PER];
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < PER; ++j) { v[j] = to_f<T>(x[r * D + lane + 32 * j]); s += v[j]; }
+    const float mean = warp_sum(s) / (float)D;
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < PER; ++j) { v[j] -= mean; q += v[j] * v[j]; }
+    const float scale = sqrtf(warp_sum(q) / (float)D + eps);
+#pragma unroll
+    for (int j = 0; j < PER; ++j) y[r * D + lane + 32 * j] = from_f<T>(v[j] / scale);
+    if (lane == 0 && rstd) rstd[r] = 1.f / scale;
+  }
+}
+// dx = rstd * (dy - mean(dy) - y * mean(dy * y))
+template <typename T, int PER>
+__global__ void __launch_bounds__(256) lnpre_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ y,
+                                                        const float* __restrict__ rstd, T* __restrict__ dx, int64_t rows, int D) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp; r < rows; r += nw) {
+    float g[PER], yy[PER];
+    float a = 0.f, b = 0.f;
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+      g[j] = to_f<T>(dy[r * D + lane + 32 * j]);
+      yy[j] = to_f<T>(y[r * D + lane + 32 * j]);
+      a += g[j]; b += g[j] * yy[j];
+    }
+    a = warp_sum(a) / (float)D;
+    b = warp_sum(b) / (float)D;
+    const float rs = rstd[r];
+#pragma unroll
+    for (int j = 0; j < PER; ++j) dx[r * D + lane + 32 * j] = from_f<T>(rs * (g[j] - a - yy[j] * b));
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- bias / GELU / residual
+__device__ __forceinline__ float gelu_new_f(float x) {
+  const float k = 0.7978845608028654f;  // sqrt(2/pi)
+  return 0.5f * x * (1.f + tanhf(k * (x + 0.044715f * x * x * x)));
+}
+__device__ __forceinline__ float gelu_new_grad(float x) {
+  const float k = 0.7978845608028654f;
+  const float u = k * (x + 0.044715f * x * x * x);
+  const float th = tanhf(u);
+  return 0.5f * (1.f + th) + 0.5f * x * (1.f - th * th) * k * (1.f + 3.f * 0.044715f * x * x);
+}
+
+// pre = x + bias (+ resid);  out = act(pre).  pre_out optional (the MLP's hook_pre / what GELU's backward needs)
+template <typename T>
+__global__ void __launch_bounds__(256) bias_act_kernel(const T* __restrict__ x, const float* __restrict__ bias,
+                                                       const T* __restrict__ resid, T* __restrict__ pre_out, T* __restrict__ out,
+                                                       int64_t n4, int N, int act) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t e = i * 4;
+    const int c = (int)(e % N);
+    float v[4];
+    Vec4<T>::load(x + e, v);
+    if (bias) {
+      float4 b = *reinterpret_cast<const float4*>(bias + c);
+      v[0] += b.x; v[1] += b.y; v[2] += b.z; v[3] += b.w;
+    }
+    if (resid) {
+      float r[4];
+      Vec4<T>::load(resid + e, r);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] += r[j];
+    }
+    if (pre_out) Vec4<T>::store(pre_out + e, v);
+    if (act == 1) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = gelu_new_f(v[j]);
+    }
+    Vec4<T>::store(out + e, v);
+  }
+}
+// same, element by element, for widths that are not a multiple of 4 (the 50257-wide unembed bias)
+template <typename T>
+__global__ void __launch_bounds__(256) bias_act_scalar_kernel(const T* __restrict__ x, const float* __restrict__ bias,
+                                                              const T* __restrict__ resid, T* __restrict__ pre_out,
+                                                              T* __restrict__ out, int64_t n, int N, int act) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float v = to_f<T>(x[i]);
+    if (bias) v += bias[i % N];
+    if (resid) v += to_f<T>(resid[i]);
+    if (pre_out) pre_out[i] = from_f<T>(v);
+    if (act == 1) v = gelu_new_f(v);
+    out[i] = from_f<T>(v);
+  }
+}
+template <typename T>
+__global__ void __launch_bounds__(256) gelu_bwd_kernel(const T* __restrict__ dpost, const T* __restrict__ pre, T* __restrict__ dpre,
+                                                       int64_t n4) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float g[4], p[4];
+    Vec4<T>::load(dpost + i * 4, g);
+    Vec4<T>::load(pre + i * 4, p);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) g[j] *= gelu_new_grad(p[j]);
+    Vec4<T>::store(dpre + i * 4, g);
+  }
+}
+
+// out[c] += sum_r x[r, c]  (bias gradients). Block = 32 columns x 8 row lanes.
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x, float* __restrict__ out, int64_t rows, int64_t N) {
+  __shared__ float s[8][33];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int64_t c = (int64_t)blockIdx.x * 32 + cx;
+  float acc = 0.f;
+  if (c < N)
+    for (int64_t r = (int64_t)blockIdx.y * 8 + ry; r < rows; r += (int64_t)gridDim.y * 8) acc += to_f<T>(x[r * N + c]);
+  s[ry][cx] = acc;
+  __syncthreads();
+  if (ry == 0 && c < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) t += s[j][cx];
+    atomicAdd(out + c, t);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- attention core
+// qkv: [B, S, 3, H, DH] (one fused projection), z: [B, S, H, DH]. Causal, scores / sqrt(DH).
+// One warp per (batch, head); lane i < S owns query row i. S <= 32, DH <= 32.
+template <typename T, int S_MAX, int DH_MAX>
+__global__ void __launch_bounds__(128) attn_fwd_kernel(const T* __restrict__ qkv, T* __restrict__ z, int64_t BH, int S, int H,
+                                                       int DH, float scale) {
+  __shared__ float sk[4][S_MAX][DH_MAX + 1], sv[4][S_MAX][DH_MAX + 1];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int64_t bh0 = (int64_t)blockIdx.x * 4; bh0 < BH; bh0 += (int64_t)gridDim.x * 4) {
+    const int64_t bh = bh0 + w;
+    const bool live = bh < BH;
+    const int64_t b = live ? bh / H : 0;
+    const int h = live ? (int)(bh - b * H) : 0;
+    const T* base = qkv + b * (int64_t)S * 3 * H * DH;
+    if (live)
+      for (int i = lane; i < S * DH; i += 32) {
+        const int s = i / DH, d = i - s * DH;
+        sk[w][s][d] = to_f<T>(base[((int64_t)s * 3 + 1) * H * DH + h * DH + d]);
+        sv[w][s][d] = to_f<T>(base[((int64_t)s * 3 + 2) * H * DH + h * DH + d]);
+      }
+    __syncwarp();
+    if (live && lane < S) {
+      float q[DH_MAX], o[DH_MAX];
+#pragma unroll
+      for (int d = 0; d < DH_MAX; ++d) {
+        q[d] = d < DH ? to_f<T>(base[((int64_t)lane * 3) * H * DH + h * DH + d]) : 0.f;
+        o[d] = 0.f;
+      }
+      float m = -INFINITY, l = 0.f;
+      for (int j = 0; j <= lane; ++j) {
+        float sc = 0.f;
+#pragma unroll
+        for (int d = 0; d < DH_MAX; ++d) if (d < DH) sc = fmaf(q[d], sk[w][j][d], sc);
+        sc *= scale;
+        const float mn = fmaxf(m, sc);
+        const float corr = __expf(m - mn), p = __expf(sc - mn);
+        l = l * corr + p;
+#pragma unroll
+        for (int d = 0; d < DH_MAX; ++d) if (d < DH) o[d] = o[d] * corr + p * sv[w][j][d];
+        m = mn;
+      }
+      T* zo = z + ((b * S + lane) * H + h) * DH;
+#pragma unroll
+      for (int d = 0; d < DH_MAX; ++d) if (d < DH) zo[d] = from_f<T>(o[d] / l);
+    }
+    __syncwarp();
+  }
+}
+
+// dqkv [B,S,3,H,DH] from dz, recomputing the pattern.
+template <typename T, int S_MAX, int DH_MAX>
+__global__ void __launch_bounds__(128) attn_bwd_kernel(const T* __restrict__ qkv, const T* __restrict__ dz, T* __restrict__ dqkv,
+                                                       int64_t BH, int S, int H, int DH, float scale) {
+  __shared__ float sq[4][S_MAX][DH_MAX + 1], sk[4][S_MAX][DH_MAX + 1], sv[4][S_MAX][DH_MAX + 1], sdz[4][S_MAX][DH_MAX + 1];
+  __shared__ float sp[4][S_MAX][S_MAX + 1], sds[4][S_MAX][S_MAX + 1];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int64_t bh0 = (int64_t)blockIdx.x * 4; bh0 < BH; bh0 += (int64_t)gridDim.x * 4) {
+    const int64_t bh = bh0 + w;
+    const bool live = bh < BH;
+    const int64_t b = live ? bh / H : 0;
+    const int h = live ? (int)(bh - b * H) : 0;
+    const T* base = qkv + b * (int64_t)S * 3 * H * DH;
+    T* dbase = dqkv + b * (int64_t)S * 3 * H * DH;
+    if (live)
+      for (int i = lane; i < S * DH; i += 32) {
+        const int s = i / DH, d = i - s * DH;
+        sq[w][s][d] = to_f<T>(base[((int64_t)s * 3 + 0) * H * DH + h * DH + d]);
+        sk[w][s][d] = to_f<T>(base[((int64_t)s * 3 + 1) * H * DH + h * DH + d]);
+        sv[w][s][d] = to_f<T>(base[((int64_t)s * 3 + 2) * H * DH + h * DH + d]);
+        sdz[w][s][d] = to_f<T>(dz[((b * S + s) * H + h) * DH + d]);
+      }
+    __syncwarp();
+    if (live && lane < S) {  // phase 1: row i of the pattern P and of dS
+      const int i = lane;
+      // scores -> pattern row (kept in shared memory: sp), dP row (kept in sds until rescaled)
+      float m = -INFINITY;
+      for (int j = 0; j <= i; ++j) {
+        float a = 0.f;
+        for (int d = 0; d < DH; ++d) a = fmaf(sq[w][i][d], sk[w][j][d], a);
+        a *= scale;
+        sp[w][i][j] = a;
+        m = fmaxf(m, a);
+      }
+      float l = 0.f;
+      for (int j = 0; j <= i; ++j) { const float e = __expf(sp[w][i][j] - m); sp[w][i][j] = e; l += e; }
+      float dot = 0.f;
+      for (int j = 0; j <= i; ++j) {
+        const float p = sp[w][i][j] / l;
+        float a = 0.f;
+        for (int d = 0; d < DH; ++d) a = fmaf(sdz[w][i][d], sv[w][j][d], a);
+        sds[w][i][j] = a;
+        dot += p * a;
+        sp[w][i][j] = p;
+      }
+      for (int j = 0; j < S; ++j) {
+        if (j <= i) sds[w][i][j] = sp[w][i][j] * (sds[w][i][j] - dot) * scale;
+        else { sds[w][i][j] = 0.f; sp[w][i][j] = 0.f; }
+      }
+      // dq_i = sum_j dS_ij k_j
+      for (int d = 0; d < DH; ++d) {
+        float a = 0.f;
+        for (int j = 0; j <= i; ++j) a = fmaf(sds[w][i][j], sk[w][j][d], a);
+        dbase[((int64_t)i * 3 + 0) * H * DH + h * DH + d] = from_f<T>(a);
+      }
+    }
+    __syncwarp();
+    if (live && lane < S) {  // phase 2: column j: dk_j = sum_i dS_ij q_i, dv_j = sum_i P_ij dz_i
+      const int j = lane;
+      for (int d = 0; d < DH; ++d) {
+        float a = 0.f, c = 0.f;
+        for (int i = j; i < S; ++i) { a = fmaf(sds[w][i][j], sq[w][i][d], a); c = fmaf(sp[w][i][j], sdz[w][i][d], c); }
+        dbase[((int64_t)j * 3 + 1) * H * DH + h * DH + d] = from_f<T>(a);
+        dbase[((int64_t)j * 3 + 2) * H * DH + h * DH + d] = from_f<T>(c);
+      }
+    }
+    __syncwarp();
+  }
+}
+
+}  // namespace iit
+
+using namespace iit;
+
+extern "C" int iit_embed_fwd(const int64_t* tokens, const float* W_E, const float* W_pos, void* out, int dtype, int64_t ntok,
+                             int seq, int d_model, int64_t d_vocab, void* stream) {
+  IIT_REQUIRE(tokens && W_E && W_pos && out && d_model % 4 == 0 && seq >= 1, "iit_embed_fwd: bad arguments");
+  IIT_DISPATCH_DTYPE(dtype, T, {
+    embed_fwd_kernel<T><<<grid_for(ntok * (d_model / 4), 256), 256, 0, as_stream(stream)>>>(tokens, W_E, W_pos, (T*)out, ntok, seq,
+                                                                                           d_model, d_vocab);
+  })
+  IIT_LAUNCH_CHECK("iit_embed_fwd");
+  return 0;
+}
+extern "C" int iit_embed_bwd(const int64_t* tokens, const void* dresid, int dtype, float* dW_E, float* dW_pos, int64_t ntok,
+                             int seq, int d_model, int64_t d_vocab, void* stream) {
+  IIT_REQUIRE(tokens && dresid && dW_E && dW_pos, "iit_embed_bwd: null pointer");
+  IIT_DISPATCH_DTYPE(dtype, T, {
+    embed_bwd_kernel<T><<<grid_for(ntok * d_model, 256), 256, 0, as_stream(stream)>>>(tokens, (const T*)dresid, dW_E, dW_pos, ntok,
+                                                                                     seq, d_model, d_vocab);
+  })
+  IIT_LAUNCH_CHECK("iit_embed_bwd");
+  return 0;
+}
+
+#define IIT_LN_DISPATCH(KERNEL, ...)                                                                   \
+  switch (d / 32) {                                                                                    \
+    case 1: KERNEL<T, 1><<<grid_for(rows, 8), 256, 0, st>>>(__VA_ARGS__); break;                       \
+    case 2: KERNEL<T, 2><<<grid_for(rows, 8), 256, 0, st>>>(__VA_ARGS__); break;                       \
+    case 4: KERNEL<T, 4><<<grid_for(rows, 8), 256, 0, st>>>(__VA_ARGS__); break;                       \
+    case 8: KERNEL<T, 8><<<grid_for(rows, 8), 256, 0, st>>>(__VA_ARGS__); break;                       \
+    case 16: KERNEL<T, 16><<<grid_for(rows, 8), 256, 0, st>>>(__VA_ARGS__); break;                     \
+    case 24: KERNEL<T, 24><<<grid_for(rows, 8), 256, 0, st>>>(__VA_ARGS__); break;                     \
+    case 32: KERNEL<T, 32><<<grid_for(rows, 8), 256, 0, st>>>(__VA_ARGS__); break;                     \
+    default: iit::set_error("LayerNormPre: unsupported width %d", d); return 1;                        \
+  }
+
+extern "C" int iit_lnpre_fwd(const void* x, void* y, float* rstd, int dtype, int64_t rows, int d, float eps, void* stream) {
+  IIT_REQUIRE(x && y && d % 32 == 0, "iit_lnpre_fwd: bad arguments (width must be a multiple of 32)");
+  cudaStream_t st = as_stream(stream);
+  IIT_DISPATCH_DTYPE(dtype, T, { IIT_LN_DISPATCH(lnpre_fwd_kernel, (const T*)x, (T*)y, rstd, rows, d, eps) })
+  IIT_LAUNCH_CHECK("iit_lnpre_fwd");
+  return 0;
+}
+extern "C" int iit_lnpre_bwd(const void* dy, const void* y, const float* rstd, void* dx, int dtype, int64_t rows, int d,
+                             void* stream) {
+  IIT_REQUIRE(dy && y && rstd && dx && d % 32 == 0, "iit_lnpre_bwd: bad arguments");
+  cudaStream_t st = as_stream(stream);
+  IIT_DISPATCH_DTYPE(dtype, T, { IIT_LN_DISPATCH(lnpre_bwd_kernel, (const T*)dy, (const T*)y, rstd, (T*)dx, rows, d) })
+  IIT_LAUNCH_CHECK("iit_lnpre_bwd");
+  return 0;
+}
+
+extern "C" int iit_bias_act_fwd(const void* x, const float* bias, const void* resid, void* pre_out, void* out, int dtype,
+                                int64_t rows, int n, int act, void* stream) {
+  IIT_REQUIRE(x && out && (act == 0 || act == 1), "iit_bias_act_fwd: bad arguments");
+  if (n % 4 != 0) {
+    IIT_DISPATCH_DTYPE(dtype, T, {
+      bias_act_scalar_kernel<T><<<grid_for(rows * n, 1024), 256, 0, as_stream(stream)>>>((const T*)x, bias, (const T*)resid,
+                                                                                        (T*)pre_out, (T*)out, rows * n, n, act);
+    })
+    IIT_LAUNCH_CHECK("iit_bias_act_fwd");
+    return 0;
+  }
+  int64_t n4 = rows * n / 4;
+  IIT_DISPATCH_DTYPE(dtype, T, {
+    bias_act_kernel<T><<<grid_for(n4, 512), 256, 0, as_stream(stream)>>>((const T*)x, bias, (const T*)resid, (T*)pre_out, (T*)out,
+                                                                        n4, n, act);
+  })
+  IIT_LAUNCH_CHECK("iit_bias_act_fwd");
+  return 0;
+}
+extern "C" int iit_gelu_bwd(const void* dpost, const void* pre, void* dpre, int dtype, int64_t n, void* stream) {
+  IIT_REQUIRE(dpost && pre && dpre && n % 4 == 0, "iit_gelu_bwd: bad arguments");
+  IIT_DISPATCH_DTYPE(dtype, T, {
+    gelu_bwd_kernel<T><<<grid_for(n / 4, 512), 256, 0, as_stream(stream)>>>((const T*)dpost, (const T*)pre, (T*)dpre, n / 4);
+  })
+  IIT_LAUNCH_CHECK("iit_gelu_bwd");
+  return 0;
+}
+extern "C" int iit_colsum(const void* x, int dtype, float* out, int64_t rows, int64_t n, void* stream) {
+  IIT_REQUIRE(x && out, "iit_colsum: null pointer");
+  int64_t by = (rows + 255) / 256;
+  if (by > 64) by = 64;
+  if (by < 1) by = 1;
+  dim3 grid((unsigned)((n + 31) / 32), (unsigned)by);
+  IIT_DISPATCH_DTYPE(dtype, T, { colsum_kernel<T><<<grid, 256, 0, as_stream(stream)>>>((const T*)x, out, rows, n); })
+  IIT_LAUNCH_CHECK("iit_colsum");
+  return 0;
+}
+
+extern "C" int iit_attn_fwd(const void* qkv, void* z, int dtype, int64_t batch, int seq, int heads, int d_head, void* stream) {
+  IIT_REQUIRE(qkv && z && seq >= 1 && seq <= 32 && d_head >= 1 && d_head <= 32, "iit_attn_fwd: seq and d_head must be <= 32");
+  const float scale = 1.0f / sqrtf((float)d_head);
+  int64_t BH = batch * heads;
+  IIT_DISPATCH_DTYPE(dtype, T, {
+    attn_fwd_kernel<T, 32, 32><<<grid_for(BH, 4), 128, 0, as_stream(stream)>>>((const T*)qkv, (T*)z, BH, seq, heads, d_head, scale);
+  })
+  IIT_LAUNCH_CHECK("iit_attn_fwd");
+  return 0;
+}
+extern "C" int iit_attn_bwd(const void* qkv, const void* dz, void* dqkv, int dtype, int64_t batch, int seq, int heads, int d_head,
+                            void* stream) {
+  IIT_REQUIRE(qkv && dz && dqkv && seq >= 1 && seq <= 16 && d_head >= 1 && d_head <= 16,
+              "iit_attn_bwd: seq and d_head must be <= 16");
+  const float scale = 1.0f / sqrtf((float)d_head);
+  int64_t BH = batch * heads;
+  IIT_DISPATCH_DTYPE(dtype, T, {
+    attn_bwd_kernel<T, 16, 16><<<grid_for(BH, 4), 128, 0, as_stream(stream)>>>((const T*)qkv, (const T*)dz, (T*)dqkv, BH, seq, heads,
+                                                                               d_head, scale);
+  })
+  IIT_LAUNCH_CHECK("iit_attn_bwd");
+  return 0;
+}

@@ -9,6 +9,8 @@ one-hot probability target -- and (iii) labels reduced once per batch to their l
 `do_intervention` still returns the dense tensors for callers that want them."""
 from __future__ import annotations
 
+import weakref
+
 import numpy as np
 import torch as t
 
@@ -27,7 +29,7 @@ class IOI_ModelPair(StrictIITModelPair):
         self.training_args = {**defaults, **self.training_args}
         # the reference reads this from the DEFAULTS, not the merged args (ioi_model_pair.py:20): always False
         self.next_token = defaults["next_token"]
-        self._label_cache = (None, None)
+        self._label_cache = (None, None, None)
 
     @property
     def loss_fn(self):
@@ -59,11 +61,11 @@ class IOI_ModelPair(StrictIITModelPair):
         """[B,S] int64 ids from one-hot [B,S,V] labels (one argmax pass per batch tensor, memoised)."""
         if base_y.dtype == t.int64:
             return base_y
-        key = (base_y.data_ptr(), tuple(base_y.shape), base_y._version)
-        if self._label_cache[0] != key:
+        ref, version, ids = self._label_cache
+        if ref is None or ref() is not base_y or version != base_y._version:  # same tensor object, unmodified
             ids = ops.argmax_rows(base_y.reshape(-1, base_y.shape[-1])).view(base_y.shape[:-1])
-            self._label_cache = (key, ids)
-        return self._label_cache[1]
+            self._label_cache = (weakref.ref(base_y), base_y._version, ids)
+        return ids
 
     def _last_logits(self, fwd_hooks, x):
         """LL run returning last-position logits [B,V] (unembeds one position when the model can)."""

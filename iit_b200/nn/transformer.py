@@ -1,0 +1,173 @@
+"""Low-level model for the IOI task: a small GPT-2-style `HookedTransformer` whose layers are the
+sm_100a kernels.
+
+Replaces `transformer_lens.HookedTransformer(cfg)` as `train_ioi.py:30-34` builds it (gpt2 config with
+iit/tasks/ioi/__init__.py:8-17 applied: 6 layers, 4 heads, d_model 64, d_head 16; inherited d_mlp 3072,
+d_vocab 50257, n_ctx 1024, gelu_new, LNPre = folded layer norm) and keeps what callers see [TL-knowledge]:
+  * parameter names / shapes: embed.W_E [V,D], pos_embed.W_pos [n_ctx,D], blocks.i.attn.W_Q/K/V [H,D,dh],
+    W_O [H,dh,D], b_Q/K/V [H,dh], b_O [D], blocks.i.mlp.W_in [D,d_mlp], b_in, W_out [d_mlp,D], b_out,
+    unembed.W_U [D,V], b_U (+ the attention `mask` / `IGNORE` buffers, so reference checkpoints load);
+  * hook-point names: blocks.i.attn.hook_z [B,S,H,dh] and blocks.i.mlp.hook_post [B,S,d_mlp] (the patch
+    sites of the shipped correspondence and of the strict loss), plus hook_resid_pre/mid/post,
+    hook_attn_out, hook_mlp_out, mlp.hook_pre. The remaining transformer_lens hook points exist by name;
+    putting a hook on one of those raises (their tensors live only inside fused kernels);
+  * `cfg` with n_layers, n_heads, d_vocab_out, device, to_dict().
+`forward(tokens, last_pos_only=True)` unembeds only the last position ([B,V]): all the IOI losses read
+nothing else (ioi_model_pair.py:20,35), and it avoids the [B,16,50257] logits tensor.
+"""
+from __future__ import annotations
+
+import math
+from types import SimpleNamespace
+
+import torch
+import torch.nn as nn
+
+from .. import ops
+from ..hooks import HookedRootModule, HookPoint
+
+
+class TransformerConfig(SimpleNamespace):
+    def to_dict(self):
+        return dict(self.__dict__)
+
+
+def make_cfg(cfg) -> TransformerConfig:
+    d = dict(n_layers=None, d_model=None, n_ctx=1024, d_head=None, n_heads=-1, d_mlp=None, act_fn="gelu_new",
+             d_vocab=50257, d_vocab_out=-1, eps=1e-5, normalization_type="LNPre", init_weights=True, initializer_range=-1.0,
+             seed=None, device=None, use_attn_result=False, attn_only=False, dtype=torch.float32)
+    d.update(dict(cfg) if isinstance(cfg, dict) else cfg.__dict__)
+    c = TransformerConfig(**d)
+    if c.n_heads == -1:
+        c.n_heads = c.d_model // c.d_head
+    if c.d_vocab_out == -1:
+        c.d_vocab_out = c.d_vocab
+    if c.d_mlp is None:
+        c.d_mlp = 4 * c.d_model
+    if c.initializer_range < 0:
+        c.initializer_range = 0.8 / math.sqrt(c.d_model)
+    if c.device is None:
+        c.device = "cuda" if torch.cuda.is_available() else "cpu"
+    if c.normalization_type != "LNPre" or c.act_fn != "gelu_new" or c.use_attn_result or c.attn_only:
+        raise NotImplementedError("the kernels implement the train_ioi.py configuration: LNPre, gelu_new, "
+                                  "use_attn_result=False, attn_only=False")
+    return c
+
+
+class _Holder(nn.Module):
+    """Namespace module so that parameters / hook points get transformer_lens' dotted names."""
+
+
+def _hp():
+    return HookPoint()
+
+
+class HookedTransformerLL(HookedRootModule):
+    supports_last_pos = True
+
+    def __init__(self, cfg, dtype=None):
+        super().__init__()
+        self.cfg = c = make_cfg(cfg)
+        self.act_dtype = dtype or torch.float32
+        V, D, H, dh, F_ = c.d_vocab, c.d_model, c.n_heads, c.d_head, c.d_mlp
+        self.embed = _Holder()
+        self.embed.W_E = nn.Parameter(torch.empty(V, D))
+        self.hook_embed = _hp()
+        self.pos_embed = _Holder()
+        self.pos_embed.W_pos = nn.Parameter(torch.empty(c.n_ctx, D))
+        self.hook_pos_embed = _hp()
+        self.blocks = nn.ModuleList()
+        for _ in range(c.n_layers):
+            b = _Holder()
+            b.ln1 = _Holder(); b.ln1.hook_scale = _hp(); b.ln1.hook_normalized = _hp()
+            b.ln2 = _Holder(); b.ln2.hook_scale = _hp(); b.ln2.hook_normalized = _hp()
+            a = b.attn = _Holder()
+            a.W_Q = nn.Parameter(torch.empty(H, D, dh)); a.W_K = nn.Parameter(torch.empty(H, D, dh))
+            a.W_V = nn.Parameter(torch.empty(H, D, dh)); a.W_O = nn.Parameter(torch.empty(H, dh, D))
+            a.b_Q = nn.Parameter(torch.zeros(H, dh)); a.b_K = nn.Parameter(torch.zeros(H, dh))
+            a.b_V = nn.Parameter(torch.zeros(H, dh)); a.b_O = nn.Parameter(torch.zeros(D))
+            a.register_buffer("mask", torch.tril(torch.ones(c.n_ctx, c.n_ctx, dtype=torch.bool)))
+            a.register_buffer("IGNORE", torch.tensor(-torch.inf))
+            for n in ("hook_k", "hook_q", "hook_v", "hook_z", "hook_attn_scores", "hook_pattern", "hook_result"):
+                setattr(a, n, _hp())
+            m = b.mlp = _Holder()
+            m.W_in = nn.Parameter(torch.empty(D, F_)); m.b_in = nn.Parameter(torch.zeros(F_))
+            m.W_out = nn.Parameter(torch.empty(F_, D)); m.b_out = nn.Parameter(torch.zeros(D))
+            m.hook_pre = _hp(); m.hook_post = _hp()
+            for n in ("hook_attn_in", "hook_q_input", "hook_k_input", "hook_v_input", "hook_mlp_in", "hook_attn_out",
+                      "hook_mlp_out", "hook_resid_pre", "hook_resid_mid", "hook_resid_post"):
+                setattr(b, n, _hp())
+            self.blocks.append(b)
+        self.ln_final = _Holder(); self.ln_final.hook_scale = _hp(); self.ln_final.hook_normalized = _hp()
+        self.unembed = _Holder()
+        self.unembed.W_U = nn.Parameter(torch.empty(D, c.d_vocab_out))
+        self.unembed.b_U = nn.Parameter(torch.zeros(c.d_vocab_out))
+        if c.init_weights:
+            if c.seed is not None:
+                torch.manual_seed(c.seed)
+            for name, p in self.named_parameters():
+                if "W_" in name:
+                    nn.init.normal_(p, std=c.initializer_range)
+        self.setup()
+        self._unsupported = [n for n in self.hook_dict if n.split(".")[-1] in (
+            "hook_embed", "hook_pos_embed", "hook_scale", "hook_normalized", "hook_k", "hook_q", "hook_v",
+            "hook_attn_scores", "hook_pattern", "hook_result", "hook_attn_in", "hook_q_input", "hook_k_input",
+            "hook_v_input", "hook_mlp_in")]
+
+    def load_state_dict(self, state_dict, strict=True, assign=False):
+        sd = dict(state_dict)
+        own = self.state_dict()
+        for k in own:  # mask / IGNORE buffers are constants: tolerate checkpoints without them
+            if k not in sd and (k.endswith(".mask") or k.endswith(".IGNORE")):
+                sd[k] = own[k]
+        return super().load_state_dict(sd, strict=strict, assign=assign)
+
+    # ------------------------------------------------------------------------------------------
+    def _check_hooks(self):
+        for n in self._unsupported:
+            if self.hook_dict[n].has_hooks():
+                raise NotImplementedError(f"hook point {n} lives inside a fused kernel; hook hook_z / hook_post / "
+                                          "the residual-stream hook points instead")
+
+    def forward(self, tokens, last_pos_only=False, return_type="logits"):
+        self._check_hooks()
+        c = self.cfg
+        B, S = tokens.shape
+        D, H, dh = c.d_model, c.n_heads, c.d_head
+        T = B * S
+        resid = ops.embed(tokens, self.embed.W_E, self.pos_embed.W_pos, self.act_dtype).view(T, D)
+        for blk in self.blocks:
+            a, m = blk.attn, blk.mlp
+            resid = blk.hook_resid_pre(resid.view(B, S, D)).reshape(T, D)
+            x = ops.lnpre(resid, c.eps)
+            # fused QKV projection: [D, (3,H,dh)] assembled from the per-head parameters (tiny; autograd routes grads)
+            w_qkv = torch.cat([w.permute(1, 0, 2).reshape(D, H * dh) for w in (a.W_Q, a.W_K, a.W_V)], dim=1)
+            b_qkv = torch.cat([b.reshape(-1) for b in (a.b_Q, a.b_K, a.b_V)])
+            qkv = ops.bias_add(ops.linear_tokens(x, w_qkv), b_qkv).view(B, S, 3, H, dh)
+            z = a.hook_z(ops.attention(qkv))
+            proj = ops.linear_tokens(z.reshape(T, H * dh), a.W_O.reshape(H * dh, D))
+            if blk.hook_attn_out.has_hooks():
+                attn_out = blk.hook_attn_out(ops.bias_add(proj, a.b_O).view(B, S, D)).reshape(T, D)
+                resid = ops.bias_add(attn_out, None, resid)
+            else:
+                resid = ops.bias_add(proj, a.b_O, resid)
+            resid = blk.hook_resid_mid(resid.view(B, S, D)).reshape(T, D)
+            x = ops.lnpre(resid, c.eps)
+            h = ops.linear_tokens(x, m.W_in)
+            if m.hook_pre.has_hooks():  # observers only: the activation below is computed from the unhooked value
+                pre = ops.bias_add(h, m.b_in).view(B, S, -1)
+                if m.hook_pre(pre) is not pre:
+                    raise NotImplementedError("mlp.hook_pre is read-only here; hook mlp.hook_post to intervene")
+            post = m.hook_post(ops.bias_gelu(h, m.b_in, (B, S, c.d_mlp))).reshape(T, -1)
+            out = ops.linear_tokens(post, m.W_out)
+            if blk.hook_mlp_out.has_hooks():
+                mlp_out = blk.hook_mlp_out(ops.bias_add(out, m.b_out).view(B, S, D)).reshape(T, D)
+                resid = ops.bias_add(mlp_out, None, resid)
+            else:
+                resid = ops.bias_add(out, m.b_out, resid)
+            resid = blk.hook_resid_post(resid.view(B, S, D)).reshape(T, D)
+        if last_pos_only:
+            last = resid.view(B, S, D)[:, -1, :].contiguous()
+            return ops.bias_add(ops.linear_tokens(ops.lnpre(last, c.eps), self.unembed.W_U), self.unembed.b_U)
+        logits = ops.bias_add(ops.linear_tokens(ops.lnpre(resid, c.eps), self.unembed.W_U), self.unembed.b_U)
+        return logits.view(B, S, -1)

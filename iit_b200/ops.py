@@ -603,6 +603,215 @@ def linear(x, w, b):
 
 
 # =================================================================================================
+# (b) transformer layers
+# =================================================================================================
+def _as_filter4(w_in_out: torch.Tensor) -> torch.Tensor:
+    """[in, out] weight (transformer_lens layout) viewed as a [K=out, C=in, 1, 1] filter (no copy)."""
+    return w_in_out.t().unsqueeze(-1).unsqueeze(-1)
+
+
+class _LinearTokensFn(torch.autograd.Function):
+    """y[T, out] = x[T, in] @ W[in, out]: a 1x1 convolution over T 'pixels' on the convolution GEMM kernels
+    (tcgen05 when bf16 and both widths are multiples of 64, the exact-fp32 CUDA-core GEMM otherwise)."""
+
+    @staticmethod
+    def forward(ctx, x, W):
+        _require_cuda(x, W)
+        x = x.contiguous()
+        T, cin = x.shape
+        cout = W.shape[1]
+        d = Conv()
+        d.n, d.h, d.w, d.c, d.k, d.r, d.s, d.stride, d.pad, d.p, d.q = T, 1, 1, cin, cout, 1, 1, 1, 0, 1, 1
+        tc = USE_TENSOR_CORES and bool(_lib.lib.iit_conv2d_tc_supported(C.byref(d), _dt(x)))
+        w_oi = filter_relayout(_as_filter4(W.detach()), False, x.dtype)      # dense [out][in]
+        y = torch.empty((T, cout), dtype=x.dtype, device=x.device)
+        if tc:
+            call("iit_conv2d_fprop_tc", _p(x), _p(w_oi), _p(y), C.byref(d), None, None, _stream())
+        else:
+            call("iit_conv2d_fprop", _p(x), _p(w_oi), _p(y), C.byref(d), _dt(x), None, None, _stream())
+        ctx.save_for_backward(x, W)
+        ctx.d, ctx.tc = d, tc
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, W = ctx.saved_tensors
+        d = ctx.d
+        dy = dy.contiguous()
+        dx = dW = None
+        if ctx.needs_input_grad[0]:
+            # dgrad wants the filter as [in][out]: W itself when it is fp32 and dense
+            if x.dtype == torch.float32 and W.is_contiguous():
+                w_io = W.detach()
+            else:
+                w_io = filter_relayout(_as_filter4(W.detach()), True, x.dtype)
+            dx = torch.empty_like(x)
+            if ctx.tc:
+                call("iit_conv2d_dgrad_tc", _p(dy), _p(w_io), _p(dx), C.byref(d), _stream())
+            else:
+                call("iit_conv2d_dgrad", _p(dy), _p(w_io), _p(dx), C.byref(d), _dt(x), _stream())
+        if ctx.needs_input_grad[1]:
+            dwb = torch.empty((d.k, d.c), dtype=torch.float32, device=x.device)   # [out][in]
+            if ctx.tc:
+                need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
+                scratch = torch.empty(need, dtype=torch.uint8, device=x.device)
+                call("iit_conv2d_wgrad_tc", _p(dy), _p(x), _p(dwb), C.byref(d), _p(scratch), need, _stream())
+            else:
+                need = int(_lib.lib.iit_conv2d_wgrad_scratch_bytes(C.byref(d)))
+                scratch = torch.empty(need, dtype=torch.uint8, device=x.device) if need else None
+                call("iit_conv2d_wgrad", _p(dy), _p(x), _p(dwb), C.byref(d), _dt(x), _p(scratch), need, _stream())
+            dW = dwb.t()                                                       # [in][out] view
+        return dx, dW
+
+
+def linear_tokens(x2d: torch.Tensor, W_in_out: torch.Tensor) -> torch.Tensor:
+    return _LinearTokensFn.apply(x2d, W_in_out)
+
+
+def colsum(x2d: torch.Tensor) -> torch.Tensor:
+    out = torch.zeros(x2d.shape[1], dtype=torch.float32, device=x2d.device)
+    call("iit_colsum", _p(x2d), _dt(x2d), _p(out), x2d.shape[0], x2d.shape[1], _stream())
+    return out
+
+
+class _BiasAddFn(torch.autograd.Function):
+    """out = x + bias (+ resid)"""
+
+    @staticmethod
+    def forward(ctx, x, bias, resid):
+        _require_cuda(x, bias, resid)
+        x = x.contiguous()
+        if resid is not None:
+            resid = resid.contiguous()
+        out = torch.empty_like(x)
+        rows, n = x.shape
+        call("iit_bias_act_fwd", _p(x), _p(bias), _p(resid), None, _p(out), _dt(x), rows, n, 0, _stream())
+        ctx.has_bias, ctx.has_res = bias is not None, resid is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        dy = dy.contiguous()
+        db = colsum(dy) if (ctx.has_bias and ctx.needs_input_grad[1]) else None
+        return dy, db, (dy if ctx.has_res else None)
+
+
+def bias_add(x2d, bias, resid=None):
+    return _BiasAddFn.apply(x2d, bias, resid)
+
+
+class _BiasGeluFn(torch.autograd.Function):
+    """post = gelu_new(x + bias), returned in `out_shape` (a fresh tensor, not a view, so a patch hook may
+    overwrite it in place). The pre-activation is kept for the backward only."""
+
+    @staticmethod
+    def forward(ctx, x, bias, out_shape):
+        _require_cuda(x, bias)
+        x = x.contiguous()
+        pre = torch.empty_like(x)
+        post = torch.empty(out_shape, dtype=x.dtype, device=x.device)
+        rows, n = x.shape
+        call("iit_bias_act_fwd", _p(x), _p(bias), None, _p(pre), _p(post), _dt(x), rows, n, 1, _stream())
+        ctx.save_for_backward(pre)
+        return post
+
+    @staticmethod
+    def backward(ctx, dpost):
+        (pre,) = ctx.saved_tensors
+        dpost = dpost.contiguous()
+        dpre = torch.empty_like(pre)
+        call("iit_gelu_bwd", _p(dpost), _p(pre), _p(dpre), _dt(pre), pre.numel(), _stream())
+        db = colsum(dpre) if ctx.needs_input_grad[1] else None
+        return dpre, db, None
+
+
+def bias_gelu(x2d, bias, out_shape):
+    return _BiasGeluFn.apply(x2d, bias, tuple(out_shape))
+
+
+class _LNPreFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, eps):
+        _require_cuda(x)
+        x = x.contiguous()
+        rows, d = x.shape
+        y = torch.empty_like(x)
+        rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+        call("iit_lnpre_fwd", _p(x), _p(y), _p(rstd), _dt(x), rows, d, float(eps), _stream())
+        ctx.save_for_backward(y, rstd)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        y, rstd = ctx.saved_tensors
+        dy = dy.contiguous()
+        dx = torch.empty_like(y)
+        call("iit_lnpre_bwd", _p(dy), _p(y), _p(rstd), _p(dx), _dt(y), y.shape[0], y.shape[1], _stream())
+        return dx, None
+
+
+def lnpre(x2d, eps):
+    return _LNPreFn.apply(x2d, eps)
+
+
+class _AttnFn(torch.autograd.Function):
+    """qkv [B,S,3,H,DH] -> z [B,S,H,DH], causal softmax(q k^T / sqrt(DH)) v."""
+
+    @staticmethod
+    def forward(ctx, qkv):
+        _require_cuda(qkv)
+        qkv = qkv.contiguous()
+        b, s, _, h, dh = qkv.shape
+        z = torch.empty((b, s, h, dh), dtype=qkv.dtype, device=qkv.device)
+        call("iit_attn_fwd", _p(qkv), _p(z), _dt(qkv), b, s, h, dh, _stream())
+        ctx.save_for_backward(qkv)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        (qkv,) = ctx.saved_tensors
+        b, s, _, h, dh = qkv.shape
+        dz = dz.contiguous()
+        dqkv = torch.empty_like(qkv)
+        call("iit_attn_bwd", _p(qkv), _p(dz), _p(dqkv), _dt(qkv), b, s, h, dh, _stream())
+        return dqkv
+
+
+def attention(qkv):
+    return _AttnFn.apply(qkv)
+
+
+class _EmbedFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, tokens, W_E, W_pos, dtype):
+        _require_cuda(tokens, W_E, W_pos)
+        tokens = tokens.contiguous()
+        b, s = tokens.shape
+        v, dm = W_E.shape
+        out = torch.empty((b, s, dm), dtype=dtype, device=tokens.device)
+        call("iit_embed_fwd", _p(tokens), _p(W_E.contiguous()), _p(W_pos.contiguous()), _p(out), _DT[dtype], b * s, s, dm, v,
+             _stream())
+        ctx.save_for_backward(tokens)
+        ctx.shapes = (W_E.shape, W_pos.shape)
+        return out
+
+    @staticmethod
+    def backward(ctx, dres):
+        (tokens,) = ctx.saved_tensors
+        dres = dres.contiguous()
+        (v, dm), pshape = ctx.shapes
+        dWE = torch.zeros((v, dm), dtype=torch.float32, device=dres.device)
+        dWpos = torch.zeros(pshape, dtype=torch.float32, device=dres.device)
+        b, s = tokens.shape
+        call("iit_embed_bwd", _p(tokens), _p(dres), _dt(dres), _p(dWE), _p(dWpos), b * s, s, dm, v, _stream())
+        return None, dWE, dWpos, None
+
+
+def embed(tokens, W_E, W_pos, dtype):
+    return _EmbedFn.apply(tokens, W_E, W_pos, dtype)
+
+
+# =================================================================================================
 # optimiser pieces
 # =================================================================================================
 def sqnorm_(g_flat: torch.Tensor, out: torch.Tensor):

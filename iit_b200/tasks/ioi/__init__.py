@@ -16,3 +16,13 @@ corr_dict = {
 }
 suffixes = {"attn": "attn.hook_z", "mlp": "mlp.hook_post"}
 corr = Correspondence.make_corr_from_dict(corr_dict, suffixes=suffixes, make_suffixes_from_corr=False)
+
+from iit_b200.tasks.ioi.ioi_hl import IOI_HL  # noqa: E402
+
+
+def make_ll_model(device="cuda", dtype=None, **overrides):
+    """The LL transformer of train_ioi.py:30-34 (gpt2 cfg with ioi_cfg applied; no tokenizer needed)."""
+    from iit_b200.nn.transformer import HookedTransformerLL
+    cfg = {"n_ctx": 1024, "d_mlp": 3072, "d_vocab": 50257, "act_fn": "gelu_new", "normalization_type": "LNPre",
+           "init_weights": True, **ioi_cfg, **overrides, "device": str(device)}
+    return HookedTransformerLL(cfg, dtype=dtype).to(device)

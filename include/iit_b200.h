@@ -226,6 +226,33 @@ int iit_linear_bwd(const float* x, const float* w, const float* dy, float* dx, f
                    int n, int in, int out, void* stream);
 
 /* ------------------------------------------------------------------------------------------ */
+/* (b) low-level HookedTransformer (train_ioi.py:30-34; transformer_lens 1.12.1 semantics):        */
+/* everything but the dense contractions, which run on the convolution GEMMs above (a linear layer  */
+/* over tokens is a 1x1 convolution with n = tokens, h = w = 1).                                    */
+/* ------------------------------------------------------------------------------------------ */
+/* resid[t,:] = W_E[tokens[t],:] + W_pos[t % seq,:]  (embed + pos_embed hooks' sum) and its scatter-add
+ * backward into fp32 dW_E / dW_pos (accumulated; caller zeroes). */
+int iit_embed_fwd(const int64_t* tokens, const float* W_E, const float* W_pos, void* out, int dtype,
+                  int64_t ntok, int seq, int d_model, int64_t d_vocab, void* stream);
+int iit_embed_bwd(const int64_t* tokens, const void* dresid, int dtype, float* dW_E, float* dW_pos,
+                  int64_t ntok, int seq, int d_model, int64_t d_vocab, void* stream);
+/* LayerNormPre (folded layer norm): y = (x - mean) / sqrt(var + eps); rstd saved for the backward. */
+int iit_lnpre_fwd(const void* x, void* y, float* rstd, int dtype, int64_t rows, int d, float eps, void* stream);
+int iit_lnpre_bwd(const void* dy, const void* y, const float* rstd, void* dx, int dtype, int64_t rows, int d,
+                  void* stream);
+/* pre = x + bias (+ resid); out = act(pre), act 0: identity, 1: gelu_new. pre_out optional (hook_pre). */
+int iit_bias_act_fwd(const void* x, const float* bias, const void* resid, void* pre_out, void* out, int dtype,
+                     int64_t rows, int n, int act, void* stream);
+int iit_gelu_bwd(const void* dpost, const void* pre, void* dpre, int dtype, int64_t n, void* stream);
+/* out[c] += sum_r x[r,c] (bias gradients; fp32, caller zeroes) */
+int iit_colsum(const void* x, int dtype, float* out, int64_t rows, int64_t n, void* stream);
+/* Causal attention core on the fused projection qkv [B,S,3,H,DH] -> z [B,S,H,DH] (blocks.i.attn.hook_z),
+ * scores / sqrt(DH), softmax over keys <= query. Backward recomputes the pattern. */
+int iit_attn_fwd(const void* qkv, void* z, int dtype, int64_t batch, int seq, int heads, int d_head, void* stream);
+int iit_attn_bwd(const void* qkv, const void* dz, void* dqkv, int dtype, int64_t batch, int seq, int heads,
+                 int d_head, void* stream);
+
+/* ------------------------------------------------------------------------------------------ */
 /* optimiser step pieces (iit_behavior_model_pair.py:60-64, base_model_pair.py:176-180,229)     */
 /* ------------------------------------------------------------------------------------------ */
 /* sqnorm[0] += sum(g^2) over a flat fp32 buffer (clip_grad_norm_'s total norm) */

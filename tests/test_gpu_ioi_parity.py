@@ -1,0 +1,240 @@
+"""GPU parity of the IOI path (HookedTransformer LL, IOI HL, IOI_ModelPair) through the C-ABI against
+  (1) tests/golden/ioi.npz -- the UNMODIFIED reference run through the transformer_lens shim, and
+  (2) oracle/restate.py on the CPU (TransformerOracle / OraclePair) on the same seeded prompts and weights.
+Bars: HL outputs / argmax, node choices, IIA and per-token counts bit-exact; logits and losses 1e-3 (fp32)."""
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from oracle import restate as R  # noqa: E402
+
+GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "ioi.npz"))
+DEV = "cuda"
+V, DM = 101, 128   # the fixture's vocabulary and d_mlp (full-size check below)
+
+
+def dev(inp):
+    return tuple(t.to(DEV) for t in inp)
+
+
+def rel(a, b):
+    return abs(a - b) / max(abs(b), 1e-12)
+
+
+def small_sd():
+    return R.transformer_state_dict(0, d_mlp=DM, d_vocab=V, n_ctx=32)
+
+
+def make_pair(targs=None):
+    from iit_b200.model_pairs import IOI_ModelPair
+    from iit_b200.tasks.ioi import IOI_HL, corr, make_ll_model
+    ll = make_ll_model(device=DEV, d_mlp=DM, d_vocab=V, n_ctx=32)
+    ll.load_state_dict(small_sd())
+    _, names = R.synthetic_ioi(8, 100, d_vocab=V, n_names=20)
+    hl = IOI_HL(V, names).to(DEV)
+    args = {"batch_size": 8, "lr": 1e-3, "iit_weight": 1.0, "behavior_weight": 1.0, "strict_weight": 0.4,
+            "lr_scheduler": None, "clip_grad_norm": 1.0}
+    return IOI_ModelPair(hl, ll, corr, training_args={**args, **(targs or {})}), names
+
+
+def oracle_pair():
+    oll = R.TransformerOracle(small_sd(), 6, 4, 16)
+    _, names = R.synthetic_ioi(8, 100, d_vocab=V, n_names=20)
+    corr = R.ioi_corr()
+    strict = R.nodes_not_in_circuit(6, 4, corr, {"attn": "attn.hook_z", "mlp": "mlp.hook_post"})
+    return R.OraclePair(oll, "ioi", corr, lr=1e-3, weights=(1.0, 1.0, 0.4), strict_nodes=strict, names=names, d_vocab=V), oll
+
+
+def batch(seed):
+    return R.synthetic_ioi(8, seed, d_vocab=V, n_names=20)[0]
+
+
+# ------------------------------------------------------------------------------------------ kernels
+def test_transformer_layer_kernels_match_torch():
+    from iit_b200 import ops
+    g = torch.Generator().manual_seed(0)
+    # LayerNormPre
+    x = (torch.randn(37, 64, generator=g) * 3 + 1).requires_grad_(True)
+    xc = x - x.mean(-1, keepdim=True)
+    y = xc / (xc.pow(2).mean(-1, keepdim=True) + 1e-5).sqrt()
+    gy = torch.randn(y.shape, generator=g)
+    y.backward(gy)
+    xd = x.detach().to(DEV).requires_grad_(True)
+    yd = ops.lnpre(xd, 1e-5)
+    yd.backward(gy.to(DEV))
+    torch.testing.assert_close(yd.cpu(), y.detach(), rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(xd.grad.cpu(), x.grad, rtol=1e-4, atol=1e-6)
+    # attention core
+    B, S, H, dh = 5, 16, 4, 16
+    qkv = torch.randn(B, S, 3, H, dh, generator=g).requires_grad_(True)
+    q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
+    sc = torch.einsum("bqhd,bkhd->bhqk", q, k) / math.sqrt(dh)
+    sc = torch.where(torch.tril(torch.ones(S, S, dtype=torch.bool)), sc, torch.tensor(-torch.inf))
+    z = torch.einsum("bkhd,bhqk->bqhd", v, F.softmax(sc, -1))
+    gz = torch.randn(z.shape, generator=g)
+    z.backward(gz)
+    qd = qkv.detach().to(DEV).requires_grad_(True)
+    zd = ops.attention(qd)
+    zd.backward(gz.to(DEV))
+    torch.testing.assert_close(zd.cpu(), z.detach(), rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(qd.grad.cpu(), qkv.grad, rtol=1e-4, atol=1e-6)
+    # bias + gelu_new, bias + residual, column sums
+    h = torch.randn(33, 128, generator=g).requires_grad_(True)
+    b = torch.randn(128, generator=g).requires_grad_(True)
+    post = R.gelu_new(h + b)
+    gp = torch.randn(post.shape, generator=g)
+    post.backward(gp)
+    hd, bd = h.detach().to(DEV).requires_grad_(True), b.detach().to(DEV).requires_grad_(True)
+    pd = ops.bias_gelu(hd, bd, (33, 128))
+    pd.backward(gp.to(DEV))
+    torch.testing.assert_close(pd.cpu(), post.detach(), rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(hd.grad.cpu(), h.grad, rtol=1e-4, atol=1e-6)
+    torch.testing.assert_close(bd.grad.cpu(), b.grad, rtol=1e-4, atol=1e-5)
+    r = torch.randn(33, 101, generator=g)      # odd width: scalar path
+    b2 = torch.randn(101, generator=g)
+    torch.testing.assert_close(ops.bias_add(r.to(DEV), b2.to(DEV), r.to(DEV)).cpu(), r + b2 + r, rtol=1e-6, atol=1e-6)
+    # linear over tokens (a 1x1 convolution) incl. the odd-width unembed shape, and embedding
+    for (T, cin, cout) in [(40, 64, 192), (40, 128, 64), (9, 64, 101)]:
+        x = torch.randn(T, cin, generator=g).requires_grad_(True)
+        W = (torch.randn(cin, cout, generator=g) / math.sqrt(cin)).requires_grad_(True)
+        y = x @ W
+        gy = torch.randn(y.shape, generator=g)
+        y.backward(gy)
+        xd, Wd = x.detach().to(DEV).requires_grad_(True), W.detach().to(DEV).requires_grad_(True)
+        yd = ops.linear_tokens(xd, Wd)
+        yd.backward(gy.to(DEV))
+        for a, c in ((yd, y), (xd.grad, x.grad), (Wd.grad, W.grad)):
+            torch.testing.assert_close(a.detach().cpu(), c.detach(), rtol=1e-4, atol=1e-5)
+    tok = torch.randint(0, V, (6, 16), generator=g)
+    WE = torch.randn(V, 64, generator=g).requires_grad_(True)
+    WP = torch.randn(32, 64, generator=g).requires_grad_(True)
+    e = WE[tok] + WP[:16].unsqueeze(0)
+    ge = torch.randn(e.shape, generator=g)
+    e.backward(ge)
+    WEd, WPd = WE.detach().to(DEV).requires_grad_(True), WP.detach().to(DEV).requires_grad_(True)
+    ed = ops.embed(tok.to(DEV), WEd, WPd, torch.float32)
+    ed.backward(ge.to(DEV))
+    torch.testing.assert_close(ed.cpu(), e.detach(), rtol=1e-6, atol=1e-6)
+    torch.testing.assert_close(WEd.grad.cpu(), WE.grad, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(WPd.grad.cpu(), WP.grad, rtol=1e-5, atol=1e-5)
+
+
+def test_full_size_forward_matches_oracle():
+    """The real IOI configuration (d_mlp 3072, vocabulary 50257): logits at every position and last-position only."""
+    from iit_b200.tasks.ioi import make_ll_model
+    sd = R.transformer_state_dict(1)
+    ll = make_ll_model(device=DEV)
+    ll.load_state_dict(sd)
+    oll = R.TransformerOracle(sd, 6, 4, 16)
+    (x, _, _), _ = R.synthetic_ioi(3, 5, one_hot=False)
+    with torch.no_grad():
+        want = oll(x)
+        got = ll(x.to(DEV))
+        last = ll(x.to(DEV), last_pos_only=True)
+    scale = want.abs().max().item()
+    assert (got.cpu() - want).abs().max().item() <= 1e-3 * scale
+    assert (last.cpu() - want[:, -1, :]).abs().max().item() <= 1e-3 * scale
+    assert torch.equal(got.cpu().argmax(-1), want.argmax(-1))
+
+
+# ------------------------------------------------------------------------------------------ pair
+def test_do_intervention_and_losses_match_reference_golden():
+    pair, names = make_pair()
+    assert np.array_equal(names.numpy(), GOLD["names"])
+    assert [f"{n.name}|{n.index}" for n in pair.nodes_not_in_circuit] == GOLD["nodes_not_in_circuit"].tolist()
+    pair.ll_model.train()
+    base, src = dev(batch(100)), dev(batch(200))
+    hl_full = pair.hl_model((base[0], None, None))
+    assert np.array_equal(hl_full.cpu().numpy(), GOLD["hl/base_full"])
+    for k in pair.corr:
+        hl, llo = pair.do_intervention(base, src, k)
+        assert np.array_equal(hl[:, -1, :].cpu().numpy(), GOLD[f"di/{k.name}/hl_last"])
+        np.testing.assert_allclose(llo[:, -1, :].detach().cpu().numpy(), GOLD[f"di/{k.name}/ll_last"], rtol=1e-3, atol=1e-4)
+        loss = pair.get_IIT_loss_over_batch(base, src, k, pair.loss_fn)
+        assert rel(loss.item(), float(GOLD[f"di/{k.name}/iit_loss"])) < 1e-3
+        # the reference-style loss_fn on the dense tensors gives the same number as the sparse fast path
+        am = torch.argmax(hl[:, -1, :], dim=-1)
+        probs = F.one_hot(am, num_classes=V).float()
+        assert rel(pair.loss_fn(llo, probs.unsqueeze(1).expand(-1, 16, -1).contiguous()).item(),
+                   float(GOLD[f"di/{k.name}/iit_loss"])) < 1e-3
+
+
+def test_train_steps_follow_reference_golden():
+    """Free-running IOI_ModelPair.run_train_step x3 (strict: 3 updates per step). The transformer has no
+    batch statistics / ReLU kinks, so the trajectory stays close: 1e-3 on the first loss, 5e-3 after updates."""
+    pair, _ = make_pair()
+    opt = pair.make_optimizer()
+    pair.ll_model.train()
+    seq = []
+    for step in range(3):
+        state = pair.rng.bit_generator.state
+        seq.append(str(pair.sample_hl_name()))
+        n = pair.sample_ll_node()
+        seq.append(f"{n.name}|{n.index}")
+        pair.rng.bit_generator.state = state
+        m = pair.run_train_step(dev(batch(100 + step)), dev(batch(200 + step)), pair.loss_fn, opt)
+        tol = 1e-3 if step == 0 else 5e-3
+        assert rel(m["train/iit_loss"], GOLD["train/iit_loss"][step]) < tol, (step, m)
+        assert rel(m["train/strict_loss"], GOLD["train/strict_loss"][step]) < 5e-3, (step, m)
+        assert rel(m["train/behavior_loss"], GOLD["train/behavior_loss"][step]) < 5e-3, (step, m)
+    assert seq == GOLD["choice_sequence"].tolist()     # HL node then LL node per step: bit-exact
+
+
+def test_teacher_forced_terms_and_eval_match_oracle():
+    pair, _ = make_pair()
+    opair, oll = oracle_pair()
+    opt = pair.make_optimizer()
+    ll = pair.ll_model
+    ll.train()
+    for step in range(2):
+        b, s = batch(100 + step), batch(200 + step)
+        bd, sd_ = dev(b), dev(s)
+        hl_node = pair.sample_hl_name()
+        assert str(hl_node) == opair.sample_hl_name()
+        ll_node = pair.sample_ll_node()
+        o_ll_node = opair.sample_ll_node()
+        assert ll_node.name == o_ll_node[0]
+        terms = [
+            ("iit", lambda: pair.get_IIT_loss_over_batch(bd, sd_, hl_node, pair.loss_fn),
+             lambda: opair.iit_loss(b, s, str(hl_node))),
+            ("strict", lambda: pair.get_strict_loss_over_batch(bd, sd_, ll_node, pair.loss_fn),
+             lambda: opair.loss_fn(R.ll_intervention(oll, b[0], s[0], [o_ll_node])[0], b[1])),
+            ("behaviour", lambda: pair.get_behaviour_loss_over_batch(bd, pair.loss_fn),
+             lambda: opair.loss_fn(oll(b[0]), b[1])),
+        ]
+        for name, mine_fn, oracle_fn in terms:
+            ll.load_state_dict({k: v.detach() for k, v in oll.p.items()})
+            opt.zero_grad()
+            lm = mine_fn()
+            lm.backward()
+            opair.opt.zero_grad()
+            lo = oracle_fn()
+            lo.backward()
+            assert rel(lm.item(), lo.item()) < 1e-3, (step, name, lm.item(), lo.item())
+            num = den = 0.0
+            for k, p in ll.named_parameters():
+                og = oll.p[k].grad
+                og = torch.zeros_like(oll.p[k]) if og is None else og
+                num += float(((p.grad.detach().cpu().double() - og.double()) ** 2).sum())
+                den += float((og.double() ** 2).sum())
+            assert (num / den) ** 0.5 < 1e-3, (step, name, (num / den) ** 0.5)
+            torch.nn.utils.clip_grad_norm_(oll.parameters(), 1.0)
+            opair.opt.step()
+    # evaluation from the oracle's weights: integer counts must be equal
+    ll.load_state_dict({k: v.detach() for k, v in oll.p.items()})
+    ll.eval()
+    for i in range(2):
+        b, s = batch(300 + i), batch(400 + i)
+        want = opair.eval_step(b, s)
+        with torch.no_grad():
+            got = pair.run_eval_step(dev(b), dev(s), pair.loss_fn)
+        assert got["val/IIA"] == want["val/IIA"], (got, want)
+        assert np.array_equal(got["val/per_token_accuracy"], want["val/per_token_accuracy"])
+        assert got["val/accuracy"] == want["val/accuracy"]
+        assert rel(got["val/iit_loss"], want["val/iit_loss"]) < 1e-3
