@@ -269,7 +269,11 @@ def run_ours(args, rank, world, local):
     sampler.start()
     launches0 = _lib.launch_count()
     timer.enabled = not args.graphs
+    if args.profile_range:
+        torch.cuda.profiler.start()   # ncu --profile-from-start off: only the timed region is profiled
     sec, metrics = timed(step_resident, args.steps)
+    if args.profile_range:
+        torch.cuda.profiler.stop()
     timer.enabled = False
     launches = _lib.launch_count() - launches0
     clocks = sampler.stop()
@@ -328,6 +332,7 @@ def main():
     ap.add_argument("--batch", type=int, default=4096)
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around the timed region")
     ap.add_argument("--graphs", type=int, default=1, help="1: replay each (loss term, node) variant from a CUDA graph")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

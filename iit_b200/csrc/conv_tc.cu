@@ -102,8 +102,13 @@ struct TcParams {
   int8_t wk[9];           // per-tap block index in the filter matrix (reduction offset = wk*Cin)
   int BW, BH, BNI;        // pixel box
   int tiles_w, tiles_h;   // boxes per image row / column
+  int tiles_n;            // image blocks
 };
 
+// Persistent: gridDim.x CTAs walk the tile list (tile = pixel box x filter block; filter block fastest so that CTAs
+// working at the same time share the pixel box through L2). The shared-memory ring runs across tile boundaries, and
+// the accumulator is double-buffered in TMEM (2 x BN columns): while the epilogue warps drain tile i the MMA warp is
+// already accumulating tile i+1.
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_constant__ CUtensorMap map_a,
                                                                 const __grid_constant__ CUtensorMap map_b,
@@ -117,28 +122,25 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
   uint8_t* sB = smem + STAGES * A_BYTES;
   uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * B_BYTES);
   uint64_t* empty = full + STAGES;
-  uint64_t* tmem_full = empty + STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
-  float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [2][BN] per-channel sum / sum of squares of this tile
-  if (bn_sum != nullptr && threadIdx.x < 2 * BN / 2) { s_stat[threadIdx.x] = 0.f; s_stat[threadIdx.x + BN] = 0.f; }
+  uint64_t* tmem_full = empty + STAGES;      // [2]
+  uint64_t* tmem_empty = tmem_full + 2;      // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [2][BN] per-channel sum / sum of squares of one tile
+  if (bn_sum != nullptr && threadIdx.x < BN) { s_stat[threadIdx.x] = 0.f; s_stat[threadIdx.x + BN] = 0.f; }
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // tile -> (image block, row block, column block); blockIdx.y -> filter block
-  int t = blockIdx.x;
-  const int tw = t % p.tiles_w; t /= p.tiles_w;
-  const int th = t % p.tiles_h; t /= p.tiles_h;
-  const int n0 = t * p.BNI, p0 = th * p.BH, q0 = tw * p.BW;
-  const int co0 = blockIdx.y * BN;
   const int kchunks = p.Cin / TC_BK;
   const int nk = p.ntaps * kchunks;
+  const int nblk = p.Cout / BN;
+  const int total_tiles = p.tiles_w * p.tiles_h * p.tiles_n * nblk;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    mbar_init(tmem_full, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {  // TMEM allocation is warp-collective; this warp also frees it
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(BN));
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(2 * BN));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -147,40 +149,54 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (lane == 0 && nk > 0) {
       asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
       int stage = 0;
       uint32_t phase = 0;
-      for (int kb = 0; kb < nk; ++kb) {
-        const int tap = kb / kchunks, kc = kb - tap * kchunks;
-        mbar_wait(&empty[stage], phase ^ 1);
-        mbar_expect_tx(&full[stage], A_BYTES + B_BYTES);
-        tma_load_4d(sA + stage * A_BYTES, &map_a, &full[stage], kc * TC_BK, q0 * p.in_mul + p.dw[tap],
-                    p0 * p.in_mul + p.dh[tap], n0);
-        tma_load_2d(sB + stage * B_BYTES, &map_b, &full[stage], p.wk[tap] * p.Cin + kc * TC_BK, co0);
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        int t = tile;
+        const int co0 = (t % nblk) * BN; t /= nblk;
+        const int tw = t % p.tiles_w; t /= p.tiles_w;
+        const int th = t % p.tiles_h; t /= p.tiles_h;
+        const int n0 = t * p.BNI, p0 = th * p.BH, q0 = tw * p.BW;
+        for (int kb = 0; kb < nk; ++kb) {
+          const int tap = kb / kchunks, kc = kb - tap * kchunks;
+          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_expect_tx(&full[stage], A_BYTES + B_BYTES);
+          tma_load_4d(sA + stage * A_BYTES, &map_a, &full[stage], kc * TC_BK, q0 * p.in_mul + p.dw[tap],
+                      p0 * p.in_mul + p.dh[tap], n0);
+          tma_load_2d(sB + stage * B_BYTES, &map_b, &full[stage], p.wk[tap] * p.Cin + kc * TC_BK, co0);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (lane == 0 && nk > 0) {
       // instruction descriptor: D=f32, A=B=bf16, both K-major, N at [17,23), M at [24,29)
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
       int stage = 0;
       uint32_t phase = 0;
-      for (int kb = 0; kb < nk; ++kb) {
-        mbar_wait(&full[stage], phase);
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        const uint32_t acc = it & 1, acc_phase = (it >> 1) & 1;
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);   // the epilogue has drained this accumulator
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t a0 = smem_u32(sA + stage * A_BYTES), b0 = smem_u32(sB + stage * B_BYTES);
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = 0; kb < nk; ++kb) {
+          mbar_wait(&full[stage], phase);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t a0 = smem_u32(sA + stage * A_BYTES), b0 = smem_u32(sB + stage * B_BYTES);
 #pragma unroll
-        for (int k = 0; k < TC_BK / TC_UK; ++k) {
-          umma_bf16(tmem_base, umma_desc_k_sw128(a0 + k * TC_UK * 2), umma_desc_k_sw128(b0 + k * TC_UK * 2), idesc,
-                    (uint32_t)((kb | k) != 0));
+          for (int k = 0; k < TC_BK / TC_UK; ++k) {
+            umma_bf16(tmem_d, umma_desc_k_sw128(a0 + k * TC_UK * 2), umma_desc_k_sw128(b0 + k * TC_UK * 2), idesc,
+                      (uint32_t)((kb | k) != 0));
+          }
+          umma_commit(&empty[stage]);  // frees this smem stage once the MMAs above have read it
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&empty[stage]);  // frees this smem stage once the MMAs above have read it
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        umma_commit(&tmem_full[acc]);  // accumulator complete
       }
-      if (nk > 0) umma_commit(tmem_full);  // accumulator complete
     }
   } else {
     // epilogue: warp w may read TMEM lanes [32*(w%4), 32*(w%4)+32)
@@ -189,74 +205,98 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
     const int wl = m % p.BW;
     const int hl = (m / p.BW) % p.BH;
     const int nl = m / (p.BW * p.BH);
-    const int n = n0 + nl, pp = p0 + hl, qq = q0 + wl;
-    const bool ok = n < p.N && pp < p.P && qq < p.Q;
-    __nv_bfloat16* dst = out + (((int64_t)n * p.OH + (pp * p.out_mul + p.out_oh)) * p.OW + (qq * p.out_mul + p.out_ow)) * p.Cout + co0;
-    if (nk > 0) {
-      mbar_wait(tmem_full, 0);
-      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    }
-#pragma unroll
-    for (int c = 0; c < BN; c += 32) {
-      uint32_t v[32];
+    const int e = threadIdx.x - 64;     // 0..127: owner of channel e of the current filter block's statistics
+    double run_s = 0.0, run_q = 0.0;    // this CTA's running totals for channel run_co + e
+    int run_co = -1;
+    uint32_t it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      int t = tile;
+      const int co0 = (t % nblk) * BN; t /= nblk;
+      const int tw = t % p.tiles_w; t /= p.tiles_w;
+      const int th = t % p.tiles_h; t /= p.tiles_h;
+      const int n = t * p.BNI + nl, pp = th * p.BH + hl, qq = tw * p.BW + wl;
+      const bool ok = n < p.N && pp < p.P && qq < p.Q;
+      __nv_bfloat16* dst = out + (((int64_t)n * p.OH + (pp * p.out_mul + p.out_oh)) * p.OW + (qq * p.out_mul + p.out_ow)) * p.Cout + co0;
+      const uint32_t acc = it & 1, acc_phase = (it >> 1) & 1;
       if (nk > 0) {
-        tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c, v);
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = 0u;
+        mbar_wait(&tmem_full[acc], acc_phase);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       }
-      if (ok) {
 #pragma unroll
-        for (int j = 0; j < 32; j += 8) {
-          uint4 o;
-          __nv_bfloat162 h0 = __floats2bfloat162_rn(__uint_as_float(v[j + 0]), __uint_as_float(v[j + 1]));
-          __nv_bfloat162 h1 = __floats2bfloat162_rn(__uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
-          __nv_bfloat162 h2 = __floats2bfloat162_rn(__uint_as_float(v[j + 4]), __uint_as_float(v[j + 5]));
-          __nv_bfloat162 h3 = __floats2bfloat162_rn(__uint_as_float(v[j + 6]), __uint_as_float(v[j + 7]));
-          o.x = *reinterpret_cast<uint32_t*>(&h0); o.y = *reinterpret_cast<uint32_t*>(&h1);
-          o.z = *reinterpret_cast<uint32_t*>(&h2); o.w = *reinterpret_cast<uint32_t*>(&h3);
-          *reinterpret_cast<uint4*>(dst + c + j) = o;
+      for (int c = 0; c < BN; c += 32) {
+        uint32_t v[32];
+        if (nk > 0) {
+          tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c), v);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0u;
+        }
+        if (c + 32 >= BN && nk > 0) {
+          // all of this warp's TMEM reads of the accumulator are complete: hand it back to the MMA warp
+          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[acc])) : "memory");
+        }
+        if (ok) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            uint4 o;
+            __nv_bfloat162 h0 = __floats2bfloat162_rn(__uint_as_float(v[j + 0]), __uint_as_float(v[j + 1]));
+            __nv_bfloat162 h1 = __floats2bfloat162_rn(__uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(__uint_as_float(v[j + 4]), __uint_as_float(v[j + 5]));
+            __nv_bfloat162 h3 = __floats2bfloat162_rn(__uint_as_float(v[j + 6]), __uint_as_float(v[j + 7]));
+            o.x = *reinterpret_cast<uint32_t*>(&h0); o.y = *reinterpret_cast<uint32_t*>(&h1);
+            o.z = *reinterpret_cast<uint32_t*>(&h2); o.w = *reinterpret_cast<uint32_t*>(&h3);
+            *reinterpret_cast<uint4*>(dst + c + j) = o;
+          }
+        }
+        if (bn_sum != nullptr) {
+          // BatchNorm statistics of the values as stored (bf16-rounded), for the BN that follows this conv.
+          // Each lane holds one pixel x 32 channels; a butterfly that halves the channel set per step leaves
+          // lane l with the warp total of channel c+l after 31 shuffles (instead of 32 x 5).
+          float a[32], b[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            float f = ok ? __bfloat162float(__float2bfloat16_rn(__uint_as_float(v[j]))) : 0.f;
+            a[j] = f; b[j] = f * f;
+          }
+#pragma unroll
+          for (int h = 16; h >= 1; h >>= 1) {
+            const bool up = (lane & h) != 0;
+#pragma unroll
+            for (int i = 0; i < h; ++i) {
+              float sa = up ? a[i] : a[i + h], ka = up ? a[i + h] : a[i];
+              float sb = up ? b[i] : b[i + h], kb = up ? b[i + h] : b[i];
+              a[i] = ka + __shfl_xor_sync(0xffffffffu, sa, h);
+              b[i] = kb + __shfl_xor_sync(0xffffffffu, sb, h);
+            }
+          }
+          atomicAdd(&s_stat[c + lane], a[0]);
+          atomicAdd(&s_stat[BN + c + lane], b[0]);
         }
       }
       if (bn_sum != nullptr) {
-        // BatchNorm statistics of the values as stored (bf16-rounded), for the BN that follows this conv.
-        // Each lane holds one pixel x 32 channels; a butterfly that halves the channel set per step leaves
-        // lane l with the warp total of channel c+l after 31 shuffles (instead of 32 x 5).
-        float a[32], b[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          float f = ok ? __bfloat162float(__float2bfloat16_rn(__uint_as_float(v[j]))) : 0.f;
-          a[j] = f; b[j] = f * f;
-        }
-#pragma unroll
-        for (int h = 16; h >= 1; h >>= 1) {
-          const bool up = (lane & h) != 0;
-#pragma unroll
-          for (int i = 0; i < h; ++i) {
-            float sa = up ? a[i] : a[i + h], ka = up ? a[i + h] : a[i];
-            float sb = up ? b[i] : b[i + h], kb = up ? b[i + h] : b[i];
-            a[i] = ka + __shfl_xor_sync(0xffffffffu, sa, h);
-            b[i] = kb + __shfl_xor_sync(0xffffffffu, sb, h);
+        asm volatile("bar.sync 1, 128;" ::: "memory");   // the four epilogue warps only: the tile's sums are complete
+        if (e < BN) {
+          if (run_co != co0) {
+            if (run_co >= 0) { atomicAdd(&bn_sum[run_co + e], run_s); atomicAdd(&bn_sq[run_co + e], run_q); }
+            run_co = co0; run_s = 0.0; run_q = 0.0;
           }
+          run_s += (double)s_stat[e]; run_q += (double)s_stat[BN + e];
+          s_stat[e] = 0.f; s_stat[BN + e] = 0.f;
         }
-        atomicAdd(&s_stat[c + lane], a[0]);
-        atomicAdd(&s_stat[BN + c + lane], b[0]);
+        asm volatile("bar.sync 1, 128;" ::: "memory");   // zeroed before the next tile adds to it
       }
     }
-    if (bn_sum != nullptr) {
-      asm volatile("bar.sync 1, 128;" ::: "memory");   // the four epilogue warps only
-      const int e = threadIdx.x - 64;                  // 0..127
-      if (e < BN) {
-        atomicAdd(&bn_sum[co0 + e], (double)s_stat[e]);
-        atomicAdd(&bn_sq[co0 + e], (double)s_stat[BN + e]);
-      }
+    if (bn_sum != nullptr && e < BN && run_co >= 0) {
+      atomicAdd(&bn_sum[run_co + e], run_s); atomicAdd(&bn_sq[run_co + e], run_q);
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(BN));
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * BN));
   }
 }
 
@@ -280,15 +320,20 @@ static EncodeTiledFn get_encode() {
 static int pow2_ge(int v) { int r = 1; while (r < v) r <<= 1; return r; }
 
 template <int BN>
-static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16* out, const TcParams& p, dim3 grid,
+static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16* out, const TcParams& p, int total_tiles,
                      cudaStream_t st, double* bn_sum, double* bn_sq) {
-  constexpr int STAGES = BN == 64 ? 4 : 4;
-  constexpr size_t smem = STAGES * (TC_BM * TC_BK * 2 + BN * TC_BK * 2) + (2 * STAGES + 1) * 8 + 16 + 2 * BN * 4 + 1024;
-  static bool attr_set = false;
-  if (!attr_set) {
+  constexpr int STAGES = 4;
+  constexpr size_t smem = STAGES * (TC_BM * TC_BK * 2 + BN * TC_BK * 2) + (2 * STAGES + 4) * 8 + 16 + 2 * BN * 4 + 1024;
+  static int ctas_per_sm = 0;
+  if (!ctas_per_sm) {
     IIT_CUDA(cudaFuncSetAttribute(conv3x3_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
+    int occ = 0;
+    IIT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv3x3_tc_kernel<BN, STAGES>, TC_THREADS, smem));
+    const int tmem_limit = 512 / (2 * BN);   // every resident CTA holds 2*BN TMEM columns for its whole life
+    ctas_per_sm = occ < 1 ? 1 : (occ > tmem_limit ? tmem_limit : occ);
   }
+  int grid = kNumSMs * ctas_per_sm;
+  if (grid > total_tiles) grid = total_tiles;
   conv3x3_tc_kernel<BN, STAGES><<<grid, TC_THREADS, smem, st>>>(ma, mb, out, p, bn_sum, bn_sq);
   return 0;
 }
@@ -336,14 +381,15 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
   plan_box(tp.P, tp.Q, TC_BM, &tp.BW, &tp.BH, &tp.BNI);
   tp.tiles_w = (tp.Q + tp.BW - 1) / tp.BW;
   tp.tiles_h = (tp.P + tp.BH - 1) / tp.BH;
-  const int tiles_n = (tp.N + tp.BNI - 1) / tp.BNI;
+  tp.tiles_n = (tp.N + tp.BNI - 1) / tp.BNI;
   const int BN = (tp.Cout % 128 == 0) ? 128 : 64;
   CUtensorMap ma, mb;
   if (encode_nhwc_strided(&ma, gathered, gC, gW, gH, tp.N, tp.BW, tp.BH, tp.BNI, tp.in_mul, name)) return 1;
   if (encode_filter(&mb, wmat, Kg, tp.Cout, BN, name)) return 1;
-  dim3 grid((unsigned)(tp.tiles_w * tp.tiles_h * tiles_n), (unsigned)(tp.Cout / BN));
-  int rc = BN == 128 ? launch_tc<128>(ma, mb, (__nv_bfloat16*)out, tp, grid, st, bn_sum, bn_sq)
-                     : launch_tc<64>(ma, mb, (__nv_bfloat16*)out, tp, grid, st, bn_sum, bn_sq);
+  const int64_t total = (int64_t)tp.tiles_w * tp.tiles_h * tp.tiles_n * (tp.Cout / BN);
+  IIT_REQUIRE(total < (1ll << 31), "%s: too many tiles", name);
+  int rc = BN == 128 ? launch_tc<128>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq)
+                     : launch_tc<64>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq);
   if (rc) return rc;
   IIT_LAUNCH_CHECK(name);
   return 0;

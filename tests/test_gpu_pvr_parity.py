@@ -278,7 +278,7 @@ def test_bf16_path_close_to_fp32_oracle():
 def test_cuda_graph_step_equals_eager_step():
     """training_args["cuda_graphs"]: each (term, node) variant replayed from a captured graph. Same kernels, same
     order, same inputs => the losses of a free-running 3-step trajectory must agree with the eager path to fp32
-    rounding of the atomically accumulated BN sums (1e-4), and capture must leave model/optimizer state untouched."""
+    rounding of the atomically accumulated BN sums re-rounded to bf16 (1e-3 at this 8-pair batch), and capture must leave model/optimizer state untouched."""
     from iit_b200.model_pairs import StrictIITModelPair
     res = {}
     for mode in ("eager", "graphs"):
@@ -303,4 +303,4 @@ def test_cuda_graph_step_equals_eager_step():
     for i, (e, g) in enumerate(zip(res["eager"], res["graphs"])):
         for k in e:  # bf16 free-running trajectories with atomically ordered BN sums (see the chaos note above)
             assert rel(g[k], e[k]) < (5e-2 if i == 0 else 2e-1), (i, k, e, g)
-    assert rel(res["graphs"][0]["train/iit_loss"], res["eager"][0]["train/iit_loss"]) < 1e-4
+    assert rel(res["graphs"][0]["train/iit_loss"], res["eager"][0]["train/iit_loss"]) < 1e-3
