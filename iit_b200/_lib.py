@@ -83,6 +83,8 @@ SIGNATURES = {
     "iit_colsum": [_vp, _i, _vp, _i64, _i64, _vp],
     "iit_attn_fwd": [_vp, _vp, _i, _i64, _i, _i, _i, _vp],
     "iit_attn_bwd": [_vp, _vp, _vp, _i, _i64, _i, _i, _i, _vp],
+    "iit_bn_relu_maxpool_fwd": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp],
+    "iit_bn_relu_maxpool_bwd": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "iit_sqnorm": [_vp, _i64, _vp, _vp],
     "iit_adam_step": [_vp, _vp, _vp, _vp, _i64, _d, _d, _d, _d, _i64, _vp, _d, _vp],
     "iit_adam_step_dev": [_vp, _vp, _vp, _vp, _i64, _vp, _d, _d, _d, _vp, _vp, _d, _vp],

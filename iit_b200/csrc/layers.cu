@@ -446,6 +446,17 @@ __global__ void __launch_bounds__(256) adam_dev_kernel(float* __restrict__ p, co
   }
 }
 
+// bn_fast.cu: 16-byte-per-thread kernels with register-resident per-channel constants
+bool bn_fast_ok(int dtype, int C, const void* a, const void* b, const void* c, const void* d, const void* e);
+int bn_stats_fast(const void* x, int dtype, int64_t rows, int C, double* sum, double* sq, cudaStream_t st);
+int bn_act_fwd_fast(const void* x, const void* res, void* y, int dtype, int64_t rows, int C, const float* mean, const float* invstd,
+                    const float* gamma, const float* beta, int relu, cudaStream_t st);
+int bn_bwd_reduce_fast(const void* dy, const void* y, const void* x, int dtype, int64_t rows, int C, const float* mean,
+                       const float* invstd, int relu, double* dgamma, double* dbeta, cudaStream_t st);
+int bn_bwd_apply_fast(const void* dy, const void* y, const void* x, void* dx, void* dres, int dtype, int64_t rows, int C,
+                      const float* mean, const float* invstd, const float* gamma, const double* dgamma, const double* dbeta,
+                      int relu, cudaStream_t st);
+
 }  // namespace iit
 
 using namespace iit;
@@ -467,6 +478,7 @@ static inline dim3 red_grid(int64_t rows, int C) {
 
 extern "C" int iit_bn_stats(const void* x, int dtype, int64_t rows, int c, double* sum, double* sqsum, void* stream) {
   IIT_REQUIRE(x && sum && sqsum && rows >= 1, "iit_bn_stats: bad arguments");
+  if (bn_fast_ok(dtype, c, x, nullptr, nullptr, nullptr, nullptr)) return bn_stats_fast(x, dtype, rows, c, sum, sqsum, as_stream(stream));
   IIT_REQUIRE(c % 4 == 0 && (c / 4 <= 64 ? 256 % (c / 4) == 0 : (c / 4) % 64 == 0), "iit_bn_stats: unsupported channel count %d", c);
   RedPtrs2 o{{sum, sqsum}};
   IIT_DISPATCH_DTYPE(dtype, T, {
@@ -496,6 +508,8 @@ extern "C" int iit_bn_eval_invstd(const float* running_var, int c, float eps, fl
 extern "C" int iit_bn_act_fwd(const void* x, const void* residual, void* y, int dtype, int64_t rows, int c, const float* mean,
                               const float* invstd, const float* gamma, const float* beta, int relu, void* stream) {
   IIT_REQUIRE(x && y && mean && invstd && gamma && beta, "iit_bn_act_fwd: null pointer");
+  if (bn_fast_ok(dtype, c, x, residual, y, mean, invstd) && bn_fast_ok(dtype, c, gamma, beta, nullptr, nullptr, nullptr))
+    return bn_act_fwd_fast(x, residual, y, dtype, rows, c, mean, invstd, gamma, beta, relu, as_stream(stream));
   IIT_REQUIRE(c % 4 == 0, "iit_bn_act_fwd: channels must be a multiple of 4");
   int64_t n4 = rows * c / 4;
   IIT_DISPATCH_DTYPE(dtype, T, {
@@ -510,6 +524,8 @@ extern "C" int iit_bn_act_bwd_reduce(const void* dy, const void* y, const void* 
                                      const float* mean, const float* invstd, int relu, double* dgamma, double* dbeta,
                                      void* stream) {
   IIT_REQUIRE(dy && x && mean && invstd && dgamma && dbeta && (!relu || y), "iit_bn_act_bwd_reduce: null pointer");
+  if (bn_fast_ok(dtype, c, dy, y, x, mean, invstd))
+    return bn_bwd_reduce_fast(dy, y, x, dtype, rows, c, mean, invstd, relu, dgamma, dbeta, as_stream(stream));
   IIT_REQUIRE(c % 4 == 0 && (c / 4 <= 64 ? 256 % (c / 4) == 0 : (c / 4) % 64 == 0), "iit_bn_act_bwd_reduce: unsupported channel count %d", c);
   RedPtrs2 o{{dgamma, dbeta}};
   IIT_DISPATCH_DTYPE(dtype, T, {
@@ -524,6 +540,8 @@ extern "C" int iit_bn_act_bwd_apply(const void* dy, const void* y, const void* x
                                     int c, const float* mean, const float* invstd, const float* gamma, const double* dgamma,
                                     const double* dbeta, int relu, void* stream) {
   IIT_REQUIRE(dy && x && dx && mean && invstd && gamma && dgamma && dbeta && (!relu || y), "iit_bn_act_bwd_apply: null pointer");
+  if (bn_fast_ok(dtype, c, dy, y, x, dx, dres) && bn_fast_ok(dtype, c, mean, invstd, gamma, nullptr, nullptr))
+    return bn_bwd_apply_fast(dy, y, x, dx, dres, dtype, rows, c, mean, invstd, gamma, dgamma, dbeta, relu, as_stream(stream));
   IIT_REQUIRE(c % 4 == 0, "iit_bn_act_bwd_apply: channels must be a multiple of 4");
   int64_t n4 = rows * c / 4;
   IIT_DISPATCH_DTYPE(dtype, T, {

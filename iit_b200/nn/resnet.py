@@ -223,12 +223,27 @@ class ResNet18LL(HookedRootModule):
         if not stem_tc and (x.dtype != self.act_dtype or not ops._is_cl(x)):
             # the tensor-core stem reads the caller's tensor (fp32 NCHW included) directly; otherwise convert
             x = x.to(self.act_dtype).contiguous(memory_format=torch.channels_last)
-        if m.bn1.hook_point.has_hooks():
-            x = m.bn1.hook_point(_conv_bn(m.conv1, m.bn1, x, act_dtype=self.act_dtype))
-            x = m.relu.hook_point(m.relu.mod(x))
+        bn = m.bn1.mod
+        fuse_tail = (not m.bn1.hook_point.has_hooks() and not m.relu.hook_point.has_hooks()
+                     and bn.c % 64 == 0 and (bn.training or not torch.is_grad_enabled()))
+        if fuse_tail:
+            # conv1 -> hook -> [bn1 -> relu -> maxpool] in one kernel: nothing between them is observed
+            sums = None
+            if bn.training and not m.conv1.hook_point.has_hooks():
+                sums = ops.new_bn_sums(bn.c, x.device)
+            y0 = m.conv1.hook_point(m.conv1.mod(x, sums, self.act_dtype))
+            if bn.training:
+                bn.num_batches_tracked.add_(1)
+            x = ops.bn_relu_maxpool(y0, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.training, bn.momentum,
+                                    bn.eps, sums)
+            x = m.maxpool.hook_point(x)
         else:
-            x = m.relu.hook_point(_conv_bn(m.conv1, m.bn1, x, relu=True, act_dtype=self.act_dtype))
-        x = m.maxpool.hook_point(m.maxpool.mod(x))
+            if m.bn1.hook_point.has_hooks():
+                x = m.bn1.hook_point(_conv_bn(m.conv1, m.bn1, x, act_dtype=self.act_dtype))
+                x = m.relu.hook_point(m.relu.mod(x))
+            else:
+                x = m.relu.hook_point(_conv_bn(m.conv1, m.bn1, x, relu=True, act_dtype=self.act_dtype))
+            x = m.maxpool.hook_point(m.maxpool.mod(x))
         for i in range(1, 5):
             layer: Wrapped = getattr(m, f"layer{i}")
             x = self._block(layer.mod[0], x)

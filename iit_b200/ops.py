@@ -468,6 +468,55 @@ def bn_act(x, gamma, beta, residual, running_mean, running_var, training, moment
     return _BNActFn.apply(x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums)
 
 
+class _BNReluPoolFn(torch.autograd.Function):
+    """bn (train or eval statistics) -> relu -> maxpool 3x3/2 of the stem conv output as one kernel; the
+    backward recomputes the activation from the conv output (nothing but the window index is stored)."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, running_mean, running_var, training, momentum, eps, sums):
+        _require_cuda(x, gamma, beta)
+        x = _cl(x)
+        n, c, h, w = x.shape
+        rows = n * h * w
+        st = _stream()
+        if training:
+            if sums is None:
+                sums = new_bn_sums(c, x.device)
+                call("iit_bn_stats", _p(x), _dt(x), rows, c, _p(sums[0]), _p(sums[1]), st)
+            mean = torch.empty(c, dtype=torch.float32, device=x.device)
+            invstd = torch.empty(c, dtype=torch.float32, device=x.device)
+            call("iit_bn_finalize", _p(sums[0]), _p(sums[1]), rows, c, float(eps), float(momentum), _p(mean), _p(invstd),
+                 _p(running_mean), _p(running_var), st)
+        else:
+            mean = running_mean
+            invstd = torch.empty(c, dtype=torch.float32, device=x.device)
+            call("iit_bn_eval_invstd", _p(running_var), c, float(eps), _p(invstd), st)
+        p, q = (h + 2 - 3) // 2 + 1, (w + 2 - 3) // 2 + 1
+        y = empty_cl(n, c, p, q, x.dtype, x.device)
+        idx = torch.empty((n, p, q, c), dtype=torch.int8, device=x.device)
+        call("iit_bn_relu_maxpool_fwd", _p(x), _p(y), _p(idx), _dt(x), n, h, w, c, _p(mean), _p(invstd), _p(gamma), _p(beta), st)
+        ctx.save_for_backward(x, idx, gamma, beta, mean, invstd)
+        ctx.training = training
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, idx, gamma, beta, mean, invstd = ctx.saved_tensors
+        dy = _cl(dy)
+        n, c, h, w = x.shape
+        red = torch.zeros((2, c), dtype=torch.float64, device=x.device)
+        dx = torch.empty_like(x)
+        if not ctx.training:
+            raise NotImplementedError("fused bn+relu+maxpool backward is for batch statistics (train mode)")
+        call("iit_bn_relu_maxpool_bwd", _p(dy), _p(idx), _p(x), _p(dx), _dt(x), n, h, w, c, _p(mean), _p(invstd), _p(gamma),
+             _p(beta), _p(red[0]), _p(red[1]), _stream())
+        return dx, red[0].float(), red[1].float(), None, None, None, None, None, None
+
+
+def bn_relu_maxpool(x, gamma, beta, running_mean, running_var, training, momentum, eps, sums=None):
+    return _BNReluPoolFn.apply(x, gamma, beta, running_mean, running_var, training, momentum, eps, sums)
+
+
 class _ReluFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x):

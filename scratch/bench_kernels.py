@@ -106,6 +106,12 @@ if which in ("all", "bn"):
     t_fb = timeit(lambda: ops.maxpool3x3s2(x).backward(dy))
     nb = x.numel() * 2
     print(f"maxpool fwd {t_f * 1e6:8.1f} us ({1.25 * nb / t_f / 1e9:6.0f} GB/s)  bwd {(t_fb - t_f) * 1e6:8.1f} us ({1.25 * nb / (t_fb - t_f) / 1e9:6.0f} GB/s)")
+    gam = torch.ones(64, device=dev, requires_grad=True)
+    bet = torch.zeros(64, device=dev, requires_grad=True)
+    rm, rv = torch.zeros(64, device=dev), torch.ones(64, device=dev)
+    t_f = timeit(lambda: ops.bn_relu_maxpool(x, gam, bet, rm, rv, True, 0.1, 1e-5))
+    t_fb = timeit(lambda: ops.bn_relu_maxpool(x, gam, bet, rm, rv, True, 0.1, 1e-5).backward(dy))
+    print(f"fused stats+bn+relu+pool fwd {t_f * 1e6:8.1f} us ({2.375 * nb / t_f / 1e9:6.0f} GB/s)  bwd {(t_fb - t_f) * 1e6:8.1f} us ({3.75 * nb / (t_fb - t_f) / 1e9:6.0f} GB/s)")
     img = torch.rand(N, 3, 56, 56, device=dev)
     t_i = timeit(lambda: ops.stem_im2col(img))
     print(f"stem im2col {t_i * 1e6:8.1f} us ({(img.numel() * 4 + N * 784 * 192 * 2) / t_i / 1e9:6.0f} GB/s)")

@@ -292,6 +292,83 @@ def test_bn_act_fwd_bwd(ops, c, hw, relu, res, training):
     assert int(bn.num_batches_tracked) == (1 if training else 0)
 
 
+@pytest.mark.parametrize("c,hw", [(64, 28), (64, 13), (128, 6)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_bn_relu_maxpool_fused_equals_unfused_chain(ops, c, hw, dtype):
+    """The fused stem tail (iit_bn_relu_maxpool_fwd/bwd) against (i) the unfused kernels bn_act(relu) -> maxpool:
+    forward values and window winners bit-identical, gradients to fp32 rounding; (ii) plain PyTorch fp32 on the CPU
+    (fp32 case: 1e-4 relative; the bf16 case is covered by (i))."""
+    g = torch.Generator().manual_seed(11)
+    n = 5
+    x = (torch.randn(n, c, hw, hw, generator=g) * 2 + 0.3)
+    gamma, beta = torch.rand(c, generator=g) + 0.5, torch.randn(c, generator=g) * 0.3
+    rm, rv = torch.zeros(c), torch.ones(c)
+
+    def run(fused):
+        xd = x.to(DEV).to(dtype).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+        gd, bd = gamma.to(DEV).requires_grad_(True), beta.to(DEV).requires_grad_(True)
+        rmd, rvd = rm.to(DEV), rv.to(DEV)
+        if fused:
+            y = ops.bn_relu_maxpool(xd, gd, bd, rmd, rvd, True, 0.1, 1e-5)
+        else:
+            y = ops.maxpool3x3s2(ops.bn_act(xd, gd, bd, None, rmd, rvd, True, 0.1, 1e-5, True))
+        gy = torch.randn(y.shape, generator=torch.Generator().manual_seed(12)).to(DEV).to(dtype)
+        y.backward(gy)
+        return y.detach(), xd.grad, gd.grad, bd.grad, rmd, rvd, gy
+
+    yf, dxf, dgf, dbf, rmf, rvf, gy = run(True)
+    yu, dxu, dgu, dbu, rmu, rvu, _ = run(False)
+    assert torch.equal(yf, yu)
+    assert torch.equal(rmf, rmu) and torch.equal(rvf, rvu)
+    if dtype == torch.float32:
+        torch.testing.assert_close(dxf, dxu, rtol=1e-4, atol=1e-5)
+        torch.testing.assert_close(dgf, dgu, rtol=1e-3, atol=1e-3)
+        torch.testing.assert_close(dbf, dbu, rtol=1e-3, atol=1e-3)
+    else:
+        # bf16: activations that tie after rounding send their gradient to the first of them in the unfused chain
+        # and to the largest pre-rounding one here (as fp32 would): a few elements differ by a whole gradient value.
+        # The unfused chain also rounds the pooled-gradient tensor to bf16 before the per-channel sums.
+        bad = ((dxf.float() - dxu.float()).abs() > 2e-2 + 2e-2 * dxu.float().abs()).float().mean().item()
+        assert bad < 0.02, bad
+        torch.testing.assert_close(dgf, dgu, rtol=5e-2, atol=1.5)
+        torch.testing.assert_close(dbf, dbu, rtol=5e-2, atol=1.5)
+    if dtype == torch.float32:
+        xr = x.clone().requires_grad_(True)
+        gr, br = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+        yr = F.max_pool2d(F.relu(F.batch_norm(xr, rm.clone(), rv.clone(), gr, br, True, 0.1, 1e-5)), 3, 2, 1)
+        yr.backward(gy.cpu().float())
+        torch.testing.assert_close(yf.cpu(), yr.detach(), rtol=1e-4, atol=2e-5)
+        torch.testing.assert_close(dxf.cpu(), xr.grad, rtol=1e-4, atol=2e-5)
+        torch.testing.assert_close(dgf.cpu(), gr.grad, rtol=1e-4, atol=1e-4)
+        torch.testing.assert_close(dbf.cpu(), br.grad, rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("c", [64, 256, 4])
+def test_bn_bf16_fast_and_generic_paths_match_fp32_reference(ops, c):
+    """bf16 BatchNorm(+residual+ReLU) forward/backward: c=64/256 take the 16-byte kernels, c=4 the generic ones;
+    both within bf16 rounding (2e-2) of PyTorch fp32 evaluated on the same bf16-rounded inputs."""
+    g = torch.Generator().manual_seed(13)
+    n, hw = 4, 6
+    x = (torch.randn(n, c, hw, hw, generator=g) * 2 + 0.5).bfloat16().float().requires_grad_(True)
+    r = torch.randn(n, c, hw, hw, generator=g).bfloat16().float().requires_grad_(True)
+    gamma = (torch.rand(c, generator=g) + 0.5).requires_grad_(True)
+    beta = torch.randn(c, generator=g).requires_grad_(True)
+    y = F.relu(F.batch_norm(x, None, None, gamma, beta, True, 0.1, 1e-5) + r)
+    gy = torch.randn(y.shape, generator=g).bfloat16().float()
+    y.backward(gy)
+    xd = x.detach().to(DEV).bfloat16().contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    rd = r.detach().to(DEV).bfloat16().contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    gd, bd = gamma.detach().to(DEV).requires_grad_(True), beta.detach().to(DEV).requires_grad_(True)
+    yd = ops.bn_act(xd, gd, bd, rd, torch.zeros(c, device=DEV), torch.ones(c, device=DEV), True, 0.1, 1e-5, True)
+    yd.backward(gy.to(DEV).bfloat16())
+    kw = dict(rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(yd.float().cpu(), y.detach(), **kw)
+    torch.testing.assert_close(xd.grad.float().cpu(), x.grad, **kw)
+    torch.testing.assert_close(rd.grad.float().cpu(), r.grad, **kw)
+    torch.testing.assert_close(gd.grad.cpu(), gamma.grad, rtol=2e-2, atol=5e-2)
+    torch.testing.assert_close(bd.grad.cpu(), beta.grad, rtol=2e-2, atol=5e-2)
+
+
 def test_pool_linear_relu(ops):
     g = torch.Generator().manual_seed(8)
     x = torch.randn(5, 64, 28, 28, generator=g).requires_grad_(True)
