@@ -160,6 +160,10 @@ class BaseModelPair(ABC):
         for dst, src in zip((*st[1], *st[2]), (*base_input, *ablation_input)):
             if dst is not src:
                 dst.copy_(src, non_blocking=True)
+        refresh = getattr(self.ll_model, "refresh_input_cache", None)
+        if refresh is not None:  # per-batch operands derived from the inputs (the stem's im2col): once per step
+            refresh(st[1][0])
+            refresh(st[2][0])
         return st[1], st[2]
 
     def _graphed_term(self, key, optimizer, build_loss):

@@ -217,6 +217,12 @@ class ResNet18LL(HookedRootModule):
         out = b.relu.hook_point(out)
         return wb.hook_point(out)
 
+    def refresh_input_cache(self, x):
+        """Rebuild the per-batch stem operand of a registered (static) input tensor after its contents changed;
+        model pairs call this before replaying captured graphs (ops.stem_cols)."""
+        if self.act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES and self.mod.conv1.mod.is_stem():
+            ops.stem_cols(x)
+
     def forward(self, x):
         m = self.mod
         stem_tc = self.act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES and m.conv1.mod.is_stem()

@@ -10,6 +10,7 @@ Layout convention for image activations: logical shape [N, C, H, W] with channel
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 from typing import Optional
 
 import torch
@@ -361,16 +362,39 @@ def conv2d(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums=None):
 STEM_K = 192
 
 
-def stem_im2col(x: torch.Tensor) -> torch.Tensor:
+def stem_im2col(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """[N,3,H,W] image (fp32 or bf16, any strides) -> bf16 [N,192,P,Q] channels-last im2col tensor of the stem."""
     _require_cuda(x)
     n, c, h, w = x.shape
     if c != 3:
         raise ValueError("stem_im2col expects 3 input channels")
     p, q = (h + 6 - 7) // 2 + 1, (w + 6 - 7) // 2 + 1
-    col = empty_cl(n, STEM_K, p, q, torch.bfloat16, x.device)
+    col = out if out is not None else empty_cl(n, STEM_K, p, q, torch.bfloat16, x.device)
     strides = (C.c_int64 * 4)(*x.stride())
     call("iit_stem_im2col", _p(x), _dt(x), strides, _p(col), n, h, w, _stream())
+    return col
+
+
+# The im2col matrix depends on the image batch only, not on the weights: the five LL forwards of one train step see two
+# distinct batches (base, source), so it is built once per batch tensor and kept while that tensor object is alive and
+# unmodified (`_version`). Under CUDA-graph capture a registered tensor is a static buffer: the captured kernels read
+# its im2col buffer, which the caller refreshes eagerly (`stem_cols`, outside capture) before replaying.
+_stem_cols: dict = {}
+
+
+def stem_cols(x: torch.Tensor) -> torch.Tensor:
+    key = id(x)
+    ent = _stem_cols.get(key)
+    if ent is not None and ent[0]() is x and ent[2].shape[0] == x.shape[0]:
+        if capturing() or ent[1] == x._version:
+            return ent[2]
+        stem_im2col(x, out=ent[2])
+        ent[1] = x._version
+        return ent[2]
+    if capturing():
+        return stem_im2col(x)
+    col = stem_im2col(x)
+    _stem_cols[key] = [weakref.ref(x, lambda _r, k=key: _stem_cols.pop(k, None)), x._version, col]
     return col
 
 
@@ -380,7 +404,7 @@ class _StemConvFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, w192, bn_sums):
         _require_cuda(x, weight)
-        col = stem_im2col(x)
+        col = stem_cols(x)
         n, _, p, q = col.shape
         k = weight.shape[0]
         d = _conv_desc(col, k, 1, 1, 1, 0)

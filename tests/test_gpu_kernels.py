@@ -506,3 +506,22 @@ def test_stem_tensor_core_path(ops, hw, layout):
         assert (a - b).abs().max().item() <= 1e-2 * scale, (what, hw, layout)
     rows = yd.numel() // 64
     torch.testing.assert_close(sums[0].cpu().float() / rows, yd.float().cpu().mean(dim=(0, 2, 3)), rtol=1e-3, atol=1e-4)
+
+
+def test_stem_cols_cache_follows_the_tensor(ops):
+    """ops.stem_cols: one im2col per batch tensor; an in-place change of the tensor (new `_version`) rebuilds it into
+    the same buffer, a different tensor object gets its own entry, dead tensors are dropped."""
+    import gc
+    x = torch.rand(3, 3, 56, 56, device=DEV)
+    c1 = ops.stem_cols(x)
+    assert ops.stem_cols(x) is c1
+    assert torch.equal(c1, ops.stem_im2col(x))
+    x.mul_(0.5)
+    c2 = ops.stem_cols(x)
+    assert c2 is c1 and torch.equal(c2, ops.stem_im2col(x))
+    y = torch.rand(3, 3, 56, 56, device=DEV)
+    assert ops.stem_cols(y) is not c1
+    n = len(ops._stem_cols)
+    del x, y
+    gc.collect()
+    assert len(ops._stem_cols) == n - 2
