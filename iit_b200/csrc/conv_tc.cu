@@ -18,9 +18,7 @@
 //   and <= 128 TMEM columns each) so one tile's epilogue overlaps another tile's main loop.
 //
 // Every mbarrier wait is bounded: a protocol bug traps (CUDA error) instead of hanging the GPU.
-#include <cuda.h>
-
-#include "common.cuh"
+#include "tc_common.cuh"
 
 namespace iit {
 
@@ -28,68 +26,6 @@ constexpr int TC_BM = 128;      // pixels per tile (UMMA M)
 constexpr int TC_BK = 64;       // bf16 elements per 128-byte swizzle row
 constexpr int TC_UK = 16;       // UMMA K for 16-bit inputs
 constexpr int TC_THREADS = 192;
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  const uint32_t addr = smem_u32(bar);
-  uint32_t done = 0;
-  for (uint32_t spins = 0; !done; ++spins) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(addr), "r"(parity)
-        : "memory");
-    if (!done && spins > (1u << 24)) __trap();  // protocol bug: fail loudly, never hang the GPU
-  }
-}
-__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3) {
-  asm volatile(
-      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
-      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
-      : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
-      : "memory");
-}
-// K-major, SWIZZLE_128B operand descriptor: 128-byte rows, 8-row (1024 B) swizzle atoms stacked along M/N
-__device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t smem_addr) {
-  return (uint64_t)((smem_addr >> 4) & 0x3FFF) | (1ull << 16) /* LBO (unused) */ | ((uint64_t)(1024 >> 4) << 32) /* SBO */ |
-         (1ull << 46) /* descriptor version: Blackwell */ | (2ull << 61) /* SWIZZLE_128B */;
-}
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
 
 struct TcParams {
   int N, P, Q;            // pixel grid enumerated by the tiles (a parity class of the output for strided dgrad)
@@ -178,6 +114,10 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
       int stage = 0;
       uint32_t phase = 0;
       uint32_t it = 0;
+      // descriptor = constant high word + low word (1 << 16) | (address >> 4): operands are stepped with 32-bit adds
+      const uint64_t proto = umma_desc_k_sw128(0);
+      const uint32_t desc_hi = (uint32_t)(proto >> 32);
+      const uint32_t a_lo0 = (uint32_t)proto + (smem_u32(sA) >> 4), b_lo0 = (uint32_t)proto + (smem_u32(sB) >> 4);
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
         const uint32_t acc = it & 1, acc_phase = (it >> 1) & 1;
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);   // the epilogue has drained this accumulator
@@ -186,12 +126,10 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
         for (int kb = 0; kb < nk; ++kb) {
           mbar_wait(&full[stage], phase);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          const uint32_t a0 = smem_u32(sA + stage * A_BYTES), b0 = smem_u32(sB + stage * B_BYTES);
+          const uint32_t a_lo = a_lo0 + stage * (A_BYTES >> 4), b_lo = b_lo0 + stage * (B_BYTES >> 4);
 #pragma unroll
-          for (int k = 0; k < TC_BK / TC_UK; ++k) {
-            umma_bf16(tmem_d, umma_desc_k_sw128(a0 + k * TC_UK * 2), umma_desc_k_sw128(b0 + k * TC_UK * 2), idesc,
-                      (uint32_t)((kb | k) != 0));
-          }
+          for (int k = 0; k < TC_BK / TC_UK; ++k)
+            umma_bf16_lohi(tmem_d, a_lo + 2 * k, desc_hi, b_lo + 2 * k, desc_hi, idesc, (uint32_t)((kb | k) != 0));
           umma_commit(&empty[stage]);  // frees this smem stage once the MMAs above have read it
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -301,22 +239,6 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
 }
 
 // ---- host side -----------------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode() {
-  static EncodeTiledFn fn = nullptr;
-  if (!fn) {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-  }
-  return fn;
-}
-
 static int pow2_ge(int v) { int r = 1; while (r < v) r <<= 1; return r; }
 
 template <int BN>
@@ -646,9 +568,21 @@ static int launch_wgrad_tc(const CUtensorMap& mdy, const CUtensorMap& mx, float*
   return 0;
 }
 
+// conv_win.cu: shifted-window kernel for 3x3 / stride-1 / 64 -> 64 convolutions on small images
+bool conv_win_3x3_supported(const iit_conv_t* d);
+int conv_win_3x3(const void* in, const void* wmat, void* out, const iit_conv_t* d, bool flip, cudaStream_t st, double* bn_sum,
+                 double* bn_sq, const char* name);
+static bool g_use_win = true;
+
 }  // namespace iit
 
 using namespace iit;
+
+extern "C" int iit_conv_win_enable(int on) {
+  const int was = g_use_win ? 1 : 0;
+  g_use_win = on != 0;
+  return was;
+}
 
 extern "C" int iit_conv2d_tc_supported(const iit_conv_t* d, int dtype) {
   if (!d || dtype != IIT_BF16) return 0;
@@ -663,6 +597,10 @@ extern "C" int iit_conv2d_fprop_tc(const void* x, const void* w_krsc, void* y, c
   IIT_REQUIRE((bn_sum == nullptr) == (bn_sqsum == nullptr), "iit_conv2d_fprop_tc: bn_sum and bn_sqsum go together");
   IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "iit_conv2d_fprop_tc: only bf16 3x3/pad-1 or 1x1/pad-0 convolutions, stride 1 "
               "or 2, with channel counts that are multiples of 64");
+  if (g_use_win && conv_win_3x3_supported(d)) {
+    if (check_tc_ptrs(x, w_krsc, y, "iit_conv2d_fprop_tc")) return 1;
+    return conv_win_3x3(x, w_krsc, y, d, false, as_stream(stream), bn_sum, bn_sqsum, "iit_conv2d_fprop_tc");
+  }
   return conv_tc_fprop(x, w_krsc, y, d, as_stream(stream), bn_sum, bn_sqsum);
 }
 
@@ -670,6 +608,10 @@ extern "C" int iit_conv2d_dgrad_tc(const void* dy, const void* w_crsk, void* dx,
   IIT_REQUIRE(dy && w_crsk && dx && d, "iit_conv2d_dgrad_tc: null pointer");
   IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "iit_conv2d_dgrad_tc: only bf16 3x3/pad-1 or 1x1/pad-0 convolutions, stride 1 "
               "or 2, with channel counts that are multiples of 64");
+  if (g_use_win && conv_win_3x3_supported(d)) {
+    if (check_tc_ptrs(dy, w_crsk, dx, "iit_conv2d_dgrad_tc")) return 1;
+    return conv_win_3x3(dy, w_crsk, dx, d, true, as_stream(stream), nullptr, nullptr, "iit_conv2d_dgrad_tc");
+  }
   return conv_tc_dgrad(dy, w_crsk, dx, d, as_stream(stream));
 }
 

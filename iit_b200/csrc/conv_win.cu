@@ -1,0 +1,380 @@
+// (b) "Shifted-window" convolutions on tcgen05: stride-1 convolutions whose input rows are short enough that a
+// whole zero-padded image (or row band) fits in shared memory as ONE TMA box, loaded ONCE.
+//
+// The box lands as a list of padded pixels, one swizzled row of RB bytes (the pixel's channels) per pixel, in
+// raster order with PW pixels per image row. Output pixel j (raster index in the same padded grid) needs, for
+// filter tap (dh, dw), input pixel j + dh*PW + dw: a constant row offset. UMMA's K-major swizzled operand may start
+// at ANY row of such a tile - the 128B/32B swizzle is a function of the absolute shared-memory address
+// (scratch/umma_shift_test*.cu measured it on B200) - so every tap's A operand is the same tile addressed
+// `doff[tap]` rows further on: no im2col, no per-tap reload. The implicit GEMM
+//     D[128 padded positions, 64 filters] += A_tile[rows j0+128t+doff[tap] ...][RB/2] * W_tap[64][RB/2]^T
+// computes the halo columns too (they are discarded in the epilogue): 196/256 of the MMA work is useful for a
+// 14x14 image, in exchange for 7x less L2->SMEM traffic than nine shifted loads (the previous bound of these layers).
+//
+// Used for: the four 3x3 / 64->64 convolutions of layer1 and their dgrads (RB = 128), and the 7x7/2 stem as a
+// 4x4 stride-1 convolution over the 2x2 space-to-depth image (12 -> 16 channels, RB = 32).
+//
+// Persistent CTAs; all filter taps resident in shared memory; STAGES image tiles in flight; 4 TMEM accumulators of
+// 64 columns so that the epilogue (TMEM -> bf16 NHWC + BatchNorm statistics) overlaps the next tiles' MMAs.
+#include "tc_common.cuh"
+
+namespace iit {
+
+constexpr int WIN_THREADS = 192;
+constexpr int WIN_BN = 64;        // filters per tile (all of them: these layers have 64)
+constexpr int WIN_NACC = 4;       // TMEM accumulators in the ring
+constexpr int WIN_MAX_TAPS = 16;
+
+struct WinParams {
+  int N, OH, OW;            // images, output size
+  int PW;                   // pixels per padded image row (= shared-memory rows per image row)
+  int bands, band_h;        // row bands per image, output rows per band
+  int pad_top, pad_left;    // position of output (0,0) inside the box
+  int y_step, y0, x0;       // TMA start row of band b = y0 + b*y_step; start column x0
+  int mtiles;               // 128-position M tiles per band
+  int ntaps;
+  int stage_bytes;          // shared-memory bytes reserved per tile (multiple of 1024, includes the overrun rows)
+  int tile_bytes;           // bytes TMA delivers per tile
+  int16_t doff[WIN_MAX_TAPS];  // tap -> row offset dh*PW + dw (relative to the output position)
+  int8_t wk[WIN_MAX_TAPS];     // tap -> block column of the filter matrix
+};
+
+// K-major operand descriptor for rows of RB bytes: SWIZZLE_128B (RB = 128) or SWIZZLE_32B (RB = 32)
+template <int RB>
+__device__ __forceinline__ uint64_t win_desc(uint32_t smem_addr) {
+  constexpr uint64_t swz = RB == 128 ? 2ull : 6ull;
+  return (uint64_t)((smem_addr >> 4) & 0x3FFF) | (1ull << 16) | ((uint64_t)((8 * RB) >> 4) << 32) | (1ull << 46) | (swz << 61);
+}
+
+template <int RB, int NTAPS, int STAGES>
+__global__ void __launch_bounds__(WIN_THREADS) conv_win_kernel(const __grid_constant__ CUtensorMap map_a,
+                                                               const __grid_constant__ CUtensorMap map_b,
+                                                               __nv_bfloat16* __restrict__ out, WinParams p,
+                                                               double* __restrict__ bn_sum, double* __restrict__ bn_sq) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr int BN = WIN_BN;
+  constexpr uint32_t B_TAP = BN * RB;                 // one tap's filter block
+  constexpr int KSTEPS = RB / 32;                     // UMMA K = 16 bf16 = 32 bytes
+  uint8_t* sB = smem;                                 // [ntaps][64][RB]
+  uint8_t* sA = smem + ((p.ntaps * B_TAP + 1023) & ~1023u);
+  uint64_t* full = reinterpret_cast<uint64_t*>(sA + (size_t)STAGES * p.stage_bytes);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tmem_full = empty + STAGES;               // [NACC]
+  uint64_t* tmem_empty = tmem_full + WIN_NACC;        // [NACC]
+  uint64_t* b_full = tmem_empty + WIN_NACC;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(b_full + 1);
+  float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [2][BN]
+  if (bn_sum != nullptr && threadIdx.x < BN) { s_stat[threadIdx.x] = 0.f; s_stat[threadIdx.x + BN] = 0.f; }
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_tiles = p.N * p.bands;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < WIN_NACC; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+    mbar_init(b_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(WIN_NACC * BN));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+      // all filter taps, once
+      mbar_expect_tx(b_full, p.ntaps * B_TAP);
+      for (int t = 0; t < p.ntaps; ++t) tma_load_2d(sB + t * B_TAP, &map_b, b_full, p.wk[t] * (RB / 2), 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int n = tile / p.bands, band = tile - n * p.bands;
+        mbar_wait(&empty[stage], phase ^ 1);
+        mbar_expect_tx(&full[stage], p.tile_bytes);
+        tma_load_4d(sA + (size_t)stage * p.stage_bytes, &map_a, &full[stage], 0, p.x0, p.y0 + band * p.y_step, n);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+      mbar_wait(b_full, 0);
+      int stage = 0;
+      uint32_t phase = 0, it = 0;
+      const int j0 = p.pad_top * p.PW + p.pad_left;
+      // descriptor words: high word constant, low word = (1 << 16) | (address >> 4); per-tap steps in registers
+      const uint64_t proto = win_desc<RB>(0);
+      const uint32_t hi = (uint32_t)(proto >> 32), lo_flags = (uint32_t)proto;
+      const uint32_t b_lo = lo_flags + (smem_u32(sB) >> 4);
+      uint32_t a_step[NTAPS];
+#pragma unroll
+      for (int tap = 0; tap < NTAPS; ++tap) a_step[tap] = (uint32_t)((j0 + p.doff[tap]) * (RB / 16));
+      const uint32_t a_lo0 = lo_flags + (smem_u32(sA) >> 4), stage_step = (uint32_t)p.stage_bytes >> 4;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        mbar_wait(&full[stage], phase);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t a_tile = a_lo0 + stage * stage_step;
+        for (int t = 0; t < p.mtiles; ++t, ++it) {
+          const uint32_t acc = it % WIN_NACC, acc_phase = (it / WIN_NACC) & 1;
+          mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t tmem_d = tmem_base + acc * BN;
+          const uint32_t a_m = a_tile + t * (128 * RB / 16);
+#pragma unroll
+          for (int tap = 0; tap < NTAPS; ++tap) {
+#pragma unroll
+            for (int k = 0; k < KSTEPS; ++k)
+              umma_bf16_lohi(tmem_d, a_m + a_step[tap] + 2 * k, hi, b_lo + tap * (B_TAP / 16) + 2 * k, hi, idesc,
+                             (uint32_t)((tap | k) != 0));
+          }
+          umma_commit(&tmem_full[acc]);
+        }
+        umma_commit(&empty[stage]);   // the tile may be overwritten once every MMA above has read it
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int m = quarter * 32 + lane;
+    const int e = threadIdx.x - 64;
+    float st_s[BN], st_q[BN];
+#pragma unroll
+    for (int j = 0; j < BN; ++j) { st_s[j] = 0.f; st_q[j] = 0.f; }
+    uint32_t it = 0;
+    const int j0 = p.pad_top * p.PW + p.pad_left;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int n = tile / p.bands, band = tile - n * p.bands;
+      for (int t = 0; t < p.mtiles; ++t, ++it) {
+        const int jj = j0 + 128 * t + m;
+        const int hh = jj / p.PW - p.pad_top, ww = jj % p.PW - p.pad_left;
+        const int oh = band * p.band_h + hh;
+        const bool ok = ww >= 0 && ww < p.OW && hh >= 0 && hh < p.band_h && oh < p.OH;
+        __nv_bfloat16* dst = out + (((int64_t)n * p.OH + oh) * p.OW + ww) * BN;
+        const uint32_t acc = it % WIN_NACC, acc_phase = (it / WIN_NACC) & 1;
+        mbar_wait(&tmem_full[acc], acc_phase);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+        for (int c = 0; c < BN; c += 32) {
+          uint32_t v[32];
+          tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c), v);
+          if (c + 32 >= BN) {
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[acc])) : "memory");
+          }
+          // bf16 pairs as stored; the BatchNorm statistics are taken from these rounded values. Each lane keeps
+          // running sums for its own accumulator row across all the tiles of this CTA (2 x 64 fp32 registers); the
+          // cross-lane reduction happens once, after the tile loop.
+          uint32_t pk[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+            pk[j] = *reinterpret_cast<uint32_t*>(&h);
+          }
+          if (ok) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 4)
+              *reinterpret_cast<uint4*>(dst + c + 2 * j) = make_uint4(pk[j], pk[j + 1], pk[j + 2], pk[j + 3]);
+            if (bn_sum != nullptr) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const float f0 = __uint_as_float(pk[j] << 16), f1 = __uint_as_float(pk[j] & 0xffff0000u);
+                if (c == 0) {
+                  st_s[2 * j] += f0; st_q[2 * j] = fmaf(f0, f0, st_q[2 * j]);
+                  st_s[2 * j + 1] += f1; st_q[2 * j + 1] = fmaf(f1, f1, st_q[2 * j + 1]);
+                } else {
+                  st_s[32 + 2 * j] += f0; st_q[32 + 2 * j] = fmaf(f0, f0, st_q[32 + 2 * j]);
+                  st_s[32 + 2 * j + 1] += f1; st_q[32 + 2 * j + 1] = fmaf(f1, f1, st_q[32 + 2 * j + 1]);
+                }
+              }
+            }
+          }
+        }
+      }
+    }
+    if (bn_sum != nullptr) {
+      // once per CTA: butterfly over the 32 lanes (lane l ends with the warp total of channel c+l), shared-memory
+      // atomics over the four warps, one fp64 atomic per channel
+#pragma unroll
+      for (int c = 0; c < BN; c += 32) {
+        float a[32], b[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) { a[j] = st_s[c + j]; b[j] = st_q[c + j]; }
+#pragma unroll
+        for (int h = 16; h >= 1; h >>= 1) {
+          const bool up = (lane & h) != 0;
+#pragma unroll
+          for (int i = 0; i < h; ++i) {
+            float sa = up ? a[i] : a[i + h], ka = up ? a[i + h] : a[i];
+            float sb = up ? b[i] : b[i + h], kb = up ? b[i + h] : b[i];
+            a[i] = ka + __shfl_xor_sync(0xffffffffu, sa, h);
+            b[i] = kb + __shfl_xor_sync(0xffffffffu, sb, h);
+          }
+        }
+        atomicAdd(&s_stat[c + lane], a[0]);
+        atomicAdd(&s_stat[BN + c + lane], b[0]);
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (e < BN) { atomicAdd(&bn_sum[e], (double)s_stat[e]); atomicAdd(&bn_sq[e], (double)s_stat[BN + e]); }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(WIN_NACC * BN));
+  }
+}
+
+// ---- host side -----------------------------------------------------------------------------------
+constexpr size_t WIN_SMEM_MAX = 227 * 1024;
+
+static size_t win_smem_bytes(const WinParams& p, int RB, int stages) {
+  const size_t b = ((size_t)p.ntaps * WIN_BN * RB + 1023) & ~(size_t)1023;
+  return b + (size_t)stages * p.stage_bytes + (2 * stages + 2 * WIN_NACC + 1) * 8 + 16 + 2 * WIN_BN * 4 + 1024;
+}
+
+// Fills the geometry for an image of IH x IW input pixels whose TMA box is (PW x box_h) pixels per band.
+static bool win_plan(WinParams* p, int RB, int OH, int OW, int PW, int halo_h, int pad_top, int pad_left, int max_doff,
+                     int min_doff) {
+  // band height: the whole image when its box fits 256 rows of TMA box height and the shared-memory budget
+  for (int band_h = OH; band_h >= 1; --band_h) {
+    const int box_h = band_h + halo_h;
+    if (box_h > 256 || PW > 256) continue;
+    const int j0 = pad_top * PW + pad_left;
+    const int span = (band_h - 1) * PW + OW;                  // padded positions from the first to the last output
+    const int mtiles = (span + 127) / 128;
+    if (j0 + min_doff < 0) return false;
+    const int rows_touched = j0 + 128 * mtiles + max_doff;    // highest row an MMA reads, + 1
+    const int rows = rows_touched > box_h * PW ? rows_touched : box_h * PW;
+    const int stage_bytes = (rows * RB + 1023) & ~1023;
+    p->OH = OH; p->OW = OW; p->PW = PW; p->band_h = band_h; p->bands = (OH + band_h - 1) / band_h;
+    p->pad_top = pad_top; p->pad_left = pad_left; p->mtiles = mtiles; p->stage_bytes = stage_bytes;
+    p->tile_bytes = box_h * PW * RB;
+    if (win_smem_bytes(*p, RB, 2) <= WIN_SMEM_MAX) return true;
+  }
+  return false;
+}
+
+static int win_encode_a(CUtensorMap* m, const void* ptr, int C, int W, int H, int N, int box_w, int box_h, int RB, const char* name) {
+  EncodeTiledFn enc = get_encode();
+  IIT_REQUIRE(enc != nullptr, "%s: cuTensorMapEncodeTiled is unavailable in this driver", name);
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint32_t box[4] = {(cuuint32_t)(RB / 2), (cuuint32_t)box_w, (cuuint32_t)box_h, 1};
+  cuuint32_t es[4] = {1, 1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, RB == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_32B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  IIT_REQUIRE(r == CUDA_SUCCESS, "%s: tensor map rejected (CUresult %d)", name, (int)r);
+  return 0;
+}
+
+static int win_encode_b(CUtensorMap* m, const void* wmat, int Kg, int RB, const char* name) {
+  EncodeTiledFn enc = get_encode();
+  IIT_REQUIRE(enc != nullptr, "%s: cuTensorMapEncodeTiled is unavailable in this driver", name);
+  cuuint64_t dims[2] = {(cuuint64_t)Kg, (cuuint64_t)WIN_BN};
+  cuuint64_t strides[1] = {(cuuint64_t)Kg * 2};
+  cuuint32_t box[2] = {(cuuint32_t)(RB / 2), (cuuint32_t)WIN_BN};
+  cuuint32_t es[2] = {1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(wmat), dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, RB == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_32B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  IIT_REQUIRE(r == CUDA_SUCCESS, "%s: filter tensor map rejected (CUresult %d)", name, (int)r);
+  return 0;
+}
+
+template <int RB, int NTAPS>
+static int win_launch(const CUtensorMap& ma, const CUtensorMap& mb, void* out, const WinParams& p, cudaStream_t st,
+                      double* bn_sum, double* bn_sq, const char* name) {
+  // as many tiles in flight as the shared-memory budget allows, at most 4
+  int stages = 4;
+  while (stages > 2 && win_smem_bytes(p, RB, stages) > WIN_SMEM_MAX) --stages;
+  const size_t smem = win_smem_bytes(p, RB, stages);
+  IIT_REQUIRE(smem <= WIN_SMEM_MAX, "%s: tile does not fit shared memory", name);
+  int grid = kNumSMs;
+  if (grid > p.N * p.bands) grid = p.N * p.bands;
+  static bool attr_set[5] = {false, false, false, false, false};
+#define IIT_WIN_LAUNCH(S)                                                                                              \
+  case S:                                                                                                              \
+    if (!attr_set[S]) {                                                                                                \
+      IIT_CUDA(cudaFuncSetAttribute(conv_win_kernel<RB, NTAPS, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WIN_SMEM_MAX)); \
+      attr_set[S] = true;                                                                                              \
+    }                                                                                                                  \
+    conv_win_kernel<RB, NTAPS, S><<<grid, WIN_THREADS, smem, st>>>(ma, mb, (__nv_bfloat16*)out, p, bn_sum, bn_sq);            \
+    break;
+  switch (stages) {
+    IIT_WIN_LAUNCH(2)
+    IIT_WIN_LAUNCH(3)
+    IIT_WIN_LAUNCH(4)
+  }
+#undef IIT_WIN_LAUNCH
+  IIT_LAUNCH_CHECK(name);
+  return 0;
+}
+
+// 3x3 / stride 1 / pad 1, 64 -> 64 channels. `flip` selects the dgrad tap table (taps mirrored, filter given as CRSK).
+bool conv_win_3x3_supported(const iit_conv_t* d) {
+  if (!(d->r == 3 && d->s == 3 && d->pad == 1 && d->stride == 1 && d->c == 64 && d->k == 64)) return false;
+  WinParams p{};
+  p.ntaps = 9;
+  return win_plan(&p, 128, d->p, d->q, d->w + 2, 2, 1, 1, d->w + 3, -(d->w + 3));
+}
+
+int conv_win_3x3(const void* in, const void* wmat, void* out, const iit_conv_t* d, bool flip, cudaStream_t st, double* bn_sum,
+                 double* bn_sq, const char* name) {
+  WinParams p{};
+  p.N = d->n; p.ntaps = 9;
+  const int PW = d->w + 2;
+  IIT_REQUIRE(win_plan(&p, 128, d->p, d->q, PW, 2, 1, 1, PW + 1, -(PW + 1)), "%s: image does not fit the shifted-window kernel", name);
+  p.x0 = -1; p.y0 = -1; p.y_step = p.band_h;
+  for (int r = 0; r < 3; ++r)
+    for (int s = 0; s < 3; ++s) {
+      const int t = r * 3 + s;
+      // fprop reads x[h + r - 1, w + s - 1]; dgrad reads dy[h + 1 - r, w + 1 - s]
+      const int dh = flip ? 1 - r : r - 1, dw = flip ? 1 - s : s - 1;
+      p.doff[t] = (int16_t)(dh * PW + dw);
+      p.wk[t] = (int8_t)t;
+    }
+  CUtensorMap ma, mb;
+  if (win_encode_a(&ma, in, 64, d->w, d->h, d->n, PW, p.band_h + 2, 128, name)) return 1;
+  if (win_encode_b(&mb, wmat, 9 * 64, 128, name)) return 1;
+  return win_launch<128, 9>(ma, mb, out, p, st, bn_sum, bn_sq, name);
+}
+
+}  // namespace iit
+
+using namespace iit;
+
+// Stem: y[n,p,q,k] = sum_{R,S<4} sum_{c<16} s2d[n, p+R, q+S, c] * w2[k, R, S, c], where s2d is the zero-padded image
+// after a 2x2 space-to-depth ([N, (H+6)/2, (W+6)/2, 16] bf16, 12 real channels) and w2 the 7x7 filter regrouped
+// accordingly ([64, 4, 4, 16] bf16): exactly the 7x7 / stride-2 / pad-3 convolution.
+extern "C" int iit_stem_conv_s2d(const void* s2d, const void* w2, void* y, int n, int sh, int sw, double* bn_sum, double* bn_sqsum,
+                                 void* stream) {
+  const char* name = "iit_stem_conv_s2d";
+  IIT_REQUIRE(s2d && w2 && y && n >= 1 && sh >= 4 && sw >= 4, "%s: bad arguments", name);
+  IIT_REQUIRE((bn_sum == nullptr) == (bn_sqsum == nullptr), "%s: bn_sum and bn_sqsum go together", name);
+  IIT_REQUIRE(((reinterpret_cast<uintptr_t>(s2d) | reinterpret_cast<uintptr_t>(w2) | reinterpret_cast<uintptr_t>(y)) & 15) == 0,
+              "%s: pointers must be 16-byte aligned", name);
+  WinParams p{};
+  p.N = n; p.ntaps = 16;
+  const int OH = sh - 3, OW = sw - 3, PW = sw;
+  IIT_REQUIRE(win_plan(&p, 32, OH, OW, PW, 3, 0, 0, 3 * PW + 3, 0), "%s: image %dx%d does not fit the shifted-window kernel", name, sh, sw);
+  p.x0 = 0; p.y0 = 0; p.y_step = p.band_h;
+  for (int R = 0; R < 4; ++R)
+    for (int S = 0; S < 4; ++S) {
+      p.doff[R * 4 + S] = (int16_t)(R * PW + S);
+      p.wk[R * 4 + S] = (int8_t)(R * 4 + S);
+    }
+  CUtensorMap ma, mb;
+  if (win_encode_a(&ma, s2d, 16, sw, sh, n, PW, p.band_h + 3, 32, name)) return 1;
+  if (win_encode_b(&mb, w2, 16 * 16, 32, name)) return 1;
+  return win_launch<32, 16>(ma, mb, y, p, as_stream(stream), bn_sum, bn_sqsum, name);
+}

@@ -167,6 +167,22 @@ int iit_conv2d_tc_supported(const iit_conv_t* d, int dtype);
 int iit_conv2d_fprop_tc(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, double* bn_sum,
                         double* bn_sqsum, void* stream);
 int iit_conv2d_dgrad_tc(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream);
+/* 3x3 / stride-1 / pad-1 convolutions with 64 -> 64 channels on images whose padded form fits shared memory
+ * (layer1 of the ResNet) run on a "shifted-window" kernel inside the two entry points above: the padded image
+ * is loaded once and every filter tap addresses it at a row offset. Same results bit for bit; this switch
+ * (returns the previous setting) exists so that tests and profiles can compare the two kernels. */
+int iit_conv_win_enable(int on);
+/* The 7x7 / stride-2 / pad-3 stem on 3 input channels (torchvision resnet18.conv1 under
+ * iit/utils/wrapper.py:33-66) as a 4x4 stride-1 convolution over the 2x2 space-to-depth image:
+ *   iit_stem_s2d:      x [n,3,h,w] (fp32 or bf16, any strides; h, w even) -> s2d [n,(h+6)/2,(w+6)/2,16] bf16,
+ *                      channel (a*2+b)*3+c of s2d[y,x] = padded image [c, 2y+a, 2x+b]; channels 12..15 zero;
+ *   iit_stem_filter_s2d: w [64,3,7,7] fp32 (any strides) -> w2 [64,4,4,16] bf16 regrouped the same way;
+ *   iit_stem_conv_s2d: y [n,h/2,w/2,64] bf16 = conv(s2d, w2) on the shifted-window tcgen05 kernel, optionally
+ *                      adding the per-channel sum / sum of squares of y into bn_sum / bn_sqsum (fp64). */
+int iit_stem_s2d(const void* x, int dtype, const int64_t* strides_nchw, void* s2d, int n, int h, int w, void* stream);
+int iit_stem_filter_s2d(const float* w, const int64_t* strides_kcrs, void* w2, void* stream);
+int iit_stem_conv_s2d(const void* s2d, const void* w2, void* y, int n, int sh, int sw, double* bn_sum,
+                      double* bn_sqsum, void* stream);
 /* dw[k,r,s,c] fp32: pixels are the GEMM K dimension (MN-major operands straight from NHWC), split across
  * CTAs; scratch holds the per-split partial sums (iit_conv2d_wgrad_tc_scratch_bytes), reduced in fixed order. */
 size_t iit_conv2d_wgrad_tc_scratch_bytes(const iit_conv_t* d);

@@ -77,6 +77,21 @@ if which in ("all", "conv"):
         print(f"{name:10s} {fl / 1e9:7.1f} | {tf * 1e6:9.1f} {fl / tf / 1e12:6.0f} | {tdg * 1e6:9.1f} {fl / tdg / 1e12:6.0f} | "
               f"{tw * 1e6:9.1f} {fl / tw / 1e12:6.0f} | {hbm * 1e6:7.1f}")
 
+if which in ("all", "conv", "stem"):
+    img = torch.rand(N, 3, 56, 56, device=dev)
+    s2d = torch.empty(N, 31, 31, 16, dtype=torch.bfloat16, device=dev)
+    w7 = torch.randn(64, 3, 7, 7, device=dev) * 0.1
+    w2 = torch.empty(64, 4, 4, 16, dtype=torch.bfloat16, device=dev)
+    y = torch.empty(N, 28, 28, 64, dtype=torch.bfloat16, device=dev)
+    sums = torch.zeros(2, 64, dtype=torch.float64, device=dev)
+    _lib.call("iit_stem_filter_s2d", p(w7), (C.c_int64 * 4)(*w7.stride()), p(w2), st())
+    t1 = timeit(lambda: _lib.call("iit_stem_s2d", p(img), _lib.IIT_F32, (C.c_int64 * 4)(*img.stride()), p(s2d), N, 56, 56, st()))
+    t2 = timeit(lambda: _lib.call("iit_stem_conv_s2d", p(s2d), p(w2), p(y), N, 31, 31, p(sums[0]), p(sums[1]), st()))
+    fl = 2.0 * N * 784 * 64 * 147
+    print(f"stem s2d transform {t1 * 1e6:8.1f} us ({(img.numel() * 4 + s2d.numel() * 2) / t1 / 1e9:6.0f} GB/s)   "
+          f"stem conv (shifted window) {t2 * 1e6:8.1f} us  {fl / t2 / 1e12:5.0f} TF/s (147-tap FLOPs)  "
+          f"{(s2d.numel() * 2 + y.numel() * 2) / t2 / 1e9:6.0f} GB/s")
+
 if which in ("all", "bn"):
     print("\nBN / pool kernels (bf16): us and GB/s of algorithmic bytes")
     for name, c, hw in [("stem", 64, 28), ("l1", 64, 14), ("l2", 128, 7), ("l3", 256, 4), ("l4", 512, 2)]:

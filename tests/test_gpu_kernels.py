@@ -525,3 +525,83 @@ def test_stem_cols_cache_follows_the_tensor(ops):
     del x, y
     gc.collect()
     assert len(ops._stem_cols) == n - 2
+
+
+def _conv_desc(n, h, w, c, k, r, stride, pad):
+    from iit_b200._lib import Conv
+    d = Conv()
+    d.n, d.h, d.w, d.c, d.k, d.r, d.s, d.stride, d.pad = n, h, w, c, k, r, r, stride, pad
+    d.p = (h + 2 * pad - r) // stride + 1
+    d.q = (w + 2 * pad - r) // stride + 1
+    return d
+
+
+@pytest.mark.parametrize("n,h,w", [(5, 14, 14), (3, 21, 21), (2, 9, 13), (150, 14, 14), (1, 40, 40)])
+def test_shifted_window_conv_is_bit_identical_to_the_tiled_kernel(ops, n, h, w):
+    """layer1's 3x3 64->64 convolutions: the shifted-window tcgen05 kernel (padded image loaded once, taps as row
+    offsets; bands when the image is tall) accumulates the same products in the same order as the tiled kernel, so
+    fprop, its BatchNorm sums and dgrad must agree bit for bit; both are also checked against PyTorch fp32."""
+    import ctypes as C
+    from iit_b200 import _lib
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(n, h, w, 64, generator=g).bfloat16().to(DEV)
+    wt = (torch.randn(64, 3, 3, 64, generator=g) * 0.05).bfloat16().to(DEV)       # KRSC
+    wt_crsk = wt.permute(3, 1, 2, 0).contiguous()
+    d = _conv_desc(n, h, w, 64, 64, 3, 1, 1)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    res = {}
+    for on in (1, 0):
+        was = _lib.lib.iit_conv_win_enable(on)
+        try:
+            y = torch.full((n, h, w, 64), 7.0, dtype=torch.bfloat16, device=DEV)
+            dx = torch.full((n, h, w, 64), 7.0, dtype=torch.bfloat16, device=DEV)
+            sums = torch.zeros(2, 64, dtype=torch.float64, device=DEV)
+            _lib.call("iit_conv2d_fprop_tc", p(x), p(wt), p(y), C.byref(d), p(sums[0]), p(sums[1]), st)
+            _lib.call("iit_conv2d_dgrad_tc", p(y), p(wt_crsk), p(dx), C.byref(d), st)
+            res[on] = (y, dx, sums)
+        finally:
+            _lib.lib.iit_conv_win_enable(was)
+    assert torch.equal(res[1][0], res[0][0])
+    assert torch.equal(res[1][1], res[0][1])
+    torch.testing.assert_close(res[1][2], res[0][2], rtol=1e-6, atol=1e-6)   # fp32 partial sums in a different grouping
+    ref = F.conv2d(x.float().cpu().permute(0, 3, 1, 2), wt.float().cpu().permute(0, 3, 1, 2), padding=1).permute(0, 2, 3, 1)
+    torch.testing.assert_close(res[1][0].float().cpu(), ref, rtol=2e-2, atol=2e-2)
+    yb = res[1][0].double()
+    torch.testing.assert_close(res[1][2][0].cpu(), yb.sum((0, 1, 2)).cpu(), rtol=1e-5, atol=1e-3)
+    torch.testing.assert_close(res[1][2][1].cpu(), (yb * yb).sum((0, 1, 2)).cpu(), rtol=1e-5, atol=1e-3)
+
+
+@pytest.mark.parametrize("n,hw", [(4, 56), (3, 84), (149, 56), (2, 30)])
+def test_stem_space_to_depth_conv_matches_conv2d(ops, n, hw):
+    """7x7/2 stem as space-to-depth + 4x4 shifted-window convolution (iit_stem_s2d / iit_stem_filter_s2d /
+    iit_stem_conv_s2d) against F.conv2d in fp32 on the bf16-rounded image and filter: products are exact in fp32, so
+    the only differences are accumulation order and the bf16 rounding of the result (2^-8 relative)."""
+    import ctypes as C
+    from iit_b200 import _lib
+    g = torch.Generator().manual_seed(5)
+    x = torch.rand(n, 3, hw, hw, generator=g)
+    w = torch.randn(64, 3, 7, 7, generator=g) * 0.1
+    xd, wd = x.to(DEV), w.to(DEV)
+    sh = (hw + 6) // 2
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    s2d = torch.empty(n, sh, sh, 16, dtype=torch.bfloat16, device=DEV)
+    w2 = torch.empty(64, 4, 4, 16, dtype=torch.bfloat16, device=DEV)
+    _lib.call("iit_stem_s2d", p(xd), _lib.IIT_F32, (C.c_int64 * 4)(*xd.stride()), p(s2d), n, hw, hw, st)
+    _lib.call("iit_stem_filter_s2d", p(wd), (C.c_int64 * 4)(*wd.stride()), p(w2), st)
+    # the two re-layouts are pure data movement + rounding: exact
+    xp = F.pad(x, (3, 3, 3, 3)).bfloat16()
+    want = torch.zeros(n, sh, sh, 16, dtype=torch.bfloat16)
+    for a in range(2):
+        for b in range(2):
+            want[..., (a * 2 + b) * 3:(a * 2 + b) * 3 + 3] = xp[:, :, a::2, b::2].permute(0, 2, 3, 1)
+    assert torch.equal(s2d.cpu(), want)
+    y = torch.full((n, hw // 2, hw // 2, 64), 7.0, dtype=torch.bfloat16, device=DEV)
+    sums = torch.zeros(2, 64, dtype=torch.float64, device=DEV)
+    _lib.call("iit_stem_conv_s2d", p(s2d), p(w2), p(y), n, sh, sh, p(sums[0]), p(sums[1]), st)
+    ref = F.conv2d(x.bfloat16().float(), w.bfloat16().float(), stride=2, padding=3).permute(0, 2, 3, 1)
+    torch.testing.assert_close(y.float().cpu(), ref, rtol=1e-2, atol=1e-2)
+    yb = y.double()
+    torch.testing.assert_close(sums[0].cpu(), yb.sum((0, 1, 2)).cpu(), rtol=1e-5, atol=1e-3)
+    torch.testing.assert_close(sums[1].cpu(), (yb * yb).sum((0, 1, 2)).cpu(), rtol=1e-5, atol=1e-3)
