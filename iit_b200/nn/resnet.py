@@ -58,21 +58,26 @@ class Conv2d(nn.Module):
     def is_stem(self):
         return tuple(self.weight.shape[1:]) == (3, 7, 7) and self.stride == 2 and self.pad == 3
 
-    def stem_filter(self):
-        """[K,192] bf16: the KRSC filter rows (147 values) zero-padded to three 128-byte rows; cached per version."""
+    def stem_filter(self, s2d: bool):
+        """The stem filter as the kernels want it, cached per weight version: [64,4,4,16] bf16 in the space-to-depth
+        grouping (`s2d`), or [K,192] bf16 = the KRSC rows (147 values) zero-padded to three 128-byte rows."""
         w = self.weight
-        key = (w._version, w.data_ptr())
+        key = (w._version, w.data_ptr(), s2d)
         ent = self._prep.get("stem")
         if ent is None or ent[0] != key or ops.capturing():
-            w192 = torch.zeros((w.shape[0], ops.STEM_K), dtype=torch.bfloat16, device=w.device)
-            w192[:, :147] = w.detach().permute(0, 2, 3, 1).reshape(w.shape[0], 147)
-            ent = (key, w192)
+            if s2d:
+                wp = ops.stem_filter_s2d(w.detach())
+            else:
+                wp = torch.zeros((w.shape[0], ops.STEM_K), dtype=torch.bfloat16, device=w.device)
+                wp[:, :147] = w.detach().permute(0, 2, 3, 1).reshape(w.shape[0], 147)
+            ent = (key, wp)
             self._prep["stem"] = ent
         return ent[1]
 
     def forward(self, x, bn_sums=None, act_dtype=None):
         if act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES and self.is_stem():
-            return ops.stem_conv(x, self.weight, self.stem_filter(), bn_sums)
+            s2d = self.weight.shape[0] == 64 and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0
+            return ops.stem_conv(x, self.weight, self.stem_filter(s2d), bn_sums)
         krsc, crsk = self.prepared(x.dtype)
         return ops.conv2d(x, self.weight, krsc, crsk, self.stride, self.pad, bn_sums)
 
@@ -220,8 +225,7 @@ class ResNet18LL(HookedRootModule):
     def refresh_input_cache(self, x):
         """Rebuild the per-batch stem operand of a registered (static) input tensor after its contents changed;
         model pairs call this before replaying captured graphs (ops.stem_cols)."""
-        if self.act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES and self.mod.conv1.mod.is_stem():
-            ops.stem_cols(x)
+        ops.refresh_batch_operands(x)
 
     def forward(self, x):
         m = self.mod

@@ -375,54 +375,104 @@ def stem_im2col(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Te
     return col
 
 
-# The im2col matrix depends on the image batch only, not on the weights: the five LL forwards of one train step see two
-# distinct batches (base, source), so it is built once per batch tensor and kept while that tensor object is alive and
-# unmodified (`_version`). Under CUDA-graph capture a registered tensor is a static buffer: the captured kernels read
-# its im2col buffer, which the caller refreshes eagerly (`stem_cols`, outside capture) before replaying.
-_stem_cols: dict = {}
+# Operands derived from the image batch alone (not from the weights) -- the stem's space-to-depth image for the forward,
+# its im2col matrix for the weight gradient -- are built once per batch tensor and kept while that tensor object is alive
+# and unmodified (`_version`): the five LL forwards of one train step see only two distinct batches (base, source).
+# Under CUDA-graph capture a registered tensor is a static buffer: the captured kernels read the derived buffer, which
+# the caller refreshes eagerly (`refresh_batch_operands`, outside capture) before replaying.
+_batch_cache: dict = {}
 
 
-def stem_cols(x: torch.Tensor) -> torch.Tensor:
-    key = id(x)
-    ent = _stem_cols.get(key)
+def _batch_cached(x: torch.Tensor, kind: str, build):
+    key = (id(x), kind)
+    ent = _batch_cache.get(key)
     if ent is not None and ent[0]() is x and ent[2].shape[0] == x.shape[0]:
         if capturing() or ent[1] == x._version:
             return ent[2]
-        stem_im2col(x, out=ent[2])
+        build(x, ent[2])
         ent[1] = x._version
         return ent[2]
     if capturing():
-        return stem_im2col(x)
-    col = stem_im2col(x)
-    _stem_cols[key] = [weakref.ref(x, lambda _r, k=key: _stem_cols.pop(k, None)), x._version, col]
-    return col
+        return build(x, None)
+    buf = build(x, None)
+    _batch_cache[key] = [weakref.ref(x, lambda _r, k=key: _batch_cache.pop(k, None)), x._version, buf]
+    return buf
+
+
+def refresh_batch_operands(x: torch.Tensor):
+    """Rebuild every operand already derived from `x` (after its contents changed in place)."""
+    for kind, build in (("s2d", stem_s2d), ("col", stem_im2col)):
+        if (id(x), kind) in _batch_cache:
+            _batch_cached(x, kind, build)
+
+
+def stem_s2d(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """[N,3,H,W] image (fp32 or bf16, any strides; H, W even) -> bf16 [N,(H+6)/2,(W+6)/2,16]: zero-padded by 3 and 2x2
+    space-to-depth, channel (a*2+b)*3+c <- padded[c, 2y+a, 2x+b]."""
+    _require_cuda(x)
+    n, c, h, w = x.shape
+    if c != 3 or h % 2 or w % 2:
+        raise ValueError("stem_s2d expects 3 input channels and even height / width")
+    buf = out if out is not None else torch.empty((n, (h + 6) // 2, (w + 6) // 2, 16), dtype=torch.bfloat16, device=x.device)
+    strides = (C.c_int64 * 4)(*x.stride())
+    call("iit_stem_s2d", _p(x), _dt(x), strides, _p(buf), n, h, w, _stream())
+    return buf
+
+
+def stem_filter_s2d(weight: torch.Tensor) -> torch.Tensor:
+    """fp32 [64,3,7,7] filter (any strides) -> bf16 [64,4,4,16] in the space-to-depth grouping."""
+    _require_cuda(weight)
+    if tuple(weight.shape) != (64, 3, 7, 7) or weight.dtype != torch.float32:
+        raise ValueError("stem_filter_s2d expects the fp32 [64,3,7,7] stem filter")
+    w2 = torch.empty((64, 4, 4, 16), dtype=torch.bfloat16, device=weight.device)
+    strides = (C.c_int64 * 4)(*weight.stride())
+    call("iit_stem_filter_s2d", _p(weight), strides, _p(w2), _stream())
+    return w2
+
+
+def stem_cols(x: torch.Tensor) -> torch.Tensor:
+    return _batch_cached(x, "col", stem_im2col)
+
+
+def stem_s2d_cached(x: torch.Tensor) -> torch.Tensor:
+    return _batch_cached(x, "s2d", stem_s2d)
 
 
 class _StemConvFn(torch.autograd.Function):
-    """7x7/2 stem on the tensor cores: im2col (HBM-bound) + a 1x1 convolution with 192 input channels."""
+    """7x7/2 stem on the tensor cores. Forward: the 4x4 stride-1 convolution over the space-to-depth image on the
+    shifted-window kernel (even image sizes with 64 filters), else im2col + a 1x1 convolution with 192 channels.
+    Weight gradient: im2col (built once per batch) + the 1x1 wgrad kernel."""
 
     @staticmethod
-    def forward(ctx, x, weight, w192, bn_sums):
+    def forward(ctx, x, weight, w_prepared, bn_sums):
         _require_cuda(x, weight)
-        col = stem_cols(x)
-        n, _, p, q = col.shape
+        n, _, h, w = x.shape
         k = weight.shape[0]
-        d = _conv_desc(col, k, 1, 1, 1, 0)
-        y = empty_cl(n, k, p, q, torch.bfloat16, x.device)
         s0 = s1 = None
         if bn_sums is not None:
             s0, s1 = bn_sums[0], bn_sums[1]
-        call("iit_conv2d_fprop_tc", _p(col), _p(w192), _p(y), C.byref(d), _p(s0), _p(s1), _stream())
-        ctx.save_for_backward(col, weight)   # kept for the weight gradient (1.2 GB at batch 4096, bf16)
-        ctx.d = d
+        if w_prepared.dim() == 4:     # [64,4,4,16]: space-to-depth form
+            s2d = stem_s2d_cached(x)
+            y = empty_cl(n, k, h // 2, w // 2, torch.bfloat16, x.device)
+            call("iit_stem_conv_s2d", _p(s2d), _p(w_prepared), _p(y), n, s2d.shape[1], s2d.shape[2], _p(s0), _p(s1), _stream())
+        else:                          # [K,192]: im2col form
+            col = stem_cols(x)
+            _, _, p, q = col.shape
+            d = _conv_desc(col, k, 1, 1, 1, 0)
+            y = empty_cl(n, k, p, q, torch.bfloat16, x.device)
+            call("iit_conv2d_fprop_tc", _p(col), _p(w_prepared), _p(y), C.byref(d), _p(s0), _p(s1), _stream())
+        ctx.x = x                      # not a saved tensor: the batch is an input, never produced by autograd
+        ctx.save_for_backward(weight)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        col, weight = ctx.saved_tensors
-        d = ctx.d
+        (weight,) = ctx.saved_tensors
         dw = None
         if ctx.needs_input_grad[1]:
+            col = stem_cols(ctx.x)     # 1.2 GB at batch 4096 (bf16), shared by every backward of this batch
+            k = weight.shape[0]
+            d = _conv_desc(col, k, 1, 1, 1, 0)
             dy = _cl(dy)
             dw192 = torch.empty((d.k, STEM_K), dtype=torch.float32, device=col.device)
             need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))

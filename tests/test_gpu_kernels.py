@@ -475,7 +475,8 @@ def test_tensor_core_path_is_taken_and_matches_cuda_core_path(ops):
 
 @pytest.mark.parametrize("hw,layout", [(56, "nchw_f32"), (84, "nchw_f32"), (56, "cl_bf16")])
 def test_stem_tensor_core_path(ops, hw, layout):
-    """7x7/2 stem = im2col (from the caller's own tensor layout/dtype) + tcgen05 1x1 conv with 192 channels."""
+    """7x7/2 stem through the Conv2d module: forward = space-to-depth + shifted-window tcgen05 convolution, weight
+    gradient = im2col (from the caller's own tensor layout/dtype) + tcgen05 1x1 wgrad with 192 channels."""
     from iit_b200.nn.resnet import Conv2d
     g = torch.Generator().manual_seed(12)
     n = 6
@@ -499,7 +500,7 @@ def test_stem_tensor_core_path(ops, hw, layout):
         yd.backward(gy.to(DEV).bfloat16())
     finally:
         ops.call = inner
-    assert "iit_stem_im2col" in seen and "iit_conv2d_fprop_tc" in seen and "iit_conv2d_wgrad_tc" in seen
+    assert "iit_stem_s2d" in seen and "iit_stem_conv_s2d" in seen and "iit_stem_im2col" in seen and "iit_conv2d_wgrad_tc" in seen
     assert "iit_conv2d_fprop" not in seen and "iit_conv2d_wgrad" not in seen
     for a, b, what in ((yd.float().cpu(), y.detach(), "fprop"), (conv.weight.grad.cpu(), w.grad, "wgrad")):
         scale = b.abs().max().item()
@@ -521,10 +522,10 @@ def test_stem_cols_cache_follows_the_tensor(ops):
     assert c2 is c1 and torch.equal(c2, ops.stem_im2col(x))
     y = torch.rand(3, 3, 56, 56, device=DEV)
     assert ops.stem_cols(y) is not c1
-    n = len(ops._stem_cols)
+    n = len(ops._batch_cache)
     del x, y
     gc.collect()
-    assert len(ops._stem_cols) == n - 2
+    assert len(ops._batch_cache) == n - 2
 
 
 def _conv_desc(n, h, w, c, k, r, stride, pad):
