@@ -572,6 +572,9 @@ static int launch_wgrad_tc(const CUtensorMap& mdy, const CUtensorMap& mx, float*
 bool conv_win_3x3_supported(const iit_conv_t* d);
 int conv_win_3x3(const void* in, const void* wmat, void* out, const iit_conv_t* d, bool flip, cudaStream_t st, double* bn_sum,
                  double* bn_sq, const char* name);
+bool wgrad_win_supported(const iit_conv_t* d);
+size_t wgrad_win_scratch_bytes(const iit_conv_t* d);
+int wgrad_win(const void* dy, const void* x, float* part, const iit_conv_t* d, int* splits, cudaStream_t st, const char* name);
 static bool g_use_win = true;
 
 }  // namespace iit
@@ -620,7 +623,9 @@ extern "C" size_t iit_conv2d_wgrad_tc_scratch_bytes(const iit_conv_t* d) {
   TcWgradParams p;
   int splits, CB;
   wgrad_tc_plan(d, &p, &splits, &CB);
-  return (size_t)splits * d->k * d->r * d->s * d->c * sizeof(float);
+  size_t need = (size_t)splits * d->k * d->r * d->s * d->c * sizeof(float);
+  const size_t win = wgrad_win_scratch_bytes(d);     // enough for either kernel, whichever the switch selects
+  return need > win ? need : win;
 }
 
 extern "C" int iit_conv2d_wgrad_tc(const void* dy, const void* x, float* dw, const iit_conv_t* d, void* scratch,
@@ -628,13 +633,27 @@ extern "C" int iit_conv2d_wgrad_tc(const void* dy, const void* x, float* dw, con
   IIT_REQUIRE(dy && x && dw && d, "iit_conv2d_wgrad_tc: null pointer");
   IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "iit_conv2d_wgrad_tc: only bf16 3x3/pad-1 or 1x1/pad-0 convolutions, stride 1 "
               "or 2, with channel counts that are multiples of 64");
+  IIT_REQUIRE((reinterpret_cast<uintptr_t>(scratch) & 15) == 0 && (reinterpret_cast<uintptr_t>(dw) & 15) == 0,
+              "iit_conv2d_wgrad_tc: scratch and dw must be 16-byte aligned");
+  if (g_use_win && wgrad_win_supported(d)) {
+    const size_t need_win = wgrad_win_scratch_bytes(d);
+    IIT_REQUIRE(scratch && scratch_bytes >= need_win, "iit_conv2d_wgrad_tc: scratch too small: need %zu bytes, got %zu", need_win,
+                scratch_bytes);
+    IIT_REQUIRE(((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(x)) & 15) == 0,
+                "iit_conv2d_wgrad_tc: dy and x must be 16-byte aligned");
+    int nsplit = 0;
+    int rc = wgrad_win(dy, x, (float*)scratch, d, &nsplit, as_stream(stream), "iit_conv2d_wgrad_tc");
+    if (rc) return rc;
+    const int64_t n = (int64_t)d->k * d->r * d->s * d->c;
+    tc_splitk_reduce_kernel<<<grid_for(n / 4, 256), 256, 0, as_stream(stream)>>>((const float*)scratch, dw, n, nsplit);
+    IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc(reduce)");
+    return 0;
+  }
   TcWgradParams p;
   int splits, CB;
   wgrad_tc_plan(d, &p, &splits, &CB);
   size_t need = (size_t)splits * d->k * d->r * d->s * d->c * sizeof(float);
   IIT_REQUIRE(scratch && scratch_bytes >= need, "iit_conv2d_wgrad_tc: scratch too small: need %zu bytes, got %zu", need, scratch_bytes);
-  IIT_REQUIRE((reinterpret_cast<uintptr_t>(scratch) & 15) == 0 && (reinterpret_cast<uintptr_t>(dw) & 15) == 0,
-              "iit_conv2d_wgrad_tc: scratch and dw must be 16-byte aligned");
   CUtensorMap mdy, mx;
   if (encode_nhwc_strided(&mdy, dy, d->k, d->q, d->p, d->n, p.BW, p.BH, p.BNI, 1, "iit_conv2d_wgrad_tc(dy)")) return 1;
   if (encode_nhwc_strided(&mx, x, d->c, d->w, d->h, d->n, p.BW, p.BH, p.BNI, d->stride, "iit_conv2d_wgrad_tc(x)")) return 1;

@@ -349,6 +349,200 @@ int conv_win_3x3(const void* in, const void* wmat, void* out, const iit_conv_t* 
   return win_launch<128, 9>(ma, mb, out, p, st, bn_sum, bn_sq, name);
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Weight gradient of the same 3x3 / 64 -> 64 layers with shifted windows:
+//     dW[k, r, s, c] = sum over padded positions j of  dy[j, k] * x[j + (r-1)*PW + (s-1), c]
+// dy and x are loaded once per image as zero-padded tiles in the same raster (the halo of dy is zero, so halo positions
+// contribute nothing). Pixels are the GEMM K dimension, both operands MN-major (a pixel's 64 channels are one 128-byte
+// row). The 64-element M / N blocks of an MN-major operand are LBO bytes apart - and LBO may be ONE ROW (128 B) or one
+// image row (PW*128 B), making the blocks overlapping shifted windows of the same tile (scratch/umma_mn_test.cu):
+//     MMA 1 (M=128, N=192): A = [dy | dy shifted by PW rows], B = [x at +PW-1 | +PW | +PW+1]  -> taps r=2 (rows 0-63) and
+//                                                                                           r=1 (rows 64-127), s=0,1,2
+//     MMA 2 (M=128, N=192): A = [dy | (ignored)],            B = [x at -PW-1 | -PW | -PW+1]  -> taps r=0 (rows 0-63)
+// Two MMAs per 16 pixels instead of nine loads + nine MMAs. The accumulators (2 x 192 TMEM columns) persist over all the
+// images of a CTA; each CTA writes one partial dW, reduced in fixed order by tc_splitk_reduce (conv_tc.cu).
+struct WgradWinParams {
+  int N, PW, box_h;
+  int ks1, ks2;           // 16-row K steps of MMA 1 / MMA 2
+  int tile_rows;          // rows TMA delivers per tile
+  int alloc_rows;         // rows reserved per tile (the extra ones are zeroed once and never written)
+};
+
+__device__ __forceinline__ uint64_t win_desc_mn(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return (uint64_t)((smem_addr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) | ((uint64_t)(1024 >> 4) << 32) |
+         (1ull << 46) | (2ull << 61);
+}
+
+template <int STAGES>
+__global__ void __launch_bounds__(WIN_THREADS) wgrad_win_kernel(const __grid_constant__ CUtensorMap map_dy,
+                                                                const __grid_constant__ CUtensorMap map_x,
+                                                                float* __restrict__ part, WgradWinParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const uint32_t tile_alloc = (uint32_t)p.alloc_rows * 128;      // multiple of 1024
+  const uint32_t stage_bytes = 2 * tile_alloc;                   // [dy tile][x tile]
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)STAGES * stage_bytes);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tmem_full = empty + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // rows past the TMA box are read by the last K steps against zero gradient rows: they must be finite -> zero
+  {
+    const uint32_t tail = (uint32_t)(p.alloc_rows - p.tile_rows) * 128 / 16;   // uint4 per tile
+    for (uint32_t i = threadIdx.x; i < tail * 2 * STAGES; i += blockDim.x) {
+      const uint32_t tile = i / tail, off = i - tile * tail;
+      reinterpret_cast<uint4*>(smem + (size_t)tile * tile_alloc + (size_t)p.tile_rows * 128)[off] = make_uint4(0, 0, 0, 0);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the tensor-core reads
+  }
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(tmem_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+  const bool has_work = (int)blockIdx.x < p.N;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_dy)) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_x)) : "memory");
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int n = blockIdx.x; n < p.N; n += gridDim.x) {
+        uint8_t* st = smem + (size_t)stage * stage_bytes;
+        mbar_wait(&empty[stage], phase ^ 1);
+        mbar_expect_tx(&full[stage], 2u * p.tile_rows * 128);
+        tma_load_4d(st, &map_dy, &full[stage], 0, -1, -1, n);
+        tma_load_4d(st + tile_alloc, &map_x, &full[stage], 0, -1, -1, n);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && has_work) {
+      // D=f32, A=B=bf16, both MN-major, N=192, M=128
+      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(192 >> 3) << 17) |
+                                 ((uint32_t)(128 >> 4) << 24);
+      const uint32_t lbo_a = (uint32_t)p.PW * 128, lbo_b = 128;
+      const uint64_t pa = win_desc_mn(0, lbo_a), pb = win_desc_mn(0, lbo_b);
+      const uint32_t a_hi = (uint32_t)(pa >> 32), a_flags = (uint32_t)pa, b_hi = (uint32_t)(pb >> 32), b_flags = (uint32_t)pb;
+      const uint32_t row = 128 / 16;                       // descriptor address units per tile row
+      int stage = 0;
+      uint32_t phase = 0, first = 1;
+      for (int n = blockIdx.x; n < p.N; n += gridDim.x) {
+        mbar_wait(&full[stage], phase);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t dy0 = smem_u32(smem + (size_t)stage * stage_bytes) >> 4, x0 = dy0 + (tile_alloc >> 4);
+        // MMA 1: dy rows [0, 16*ks1) and [PW, PW+16*ks1); x rows from PW-1, PW, PW+1
+        const uint32_t a1 = a_flags + dy0, b1 = b_flags + x0 + (uint32_t)(p.PW - 1) * row;
+        for (int kk = 0; kk < p.ks1; ++kk)
+          umma_bf16_lohi(tmem_base, a1 + kk * 16 * row, a_hi, b1 + kk * 16 * row, b_hi, idesc, (uint32_t)(!first || kk != 0));
+        // MMA 2: dy rows from PW+1; x rows from 0, 1, 2
+        const uint32_t a2 = a_flags + dy0 + (uint32_t)(p.PW + 1) * row, b2 = b_flags + x0;
+        for (int kk = 0; kk < p.ks2; ++kk)
+          umma_bf16_lohi(tmem_base + 192, a2 + kk * 16 * row, a_hi, b2 + kk * 16 * row, b_hi, idesc, (uint32_t)(!first || kk != 0));
+        umma_commit(&empty[stage]);
+        first = 0;
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      umma_commit(tmem_full);
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int L = quarter * 32 + lane;          // TMEM lane
+    const int k = L & 63, mb = L >> 6;
+    float* base = part + ((int64_t)blockIdx.x * 64 + k) * 9 * 64;
+    if (has_work) {
+      mbar_wait(tmem_full, 0);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
+#pragma unroll 1
+    for (int which = 0; which < 2; ++which) {
+      if (which == 1 && mb == 1) break;        // rows 64-127 of the second accumulator are not a tap
+      const int r = which == 0 ? (mb == 0 ? 2 : 1) : 0;
+#pragma unroll 1
+      for (int chunk = 0; chunk < 6; ++chunk) {
+        uint32_t v[32];
+        if (has_work) {
+          tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(which * 192 + chunk * 32), v);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0u;
+        }
+        float* dst = base + (r * 3 + (chunk >> 1)) * 64 + (chunk & 1) * 32;
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) *reinterpret_cast<uint4*>(dst + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+  }
+}
+
+static bool wgrad_win_plan(const iit_conv_t* d, WgradWinParams* p, int* grid) {
+  if (!(d->r == 3 && d->s == 3 && d->pad == 1 && d->stride == 1 && d->c == 64 && d->k == 64)) return false;
+  const int PW = d->w + 2, box_h = d->h + 2;
+  if (PW > 256 || box_h > 256 || PW * box_h > 256) return false;      // whole padded image as one tile
+  p->N = d->n; p->PW = PW; p->box_h = box_h;
+  p->tile_rows = PW * box_h;
+  p->ks1 = ((d->h + 1) * PW + 15) / 16;
+  p->ks2 = (d->h * PW - 2 + 15) / 16;
+  int need = PW + 16 * p->ks1;                                         // dy, MMA 1, second block
+  if (PW + 1 + 16 * p->ks1 > need) need = PW + 1 + 16 * p->ks1;        // x, MMA 1
+  if (2 * PW + 1 + 16 * p->ks2 > need) need = 2 * PW + 1 + 16 * p->ks2;  // dy, MMA 2, (ignored) second block
+  if (need < p->tile_rows) need = p->tile_rows;
+  p->alloc_rows = (need + 7) & ~7;
+  *grid = d->n < kNumSMs ? d->n : kNumSMs;
+  return true;
+}
+
+bool wgrad_win_supported(const iit_conv_t* d) {
+  WgradWinParams p;
+  int grid;
+  return wgrad_win_plan(d, &p, &grid);
+}
+
+size_t wgrad_win_scratch_bytes(const iit_conv_t* d) {
+  WgradWinParams p;
+  int grid;
+  if (!wgrad_win_plan(d, &p, &grid)) return 0;
+  return (size_t)grid * 64 * 9 * 64 * sizeof(float);
+}
+
+// writes grid partial sums [split][k][r][s][c] into `part`; returns the number of splits through *splits
+int wgrad_win(const void* dy, const void* x, float* part, const iit_conv_t* d, int* splits, cudaStream_t st, const char* name) {
+  WgradWinParams p;
+  int grid;
+  IIT_REQUIRE(wgrad_win_plan(d, &p, &grid), "%s: shape does not fit the shifted-window weight-gradient kernel", name);
+  constexpr int STAGES = 3;
+  const size_t smem = (size_t)STAGES * 2 * p.alloc_rows * 128 + (2 * STAGES + 1) * 8 + 16 + 1024;
+  IIT_REQUIRE(smem <= WIN_SMEM_MAX, "%s: tiles do not fit shared memory", name);
+  CUtensorMap mdy, mx;
+  if (win_encode_a(&mdy, dy, 64, d->q, d->p, d->n, p.PW, p.box_h, 128, name)) return 1;
+  if (win_encode_a(&mx, x, 64, d->w, d->h, d->n, p.PW, p.box_h, 128, name)) return 1;
+  static bool attr_set = false;
+  if (!attr_set) {
+    IIT_CUDA(cudaFuncSetAttribute(wgrad_win_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WIN_SMEM_MAX));
+    attr_set = true;
+  }
+  wgrad_win_kernel<STAGES><<<grid, WIN_THREADS, smem, st>>>(mdy, mx, part, p);
+  IIT_LAUNCH_CHECK(name);
+  *splits = grid;
+  return 0;
+}
+
 }  // namespace iit
 
 using namespace iit;

@@ -560,7 +560,11 @@ def test_shifted_window_conv_is_bit_identical_to_the_tiled_kernel(ops, n, h, w):
             sums = torch.zeros(2, 64, dtype=torch.float64, device=DEV)
             _lib.call("iit_conv2d_fprop_tc", p(x), p(wt), p(y), C.byref(d), p(sums[0]), p(sums[1]), st)
             _lib.call("iit_conv2d_dgrad_tc", p(y), p(wt_crsk), p(dx), C.byref(d), st)
-            res[on] = (y, dx, sums)
+            need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
+            scratch = torch.full((need,), 0x7f, dtype=torch.uint8, device=DEV)
+            dw = torch.full((64, 3, 3, 64), 7.0, device=DEV)
+            _lib.call("iit_conv2d_wgrad_tc", p(y), p(x), p(dw), C.byref(d), p(scratch), need, st)
+            res[on] = (y, dx, sums, dw)
         finally:
             _lib.lib.iit_conv_win_enable(was)
     assert torch.equal(res[1][0], res[0][0])
@@ -568,6 +572,14 @@ def test_shifted_window_conv_is_bit_identical_to_the_tiled_kernel(ops, n, h, w):
     torch.testing.assert_close(res[1][2], res[0][2], rtol=1e-6, atol=1e-6)   # fp32 partial sums in a different grouping
     ref = F.conv2d(x.float().cpu().permute(0, 3, 1, 2), wt.float().cpu().permute(0, 3, 1, 2), padding=1).permute(0, 2, 3, 1)
     torch.testing.assert_close(res[1][0].float().cpu(), ref, rtol=2e-2, atol=2e-2)
+    # weight gradient (dy := y): exact bf16 products, fp32 accumulation in a different order -> 1e-3 of the largest entry
+    xr = x.float().cpu().permute(0, 3, 1, 2)
+    wr = wt.float().cpu().permute(0, 3, 1, 2).clone().requires_grad_(True)
+    F.conv2d(xr, wr, padding=1).backward(res[1][0].float().cpu().permute(0, 3, 1, 2))
+    dw_ref = wr.grad.permute(0, 2, 3, 1)
+    for on in (1, 0):
+        err = (res[on][3].cpu() - dw_ref).abs().max().item()
+        assert err <= 1e-3 * dw_ref.abs().max().item(), (on, err, dw_ref.abs().max().item())
     yb = res[1][0].double()
     torch.testing.assert_close(res[1][2][0].cpu(), yb.sum((0, 1, 2)).cpu(), rtol=1e-5, atol=1e-3)
     torch.testing.assert_close(res[1][2][1].cpu(), (yb * yb).sum((0, 1, 2)).cpu(), rtol=1e-5, atol=1e-3)
