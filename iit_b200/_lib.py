@@ -89,6 +89,8 @@ SIGNATURES = {
     "iit_stem_s2d": [_vp, _i, _vp, _vp, _i, _i, _i, _vp],
     "iit_stem_filter_s2d": [_vp, _vp, _vp, _vp],
     "iit_stem_conv_s2d": [_vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp],
+    "iit_stem_wgrad_s2d_scratch_bytes": [_i, _i, _i],
+    "iit_stem_wgrad_s2d": [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, C.c_size_t, _vp],
     "iit_sqnorm": [_vp, _i64, _vp, _vp],
     "iit_adam_step": [_vp, _vp, _vp, _vp, _i64, _d, _d, _d, _d, _i64, _vp, _d, _vp],
     "iit_adam_step_dev": [_vp, _vp, _vp, _vp, _i64, _vp, _d, _d, _d, _vp, _vp, _d, _vp],
@@ -97,7 +99,8 @@ SIGNATURES = {
     "iit_launch_count": [],
 }
 _RESTYPES = {"iit_last_error": C.c_char_p, "iit_launch_count": C.c_ulonglong,
-             "iit_conv2d_wgrad_scratch_bytes": C.c_size_t, "iit_conv2d_wgrad_tc_scratch_bytes": C.c_size_t}
+             "iit_conv2d_wgrad_scratch_bytes": C.c_size_t, "iit_conv2d_wgrad_tc_scratch_bytes": C.c_size_t,
+             "iit_stem_wgrad_s2d_scratch_bytes": C.c_size_t}
 _NO_STATUS = set(_RESTYPES) | {"iit_version", "iit_conv2d_tc_supported", "iit_conv_win_enable"}
 
 

@@ -543,9 +543,220 @@ int wgrad_win(const void* dy, const void* x, float* part, const iit_conv_t* d, i
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Weight gradient of the stem in its space-to-depth form:
+//     dW2[k, R, S, c] = sum over output pixels (p, q) of  dy[p, q, k] * s2d[p + R, q + S, c]        (R, S < 4, c < 16)
+// Same construction as above on the s2d raster (PW pixels per row; dy is loaded with PW - OW zero columns through TMA's
+// out-of-bounds fill). An image is processed in bands of BH output rows; the dy band sits between two zeroed regions of
+// shared memory so that both 64-row M blocks (dy, and dy shifted by one raster row) sweep every real row:
+//     MMA 1 (M=128, N=64): A = [dy | dy shifted by PW rows], B = [s2d at +PW+S, S=0..3 (32-byte rows, LBO = 1 row)] -> R = 1, 0
+//     MMA 2 (M=128, N=64): same A,                            B = [s2d at +3PW+S]                                  -> R = 3, 2
+struct StemWgradParams {
+  int N, OH, OW, PW, SH;   // images, output size, raster width (= s2d width), s2d height
+  int BH, bands;           // output rows per band
+  int ks;                  // 16-row K steps per band
+  int dy_alloc, x_alloc;   // bytes reserved per dy / s2d tile (multiples of 1024)
+  int dy_rows, x_rows;     // rows TMA delivers
+};
+
+constexpr int STEM_LEAD = 32;   // zeroed rows in front of each tile (TMA destination stays 1024-byte aligned)
+
+template <int STAGES>
+__global__ void __launch_bounds__(WIN_THREADS) stem_wgrad_win_kernel(const __grid_constant__ CUtensorMap map_dy,
+                                                                     const __grid_constant__ CUtensorMap map_x,
+                                                                     float* __restrict__ part, StemWgradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const uint32_t stage_bytes = (uint32_t)(p.dy_alloc + p.x_alloc);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)STAGES * stage_bytes);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tmem_full = empty + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total = p.N * p.bands;
+
+  // everything TMA does not overwrite must be zero (dy) / finite (s2d): clear all stages once
+  for (uint32_t i = threadIdx.x; i < (uint32_t)STAGES * stage_bytes / 16; i += blockDim.x)
+    reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(tmem_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(128));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+  const bool has_work = (int)blockIdx.x < total;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_dy)) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_x)) : "memory");
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        const int n = t / p.bands, band = t - n * p.bands;
+        uint8_t* st = smem + (size_t)stage * stage_bytes;
+        mbar_wait(&empty[stage], phase ^ 1);
+        mbar_expect_tx(&full[stage], (uint32_t)p.dy_rows * 128 + (uint32_t)p.x_rows * 32);
+        tma_load_4d(st + STEM_LEAD * 128, &map_dy, &full[stage], 0, 0, band * p.BH, n);
+        tma_load_4d(st + p.dy_alloc + STEM_LEAD * 32, &map_x, &full[stage], 0, 0, band * p.BH, n);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && has_work) {
+      // D=f32, A=B=bf16, both MN-major, N=64, M=128
+      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(64 >> 3) << 17) |
+                                 ((uint32_t)(128 >> 4) << 24);
+      const uint64_t pa = win_desc_mn(0, (uint32_t)p.PW * 128);
+      // s2d rows are 32 bytes: SWIZZLE_32B, 8-row groups 256 bytes apart, 16-channel N blocks one row (32 bytes) apart
+      const uint64_t pb = (uint64_t)(32 >> 4) << 16 | ((uint64_t)(256 >> 4) << 32) | (1ull << 46) | (6ull << 61);
+      const uint32_t a_hi = (uint32_t)(pa >> 32), a_flags = (uint32_t)pa, b_hi = (uint32_t)(pb >> 32), b_flags = (uint32_t)pb;
+      int stage = 0;
+      uint32_t phase = 0, first = 1;
+      for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        mbar_wait(&full[stage], phase);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t dy0 = smem_u32(smem + (size_t)stage * stage_bytes) >> 4, x0 = dy0 + ((uint32_t)p.dy_alloc >> 4);
+        // both tiles hold raster position j in tile row STEM_LEAD + j: for tap offset o the s2d row is the dy row + o.
+        // M block 0 starts PW rows before the first real row (zeros), block 1 (LBO = PW rows) exactly on it.
+        const uint32_t a0 = (uint32_t)(STEM_LEAD - p.PW);
+        const uint32_t a = a_flags + dy0 + a0 * 8;
+        const uint32_t b1 = b_flags + x0 + (a0 + p.PW) * 2, b2 = b_flags + x0 + (a0 + 3 * p.PW) * 2;
+        for (int kk = 0; kk < p.ks; ++kk) {
+          const uint32_t acc = (uint32_t)(!first || kk != 0);
+          umma_bf16_lohi(tmem_base, a + kk * 128, a_hi, b1 + kk * 32, b_hi, idesc, acc);
+          umma_bf16_lohi(tmem_base + 64, a + kk * 128, a_hi, b2 + kk * 32, b_hi, idesc, acc);
+        }
+        umma_commit(&empty[stage]);
+        first = 0;
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      umma_commit(tmem_full);
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int L = quarter * 32 + lane;
+    const int k = L & 63, mb = L >> 6;
+    float* base = part + ((int64_t)blockIdx.x * 64 + k) * 256;      // [k][R][S][c]
+    if (has_work) {
+      mbar_wait(tmem_full, 0);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
+#pragma unroll 1
+    for (int chunk = 0; chunk < 4; ++chunk) {      // 32 columns = S pair {0,1} / {2,3} of accumulator chunk / 2
+      uint32_t v[32];
+      if (has_work) {
+        tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(chunk * 32), v);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = 0u;
+      }
+      const int R = (chunk >> 1) == 0 ? (mb == 0 ? 1 : 0) : (mb == 0 ? 3 : 2);
+      float* dst = base + R * 64 + (chunk & 1) * 32;
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) *reinterpret_cast<uint4*>(dst + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128));
+  }
+}
+
+// sum of the per-CTA partials [split][64][4][4][16] -> dw [64,3,7,7] (given strides): inverse of stem_filter_s2d
+__global__ void stem_wgrad_finish_kernel(const float* __restrict__ part, int splits, float* __restrict__ dw, int64_t sk, int64_t sc,
+                                         int64_t sr, int64_t ss) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 64 * 256) return;
+  const int ch = i & 15, S = (i >> 4) & 3, R = (i >> 6) & 3, k = i >> 8;
+  if (ch >= 12) return;
+  const int ab = ch / 3, c = ch - ab * 3, a = ab >> 1, b = ab & 1;
+  const int r = 2 * R + a, s = 2 * S + b;
+  if (r >= 7 || s >= 7) return;
+  float acc = 0.f;
+  for (int z = 0; z < splits; ++z) acc += part[(int64_t)z * 64 * 256 + i];   // fixed order: deterministic
+  dw[k * sk + c * sc + r * sr + s * ss] = acc;
+}
+
+static bool stem_wgrad_plan(int n, int sh, int sw, StemWgradParams* p, int* grid, size_t* smem, int stages) {
+  const int OH = sh - 3, OW = sw - 3, PW = sw;
+  if (OH < 1 || OW < 1 || PW > STEM_LEAD) return false;      // one raster row of zeros must fit in front of the dy band
+  const int a0 = STEM_LEAD - PW;                             // first tile row of M block 0 (block 1 starts at STEM_LEAD)
+  for (int BH = OH; BH >= 1; --BH) {
+    if (BH + 3 > 256) continue;
+    const int ks = ((BH + 1) * PW + 15) / 16;
+    const int dy_rows = BH * PW, x_rows = (BH + 3) * PW;
+    int dy_alloc_rows = STEM_LEAD + 16 * ks;                 // block 1 reads tile rows [STEM_LEAD, STEM_LEAD + 16 ks)
+    if (dy_alloc_rows < STEM_LEAD + dy_rows) dy_alloc_rows = STEM_LEAD + dy_rows;
+    int x_alloc_rows = a0 + 3 * PW + 3 + 16 * ks;            // MMA 2, S = 3, last K step
+    if (x_alloc_rows < STEM_LEAD + x_rows) x_alloc_rows = STEM_LEAD + x_rows;
+    p->dy_alloc = (dy_alloc_rows * 128 + 1023) & ~1023;
+    p->x_alloc = (x_alloc_rows * 32 + 1023) & ~1023;
+    const size_t need = (size_t)stages * (p->dy_alloc + p->x_alloc) + (2 * stages + 1) * 8 + 16 + 1024;
+    if (need > WIN_SMEM_MAX) continue;
+    p->N = n; p->OH = OH; p->OW = OW; p->PW = PW; p->SH = sh; p->BH = BH; p->bands = (OH + BH - 1) / BH; p->ks = ks;
+    p->dy_rows = dy_rows; p->x_rows = x_rows;
+    const int64_t total = (int64_t)n * p->bands;
+    *grid = total < kNumSMs ? (int)total : kNumSMs;
+    *smem = need;
+    return true;
+  }
+  return false;
+}
+
 }  // namespace iit
 
 using namespace iit;
+
+extern "C" size_t iit_stem_wgrad_s2d_scratch_bytes(int n, int sh, int sw) {
+  StemWgradParams p;
+  int grid; size_t smem;
+  if (!stem_wgrad_plan(n, sh, sw, &p, &grid, &smem, 3)) return 0;
+  return (size_t)grid * 64 * 256 * sizeof(float);
+}
+
+extern "C" int iit_stem_wgrad_s2d(const void* dy, const void* s2d, float* dw, const int64_t* dw_strides_kcrs, int n, int sh, int sw,
+                                  void* scratch, size_t scratch_bytes, void* stream) {
+  const char* name = "iit_stem_wgrad_s2d";
+  IIT_REQUIRE(dy && s2d && dw && dw_strides_kcrs && scratch, "%s: null pointer", name);
+  IIT_REQUIRE(((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(s2d) | reinterpret_cast<uintptr_t>(scratch)) & 15) == 0,
+              "%s: dy, s2d and scratch must be 16-byte aligned", name);
+  // one raster row of zeros has to fit in front of the gradient tile
+  IIT_REQUIRE(sw <= STEM_LEAD, "%s: s2d width %d exceeds %d (images wider than %d pixels take the im2col path)", name, sw, STEM_LEAD,
+              2 * STEM_LEAD - 6);
+  constexpr int STAGES = 3;
+  StemWgradParams p;
+  int grid; size_t smem;
+  IIT_REQUIRE(stem_wgrad_plan(n, sh, sw, &p, &grid, &smem, STAGES), "%s: image %dx%d does not fit", name, sh, sw);
+  const size_t need = (size_t)grid * 64 * 256 * sizeof(float);
+  IIT_REQUIRE(scratch_bytes >= need, "%s: scratch too small: need %zu bytes, got %zu", name, need, scratch_bytes);
+  CUtensorMap mdy, mx;
+  // dy [n, OH, OW, 64] read on the PW-wide raster: the box is wider than the tensor, the excess columns are zero-filled
+  if (win_encode_a(&mdy, dy, 64, p.OW, p.OH, n, p.PW, p.BH, 128, name)) return 1;
+  if (win_encode_a(&mx, s2d, 16, sw, sh, n, p.PW, p.BH + 3, 32, name)) return 1;
+  static bool attr_set = false;
+  if (!attr_set) {
+    IIT_CUDA(cudaFuncSetAttribute(stem_wgrad_win_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WIN_SMEM_MAX));
+    attr_set = true;
+  }
+  cudaStream_t st = as_stream(stream);
+  stem_wgrad_win_kernel<STAGES><<<grid, WIN_THREADS, smem, st>>>(mdy, mx, (float*)scratch, p);
+  IIT_LAUNCH_CHECK(name);
+  stem_wgrad_finish_kernel<<<64, 256, 0, st>>>((const float*)scratch, grid, dw, dw_strides_kcrs[0], dw_strides_kcrs[1],
+                                               dw_strides_kcrs[2], dw_strides_kcrs[3]);
+  IIT_LAUNCH_CHECK("iit_stem_wgrad_s2d(finish)");
+  return 0;
+}
 
 // Stem: y[n,p,q,k] = sum_{R,S<4} sum_{c<16} s2d[n, p+R, q+S, c] * w2[k, R, S, c], where s2d is the zero-padded image
 // after a 2x2 space-to-depth ([N, (H+6)/2, (W+6)/2, 16] bf16, 12 real channels) and w2 the 7x7 filter regrouped

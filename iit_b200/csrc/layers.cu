@@ -347,32 +347,41 @@ __global__ void __launch_bounds__(256) linear_dx_kernel(const float* __restrict_
     dx[e] = s;
   }
 }
-// dw[o,i] = sum_n dy[n,o] x[n,i]; block (o, i-chunk of 64): 64 columns x 4 row lanes
+// dw[o,i] = sum_n dy[n,o] x[n,i], db[o] = sum_n dy[n,o]. The head is tiny (O = 10) but N is the batch: rows are split
+// over gridDim.y blocks; a block covers 64 columns x 4 row lanes, keeps all O (<= 16) outputs of its column in registers
+// so that x is read once, and adds its partial sums to the zeroed dw / db with fp32 atomics.
+constexpr int LIN_MAX_O = 16;
 __global__ void __launch_bounds__(256) linear_dw_kernel(const float* __restrict__ dy, const float* __restrict__ x,
-                                                        float* __restrict__ dw, float* __restrict__ db, int N, int I, int O) {
-  __shared__ float s_part[4][64];
-  __shared__ float s_db[256];
-  int o = blockIdx.y;
-  int col = threadIdx.x & 63, rl = threadIdx.x >> 6;
-  int i = blockIdx.x * 64 + col;
-  float s = 0.f, sb = 0.f;
-  for (int n = rl; n < N; n += 4) {
-    float g = dy[(int64_t)n * O + o];
-    if (i < I) s = fmaf(g, x[(int64_t)n * I + i], s);
-  }
-  s_part[rl][col] = s;
-  if (blockIdx.x == 0) {
-    for (int n = threadIdx.x; n < N; n += 256) sb += dy[(int64_t)n * O + o];
-    s_db[threadIdx.x] = sb;
-  }
-  __syncthreads();
-  if (threadIdx.x < 64 && i < I) dw[(int64_t)o * I + i] = s_part[0][col] + s_part[1][col] + s_part[2][col] + s_part[3][col];
-  if (blockIdx.x == 0 && db) {
-    for (int st = 128; st > 0; st >>= 1) {
-      if (threadIdx.x < st) s_db[threadIdx.x] += s_db[threadIdx.x + st];
-      __syncthreads();
+                                                        float* __restrict__ dw, float* __restrict__ db, int N, int I, int O,
+                                                        int rows_per_block) {
+  __shared__ float s_part[4][LIN_MAX_O][64];
+  const int col = threadIdx.x & 63, rl = threadIdx.x >> 6;
+  const int i = blockIdx.x * 64 + col;
+  const int n0 = blockIdx.y * rows_per_block;
+  const int n1 = min(N, n0 + rows_per_block);
+  float acc[LIN_MAX_O];
+#pragma unroll
+  for (int o = 0; o < LIN_MAX_O; ++o) acc[o] = 0.f;
+  if (i < I) {
+    for (int n = n0 + rl; n < n1; n += 4) {
+      const float xv = x[(int64_t)n * I + i];
+#pragma unroll
+      for (int o = 0; o < LIN_MAX_O; ++o)
+        if (o < O) acc[o] = fmaf(dy[(int64_t)n * O + o], xv, acc[o]);
     }
-    if (threadIdx.x == 0) db[o] = s_db[0];
+  }
+#pragma unroll
+  for (int o = 0; o < LIN_MAX_O; ++o) s_part[rl][o][col] = acc[o];
+  __syncthreads();
+  for (int e = threadIdx.x; e < O * 64; e += 256) {
+    const int o = e >> 6, c = e & 63;
+    const int ii = blockIdx.x * 64 + c;
+    if (ii < I) atomicAdd(&dw[(int64_t)o * I + ii], s_part[0][o][c] + s_part[1][o][c] + s_part[2][o][c] + s_part[3][o][c]);
+  }
+  if (db && blockIdx.x == 0 && threadIdx.x < O) {
+    float sb = 0.f;
+    for (int n = n0; n < n1; ++n) sb += dy[(int64_t)n * O + threadIdx.x];
+    atomicAdd(&db[threadIdx.x], sb);
   }
 }
 
@@ -630,7 +639,16 @@ extern "C" int iit_linear_bwd(const float* x, const float* w, const float* dy, f
     IIT_LAUNCH_CHECK("iit_linear_bwd(dx)");
   }
   if (dw) {
-    linear_dw_kernel<<<dim3((in + 63) / 64, out), 256, 0, st>>>(dy, x, dw, db, n, in, out);
+    IIT_REQUIRE(out <= LIN_MAX_O, "iit_linear_bwd: at most %d output features (got %d)", LIN_MAX_O, out);
+    IIT_CUDA(cudaMemsetAsync(dw, 0, (size_t)out * in * sizeof(float), st));
+    if (db) IIT_CUDA(cudaMemsetAsync(db, 0, (size_t)out * sizeof(float), st));
+    const int col_blocks = (in + 63) / 64;
+    int row_blocks = (2 * kNumSMs + col_blocks - 1) / col_blocks;
+    if (row_blocks > (n + 31) / 32) row_blocks = (n + 31) / 32;       // at least 32 rows per block
+    if (row_blocks < 1) row_blocks = 1;
+    const int rows_per_block = (n + row_blocks - 1) / row_blocks;
+    linear_dw_kernel<<<dim3(col_blocks, (n + rows_per_block - 1) / rows_per_block), 256, 0, st>>>(dy, x, dw, db, n, in, out,
+                                                                                               rows_per_block);
     IIT_LAUNCH_CHECK("iit_linear_bwd(dw)");
   }
   return 0;

@@ -441,7 +441,8 @@ def stem_s2d_cached(x: torch.Tensor) -> torch.Tensor:
 class _StemConvFn(torch.autograd.Function):
     """7x7/2 stem on the tensor cores. Forward: the 4x4 stride-1 convolution over the space-to-depth image on the
     shifted-window kernel (even image sizes with 64 filters), else im2col + a 1x1 convolution with 192 channels.
-    Weight gradient: im2col (built once per batch) + the 1x1 wgrad kernel."""
+    Weight gradient: the shifted-window kernel on the same space-to-depth image (s2d width <= 32), else im2col (built
+    once per batch) + the 1x1 wgrad kernel."""
 
     @staticmethod
     def forward(ctx, x, weight, w_prepared, bn_sums):
@@ -470,15 +471,26 @@ class _StemConvFn(torch.autograd.Function):
         (weight,) = ctx.saved_tensors
         dw = None
         if ctx.needs_input_grad[1]:
-            col = stem_cols(ctx.x)     # 1.2 GB at batch 4096 (bf16), shared by every backward of this batch
-            k = weight.shape[0]
-            d = _conv_desc(col, k, 1, 1, 1, 0)
+            x = ctx.x
+            n, _, h, w = x.shape
             dy = _cl(dy)
-            dw192 = torch.empty((d.k, STEM_K), dtype=torch.float32, device=col.device)
-            need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
-            scratch = torch.empty(need, dtype=torch.uint8, device=col.device)
-            call("iit_conv2d_wgrad_tc", _p(dy), _p(col), _p(dw192), C.byref(d), _p(scratch), need, _stream())
-            dw = dw192[:, :147].reshape(d.k, 7, 7, 3).permute(0, 3, 1, 2)
+            sh, sw = (h + 6) // 2, (w + 6) // 2
+            need = int(_lib.lib.iit_stem_wgrad_s2d_scratch_bytes(n, sh, sw)) if (h % 2 == 0 and w % 2 == 0 and weight.shape[0] == 64) else 0
+            if need:   # shifted-window kernel on the space-to-depth image (already built for the forward)
+                s2d = stem_s2d_cached(x)
+                dw = torch.empty_like(weight, memory_format=torch.preserve_format)
+                scratch = torch.empty(need, dtype=torch.uint8, device=x.device)
+                strides = (C.c_int64 * 4)(*dw.stride())
+                call("iit_stem_wgrad_s2d", _p(dy), _p(s2d), _p(dw), strides, n, sh, sw, _p(scratch), need, _stream())
+            else:      # im2col (built once per batch) + the 1x1 wgrad kernel with 192 channels
+                col = stem_cols(x)
+                k = weight.shape[0]
+                d = _conv_desc(col, k, 1, 1, 1, 0)
+                dw192 = torch.empty((d.k, STEM_K), dtype=torch.float32, device=col.device)
+                need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
+                scratch = torch.empty(need, dtype=torch.uint8, device=col.device)
+                call("iit_conv2d_wgrad_tc", _p(dy), _p(col), _p(dw192), C.byref(d), _p(scratch), need, _stream())
+                dw = dw192[:, :147].reshape(d.k, 7, 7, 3).permute(0, 3, 1, 2)
         return None, dw, None, None
 
 

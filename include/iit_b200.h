@@ -183,6 +183,13 @@ int iit_stem_s2d(const void* x, int dtype, const int64_t* strides_nchw, void* s2
 int iit_stem_filter_s2d(const float* w, const int64_t* strides_kcrs, void* w2, void* stream);
 int iit_stem_conv_s2d(const void* s2d, const void* w2, void* y, int n, int sh, int sw, double* bn_sum,
                       double* bn_sqsum, void* stream);
+/*   iit_stem_wgrad_s2d: dw [64,3,7,7] fp32 (strides given, e.g. the parameter's channels-last strides) from
+ *                      dy [n,sh-3,sw-3,64] bf16 and the s2d image, on the shifted-window tcgen05 kernel; scratch
+ *                      (iit_stem_wgrad_s2d_scratch_bytes, 0 = this image size is not supported: s2d width > 32)
+ *                      holds one partial sum per CTA, reduced in fixed order. */
+size_t iit_stem_wgrad_s2d_scratch_bytes(int n, int sh, int sw);
+int iit_stem_wgrad_s2d(const void* dy, const void* s2d, float* dw, const int64_t* dw_strides_kcrs, int n, int sh,
+                       int sw, void* scratch, size_t scratch_bytes, void* stream);
 /* dw[k,r,s,c] fp32: pixels are the GEMM K dimension (MN-major operands straight from NHWC), split across
  * CTAs; scratch holds the per-split partial sums (iit_conv2d_wgrad_tc_scratch_bytes), reduced in fixed order. */
 size_t iit_conv2d_wgrad_tc_scratch_bytes(const iit_conv_t* d);

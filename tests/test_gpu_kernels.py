@@ -476,7 +476,7 @@ def test_tensor_core_path_is_taken_and_matches_cuda_core_path(ops):
 @pytest.mark.parametrize("hw,layout", [(56, "nchw_f32"), (84, "nchw_f32"), (56, "cl_bf16")])
 def test_stem_tensor_core_path(ops, hw, layout):
     """7x7/2 stem through the Conv2d module: forward = space-to-depth + shifted-window tcgen05 convolution, weight
-    gradient = im2col (from the caller's own tensor layout/dtype) + tcgen05 1x1 wgrad with 192 channels."""
+    gradient = shifted-window kernel on the same image (56 px) or im2col + tcgen05 1x1 wgrad with 192 channels (84 px)."""
     from iit_b200.nn.resnet import Conv2d
     g = torch.Generator().manual_seed(12)
     n = 6
@@ -500,7 +500,11 @@ def test_stem_tensor_core_path(ops, hw, layout):
         yd.backward(gy.to(DEV).bfloat16())
     finally:
         ops.call = inner
-    assert "iit_stem_s2d" in seen and "iit_stem_conv_s2d" in seen and "iit_stem_im2col" in seen and "iit_conv2d_wgrad_tc" in seen
+    assert "iit_stem_s2d" in seen and "iit_stem_conv_s2d" in seen
+    if hw <= 58:
+        assert "iit_stem_wgrad_s2d" in seen and "iit_stem_im2col" not in seen
+    else:
+        assert "iit_stem_im2col" in seen and "iit_conv2d_wgrad_tc" in seen
     assert "iit_conv2d_fprop" not in seen and "iit_conv2d_wgrad" not in seen
     for a, b, what in ((yd.float().cpu(), y.detach(), "fprop"), (conv.weight.grad.cpu(), w.grad, "wgrad")):
         scale = b.abs().max().item()
@@ -618,3 +622,18 @@ def test_stem_space_to_depth_conv_matches_conv2d(ops, n, hw):
     yb = y.double()
     torch.testing.assert_close(sums[0].cpu(), yb.sum((0, 1, 2)).cpu(), rtol=1e-5, atol=1e-3)
     torch.testing.assert_close(sums[1].cpu(), (yb * yb).sum((0, 1, 2)).cpu(), rtol=1e-5, atol=1e-3)
+    # weight gradient on the same raster (s2d width <= 32, i.e. images up to 58 pixels; wider ones use im2col)
+    need = int(_lib.lib.iit_stem_wgrad_s2d_scratch_bytes(n, sh, sh))
+    if hw <= 58:
+        assert need > 0
+        gy = torch.randn(n, hw // 2, hw // 2, 64, generator=g).bfloat16()
+        gyd = gy.to(DEV)
+        scratch = torch.full((need,), 0x7f, dtype=torch.uint8, device=DEV)
+        dw = torch.full((64, 3, 7, 7), 7.0, device=DEV).contiguous(memory_format=torch.channels_last)
+        _lib.call("iit_stem_wgrad_s2d", p(gyd), p(s2d), p(dw), (C.c_int64 * 4)(*dw.stride()), n, sh, sh, p(scratch), need, st)
+        wr = w.bfloat16().float().requires_grad_(True)
+        F.conv2d(x.bfloat16().float(), wr, stride=2, padding=3).backward(gy.float().permute(0, 3, 1, 2))
+        err = (dw.cpu() - wr.grad).abs().max().item()
+        assert err <= 1e-3 * wr.grad.abs().max().item(), (err, wr.grad.abs().max().item())
+    else:
+        assert need == 0
