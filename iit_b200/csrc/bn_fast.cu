@@ -10,6 +10,8 @@
 //     the normalised activation from the conv output instead of reading stored intermediates.
 // layers.cu's entry points call the *_fast launchers when `bn_fast_ok` holds and keep their generic
 // kernels otherwise.
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace iit {
@@ -222,12 +224,18 @@ __global__ void __launch_bounds__(256) bn_relu_pool_fwd_kernel(const T* __restri
   float sgn[NP];
 #pragma unroll
   for (int j = 0; j < NP; ++j) sgn[j] = (is[j] * g[j] < 0.f) ? -1.f : 1.f;
+  uint32_t sgn2[NP / 2];     // the same as packed bf16 pairs (0x3f80 = 1, 0xbf80 = -1)
+#pragma unroll
+  for (int j = 0; j < NP / 2; ++j)
+    sgn2[j] = (sgn[2 * j] < 0.f ? 0xbf80u : 0x3f80u) | ((sgn[2 * j + 1] < 0.f ? 0xbf80u : 0x3f80u) << 16);
   const uint32_t total = (uint32_t)N * P * Q;            // 32-bit index arithmetic: 64-bit divisions cost ~100 instructions
-  for (uint32_t pix = blockIdx.x * PXB + px; pix < total; pix += gridDim.x * PXB) {
-    const int q = (int)(pix % Q);
-    const uint32_t t2 = pix / Q;
-    const int p = (int)(t2 % P);
-    const int n = (int)(t2 / P);
+  // (n, p, q) follows pix incrementally: a division costs more than the rest of the index arithmetic together
+  const uint32_t stride = gridDim.x * PXB, first = blockIdx.x * PXB + px;
+  const int sq = (int)(stride % Q), sp = (int)((stride / Q) % P), sn = (int)(stride / ((uint32_t)Q * P));
+  int q = (int)(first % Q), p = (int)((first / Q) % P), n = (int)(first / ((uint32_t)Q * P));
+  for (uint32_t pix = first; pix < total; pix += stride, q += sq, p += sp, n += sn) {
+    if (q >= Q) { q -= Q; ++p; }
+    if (p >= P) { p -= P; ++n; }
     // all nine window loads are issued before any is used (clamped addresses, validity applied afterwards):
     // one memory round trip per pooled pixel instead of nine dependent ones
     uint4 raw[9];
@@ -249,29 +257,72 @@ __global__ void __launch_bounds__(256) bn_relu_pool_fwd_kernel(const T* __restri
     // compare per element; the affine map, ReLU and rounding are applied to the nine winners only. The pooled value
     // is bit-identical to pooling the rounded activations; among activations that tie after ReLU / rounding the
     // winner is the one with the largest pre-rounding value (the fp32 reference's choice).
-    float best[NP], bkey[NP];
-    int bi[NP];
+    float best[NP];
+    uint32_t ipk[NP / 4];      // the winners' window slots, one byte per channel
+    if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+      // two channels per instruction on packed bf16: key = raw * (+-1), running maximum with HMNMX2, then the first
+      // tap equal to the maximum (scanning backwards so that the earliest one is kept)
+      const uint32_t NEG_INF2 = 0xff80ff80u;
+      uint32_t key[9][4], best2[4] = {NEG_INF2, NEG_INF2, NEG_INF2, NEG_INF2};
 #pragma unroll
-    for (int j = 0; j < NP; ++j) { bkey[j] = -INFINITY; bi[j] = 0; }
+      for (int t = 0; t < 9; ++t) {
+        const uint32_t w4[4] = {raw[t].x, raw[t].y, raw[t].z, raw[t].w};
 #pragma unroll
-    for (int t = 0; t < 9; ++t) {
-      float v[NP];
-      Pack<T>::unpack(raw[t], v);
-#pragma unroll
-      for (int j = 0; j < NP; ++j) {
-        const float key = v[j] * sgn[j];
-        const bool take = valid[t] & !(key <= bkey[j]);   // unordered compare: a NaN is taken and then kept
-        bkey[j] = take ? key : bkey[j];
-        bi[j] = take ? t : bi[j];
+        for (int w = 0; w < 4; ++w) {
+          __nv_bfloat162 k2 = __hmul2(*reinterpret_cast<const __nv_bfloat162*>(&w4[w]), *reinterpret_cast<const __nv_bfloat162*>(&sgn2[w]));
+          uint32_t kb = *reinterpret_cast<uint32_t*>(&k2);
+          kb = valid[t] ? kb : NEG_INF2;
+          key[t][w] = kb;
+          __nv_bfloat162 m2 = __hmax2_nan(*reinterpret_cast<__nv_bfloat162*>(&best2[w]), *reinterpret_cast<__nv_bfloat162*>(&kb));
+          best2[w] = *reinterpret_cast<uint32_t*>(&m2);
+        }
       }
+      uint32_t idx2[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+      for (int t = 8; t >= 0; --t) {
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+          const uint32_t m = __heq2_mask(*reinterpret_cast<__nv_bfloat162*>(&key[t][w]), *reinterpret_cast<__nv_bfloat162*>(&best2[w]));
+          idx2[w] = (idx2[w] & ~m) | ((uint32_t)(t | (t << 16)) & m);
+        }
+      }
+      ipk[0] = __byte_perm(idx2[0], idx2[1], 0x6420);
+      ipk[1] = __byte_perm(idx2[2], idx2[3], 0x6420);
+#pragma unroll
+      for (int w = 0; w < 4; ++w) {
+        __nv_bfloat162 v2 = __hmul2(*reinterpret_cast<__nv_bfloat162*>(&best2[w]), *reinterpret_cast<const __nv_bfloat162*>(&sgn2[w]));
+        const uint32_t vb = *reinterpret_cast<uint32_t*>(&v2);
+        best[2 * w] = __uint_as_float(vb << 16);
+        best[2 * w + 1] = __uint_as_float(vb & 0xffff0000u);
+      }
+    } else {
+      float bkey[NP];
+      int bi[NP];
+#pragma unroll
+      for (int j = 0; j < NP; ++j) { bkey[j] = -INFINITY; bi[j] = 0; }
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        float v[NP];
+        Pack<T>::unpack(raw[t], v);
+#pragma unroll
+        for (int j = 0; j < NP; ++j) {
+          const float key = v[j] * sgn[j];
+          const bool take = valid[t] & !(key <= bkey[j]);   // unordered compare: a NaN is taken and then kept
+          bkey[j] = take ? key : bkey[j];
+          bi[j] = take ? t : bi[j];
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < NP; ++j) best[j] = bkey[j] * sgn[j];
+#pragma unroll
+      for (int j = 0; j < NP; j += 4) ipk[j / 4] = (uint32_t)bi[j] | ((uint32_t)bi[j + 1] << 8) | ((uint32_t)bi[j + 2] << 16) | ((uint32_t)bi[j + 3] << 24);
     }
 #pragma unroll
-    for (int j = 0; j < NP; ++j) best[j] = fmaxf((bkey[j] * sgn[j] - mu[j]) * is[j] * g[j] + b[j], 0.f);
+    for (int j = 0; j < NP; ++j) best[j] = fmaxf((best[j] - mu[j]) * is[j] * g[j] + b[j], 0.f);
     Pack<T>::store(y + (int64_t)pix * C + cp * NP, best);
-    int8_t* ip = idx + (int64_t)pix * C + cp * NP;
+    uint32_t* ip = reinterpret_cast<uint32_t*>(idx + (int64_t)pix * C + cp * NP);
 #pragma unroll
-    for (int j = 0; j < NP; j += 4)
-      *reinterpret_cast<char4*>(ip + j) = make_char4((char)bi[j], (char)bi[j + 1], (char)bi[j + 2], (char)bi[j + 3]);
+    for (int j = 0; j < NP / 4; ++j) ip[j] = ipk[j];
   }
 }
 
@@ -298,22 +349,45 @@ __device__ __forceinline__ void pool_bwd_gather(const T* __restrict__ dy, const 
 #pragma unroll
       for (int j = 0; j < NP / 4; ++j) kraw[t][j] = *reinterpret_cast<const uint32_t*>(idx + op + 4 * j);
     }
+  if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+    // four channels per compare (__vcmpeq4 on the slot bytes), two per masked packed add; an element is the winner of
+    // more than one window only occasionally, so the bf16 additions are mostly exact
+    uint32_t g2[4] = {0u, 0u, 0u, 0u};
 #pragma unroll
-  for (int j = 0; j < NP; ++j) g[j] = 0.f;
+    for (int t = 0; t < 4; ++t) {
+      const uint32_t s4 = (uint32_t)(slot[t] & 0xff) * 0x01010101u;
+      const uint32_t w4[4] = {raw[t].x, raw[t].y, raw[t].z, raw[t].w};
 #pragma unroll
-  for (int t = 0; t < 4; ++t) {
-    float d[NP];
-    Pack<T>::unpack(raw[t], d);
+      for (int hlf = 0; hlf < 2; ++hlf) {
+        const uint32_t m4 = __vcmpeq4(kraw[t][hlf], s4);
+        const uint32_t mlo = __byte_perm(m4, 0u, 0x1100), mhi = __byte_perm(m4, 0u, 0x3322);
+        uint32_t a = w4[2 * hlf] & mlo, b = w4[2 * hlf + 1] & mhi;
+        __nv_bfloat162 sa = __hadd2(*reinterpret_cast<__nv_bfloat162*>(&g2[2 * hlf]), *reinterpret_cast<__nv_bfloat162*>(&a));
+        __nv_bfloat162 sb = __hadd2(*reinterpret_cast<__nv_bfloat162*>(&g2[2 * hlf + 1]), *reinterpret_cast<__nv_bfloat162*>(&b));
+        g2[2 * hlf] = *reinterpret_cast<uint32_t*>(&sa);
+        g2[2 * hlf + 1] = *reinterpret_cast<uint32_t*>(&sb);
+      }
+    }
 #pragma unroll
-    for (int j = 0; j < NP; ++j) {
-      const int k = (int)(int8_t)((kraw[t][j >> 2] >> (8 * (j & 3))) & 0xff);
-      if (k == slot[t]) g[j] += d[j];
+    for (int w = 0; w < 4; ++w) { g[2 * w] = __uint_as_float(g2[w] << 16); g[2 * w + 1] = __uint_as_float(g2[w] & 0xffff0000u); }
+  } else {
+#pragma unroll
+    for (int j = 0; j < NP; ++j) g[j] = 0.f;
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      float d[NP];
+      Pack<T>::unpack(raw[t], d);
+#pragma unroll
+      for (int j = 0; j < NP; ++j) {
+        const int k = (int)(int8_t)((kraw[t][j >> 2] >> (8 * (j & 3))) & 0xff);
+        if (k == slot[t]) g[j] += d[j];
+      }
     }
   }
 }
 
 template <typename T>
-__global__ void __launch_bounds__(256) bn_relu_pool_bwd_reduce_kernel(const T* __restrict__ dy, const int8_t* __restrict__ idx,
+__global__ void __launch_bounds__(256, 4) bn_relu_pool_bwd_reduce_kernel(const T* __restrict__ dy, const int8_t* __restrict__ idx,
                                                                       const T* __restrict__ x, int N, int H, int W, int C, int P,
                                                                       int Q, int CGB, const float* __restrict__ mean,
                                                                       const float* __restrict__ invstd, const float* __restrict__ gamma,
@@ -328,10 +402,12 @@ __global__ void __launch_bounds__(256) bn_relu_pool_bwd_reduce_kernel(const T* _
 #pragma unroll
   for (int j = 0; j < NP; ++j) { acc[0][j] = 0.f; acc[1][j] = 0.f; }
   const uint32_t rows = (uint32_t)N * H * W;
-  for (uint32_t r = blockIdx.x * RL + rl; r < rows; r += gridDim.x * RL) {
-    const int w = (int)(r % W);
-    const uint32_t t2 = r / W;
-    const int h = (int)(t2 % H), n = (int)(t2 / H);
+  const uint32_t stride = gridDim.x * RL, first = blockIdx.x * RL + rl;
+  const int sw = (int)(stride % W), sh = (int)((stride / W) % H), sn = (int)(stride / ((uint32_t)W * H));
+  int w = (int)(first % W), h = (int)((first / W) % H), n = (int)(first / ((uint32_t)W * H));
+  for (uint32_t r = first; r < rows; r += stride, w += sw, h += sh, n += sn) {
+    if (w >= W) { w -= W; ++h; }
+    if (h >= H) { h -= H; ++n; }
     float g[NP], xv[NP];
     Pack<T>::load(x + (int64_t)r * C + c, xv);
     pool_bwd_gather<T>(dy, idx, n, h, w, c, C, P, Q, g);
@@ -347,7 +423,7 @@ __global__ void __launch_bounds__(256) bn_relu_pool_bwd_reduce_kernel(const T* _
 }
 
 template <typename T>
-__global__ void __launch_bounds__(256) bn_relu_pool_bwd_apply_kernel(const T* __restrict__ dy, const int8_t* __restrict__ idx,
+__global__ void __launch_bounds__(256, 4) bn_relu_pool_bwd_apply_kernel(const T* __restrict__ dy, const int8_t* __restrict__ idx,
                                                                      const T* __restrict__ x, T* __restrict__ dx, int N, int H, int W,
                                                                      int C, int P, int Q, float inv_rows,
                                                                      const float* __restrict__ mean, const float* __restrict__ invstd,
@@ -362,10 +438,12 @@ __global__ void __launch_bounds__(256) bn_relu_pool_bwd_apply_kernel(const T* __
 #pragma unroll
   for (int j = 0; j < NP; ++j) { dbn[j] = (float)dbeta[c + j] * inv_rows; dgn[j] = (float)dgamma[c + j] * inv_rows; }
   const uint32_t rows = (uint32_t)N * H * W;
-  for (uint32_t r = blockIdx.x * PXB + px; r < rows; r += gridDim.x * PXB) {
-    const int w = (int)(r % W);
-    const uint32_t t2 = r / W;
-    const int h = (int)(t2 % H), n = (int)(t2 / H);
+  const uint32_t stride = gridDim.x * PXB, first = blockIdx.x * PXB + px;
+  const int sw = (int)(stride % W), sh = (int)((stride / W) % H), sn = (int)(stride / ((uint32_t)W * H));
+  int w = (int)(first % W), h = (int)((first / W) % H), n = (int)(first / ((uint32_t)W * H));
+  for (uint32_t r = first; r < rows; r += stride, w += sw, h += sh, n += sn) {
+    if (w >= W) { w -= W; ++h; }
+    if (h >= H) { h -= H; ++n; }
     float g[NP], xv[NP], o[NP];
     Pack<T>::load(x + (int64_t)r * C + c, xv);
     pool_bwd_gather<T>(dy, idx, n, h, w, c, C, P, Q, g);
