@@ -45,7 +45,10 @@ struct TcParams {
 // working at the same time share the pixel box through L2). The shared-memory ring runs across tile boundaries, and
 // the accumulator is double-buffered in TMEM (2 x BN columns): while the epilogue warps drain tile i the MMA warp is
 // already accumulating tile i+1.
-template <int BN, int STAGES>
+// MT pixel boxes share one filter block per tile (MT = 2: 256 pixels x 128 filters). The kernel is bound by L2 -> shared
+// memory traffic (ncu: ~11 TB/s through the crossbar at 36-42 % tensor-pipe activity with 128 x 128 tiles); a filter block
+// that serves two pixel boxes cuts the bytes per FLOP by a quarter.
+template <int BN, int STAGES, int MT>
 __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_constant__ CUtensorMap map_a,
                                                                 const __grid_constant__ CUtensorMap map_b,
                                                                 __nv_bfloat16* __restrict__ out, TcParams p,
@@ -54,8 +57,8 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
   // SWIZZLE_128B operands need 1024-byte aligned tiles
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2, B_BYTES = BN * TC_BK * 2;
-  uint8_t* sA = smem;
-  uint8_t* sB = smem + STAGES * A_BYTES;
+  uint8_t* sA = smem;                         // [STAGES][MT] pixel boxes
+  uint8_t* sB = smem + STAGES * MT * A_BYTES;
   uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * B_BYTES);
   uint64_t* empty = full + STAGES;
   uint64_t* tmem_full = empty + STAGES;      // [2]
@@ -68,7 +71,8 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
   const int kchunks = p.Cin / TC_BK;
   const int nk = p.ntaps * kchunks;
   const int nblk = p.Cout / BN;
-  const int total_tiles = p.tiles_w * p.tiles_h * p.tiles_n * nblk;
+  const int mtiles = p.tiles_w * p.tiles_h * p.tiles_n;            // pixel boxes
+  const int total_tiles = ((mtiles + MT - 1) / MT) * nblk;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
@@ -76,7 +80,7 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {  // TMEM allocation is warp-collective; this warp also frees it
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(2 * BN));
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(2 * MT * BN));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -91,17 +95,24 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        int t = tile;
-        const int co0 = (t % nblk) * BN; t /= nblk;
-        const int tw = t % p.tiles_w; t /= p.tiles_w;
-        const int th = t % p.tiles_h; t /= p.tiles_h;
-        const int n0 = t * p.BNI, p0 = th * p.BH, q0 = tw * p.BW;
+        const int co0 = (tile % nblk) * BN;
+        int n0[MT], p0[MT], q0[MT];
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt) {
+          int t = (tile / nblk) * MT + mt;
+          if (t >= mtiles) t = mtiles - 1;            // odd tail: the box is loaded twice, its second copy never stored
+          const int tw = t % p.tiles_w; t /= p.tiles_w;
+          const int th = t % p.tiles_h; t /= p.tiles_h;
+          n0[mt] = t * p.BNI; p0[mt] = th * p.BH; q0[mt] = tw * p.BW;
+        }
         for (int kb = 0; kb < nk; ++kb) {
           const int tap = kb / kchunks, kc = kb - tap * kchunks;
           mbar_wait(&empty[stage], phase ^ 1);
-          mbar_expect_tx(&full[stage], A_BYTES + B_BYTES);
-          tma_load_4d(sA + stage * A_BYTES, &map_a, &full[stage], kc * TC_BK, q0 * p.in_mul + p.dw[tap],
-                      p0 * p.in_mul + p.dh[tap], n0);
+          mbar_expect_tx(&full[stage], MT * A_BYTES + B_BYTES);
+#pragma unroll
+          for (int mt = 0; mt < MT; ++mt)
+            tma_load_4d(sA + (stage * MT + mt) * A_BYTES, &map_a, &full[stage], kc * TC_BK, q0[mt] * p.in_mul + p.dw[tap],
+                        p0[mt] * p.in_mul + p.dh[tap], n0[mt]);
           tma_load_2d(sB + stage * B_BYTES, &map_b, &full[stage], p.wk[tap] * p.Cin + kc * TC_BK, co0);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -122,14 +133,17 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
         const uint32_t acc = it & 1, acc_phase = (it >> 1) & 1;
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);   // the epilogue has drained this accumulator
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t tmem_d = tmem_base + acc * BN;
+        const uint32_t tmem_d = tmem_base + acc * (MT * BN);
         for (int kb = 0; kb < nk; ++kb) {
           mbar_wait(&full[stage], phase);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          const uint32_t a_lo = a_lo0 + stage * (A_BYTES >> 4), b_lo = b_lo0 + stage * (B_BYTES >> 4);
+          const uint32_t a_lo = a_lo0 + stage * (MT * A_BYTES >> 4), b_lo = b_lo0 + stage * (B_BYTES >> 4);
 #pragma unroll
-          for (int k = 0; k < TC_BK / TC_UK; ++k)
-            umma_bf16_lohi(tmem_d, a_lo + 2 * k, desc_hi, b_lo + 2 * k, desc_hi, idesc, (uint32_t)((kb | k) != 0));
+          for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+            for (int k = 0; k < TC_BK / TC_UK; ++k)
+              umma_bf16_lohi(tmem_d + mt * BN, a_lo + mt * (A_BYTES >> 4) + 2 * k, desc_hi, b_lo + 2 * k, desc_hi, idesc,
+                             (uint32_t)((kb | k) != 0));
           umma_commit(&empty[stage]);  // frees this smem stage once the MMAs above have read it
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -148,28 +162,31 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
     int run_co = -1;
     uint32_t it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      int t = tile;
-      const int co0 = (t % nblk) * BN; t /= nblk;
-      const int tw = t % p.tiles_w; t /= p.tiles_w;
-      const int th = t % p.tiles_h; t /= p.tiles_h;
-      const int n = t * p.BNI + nl, pp = th * p.BH + hl, qq = tw * p.BW + wl;
-      const bool ok = n < p.N && pp < p.P && qq < p.Q;
-      __nv_bfloat16* dst = out + (((int64_t)n * p.OH + (pp * p.out_mul + p.out_oh)) * p.OW + (qq * p.out_mul + p.out_ow)) * p.Cout + co0;
+      const int co0 = (tile % nblk) * BN;
       const uint32_t acc = it & 1, acc_phase = (it >> 1) & 1;
       if (nk > 0) {
         mbar_wait(&tmem_full[acc], acc_phase);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       }
+#pragma unroll 1
+     for (int mt = 0; mt < MT; ++mt) {
+      int t = (tile / nblk) * MT + mt;
+      const bool box_ok = t < mtiles;
+      const int tw = t % p.tiles_w; t /= p.tiles_w;
+      const int th = t % p.tiles_h; t /= p.tiles_h;
+      const int n = t * p.BNI + nl, pp = th * p.BH + hl, qq = tw * p.BW + wl;
+      const bool ok = box_ok && n < p.N && pp < p.P && qq < p.Q;
+      __nv_bfloat16* dst = out + (((int64_t)n * p.OH + (pp * p.out_mul + p.out_oh)) * p.OW + (qq * p.out_mul + p.out_ow)) * p.Cout + co0;
 #pragma unroll
       for (int c = 0; c < BN; c += 32) {
         uint32_t v[32];
         if (nk > 0) {
-          tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c), v);
+          tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * (MT * BN) + mt * BN + c), v);
         } else {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = 0u;
         }
-        if (c + 32 >= BN && nk > 0) {
+        if (c + 32 >= BN && mt == MT - 1 && nk > 0) {
           // all of this warp's TMEM reads of the accumulator are complete: hand it back to the MMA warp
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
           __syncwarp();
@@ -213,6 +230,7 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
           atomicAdd(&s_stat[BN + c + lane], b[0]);
         }
       }
+     }  // mt
       if (bn_sum != nullptr) {
         asm volatile("bar.sync 1, 128;" ::: "memory");   // the four epilogue warps only: the tile's sums are complete
         if (e < BN) {
@@ -234,29 +252,31 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
   __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * BN));
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * MT * BN));
   }
 }
 
 // ---- host side -----------------------------------------------------------------------------------
+static bool g_tile_pairs = true;
+
 static int pow2_ge(int v) { int r = 1; while (r < v) r <<= 1; return r; }
 
-template <int BN>
+template <int BN, int MT>
 static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16* out, const TcParams& p, int total_tiles,
                      cudaStream_t st, double* bn_sum, double* bn_sq) {
   constexpr int STAGES = 4;
-  constexpr size_t smem = STAGES * (TC_BM * TC_BK * 2 + BN * TC_BK * 2) + (2 * STAGES + 4) * 8 + 16 + 2 * BN * 4 + 1024;
+  constexpr size_t smem = STAGES * (MT * TC_BM * TC_BK * 2 + BN * TC_BK * 2) + (2 * STAGES + 4) * 8 + 16 + 2 * BN * 4 + 1024;
   static int ctas_per_sm = 0;
   if (!ctas_per_sm) {
-    IIT_CUDA(cudaFuncSetAttribute(conv3x3_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    IIT_CUDA(cudaFuncSetAttribute(conv3x3_tc_kernel<BN, STAGES, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int occ = 0;
-    IIT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv3x3_tc_kernel<BN, STAGES>, TC_THREADS, smem));
-    const int tmem_limit = 512 / (2 * BN);   // every resident CTA holds 2*BN TMEM columns for its whole life
+    IIT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv3x3_tc_kernel<BN, STAGES, MT>, TC_THREADS, smem));
+    const int tmem_limit = 512 / (2 * MT * BN);   // every resident CTA holds 2*MT*BN TMEM columns for its whole life
     ctas_per_sm = occ < 1 ? 1 : (occ > tmem_limit ? tmem_limit : occ);
   }
   int grid = kNumSMs * ctas_per_sm;
   if (grid > total_tiles) grid = total_tiles;
-  conv3x3_tc_kernel<BN, STAGES><<<grid, TC_THREADS, smem, st>>>(ma, mb, out, p, bn_sum, bn_sq);
+  conv3x3_tc_kernel<BN, STAGES, MT><<<grid, TC_THREADS, smem, st>>>(ma, mb, out, p, bn_sum, bn_sq);
   return 0;
 }
 
@@ -308,10 +328,14 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
   CUtensorMap ma, mb;
   if (encode_nhwc_strided(&ma, gathered, gC, gW, gH, tp.N, tp.BW, tp.BH, tp.BNI, tp.in_mul, name)) return 1;
   if (encode_filter(&mb, wmat, Kg, tp.Cout, BN, name)) return 1;
-  const int64_t total = (int64_t)tp.tiles_w * tp.tiles_h * tp.tiles_n * (tp.Cout / BN);
+  const int64_t mtiles = (int64_t)tp.tiles_w * tp.tiles_h * tp.tiles_n;
+  // two pixel boxes per filter block whenever that still leaves a tile for every SM
+  const int MT = (BN == 128 && g_tile_pairs && ((mtiles + 1) / 2) * (tp.Cout / BN) >= kNumSMs) ? 2 : 1;
+  const int64_t total = ((mtiles + MT - 1) / MT) * (tp.Cout / BN);
   IIT_REQUIRE(total < (1ll << 31), "%s: too many tiles", name);
-  int rc = BN == 128 ? launch_tc<128>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq)
-                     : launch_tc<64>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq);
+  int rc = BN == 128 ? (MT == 2 ? launch_tc<128, 2>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq)
+                                : launch_tc<128, 1>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq))
+                     : launch_tc<64, 1>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq);
   if (rc) return rc;
   IIT_LAUNCH_CHECK(name);
   return 0;
