@@ -91,6 +91,9 @@ SIGNATURES = {
     "iit_stem_conv_s2d": [_vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp],
     "iit_stem_wgrad_s2d_scratch_bytes": [_i, _i, _i],
     "iit_stem_wgrad_s2d": [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, C.c_size_t, _vp],
+    "iit_gather_rows": [_vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp],
+    "iit_gather_box": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i64, _vp, _vp],
+    "iit_pick_other_class": [_vp, _vp, _i, _i64, C.c_uint64, _i64, _vp, _vp, _vp, _vp],
     "iit_sqnorm": [_vp, _i64, _vp, _vp],
     "iit_adam_step": [_vp, _vp, _vp, _vp, _i64, _d, _d, _d, _d, _i64, _vp, _d, _vp],
     "iit_adam_step_dev": [_vp, _vp, _vp, _vp, _i64, _vp, _d, _d, _d, _vp, _vp, _d, _vp],

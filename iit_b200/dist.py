@@ -65,6 +65,15 @@ class DataParallel:
             dist.all_reduce(counts, op=dist.ReduceOp.SUM, group=self.group)
         return counts
 
+    def allgather_counts(self, counts: torch.Tensor) -> torch.Tensor:
+        """[entries, batches, 2] per rank -> [entries, world * batches, 2]: the sweep keeps per-batch counts because the
+        reference averages per-batch ratios (eval_causality.py:85-88)."""
+        if self.world == 1:
+            return counts
+        parts = [torch.empty_like(counts) for _ in range(self.world)]
+        dist.all_gather(parts, counts.contiguous(), group=self.group)
+        return torch.cat(parts, dim=1)
+
     def max_over_ranks(self, seconds: float, device) -> float:
         t = torch.tensor([seconds], dtype=torch.float64, device=device)
         if self.world > 1:

@@ -73,6 +73,10 @@ def _as_filter(names_filter: NamesFilter):
     return lambda name: name in wanted
 
 
+class _StopForward(Exception):
+    """Raised by run_with_cache(stop_when_cached=True) from the last wanted hook point."""
+
+
 class HookedRootModule(nn.Module):
     """Root of a hooked model. Call `setup()` at the end of __init__."""
 
@@ -145,8 +149,24 @@ class HookedRootModule(nn.Module):
         return cache, [(n, save_hook) for n in self.hook_dict if flt(n)], []
 
     def run_with_cache(self, *model_args, names_filter: NamesFilter = None, device=None, remove_batch_dim=False,
-                       incl_bwd=False, reset_hooks_end=True, clear_contexts=False, **model_kwargs):
+                       incl_bwd=False, reset_hooks_end=True, clear_contexts=False, stop_when_cached=False, **model_kwargs):
+        """`stop_when_cached` (not in transformer_lens): with an explicit list of names, abandon the forward pass once
+        every listed hook point has been cached; the returned output is then None. Only meaningful when the rest of
+        the pass has no side effect the caller wants (eval mode: no BatchNorm statistics to update)."""
         cache, fwd, bwd = self.get_caching_hooks(names_filter, incl_bwd, device, remove_batch_dim)
+        if stop_when_cached:
+            if names_filter is None or callable(names_filter):
+                raise ValueError("stop_when_cached needs an explicit list of hook-point names")
+            wanted = {names_filter} if isinstance(names_filter, str) else set(names_filter)
+
+            def stop_hook(tensor, hook):
+                if wanted.issubset(cache.keys()):
+                    raise _StopForward()
+
+            fwd = fwd + [(n, stop_hook) for n in wanted]
         with self.hooks(fwd_hooks=fwd, bwd_hooks=bwd, reset_hooks_end=reset_hooks_end, clear_contexts=clear_contexts):
-            out = self(*model_args, **model_kwargs)
+            try:
+                out = self(*model_args, **model_kwargs)
+            except _StopForward:
+                out = None
         return out, cache

@@ -71,8 +71,14 @@ class BaseModelPair(ABC):
         """Source (ablation) forward of the LL model; caches the hook points of `ll_nodes` only.
         Train-mode side effects (BatchNorm running statistics) happen exactly as in a full forward."""
         names = list({n.name for n in ll_nodes})
+        # in eval mode nothing after the last cached hook point matters (no BatchNorm statistics move): the sweep
+        # sets `stop_source_run_at_hook` and saves that part of the source forward
+        stop = bool(getattr(self, "stop_source_run_at_hook", False)) and not self.ll_model.training
         with t.no_grad():
-            out, cache = self.ll_model.run_with_cache(ablation_x, names_filter=names)
+            if stop:
+                out, cache = self.ll_model.run_with_cache(ablation_x, names_filter=names, stop_when_cached=True)
+            else:
+                out, cache = self.ll_model.run_with_cache(ablation_x, names_filter=names)
         self.ll_cache = cache
         return out
 

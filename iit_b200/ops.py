@@ -947,6 +947,69 @@ def embed(tokens, W_E, W_pos, dtype):
 
 
 # =================================================================================================
+# either side of the step: batches of pairs, counterfactual inputs
+# =================================================================================================
+_err_flags: dict = {}
+
+
+def _err_flag(device) -> torch.Tensor:
+    dev = torch.device(device)
+    if dev.type == "cuda" and dev.index is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+    f = _err_flags.get(dev)
+    if f is None:
+        f = _err_flags[dev] = torch.zeros(1, dtype=torch.int32, device=dev)
+    return f
+
+
+def raise_on_index_error(device="cuda"):
+    """Synchronising check of the out-of-range flag the gather kernels set instead of faulting."""
+    f = _err_flag(device)
+    if int(f.item()):
+        f.zero_()
+        raise IndexError("a gather kernel was given an index outside its source tensor")
+
+
+def gather_rows(src: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    """src[idx] along dim 0 for a dense `src` (any trailing shape) and int64 `idx`, as one coalesced gather."""
+    _require_cuda(src, idx)
+    if not src.is_contiguous():
+        raise ValueError("gather_rows: source must be dense (contiguous)")
+    if idx.dtype != torch.int64 or idx.dim() != 1:
+        raise ValueError("gather_rows: idx must be a 1-D int64 tensor")
+    out = torch.empty((idx.shape[0],) + tuple(src.shape[1:]), dtype=src.dtype, device=src.device)
+    row_bytes = (src.numel() // max(src.shape[0], 1)) * src.element_size()
+    if idx.shape[0] and row_bytes:
+        call("iit_gather_rows", _p(out), _p(src), _p(idx.contiguous()), idx.shape[0], row_bytes, src.shape[0],
+             _p(_err_flag(src.device)), _stream())
+    return out
+
+
+def gather_box_(dst: torch.Tensor, bank: torch.Tensor, idx: torch.Tensor, r0: int, c0: int) -> torch.Tensor:
+    """In place: dst[b, :, r0:r0+h, c0:c0+w] = bank[idx[b]] for bank [items, C, h, w] (dense)."""
+    _require_cuda(dst, bank, idx)
+    n, c, hh, ww = dst.shape
+    items, cb, h, w = bank.shape
+    if cb != c or dst.dtype != bank.dtype or not bank.is_contiguous() or r0 + h > hh or c0 + w > ww or idx.shape[0] != n:
+        raise ValueError("gather_box_: shape / dtype mismatch")
+    strides = (C.c_int64 * 4)(*dst.stride())
+    call("iit_gather_box", _p(dst), strides, _p(bank), _p(idx.contiguous()), _dt(dst), n, c, h, w, int(r0), int(c0), items,
+         _p(_err_flag(dst.device)), _stream())
+    return dst
+
+
+def pick_other_class(cur_class: torch.Tensor, class_start: torch.Tensor, bank_items: int, seed: int):
+    """(bank index, its label) per sample, uniform over the bank items of every class but cur_class[b]."""
+    _require_cuda(cur_class, class_start)
+    n = cur_class.shape[0]
+    out_idx = torch.empty(n, dtype=torch.int64, device=cur_class.device)
+    out_lab = torch.empty(n, dtype=torch.int64, device=cur_class.device)
+    call("iit_pick_other_class", _p(cur_class.contiguous()), _p(class_start), class_start.numel() - 1, int(bank_items),
+         C.c_uint64(seed & 0xFFFFFFFFFFFFFFFF), n, _p(out_idx), _p(out_lab), _p(_err_flag(cur_class.device)), _stream())
+    return out_idx, out_lab
+
+
+# =================================================================================================
 # optimiser pieces
 # =================================================================================================
 def sqnorm_(g_flat: torch.Tensor, out: torch.Tensor):

@@ -56,6 +56,64 @@ class IITDataset(Dataset):
                           collate_fn=lambda x: self.collate_fn(x, self.device))
 
 
+class DeviceIITDataset(IITDataset):
+    """IITDataset over datasets that live on the GPU as stacked tensors: `base_data` / `ablation_data` are
+    `(x, y, intermediate_vars)` tuples of device tensors with one row per sample.
+
+    What stays exactly as in the reference: item `i` pairs base/ablation rows drawn from
+    `default_rng(seed * 1_000_000 + i)` (two `choice` calls, iit_dataset.py:33-35), and `make_loader` walks the items in
+    the order torch's own `DataLoader(shuffle=True)` produces from the global RNG (the loader below IS a DataLoader, over
+    item numbers). What changes: the pair table is computed once, and a batch is built by one gather kernel per field
+    (ops.gather_rows) instead of per-sample indexing, stacking and `.to(device)` (iit_dataset.py:47-59)."""
+
+    def __init__(self, base_data, ablation_data, seed=0, every_combination=False, device=None):
+        super().__init__(base_data, ablation_data, seed, every_combination, device)
+        for name, d in (("base_data", base_data), ("ablation_data", ablation_data)):
+            if not (isinstance(d, (tuple, list)) and len(d) == 3 and all(isinstance(t, torch.Tensor) for t in d)):
+                raise TypeError(f"{name} must be an (x, y, intermediate_vars) tuple of stacked tensors")
+        self._n_base, self._n_abl = int(base_data[0].shape[0]), int(ablation_data[0].shape[0])
+        self._table = None
+
+    def __len__(self):
+        return self._n_base * self._n_abl if self.every_combination else self._n_base
+
+    def pair_indices(self, index):
+        if self.every_combination:
+            return index // self._n_abl, index % self._n_abl
+        rng = np.random.default_rng(self.seed * 1000000 + index)
+        return int(rng.choice(self._n_base)), int(rng.choice(self._n_abl))
+
+    def pair_table(self) -> np.ndarray:
+        """[len, 2] int64: (base row, ablation row) of every item; computed once (the rule is per item, not per epoch)."""
+        if self._table is None:
+            n = len(self)
+            if self.every_combination:
+                i = np.arange(n, dtype=np.int64)
+                self._table = np.stack([i // self._n_abl, i % self._n_abl], axis=1)
+            else:
+                self._table = np.array([self.pair_indices(i) for i in range(n)], dtype=np.int64).reshape(n, 2)
+        return self._table
+
+    def __getitem__(self, index):
+        b, a = self.pair_indices(index)
+        return tuple(t[b] for t in self.base_data), tuple(t[a] for t in self.ablation_data)
+
+    def gather_batch(self, items):
+        """(base_input, ablation_input) for a list of item numbers: two index uploads, six gathers."""
+        from iit_b200 import ops
+        if not self.base_data[0].is_cuda:
+            raise RuntimeError("DeviceIITDataset batches are gathered by a CUDA kernel (no CPU fallback exists)")
+        rows = self.pair_table()[np.asarray(items, dtype=np.int64)]
+        dev = self.base_data[0].device
+        idx = torch.from_numpy(np.ascontiguousarray(rows.T)).to(dev, non_blocking=True)   # [2, B]
+        base = tuple(ops.gather_rows(t, idx[0]) for t in self.base_data)
+        abl = tuple(ops.gather_rows(t, idx[1]) for t in self.ablation_data)
+        return base, abl
+
+    def make_loader(self, batch_size, num_workers=0) -> DataLoader:
+        return DataLoader(range(len(self)), batch_size=batch_size, shuffle=True, num_workers=0, collate_fn=self.gather_batch)
+
+
 def train_test_split(dataset, test_size=0.2, random_state=None):
     n = len(dataset)
     split = int(n * test_size)

@@ -262,6 +262,25 @@ int iit_linear_bwd(const float* x, const float* w, const float* dy, float* dx, f
                    int n, int in, int out, void* stream);
 
 /* ------------------------------------------------------------------------------------------ */
+/* Either side of the step: batches of pairs and counterfactual inputs.  */
+/* err_flag: device int the kernels set to non-zero on an out-of-range index (the wrapper checks it). */
+/* ------------------------------------------------------------------------------------------ */
+/* dst[b, :] = src[idx[b], :], rows of row_bytes bytes: the collate step of IITDataset
+ * (iit/utils/iit_dataset.py:24-59) over a device-resident dataset. */
+int iit_gather_rows(void* dst, const void* src, const int64_t* idx, int64_t rows, int64_t row_bytes,
+                    int64_t src_rows, int* err_flag, void* stream);
+/* dst[b, :, r0:r0+h, c0:c0+w] = bank[idx[b]] (bank: [items, c, h, w] dense; dst: given NCHW strides): the
+ * quadrant swap of MNIST_PVR_Dataset.patch_at_hl_idx (iit/tasks/mnist_pvr/dataset.py:125-155). */
+int iit_gather_box(void* dst, const int64_t* dst_strides_nchw, const void* bank, const int64_t* idx, int dtype,
+                   int n, int c, int h, int w, int r0, int c0, int64_t bank_items, int* err_flag, void* stream);
+/* For each sample, a uniform draw among the bank items whose label differs from cur_class[b] (the bank is sorted
+ * by label; class_start has n_classes + 1 entries): the rejection loop of dataset.py:137-149 in one pass.
+ * Counter-based generator (splitmix64 of seed and b): reproducible, not the reference's numpy stream. */
+int iit_pick_other_class(const int64_t* cur_class, const int64_t* class_start, int n_classes, int64_t bank_items,
+                         uint64_t seed, int64_t n, int64_t* out_idx, int64_t* out_label, int* err_flag,
+                         void* stream);
+
+/* ------------------------------------------------------------------------------------------ */
 /* (b) low-level HookedTransformer (train_ioi.py:30-34; transformer_lens 1.12.1 semantics):        */
 /* everything but the dense contractions, which run on the convolution GEMMs above (a linear layer  */
 /* over tokens is a 1x1 convolution with n = tokens, h = w = 1).                                    */

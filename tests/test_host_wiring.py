@@ -137,3 +137,61 @@ def test_dry_run_pvr_train_and_eval_steps():
         hl_o, ll_o = pair.do_intervention(base, src, "hook_tr")
         assert hl_o.shape == (4,) and ll_o.shape == (4, 10)
     assert "iit_patch_fwd" in calls and "iit_conv2d_wgrad" in calls and "iit_hl_pvr" in calls
+
+
+def test_device_dataset_pair_rule_and_loader_order_on_the_host():
+    """Host logic of DeviceIITDataset (the gather itself needs a GPU): the pair table follows the reference's per-item
+    rule (iit_dataset.py:33-35) and the loader walks the items in DataLoader(shuffle=True)'s own order."""
+    from iit_b200.utils.iit_dataset import DeviceIITDataset, IITDataset
+    x, y, v = torch.arange(40.).view(20, 2), torch.arange(20), torch.arange(80).view(20, 4)
+    ds = DeviceIITDataset((x, y, v), (x[:7], y[:7], v[:7]), seed=3)
+    rule = []
+    for i in range(len(ds)):
+        rng = np.random.default_rng(3 * 1000000 + i)
+        rule.append([int(rng.choice(20)), int(rng.choice(7))])
+    assert ds.pair_table().tolist() == rule
+    samples = [(x[i], y[i], v[i]) for i in range(20)]
+    ref = IITDataset(samples, samples[:7], seed=3, device="cpu")
+    seen = []
+    ds.gather_batch = lambda items: seen.append(list(items)) or items
+    torch.manual_seed(5)
+    order = [i for b in ds.make_loader(6, 0) for i in b]
+    torch.manual_seed(5)
+    want = []
+    for base, abl in ref.make_loader(6, 0):
+        want += base[1].tolist()            # y of the base sample == its row number
+    assert [rule[i][0] for i in order] == want
+    with pytest.raises(RuntimeError):
+        DeviceIITDataset((x, y, v), (x, y, v)).gather_batch([0, 1])
+
+
+def _gather_worker(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from iit_b200.dist import DataParallel
+        dp = DataParallel()
+        c = torch.full((3, 2, 2), rank + 1, dtype=torch.int64)
+        out = dp.allgather_counts(c)
+        q.put((rank, out.shape, out[:, :, 0].tolist()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sweep_counts_allgather_world2_gloo():
+    """The sweep keeps per-batch counts; ranks concatenate theirs along the batch axis (gloo, world size 2)."""
+    import socket
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_gather_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, shape, col in res:
+        assert tuple(shape) == (3, 4, 2) and col == [[1, 1, 2, 2]] * 3
