@@ -41,6 +41,16 @@ def peaks():
     return {"hbm_gbs": 6650.0, "tflops": 1400.0, "src": "fallback"}
 
 
+def ncu_traffic(entry_point):
+    """Average DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of the kernels behind `entry_point`,
+    from the committed `ncu --set full` capture of this same command (profiles/ncu_traffic.json); None if not captured."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(path):
+        return None
+    ent = json.load(open(path)).get(entry_point)
+    return None if ent is None else ent.get("dram_bytes_per_launch")
+
+
 def workload_config(args, world):
     return {
         "workload": f"MNIST-PVR IIT+behaviour+strict train step, ResNet-18 LL, synthetic 56x56 4-digit grids, "
@@ -210,8 +220,75 @@ def conv_flops(call_args):
     return 0.0
 
 
+def _timed_region(dp, dev, fn, steps):
+    dp.barrier()
+    torch.cuda.synchronize()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(steps):
+        out = fn()
+    e.record()
+    torch.cuda.synchronize()
+    dp.barrier()
+    return dp.max_over_ranks(s.elapsed_time(e) * 1e-3, dev), out
+
+
+def run_ioi_extra(rank, world, dev, dp, batch=1024, steps=3, warmup=2):
+    """BASELINE.json configs[2]/[3]: IOI strict-IIT train step (small HookedTransformer LL, head-level interventions),
+    data-parallel with gradient all-reduce when world > 1. fp32 activations (the reference's dtype), integer labels,
+    last-position unembed (0.94 GFLOP / pair)."""
+    from iit_b200.model_pairs import IOI_ModelPair
+    from iit_b200.tasks.ioi import IOI_HL, corr, make_ll_model
+    from oracle import restate as R
+    torch.manual_seed(0)
+    ll = make_ll_model(device=dev)
+    (bx, by, bv), names = R.synthetic_ioi(batch, 21 + 2 * rank, one_hot=False)
+    (sx, sy, sv), _ = R.synthetic_ioi(batch, 22 + 2 * rank, one_hot=False)
+    hl = IOI_HL(50257, names).to(dev)
+    pair = IOI_ModelPair(hl, ll, corr, training_args={"lr": 1e-3, "batch_size": batch, "lr_scheduler": None})
+    if world > 1:
+        pair.dp = dp
+    opt = pair.make_optimizer()
+    ll.train()
+    base = tuple(t.to(dev) for t in (bx, by, bv))
+    src = tuple(t.to(dev) for t in (sx, sy, sv))
+    for _ in range(warmup):
+        pair.run_train_step(base, src, pair.loss_fn, opt)
+    sec, m = _timed_region(dp, dev, lambda: pair.run_train_step(base, src, pair.loss_fn, opt), steps)
+    return {"metric": "ioi_iit_train_pairs_per_sec", "value": batch * world * steps / sec, "unit": UNIT, "ms_per_step": 1e3 * sec / steps,
+            "config": {"workload": f"IOI strict-IIT train step (train_ioi.py), HookedTransformer 6L/4H/d64/d_mlp 3072/vocab 50257, "
+                                   f"batch {batch} prompts/GPU x 16 tokens, fp32, integer labels, last-position unembed",
+                       "baseline_config": "configs[2]" if world == 1 else "configs[3]", "parallelism": f"dp{world}"},
+            "steps": steps, "warmup": warmup, "dtype": "f32", "last_step_metrics": m}
+
+
+def run_sweep_extra(rank, world, dev, dp, batch=1024, batches_per_rank=2):
+    """BASELINE.json configs[4]: the causality sweep of eval_causality.py -- 17 hook points x 4 HL nodes, counterfactuals
+    generated on the device, batches sharded over ranks, counts gathered at the end. One "pair" = one (base,
+    counterfactual) interchange evaluation (two LL forwards, the source one truncated at the hook point)."""
+    from iit_b200 import eval_causality
+    from iit_b200.tasks.mnist_pvr.counterfactual import DigitBank
+    from iit_b200.tasks.mnist_pvr.get_alignment import get_alignment
+    from oracle import restate as R
+    ll, _, _ = get_alignment("mnist_pvr", {"input_shape": (1, 3, 56, 56)}, device=dev, dtype=torch.bfloat16)
+    ll.load_state_dict(R.resnet18_state_dict(0))
+    g = torch.Generator().manual_seed(5)
+    bank = DigitBank(torch.rand(2000, 1, 28, 28, generator=g).to(dev), torch.randint(0, 10, (2000,), generator=g).to(dev))
+    batches = [tuple(t.to(dev) for t in R.synthetic_pvr(batch, 300 + 10 * rank + i)) for i in range(batches_per_rank)]
+    args = {"batch_size": batch, "count_pairs": True}
+    eval_causality.evaluate_model_on_ablations(ll, "mnist_pvr", batches[:1], args, bank, dp=dp)      # warm-up
+    sec, stats = _timed_region(dp, dev, lambda: eval_causality.evaluate_model_on_ablations(ll, "mnist_pvr", batches, args, bank,
+                                                                                           dp=dp), 1)
+    pairs = stats.pop("_pairs") * world
+    return {"metric": "iia_eval_pairs_per_sec", "value": pairs / sec, "unit": UNIT, "seconds": sec, "pairs_evaluated": pairs,
+            "config": {"workload": f"causality sweep (eval_causality.py): 17 conv hook points x 4 HL nodes x {batches_per_rank} "
+                                   f"batches of {batch} pairs per GPU, ResNet-18 LL bf16 eval mode, device-side counterfactuals",
+                       "baseline_config": "configs[4]", "parallelism": f"dp{world}"},
+            "dtype": "bf16", "mean_stat": float(np.mean([v for d in stats.values() for v in d.values()]))}
+
+
 def run_ours(args, rank, world, local):
-    from iit_b200 import _lib, dist as idist
+    from iit_b200 import _lib, dist as idist, ops as ops_mod
     from iit_b200.model_pairs import StrictIITModelPair
     from iit_b200.tasks.mnist_pvr.get_alignment import get_alignment
     from oracle import restate as R  # synthetic pair generators only (shared with the CPU arm)
@@ -292,6 +369,18 @@ def run_ours(args, rank, world, local):
         launches = _lib.launch_count() - launches0
         pair.training_args["cuda_graphs"] = True
 
+    extras = {}
+    if args.extras:   # the other two metrics BASELINE.json names, measured briefly on every rank of the same job
+        del base_d, src_d, base_h, src_h
+        pair._graphs = {}
+        pair._static = None
+        ops_mod._batch_cache.clear()
+        torch.cuda.empty_cache()
+        for name, fn in (("iia_eval_sweep", run_sweep_extra), ("ioi_train", run_ioi_extra)):
+            try:
+                extras[name] = fn(rank, world, dev, dp)
+            except Exception as e:  # the headline line must survive a failure here; the failure is reported, not hidden
+                extras[name] = {"error": f"{type(e).__name__}: {e}"}
     if rank != 0:
         return
     pk = peaks()
@@ -301,7 +390,7 @@ def run_ours(args, rank, world, local):
         top = max(ks, key=lambda n: ks[n]["total_ms"])
         k = ks[top]
         roof = {"kernel": top, "bound": "tensor", "achieved": k["tflops"], "peak": pk["tflops"], "unit": "TFLOP/s",
-                "frac": k["tflops"] / pk["tflops"], "traffic": None, "peak_source": pk["src"] + " bf16 sustained",
+                "frac": k["tflops"] / pk["tflops"], "traffic": ncu_traffic(top), "peak_source": pk["src"] + " bf16 sustained",
                 "share_of_step": k["total_ms"] / ((sec_eager or sec) * 1e3), "launches": k["launches"], "avg_ms": k["avg_ms"],
                 "timed_in": "eager pass of the same steps (CUDA events around each launch)" if sec_eager else "timed region"}
     value = B * world * args.steps / sec
@@ -316,6 +405,8 @@ def run_ours(args, rank, world, local):
         "cuda_graphs": bool(args.graphs), "ms_per_step_eager": (1e3 * sec_eager / args.steps) if sec_eager else None,
         "last_step_metrics": metrics,
     }
+    if extras:
+        line["other_workloads"] = extras
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline()
     print(json.dumps(line), flush=True)
@@ -332,6 +423,7 @@ def main():
     ap.add_argument("--batch", type=int, default=4096)
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--extras", type=int, default=1, help="1: also time the IIA sweep and the IOI train step (other_workloads)")
     ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around the timed region")
     ap.add_argument("--graphs", type=int, default=1, help="1: replay each (loss term, node) variant from a CUDA graph")
     args = ap.parse_args()

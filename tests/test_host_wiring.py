@@ -174,13 +174,22 @@ def _gather_worker(rank, world, port, q):
         dp = DataParallel()
         c = torch.full((3, 2, 2), rank + 1, dtype=torch.int64)
         out = dp.allgather_counts(c)
-        q.put((rank, out.shape, out[:, :, 0].tolist()))
+        # gradient averaging before the clip (one all-reduce per step_on_loss) and the IIA count reduction
+        lin = torch.nn.Linear(3, 2)
+        for p_ in lin.parameters():
+            p_.grad = torch.full_like(p_, float(rank + 1))
+        dp.allreduce_grads(torch.optim.SGD(lin.parameters(), lr=0.1), lin)
+        grads = [p_.grad.flatten().tolist() for p_ in lin.parameters()]
+        counts = dp.allreduce_counts(torch.tensor([rank + 1, 10], dtype=torch.int64)).tolist()
+        shard = dp.shard((torch.arange(10), torch.arange(10) * 2))
+        q.put((rank, out.shape, out[:, :, 0].tolist(), grads, counts, [t_.tolist() for t_ in shard]))
     finally:
         dist.destroy_process_group()
 
 
-def test_sweep_counts_allgather_world2_gloo():
-    """The sweep keeps per-batch counts; ranks concatenate theirs along the batch axis (gloo, world size 2)."""
+def test_data_parallel_plumbing_world2_gloo():
+    """World size 2 over gloo: gradients are averaged (before the clip), IIA counts summed, global batches sharded
+    evenly, and the sweep's per-batch counts concatenated along the batch axis."""
     import socket
     import torch.multiprocessing as mp
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
@@ -193,5 +202,8 @@ def test_sweep_counts_allgather_world2_gloo():
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    for rank, shape, col in res:
+    for rank, shape, col, grads, counts, shard in res:
         assert tuple(shape) == (3, 4, 2) and col == [[1, 1, 2, 2]] * 3
+        assert all(g == [1.5] * len(g) for g in grads)          # mean of 1 and 2 on both ranks
+        assert counts == [3, 20]
+        assert shard == [list(range(rank * 5, rank * 5 + 5)), [2 * i for i in range(rank * 5, rank * 5 + 5)]]
