@@ -342,6 +342,14 @@ def run_ours(args, rank, world, local):
 
     for _ in range(args.warmup):
         step_resident()
+    if args.profile_forward:   # for `ncu --profile-from-start off`: one LL forward = exactly the fprop launches of a step
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        with torch.no_grad():
+            ll(base_d[0])
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        return
     sampler = ClockSampler(local)
     sampler.start()
     launches0 = _lib.launch_count()
@@ -424,6 +432,7 @@ def main():
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--extras", type=int, default=1, help="1: also time the IIA sweep and the IOI train step (other_workloads)")
+    ap.add_argument("--profile-forward", action="store_true", help="profile one no-grad LL forward after warm-up, print nothing")
     ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around the timed region")
     ap.add_argument("--graphs", type=int, default=1, help="1: replay each (loss term, node) variant from a CUDA graph")
     args = ap.parse_args()
