@@ -31,6 +31,13 @@ class Conv(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("n", "h", "w", "c", "k", "r", "s", "stride", "pad", "p", "q")]
 
 
+class Relayout(C.Structure):
+    """iit_relayout_t"""
+    _fields_ = [("w", C.c_void_p), ("out", C.c_void_p), ("stride", C.c_int64 * 4),
+                ("k", C.c_int32), ("c", C.c_int32), ("r", C.c_int32), ("s", C.c_int32),
+                ("to_crsk", C.c_int32), ("dtype", C.c_int32)]
+
+
 _vp, _i, _i64, _f, _d, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_double, C.c_size_t
 _BoxP, _ConvP = C.POINTER(Box), C.POINTER(Conv)
 
@@ -60,7 +67,7 @@ SIGNATURES = {
     "iit_conv2d_wgrad_noalloc": [_vp, _vp, _vp, _ConvP, _i, _vp],
     "iit_filter_relayout": [_vp, C.POINTER(C.c_int64), _vp, _i, _i, _i, _i, _i, _i, _vp],
     "iit_bn_stats": [_vp, _i, _i64, _i, _vp, _vp, _vp],
-    "iit_bn_finalize": [_vp, _vp, _i64, _i, _f, _f, _vp, _vp, _vp, _vp, _vp],
+    "iit_bn_finalize": [_vp, _vp, _i64, _i, _f, _f, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "iit_bn_eval_invstd": [_vp, _i, _f, _vp, _vp],
     "iit_bn_act_fwd": [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _i, _vp],
     "iit_bn_act_bwd_reduce": [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _i, _vp, _vp, _vp],
@@ -94,6 +101,7 @@ SIGNATURES = {
     "iit_gather_rows": [_vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp],
     "iit_gather_box": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i64, _vp, _vp],
     "iit_pick_other_class": [_vp, _vp, _i, _i64, C.c_uint64, _i64, _vp, _vp, _vp, _vp],
+    "iit_filter_relayout_batched": [_vp, _i, _i64, _vp],
     "iit_sqnorm": [_vp, _i64, _vp, _vp],
     "iit_adam_step": [_vp, _vp, _vp, _vp, _i64, _d, _d, _d, _d, _i64, _vp, _d, _vp],
     "iit_adam_step_dev": [_vp, _vp, _vp, _vp, _i64, _vp, _d, _d, _d, _vp, _vp, _d, _vp],

@@ -61,13 +61,16 @@ __global__ void __launch_bounds__(256) bn_stats_kernel(const T* __restrict__ x, 
   else __syncthreads();
 }
 
-__global__ void bn_finalize_kernel(const double* __restrict__ sum, const double* __restrict__ sq, int64_t rows, int C,
+__global__ void bn_finalize_kernel(double* __restrict__ sum, double* __restrict__ sq, int64_t rows, int C,
                                    float eps, float momentum, float* __restrict__ mean, float* __restrict__ invstd,
-                                   float* __restrict__ rmean, float* __restrict__ rvar) {
+                                   float* __restrict__ rmean, float* __restrict__ rvar, long long* __restrict__ tracked,
+                                   int clear) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c == 0 && tracked) *tracked += 1;            // num_batches_tracked, folded into this launch
   if (c >= C) return;
   double m = sum[c] / (double)rows;
   double var = sq[c] / (double)rows - m * m;
+  if (clear) { sum[c] = 0.0; sq[c] = 0.0; }        // consume-and-clear: the accumulators are zero for their next use
   if (var < 0) var = 0;
   mean[c] = (float)m;
   invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
@@ -497,12 +500,14 @@ extern "C" int iit_bn_stats(const void* x, int dtype, int64_t rows, int c, doubl
   return 0;
 }
 
-extern "C" int iit_bn_finalize(const double* sum, const double* sqsum, int64_t rows, int c, float eps, float momentum,
-                               float* mean, float* invstd, float* running_mean, float* running_var, void* stream) {
+extern "C" int iit_bn_finalize(double* sum, double* sqsum, int64_t rows, int c, float eps, float momentum,
+                               float* mean, float* invstd, float* running_mean, float* running_var,
+                               int64_t* num_batches_tracked, int clear_sums, void* stream) {
   IIT_REQUIRE(sum && sqsum && mean && invstd && rows >= 1, "iit_bn_finalize: bad arguments");
   IIT_REQUIRE((running_mean == nullptr) == (running_var == nullptr), "iit_bn_finalize: running stats go together");
   bn_finalize_kernel<<<(c + 127) / 128, 128, 0, as_stream(stream)>>>(sum, sqsum, rows, c, eps, momentum, mean, invstd,
-                                                                    running_mean, running_var);
+                                                                    running_mean, running_var,
+                                                                    reinterpret_cast<long long*>(num_batches_tracked), clear_sums);
   IIT_LAUNCH_CHECK("iit_bn_finalize");
   return 0;
 }

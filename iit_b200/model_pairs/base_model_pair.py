@@ -211,7 +211,11 @@ class BaseModelPair(ABC):
     def make_optimizer(self):
         """Adam over the LL parameters (reference :229). Flat fused kernel on CUDA."""
         from iit_b200.nn.optim import FlatAdam
-        return FlatAdam(self.ll_model.parameters(), lr=self.training_args["lr"])
+        opt = FlatAdam(self.ll_model.parameters(), lr=self.training_args["lr"])
+        refresh = getattr(self.ll_model, "refresh_filter_shadow", None)
+        if refresh is not None:   # derived copies of the weights follow every update in one launch
+            opt.post_step.append(refresh)
+        return opt
 
     def step_scheduler(self, lr_scheduler, test_metrics):
         if isinstance(lr_scheduler, t.optim.lr_scheduler.ReduceLROnPlateau):

@@ -39,6 +39,7 @@ class FlatAdam(torch.optim.Optimizer):
         self.step_dev = torch.zeros(1, dtype=torch.int64, device=dev)
         self.lr_dev = torch.full((1,), float(lr), dtype=torch.float32, device=dev)
         self._lr_host = float(lr)
+        self.post_step = []   # callables run after every update (e.g. the model's refresh of its bf16 filter copies)
         with torch.no_grad():
             for p, o in zip(params, offs):
                 pv = self._view_like(self.flat_p, o, p)
@@ -90,6 +91,8 @@ class FlatAdam(torch.optim.Optimizer):
                            g["eps"], self.step_dev, sq, max_norm)
         for p in self._params:  # the kernel wrote through raw pointers: tell autograd / filter caches
             torch.autograd.graph.increment_version(p)
+        for cb in self.post_step:
+            cb()
 
 
 def _dense(p) -> bool:

@@ -36,6 +36,9 @@ class Conv2d(nn.Module):
     def prepared(self, dtype):
         """(KRSC filter in `dtype`, thunk for the CRSK copy used by dgrad); cached per weight version."""
         w = self.weight
+        sh = self._prep.get("shadow")
+        if sh is not None and sh[0] == (w._version, w.data_ptr(), dtype):
+            return sh[1], (lambda: sh[2])    # copies kept fresh by ResNet18LL.refresh_filter_shadow (one launch for all)
         key = (w._version, w.data_ptr(), dtype)
         ent = self._prep.get("ent")
         # under CUDA-graph capture the re-layout must be part of the graph (replays see new weights)
@@ -92,11 +95,24 @@ class BatchNorm2d(nn.Module):
         self.register_buffer("num_batches_tracked", torch.tensor(0, dtype=torch.long))
         self.eps, self.momentum, self.c = eps, momentum, c
 
+    def accumulator(self, device):
+        """Persistent fp64 [2, C] accumulator for the batch statistics: zero between uses (the finalize kernel clears it
+        after reading), so no per-forward allocation + fill. Not part of the state dict."""
+        acc = self.__dict__.get("_acc")
+        if acc is None or acc.device != device:
+            acc = torch.zeros((2, self.c), dtype=torch.float64, device=device)
+            self.__dict__["_acc"] = acc
+        return acc
+
     def forward(self, x, residual=None, relu=False, sums=None):
-        if self.training:
-            self.num_batches_tracked.add_(1)
-        return ops.bn_act(x, self.weight, self.bias, residual, self.running_mean, self.running_var, self.training,
-                          self.momentum, self.eps, relu, sums)
+        acc = self.accumulator(x.device) if (self.training and x.is_cuda) else None
+        try:
+            return ops.bn_act(x, self.weight, self.bias, residual, self.running_mean, self.running_var, self.training,
+                              self.momentum, self.eps, relu, sums, acc, self.num_batches_tracked if self.training else None)
+        except Exception:
+            if acc is not None:
+                acc.zero_()      # a failed launch sequence must not leave partial sums behind
+            raise
 
 
 class ReLU(nn.Module):
@@ -167,8 +183,13 @@ def _conv_bn(conv: Wrapped, bn: Wrapped, x, residual=None, relu=False, fuse_stat
     bnm = bn.mod
     sums = None
     if bnm.training and fuse_stats and not conv.hook_point.has_hooks():
-        sums = ops.new_bn_sums(bnm.c, x.device)
-    y = conv.hook_point(conv.mod(x, sums) if act_dtype is None else conv.mod(x, sums, act_dtype))
+        sums = bnm.accumulator(x.device) if x.is_cuda else ops.new_bn_sums(bnm.c, x.device)
+    try:
+        y = conv.hook_point(conv.mod(x, sums) if act_dtype is None else conv.mod(x, sums, act_dtype))
+    except Exception:
+        if sums is not None:
+            sums.zero_()         # the accumulator is persistent: never leave partial sums in it
+        raise
     return bnm(y, residual=residual, relu=relu, sums=sums)
 
 
@@ -222,6 +243,63 @@ class ResNet18LL(HookedRootModule):
         out = b.relu.hook_point(out)
         return wb.hook_point(out)
 
+    # --- bf16 filter copies of every convolution, refreshed by ONE kernel launch ------------------------------
+    # The tensor-core kernels read bf16 KRSC (fprop) and CRSK (dgrad) copies of the fp32 master filters. Re-making them per
+    # convolution and weight version costs ~40 small launches per update; here they live in persistent buffers described
+    # by a device-resident table, and `refresh_filter_shadow` rewrites all of them at once. FlatAdam calls it right after
+    # each update (also inside captured graphs); `forward` calls it when any copy is stale (load_state_dict, other
+    # optimizers), so a stale copy is never read.
+    def _shadow_convs(self):
+        return [m for m in self.modules() if isinstance(m, Conv2d) and not m.is_stem()
+                and m.weight.shape[0] % 64 == 0 and m.weight.shape[1] % 64 == 0]
+
+    def _build_filter_shadow(self):
+        import ctypes as C
+        from .._lib import IIT_BF16, Relayout
+        convs = self._shadow_convs()
+        dev = convs[0].weight.device
+        table = (Relayout * (2 * len(convs)))()
+        bufs = []
+        for i, m in enumerate(convs):
+            w = m.weight
+            k, c, r, s = w.shape
+            pair = [torch.empty(k * c * r * s, dtype=torch.bfloat16, device=dev) for _ in range(2)]
+            bufs.append(pair)
+            for j in range(2):
+                e = table[2 * i + j]
+                e.w, e.out = w.data_ptr(), pair[j].data_ptr()
+                for d in range(4):
+                    e.stride[d] = w.stride(d)
+                e.k, e.c, e.r, e.s, e.to_crsk, e.dtype = k, c, r, s, j, IIT_BF16
+        raw = torch.frombuffer(bytearray(bytes(table)), dtype=torch.uint8).clone()
+        self._shadow = {"convs": convs, "bufs": bufs, "table": raw.to(dev), "ptrs": [m.weight.data_ptr() for m in convs],
+                        "max": max(m.weight.numel() for m in convs)}
+
+    def refresh_filter_shadow(self):
+        if self.act_dtype != torch.bfloat16 or not ops.USE_TENSOR_CORES:
+            return
+        sh = getattr(self, "_shadow", None)
+        if sh is None or sh["ptrs"] != [m.weight.data_ptr() for m in sh["convs"]]:
+            if ops.capturing():
+                return                       # never (re)allocate the table inside a capture: the per-conv path serves it
+            self._build_filter_shadow()
+            sh = self._shadow
+        ops.filter_relayout_batched(sh["table"], 2 * len(sh["convs"]), sh["max"])
+        for m, (krsc, crsk) in zip(sh["convs"], sh["bufs"]):
+            w = m.weight
+            m._prep["shadow"] = ((w._version, w.data_ptr(), torch.bfloat16), krsc, crsk)
+
+    def _filter_shadow_stale(self):
+        sh = getattr(self, "_shadow", None)
+        if sh is None:
+            return True
+        for m in sh["convs"]:
+            ent = m._prep.get("shadow")
+            w = m.weight
+            if ent is None or ent[0] != (w._version, w.data_ptr(), torch.bfloat16):
+                return True
+        return False
+
     def refresh_input_cache(self, x):
         """Rebuild the per-batch stem operand of a registered (static) input tensor after its contents changed;
         model pairs call this before replaying captured graphs (ops.stem_cols)."""
@@ -229,6 +307,8 @@ class ResNet18LL(HookedRootModule):
 
     def forward(self, x):
         m = self.mod
+        if self.act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES and x.is_cuda and self._filter_shadow_stale():
+            self.refresh_filter_shadow()
         stem_tc = self.act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES and m.conv1.mod.is_stem()
         if not stem_tc and (x.dtype != self.act_dtype or not ops._is_cl(x)):
             # the tensor-core stem reads the caller's tensor (fp32 NCHW included) directly; otherwise convert
@@ -239,13 +319,17 @@ class ResNet18LL(HookedRootModule):
         if fuse_tail:
             # conv1 -> hook -> [bn1 -> relu -> maxpool] in one kernel: nothing between them is observed
             sums = None
+            acc = bn.accumulator(x.device) if (bn.training and x.is_cuda) else None
             if bn.training and not m.conv1.hook_point.has_hooks():
-                sums = ops.new_bn_sums(bn.c, x.device)
-            y0 = m.conv1.hook_point(m.conv1.mod(x, sums, self.act_dtype))
-            if bn.training:
-                bn.num_batches_tracked.add_(1)
-            x = ops.bn_relu_maxpool(y0, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.training, bn.momentum,
-                                    bn.eps, sums)
+                sums = acc if acc is not None else ops.new_bn_sums(bn.c, x.device)
+            try:
+                y0 = m.conv1.hook_point(m.conv1.mod(x, sums, self.act_dtype))
+                x = ops.bn_relu_maxpool(y0, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.training, bn.momentum,
+                                        bn.eps, sums, acc, bn.num_batches_tracked if bn.training else None)
+            except Exception:
+                if acc is not None:
+                    acc.zero_()
+                raise
             x = m.maxpool.hook_point(x)
         else:
             if m.bn1.hook_point.has_hooks():

@@ -309,6 +309,11 @@ def filter_relayout(weight: torch.Tensor, to_crsk: bool, dtype) -> torch.Tensor:
     return out
 
 
+def filter_relayout_batched(table_dev: torch.Tensor, entries: int, max_elements: int):
+    """Every (filter, layout) pair described by the device-resident iit_relayout_t table, in one launch."""
+    call("iit_filter_relayout_batched", _p(table_dev), int(entries), int(max_elements), _stream())
+
+
 class _ConvFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums):
@@ -504,7 +509,7 @@ def new_bn_sums(c: int, device) -> torch.Tensor:
 
 class _BNActFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums):
+    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums, acc, tracked):
         _require_cuda(x, gamma, beta, residual)
         x = _cl(x)
         n, c, h, w = x.shape
@@ -513,13 +518,17 @@ class _BNActFn(torch.autograd.Function):
         if residual is not None:
             residual = _cl(residual)
         if training:
+            clear = 0
             if sums is None:
-                sums = new_bn_sums(c, x.device)
+                # `acc`: the layer's persistent accumulator (zero between uses: the finalize kernel clears it)
+                sums, clear = (acc, 1) if acc is not None else (new_bn_sums(c, x.device), 0)
                 call("iit_bn_stats", _p(x), _dt(x), rows, c, _p(sums[0]), _p(sums[1]), st)
+            elif acc is not None and sums.data_ptr() == acc.data_ptr():
+                clear = 1
             mean = torch.empty(c, dtype=torch.float32, device=x.device)
             invstd = torch.empty(c, dtype=torch.float32, device=x.device)
             call("iit_bn_finalize", _p(sums[0]), _p(sums[1]), rows, c, float(eps), float(momentum), _p(mean), _p(invstd),
-                 _p(running_mean), _p(running_var), st)
+                 _p(running_mean), _p(running_var), _p(tracked), clear, st)
         else:
             mean = running_mean
             invstd = torch.empty(c, dtype=torch.float32, device=x.device)
@@ -547,11 +556,15 @@ class _BNActFn(torch.autograd.Function):
         corr = red if ctx.training else torch.zeros_like(red)
         call("iit_bn_act_bwd_apply", _p(dy), _p(y), _p(x), _p(dx), _p(dres), _dt(x), rows, c, _p(mean), _p(invstd),
              _p(gamma), _p(corr[0]), _p(corr[1]), int(ctx.relu), st)
-        return dx, red[0].float(), red[1].float(), dres, None, None, None, None, None, None, None
+        return dx, red[0].float(), red[1].float(), dres, None, None, None, None, None, None, None, None, None
 
 
-def bn_act(x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums=None):
-    return _BNActFn.apply(x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums)
+def bn_act(x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums=None, acc=None,
+           tracked=None):
+    """`sums`: statistics already accumulated by the producing convolution's epilogue; `acc`: the layer's persistent
+    fp64 accumulator [2, C] (kept zero between uses; `sums` may be it); `tracked`: num_batches_tracked, incremented by the
+    finalize kernel."""
+    return _BNActFn.apply(x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums, acc, tracked)
 
 
 class _BNReluPoolFn(torch.autograd.Function):
@@ -559,20 +572,23 @@ class _BNReluPoolFn(torch.autograd.Function):
     backward recomputes the activation from the conv output (nothing but the window index is stored)."""
 
     @staticmethod
-    def forward(ctx, x, gamma, beta, running_mean, running_var, training, momentum, eps, sums):
+    def forward(ctx, x, gamma, beta, running_mean, running_var, training, momentum, eps, sums, acc, tracked):
         _require_cuda(x, gamma, beta)
         x = _cl(x)
         n, c, h, w = x.shape
         rows = n * h * w
         st = _stream()
         if training:
+            clear = 0
             if sums is None:
-                sums = new_bn_sums(c, x.device)
+                sums, clear = (acc, 1) if acc is not None else (new_bn_sums(c, x.device), 0)
                 call("iit_bn_stats", _p(x), _dt(x), rows, c, _p(sums[0]), _p(sums[1]), st)
+            elif acc is not None and sums.data_ptr() == acc.data_ptr():
+                clear = 1
             mean = torch.empty(c, dtype=torch.float32, device=x.device)
             invstd = torch.empty(c, dtype=torch.float32, device=x.device)
             call("iit_bn_finalize", _p(sums[0]), _p(sums[1]), rows, c, float(eps), float(momentum), _p(mean), _p(invstd),
-                 _p(running_mean), _p(running_var), st)
+                 _p(running_mean), _p(running_var), _p(tracked), clear, st)
         else:
             mean = running_mean
             invstd = torch.empty(c, dtype=torch.float32, device=x.device)
@@ -596,11 +612,11 @@ class _BNReluPoolFn(torch.autograd.Function):
             raise NotImplementedError("fused bn+relu+maxpool backward is for batch statistics (train mode)")
         call("iit_bn_relu_maxpool_bwd", _p(dy), _p(idx), _p(x), _p(dx), _dt(x), n, h, w, c, _p(mean), _p(invstd), _p(gamma),
              _p(beta), _p(red[0]), _p(red[1]), _stream())
-        return dx, red[0].float(), red[1].float(), None, None, None, None, None, None
+        return dx, red[0].float(), red[1].float(), None, None, None, None, None, None, None, None
 
 
-def bn_relu_maxpool(x, gamma, beta, running_mean, running_var, training, momentum, eps, sums=None):
-    return _BNReluPoolFn.apply(x, gamma, beta, running_mean, running_var, training, momentum, eps, sums)
+def bn_relu_maxpool(x, gamma, beta, running_mean, running_var, training, momentum, eps, sums=None, acc=None, tracked=None):
+    return _BNReluPoolFn.apply(x, gamma, beta, running_mean, running_var, training, momentum, eps, sums, acc, tracked)
 
 
 class _ReluFn(torch.autograd.Function):

@@ -207,14 +207,28 @@ int iit_stem_im2col(const void* x, int dtype, const int64_t* strides_nchw, void*
  * (any memory format) -> dense KRSC (to_crsk=0) or CRSK (to_crsk=1) in `dtype`. */
 int iit_filter_relayout(const float* w, const int64_t* strides_kcrs, void* w_out, int k, int c, int r,
                         int s, int to_crsk, int dtype, void* stream);
+/* The same for many filters in one launch: `table_dev` is an array of `entries` descriptors in DEVICE memory
+ * (max_elements = the largest k*c*r*s among them, for the launch geometry). Used to refresh every bf16 filter copy of
+ * the ResNet right after an optimizer update; replayable from a CUDA graph because nothing is baked into the launch. */
+typedef struct {
+  const void* w;      /* fp32 master filter [k,c,r,s], element strides below */
+  void* out;          /* dense KRSC (to_crsk = 0) or CRSK (to_crsk = 1) buffer in `dtype` */
+  int64_t stride[4];
+  int32_t k, c, r, s;
+  int32_t to_crsk, dtype;
+} iit_relayout_t;
+int iit_filter_relayout_batched(const iit_relayout_t* table_dev, int entries, int64_t max_elements, void* stream);
 
 /* BatchNorm2d (training): per-channel statistics over n*h*w rows of an NHWC tensor.
  * sum/sqsum fp64 [c] zeroed by caller. Replaces F.batch_norm's statistics pass. */
 int iit_bn_stats(const void* x, int dtype, int64_t rows, int c, double* sum, double* sqsum, void* stream);
 /* From sums: mean, invstd (biased var + eps), and running-stat update with momentum and the
- * unbiased variance (torch.nn.BatchNorm2d semantics). running_* may be NULL (no update). */
-int iit_bn_finalize(const double* sum, const double* sqsum, int64_t rows, int c, float eps, float momentum,
-                    float* mean, float* invstd, float* running_mean, float* running_var, void* stream);
+ * unbiased variance (torch.nn.BatchNorm2d semantics). running_* may be NULL (no update).
+ * num_batches_tracked (may be NULL) is incremented; clear_sums != 0 zeroes sum / sqsum after reading them, so a
+ * persistent accumulator is ready for its next use without a fill launch. */
+int iit_bn_finalize(double* sum, double* sqsum, int64_t rows, int c, float eps, float momentum,
+                    float* mean, float* invstd, float* running_mean, float* running_var,
+                    int64_t* num_batches_tracked, int clear_sums, void* stream);
 /* y = act((x-mean)*invstd*gamma+beta (+ residual)); act = relu if relu!=0. In eval mode pass
  * mean=running_mean and invstd=1/sqrt(running_var+eps) (iit_bn_eval_invstd). */
 int iit_bn_eval_invstd(const float* running_var, int c, float eps, float* invstd, void* stream);
