@@ -317,10 +317,35 @@ def run_ours(args, rank, world, local):
     def step_resident():
         return pair.run_train_step(base_d, src_d, pair.loss_fn, opt)
 
+    # end to end: every step uploads its batch from pinned host memory (H2D inside the timed region) and reads its losses
+    # back. The upload of step i+1 runs on a copy stream while step i computes, into the other of two device buffers --
+    # what a prefetching loader does; the first upload of the timed region is waited for, so all K uploads are inside it.
+    copy_stream = torch.cuda.Stream()
+    slots = [tuple(torch.empty_like(t, device=dev) for t in (*base_h, *src_h)) for _ in range(2)]
+    ready = [torch.cuda.Event(), torch.cuda.Event()]
+    consumed = [torch.cuda.Event(), torch.cuda.Event()]
+    e2e_state = {"i": 0, "primed": False}
+
+    def upload(slot):
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[slot])          # the step that last read this slot has finished
+            for dst, srch in zip(slots[slot], (*base_h, *src_h)):
+                dst.copy_(srch, non_blocking=True)
+            ready[slot].record(copy_stream)
+
     def step_e2e():
-        b = tuple(t.to(dev, non_blocking=True) for t in base_h)
-        s = tuple(t.to(dev, non_blocking=True) for t in src_h)
-        return pair.run_train_step(b, s, pair.loss_fn, opt)  # returns host floats: the D2H read of the losses
+        i = e2e_state["i"]
+        slot = i & 1
+        if not e2e_state["primed"]:
+            upload(slot)
+            e2e_state["primed"] = True
+        torch.cuda.current_stream().wait_event(ready[slot])
+        upload(slot ^ 1)                                     # next step's batch, overlapped with this step's kernels
+        bufs = slots[slot]
+        out = pair.run_train_step(bufs[:3], bufs[3:], pair.loss_fn, opt)  # returns host floats: the D2H read of the losses
+        consumed[slot].record(torch.cuda.current_stream())
+        e2e_state["i"] = i + 1
+        return out
 
     if args.graphs:  # capture all 21 (term, node) variants before anything is timed; leaves state untouched
         pair.prepare_graphs(base_d, src_d, pair.loss_fn, opt)
@@ -363,6 +388,8 @@ def run_ours(args, rank, world, local):
     launches = _lib.launch_count() - launches0
     clocks = sampler.stop()
     step_e2e()  # warm the copy path
+    torch.cuda.synchronize()
+    e2e_state["primed"] = False   # the timed region starts with its own first upload (K uploads + 1 prefetch inside it)
     sec_e2e, _ = timed(step_e2e, args.steps)
     sec_eager = None
     if args.graphs:

@@ -491,17 +491,20 @@ __global__ void __launch_bounds__(TC_THREADS) wgrad3x3_tc_kernel(const __grid_co
                                  ((uint32_t)(128 >> 4) << 24);
       int stage = 0;
       uint32_t phase = 0;
+      // descriptor = constant high word + low word (LBO << 16) | (address >> 4): stepped with 32-bit adds (tc_common.cuh)
+      const uint64_t proto = umma_desc_mn_sw128(0, BOX);
+      const uint32_t d_hi = (uint32_t)(proto >> 32), lo0 = (uint32_t)proto + (smem_u32(smem) >> 4);
       for (int i = 0; i < nchunks; ++i) {
         mbar_wait(&full[stage], phase);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t a0 = smem_u32(smem + stage * STAGE_BYTES);
-        const uint32_t b0 = a0 + A_BYTES;
+        const uint32_t a_lo = lo0 + stage * (STAGE_BYTES >> 4);
+        const uint32_t b_lo = a_lo + (A_BYTES >> 4);
 #pragma unroll
         for (int s = 0; s < S; ++s) {
 #pragma unroll
           for (int k = 0; k < 4; ++k) {   // 64 pixels = 4 x UMMA_K(16); 16 pixel rows = 2048 bytes
-            umma_bf16(tmem_base + s * CB, umma_desc_mn_sw128(a0 + k * 2048, BOX), umma_desc_mn_sw128(b0 + s * B_TAP + k * 2048, BOX),
-                      idesc, (uint32_t)((i | k) != 0));
+            umma_bf16_lohi(tmem_base + s * CB, a_lo + k * (2048 >> 4), d_hi, b_lo + s * (B_TAP >> 4) + k * (2048 >> 4), d_hi, idesc,
+                           (uint32_t)((i | k) != 0));
           }
         }
         umma_commit(&empty[stage]);
