@@ -448,8 +448,8 @@ def run_ours(args, rank, world, local):
 
 
 def main():
-    if os.environ.get("NCCL_DEBUG", "VERSION") == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line
+    if os.environ.get("NCCL_DEBUG", "VERSION").upper() in ("VERSION", "WARN"):
+        os.environ.pop("NCCL_DEBUG", None)  # NCCL writes its version banner to stdout: keep stdout to the one JSON line
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
