@@ -235,13 +235,13 @@ def _timed_region(dp, dev, fn, steps):
 
 def run_ioi_extra(rank, world, dev, dp, batch=1024, steps=3, warmup=2):
     """BASELINE.json configs[2]/[3]: IOI strict-IIT train step (small HookedTransformer LL, head-level interventions),
-    data-parallel with gradient all-reduce when world > 1. fp32 activations (the reference's dtype), integer labels,
+    data-parallel with gradient all-reduce when world > 1. bf16 activations on the tensor-core GEMMs, integer labels,
     last-position unembed (0.94 GFLOP / pair)."""
     from iit_b200.model_pairs import IOI_ModelPair
     from iit_b200.tasks.ioi import IOI_HL, corr, make_ll_model
     from oracle import restate as R
     torch.manual_seed(0)
-    ll = make_ll_model(device=dev)
+    ll = make_ll_model(device=dev, dtype=torch.bfloat16)
     (bx, by, bv), names = R.synthetic_ioi(batch, 21 + 2 * rank, one_hot=False)
     (sx, sy, sv), _ = R.synthetic_ioi(batch, 22 + 2 * rank, one_hot=False)
     hl = IOI_HL(50257, names).to(dev)
@@ -257,9 +257,10 @@ def run_ioi_extra(rank, world, dev, dp, batch=1024, steps=3, warmup=2):
     sec, m = _timed_region(dp, dev, lambda: pair.run_train_step(base, src, pair.loss_fn, opt), steps)
     return {"metric": "ioi_iit_train_pairs_per_sec", "value": batch * world * steps / sec, "unit": UNIT, "ms_per_step": 1e3 * sec / steps,
             "config": {"workload": f"IOI strict-IIT train step (train_ioi.py), HookedTransformer 6L/4H/d64/d_mlp 3072/vocab 50257, "
-                                   f"batch {batch} prompts/GPU x 16 tokens, fp32, integer labels, last-position unembed",
+                                   f"batch {batch} prompts/GPU x 16 tokens, bf16 activations (fp32 master weights), integer labels, "
+                                   f"last-position unembed",
                        "baseline_config": "configs[2]" if world == 1 else "configs[3]", "parallelism": f"dp{world}"},
-            "steps": steps, "warmup": warmup, "dtype": "f32", "last_step_metrics": m}
+            "steps": steps, "warmup": warmup, "dtype": "bf16", "last_step_metrics": m}
 
 
 def run_sweep_extra(rank, world, dev, dp, batch=1024, batches_per_rank=2):

@@ -166,8 +166,15 @@ class HookedTransformerLL(HookedRootModule):
             else:
                 resid = ops.bias_add(out, m.b_out, resid)
             resid = blk.hook_resid_post(resid.view(B, S, D)).reshape(T, D)
+        W_U, b_U, V = self.unembed.W_U, self.unembed.b_U, c.d_vocab_out
+        pad = (-V) % 64
+        if pad and self.act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES:
+            # the tensor-core GEMMs want widths that are multiples of 64: unembed into V + pad columns (zero weights and
+            # bias) and slice them off again; autograd routes the gradient (50257 -> 50304 for GPT-2's vocabulary)
+            W_U = torch.nn.functional.pad(W_U, (0, pad))
+            b_U = torch.nn.functional.pad(b_U, (0, pad))
         if last_pos_only:
             last = resid.view(B, S, D)[:, -1, :].contiguous()
-            return ops.bias_add(ops.linear_tokens(ops.lnpre(last, c.eps), self.unembed.W_U), self.unembed.b_U)
-        logits = ops.bias_add(ops.linear_tokens(ops.lnpre(resid, c.eps), self.unembed.W_U), self.unembed.b_U)
-        return logits.view(B, S, -1)
+            return ops.bias_add(ops.linear_tokens(ops.lnpre(last, c.eps), W_U), b_U)[:, :V]
+        logits = ops.bias_add(ops.linear_tokens(ops.lnpre(resid, c.eps), W_U), b_U)[:, :V]
+        return logits.reshape(B, S, -1)

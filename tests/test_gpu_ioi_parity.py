@@ -238,3 +238,33 @@ def test_teacher_forced_terms_and_eval_match_oracle():
         assert np.array_equal(got["val/per_token_accuracy"], want["val/per_token_accuracy"])
         assert got["val/accuracy"] == want["val/accuracy"]
         assert rel(got["val/iit_loss"], want["val/iit_loss"]) < 1e-3
+
+
+def test_bf16_transformer_close_to_fp32_path_full_vocab():
+    """bf16 activations on the tensor-core GEMMs (unembed padded from 50257 to 50304 columns) against this library's
+    exact-fp32 path on the same weights: last-position logits within 3e-2 of their range, one strict train step's
+    losses within 5e-2 relative (stated separately from the fp32 bar, as for the ResNet)."""
+    from iit_b200.model_pairs import IOI_ModelPair
+    from iit_b200.tasks.ioi import IOI_HL, corr, make_ll_model
+    sd = R.transformer_state_dict(0)
+    (bx, by, bv), names = R.synthetic_ioi(16, 5, one_hot=False)
+    (sx, sy, sv), _ = R.synthetic_ioi(16, 6, one_hot=False)
+    base, src = dev((bx, by, bv)), dev((sx, sy, sv))
+    out = {}
+    for dtype in (torch.float32, torch.bfloat16):
+        ll = make_ll_model(device=DEV, dtype=dtype)
+        ll.load_state_dict(sd)
+        with torch.no_grad():
+            logits = ll(base[0], last_pos_only=True).float()
+            full = ll(base[0]).float()
+        assert logits.shape == (16, 50257) and full.shape == (16, 16, 50257)
+        torch.testing.assert_close(full[:, -1], logits, rtol=1e-3, atol=1e-3)
+        hl = IOI_HL(50257, names).to(DEV)
+        pair = IOI_ModelPair(hl, ll, corr, training_args={"lr": 1e-3, "batch_size": 16, "lr_scheduler": None})
+        opt = pair.make_optimizer()
+        ll.train()
+        out[dtype] = (logits.cpu(), pair.run_train_step(base, src, pair.loss_fn, opt))
+    lf, lb = out[torch.float32][0], out[torch.bfloat16][0]
+    assert (lf - lb).abs().max().item() <= 3e-2 * (lf.max() - lf.min()).item()
+    for k, v in out[torch.float32][1].items():
+        assert rel(out[torch.bfloat16][1][k], v) < 5e-2, (k, out)
