@@ -65,7 +65,8 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
   uint64_t* tmem_empty = tmem_full + 2;      // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
   float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [2][BN] per-channel sum / sum of squares of one tile
-  if (bn_sum != nullptr && threadIdx.x < BN) { s_stat[threadIdx.x] = 0.f; s_stat[threadIdx.x + BN] = 0.f; }
+  if (bn_sum != nullptr)
+    for (int i = threadIdx.x; i < 2 * BN; i += TC_THREADS) s_stat[i] = 0.f;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kchunks = p.Cin / TC_BK;
@@ -158,7 +159,10 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
     const int hl = (m / p.BW) % p.BH;
     const int nl = m / (p.BW * p.BH);
     const int e = threadIdx.x - 64;     // 0..127: owner of channel e of the current filter block's statistics
-    double run_s = 0.0, run_q = 0.0;    // this CTA's running totals for channel run_co + e
+    constexpr int NCH = (BN + 127) / 128;   // channels of the filter block owned by each of the 128 epilogue threads
+    double run_s[NCH], run_q[NCH];          // this CTA's running totals for channels run_co + e + 128*i
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) { run_s[i] = 0.0; run_q[i] = 0.0; }
     int run_co = -1;
     uint32_t it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
@@ -233,19 +237,32 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
      }  // mt
       if (bn_sum != nullptr) {
         asm volatile("bar.sync 1, 128;" ::: "memory");   // the four epilogue warps only: the tile's sums are complete
-        if (e < BN) {
-          if (run_co != co0) {
-            if (run_co >= 0) { atomicAdd(&bn_sum[run_co + e], run_s); atomicAdd(&bn_sq[run_co + e], run_q); }
-            run_co = co0; run_s = 0.0; run_q = 0.0;
+        if (run_co != co0) {
+#pragma unroll
+          for (int i = 0; i < NCH; ++i) {
+            const int ch = e + 128 * i;
+            if (run_co >= 0 && ch < BN) { atomicAdd(&bn_sum[run_co + ch], run_s[i]); atomicAdd(&bn_sq[run_co + ch], run_q[i]); }
+            run_s[i] = 0.0; run_q[i] = 0.0;
           }
-          run_s += (double)s_stat[e]; run_q += (double)s_stat[BN + e];
-          s_stat[e] = 0.f; s_stat[BN + e] = 0.f;
+          run_co = co0;
+        }
+#pragma unroll
+        for (int i = 0; i < NCH; ++i) {
+          const int ch = e + 128 * i;
+          if (ch < BN) {
+            run_s[i] += (double)s_stat[ch]; run_q[i] += (double)s_stat[BN + ch];
+            s_stat[ch] = 0.f; s_stat[BN + ch] = 0.f;
+          }
         }
         asm volatile("bar.sync 1, 128;" ::: "memory");   // zeroed before the next tile adds to it
       }
     }
-    if (bn_sum != nullptr && e < BN && run_co >= 0) {
-      atomicAdd(&bn_sum[run_co + e], run_s); atomicAdd(&bn_sq[run_co + e], run_q);
+    if (bn_sum != nullptr && run_co >= 0) {
+#pragma unroll
+      for (int i = 0; i < NCH; ++i) {
+        const int ch = e + 128 * i;
+        if (ch < BN) { atomicAdd(&bn_sum[run_co + ch], run_s[i]); atomicAdd(&bn_sq[run_co + ch], run_q[i]); }
+      }
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -258,6 +275,7 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
 
 // ---- host side -----------------------------------------------------------------------------------
 static bool g_tile_pairs = true;
+static bool g_bn256 = true;
 
 static int pow2_ge(int v) { int r = 1; while (r < v) r <<= 1; return r; }
 
@@ -324,7 +342,9 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
   tp.tiles_w = (tp.Q + tp.BW - 1) / tp.BW;
   tp.tiles_h = (tp.P + tp.BH - 1) / tp.BH;
   tp.tiles_n = (tp.N + tp.BNI - 1) / tp.BNI;
-  const int BN = (tp.Cout % 128 == 0) ? 128 : 64;
+  // 256 filters per tile where the layer has them: with N = 256 an MMA reads 12 KB of shared memory per 128 tensor cycles
+  // (96 B/clk); with N = 128 it is 8 KB per 64 cycles, exactly the 128 B/clk shared memory delivers
+  const int BN = (tp.Cout % 256 == 0 && g_bn256) ? 256 : (tp.Cout % 128 == 0) ? 128 : 64;
   CUtensorMap ma, mb;
   if (encode_nhwc_strided(&ma, gathered, gC, gW, gH, tp.N, tp.BW, tp.BH, tp.BNI, tp.in_mul, name)) return 1;
   if (encode_filter(&mb, wmat, Kg, tp.Cout, BN, name)) return 1;
@@ -333,7 +353,8 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
   const int MT = (BN == 128 && g_tile_pairs && ((mtiles + 1) / 2) * (tp.Cout / BN) >= kNumSMs) ? 2 : 1;
   const int64_t total = ((mtiles + MT - 1) / MT) * (tp.Cout / BN);
   IIT_REQUIRE(total < (1ll << 31), "%s: too many tiles", name);
-  int rc = BN == 128 ? (MT == 2 ? launch_tc<128, 2>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq)
+  int rc = BN == 256 ? launch_tc<256, 1>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq)
+         : BN == 128 ? (MT == 2 ? launch_tc<128, 2>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq)
                                 : launch_tc<128, 1>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq))
                      : launch_tc<64, 1>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq);
   if (rc) return rc;
