@@ -193,7 +193,7 @@ class KernelTimer:
                 s.record()
                 inner(name, *a)
                 e.record()
-                self.records[name].append((s, e, conv_flops(a)))
+                self.records[name].append((s, e, hbm_bytes(name, a) if name in HBM_ENTRY_POINTS else conv_flops(a)))
             else:
                 inner(name, *a)
 
@@ -205,9 +205,47 @@ class KernelTimer:
             if recs:
                 ms = [s.elapsed_time(e) for s, e, _ in recs]
                 fl = [f for _, _, f in recs]
-                out[n] = {"launches": len(recs), "total_ms": float(sum(ms)), "avg_ms": float(np.mean(ms)),
-                          "tflops": float(sum(fl) / (sum(ms) * 1e-3) / 1e12)}
+                out[n] = {"launches": len(recs), "total_ms": float(sum(ms)), "avg_ms": float(np.mean(ms))}
+                if n in HBM_ENTRY_POINTS:
+                    out[n]["gbs"] = float(sum(fl) / (sum(ms) * 1e-3) / 1e9)
+                else:
+                    out[n]["tflops"] = float(sum(fl) / (sum(ms) * 1e-3) / 1e12)
         return out
+
+
+def _es(dtype_code):
+    return 2 if dtype_code == 1 else 4      # IIT_BF16 = 1, IIT_F32 = 0
+
+
+def hbm_bytes(name, a):
+    """Algorithmic HBM bytes of one launch of an HBM-bound entry point, from its arguments (DESIGN.md section 3:
+    every tensor the arithmetic needs is read once and every result written once)."""
+    def ptr(v):
+        return v is not None and getattr(v, "value", v) not in (None, 0)
+    if name == "iit_bn_act_fwd":            # x, residual, y, dtype, rows, c, ...
+        return a[4] * a[5] * _es(a[3]) * (2 + ptr(a[1]))
+    if name == "iit_bn_act_bwd_reduce":     # dy, y, x, dtype, rows, c, mean, invstd, relu, ...
+        return a[4] * a[5] * _es(a[3]) * (2 + (1 if a[8] else 0))
+    if name == "iit_bn_act_bwd_apply":      # dy, y, x, dx, dres, dtype, rows, c, ..., relu, stream
+        return a[6] * a[7] * _es(a[5]) * (3 + (1 if a[-2] else 0) + ptr(a[4]))
+    if name == "iit_bn_relu_maxpool_fwd":   # x, y, idx, dtype, n, h, w, c: read x, write y (1/4) + idx (1 B / pooled element)
+        n, h, w, c = a[4:8]
+        return n * h * w * c * _es(a[3]) + n * ((h + 1) // 2) * ((w + 1) // 2) * c * (_es(a[3]) + 1)
+    if name == "iit_bn_relu_maxpool_bwd":   # two kernels: each reads x + dy + idx; the second writes dx
+        n, h, w, c = a[5:9]
+        pooled = n * ((h + 1) // 2) * ((w + 1) // 2) * c
+        return 2 * (n * h * w * c * _es(a[4]) + pooled * (_es(a[4]) + 1)) + n * h * w * c * _es(a[4])
+    if name == "iit_patch_fwd":             # dst, src, box: read the box from src, write it to dst
+        b = a[2]._obj
+        n = b.elem_bytes
+        for d in range(b.rank):
+            n *= b.extent[d]
+        return 2 * n
+    return 0
+
+
+HBM_ENTRY_POINTS = ["iit_bn_act_fwd", "iit_bn_act_bwd_reduce", "iit_bn_act_bwd_apply", "iit_bn_relu_maxpool_fwd",
+                    "iit_bn_relu_maxpool_bwd", "iit_patch_fwd"]
 
 
 def conv_flops(call_args):
@@ -351,7 +389,7 @@ def run_ours(args, rank, world, local):
     if args.graphs:  # capture all 21 (term, node) variants before anything is timed; leaves state untouched
         pair.prepare_graphs(base_d, src_d, pair.loss_fn, opt)
     timer = KernelTimer(["iit_conv2d_fprop", "iit_conv2d_dgrad", "iit_conv2d_wgrad", "iit_conv2d_fprop_tc",
-                         "iit_conv2d_dgrad_tc", "iit_conv2d_wgrad_tc"])
+                         "iit_conv2d_dgrad_tc", "iit_conv2d_wgrad_tc", *HBM_ENTRY_POINTS])
     timer.install()
 
     def timed(fn, steps):
@@ -422,8 +460,10 @@ def run_ours(args, rank, world, local):
     pk = peaks()
     ks = timer.summary()
     roof = None
+    for n, k in ks.items():   # fraction of the measured roofline per entry point: HBM copy GB/s or sustained bf16 TFLOP/s
+        k["frac_of_measured_peak"] = k["gbs"] / pk["hbm_gbs"] if "gbs" in k else k["tflops"] / pk["tflops"]
     if ks:
-        top = max(ks, key=lambda n: ks[n]["total_ms"])
+        top = max((n for n in ks if "tflops" in ks[n]), key=lambda n: ks[n]["total_ms"])
         k = ks[top]
         roof = {"kernel": top, "bound": "tensor", "achieved": k["tflops"], "peak": pk["tflops"], "unit": "TFLOP/s",
                 "frac": k["tflops"] / pk["tflops"], "traffic": ncu_traffic(top), "peak_source": pk["src"] + " bf16 sustained",

@@ -155,7 +155,32 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_fast_kernel(const T* __rest
   load_consts<NP>(mean, c, mu); load_consts<NP>(invstd, c, is);
 #pragma unroll
   for (int j = 0; j < NP; ++j) { acc[0][j] = 0.f; acc[1][j] = 0.f; }
-  for (int64_t r = (int64_t)blockIdx.x * RL + rl; r < rows; r += (int64_t)gridDim.x * RL) {
+  const int64_t step = (int64_t)gridDim.x * RL;
+  int64_t r = (int64_t)blockIdx.x * RL + rl;
+  for (; r + step < rows; r += 2 * step) {      // two rows (six 16-byte loads) in flight per thread
+    uint4 rg[2], rx[2], ry[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      rg[u] = *reinterpret_cast<const uint4*>(dy + (r + u * step) * C + c);
+      rx[u] = *reinterpret_cast<const uint4*>(x + (r + u * step) * C + c);
+      if (relu) ry[u] = *reinterpret_cast<const uint4*>(y + (r + u * step) * C + c);
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      float g[NP], xv[NP];
+      Pack<T>::unpack(rg[u], g);
+      Pack<T>::unpack(rx[u], xv);
+      if (relu) {
+        float yv[NP];
+        Pack<T>::unpack(ry[u], yv);
+#pragma unroll
+        for (int j = 0; j < NP; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < NP; ++j) { acc[0][j] += g[j] * (xv[j] - mu[j]) * is[j]; acc[1][j] += g[j]; }
+    }
+  }
+  for (; r < rows; r += step) {
     float g[NP], xv[NP];
     Pack<T>::load(dy + r * C + c, g);
     Pack<T>::load(x + r * C + c, xv);
