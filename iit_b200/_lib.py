@@ -102,6 +102,7 @@ SIGNATURES = {
     "iit_gather_box": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i64, _vp, _vp],
     "iit_pick_other_class": [_vp, _vp, _i, _i64, C.c_uint64, _i64, _vp, _vp, _vp, _vp],
     "iit_filter_relayout_batched": [_vp, _i, _i64, _vp],
+    "iit_kl_div_rows": [_vp, _vp, _i64, _i64, _i64, _i64, _i, _i, _vp, _vp],
     "iit_sqnorm": [_vp, _i64, _vp, _vp],
     "iit_adam_step": [_vp, _vp, _vp, _vp, _i64, _d, _d, _d, _d, _i64, _vp, _d, _vp],
     "iit_adam_step_dev": [_vp, _vp, _vp, _vp, _i64, _vp, _d, _d, _d, _vp, _vp, _d, _vp],

@@ -469,3 +469,62 @@ extern "C" int iit_ce_prob_bwd(const void* logits, int dtype, int64_t rows, int6
   IIT_LAUNCH_CHECK("iit_ce_prob_bwd");
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// KL(b || a) per row, the metric of the resample-ablation evaluation:
+//   kl[r] = sum_c  B[r,c] * (log B[r,c] - log A[r,c]),   terms with B[r,c] == 0 are 0 (xlogy),
+// where A / B are the rows themselves when they are probability vectors already, else softmax(row)
+// (reference: iit/utils/eval_metrics.py:4-20 followed by F.kl_div(a.log(), b, reduction="none").sum(-1)).
+// One block per row: pass 1 max and sum of exponentials of both rows, pass 2 the sum. Rows are read twice.
+// ------------------------------------------------------------------------------------------------
+namespace iit {
+
+__device__ __forceinline__ float block_reduce(float v, bool is_max, float* s) {
+  v = is_max ? warp_max(v) : warp_sum(v);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  __syncthreads();
+  if (l == 0) s[w] = v;
+  __syncthreads();
+  float r = is_max ? -INFINITY : 0.f;
+  for (int i = 0; i < (int)(blockDim.x >> 5); ++i) r = is_max ? fmaxf(r, s[i]) : r + s[i];
+  return r;
+}
+
+__global__ void __launch_bounds__(256) kl_rows_kernel(const float* __restrict__ a, const float* __restrict__ b, int64_t classes,
+                                                      int64_t a_stride, int64_t b_stride, int a_is_pmf, int b_is_pmf,
+                                                      float* __restrict__ out) {
+  __shared__ float s[8];
+  const float* ar = a + (int64_t)blockIdx.x * a_stride;
+  const float* br = b + (int64_t)blockIdx.x * b_stride;
+  float ma = -INFINITY, mb = -INFINITY;
+  for (int64_t c = threadIdx.x; c < classes; c += blockDim.x) { ma = fmaxf(ma, ar[c]); mb = fmaxf(mb, br[c]); }
+  ma = block_reduce(ma, true, s);
+  mb = block_reduce(mb, true, s);
+  float sa = 0.f, sb = 0.f;
+  for (int64_t c = threadIdx.x; c < classes; c += blockDim.x) { sa += expf(ar[c] - ma); sb += expf(br[c] - mb); }
+  sa = block_reduce(sa, false, s);
+  sb = block_reduce(sb, false, s);
+  const float lza = ma + logf(sa), lzb = mb + logf(sb);      // log partition functions
+  float kl = 0.f;
+  for (int64_t c = threadIdx.x; c < classes; c += blockDim.x) {
+    const float la = a_is_pmf ? logf(ar[c]) : ar[c] - lza;
+    const float pb = b_is_pmf ? br[c] : expf(br[c] - lzb);
+    const float lb = b_is_pmf ? logf(br[c]) : br[c] - lzb;
+    if (pb > 0.f) kl += pb * (lb - la);
+  }
+  kl = block_reduce(kl, false, s);
+  if (threadIdx.x == 0) out[blockIdx.x] = kl;
+}
+
+}  // namespace iit
+
+extern "C" int iit_kl_div_rows(const float* a, const float* b, int64_t rows, int64_t classes, int64_t a_row_stride,
+                               int64_t b_row_stride, int a_is_pmf, int b_is_pmf, float* kl, void* stream) {
+  IIT_REQUIRE(a && b && kl && rows >= 0 && classes >= 1, "iit_kl_div_rows: bad arguments");
+  if (rows == 0) return 0;
+  IIT_REQUIRE(rows < (1ll << 31), "iit_kl_div_rows: too many rows");
+  iit::kl_rows_kernel<<<(unsigned)rows, 256, 0, iit::as_stream(stream)>>>(a, b, classes, a_row_stride, b_row_stride, a_is_pmf,
+                                                                        b_is_pmf, kl);
+  IIT_LAUNCH_CHECK("iit_kl_div_rows");
+  return 0;
+}

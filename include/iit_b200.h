@@ -275,6 +275,12 @@ int iit_linear_fwd(const float* x, const float* w, const float* b, float* y, int
 int iit_linear_bwd(const float* x, const float* w, const float* dy, float* dx, float* dw, float* db,
                    int n, int in, int out, void* stream);
 
+/* kl[r] = sum_c B[r,c] * (log B[r,c] - log A[r,c]) with A / B = the row itself (x_is_pmf != 0) or softmax(row);
+ * fp32 rows with the given strides. The metric of the resample-ablation evaluation
+ * (iit/utils/eval_metrics.py:4-20, iit/utils/eval_ablations.py:59-61). */
+int iit_kl_div_rows(const float* a, const float* b, int64_t rows, int64_t classes, int64_t a_row_stride,
+                    int64_t b_row_stride, int a_is_pmf, int b_is_pmf, float* kl, void* stream);
+
 /* ------------------------------------------------------------------------------------------ */
 /* Either side of the step: batches of pairs and counterfactual inputs.  */
 /* err_flag: device int the kernels set to non-zero on an out-of-range index (the wrapper checks it). */

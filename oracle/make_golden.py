@@ -201,10 +201,86 @@ def golden_ioi():
     print("wrote ioi.npz", len(res), "arrays")
 
 
+def _ioi_ablation_setup(bias):
+    """Small IOI pair (as golden_ioi) on 48 prompts with 4 names; `bias` is added to one name's unembed bias so that the
+    accuracy-based statistics are not trivially zero."""
+    import iit.model_pairs as mp
+    from iit.tasks.ioi import corr, IOI_HL
+    import transformer_lens
+    V, N = 101, 48
+    cfg = dict(n_layers=6, n_heads=4, d_model=64, d_head=16, d_mlp=128, d_vocab=V, n_ctx=32, act_fn="gelu_new",
+               normalization_type="LNPre", init_weights=True, device="cpu")
+    ll = transformer_lens.HookedTransformer(cfg)
+    sd, data, names = restate.ioi_ablation_fixture(bias)
+    ll.load_state_dict(sd, strict=False)
+    hl = IOI_HL(d_vocab=V, names=names)
+    pair = mp.IOI_ModelPair(ll_model=ll, hl_model=hl, corr=corr, training_args={"next_token": False})
+    ll.eval()
+    return pair, data
+
+
+def golden_ioi_ablations():
+    """iit/utils/eval_ablations.py run unmodified: resample (KL), mean and zero ablation."""
+    from iit.utils import eval_ablations as ea
+    from iit.utils.eval_datasets import IITUniqueDataset
+    from iit.utils.iit_dataset import IITDataset
+    from iit.model_pairs.nodes import LLNode
+    from iit.utils.index import Ix
+
+    def key(n):
+        return f"{n.name}|{n.index}"
+
+    res = {}
+    pair, data = _ioi_ablation_setup(0.0)
+    ds = IITDataset(data, data, seed=0, device="cpu")
+    for nt in ("n", "c"):
+        torch.manual_seed(0)
+        with torch.no_grad():
+            r = ea.check_causal_effect(pair, ds, batch_size=16, node_type=nt)
+        res[f"resample_kl/{nt}/nodes"] = np.array([key(n) for n in r])
+        res[f"resample_kl/{nt}/values"] = np.array(list(r.values()), dtype=np.float64)
+    uni = IITUniqueDataset(data, data, seed=0, device="cpu")
+    torch.manual_seed(0)
+    with torch.no_grad():
+        mc = ea.get_mean_cache(pair, uni, batch_size=16)
+    for name in ("blocks.1.attn.hook_z", "blocks.2.mlp.hook_post", "blocks.0.hook_resid_pre"):
+        res[f"mean_cache/{name}"] = mc[name]
+    # logits of the base run with one node mean- / zero-ablated, first 8 prompts
+    x8 = torch.stack([d[0] for d in data[:8]])
+    for node in (LLNode("blocks.1.attn.hook_z", Ix[:, :, 2, :]), LLNode("blocks.3.mlp.hook_post", Ix[[None]])):
+        for use_mean in (True, False):
+            hook = ea.make_ablation_hook(node, mc, use_mean)
+            with torch.no_grad():
+                out = pair.ll_model.run_with_hooks(x8, fwd_hooks=[(node.name, hook)])
+            res[f"ablated_logits/{key(node)}/{'mean' if use_mean else 'zero'}"] = out[:, -1, :]
+    # the statistics themselves where every decision has a wide margin (one name's bias + 4)
+    pair4, data4 = _ioi_ablation_setup(4.0)
+    uni4 = IITUniqueDataset(data4, data4, seed=0, device="cpu")
+    for use_mean in (True, False):
+        torch.manual_seed(0)
+        with torch.no_grad():
+            mc4 = ea.get_mean_cache(pair4, uni4, batch_size=16) if use_mean else None
+            a = ea.check_causal_effect_on_ablation(pair4, uni4, batch_size=16, node_type="n", mean_cache=mc4)
+            b = ea.check_causal_effect_on_ablation(pair4, uni4, batch_size=16, node_type="c", mean_cache=mc4)
+        tag = "mean" if use_mean else "zero"
+        res[f"ablate/{tag}/n/nodes"] = np.array([key(n) for n in a])
+        res[f"ablate/{tag}/n/values"] = np.array(list(a.values()), dtype=np.float64)
+        res[f"ablate/{tag}/c/nodes"] = np.array([key(n) for n in b])
+        res[f"ablate/{tag}/c/values"] = np.array(list(b.values()), dtype=np.float64)
+    with torch.no_grad():
+        base_ll = pair4.ll_model(torch.stack([d[0] for d in data4]))[:, -1, :]
+        base_hl = pair4.hl_model((torch.stack([d[0] for d in data4]), None, None))[:, -1, :]
+    res["ablate/base_accuracy"] = (base_ll.argmax(-1) == base_hl.argmax(-1)).float().mean()
+    np.savez_compressed(os.path.join(OUT, "ioi_ablations.npz"), **to_np(res))
+    print("wrote ioi_ablations.npz", len(res), "arrays")
+
+
 if __name__ == "__main__":
     ref_env.setup()
     import iit.model_pairs  # noqa: F401  (import first: the reference has an import cycle otherwise)
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(4)
-    golden_pvr()
-    golden_ioi()
+    if "ablations" not in sys.argv[1:]:
+        golden_pvr()
+        golden_ioi()
+    golden_ioi_ablations()

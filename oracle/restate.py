@@ -666,3 +666,110 @@ def transformer_state_dict(seed=0, n_layers=6, n_heads=4, d_model=64, d_head=16,
     w("unembed.W_U", d_model, d_vocab)
     sd["unembed.b_U"] = torch.zeros(d_vocab)
     return sd
+
+
+def ioi_ablation_fixture(bias: float, n=48, d_vocab=101, n_names=4):
+    """Weights, samples and names of the ablation-evaluation fixtures (oracle/make_golden.py:golden_ioi_ablations):
+    the small IOI transformer with `bias` added to one name's unembed bias, `n` prompts over `n_names` names."""
+    sd = transformer_state_dict(0, d_mlp=128, d_vocab=d_vocab, n_ctx=32)
+    (x, y, iv), names = synthetic_ioi(n, 100, d_vocab=d_vocab, n_names=n_names)
+    sd = dict(sd)
+    b = sd["unembed.b_U"].clone()
+    b[names[1]] += bias
+    sd["unembed.b_U"] = b
+    data = [(x[i], y[i], iv[i]) for i in range(n)]
+    return sd, data, names
+
+
+# --------------------------------------------------------------------------------------------
+# ablation evaluations (iit/utils/eval_ablations.py, eval_metrics.py) -- SURVEY.md 8(f) row 2
+# --------------------------------------------------------------------------------------------
+def kl_div_rows(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """eval_metrics.py:4-20 -- rows that do not sum to 1 are softmaxed; KL(b || a) summed over classes."""
+    def pmf(x):
+        s = x.sum(dim=-1)
+        return x if torch.allclose(s, torch.ones_like(s)) else F.softmax(x, dim=-1)
+    return F.kl_div(pmf(a).log(), pmf(b), reduction="none", log_target=False).sum(dim=-1)
+
+
+def pair_batches(n_items, dataset_seed, batch_size, n_base=None, n_abl=None):
+    """Batches of (base row, ablation row) exactly as IITDataset + DataLoader(shuffle=True) form them
+    (iit_dataset.py:24-72): per-item numpy pair rule, item order from torch's global RNG (seed it before calling)."""
+    n_base = n_items if n_base is None else n_base
+    n_abl = n_items if n_abl is None else n_abl
+    table = []
+    for i in range(n_items):
+        rng = np.random.default_rng(dataset_seed * 1000000 + i)
+        table.append((int(rng.choice(n_base)), int(rng.choice(n_abl))))
+    loader = torch.utils.data.DataLoader(range(n_items), batch_size=batch_size, shuffle=True, collate_fn=list)
+    return [[table[i] for i in items] for items in loader]
+
+
+def unique_batches(n_items, batch_size):
+    """Item batches of IITUniqueDataset.make_loader (eval_datasets.py:7-19): the same shuffled DataLoader over rows."""
+    return list(torch.utils.data.DataLoader(range(n_items), batch_size=batch_size, shuffle=True, collate_fn=list))
+
+
+def resample_kl_effects(ll, names, d_vocab, data, nodes, batch_size, dataset_seed=0):
+    """check_causal_effect with the KL metric (eval_ablations.py:35-61,128-161) for IOI: label index = last position.
+    `nodes`: [(hook name, index spec)]. Returns one float per node (mean over batches of the batch-mean KL)."""
+    x = torch.stack([d[0] for d in data])
+    batches = pair_batches(len(data), dataset_seed, batch_size)
+    out = [0.0] * len(nodes)
+    with torch.no_grad():
+        for rows in batches:
+            bx = x[[r[0] for r in rows]]
+            ax = x[[r[1] for r in rows]]
+            hl = ioi_hl_forward(bx, names, d_vocab)[:, -1, :]
+            for k, node in enumerate(nodes):
+                ll_out, _ = ll_intervention(ll, bx, ax, [node])
+                out[k] += kl_div_rows(ll_out[:, -1, :], hl).mean().item()
+    return [v / len(batches) for v in out]
+
+
+def mean_cache(ll, data, names, batch_size):
+    """get_mean_cache (eval_ablations.py:164-173): sum over batches of batch-mean / number of batches."""
+    x = torch.stack([d[0] for d in data])
+    batches = unique_batches(len(data), batch_size)
+    out = {}
+    with torch.no_grad():
+        for items in batches:
+            cache = {}
+            ll(x[items], cache=cache, cache_filter=set(names))
+            for name, tensor in cache.items():
+                if name not in out:
+                    out[name] = torch.zeros_like(tensor[0].unsqueeze(0))
+                out[name] += tensor.mean(dim=0).unsqueeze(0) / len(batches)
+    return out
+
+
+def ablated_logits(ll, x, node, mean=None):
+    """Base run with the node's slice overwritten by the dataset mean, or zeros (eval_ablations.py:176-193)."""
+    name, spec = node
+    idx = as_index(spec)
+
+    def hook(act):
+        out = act.clone()
+        out[idx] = 0 if mean is None else mean[name].expand_as(act)[idx]
+        return out
+
+    with torch.no_grad():
+        return ll(x, hooks={name: hook})
+
+
+def ablation_effects(ll, names, d_vocab, data, nodes, batch_size, mean=None):
+    """check_causal_effect_on_ablation (eval_ablations.py:196-237,262-295): per node, mean over batches of
+    #(correct before, prediction != HL after) / (#correct before + 1e-6)."""
+    x = torch.stack([d[0] for d in data])
+    batches = unique_batches(len(data), batch_size)
+    out = [0.0] * len(nodes)
+    with torch.no_grad():
+        for items in batches:
+            bx = x[items]
+            hl_top = ioi_hl_forward(bx, names, d_vocab)[:, -1, :].argmax(-1)
+            base_top = ll(bx)[:, -1, :].argmax(-1)
+            acc = (base_top == hl_top).float()
+            for k, node in enumerate(nodes):
+                top = ablated_logits(ll, bx, node, mean)[:, -1, :].argmax(-1)
+                out[k] += (((top != hl_top).float() * acc).sum().item()) / (acc.sum().item() + 1e-6)
+    return [v / len(batches) for v in out]

@@ -210,3 +210,45 @@ def test_ioi_do_intervention_and_train(ioi):
     np.testing.assert_allclose(ev["val/iit_loss"], float(ioi["eval/val/iit_loss"]), rtol=1e-3)
     np.testing.assert_allclose(pair.ll.p["blocks.3.mlp.W_in"][:4, :8].detach().numpy(), ioi["final/b3_W_in"],
                                rtol=1e-3, atol=1e-6)
+
+
+# ------------------------------------------------------------------------------------------ ablation evaluations
+def _parse_node(key):
+    """'blocks.1.attn.hook_z|[:, :, 2, :]' -> (name, index spec) of the oracle."""
+    name, idx = key.split("|")
+    parts = [p.strip() for p in idx.strip("[]").split(",")]
+    spec = tuple(None if p == ":" else int(p) for p in parts)
+    return name, (None if spec == (None,) else spec)
+
+
+def test_ablation_evaluations_match_reference_golden():
+    """oracle/restate.py's restatement of iit/utils/eval_ablations.py + eval_metrics.py against the fixtures the
+    unmodified reference produced (oracle/make_golden.py:golden_ioi_ablations): resample-ablation KL per node, the mean
+    cache, mean- / zero-ablated logits, and the accuracy-based statistics."""
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ioi_ablations.npz"))
+    sd, data, names = R.ioi_ablation_fixture(0.0)
+    ll = R.TransformerOracle(sd, 6, 4, 16).eval()
+    for nt in ("n", "c"):
+        nodes = [_parse_node(k) for k in g[f"resample_kl/{nt}/nodes"].tolist()]
+        torch.manual_seed(0)
+        got = R.resample_kl_effects(ll, names, 101, data, nodes, 16)
+        np.testing.assert_allclose(got, g[f"resample_kl/{nt}/values"], rtol=1e-4)
+    torch.manual_seed(0)
+    mc = R.mean_cache(ll, data, ["blocks.1.attn.hook_z", "blocks.2.mlp.hook_post", "blocks.3.mlp.hook_post"], 16)
+    for name in ("blocks.1.attn.hook_z", "blocks.2.mlp.hook_post"):
+        np.testing.assert_allclose(mc[name].numpy(), g[f"mean_cache/{name}"], rtol=1e-4, atol=1e-5)
+    x8 = torch.stack([d[0] for d in data[:8]])
+    for key in ("blocks.1.attn.hook_z|[:, :, 2, :]", "blocks.3.mlp.hook_post|[:]"):
+        node = _parse_node(key)
+        for tag, mean in (("mean", mc), ("zero", None)):
+            out = R.ablated_logits(ll, x8, node, mean)[:, -1, :]
+            np.testing.assert_allclose(out.numpy(), g[f"ablated_logits/{key}/{tag}"], rtol=1e-3, atol=1e-4)
+    sd4, data4, names4 = R.ioi_ablation_fixture(4.0)
+    ll4 = R.TransformerOracle(sd4, 6, 4, 16).eval()
+    for tag in ("mean", "zero"):
+        for nt in ("n", "c"):
+            nodes = [_parse_node(k) for k in g[f"ablate/{tag}/{nt}/nodes"].tolist()]
+            torch.manual_seed(0)
+            mean = R.mean_cache(ll4, data4, sorted({n for n, _ in nodes}), 16) if tag == "mean" else None
+            got = R.ablation_effects(ll4, names4, 101, data4, nodes, 16, mean)
+            np.testing.assert_allclose(got, g[f"ablate/{tag}/{nt}/values"], atol=1e-6)
