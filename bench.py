@@ -283,20 +283,21 @@ def run_ioi_extra(rank, world, dev, dp, batch=1024, steps=3, warmup=2):
     (bx, by, bv), names = R.synthetic_ioi(batch, 21 + 2 * rank, one_hot=False)
     (sx, sy, sv), _ = R.synthetic_ioi(batch, 22 + 2 * rank, one_hot=False)
     hl = IOI_HL(50257, names).to(dev)
-    pair = IOI_ModelPair(hl, ll, corr, training_args={"lr": 1e-3, "batch_size": batch, "lr_scheduler": None})
+    pair = IOI_ModelPair(hl, ll, corr, training_args={"lr": 1e-3, "batch_size": batch, "lr_scheduler": None, "cuda_graphs": True})
     if world > 1:
         pair.dp = dp
     opt = pair.make_optimizer()
     ll.train()
     base = tuple(t.to(dev) for t in (bx, by, bv))
     src = tuple(t.to(dev) for t in (sx, sy, sv))
+    pair.prepare_graphs(base, src, pair.loss_fn, opt)   # 4 HL nodes + 8 strict nodes + behaviour, captured before timing
     for _ in range(warmup):
         pair.run_train_step(base, src, pair.loss_fn, opt)
     sec, m = _timed_region(dp, dev, lambda: pair.run_train_step(base, src, pair.loss_fn, opt), steps)
     return {"metric": "ioi_iit_train_pairs_per_sec", "value": batch * world * steps / sec, "unit": UNIT, "ms_per_step": 1e3 * sec / steps,
             "config": {"workload": f"IOI strict-IIT train step (train_ioi.py), HookedTransformer 6L/4H/d64/d_mlp 3072/vocab 50257, "
                                    f"batch {batch} prompts/GPU x 16 tokens, bf16 activations (fp32 master weights), integer labels, "
-                                   f"last-position unembed",
+                                   f"last-position unembed, CUDA-graph replay per (term, node)",
                        "baseline_config": "configs[2]" if world == 1 else "configs[3]", "parallelism": f"dp{world}"},
             "steps": steps, "warmup": warmup, "dtype": "bf16", "last_step_metrics": m}
 

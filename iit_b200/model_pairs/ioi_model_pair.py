@@ -61,6 +61,10 @@ class IOI_ModelPair(StrictIITModelPair):
         """[B,S] int64 ids from one-hot [B,S,V] labels (one argmax pass per batch tensor, memoised)."""
         if base_y.dtype == t.int64:
             return base_y
+        if ops.capturing():
+            # a captured graph must recompute the ids from the static label buffer at every replay: a memoised tensor
+            # would hold whatever batch some other graph last processed
+            return ops.argmax_rows(base_y.reshape(-1, base_y.shape[-1])).view(base_y.shape[:-1])
         ref, version, ids = self._label_cache
         if ref is None or ref() is not base_y or version != base_y._version:  # same tensor object, unmodified
             ids = ops.argmax_rows(base_y.reshape(-1, base_y.shape[-1])).view(base_y.shape[:-1])

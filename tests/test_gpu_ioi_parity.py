@@ -268,3 +268,23 @@ def test_bf16_transformer_close_to_fp32_path_full_vocab():
     assert (lf - lb).abs().max().item() <= 3e-2 * (lf.max() - lf.min()).item()
     for k, v in out[torch.float32][1].items():
         assert rel(out[torch.bfloat16][1][k], v) < 5e-2, (k, out)
+
+
+def test_ioi_cuda_graph_step_equals_eager_step():
+    """IOI strict train step replayed from captured CUDA graphs (one per loss term and node) against the eager path:
+    same kernels in the same order, so three free-running steps agree to fp32 rounding of atomically ordered sums;
+    capture leaves model and optimizer untouched."""
+    res = {}
+    for mode in ("eager", "graphs"):
+        pair, _ = make_pair({"cuda_graphs": mode == "graphs"})
+        opt = pair.make_optimizer()
+        pair.ll_model.train()
+        if mode == "graphs":
+            before = {k: v.clone() for k, v in pair.ll_model.state_dict().items()}
+            pair.prepare_graphs(dev(batch(100)), dev(batch(200)), pair.loss_fn, opt)
+            assert all(torch.equal(before[k], v) for k, v in pair.ll_model.state_dict().items())
+            assert opt.step_count == 0 and len(pair._graphs) == 4 + 8 + 1
+        res[mode] = [pair.run_train_step(dev(batch(100 + i)), dev(batch(200 + i)), pair.loss_fn, opt) for i in range(3)]
+    for e, g in zip(res["eager"], res["graphs"]):
+        for k in e:
+            assert rel(g[k], e[k]) < 1e-4, (k, e, g)
