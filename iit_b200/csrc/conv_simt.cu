@@ -359,14 +359,15 @@ __global__ void filter_relayout_kernel(const float* __restrict__ w, T* __restric
 // in device memory at a fixed address, so the launch can be replayed from a CUDA graph after each optimizer update)
 __global__ void __launch_bounds__(256) filter_relayout_batched_kernel(const iit_relayout_t* __restrict__ table) {
   const iit_relayout_t e = table[blockIdx.y];
-  const int64_t n = (int64_t)e.k * e.c * e.r * e.s;
+  const uint32_t n = (uint32_t)e.k * e.c * e.r * e.s;            // 32-bit index arithmetic (host checks n < 2^31)
   const float* __restrict__ w = static_cast<const float*>(e.w);
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    int64_t rem = i;   // i indexes the OUTPUT layout
-    int k, c, r, s;
-    if (!e.to_crsk) { c = rem % e.c; rem /= e.c; s = rem % e.s; rem /= e.s; r = rem % e.r; k = (int)(rem / e.r); }
-    else { k = rem % e.k; rem /= e.k; s = rem % e.s; rem /= e.s; r = rem % e.r; c = (int)(rem / e.r); }
-    const float v = w[k * e.stride[0] + c * e.stride[1] + r * e.stride[2] + s * e.stride[3]];
+  const uint32_t C = e.c, K = e.k, R = e.r, S = e.s;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    uint32_t rem = i;   // i indexes the OUTPUT layout
+    uint32_t k, c, r, s;
+    if (!e.to_crsk) { c = rem % C; rem /= C; s = rem % S; rem /= S; r = rem % R; k = rem / R; }
+    else { k = rem % K; rem /= K; s = rem % S; rem /= S; r = rem % R; c = rem / R; }
+    const float v = w[(int64_t)k * e.stride[0] + (int64_t)c * e.stride[1] + (int64_t)r * e.stride[2] + (int64_t)s * e.stride[3]];
     if (e.dtype == IIT_BF16) static_cast<__nv_bfloat16*>(e.out)[i] = __float2bfloat16_rn(v);
     else static_cast<float*>(e.out)[i] = v;
   }
@@ -492,7 +493,7 @@ extern "C" int iit_filter_relayout(const float* w, const int64_t* strides_kcrs, 
 }
 
 extern "C" int iit_filter_relayout_batched(const iit_relayout_t* table_dev, int entries, int64_t max_elements, void* stream) {
-  IIT_REQUIRE(table_dev && entries >= 1 && max_elements >= 1, "iit_filter_relayout_batched: bad arguments");
+  IIT_REQUIRE(table_dev && entries >= 1 && max_elements >= 1 && max_elements < (1ll << 31), "iit_filter_relayout_batched: bad arguments");
   int bx = (int)((max_elements + 256 * 8 - 1) / (256 * 8));
   if (bx > 64) bx = 64;
   if (bx < 1) bx = 1;

@@ -173,6 +173,9 @@ class BaseModelPair(ABC):
         return st[1], st[2]
 
     def _graphed_term(self, key, optimizer, build_loss):
+        stale = getattr(self.ll_model, "_filter_shadow_stale", None)
+        if stale is not None and stale():    # weights changed outside the optimizer (load_state_dict, manual edits)
+            self.ll_model.refresh_filter_shadow()
         graphs = self.__dict__.setdefault("_graphs", {})
         ent = graphs.get(key)
         if ent is None:
@@ -196,6 +199,8 @@ class BaseModelPair(ABC):
         with t.no_grad():
             for b, s in zip(buffers, snap_buf):
                 b.copy_(s)
+        for cb in getattr(optimizer, "post_step", ()):   # copies derived from the weights (bf16 filter shadows) follow the
+            cb()                                         # restore here, eagerly: the graph then starts from fresh copies
         graph = t.cuda.CUDAGraph()
         with t.cuda.graph(graph, pool=self._graph_pool):
             loss = build_loss()
