@@ -94,6 +94,56 @@ __global__ void __launch_bounds__(128) stem_s2d_kernel(const T* __restrict__ x, 
   }
 }
 
+// Whole image per block (images up to 63 x 63): the image is staged in shared memory with flat coalesced reads (16-byte
+// loads when it is dense NCHW fp32), then the s2d pixels - 32 contiguous bytes each, the whole output image one contiguous
+// run - are written back to back.
+template <typename T>
+__global__ void __launch_bounds__(256) stem_s2d_image_kernel(const T* __restrict__ x, int64_t sn, int64_t sc, int64_t sh, int64_t sw,
+                                                             __nv_bfloat16* __restrict__ out, int N, int H, int W, int SH, int SW,
+                                                             int dense) {
+  extern __shared__ float img[];             // [3][H][W]
+  const int HW = H * W;
+  for (int n = blockIdx.x; n < N; n += gridDim.x) {
+    const T* src = x + (int64_t)n * sn;
+    if (dense && sizeof(T) == 4 && (HW * 3) % 4 == 0) {
+      const float4* s4 = reinterpret_cast<const float4*>(src);
+      for (int i = threadIdx.x; i < HW * 3 / 4; i += blockDim.x) reinterpret_cast<float4*>(img)[i] = s4[i];
+    } else {
+      for (int i = threadIdx.x; i < HW * 3; i += blockDim.x) {
+        const int c = i / HW, r = i - c * HW, h = r / W, w = r - h * W;
+        img[i] = to_f<T>(src[c * sc + h * sh + w * sw]);
+      }
+    }
+    __syncthreads();
+    uint4* dst = reinterpret_cast<uint4*>(out + (int64_t)n * SH * SW * 16);
+    for (int i = threadIdx.x; i < SH * SW * 2; i += blockDim.x) {     // two 16-byte halves per s2d pixel
+      const int pix = i >> 1, half = i & 1;
+      const int sy = pix / SW, sx = pix - sy * SW;
+      float v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int ch = half * 8 + j;         // (a*2+b)*3+c for ch < 12, zero above
+        float val = 0.f;
+        if (ch < 12) {
+          const int ab = ch / 3, c = ch - ab * 3, a = ab >> 1, b = ab & 1;
+          const int ih = 2 * sy + a - 3, iw = 2 * sx + b - 3;
+          if (ih >= 0 && ih < H && iw >= 0 && iw < W) val = img[c * HW + ih * W + iw];
+        }
+        v[j] = val;
+      }
+      uint4 o;
+      uint32_t* w32 = reinterpret_cast<uint32_t*>(&o);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        __nv_bfloat162 h2 = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+        w32[j] = *reinterpret_cast<uint32_t*>(&h2);
+      }
+      dst[i] = o;
+    }
+    __syncthreads();
+  }
+}
+
 // w [64,3,7,7] -> w2 [64][R 4][S 4][16]: w2[k,R,S,(a*2+b)*3+c] = w[k,c,2R+a,2S+b] (zero where 2R+a or 2S+b is 7)
 __global__ void stem_filter_s2d_kernel(const float* __restrict__ w, int64_t sk, int64_t sc, int64_t sr, int64_t ss,
                                        __nv_bfloat16* __restrict__ w2) {
@@ -122,6 +172,18 @@ extern "C" int iit_stem_s2d(const void* x, int dtype, const int64_t* strides_nch
   IIT_REQUIRE(smem <= 48 * 1024, "iit_stem_s2d: image width %d too large for the staging tile", w);
   IIT_REQUIRE((int64_t)n * SH < (1ll << 31), "iit_stem_s2d: too many rows");
   cudaStream_t st = as_stream(stream);
+  const size_t img_smem = (size_t)3 * h * w * sizeof(float);
+  if (img_smem <= 48 * 1024) {
+    const int dense = strides_nchw[3] == 1 && strides_nchw[2] == w && strides_nchw[1] == (int64_t)h * w &&
+                      (reinterpret_cast<uintptr_t>(x) & 15) == 0 && ((strides_nchw[0] * (dtype == IIT_F32 ? 4 : 2)) & 15) == 0;
+    const int grid = n < kNumSMs * 4 ? n : kNumSMs * 4;
+    IIT_DISPATCH_DTYPE(dtype, T, {
+      stem_s2d_image_kernel<T><<<grid, 256, img_smem, st>>>((const T*)x, strides_nchw[0], strides_nchw[1], strides_nchw[2],
+                                                           strides_nchw[3], (__nv_bfloat16*)s2d, n, h, w, SH, SW, dense);
+    })
+    IIT_LAUNCH_CHECK("iit_stem_s2d");
+    return 0;
+  }
   IIT_DISPATCH_DTYPE(dtype, T, {
     stem_s2d_kernel<T><<<(unsigned)(n * SH), 128, smem, st>>>((const T*)x, strides_nchw[0], strides_nchw[1], strides_nchw[2],
                                                              strides_nchw[3], (__nv_bfloat16*)s2d, h, w, SH, SW);
