@@ -302,7 +302,7 @@ def run_ioi_extra(rank, world, dev, dp, batch=1024, steps=3, warmup=2):
             "steps": steps, "warmup": warmup, "dtype": "bf16", "last_step_metrics": m}
 
 
-def run_sweep_extra(rank, world, dev, dp, batch=1024, batches_per_rank=2):
+def run_sweep_extra(rank, world, dev, dp, batch=4096, batches_per_rank=2):
     """BASELINE.json configs[4]: the causality sweep of eval_causality.py -- 17 hook points x 4 HL nodes, counterfactuals
     generated on the device, batches sharded over ranks, counts gathered at the end. One "pair" = one (base,
     counterfactual) interchange evaluation (two LL forwards, the source one truncated at the hook point)."""
