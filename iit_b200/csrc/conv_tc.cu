@@ -90,9 +90,12 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0 && nk > 0) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+    if (nk > 0) {   // warp-uniform loop, one elected lane issues: the producer must stay far below the MMA time per k-block
+      const bool issuer = elect_one();
+      if (issuer) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+      }
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -104,23 +107,28 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
           if (t >= mtiles) t = mtiles - 1;            // odd tail: the box is loaded twice, its second copy never stored
           const int tw = t % p.tiles_w; t /= p.tiles_w;
           const int th = t % p.tiles_h; t /= p.tiles_h;
-          n0[mt] = t * p.BNI; p0[mt] = th * p.BH; q0[mt] = tw * p.BW;
+          n0[mt] = t * p.BNI; p0[mt] = th * p.BH * p.in_mul; q0[mt] = tw * p.BW * p.in_mul;
         }
-        for (int kb = 0; kb < nk; ++kb) {
-          const int tap = kb / kchunks, kc = kb - tap * kchunks;
-          mbar_wait(&empty[stage], phase ^ 1);
-          mbar_expect_tx(&full[stage], MT * A_BYTES + B_BYTES);
+        for (int tap = 0; tap < p.ntaps; ++tap) {
+          const int dh = p.dh[tap], dw = p.dw[tap], wk0 = p.wk[tap] * p.Cin;
+          for (int kc = 0; kc < p.Cin; kc += TC_BK) {
+            mbar_wait(&empty[stage], phase ^ 1);
+            if (issuer) {
+              mbar_expect_tx(&full[stage], MT * A_BYTES + B_BYTES);
 #pragma unroll
-          for (int mt = 0; mt < MT; ++mt)
-            tma_load_4d(sA + (stage * MT + mt) * A_BYTES, &map_a, &full[stage], kc * TC_BK, q0[mt] * p.in_mul + p.dw[tap],
-                        p0[mt] * p.in_mul + p.dh[tap], n0[mt]);
-          tma_load_2d(sB + stage * B_BYTES, &map_b, &full[stage], p.wk[tap] * p.Cin + kc * TC_BK, co0);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+              for (int mt = 0; mt < MT; ++mt)
+                tma_load_4d(sA + (stage * MT + mt) * A_BYTES, &map_a, &full[stage], kc, q0[mt] + dw, p0[mt] + dh, n0[mt]);
+              tma_load_2d(sB + stage * B_BYTES, &map_b, &full[stage], wk0 + kc, co0);
+            }
+            __syncwarp();
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && nk > 0) {
+    if (nk > 0) {   // the whole warp runs the loop; the elected lane issues (see elect_one)
+      const bool issuer = elect_one();
       // instruction descriptor: D=f32, A=B=bf16, both K-major, N at [17,23), M at [24,29)
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
       int stage = 0;
@@ -139,16 +147,20 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
           mbar_wait(&full[stage], phase);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t a_lo = a_lo0 + stage * (MT * A_BYTES >> 4), b_lo = b_lo0 + stage * (B_BYTES >> 4);
+          if (issuer) {
 #pragma unroll
-          for (int mt = 0; mt < MT; ++mt)
+            for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
-            for (int k = 0; k < TC_BK / TC_UK; ++k)
-              umma_bf16_lohi(tmem_d + mt * BN, a_lo + mt * (A_BYTES >> 4) + 2 * k, desc_hi, b_lo + 2 * k, desc_hi, idesc,
-                             (uint32_t)((kb | k) != 0));
-          umma_commit(&empty[stage]);  // frees this smem stage once the MMAs above have read it
+              for (int k = 0; k < TC_BK / TC_UK; ++k)
+                umma_bf16_lohi(tmem_d + mt * BN, a_lo + mt * (A_BYTES >> 4) + 2 * k, desc_hi, b_lo + 2 * k, desc_hi, idesc,
+                               (uint32_t)((kb | k) != 0));
+            umma_commit(&empty[stage]);  // frees this smem stage once the MMAs above have read it
+          }
+          __syncwarp();
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tmem_full[acc]);  // accumulator complete
+        if (issuer) umma_commit(&tmem_full[acc]);  // accumulator complete
+        __syncwarp();
       }
     }
   } else {
@@ -273,6 +285,215 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// CTA-pair variant (tcgen05 cta_group::2) for layers with a multiple of 256 filters: the two CTAs of a cluster compute
+// a tile of 256 pixels x 256 filters. Each CTA loads ITS pixel box (128 x 64 per k-block) and HALF of the filter block
+// (128 x 64); the leader issues M=256, N=256 MMAs that read both halves. Per CTA and k-block that is 32 KB from L2 for
+// 128 x 256 x 64 MACs - 128 FLOP per byte against 87 for the single-CTA 128 x 256 tile, which sat on the L2->SMEM limit -
+// and 8 KB of shared-memory reads per 128 tensor cycles instead of 12.
+// Barriers: `full` lives in the leader (both CTAs' TMA loads credit it); `empty` and `tmem_full` exist in both CTAs and
+// are signalled by multicast commits; `tmem_empty` lives in the leader and is arrived on by the epilogue warps of both.
+// ------------------------------------------------------------------------------------------------------------------
+// BN = filters per tile (accumulator columns per CTA); each CTA loads BN / 2 filter rows. BN = 128 gives tiles of half the
+// size at the traffic per FLOP of the single-CTA 128 x 256 tile: it is chosen when it fills the last wave better.
+template <int BN, int STAGES>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
+conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                   __nv_bfloat16* __restrict__ out, TcParams p, double* __restrict__ bn_sum, double* __restrict__ bn_sq) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr int BHALF = BN / 2;
+  constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2, B_BYTES = BHALF * TC_BK * 2;
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + STAGES * A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * B_BYTES);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tmem_full = empty + STAGES;      // [2]
+  uint64_t* tmem_empty = tmem_full + 2;      // [2] (the leader's are used)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [2][BN]
+  if (bn_sum != nullptr)
+    for (int i = threadIdx.x; i < 2 * BN; i += TC_THREADS) s_stat[i] = 0.f;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+  const int kchunks = p.Cin / TC_BK;
+  const int nk = p.ntaps * kchunks;
+  const int nblk = p.Cout / BN;
+  const int mtiles = p.tiles_w * p.tiles_h * p.tiles_n;
+  const int total_tiles = ((mtiles + 1) / 2) * nblk;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 8); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {  // the same warp of both CTAs allocates (and frees) the pair's TMEM columns
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(2 * BN));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  cluster_sync_all();   // barriers of both CTAs initialised, TMEM allocated
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0 && nk > 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = pair; tile < total_tiles; tile += npairs) {
+        const int co0 = (tile % nblk) * BN;
+        int t = (tile / nblk) * 2 + (int)rank;
+        if (t >= mtiles) t = mtiles - 1;              // odd tail: the peer repeats the last box, its copy is never stored
+        const int tw = t % p.tiles_w; t /= p.tiles_w;
+        const int th = t % p.tiles_h; t /= p.tiles_h;
+        const int n0 = t * p.BNI, p0 = th * p.BH, q0 = tw * p.BW;
+        for (int kb = 0; kb < nk; ++kb) {
+          const int tap = kb / kchunks, kc = kb - tap * kchunks;
+          mbar_wait(&empty[stage], phase ^ 1);        // multicast commit of the leader's MMAs: this CTA's stage is free
+          const uint32_t lead_full = mapa_u32(smem_u32(&full[stage]), 0);
+          if (rank == 0) mbar_expect_tx(&full[stage], 2 * (A_BYTES + B_BYTES));
+          tma2_load_4d(sA + stage * A_BYTES, &map_a, lead_full, kc * TC_BK, q0 * p.in_mul + p.dw[tap],
+                       p0 * p.in_mul + p.dh[tap], n0);
+          tma2_load_2d(sB + stage * B_BYTES, &map_b, lead_full, p.wk[tap] * p.Cin + kc * TC_BK, co0 + (int)rank * BHALF);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && nk > 0 && rank == 0) {
+      // D=f32, A=B=bf16, K-major; N = BN at [17,23), M = 256 (both CTAs) at [24,29)
+      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0, it = 0;
+      const uint64_t proto = umma_desc_k_sw128(0);
+      const uint32_t desc_hi = (uint32_t)(proto >> 32);
+      const uint32_t a_lo0 = (uint32_t)proto + (smem_u32(sA) >> 4), b_lo0 = (uint32_t)proto + (smem_u32(sB) >> 4);
+      for (int tile = pair; tile < total_tiles; tile += npairs, ++it) {
+        const uint32_t acc = it & 1, acc_phase = (it >> 1) & 1;
+        mbar_wait_cluster(&tmem_empty[acc], acc_phase ^ 1);   // epilogue warps of BOTH CTAs have drained it
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = 0; kb < nk; ++kb) {
+          mbar_wait_cluster(&full[stage], phase);              // both CTAs' loads of this stage have landed
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t a_lo = a_lo0 + stage * (A_BYTES >> 4), b_lo = b_lo0 + stage * (B_BYTES >> 4);
+#pragma unroll
+          for (int k = 0; k < TC_BK / TC_UK; ++k)
+            umma2_bf16_lohi(tmem_d, a_lo + 2 * k, desc_hi, b_lo + 2 * k, desc_hi, idesc, (uint32_t)((kb | k) != 0));
+          umma2_commit_both(&empty[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma2_commit_both(&tmem_full[acc]);
+      }
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int m = quarter * 32 + lane;
+    const int wl = m % p.BW;
+    const int hl = (m / p.BW) % p.BH;
+    const int nl = m / (p.BW * p.BH);
+    const int e = threadIdx.x - 64;
+    constexpr int NCH = BN / 128;
+    double run_s[NCH], run_q[NCH];                         // channels run_co + e + 128 * i
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) { run_s[i] = 0.0; run_q[i] = 0.0; }
+    int run_co = -1;
+    uint32_t it = 0;
+    for (int tile = pair; tile < total_tiles; tile += npairs, ++it) {
+      const int co0 = (tile % nblk) * BN;
+      const uint32_t acc = it & 1, acc_phase = (it >> 1) & 1;
+      const uint32_t lead_empty = mapa_u32(smem_u32(&tmem_empty[acc]), 0);
+      mbar_wait(&tmem_full[acc], acc_phase);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      int t = (tile / nblk) * 2 + (int)rank;
+      const bool box_ok = t < mtiles;
+      const int tw = t % p.tiles_w; t /= p.tiles_w;
+      const int th = t % p.tiles_h; t /= p.tiles_h;
+      const int n = t * p.BNI + nl, pp = th * p.BH + hl, qq = tw * p.BW + wl;
+      const bool ok = box_ok && n < p.N && pp < p.P && qq < p.Q;
+      __nv_bfloat16* dst = out + (((int64_t)n * p.OH + (pp * p.out_mul + p.out_oh)) * p.OW + (qq * p.out_mul + p.out_ow)) * p.Cout + co0;
+#pragma unroll
+      for (int c = 0; c < BN; c += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c), v);
+        if (c + 32 >= BN) {
+          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(lead_empty);
+        }
+        if (ok) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            uint4 o;
+            __nv_bfloat162 h0 = __floats2bfloat162_rn(__uint_as_float(v[j + 0]), __uint_as_float(v[j + 1]));
+            __nv_bfloat162 h1 = __floats2bfloat162_rn(__uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(__uint_as_float(v[j + 4]), __uint_as_float(v[j + 5]));
+            __nv_bfloat162 h3 = __floats2bfloat162_rn(__uint_as_float(v[j + 6]), __uint_as_float(v[j + 7]));
+            o.x = *reinterpret_cast<uint32_t*>(&h0); o.y = *reinterpret_cast<uint32_t*>(&h1);
+            o.z = *reinterpret_cast<uint32_t*>(&h2); o.w = *reinterpret_cast<uint32_t*>(&h3);
+            *reinterpret_cast<uint4*>(dst + c + j) = o;
+          }
+        }
+        if (bn_sum != nullptr) {   // statistics of the stored (bf16-rounded) values; same butterfly as the single-CTA kernel
+          float a[32], b[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            float f = ok ? __bfloat162float(__float2bfloat16_rn(__uint_as_float(v[j]))) : 0.f;
+            a[j] = f; b[j] = f * f;
+          }
+#pragma unroll
+          for (int h = 16; h >= 1; h >>= 1) {
+            const bool up = (lane & h) != 0;
+#pragma unroll
+            for (int i = 0; i < h; ++i) {
+              float sa = up ? a[i] : a[i + h], ka = up ? a[i + h] : a[i];
+              float sb = up ? b[i] : b[i + h], kb = up ? b[i + h] : b[i];
+              a[i] = ka + __shfl_xor_sync(0xffffffffu, sa, h);
+              b[i] = kb + __shfl_xor_sync(0xffffffffu, sb, h);
+            }
+          }
+          atomicAdd(&s_stat[c + lane], a[0]);
+          atomicAdd(&s_stat[BN + c + lane], b[0]);
+        }
+      }
+      if (bn_sum != nullptr) {
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (run_co != co0) {
+#pragma unroll
+          for (int i = 0; i < NCH; ++i) {
+            if (run_co >= 0) { atomicAdd(&bn_sum[run_co + e + 128 * i], run_s[i]); atomicAdd(&bn_sq[run_co + e + 128 * i], run_q[i]); }
+            run_s[i] = 0.0; run_q[i] = 0.0;
+          }
+          run_co = co0;
+        }
+#pragma unroll
+        for (int i = 0; i < NCH; ++i) {
+          const int ch = e + 128 * i;
+          run_s[i] += (double)s_stat[ch]; run_q[i] += (double)s_stat[BN + ch];
+          s_stat[ch] = 0.f; s_stat[BN + ch] = 0.f;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+      }
+    }
+    if (bn_sum != nullptr && run_co >= 0) {
+#pragma unroll
+      for (int i = 0; i < NCH; ++i) { atomicAdd(&bn_sum[run_co + e + 128 * i], run_s[i]); atomicAdd(&bn_sq[run_co + e + 128 * i], run_q[i]); }
+    }
+  }
+  // neither CTA may leave (or free the pair's TMEM) while its peer can still signal its barriers or read its operands
+  __syncwarp();
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  cluster_sync_all();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * BN));
+  }
+}
+
 // ---- host side -----------------------------------------------------------------------------------
 static bool g_tile_pairs = true;
 static bool g_bn256 = true;
@@ -295,6 +516,36 @@ static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16
   int grid = kNumSMs * ctas_per_sm;
   if (grid > total_tiles) grid = total_tiles;
   conv3x3_tc_kernel<BN, STAGES, MT><<<grid, TC_THREADS, smem, st>>>(ma, mb, out, p, bn_sum, bn_sq);
+  return 0;
+}
+
+// CTA-pair launch (256 pixels x BN filters per cluster of two)
+static int g_pair_mode = 1;   // 0 off, 1 on for Cout % 256 == 0
+template <int BN>
+static int launch_tc2(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16* out, const TcParams& p, int total_tiles,
+                      cudaStream_t st, double* bn_sum, double* bn_sq) {
+  constexpr int STAGES = BN == 256 ? 6 : 8;
+  constexpr size_t smem = STAGES * (TC_BM * TC_BK * 2 + (BN / 2) * TC_BK * 2) + (2 * STAGES + 4) * 8 + 16 + 2 * BN * 4 + 1024;
+  static int max_clusters = 0;
+  cudaLaunchConfig_t cfg = {};
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.blockDim = dim3(TC_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if (!max_clusters) {
+    IIT_CUDA(cudaFuncSetAttribute(conv3x3_tc2_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cfg.gridDim = dim3(kNumSMs);
+    int n = 0;
+    IIT_CUDA(cudaOccupancyMaxActiveClusters(&n, conv3x3_tc2_kernel<BN, STAGES>, &cfg));
+    max_clusters = n < 1 ? 1 : (n > kNumSMs / 2 ? kNumSMs / 2 : n);
+  }
+  const int clusters = total_tiles < max_clusters ? total_tiles : max_clusters;
+  cfg.gridDim = dim3(2 * clusters);
+  IIT_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_tc2_kernel<BN, STAGES>, ma, mb, out, p, bn_sum, bn_sq));
   return 0;
 }
 
@@ -347,8 +598,22 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
   const int BN = (tp.Cout % 256 == 0 && g_bn256) ? 256 : (tp.Cout % 128 == 0) ? 128 : 64;
   CUtensorMap ma, mb;
   if (encode_nhwc_strided(&ma, gathered, gC, gW, gH, tp.N, tp.BW, tp.BH, tp.BNI, tp.in_mul, name)) return 1;
-  if (encode_filter(&mb, wmat, Kg, tp.Cout, BN, name)) return 1;
   const int64_t mtiles = (int64_t)tp.tiles_w * tp.tiles_h * tp.tiles_n;
+  if (g_pair_mode && tp.Cout % 256 == 0 && tp.ntaps > 0 && mtiles >= kNumSMs) {
+    // waves of kNumSMs / 2 clusters: take the tile width that wastes less of the last wave (mode 2 / 3 force 256 / 128)
+    const int64_t pairs = (mtiles + 1) / 2, wave = kNumSMs / 2;
+    const int64_t t256 = pairs * (tp.Cout / 256), t128 = pairs * (tp.Cout / 128);
+    const double cost256 = (double)((t256 + wave - 1) / wave) * 2.0, cost128 = (double)((t128 + wave - 1) / wave);
+    const int BN2 = g_pair_mode == 2 ? 256 : g_pair_mode == 3 ? 128 : (cost128 < 0.97 * cost256 ? 128 : 256);
+    if (encode_filter(&mb, wmat, Kg, tp.Cout, BN2 / 2, name)) return 1;
+    const int64_t total2 = BN2 == 256 ? t256 : t128;
+    IIT_REQUIRE(total2 < (1ll << 31), "%s: too many tiles", name);
+    if (BN2 == 256 ? launch_tc2<256>(ma, mb, (__nv_bfloat16*)out, tp, (int)total2, st, bn_sum, bn_sq)
+                   : launch_tc2<128>(ma, mb, (__nv_bfloat16*)out, tp, (int)total2, st, bn_sum, bn_sq)) return 1;
+    IIT_LAUNCH_CHECK(name);
+    return 0;
+  }
+  if (encode_filter(&mb, wmat, Kg, tp.Cout, BN, name)) return 1;
   // two pixel boxes per filter block whenever that still leaves a tile for every SM
   const int MT = (BN == 128 && g_tile_pairs && ((mtiles + 1) / 2) * (tp.Cout / BN) >= kNumSMs) ? 2 : 1;
   const int64_t total = ((mtiles + MT - 1) / MT) * (tp.Cout / BN);
@@ -628,6 +893,12 @@ static bool g_use_win = true;
 }  // namespace iit
 
 using namespace iit;
+
+extern "C" int iit_conv_pair_enable(int on) {
+  const int was = g_pair_mode;
+  g_pair_mode = on;
+  return was;
+}
 
 extern "C" int iit_conv_win_enable(int on) {
   const int was = g_use_win ? 1 : 0;

@@ -589,6 +589,48 @@ def test_shifted_window_conv_is_bit_identical_to_the_tiled_kernel(ops, n, h, w):
     torch.testing.assert_close(res[1][2][1].cpu(), (yb * yb).sum((0, 1, 2)).cpu(), rtol=1e-5, atol=1e-3)
 
 
+@pytest.mark.parametrize("n,h,w,c,k,r,stride,pad", [
+    (1203, 4, 4, 256, 256, 3, 1, 1),      # layer3 body, ragged image count and an odd number of pixel boxes
+    (4750, 2, 2, 512, 512, 3, 1, 1),      # layer4 body: two filter blocks per pixel-box pair
+    (1203, 7, 7, 128, 256, 3, 2, 1),      # layer3 entry (stride 2): pair kernel in fprop only
+    (1203, 7, 7, 128, 256, 1, 2, 0),      # layer3 downsample 1x1
+    (4750, 4, 4, 256, 512, 3, 2, 1),      # layer4 entry: fprop and the parity classes of dgrad (256 produced channels)
+])
+def test_cta_pair_conv_is_bit_identical_to_the_single_cta_kernel(ops, n, h, w, c, k, r, stride, pad):
+    """Layers with a multiple of 256 filters: the cta_group::2 kernel (two SMs per 256 x 256 tile, M = 256 MMAs over both
+    CTAs' operands) accumulates the same products in the same k order as the single-CTA kernel, so fprop and dgrad must
+    agree bit for bit and the BatchNorm sums to fp32 regrouping; the single-CTA kernel is checked against PyTorch above."""
+    import ctypes as C
+    from iit_b200 import _lib
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(n, h, w, c, generator=g).bfloat16().to(DEV)
+    wt = (torch.randn(k, r, r, c, generator=g) * 0.05).bfloat16().to(DEV)
+    wt_crsk = wt.permute(3, 1, 2, 0).contiguous()
+    d = _conv_desc(n, h, w, c, k, r, stride, pad)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    res = {}
+    for on in (1, 2, 3, 0):      # automatic tile width, 256-filter tiles, 128-filter tiles, single-CTA kernel
+        was = _lib.lib.iit_conv_pair_enable(on)
+        try:
+            y = torch.full((n, d.p, d.q, k), 7.0, dtype=torch.bfloat16, device=DEV)
+            dx = torch.full((n, h, w, c), 7.0, dtype=torch.bfloat16, device=DEV)
+            sums = torch.zeros(2, k, dtype=torch.float64, device=DEV)
+            _lib.call("iit_conv2d_fprop_tc", p(x), p(wt), p(y), C.byref(d), p(sums[0]), p(sums[1]), st)
+            _lib.call("iit_conv2d_dgrad_tc", p(y), p(wt_crsk), p(dx), C.byref(d), st)
+            torch.cuda.synchronize()
+            res[on] = (y, dx, sums)
+        finally:
+            _lib.lib.iit_conv_pair_enable(was)
+    for on in (1, 2, 3):
+        assert torch.equal(res[on][0], res[0][0])
+        assert torch.equal(res[on][1], res[0][1])
+        torch.testing.assert_close(res[on][2], res[0][2], rtol=1e-6, atol=1e-6)
+    yb = res[1][0].double()
+    torch.testing.assert_close(res[1][2][0], yb.sum((0, 1, 2)), rtol=1e-5, atol=1e-3)
+    torch.testing.assert_close(res[1][2][1], (yb * yb).sum((0, 1, 2)), rtol=1e-5, atol=1e-3)
+
+
 @pytest.mark.parametrize("n,hw", [(4, 56), (3, 84), (149, 56), (2, 30)])
 def test_stem_space_to_depth_conv_matches_conv2d(ops, n, hw):
     """7x7/2 stem as space-to-depth + 4x4 shifted-window convolution (iit_stem_s2d / iit_stem_filter_s2d /
