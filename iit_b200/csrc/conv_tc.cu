@@ -339,32 +339,41 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0 && nk > 0) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+    if (nk > 0) {   // warp-uniform loops, the elected lane issues (tc_common.cuh: elect_one)
+      const bool issuer = elect_one();
+      if (issuer) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+      }
       int stage = 0;
       uint32_t phase = 0;
+      const uint32_t lead_full0 = mapa_u32(smem_u32(&full[0]), 0);
       for (int tile = pair; tile < total_tiles; tile += npairs) {
-        const int co0 = (tile % nblk) * BN;
+        const int co0 = (tile % nblk) * BN + (int)rank * BHALF;
         int t = (tile / nblk) * 2 + (int)rank;
         if (t >= mtiles) t = mtiles - 1;              // odd tail: the peer repeats the last box, its copy is never stored
         const int tw = t % p.tiles_w; t /= p.tiles_w;
         const int th = t % p.tiles_h; t /= p.tiles_h;
-        const int n0 = t * p.BNI, p0 = th * p.BH, q0 = tw * p.BW;
-        for (int kb = 0; kb < nk; ++kb) {
-          const int tap = kb / kchunks, kc = kb - tap * kchunks;
-          mbar_wait(&empty[stage], phase ^ 1);        // multicast commit of the leader's MMAs: this CTA's stage is free
-          const uint32_t lead_full = mapa_u32(smem_u32(&full[stage]), 0);
-          if (rank == 0) mbar_expect_tx(&full[stage], 2 * (A_BYTES + B_BYTES));
-          tma2_load_4d(sA + stage * A_BYTES, &map_a, lead_full, kc * TC_BK, q0 * p.in_mul + p.dw[tap],
-                       p0 * p.in_mul + p.dh[tap], n0);
-          tma2_load_2d(sB + stage * B_BYTES, &map_b, lead_full, p.wk[tap] * p.Cin + kc * TC_BK, co0 + (int)rank * BHALF);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        const int n0 = t * p.BNI, p0 = th * p.BH * p.in_mul, q0 = tw * p.BW * p.in_mul;
+        for (int tap = 0; tap < p.ntaps; ++tap) {
+          const int dh = p.dh[tap], dw = p.dw[tap], wk0 = p.wk[tap] * p.Cin;
+          for (int kc = 0; kc < p.Cin; kc += TC_BK) {
+            mbar_wait(&empty[stage], phase ^ 1);      // multicast commit of the leader's MMAs: this CTA's stage is free
+            if (issuer) {
+              const uint32_t lead_full = lead_full0 + stage * 8;
+              if (rank == 0) mbar_expect_tx(&full[stage], 2 * (A_BYTES + B_BYTES));
+              tma2_load_4d(sA + stage * A_BYTES, &map_a, lead_full, kc, q0 + dw, p0 + dh, n0);
+              tma2_load_2d(sB + stage * B_BYTES, &map_b, lead_full, wk0 + kc, co0);
+            }
+            __syncwarp();
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && nk > 0 && rank == 0) {
+    if (nk > 0 && rank == 0) {
+      const bool issuer = elect_one();
       // D=f32, A=B=bf16, K-major; N = BN at [17,23), M = 256 (both CTAs) at [24,29)
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
       int stage = 0;
@@ -381,13 +390,17 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
           mbar_wait_cluster(&full[stage], phase);              // both CTAs' loads of this stage have landed
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t a_lo = a_lo0 + stage * (A_BYTES >> 4), b_lo = b_lo0 + stage * (B_BYTES >> 4);
+          if (issuer) {
 #pragma unroll
-          for (int k = 0; k < TC_BK / TC_UK; ++k)
-            umma2_bf16_lohi(tmem_d, a_lo + 2 * k, desc_hi, b_lo + 2 * k, desc_hi, idesc, (uint32_t)((kb | k) != 0));
-          umma2_commit_both(&empty[stage]);
+            for (int k = 0; k < TC_BK / TC_UK; ++k)
+              umma2_bf16_lohi(tmem_d, a_lo + 2 * k, desc_hi, b_lo + 2 * k, desc_hi, idesc, (uint32_t)((kb | k) != 0));
+            umma2_commit_both(&empty[stage]);
+          }
+          __syncwarp();
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        umma2_commit_both(&tmem_full[acc]);
+        if (issuer) umma2_commit_both(&tmem_full[acc]);
+        __syncwarp();
       }
     }
   } else {
@@ -520,7 +533,7 @@ static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16
 }
 
 // CTA-pair launch (256 pixels x BN filters per cluster of two)
-static int g_pair_mode = 1;   // 0 off, 1 on for Cout % 256 == 0
+static int g_pair_mode = 1;   // 0 off; 1 / 2 on for Cout % 256 == 0 with 256-filter tiles; 3 the same with 128-filter tiles
 template <int BN>
 static int launch_tc2(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16* out, const TcParams& p, int total_tiles,
                       cudaStream_t st, double* bn_sum, double* bn_sq) {
@@ -600,11 +613,11 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
   if (encode_nhwc_strided(&ma, gathered, gC, gW, gH, tp.N, tp.BW, tp.BH, tp.BNI, tp.in_mul, name)) return 1;
   const int64_t mtiles = (int64_t)tp.tiles_w * tp.tiles_h * tp.tiles_n;
   if (g_pair_mode && tp.Cout % 256 == 0 && tp.ntaps > 0 && mtiles >= kNumSMs) {
-    // waves of kNumSMs / 2 clusters: take the tile width that wastes less of the last wave (mode 2 / 3 force 256 / 128)
-    const int64_t pairs = (mtiles + 1) / 2, wave = kNumSMs / 2;
+    // 256-filter tiles unless mode 3 asks for 128 (measured: half-width tiles fill the last wave better, 7 waves of 74
+    // clusters instead of 4 on layer3, but pay the pixel box twice and end up slower: 76.6 vs 70.5 us)
+    const int64_t pairs = (mtiles + 1) / 2;
     const int64_t t256 = pairs * (tp.Cout / 256), t128 = pairs * (tp.Cout / 128);
-    const double cost256 = (double)((t256 + wave - 1) / wave) * 2.0, cost128 = (double)((t128 + wave - 1) / wave);
-    const int BN2 = g_pair_mode == 2 ? 256 : g_pair_mode == 3 ? 128 : (cost128 < 0.97 * cost256 ? 128 : 256);
+    const int BN2 = g_pair_mode == 3 ? 128 : 256;
     if (encode_filter(&mb, wmat, Kg, tp.Cout, BN2 / 2, name)) return 1;
     const int64_t total2 = BN2 == 256 ? t256 : t128;
     IIT_REQUIRE(total2 < (1ll << 31), "%s: too many tiles", name);
@@ -746,32 +759,42 @@ __global__ void __launch_bounds__(TC_THREADS) wgrad3x3_tc_kernel(const __grid_co
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_dy)) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_x)) : "memory");
+    {   // warp-uniform loop, the elected lane issues (tc_common.cuh: elect_one); the box walks the pixel grid by counters
+      const bool issuer = elect_one();
+      if (issuer) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_dy)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_x)) : "memory");
+      }
       int stage = 0;
       uint32_t phase = 0;
+      int t = chunk_lo;
+      int tw = t % p.tiles_w; t /= p.tiles_w;
+      int th = t % p.tiles_h;
+      int tn = t / p.tiles_h;
+      const int k0 = kblk * 128, c0 = cblk * CB, roff = r - p.pad;
       for (int ch = chunk_lo; ch < chunk_hi; ++ch) {
-        int t = ch;
-        const int tw = t % p.tiles_w; t /= p.tiles_w;
-        const int th = t % p.tiles_h; t /= p.tiles_h;
-        const int n0 = t * p.BNI, p0 = th * p.BH, q0 = tw * p.BW;
+        const int n0 = tn * p.BNI, p0 = th * p.BH, q0 = tw * p.BW;
         uint8_t* st = smem + stage * STAGE_BYTES;
         mbar_wait(&empty[stage], phase ^ 1);
-        mbar_expect_tx(&full[stage], STAGE_BYTES);
-        tma_load_4d(st, &map_dy, &full[stage], kblk * 128, q0, p0, n0);
-        tma_load_4d(st + BOX, &map_dy, &full[stage], kblk * 128 + 64, q0, p0, n0);
+        if (issuer) {
+          mbar_expect_tx(&full[stage], STAGE_BYTES);
+          tma_load_4d(st, &map_dy, &full[stage], k0, q0, p0, n0);
+          tma_load_4d(st + BOX, &map_dy, &full[stage], k0 + 64, q0, p0, n0);
 #pragma unroll
-        for (int s = 0; s < S; ++s)
+          for (int s = 0; s < S; ++s)
 #pragma unroll
-          for (int j = 0; j < CB / 64; ++j)
-            tma_load_4d(st + A_BYTES + s * B_TAP + j * BOX, &map_x, &full[stage], cblk * CB + j * 64,
-                        q0 * p.stride + s - p.pad, p0 * p.stride + r - p.pad, n0);
+            for (int j = 0; j < CB / 64; ++j)
+              tma_load_4d(st + A_BYTES + s * B_TAP + j * BOX, &map_x, &full[stage], c0 + j * 64, q0 * p.stride + s - p.pad,
+                          p0 * p.stride + roff, n0);
+        }
+        __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        if (++tw == p.tiles_w) { tw = 0; if (++th == p.tiles_h) { th = 0; ++tn; } }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && nchunks > 0) {
+    if (nchunks > 0) {
+      const bool issuer = elect_one();
       // D=f32, A=B=bf16, A and B MN-major (bits 15, 16), N = CB, M = 128
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(CB >> 3) << 17) |
                                  ((uint32_t)(128 >> 4) << 24);
@@ -785,18 +808,22 @@ __global__ void __launch_bounds__(TC_THREADS) wgrad3x3_tc_kernel(const __grid_co
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t a_lo = lo0 + stage * (STAGE_BYTES >> 4);
         const uint32_t b_lo = a_lo + (A_BYTES >> 4);
+        if (issuer) {
 #pragma unroll
-        for (int s = 0; s < S; ++s) {
+          for (int s = 0; s < S; ++s) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {   // 64 pixels = 4 x UMMA_K(16); 16 pixel rows = 2048 bytes
-            umma_bf16_lohi(tmem_base + s * CB, a_lo + k * (2048 >> 4), d_hi, b_lo + s * (B_TAP >> 4) + k * (2048 >> 4), d_hi, idesc,
-                           (uint32_t)((i | k) != 0));
+            for (int k = 0; k < 4; ++k) {   // 64 pixels = 4 x UMMA_K(16); 16 pixel rows = 2048 bytes
+              umma_bf16_lohi(tmem_base + s * CB, a_lo + k * (2048 >> 4), d_hi, b_lo + s * (B_TAP >> 4) + k * (2048 >> 4), d_hi,
+                             idesc, (uint32_t)((i | k) != 0));
+            }
           }
+          umma_commit(&empty[stage]);
         }
-        umma_commit(&empty[stage]);
+        __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
-      umma_commit(tmem_full);
+      if (issuer) umma_commit(tmem_full);
+      __syncwarp();
     }
   } else {
     const int quarter = warp & 3;

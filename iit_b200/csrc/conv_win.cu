@@ -86,24 +86,32 @@ __global__ void __launch_bounds__(WIN_THREADS) conv_win_kernel(const __grid_cons
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
-      // all filter taps, once
-      mbar_expect_tx(b_full, p.ntaps * B_TAP);
-      for (int t = 0; t < p.ntaps; ++t) tma_load_2d(sB + t * B_TAP, &map_b, b_full, p.wk[t] * (RB / 2), 0);
+    {
+      const bool issuer = elect_one();
+      if (issuer) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+        // all filter taps, once
+        mbar_expect_tx(b_full, p.ntaps * B_TAP);
+        for (int t = 0; t < p.ntaps; ++t) tma_load_2d(sB + t * B_TAP, &map_b, b_full, p.wk[t] * (RB / 2), 0);
+      }
+      __syncwarp();
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int n = tile / p.bands, band = tile - n * p.bands;
         mbar_wait(&empty[stage], phase ^ 1);
-        mbar_expect_tx(&full[stage], p.tile_bytes);
-        tma_load_4d(sA + (size_t)stage * p.stage_bytes, &map_a, &full[stage], 0, p.x0, p.y0 + band * p.y_step, n);
+        if (issuer) {
+          mbar_expect_tx(&full[stage], p.tile_bytes);
+          tma_load_4d(sA + (size_t)stage * p.stage_bytes, &map_a, &full[stage], 0, p.x0, p.y0 + band * p.y_step, n);
+        }
+        __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {   // warp-uniform loop, the elected lane issues (tc_common.cuh: elect_one)
+      const bool issuer = elect_one();
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
       mbar_wait(b_full, 0);
       int stage = 0;
@@ -127,16 +135,20 @@ __global__ void __launch_bounds__(WIN_THREADS) conv_win_kernel(const __grid_cons
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t tmem_d = tmem_base + acc * BN;
           const uint32_t a_m = a_tile + t * (128 * RB / 16);
+          if (issuer) {
 #pragma unroll
-          for (int tap = 0; tap < NTAPS; ++tap) {
+            for (int tap = 0; tap < NTAPS; ++tap) {
 #pragma unroll
-            for (int k = 0; k < KSTEPS; ++k)
-              umma_bf16_lohi(tmem_d, a_m + a_step[tap] + 2 * k, hi, b_lo + tap * (B_TAP / 16) + 2 * k, hi, idesc,
-                             (uint32_t)((tap | k) != 0));
+              for (int k = 0; k < KSTEPS; ++k)
+                umma_bf16_lohi(tmem_d, a_m + a_step[tap] + 2 * k, hi, b_lo + tap * (B_TAP / 16) + 2 * k, hi, idesc,
+                               (uint32_t)((tap | k) != 0));
+            }
+            umma_commit(&tmem_full[acc]);
           }
-          umma_commit(&tmem_full[acc]);
+          __syncwarp();
         }
-        umma_commit(&empty[stage]);   // the tile may be overwritten once every MMA above has read it
+        if (issuer) umma_commit(&empty[stage]);   // the tile may be overwritten once every MMA above has read it
+        __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
@@ -412,22 +424,29 @@ __global__ void __launch_bounds__(WIN_THREADS) wgrad_win_kernel(const __grid_con
   const bool has_work = (int)blockIdx.x < p.N;
 
   if (warp == 0) {
-    if (lane == 0) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_dy)) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_x)) : "memory");
+    {   // warp-uniform loops, the elected lane issues (tc_common.cuh: elect_one)
+      const bool issuer = elect_one();
+      if (issuer) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_dy)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_x)) : "memory");
+      }
       int stage = 0;
       uint32_t phase = 0;
       for (int n = blockIdx.x; n < p.N; n += gridDim.x) {
         uint8_t* st = smem + (size_t)stage * stage_bytes;
         mbar_wait(&empty[stage], phase ^ 1);
-        mbar_expect_tx(&full[stage], 2u * p.tile_rows * 128);
-        tma_load_4d(st, &map_dy, &full[stage], 0, -1, -1, n);
-        tma_load_4d(st + tile_alloc, &map_x, &full[stage], 0, -1, -1, n);
+        if (issuer) {
+          mbar_expect_tx(&full[stage], 2u * p.tile_rows * 128);
+          tma_load_4d(st, &map_dy, &full[stage], 0, -1, -1, n);
+          tma_load_4d(st + tile_alloc, &map_x, &full[stage], 0, -1, -1, n);
+        }
+        __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && has_work) {
+    if (has_work) {
+      const bool issuer = elect_one();
       // D=f32, A=B=bf16, both MN-major, N=192, M=128
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(192 >> 3) << 17) |
                                  ((uint32_t)(128 >> 4) << 24);
@@ -443,17 +462,21 @@ __global__ void __launch_bounds__(WIN_THREADS) wgrad_win_kernel(const __grid_con
         const uint32_t dy0 = smem_u32(smem + (size_t)stage * stage_bytes) >> 4, x0 = dy0 + (tile_alloc >> 4);
         // MMA 1: dy rows [0, 16*ks1) and [PW, PW+16*ks1); x rows from PW-1, PW, PW+1
         const uint32_t a1 = a_flags + dy0, b1 = b_flags + x0 + (uint32_t)(p.PW - 1) * row;
-        for (int kk = 0; kk < p.ks1; ++kk)
-          umma_bf16_lohi(tmem_base, a1 + kk * 16 * row, a_hi, b1 + kk * 16 * row, b_hi, idesc, (uint32_t)(!first || kk != 0));
         // MMA 2: dy rows from PW+1; x rows from 0, 1, 2
         const uint32_t a2 = a_flags + dy0 + (uint32_t)(p.PW + 1) * row, b2 = b_flags + x0;
-        for (int kk = 0; kk < p.ks2; ++kk)
-          umma_bf16_lohi(tmem_base + 192, a2 + kk * 16 * row, a_hi, b2 + kk * 16 * row, b_hi, idesc, (uint32_t)(!first || kk != 0));
-        umma_commit(&empty[stage]);
+        if (issuer) {
+          for (int kk = 0; kk < p.ks1; ++kk)
+            umma_bf16_lohi(tmem_base, a1 + kk * 16 * row, a_hi, b1 + kk * 16 * row, b_hi, idesc, (uint32_t)(!first || kk != 0));
+          for (int kk = 0; kk < p.ks2; ++kk)
+            umma_bf16_lohi(tmem_base + 192, a2 + kk * 16 * row, a_hi, b2 + kk * 16 * row, b_hi, idesc, (uint32_t)(!first || kk != 0));
+          umma_commit(&empty[stage]);
+        }
+        __syncwarp();
         first = 0;
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
-      umma_commit(tmem_full);
+      if (issuer) umma_commit(tmem_full);
+      __syncwarp();
     }
   } else {
     const int quarter = warp & 3;
@@ -595,23 +618,30 @@ __global__ void __launch_bounds__(WIN_THREADS) stem_wgrad_win_kernel(const __gri
   const bool has_work = (int)blockIdx.x < total;
 
   if (warp == 0) {
-    if (lane == 0) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_dy)) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_x)) : "memory");
+    {   // warp-uniform loops, the elected lane issues (tc_common.cuh: elect_one)
+      const bool issuer = elect_one();
+      if (issuer) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_dy)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_x)) : "memory");
+      }
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < total; t += gridDim.x) {
         const int n = t / p.bands, band = t - n * p.bands;
         uint8_t* st = smem + (size_t)stage * stage_bytes;
         mbar_wait(&empty[stage], phase ^ 1);
-        mbar_expect_tx(&full[stage], (uint32_t)p.dy_rows * 128 + (uint32_t)p.x_rows * 32);
-        tma_load_4d(st + STEM_LEAD * 128, &map_dy, &full[stage], 0, 0, band * p.BH, n);
-        tma_load_4d(st + p.dy_alloc + STEM_LEAD * 32, &map_x, &full[stage], 0, 0, band * p.BH, n);
+        if (issuer) {
+          mbar_expect_tx(&full[stage], (uint32_t)p.dy_rows * 128 + (uint32_t)p.x_rows * 32);
+          tma_load_4d(st + STEM_LEAD * 128, &map_dy, &full[stage], 0, 0, band * p.BH, n);
+          tma_load_4d(st + p.dy_alloc + STEM_LEAD * 32, &map_x, &full[stage], 0, 0, band * p.BH, n);
+        }
+        __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && has_work) {
+    if (has_work) {
+      const bool issuer = elect_one();
       // D=f32, A=B=bf16, both MN-major, N=64, M=128
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(64 >> 3) << 17) |
                                  ((uint32_t)(128 >> 4) << 24);
@@ -630,16 +660,20 @@ __global__ void __launch_bounds__(WIN_THREADS) stem_wgrad_win_kernel(const __gri
         const uint32_t a0 = (uint32_t)(STEM_LEAD - p.PW);
         const uint32_t a = a_flags + dy0 + a0 * 8;
         const uint32_t b1 = b_flags + x0 + (a0 + p.PW) * 2, b2 = b_flags + x0 + (a0 + 3 * p.PW) * 2;
-        for (int kk = 0; kk < p.ks; ++kk) {
-          const uint32_t acc = (uint32_t)(!first || kk != 0);
-          umma_bf16_lohi(tmem_base, a + kk * 128, a_hi, b1 + kk * 32, b_hi, idesc, acc);
-          umma_bf16_lohi(tmem_base + 64, a + kk * 128, a_hi, b2 + kk * 32, b_hi, idesc, acc);
+        if (issuer) {
+          for (int kk = 0; kk < p.ks; ++kk) {
+            const uint32_t acc = (uint32_t)(!first || kk != 0);
+            umma_bf16_lohi(tmem_base, a + kk * 128, a_hi, b1 + kk * 32, b_hi, idesc, acc);
+            umma_bf16_lohi(tmem_base + 64, a + kk * 128, a_hi, b2 + kk * 32, b_hi, idesc, acc);
+          }
+          umma_commit(&empty[stage]);
         }
-        umma_commit(&empty[stage]);
+        __syncwarp();
         first = 0;
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
-      umma_commit(tmem_full);
+      if (issuer) umma_commit(tmem_full);
+      __syncwarp();
     }
   } else {
     const int quarter = warp & 3;

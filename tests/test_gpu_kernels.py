@@ -573,7 +573,8 @@ def test_shifted_window_conv_is_bit_identical_to_the_tiled_kernel(ops, n, h, w):
             _lib.lib.iit_conv_win_enable(was)
     assert torch.equal(res[1][0], res[0][0])
     assert torch.equal(res[1][1], res[0][1])
-    torch.testing.assert_close(res[1][2], res[0][2], rtol=1e-6, atol=1e-6)   # fp32 partial sums in a different grouping
+    # fp32 partial sums (one ulp of a partial of ~30 is 2e-6) grouped differently and added by atomics in varying order
+    torch.testing.assert_close(res[1][2], res[0][2], rtol=1e-5, atol=1e-4)
     ref = F.conv2d(x.float().cpu().permute(0, 3, 1, 2), wt.float().cpu().permute(0, 3, 1, 2), padding=1).permute(0, 2, 3, 1)
     torch.testing.assert_close(res[1][0].float().cpu(), ref, rtol=2e-2, atol=2e-2)
     # weight gradient (dy := y): exact bf16 products, fp32 accumulation in a different order -> 1e-3 of the largest entry
@@ -625,7 +626,7 @@ def test_cta_pair_conv_is_bit_identical_to_the_single_cta_kernel(ops, n, h, w, c
     for on in (1, 2, 3):
         assert torch.equal(res[on][0], res[0][0])
         assert torch.equal(res[on][1], res[0][1])
-        torch.testing.assert_close(res[on][2], res[0][2], rtol=1e-6, atol=1e-6)
+        torch.testing.assert_close(res[on][2], res[0][2], rtol=1e-5, atol=1e-4)   # fp32 partials, atomics in varying order
     yb = res[1][0].double()
     torch.testing.assert_close(res[1][2][0], yb.sum((0, 1, 2)), rtol=1e-5, atol=1e-3)
     torch.testing.assert_close(res[1][2][1], (yb * yb).sum((0, 1, 2)), rtol=1e-5, atol=1e-3)
