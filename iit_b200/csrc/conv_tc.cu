@@ -886,7 +886,9 @@ static void wgrad_tc_plan(const iit_conv_t* d, TcWgradParams* p, int* splits, in
   *CB = (d->c % 128 == 0) ? 128 : 64;
   p->ncblk = d->c / *CB;
   int groups = d->r * ((d->k + 127) / 128) * p->ncblk;
-  int want = (kNumSMs + groups - 1) / groups;
+  // one CTA per SM (192 KB of stages, 512 TMEM columns): the grid must not exceed the SM count, or the few CTAs left over
+  // run as a second wave and double the kernel time (50 x 3 = 150 CTAs did exactly that on layer2)
+  int want = kNumSMs / groups;
   int maxs = (p->total_chunks + 7) / 8;   // at least 8 chunks (512 pixels) per CTA
   if (want > maxs) want = maxs;
   if (want < 1) want = 1;

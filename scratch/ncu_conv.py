@@ -15,7 +15,7 @@ for name, c, k, h, w, r, stride, pad in [("l2", 128, 128, 7, 7, 3, 1, 1), ("l3",
     y = torch.empty(N, d.p, d.q, k, device=dev, dtype=torch.bfloat16); dx = torch.empty_like(x); dw = torch.empty(k, r, r, c, device=dev)
     sums = torch.zeros(2, k, dtype=torch.float64, device=dev)
     need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d))); scratch = torch.empty(need, dtype=torch.uint8, device=dev)
-    for _ in range(2):
+    for _ in range(int(sys.argv[1]) if len(sys.argv) > 1 else 2):
         _lib.call("iit_conv2d_fprop_tc", p(x), p(wt), p(y), C.byref(d), p(sums[0]), p(sums[1]), st())
         _lib.call("iit_conv2d_dgrad_tc", p(y), p(wt2), p(dx), C.byref(d), st())
         _lib.call("iit_conv2d_wgrad_tc", p(y), p(x), p(dw), C.byref(d), p(scratch), need, st())
