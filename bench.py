@@ -228,13 +228,14 @@ def hbm_bytes(name, a):
         return a[4] * a[5] * _es(a[3]) * (2 + (1 if a[8] else 0))
     if name == "iit_bn_act_bwd_apply":      # dy, y, x, dx, dres, dtype, rows, c, ..., relu, stream
         return a[6] * a[7] * _es(a[5]) * (3 + (1 if a[-2] else 0) + ptr(a[4]))
-    if name == "iit_bn_relu_maxpool_fwd":   # x, y, idx, dtype, n, h, w, c: read x, write y (1/4) + idx (1 B / pooled element)
-        n, h, w, c = a[4:8]
-        return n * h * w * c * _es(a[3]) + n * ((h + 1) // 2) * ((w + 1) // 2) * c * (_es(a[3]) + 1)
-    if name == "iit_bn_relu_maxpool_bwd":   # two kernels: each reads x + dy + idx; the second writes dx
+    if name == "iit_bn_relu_maxpool_fwd":   # x, y, idx, xwin, dtype, n, h, w, c: read x, write y (+ xwin) (1/4 each) + idx (1 B)
         n, h, w, c = a[5:9]
         pooled = n * ((h + 1) // 2) * ((w + 1) // 2) * c
-        return 2 * (n * h * w * c * _es(a[4]) + pooled * (_es(a[4]) + 1)) + n * h * w * c * _es(a[4])
+        return n * h * w * c * _es(a[4]) + pooled * (_es(a[4]) * (1 + ptr(a[3])) + 1)
+    if name == "iit_bn_relu_maxpool_bwd":   # dy, idx, x, y, xwin, dx, dtype, n, h, w, c: sums read dy, y, xwin; dx reads x, dy, idx
+        n, h, w, c = a[7:11]
+        pooled = n * ((h + 1) // 2) * ((w + 1) // 2) * c
+        return pooled * (4 * _es(a[6]) + 1) + 2 * n * h * w * c * _es(a[6])
     if name == "iit_patch_fwd":             # dst, src, box: read the box from src, write it to dst
         b = a[2]._obj
         n = b.elem_bytes

@@ -90,8 +90,8 @@ SIGNATURES = {
     "iit_colsum": [_vp, _i, _vp, _i64, _i64, _vp],
     "iit_attn_fwd": [_vp, _vp, _i, _i64, _i, _i, _i, _vp],
     "iit_attn_bwd": [_vp, _vp, _vp, _i, _i64, _i, _i, _i, _vp],
-    "iit_bn_relu_maxpool_fwd": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp],
-    "iit_bn_relu_maxpool_bwd": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    "iit_bn_relu_maxpool_fwd": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp],
+    "iit_bn_relu_maxpool_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "iit_conv_win_enable": [_i],
     "iit_conv_pair_enable": [_i],
     "iit_stem_s2d": [_vp, _i, _vp, _vp, _i, _i, _i, _vp],

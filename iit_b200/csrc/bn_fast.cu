@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(256, 4) bn_bwd_apply_fast_kernel(const T* __re
 // forward: one thread = one pooled pixel x one channel pack
 template <typename T>
 __global__ void __launch_bounds__(256) bn_relu_pool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int8_t* __restrict__ idx,
-                                                               int N, int H, int W, int C, int P, int Q,
+                                                               T* __restrict__ xwin, int N, int H, int W, int C, int P, int Q,
                                                                const float* __restrict__ mean, const float* __restrict__ invstd,
                                                                const float* __restrict__ gamma, const float* __restrict__ beta) {
   constexpr int NP = Pack<T>::N;
@@ -342,6 +342,9 @@ __global__ void __launch_bounds__(256) bn_relu_pool_fwd_kernel(const T* __restri
 #pragma unroll
       for (int j = 0; j < NP; j += 4) ipk[j / 4] = (uint32_t)bi[j] | ((uint32_t)bi[j + 1] << 8) | ((uint32_t)bi[j + 2] << 16) | ((uint32_t)bi[j + 3] << 24);
     }
+    // the winners' raw values (exact copies of elements of x): the backward's per-channel sums run over these pooled
+    // tensors instead of gathering through the full-resolution ones
+    if (xwin != nullptr) Pack<T>::store(xwin + (int64_t)pix * C + cp * NP, best);
 #pragma unroll
     for (int j = 0; j < NP; ++j) best[j] = fmaxf((best[j] - mu[j]) * is[j] * g[j] + b[j], 0.f);
     Pack<T>::store(y + (int64_t)pix * C + cp * NP, best);
@@ -351,104 +354,16 @@ __global__ void __launch_bounds__(256) bn_relu_pool_fwd_kernel(const T* __restri
   }
 }
 
-// gradient reaching the ReLU output at input pixel (h, w): sum of the pooled gradients whose window picked it.
-// The (up to) 2 x 2 candidate windows are loaded together from clamped addresses; invalid ones are masked afterwards.
+// Backward. The per-channel sums (dgamma, dbeta) need, for every pooled pixel, the gradient, the ReLU mask and the
+// normalised value of the window's winner: the forward saved the winners' raw values (xwin), so the sums are the generic
+// BN reduction over the POOLED tensors (bn_bwd_reduce_fast_kernel on dy, y, xwin: a quarter of the pixels, no gather).
+//
+// dx: one thread = a 2 x 2 block of input pixels x one channel pack. The block (rows 2a, 2a+1; columns 2b, 2b+1) is
+// covered by the four windows (a, b), (a, b+1), (a+1, b), (a+1, b+1) only, so four gradient packs and four slot words
+// serve four outputs (the per-pixel gather needed four of each per output). Slot of pixel (2a+i, 2b+j) inside window
+// (a+u, b+v): row 1 + i - 2u, column 1 + j - 2v when both lie in 0..2.
 template <typename T>
-__device__ __forceinline__ void pool_bwd_gather(const T* __restrict__ dy, const int8_t* __restrict__ idx, int n, int h, int w, int c,
-                                                int C, int P, int Q, float (&g)[Pack<T>::N]) {
-  constexpr int NP = Pack<T>::N;
-  const int pc[2] = {h >> 1, (h + 1) >> 1}, qc[2] = {w >> 1, (w + 1) >> 1};
-  uint4 raw[4];
-  uint32_t kraw[4][NP / 4];
-  int slot[4];
-#pragma unroll
-  for (int a = 0; a < 2; ++a)
-#pragma unroll
-    for (int b = 0; b < 2; ++b) {
-      const int t = a * 2 + b;
-      const bool ok = pc[a] < P && qc[b] < Q && (a == 0 || pc[1] != pc[0]) && (b == 0 || qc[1] != qc[0]);
-      const int p = min(pc[a], P - 1), q = min(qc[b], Q - 1);
-      slot[t] = ok ? (h - (pc[a] * 2 - 1)) * 3 + (w - (qc[b] * 2 - 1)) : -1;   // -1 never matches a stored slot
-      const int64_t op = (((int64_t)n * P + p) * Q + q) * C + c;
-      raw[t] = *reinterpret_cast<const uint4*>(dy + op);
-#pragma unroll
-      for (int j = 0; j < NP / 4; ++j) kraw[t][j] = *reinterpret_cast<const uint32_t*>(idx + op + 4 * j);
-    }
-  if constexpr (std::is_same<T, __nv_bfloat16>::value) {
-    // four channels per compare (__vcmpeq4 on the slot bytes), two per masked packed add; an element is the winner of
-    // more than one window only occasionally, so the bf16 additions are mostly exact
-    uint32_t g2[4] = {0u, 0u, 0u, 0u};
-#pragma unroll
-    for (int t = 0; t < 4; ++t) {
-      const uint32_t s4 = (uint32_t)(slot[t] & 0xff) * 0x01010101u;
-      const uint32_t w4[4] = {raw[t].x, raw[t].y, raw[t].z, raw[t].w};
-#pragma unroll
-      for (int hlf = 0; hlf < 2; ++hlf) {
-        const uint32_t m4 = __vcmpeq4(kraw[t][hlf], s4);
-        const uint32_t mlo = __byte_perm(m4, 0u, 0x1100), mhi = __byte_perm(m4, 0u, 0x3322);
-        uint32_t a = w4[2 * hlf] & mlo, b = w4[2 * hlf + 1] & mhi;
-        __nv_bfloat162 sa = __hadd2(*reinterpret_cast<__nv_bfloat162*>(&g2[2 * hlf]), *reinterpret_cast<__nv_bfloat162*>(&a));
-        __nv_bfloat162 sb = __hadd2(*reinterpret_cast<__nv_bfloat162*>(&g2[2 * hlf + 1]), *reinterpret_cast<__nv_bfloat162*>(&b));
-        g2[2 * hlf] = *reinterpret_cast<uint32_t*>(&sa);
-        g2[2 * hlf + 1] = *reinterpret_cast<uint32_t*>(&sb);
-      }
-    }
-#pragma unroll
-    for (int w = 0; w < 4; ++w) { g[2 * w] = __uint_as_float(g2[w] << 16); g[2 * w + 1] = __uint_as_float(g2[w] & 0xffff0000u); }
-  } else {
-#pragma unroll
-    for (int j = 0; j < NP; ++j) g[j] = 0.f;
-#pragma unroll
-    for (int t = 0; t < 4; ++t) {
-      float d[NP];
-      Pack<T>::unpack(raw[t], d);
-#pragma unroll
-      for (int j = 0; j < NP; ++j) {
-        const int k = (int)(int8_t)((kraw[t][j >> 2] >> (8 * (j & 3))) & 0xff);
-        if (k == slot[t]) g[j] += d[j];
-      }
-    }
-  }
-}
-
-template <typename T>
-__global__ void __launch_bounds__(256, 4) bn_relu_pool_bwd_reduce_kernel(const T* __restrict__ dy, const int8_t* __restrict__ idx,
-                                                                      const T* __restrict__ x, int N, int H, int W, int C, int P,
-                                                                      int Q, int CGB, const float* __restrict__ mean,
-                                                                      const float* __restrict__ invstd, const float* __restrict__ gamma,
-                                                                      const float* __restrict__ beta, Red2 o) {
-  extern __shared__ float smem[];
-  constexpr int NP = Pack<T>::N;
-  const int RL = 256 / CGB;                               // CGB == C / NP here: one block covers every channel
-  const int cg = threadIdx.x % CGB, rl = threadIdx.x / CGB;
-  const int cbase = 0, c = cg * NP;
-  float mu[NP], is[NP], gm[NP], bt[NP], acc[2][NP];
-  load_consts<NP>(mean, c, mu); load_consts<NP>(invstd, c, is); load_consts<NP>(gamma, c, gm); load_consts<NP>(beta, c, bt);
-#pragma unroll
-  for (int j = 0; j < NP; ++j) { acc[0][j] = 0.f; acc[1][j] = 0.f; }
-  const uint32_t rows = (uint32_t)N * H * W;
-  const uint32_t stride = gridDim.x * RL, first = blockIdx.x * RL + rl;
-  const int sw = (int)(stride % W), sh = (int)((stride / W) % H), sn = (int)(stride / ((uint32_t)W * H));
-  int w = (int)(first % W), h = (int)((first / W) % H), n = (int)(first / ((uint32_t)W * H));
-  for (uint32_t r = first; r < rows; r += stride, w += sw, h += sh, n += sn) {
-    if (w >= W) { w -= W; ++h; }
-    if (h >= H) { h -= H; ++n; }
-    float g[NP], xv[NP];
-    Pack<T>::load(x + (int64_t)r * C + c, xv);
-    pool_bwd_gather<T>(dy, idx, n, h, w, c, C, P, Q, g);
-#pragma unroll
-    for (int j = 0; j < NP; ++j) {
-      const float xh = (xv[j] - mu[j]) * is[j];
-      const float gj = (xh * gm[j] + bt[j]) > 0.f ? g[j] : 0.f;
-      acc[0][j] += gj * xh; acc[1][j] += gj;
-    }
-  }
-  double* outs[2] = {o.p[0], o.p[1]};
-  reduce_finish<2, NP>(acc, cg, rl, CGB, RL, cbase, outs, smem);
-}
-
-template <typename T>
-__global__ void __launch_bounds__(256, 4) bn_relu_pool_bwd_apply_kernel(const T* __restrict__ dy, const int8_t* __restrict__ idx,
+__global__ void __launch_bounds__(256, 2) bn_relu_pool_bwd_apply_kernel(const T* __restrict__ dy, const int8_t* __restrict__ idx,
                                                                      const T* __restrict__ x, T* __restrict__ dx, int N, int H, int W,
                                                                      int C, int P, int Q, float inv_rows,
                                                                      const float* __restrict__ mean, const float* __restrict__ invstd,
@@ -458,27 +373,96 @@ __global__ void __launch_bounds__(256, 4) bn_relu_pool_bwd_apply_kernel(const T*
   const uint32_t CPK = C / NP, PXB = 256 / CPK;
   const int c = (int)(threadIdx.x % CPK) * NP;
   const uint32_t px = threadIdx.x / CPK;
-  float mu[NP], is[NP], gm[NP], bt[NP], dbn[NP], dgn[NP];
-  load_consts<NP>(mean, c, mu); load_consts<NP>(invstd, c, is); load_consts<NP>(gamma, c, gm); load_consts<NP>(beta, c, bt);
-#pragma unroll
-  for (int j = 0; j < NP; ++j) { dbn[j] = (float)dbeta[c + j] * inv_rows; dgn[j] = (float)dgamma[c + j] * inv_rows; }
-  const uint32_t rows = (uint32_t)N * H * W;
-  const uint32_t stride = gridDim.x * PXB, first = blockIdx.x * PXB + px;
-  const int sw = (int)(stride % W), sh = (int)((stride / W) % H), sn = (int)(stride / ((uint32_t)W * H));
-  int w = (int)(first % W), h = (int)((first / W) % H), n = (int)(first / ((uint32_t)W * H));
-  for (uint32_t r = first; r < rows; r += stride, w += sw, h += sh, n += sn) {
-    if (w >= W) { w -= W; ++h; }
-    if (h >= H) { h -= H; ++n; }
-    float g[NP], xv[NP], o[NP];
-    Pack<T>::load(x + (int64_t)r * C + c, xv);
-    pool_bwd_gather<T>(dy, idx, n, h, w, c, C, P, Q, g);
+  // four constants per channel (two blocks of 2 x 2 pixels in flight leave no registers for six):
+  //   activation = x * A + B0 (its sign is the ReLU mask);  dx = A * g + K0 + K1 * x
+  float A[NP], B0[NP], K0[NP], K1[NP];
+  {
+    float mu[NP], is[NP], gm[NP], bt[NP];
+    load_consts<NP>(mean, c, mu); load_consts<NP>(invstd, c, is); load_consts<NP>(gamma, c, gm); load_consts<NP>(beta, c, bt);
 #pragma unroll
     for (int j = 0; j < NP; ++j) {
-      const float xh = (xv[j] - mu[j]) * is[j];
-      const float gj = (xh * gm[j] + bt[j]) > 0.f ? g[j] : 0.f;
-      o[j] = gm[j] * is[j] * (gj - dbn[j] - xh * dgn[j]);
+      const float dbn = (float)dbeta[c + j] * inv_rows, dgn = (float)dgamma[c + j] * inv_rows;
+      A[j] = gm[j] * is[j];
+      B0[j] = bt[j] - mu[j] * A[j];
+      K1[j] = -A[j] * dgn * is[j];
+      K0[j] = -A[j] * dbn - K1[j] * mu[j];
     }
-    Pack<T>::store(dx + (int64_t)r * C + c, o);
+  }
+  const int HB = (H + 1) >> 1, WB = (W + 1) >> 1;
+  const uint32_t blocks = (uint32_t)N * HB * WB;
+  const uint32_t stride = gridDim.x * PXB, first = blockIdx.x * PXB + px;
+  const int sb = (int)(stride % WB), sa = (int)((stride / WB) % HB), sn = (int)(stride / ((uint32_t)WB * HB));
+  int bb = (int)(first % WB), a = (int)((first / WB) % HB), n = (int)(first / ((uint32_t)WB * HB));
+  for (uint32_t r = first; r < blocks; r += stride, bb += sb, a += sa, n += sn) {
+    if (bb >= WB) { bb -= WB; ++a; }
+    if (a >= HB) { a -= HB; ++n; }
+    // the four windows: clamped loads, invalid ones get slot words that match nothing
+    uint4 g4[4];
+    uint32_t k4[4][NP / 4];
+#pragma unroll
+    for (int u = 0; u < 2; ++u)
+#pragma unroll
+      for (int v = 0; v < 2; ++v) {
+        const int t = u * 2 + v;
+        const bool ok = a + u < P && bb + v < Q;
+        const int64_t op = (((int64_t)n * P + min(a + u, P - 1)) * Q + min(bb + v, Q - 1)) * C + c;
+        g4[t] = *reinterpret_cast<const uint4*>(dy + op);
+        if constexpr (NP == 8) {
+          const uint2 kk = *reinterpret_cast<const uint2*>(idx + op);
+          k4[t][0] = ok ? kk.x : 0xffffffffu; k4[t][1] = ok ? kk.y : 0xffffffffu;
+        } else {
+          const uint32_t kk = *reinterpret_cast<const uint32_t*>(idx + op);
+          k4[t][0] = ok ? kk : 0xffffffffu;
+        }
+      }
+    uint4 xr[4];
+    bool pok[4];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int h = 2 * a + i, w = 2 * bb + j;
+        pok[i * 2 + j] = h < H && w < W;
+        xr[i * 2 + j] = *reinterpret_cast<const uint4*>(x + (((int64_t)n * H + min(h, H - 1)) * W + min(w, W - 1)) * C + c);
+      }
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        if (!pok[i * 2 + j]) continue;
+        float g[NP], xv[NP], o[NP];
+#pragma unroll
+        for (int e = 0; e < NP; ++e) g[e] = 0.f;
+#pragma unroll
+        for (int u = 0; u <= i; ++u)
+#pragma unroll
+          for (int v = 0; v <= j; ++v) {
+            const int t = u * 2 + v;
+            const uint32_t slot = (uint32_t)((1 + i - 2 * u) * 3 + (1 + j - 2 * v));
+            float d[NP];
+            Pack<T>::unpack(g4[t], d);
+            if constexpr (NP == 8) {
+              const uint32_t s4 = slot * 0x01010101u;
+              const uint32_t m0 = __vcmpeq4(k4[t][0], s4), m1 = __vcmpeq4(k4[t][1], s4);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                if ((m0 >> (8 * e)) & 1u) g[e] += d[e];
+                if ((m1 >> (8 * e)) & 1u) g[4 + e] += d[4 + e];
+              }
+            } else {
+#pragma unroll
+              for (int e = 0; e < NP; ++e)
+                if (((k4[t][e >> 2] >> (8 * (e & 3))) & 0xffu) == slot) g[e] += d[e];
+            }
+          }
+        Pack<T>::unpack(xr[i * 2 + j], xv);
+#pragma unroll
+        for (int e = 0; e < NP; ++e) {
+          const float ge = fmaf(xv[e], A[e], B0[e]) > 0.f ? g[e] : 0.f;
+          o[e] = fmaf(A[e], ge, fmaf(K1[e], xv[e], K0[e]));
+        }
+        Pack<T>::store(dx + (((int64_t)n * H + 2 * a + i) * W + 2 * bb + j) * C + c, o);
+      }
   }
 }
 
@@ -566,45 +550,50 @@ static int pool_args_ok(const char* name, int dtype, int n, int h, int w, int c)
   return 0;
 }
 
-extern "C" int iit_bn_relu_maxpool_fwd(const void* x, void* y, int8_t* idx, int dtype, int n, int h, int w, int c, const float* mean,
-                                       const float* invstd, const float* gamma, const float* beta, void* stream) {
+extern "C" int iit_bn_relu_maxpool_fwd(const void* x, void* y, int8_t* idx, void* xwin, int dtype, int n, int h, int w, int c,
+                                       const float* mean, const float* invstd, const float* gamma, const float* beta, void* stream) {
   IIT_REQUIRE(x && y && idx && mean && invstd && gamma && beta, "iit_bn_relu_maxpool_fwd: null pointer");
   if (pool_args_ok("iit_bn_relu_maxpool_fwd", dtype, n, h, w, c)) return 1;
-  IIT_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15) == 0 && (reinterpret_cast<uintptr_t>(idx) & 3) == 0,
-              "iit_bn_relu_maxpool_fwd: x and y must be 16-byte aligned, idx 4-byte aligned");
+  IIT_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(xwin)) & 15) == 0 &&
+              (reinterpret_cast<uintptr_t>(idx) & 7) == 0,
+              "iit_bn_relu_maxpool_fwd: x, y and xwin must be 16-byte aligned, idx 8-byte aligned");
   const int P = (h + 2 - 3) / 2 + 1, Q = (w + 2 - 3) / 2 + 1;
   const int64_t total = (int64_t)n * P * Q * (c / (dtype == IIT_BF16 ? 8 : 4));
   IIT_DISPATCH_DTYPE(dtype, T, {
-    bn_relu_pool_fwd_kernel<T><<<grid_for(total, 256, 16), 256, 0, as_stream(stream)>>>((const T*)x, (T*)y, idx, n, h, w, c, P, Q, mean,
-                                                                                   invstd, gamma, beta);
+    bn_relu_pool_fwd_kernel<T><<<grid_for(total, 256, 16), 256, 0, as_stream(stream)>>>((const T*)x, (T*)y, idx, (T*)xwin, n, h, w, c, P, Q,
+                                                                                   mean, invstd, gamma, beta);
   })
   IIT_LAUNCH_CHECK("iit_bn_relu_maxpool_fwd");
   return 0;
 }
 
-extern "C" int iit_bn_relu_maxpool_bwd(const void* dy, const int8_t* idx, const void* x, void* dx, int dtype, int n, int h, int w,
-                                       int c, const float* mean, const float* invstd, const float* gamma, const float* beta,
-                                       double* dgamma, double* dbeta, void* stream) {
-  IIT_REQUIRE(dy && idx && x && dx && mean && invstd && gamma && beta && dgamma && dbeta, "iit_bn_relu_maxpool_bwd: null pointer");
+extern "C" int iit_bn_relu_maxpool_bwd(const void* dy, const int8_t* idx, const void* x, const void* y, const void* xwin, void* dx,
+                                       int dtype, int n, int h, int w, int c, const float* mean, const float* invstd,
+                                       const float* gamma, const float* beta, double* dgamma, double* dbeta, void* stream) {
+  IIT_REQUIRE(dy && idx && x && y && xwin && dx && mean && invstd && gamma && beta && dgamma && dbeta,
+              "iit_bn_relu_maxpool_bwd: null pointer");
   if (pool_args_ok("iit_bn_relu_maxpool_bwd", dtype, n, h, w, c)) return 1;
-  IIT_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dx)) & 15) == 0 &&
-              (reinterpret_cast<uintptr_t>(idx) & 3) == 0, "iit_bn_relu_maxpool_bwd: x, dy, dx must be 16-byte aligned, idx 4-byte aligned");
+  IIT_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dx) |
+                reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(xwin)) & 15) == 0 &&
+              (reinterpret_cast<uintptr_t>(idx) & 7) == 0,
+              "iit_bn_relu_maxpool_bwd: x, y, xwin, dy, dx must be 16-byte aligned, idx 8-byte aligned");
   const int np = dtype == IIT_BF16 ? 8 : 4;
   const int P = (h + 2 - 3) / 2 + 1, Q = (w + 2 - 3) / 2 + 1;
-  const int64_t rows = (int64_t)n * h * w;
+  const int64_t rows = (int64_t)n * h * w, prows = (int64_t)n * P * Q;
   cudaStream_t st = as_stream(stream);
-  const int CGB = c / np;                      // pool_args_ok: divides 256, so one block spans all channels
-  const size_t smem = (size_t)2 * 256 * np * sizeof(float);
-  const dim3 grid((unsigned)grid_for(rows * CGB, 256, 6));
-  Red2 o{{dgamma, dbeta}};
+  // per-channel sums over the pooled tensors: mask = y > 0, normalised value from the winner's raw value
+  {
+    int CGB; dim3 grid; size_t smem;
+    red_geometry(prows, c, np, &CGB, &grid, &smem);
+    Red2 o{{dgamma, dbeta}};
+    IIT_DISPATCH_DTYPE(dtype, T, {
+      bn_bwd_reduce_fast_kernel<T><<<grid, 256, smem, st>>>((const T*)dy, (const T*)y, (const T*)xwin, prows, c, CGB, mean, invstd, 1, o);
+    })
+    IIT_LAUNCH_CHECK("iit_bn_relu_maxpool_bwd(reduce)");
+  }
+  const int64_t total = (int64_t)n * ((h + 1) / 2) * ((w + 1) / 2) * (c / np);
   IIT_DISPATCH_DTYPE(dtype, T, {
-    bn_relu_pool_bwd_reduce_kernel<T><<<grid, 256, smem, st>>>((const T*)dy, idx, (const T*)x, n, h, w, c, P, Q, CGB, mean, invstd,
-                                                              gamma, beta, o);
-  })
-  IIT_LAUNCH_CHECK("iit_bn_relu_maxpool_bwd(reduce)");
-  const int64_t total = rows * (c / np);
-  IIT_DISPATCH_DTYPE(dtype, T, {
-    bn_relu_pool_bwd_apply_kernel<T><<<grid_for(total, 256, 16), 256, 0, st>>>((const T*)dy, idx, (const T*)x, (T*)dx, n, h, w, c, P, Q,
+    bn_relu_pool_bwd_apply_kernel<T><<<grid_for(total, 256, 12), 256, 0, st>>>((const T*)dy, idx, (const T*)x, (T*)dx, n, h, w, c, P, Q,
                                                                           1.f / (float)rows, mean, invstd, gamma, beta, dgamma, dbeta);
   })
   IIT_LAUNCH_CHECK("iit_bn_relu_maxpool_bwd(apply)");

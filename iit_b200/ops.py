@@ -568,8 +568,8 @@ def bn_act(x, gamma, beta, residual, running_mean, running_var, training, moment
 
 
 class _BNReluPoolFn(torch.autograd.Function):
-    """bn (train or eval statistics) -> relu -> maxpool 3x3/2 of the stem conv output as one kernel; the
-    backward recomputes the activation from the conv output (nothing but the window index is stored)."""
+    """bn (train or eval statistics) -> relu -> maxpool 3x3/2 of the stem conv output as one kernel. Stored for the
+    backward: the window index and the winners' raw values (pooled size); dx recomputes the activation from the conv output."""
 
     @staticmethod
     def forward(ctx, x, gamma, beta, running_mean, running_var, training, momentum, eps, sums, acc, tracked):
@@ -596,22 +596,25 @@ class _BNReluPoolFn(torch.autograd.Function):
         p, q = (h + 2 - 3) // 2 + 1, (w + 2 - 3) // 2 + 1
         y = empty_cl(n, c, p, q, x.dtype, x.device)
         idx = torch.empty((n, p, q, c), dtype=torch.int8, device=x.device)
-        call("iit_bn_relu_maxpool_fwd", _p(x), _p(y), _p(idx), _dt(x), n, h, w, c, _p(mean), _p(invstd), _p(gamma), _p(beta), st)
-        ctx.save_for_backward(x, idx, gamma, beta, mean, invstd)
+        # the winners' raw values, kept only when a backward will follow: its per-channel sums then run over pooled tensors
+        xwin = torch.empty_like(y) if any(ctx.needs_input_grad[:3]) else None
+        call("iit_bn_relu_maxpool_fwd", _p(x), _p(y), _p(idx), _p(xwin), _dt(x), n, h, w, c, _p(mean), _p(invstd), _p(gamma),
+             _p(beta), st)
+        ctx.save_for_backward(x, idx, gamma, beta, mean, invstd, y, xwin)
         ctx.training = training
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, idx, gamma, beta, mean, invstd = ctx.saved_tensors
+        x, idx, gamma, beta, mean, invstd, y, xwin = ctx.saved_tensors
         dy = _cl(dy)
         n, c, h, w = x.shape
         red = torch.zeros((2, c), dtype=torch.float64, device=x.device)
         dx = torch.empty_like(x)
         if not ctx.training:
             raise NotImplementedError("fused bn+relu+maxpool backward is for batch statistics (train mode)")
-        call("iit_bn_relu_maxpool_bwd", _p(dy), _p(idx), _p(x), _p(dx), _dt(x), n, h, w, c, _p(mean), _p(invstd), _p(gamma),
-             _p(beta), _p(red[0]), _p(red[1]), _stream())
+        call("iit_bn_relu_maxpool_bwd", _p(dy), _p(idx), _p(x), _p(y), _p(xwin), _p(dx), _dt(x), n, h, w, c, _p(mean), _p(invstd),
+             _p(gamma), _p(beta), _p(red[0]), _p(red[1]), _stream())
         return dx, red[0].float(), red[1].float(), None, None, None, None, None, None, None, None
 
 

@@ -261,15 +261,17 @@ int iit_maxpool3x3s2_bwd(const void* dy, const int8_t* idx, void* dx, int dtype,
  * mod.bn1 / mod.relu / mod.maxpool of iit/utils/wrapper.py:33-66) as one kernel: x is the stem conv
  * output [n,h,w,c], y the pooled [n,(h+1)/2,(w+1)/2,c] tensor, idx the winning window slot per pooled
  * element. Values and window winners are identical to iit_bn_act_fwd(relu) followed by
- * iit_maxpool3x3s2_fwd. The backward recomputes the normalised activation from x: it ADDS the
- * per-channel sums into dgamma / dbeta (the caller zeroes them) and writes dx; two launches. */
-int iit_bn_relu_maxpool_fwd(const void* x, void* y, int8_t* idx, int dtype, int n, int h, int w, int c,
-                            const float* mean, const float* invstd, const float* gamma,
+ * iit_maxpool3x3s2_fwd. xwin (same shape as y; may be NULL when no backward follows) receives the raw
+ * value of x at each winner. The backward ADDS the per-channel sums into dgamma / dbeta (the caller zeroes
+ * them) from the pooled tensors dy, y, xwin, then writes dx, recomputing the normalised activation from x
+ * (one thread per 2 x 2 input block, which only four pooling windows cover); two launches. */
+int iit_bn_relu_maxpool_fwd(const void* x, void* y, int8_t* idx, void* xwin, int dtype, int n, int h, int w,
+                            int c, const float* mean, const float* invstd, const float* gamma,
                             const float* beta, void* stream);
-int iit_bn_relu_maxpool_bwd(const void* dy, const int8_t* idx, const void* x, void* dx, int dtype, int n,
-                            int h, int w, int c, const float* mean, const float* invstd,
-                            const float* gamma, const float* beta, double* dgamma, double* dbeta,
-                            void* stream);
+int iit_bn_relu_maxpool_bwd(const void* dy, const int8_t* idx, const void* x, const void* y, const void* xwin,
+                            void* dx, int dtype, int n, int h, int w, int c, const float* mean,
+                            const float* invstd, const float* gamma, const float* beta, double* dgamma,
+                            double* dbeta, void* stream);
 /* AdaptiveAvgPool2d(1) + flatten: [n,hw,c] -> fp32 [n,c]; and its backward. */
 int iit_avgpool_fwd(const void* x, float* y, int dtype, int n, int hw, int c, void* stream);
 int iit_avgpool_bwd(const float* dy, void* dx, int dtype, int n, int hw, int c, void* stream);

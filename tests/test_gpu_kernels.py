@@ -319,6 +319,10 @@ def test_bn_relu_maxpool_fused_equals_unfused_chain(ops, c, hw, dtype):
     yf, dxf, dgf, dbf, rmf, rvf, gy = run(True)
     yu, dxu, dgu, dbu, rmu, rvu, _ = run(False)
     assert torch.equal(yf, yu)
+    with torch.no_grad():     # no backward to follow: the winners' raw values are not written (NULL xwin)
+        xd = x.to(DEV).to(dtype).contiguous(memory_format=torch.channels_last)
+        yn = ops.bn_relu_maxpool(xd, gamma.to(DEV), beta.to(DEV), rm.to(DEV), rv.to(DEV), True, 0.1, 1e-5)
+    assert torch.equal(yn, yf)
     assert torch.equal(rmf, rmu) and torch.equal(rvf, rvu)
     if dtype == torch.float32:
         torch.testing.assert_close(dxf, dxu, rtol=1e-4, atol=1e-5)
