@@ -61,6 +61,8 @@ SIGNATURES = {
     "iit_conv2d_dgrad_tc": [_vp, _vp, _vp, _ConvP, _vp],
     "iit_conv2d_wgrad_tc_scratch_bytes": [_ConvP],
     "iit_conv2d_wgrad_tc": [_vp, _vp, _vp, _ConvP, _vp, _sz, _vp],
+    "iit_conv2d_wgrad_tc_accumulate": [_vp, _vp, _vp, _ConvP, _vp, _sz, _vp],
+    "iit_bn_param_grads": [_vp, _i, _vp, _vp, _i, _i, _vp],
     "iit_conv2d_wgrad_scratch_bytes": [_ConvP],
     "iit_conv2d_wgrad": [_vp, _vp, _vp, _ConvP, _i, _vp, _sz, _vp],
     "iit_stem_im2col": [_vp, _i, C.POINTER(C.c_int64), _vp, _i, _i, _i, _vp],

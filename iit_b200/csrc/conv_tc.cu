@@ -862,12 +862,21 @@ __global__ void __launch_bounds__(TC_THREADS) wgrad3x3_tc_kernel(const __grid_co
   }
 }
 
+// out[i] (+)= sum over splits of part[z][i], in fixed order (deterministic); four partials in flight per thread
 __global__ void __launch_bounds__(256) tc_splitk_reduce_kernel(const float* __restrict__ part, float* __restrict__ out,
-                                                               int64_t n, int splits) {
+                                                               int64_t n, int splits, int accumulate) {
   const int64_t n4 = n >> 2;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int z = 0; z < splits; ++z) {  // fixed order: deterministic
+    float4 s = accumulate ? reinterpret_cast<const float4*>(out)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    int z = 0;
+    for (; z + 4 <= splits; z += 4) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = reinterpret_cast<const float4*>(part + (int64_t)(z + u) * n)[i];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+    }
+    for (; z < splits; ++z) {
       float4 v = reinterpret_cast<const float4*>(part + (int64_t)z * n)[i];
       s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
     }
@@ -976,8 +985,8 @@ extern "C" size_t iit_conv2d_wgrad_tc_scratch_bytes(const iit_conv_t* d) {
   return need > win ? need : win;
 }
 
-extern "C" int iit_conv2d_wgrad_tc(const void* dy, const void* x, float* dw, const iit_conv_t* d, void* scratch,
-                                   size_t scratch_bytes, void* stream) {
+static int wgrad_tc_impl(const void* dy, const void* x, float* dw, const iit_conv_t* d, void* scratch, size_t scratch_bytes,
+                         void* stream, int accumulate) {
   IIT_REQUIRE(dy && x && dw && d, "iit_conv2d_wgrad_tc: null pointer");
   IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "iit_conv2d_wgrad_tc: only bf16 3x3/pad-1 or 1x1/pad-0 convolutions, stride 1 "
               "or 2, with channel counts that are multiples of 64");
@@ -993,7 +1002,7 @@ extern "C" int iit_conv2d_wgrad_tc(const void* dy, const void* x, float* dw, con
     int rc = wgrad_win(dy, x, (float*)scratch, d, &nsplit, as_stream(stream), "iit_conv2d_wgrad_tc");
     if (rc) return rc;
     const int64_t n = (int64_t)d->k * d->r * d->s * d->c;
-    tc_splitk_reduce_kernel<<<grid_for(n / 4, 256), 256, 0, as_stream(stream)>>>((const float*)scratch, dw, n, nsplit);
+    tc_splitk_reduce_kernel<<<grid_for(n / 4, 256), 256, 0, as_stream(stream)>>>((const float*)scratch, dw, n, nsplit, accumulate);
     IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc(reduce)");
     return 0;
   }
@@ -1015,7 +1024,17 @@ extern "C" int iit_conv2d_wgrad_tc(const void* dy, const void* x, float* dw, con
   if (rc) return rc;
   IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc");
   int64_t n = (int64_t)d->k * d->r * d->s * d->c;
-  tc_splitk_reduce_kernel<<<grid_for(n / 4, 256), 256, 0, st>>>((const float*)scratch, dw, n, splits);
+  tc_splitk_reduce_kernel<<<grid_for(n / 4, 256), 256, 0, st>>>((const float*)scratch, dw, n, splits, accumulate);
   IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc(reduce)");
   return 0;
+}
+
+extern "C" int iit_conv2d_wgrad_tc(const void* dy, const void* x, float* dw, const iit_conv_t* d, void* scratch,
+                                   size_t scratch_bytes, void* stream) {
+  return wgrad_tc_impl(dy, x, dw, d, scratch, scratch_bytes, stream, 0);
+}
+
+extern "C" int iit_conv2d_wgrad_tc_accumulate(const void* dy, const void* x, float* dw, const iit_conv_t* d, void* scratch,
+                                              size_t scratch_bytes, void* stream) {
+  return wgrad_tc_impl(dy, x, dw, d, scratch, scratch_bytes, stream, 1);
 }

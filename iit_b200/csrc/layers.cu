@@ -512,6 +512,26 @@ extern "C" int iit_bn_finalize(double* sum, double* sqsum, int64_t rows, int c, 
   return 0;
 }
 
+// fp64 per-channel sums of a BatchNorm backward -> fp32 parameter gradients, written or accumulated in place (the
+// optimizer's flat gradient buffer), and the layer's persistent accumulator cleared for its next backward: one launch
+// instead of a fill, two casts and two accumulation kernels per layer
+__global__ void bn_param_grads_kernel(double* __restrict__ sums, int c, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                      int accumulate, int clear) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= c) return;
+  const float dg = (float)sums[i], db = (float)sums[c + i];
+  dgamma[i] = accumulate ? dgamma[i] + dg : dg;
+  dbeta[i] = accumulate ? dbeta[i] + db : db;
+  if (clear) { sums[i] = 0.0; sums[c + i] = 0.0; }
+}
+
+extern "C" int iit_bn_param_grads(double* sums, int c, float* dgamma, float* dbeta, int accumulate, int clear_sums, void* stream) {
+  IIT_REQUIRE(sums && dgamma && dbeta && c >= 1, "iit_bn_param_grads: bad arguments");
+  bn_param_grads_kernel<<<(c + 127) / 128, 128, 0, as_stream(stream)>>>(sums, c, dgamma, dbeta, accumulate, clear_sums);
+  IIT_LAUNCH_CHECK("iit_bn_param_grads");
+  return 0;
+}
+
 extern "C" int iit_bn_eval_invstd(const float* running_var, int c, float eps, float* invstd, void* stream) {
   IIT_REQUIRE(running_var && invstd, "iit_bn_eval_invstd: null pointer");
   bn_eval_invstd_kernel<<<(c + 127) / 128, 128, 0, as_stream(stream)>>>(running_var, c, eps, invstd);

@@ -46,6 +46,7 @@ class FlatAdam(torch.optim.Optimizer):
                 pv.copy_(p)
                 p.data = pv
                 p.grad = self._view_like(self.flat_g, o, p)
+                p._iit_direct_grad = p.grad     # backward kernels may add into this view in place (ops.direct_grad)
 
     @staticmethod
     def _view_like(flat, off, p):

@@ -82,7 +82,8 @@ class Conv2d(nn.Module):
             s2d = self.weight.shape[0] == 64 and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0
             return ops.stem_conv(x, self.weight, self.stem_filter(s2d), bn_sums)
         krsc, crsk = self.prepared(x.dtype)
-        return ops.conv2d(x, self.weight, krsc, crsk, self.stride, self.pad, bn_sums)
+        wgrad_buf = ops.direct_grad(self.weight) if torch.is_grad_enabled() else None
+        return ops.conv2d(x, self.weight, krsc, crsk, self.stride, self.pad, bn_sums, wgrad_buf)
 
 
 class BatchNorm2d(nn.Module):
@@ -104,11 +105,28 @@ class BatchNorm2d(nn.Module):
             self.__dict__["_acc"] = acc
         return acc
 
+    def grad_accumulator(self, device):
+        """The same for the backward's per-channel sums (cleared by iit_bn_param_grads)."""
+        acc = self.__dict__.get("_bacc")
+        if acc is None or acc.device != device:
+            acc = torch.zeros((2, self.c), dtype=torch.float64, device=device)
+            self.__dict__["_bacc"] = acc
+        return acc
+
+    def backward_buffers(self, x):
+        """(persistent backward accumulator, (gamma.grad, beta.grad) when kernels may add into them) -- ops.direct_grad."""
+        if not (x.is_cuda and torch.is_grad_enabled()):
+            return None, None
+        gg, gb = ops.direct_grad(self.weight), ops.direct_grad(self.bias)
+        return self.grad_accumulator(x.device), ((gg, gb) if gg is not None and gb is not None else None)
+
     def forward(self, x, residual=None, relu=False, sums=None):
         acc = self.accumulator(x.device) if (self.training and x.is_cuda) else None
+        bacc, pgrads = self.backward_buffers(x)
         try:
             return ops.bn_act(x, self.weight, self.bias, residual, self.running_mean, self.running_var, self.training,
-                              self.momentum, self.eps, relu, sums, acc, self.num_batches_tracked if self.training else None)
+                              self.momentum, self.eps, relu, sums, acc, self.num_batches_tracked if self.training else None,
+                              bacc, pgrads)
         except Exception:
             if acc is not None:
                 acc.zero_()      # a failed launch sequence must not leave partial sums behind
@@ -324,8 +342,9 @@ class ResNet18LL(HookedRootModule):
                 sums = acc if acc is not None else ops.new_bn_sums(bn.c, x.device)
             try:
                 y0 = m.conv1.hook_point(m.conv1.mod(x, sums, self.act_dtype))
+                bacc, pgrads = bn.backward_buffers(x)
                 x = ops.bn_relu_maxpool(y0, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.training, bn.momentum,
-                                        bn.eps, sums, acc, bn.num_batches_tracked if bn.training else None)
+                                        bn.eps, sums, acc, bn.num_batches_tracked if bn.training else None, bacc, pgrads)
             except Exception:
                 if acc is not None:
                     acc.zero_()

@@ -314,9 +314,19 @@ def filter_relayout_batched(table_dev: torch.Tensor, entries: int, max_elements:
     call("iit_filter_relayout_batched", _p(table_dev), int(entries), int(max_elements), _stream())
 
 
+def direct_grad(p: torch.Tensor) -> Optional[torch.Tensor]:
+    """The gradient buffer of parameter `p` when backward kernels may add into it in place: the view of the optimizer's
+    flat gradient buffer that FlatAdam installed as `p.grad` (and marked), still in place. A backward that accumulates there
+    returns None for that input, so autograd launches no AccumulateGrad addition. None in every other case."""
+    g = p.grad
+    if g is None or getattr(p, "_iit_direct_grad", None) is not g or g.dtype != torch.float32 or (g.data_ptr() & 15):
+        return None
+    return g
+
+
 class _ConvFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums):
+    def forward(ctx, x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums, wgrad_buf):
         _require_cuda(x, weight)
         x = _cl(x)
         k, c, r, s = weight.shape
@@ -332,6 +342,9 @@ class _ConvFn(torch.autograd.Function):
             call("iit_conv2d_fprop", _p(x), _p(w_krsc), _p(y), C.byref(d), _dt(x), _p(s0), _p(s1), _stream())
         ctx.save_for_backward(x, weight)
         ctx.d, ctx.w_crsk_fn, ctx.tc = d, w_crsk_fn, tc
+        # physical KRSC (channels-last filter) gradient buffer the weight-gradient reduction may add into directly
+        ctx.wgrad_buf = wgrad_buf if (tc and wgrad_buf is not None and wgrad_buf.shape == weight.shape
+                                      and wgrad_buf.permute(0, 2, 3, 1).is_contiguous()) else None
         return y
 
     @staticmethod
@@ -346,7 +359,11 @@ class _ConvFn(torch.autograd.Function):
                 call("iit_conv2d_dgrad_tc", _p(dy), _p(ctx.w_crsk_fn()), _p(dx), C.byref(d), _stream())
             else:
                 call("iit_conv2d_dgrad", _p(dy), _p(ctx.w_crsk_fn()), _p(dx), C.byref(d), _dt(x), _stream())
-        if ctx.needs_input_grad[1]:
+        if ctx.needs_input_grad[1] and ctx.wgrad_buf is not None:
+            need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
+            scratch = torch.empty(need, dtype=torch.uint8, device=x.device)
+            call("iit_conv2d_wgrad_tc_accumulate", _p(dy), _p(x), _p(ctx.wgrad_buf), C.byref(d), _p(scratch), need, _stream())
+        elif ctx.needs_input_grad[1]:
             dwb = torch.empty((d.k, d.r, d.s, d.c), dtype=torch.float32, device=x.device)
             if ctx.tc:
                 need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
@@ -357,11 +374,12 @@ class _ConvFn(torch.autograd.Function):
                 scratch = torch.empty(need, dtype=torch.uint8, device=x.device) if need else None
                 call("iit_conv2d_wgrad", _p(dy), _p(x), _p(dwb), C.byref(d), _dt(x), _p(scratch), need, _stream())
             dw = dwb.permute(0, 3, 1, 2)  # [K,C,R,S] view with channels-last strides, like the parameter
-        return dx, dw, None, None, None, None, None
+        return dx, dw, None, None, None, None, None, None
 
 
-def conv2d(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums=None):
-    return _ConvFn.apply(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums)
+def conv2d(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums=None, wgrad_buf=None):
+    """`wgrad_buf`: see direct_grad -- the weight gradient is added into it and autograd receives None."""
+    return _ConvFn.apply(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums, wgrad_buf)
 
 
 STEM_K = 192
@@ -509,7 +527,8 @@ def new_bn_sums(c: int, device) -> torch.Tensor:
 
 class _BNActFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums, acc, tracked):
+    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums, acc, tracked,
+                bacc, pgrads):
         _require_cuda(x, gamma, beta, residual)
         x = _cl(x)
         n, c, h, w = x.shape
@@ -538,6 +557,7 @@ class _BNActFn(torch.autograd.Function):
              int(relu), st)
         ctx.save_for_backward(x, y if relu else None, gamma, mean, invstd)
         ctx.relu, ctx.training, ctx.has_res = relu, training, residual is not None
+        ctx.bacc, ctx.pgrads = bacc, pgrads
         return y
 
     @staticmethod
@@ -547,24 +567,44 @@ class _BNActFn(torch.autograd.Function):
         n, c, h, w = x.shape
         rows = n * h * w
         st = _stream()
-        red = torch.zeros((2, c), dtype=torch.float64, device=x.device)
-        call("iit_bn_act_bwd_reduce", _p(dy), _p(y), _p(x), _dt(x), rows, c, _p(mean), _p(invstd), int(ctx.relu),
-             _p(red[0]), _p(red[1]), st)
-        dx = torch.empty_like(x)
-        dres = torch.empty_like(x) if ctx.has_res else None
-        # eval mode: statistics are constants, so the two correction terms vanish
-        corr = red if ctx.training else torch.zeros_like(red)
-        call("iit_bn_act_bwd_apply", _p(dy), _p(y), _p(x), _p(dx), _p(dres), _dt(x), rows, c, _p(mean), _p(invstd),
-             _p(gamma), _p(corr[0]), _p(corr[1]), int(ctx.relu), st)
-        return dx, red[0].float(), red[1].float(), dres, None, None, None, None, None, None, None, None, None
+        # `bacc`: the layer's persistent fp64 [2, C] accumulator (zero between uses; iit_bn_param_grads clears it)
+        red = ctx.bacc if ctx.bacc is not None else torch.zeros((2, c), dtype=torch.float64, device=x.device)
+        try:
+            call("iit_bn_act_bwd_reduce", _p(dy), _p(y), _p(x), _dt(x), rows, c, _p(mean), _p(invstd), int(ctx.relu),
+                 _p(red[0]), _p(red[1]), st)
+            dx = torch.empty_like(x)
+            dres = torch.empty_like(x) if ctx.has_res else None
+            # eval mode: statistics are constants, so the two correction terms vanish
+            corr = red if ctx.training else torch.zeros_like(red)
+            call("iit_bn_act_bwd_apply", _p(dy), _p(y), _p(x), _p(dx), _p(dres), _dt(x), rows, c, _p(mean), _p(invstd),
+                 _p(gamma), _p(corr[0]), _p(corr[1]), int(ctx.relu), st)
+            dgamma, dbeta = _bn_param_grads(red, c, ctx.pgrads, ctx.bacc is not None, st)
+        except Exception:
+            if ctx.bacc is not None:
+                ctx.bacc.zero_()
+            raise
+        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None, None, None, None, None
+
+
+def _bn_param_grads(red, c, pgrads, clear, st):
+    """fp64 sums -> the fp32 gradients of (gamma, beta) in one launch: added into the optimizer's buffers (`pgrads`, see
+    direct_grad; autograd then receives None) or written to fresh tensors."""
+    if pgrads is not None:
+        call("iit_bn_param_grads", _p(red), c, _p(pgrads[0]), _p(pgrads[1]), 1, int(clear), st)
+        return None, None
+    out = torch.empty((2, c), dtype=torch.float32, device=red.device)
+    call("iit_bn_param_grads", _p(red), c, _p(out[0]), _p(out[1]), 0, int(clear), st)
+    return out[0], out[1]
 
 
 def bn_act(x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums=None, acc=None,
-           tracked=None):
+           tracked=None, bacc=None, pgrads=None):
     """`sums`: statistics already accumulated by the producing convolution's epilogue; `acc`: the layer's persistent
     fp64 accumulator [2, C] (kept zero between uses; `sums` may be it); `tracked`: num_batches_tracked, incremented by the
-    finalize kernel."""
-    return _BNActFn.apply(x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums, acc, tracked)
+    finalize kernel; `bacc`: the same kind of accumulator for the backward's sums; `pgrads`: (gamma, beta) gradient buffers
+    to add into (direct_grad)."""
+    return _BNActFn.apply(x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums, acc, tracked,
+                          bacc, pgrads)
 
 
 class _BNReluPoolFn(torch.autograd.Function):
@@ -572,7 +612,7 @@ class _BNReluPoolFn(torch.autograd.Function):
     backward: the window index and the winners' raw values (pooled size); dx recomputes the activation from the conv output."""
 
     @staticmethod
-    def forward(ctx, x, gamma, beta, running_mean, running_var, training, momentum, eps, sums, acc, tracked):
+    def forward(ctx, x, gamma, beta, running_mean, running_var, training, momentum, eps, sums, acc, tracked, bacc, pgrads):
         _require_cuda(x, gamma, beta)
         x = _cl(x)
         n, c, h, w = x.shape
@@ -602,6 +642,7 @@ class _BNReluPoolFn(torch.autograd.Function):
              _p(beta), st)
         ctx.save_for_backward(x, idx, gamma, beta, mean, invstd, y, xwin)
         ctx.training = training
+        ctx.bacc, ctx.pgrads = bacc, pgrads
         return y
 
     @staticmethod
@@ -609,17 +650,26 @@ class _BNReluPoolFn(torch.autograd.Function):
         x, idx, gamma, beta, mean, invstd, y, xwin = ctx.saved_tensors
         dy = _cl(dy)
         n, c, h, w = x.shape
-        red = torch.zeros((2, c), dtype=torch.float64, device=x.device)
-        dx = torch.empty_like(x)
         if not ctx.training:
             raise NotImplementedError("fused bn+relu+maxpool backward is for batch statistics (train mode)")
-        call("iit_bn_relu_maxpool_bwd", _p(dy), _p(idx), _p(x), _p(y), _p(xwin), _p(dx), _dt(x), n, h, w, c, _p(mean), _p(invstd),
-             _p(gamma), _p(beta), _p(red[0]), _p(red[1]), _stream())
-        return dx, red[0].float(), red[1].float(), None, None, None, None, None, None, None, None
+        red = ctx.bacc if ctx.bacc is not None else torch.zeros((2, c), dtype=torch.float64, device=x.device)
+        dx = torch.empty_like(x)
+        st = _stream()
+        try:
+            call("iit_bn_relu_maxpool_bwd", _p(dy), _p(idx), _p(x), _p(y), _p(xwin), _p(dx), _dt(x), n, h, w, c, _p(mean),
+                 _p(invstd), _p(gamma), _p(beta), _p(red[0]), _p(red[1]), st)
+            dgamma, dbeta = _bn_param_grads(red, c, ctx.pgrads, ctx.bacc is not None, st)
+        except Exception:
+            if ctx.bacc is not None:
+                ctx.bacc.zero_()
+            raise
+        return dx, dgamma, dbeta, None, None, None, None, None, None, None, None, None, None
 
 
-def bn_relu_maxpool(x, gamma, beta, running_mean, running_var, training, momentum, eps, sums=None, acc=None, tracked=None):
-    return _BNReluPoolFn.apply(x, gamma, beta, running_mean, running_var, training, momentum, eps, sums, acc, tracked)
+def bn_relu_maxpool(x, gamma, beta, running_mean, running_var, training, momentum, eps, sums=None, acc=None, tracked=None,
+                    bacc=None, pgrads=None):
+    return _BNReluPoolFn.apply(x, gamma, beta, running_mean, running_var, training, momentum, eps, sums, acc, tracked, bacc,
+                               pgrads)
 
 
 class _ReluFn(torch.autograd.Function):

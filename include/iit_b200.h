@@ -199,6 +199,9 @@ int iit_stem_wgrad_s2d(const void* dy, const void* s2d, float* dw, const int64_t
 size_t iit_conv2d_wgrad_tc_scratch_bytes(const iit_conv_t* d);
 int iit_conv2d_wgrad_tc(const void* dy, const void* x, float* dw, const iit_conv_t* d, void* scratch,
                         size_t scratch_bytes, void* stream);
+/* The same, adding the result into dw (e.g. the optimizer's gradient buffer) instead of overwriting it. */
+int iit_conv2d_wgrad_tc_accumulate(const void* dy, const void* x, float* dw, const iit_conv_t* d, void* scratch,
+                        size_t scratch_bytes, void* stream);
 
 /* Stem (7x7 stride-2 pad-3, 3 input channels): im2col matrix col[n*p*q][192] in bf16 (147 columns in
  * (r,s,c) order + zero padding) gathered from an image tensor addressed as [n,c,h,w] through the given
@@ -272,6 +275,12 @@ int iit_bn_relu_maxpool_bwd(const void* dy, const int8_t* idx, const void* x, co
                             void* dx, int dtype, int n, int h, int w, int c, const float* mean,
                             const float* invstd, const float* gamma, const float* beta, double* dgamma,
                             double* dbeta, void* stream);
+/* BatchNorm backward, last step: sums = fp64 [2][c] (dgamma sums, then dbeta sums) as accumulated by
+ * iit_bn_act_bwd_reduce / iit_bn_relu_maxpool_bwd. dgamma[i] (+)= (float)sums[i], dbeta[i] (+)= (float)sums[c+i]
+ * (accumulate != 0 adds into the existing values, e.g. the optimizer's gradient buffer); clear_sums != 0 zeroes
+ * sums afterwards so that a persistent accumulator is ready for the next backward. */
+int iit_bn_param_grads(double* sums, int c, float* dgamma, float* dbeta, int accumulate, int clear_sums,
+                       void* stream);
 /* AdaptiveAvgPool2d(1) + flatten: [n,hw,c] -> fp32 [n,c]; and its backward. */
 int iit_avgpool_fwd(const void* x, float* y, int dtype, int n, int hw, int c, void* stream);
 int iit_avgpool_bwd(const float* dy, void* dx, int dtype, int n, int hw, int c, void* stream);

@@ -684,3 +684,53 @@ def test_stem_space_to_depth_conv_matches_conv2d(ops, n, hw):
         assert err <= 1e-3 * wr.grad.abs().max().item(), (err, wr.grad.abs().max().item())
     else:
         assert need == 0
+
+
+def test_backward_adds_parameter_gradients_into_marked_buffers(ops):
+    """Parameters whose .grad is the optimizer's flat-buffer view (FlatAdam marks it) get their gradients added in place by
+    the backward kernels (conv weight-gradient reduction, iit_bn_param_grads) and autograd receives None for them. Same
+    numbers, bit for bit, as the ordinary path where autograd accumulates the returned gradient; a second backward adds."""
+    from iit_b200.nn.resnet import BatchNorm2d, Conv2d
+    g = torch.Generator().manual_seed(21)
+    x = torch.randn(6, 64, 14, 14, generator=g).to(DEV).bfloat16().contiguous(memory_format=torch.channels_last)
+    gy = torch.randn(6, 64, 14, 14, generator=g).to(DEV).bfloat16().contiguous(memory_format=torch.channels_last)
+
+    def build(direct):
+        torch.manual_seed(5)
+        conv, bn = Conv2d(64, 64, 3, 1, 1).to(DEV), BatchNorm2d(64).to(DEV)
+        with torch.no_grad():
+            bn.weight.uniform_(0.5, 1.5)
+            bn.bias.normal_(0, 0.3)
+        params = [conv.weight, bn.weight, bn.bias]
+        if direct:
+            for p in params:
+                p.grad = torch.zeros_like(p)
+                p._iit_direct_grad = p.grad
+                assert ops.direct_grad(p) is p.grad
+        return conv, bn, params
+
+    def run(direct, times):
+        conv, bn, params = build(direct)
+        xr = x.clone().requires_grad_(True)
+        for _ in range(times):
+            y = bn(conv(xr), relu=True)
+            y.backward(gy)
+        return [p.grad.clone() for p in params], xr.grad.clone()
+
+    seen = []
+    inner = ops.call
+    ops.call = lambda name, *a: (seen.append(name), inner(name, *a))[1]
+    try:
+        gd, dxd = run(True, 1)
+    finally:
+        ops.call = inner
+    assert "iit_conv2d_wgrad_tc_accumulate" in seen and "iit_bn_param_grads" in seen and "iit_conv2d_wgrad_tc" not in seen
+    gn, dxn = run(False, 1)
+    assert torch.equal(dxd, dxn)
+    for a, b in zip(gd, gn):
+        assert a.stride() == b.stride() or a.dim() == 1
+        assert torch.equal(a, b)
+    gd2, _ = run(True, 2)
+    gn2, _ = run(False, 2)
+    for a, b in zip(gd2, gn2):      # (g + p1) + p2 + ... against g + (p1 + p2 + ...): fp32 rounding order only
+        torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-4)
