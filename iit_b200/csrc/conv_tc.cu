@@ -26,6 +26,7 @@ constexpr int TC_BM = 128;      // pixels per tile (UMMA M)
 constexpr int TC_BK = 64;       // bf16 elements per 128-byte swizzle row
 constexpr int TC_UK = 16;       // UMMA K for 16-bit inputs
 constexpr int TC_THREADS = 192;
+constexpr int TC_CONV_THREADS = 64 + 256;   // fprop / dgrad: TMA warp, MMA warp, eight epilogue warps
 
 struct TcParams {
   int N, P, Q;            // pixel grid enumerated by the tiles (a parity class of the output for strided dgrad)
@@ -49,7 +50,7 @@ struct TcParams {
 // memory traffic (ncu: ~11 TB/s through the crossbar at 36-42 % tensor-pipe activity with 128 x 128 tiles); a filter block
 // that serves two pixel boxes cuts the bytes per FLOP by a quarter.
 template <int BN, int STAGES, int MT>
-__global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_constant__ CUtensorMap map_a,
+__global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __grid_constant__ CUtensorMap map_a,
                                                                 const __grid_constant__ CUtensorMap map_b,
                                                                 __nv_bfloat16* __restrict__ out, TcParams p,
                                                                 double* __restrict__ bn_sum, double* __restrict__ bn_sq) {
@@ -65,8 +66,10 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
   uint64_t* tmem_empty = tmem_full + 2;      // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
   float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [2][BN] per-channel sum / sum of squares of one tile
+  // [8 warps][32 rows][TC_STAGE_PITCH], 16-byte aligned: output transposition
+  uint8_t* s_stage = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(s_stat + 2 * BN) + 15) & ~uintptr_t(15));
   if (bn_sum != nullptr)
-    for (int i = threadIdx.x; i < 2 * BN; i += TC_THREADS) s_stat[i] = 0.f;
+    for (int i = threadIdx.x; i < 2 * BN; i += TC_CONV_THREADS) s_stat[i] = 0.f;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kchunks = p.Cin / TC_BK;
@@ -77,7 +80,7 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {  // TMEM allocation is warp-collective; this warp also frees it
@@ -164,17 +167,31 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
       }
     }
   } else {
-    // epilogue: warp w may read TMEM lanes [32*(w%4), 32*(w%4)+32)
+    // epilogue, eight warps: warp w may read TMEM lanes [32*(w%4), 32*(w%4)+32), so two warps share each lane quarter and
+    // take alternate 32-column chunks. With small reductions (1x1 and 64-channel layers) the tile time IS the epilogue time:
+    // one warp per scheduler ran a dependent chain of ~350 instructions per chunk with nothing to overlap it with.
     const int quarter = warp & 3;
+    const int half = (warp - 2) >> 2;   // which of the two warps of this lane quarter
     const int m = quarter * 32 + lane;  // accumulator row == pixel of the box
     const int wl = m % p.BW;
     const int hl = (m / p.BW) % p.BH;
     const int nl = m / (p.BW * p.BH);
-    const int e = threadIdx.x - 64;     // 0..127: owner of channel e of the current filter block's statistics
-    constexpr int NCH = (BN + 127) / 128;   // channels of the filter block owned by each of the 128 epilogue threads
-    double run_s[NCH], run_q[NCH];          // this CTA's running totals for channels run_co + e + 128*i
+    const int e = threadIdx.x - 64;     // 0..255: owner of channel e of the current filter block's statistics
+    constexpr int NCH = (BN + 255) / 256;   // channels of the filter block owned by each of the 256 epilogue threads
+    double run_s[NCH], run_q[NCH];          // this CTA's running totals for channels run_co + e + 256*i
 #pragma unroll
     for (int i = 0; i < NCH; ++i) { run_s[i] = 0.0; run_q[i] = 0.0; }
+    // Stores: a lane holds one pixel x 32 channels (64 bytes). Written as such, a warp store touches 32 lines with 16 bytes
+    // each (half a sector): 10-15 % of the kernel. Each warp instead passes the chunk through its own staging rows and
+    // stores 64 contiguous bytes per pixel: four lanes per pixel, pixels (lane/4) + 8i of the warp's 32.
+    uint8_t* my_stage = s_stage + (warp - 2) * (32 * TC_STAGE_PITCH);
+    const int sub = lane >> 2, piece = lane & 3;
+    int swl[4], shl[4], snl[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int mm = quarter * 32 + sub + 8 * i;
+      swl[i] = mm % p.BW; shl[i] = (mm / p.BW) % p.BH; snl[i] = mm / (p.BW * p.BH);
+    }
     int run_co = -1;
     uint32_t it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
@@ -192,9 +209,17 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
       const int th = t % p.tiles_h; t /= p.tiles_h;
       const int n = t * p.BNI + nl, pp = th * p.BH + hl, qq = tw * p.BW + wl;
       const bool ok = box_ok && n < p.N && pp < p.P && qq < p.Q;
-      __nv_bfloat16* dst = out + (((int64_t)n * p.OH + (pp * p.out_mul + p.out_oh)) * p.OW + (qq * p.out_mul + p.out_ow)) * p.Cout + co0;
+      __nv_bfloat16* sdst[4];      // the four pixels this lane stores a 16-byte piece of (nullptr: outside the tensor)
 #pragma unroll
-      for (int c = 0; c < BN; c += 32) {
+      for (int i = 0; i < 4; ++i) {
+        const int sn = t * p.BNI + snl[i], sp = th * p.BH + shl[i], sq = tw * p.BW + swl[i];
+        sdst[i] = (box_ok && sn < p.N && sp < p.P && sq < p.Q)
+                      ? out + (((int64_t)sn * p.OH + (sp * p.out_mul + p.out_oh)) * p.OW + (sq * p.out_mul + p.out_ow)) * p.Cout + co0 + piece * 8
+                      : nullptr;
+      }
+#pragma unroll
+      for (int cc = 0; cc < BN / 64; ++cc) {
+        const int c = cc * 64 + half * 32;
         uint32_t v[32];
         if (nk > 0) {
           tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * (MT * BN) + mt * BN + c), v);
@@ -202,25 +227,13 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = 0u;
         }
-        if (c + 32 >= BN && mt == MT - 1 && nk > 0) {
+        if (cc == BN / 64 - 1 && mt == MT - 1 && nk > 0) {
           // all of this warp's TMEM reads of the accumulator are complete: hand it back to the MMA warp
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
           __syncwarp();
           if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[acc])) : "memory");
         }
-        if (ok) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 8) {
-            uint4 o;
-            __nv_bfloat162 h0 = __floats2bfloat162_rn(__uint_as_float(v[j + 0]), __uint_as_float(v[j + 1]));
-            __nv_bfloat162 h1 = __floats2bfloat162_rn(__uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
-            __nv_bfloat162 h2 = __floats2bfloat162_rn(__uint_as_float(v[j + 4]), __uint_as_float(v[j + 5]));
-            __nv_bfloat162 h3 = __floats2bfloat162_rn(__uint_as_float(v[j + 6]), __uint_as_float(v[j + 7]));
-            o.x = *reinterpret_cast<uint32_t*>(&h0); o.y = *reinterpret_cast<uint32_t*>(&h1);
-            o.z = *reinterpret_cast<uint32_t*>(&h2); o.w = *reinterpret_cast<uint32_t*>(&h3);
-            *reinterpret_cast<uint4*>(dst + c + j) = o;
-          }
-        }
+        tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c);
         if (bn_sum != nullptr) {
           // BatchNorm statistics of the values as stored (bf16-rounded), for the BN that follows this conv.
           // Each lane holds one pixel x 32 channels; a butterfly that halves the channel set per step leaves
@@ -248,11 +261,11 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
       }
      }  // mt
       if (bn_sum != nullptr) {
-        asm volatile("bar.sync 1, 128;" ::: "memory");   // the four epilogue warps only: the tile's sums are complete
+        asm volatile("bar.sync 1, 256;" ::: "memory");   // the eight epilogue warps only: the tile's sums are complete
         if (run_co != co0) {
 #pragma unroll
           for (int i = 0; i < NCH; ++i) {
-            const int ch = e + 128 * i;
+            const int ch = e + 256 * i;
             if (run_co >= 0 && ch < BN) { atomicAdd(&bn_sum[run_co + ch], run_s[i]); atomicAdd(&bn_sq[run_co + ch], run_q[i]); }
             run_s[i] = 0.0; run_q[i] = 0.0;
           }
@@ -260,19 +273,19 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
         }
 #pragma unroll
         for (int i = 0; i < NCH; ++i) {
-          const int ch = e + 128 * i;
+          const int ch = e + 256 * i;
           if (ch < BN) {
             run_s[i] += (double)s_stat[ch]; run_q[i] += (double)s_stat[BN + ch];
             s_stat[ch] = 0.f; s_stat[BN + ch] = 0.f;
           }
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");   // zeroed before the next tile adds to it
+        asm volatile("bar.sync 1, 256;" ::: "memory");   // zeroed before the next tile adds to it
       }
     }
     if (bn_sum != nullptr && run_co >= 0) {
 #pragma unroll
       for (int i = 0; i < NCH; ++i) {
-        const int ch = e + 128 * i;
+        const int ch = e + 256 * i;
         if (ch < BN) { atomicAdd(&bn_sum[run_co + ch], run_s[i]); atomicAdd(&bn_sq[run_co + ch], run_q[i]); }
       }
     }
@@ -297,7 +310,7 @@ __global__ void __launch_bounds__(TC_THREADS) conv3x3_tc_kernel(const __grid_con
 // BN = filters per tile (accumulator columns per CTA); each CTA loads BN / 2 filter rows. BN = 128 gives tiles of half the
 // size at the traffic per FLOP of the single-CTA 128 x 256 tile: it is chosen when it fills the last wave better.
 template <int BN, int STAGES>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_CONV_THREADS, 1)
 conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                    __nv_bfloat16* __restrict__ out, TcParams p, double* __restrict__ bn_sum, double* __restrict__ bn_sq) {
   extern __shared__ uint8_t smem_raw[];
@@ -312,8 +325,9 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
   uint64_t* tmem_empty = tmem_full + 2;      // [2] (the leader's are used)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
   float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [2][BN]
+  uint8_t* s_stage = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(s_stat + 2 * BN) + 15) & ~uintptr_t(15));
   if (bn_sum != nullptr)
-    for (int i = threadIdx.x; i < 2 * BN; i += TC_THREADS) s_stat[i] = 0.f;
+    for (int i = threadIdx.x; i < 2 * BN; i += TC_CONV_THREADS) s_stat[i] = 0.f;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -326,7 +340,7 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 8); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 16); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {  // the same warp of both CTAs allocates (and frees) the pair's TMEM columns
@@ -404,16 +418,26 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       }
     }
   } else {
+    // eight epilogue warps, two per TMEM lane quarter on alternate 32-column chunks; staged 64-byte stores (tc_store_chunk)
     const int quarter = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int m = quarter * 32 + lane;
     const int wl = m % p.BW;
     const int hl = (m / p.BW) % p.BH;
     const int nl = m / (p.BW * p.BH);
-    const int e = threadIdx.x - 64;
-    constexpr int NCH = BN / 128;
-    double run_s[NCH], run_q[NCH];                         // channels run_co + e + 128 * i
+    const int e = threadIdx.x - 64;                        // 0..255
+    constexpr int NCH = (BN + 255) / 256;
+    double run_s[NCH], run_q[NCH];                         // channels run_co + e + 256 * i
 #pragma unroll
     for (int i = 0; i < NCH; ++i) { run_s[i] = 0.0; run_q[i] = 0.0; }
+    uint8_t* my_stage = s_stage + (warp - 2) * (32 * TC_STAGE_PITCH);
+    const int sub = lane >> 2, piece = lane & 3;
+    int swl[4], shl[4], snl[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int mm = quarter * 32 + sub + 8 * i;
+      swl[i] = mm % p.BW; shl[i] = (mm / p.BW) % p.BH; snl[i] = mm / (p.BW * p.BH);
+    }
     int run_co = -1;
     uint32_t it = 0;
     for (int tile = pair; tile < total_tiles; tile += npairs, ++it) {
@@ -428,29 +452,25 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       const int th = t % p.tiles_h; t /= p.tiles_h;
       const int n = t * p.BNI + nl, pp = th * p.BH + hl, qq = tw * p.BW + wl;
       const bool ok = box_ok && n < p.N && pp < p.P && qq < p.Q;
-      __nv_bfloat16* dst = out + (((int64_t)n * p.OH + (pp * p.out_mul + p.out_oh)) * p.OW + (qq * p.out_mul + p.out_ow)) * p.Cout + co0;
+      __nv_bfloat16* sdst[4];
 #pragma unroll
-      for (int c = 0; c < BN; c += 32) {
+      for (int i = 0; i < 4; ++i) {
+        const int sn = t * p.BNI + snl[i], sp = th * p.BH + shl[i], sq = tw * p.BW + swl[i];
+        sdst[i] = (box_ok && sn < p.N && sp < p.P && sq < p.Q)
+                      ? out + (((int64_t)sn * p.OH + (sp * p.out_mul + p.out_oh)) * p.OW + (sq * p.out_mul + p.out_ow)) * p.Cout + co0 + piece * 8
+                      : nullptr;
+      }
+#pragma unroll
+      for (int cc = 0; cc < BN / 64; ++cc) {
+        const int c = cc * 64 + half * 32;
         uint32_t v[32];
         tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c), v);
-        if (c + 32 >= BN) {
+        if (cc == BN / 64 - 1) {
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
           __syncwarp();
           if (lane == 0) mbar_arrive_cluster(lead_empty);
         }
-        if (ok) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 8) {
-            uint4 o;
-            __nv_bfloat162 h0 = __floats2bfloat162_rn(__uint_as_float(v[j + 0]), __uint_as_float(v[j + 1]));
-            __nv_bfloat162 h1 = __floats2bfloat162_rn(__uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
-            __nv_bfloat162 h2 = __floats2bfloat162_rn(__uint_as_float(v[j + 4]), __uint_as_float(v[j + 5]));
-            __nv_bfloat162 h3 = __floats2bfloat162_rn(__uint_as_float(v[j + 6]), __uint_as_float(v[j + 7]));
-            o.x = *reinterpret_cast<uint32_t*>(&h0); o.y = *reinterpret_cast<uint32_t*>(&h1);
-            o.z = *reinterpret_cast<uint32_t*>(&h2); o.w = *reinterpret_cast<uint32_t*>(&h3);
-            *reinterpret_cast<uint4*>(dst + c + j) = o;
-          }
-        }
+        tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c);
         if (bn_sum != nullptr) {   // statistics of the stored (bf16-rounded) values; same butterfly as the single-CTA kernel
           float a[32], b[32];
 #pragma unroll
@@ -474,27 +494,30 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
         }
       }
       if (bn_sum != nullptr) {
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, 256;" ::: "memory");
         if (run_co != co0) {
 #pragma unroll
           for (int i = 0; i < NCH; ++i) {
-            if (run_co >= 0) { atomicAdd(&bn_sum[run_co + e + 128 * i], run_s[i]); atomicAdd(&bn_sq[run_co + e + 128 * i], run_q[i]); }
+            if (run_co >= 0 && e + 256 * i < BN) { atomicAdd(&bn_sum[run_co + e + 256 * i], run_s[i]); atomicAdd(&bn_sq[run_co + e + 256 * i], run_q[i]); }
             run_s[i] = 0.0; run_q[i] = 0.0;
           }
           run_co = co0;
         }
 #pragma unroll
         for (int i = 0; i < NCH; ++i) {
-          const int ch = e + 128 * i;
-          run_s[i] += (double)s_stat[ch]; run_q[i] += (double)s_stat[BN + ch];
-          s_stat[ch] = 0.f; s_stat[BN + ch] = 0.f;
+          const int ch = e + 256 * i;
+          if (ch < BN) {
+            run_s[i] += (double)s_stat[ch]; run_q[i] += (double)s_stat[BN + ch];
+            s_stat[ch] = 0.f; s_stat[BN + ch] = 0.f;
+          }
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, 256;" ::: "memory");
       }
     }
     if (bn_sum != nullptr && run_co >= 0) {
 #pragma unroll
-      for (int i = 0; i < NCH; ++i) { atomicAdd(&bn_sum[run_co + e + 128 * i], run_s[i]); atomicAdd(&bn_sq[run_co + e + 128 * i], run_q[i]); }
+      for (int i = 0; i < NCH; ++i)
+        if (e + 256 * i < BN) { atomicAdd(&bn_sum[run_co + e + 256 * i], run_s[i]); atomicAdd(&bn_sq[run_co + e + 256 * i], run_q[i]); }
     }
   }
   // neither CTA may leave (or free the pair's TMEM) while its peer can still signal its barriers or read its operands
@@ -517,18 +540,19 @@ template <int BN, int MT>
 static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16* out, const TcParams& p, int total_tiles,
                      cudaStream_t st, double* bn_sum, double* bn_sq) {
   constexpr int STAGES = 4;
-  constexpr size_t smem = STAGES * (MT * TC_BM * TC_BK * 2 + BN * TC_BK * 2) + (2 * STAGES + 4) * 8 + 16 + 2 * BN * 4 + 1024;
+  constexpr size_t smem = STAGES * (MT * TC_BM * TC_BK * 2 + BN * TC_BK * 2) + (2 * STAGES + 4) * 8 + 16 + 2 * BN * 4 +
+                          16 + 8 * 32 * TC_STAGE_PITCH + 1024;
   static int ctas_per_sm = 0;
   if (!ctas_per_sm) {
     IIT_CUDA(cudaFuncSetAttribute(conv3x3_tc_kernel<BN, STAGES, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int occ = 0;
-    IIT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv3x3_tc_kernel<BN, STAGES, MT>, TC_THREADS, smem));
+    IIT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv3x3_tc_kernel<BN, STAGES, MT>, TC_CONV_THREADS, smem));
     const int tmem_limit = 512 / (2 * MT * BN);   // every resident CTA holds 2*MT*BN TMEM columns for its whole life
     ctas_per_sm = occ < 1 ? 1 : (occ > tmem_limit ? tmem_limit : occ);
   }
   int grid = kNumSMs * ctas_per_sm;
   if (grid > total_tiles) grid = total_tiles;
-  conv3x3_tc_kernel<BN, STAGES, MT><<<grid, TC_THREADS, smem, st>>>(ma, mb, out, p, bn_sum, bn_sq);
+  conv3x3_tc_kernel<BN, STAGES, MT><<<grid, TC_CONV_THREADS, smem, st>>>(ma, mb, out, p, bn_sum, bn_sq);
   return 0;
 }
 
@@ -538,13 +562,14 @@ template <int BN>
 static int launch_tc2(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16* out, const TcParams& p, int total_tiles,
                       cudaStream_t st, double* bn_sum, double* bn_sq) {
   constexpr int STAGES = BN == 256 ? 6 : 8;
-  constexpr size_t smem = STAGES * (TC_BM * TC_BK * 2 + (BN / 2) * TC_BK * 2) + (2 * STAGES + 4) * 8 + 16 + 2 * BN * 4 + 1024;
+  constexpr size_t smem = STAGES * (TC_BM * TC_BK * 2 + (BN / 2) * TC_BK * 2) + (2 * STAGES + 4) * 8 + 16 + 2 * BN * 4 + 16 +
+                          8 * 32 * TC_STAGE_PITCH + 1024;
   static int max_clusters = 0;
   cudaLaunchConfig_t cfg = {};
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-  cfg.blockDim = dim3(TC_THREADS);
+  cfg.blockDim = dim3(TC_CONV_THREADS);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cfg.attrs = attr;
