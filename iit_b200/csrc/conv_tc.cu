@@ -695,6 +695,17 @@ static int conv_tc_dgrad(const void* dy, const void* w_crsk, void* dx, const iit
   const char* name = "iit_conv2d_dgrad_tc";
   if (check_tc_ptrs(dy, w_crsk, dx, name)) return 1;
   const int st_ = d->stride;
+  // Parity classes of dx that no filter tap reaches (three of the four for a 1x1 stride-2 convolution) are zeros: one memset
+  // of dx replaces their launches (each would push zeros through the tile epilogue into 128-byte rows 2 pixels apart).
+  bool zero_class = false;
+  for (int a = 0; a < st_; ++a)
+    for (int b = 0; b < st_; ++b) {
+      bool any = false;
+      for (int r = 0; r < d->r; ++r)
+        for (int s = 0; s < d->s; ++s) any = any || ((a + d->pad - r) % st_ == 0 && (b + d->pad - s) % st_ == 0);
+      zero_class = zero_class || !any;
+    }
+  if (zero_class) IIT_CUDA(cudaMemsetAsync(dx, 0, (size_t)d->n * d->h * d->w * d->c * sizeof(__nv_bfloat16), st));
   for (int a = 0; a < st_; ++a)
     for (int b = 0; b < st_; ++b) {
       TcParams tp{};
@@ -715,6 +726,7 @@ static int conv_tc_dgrad(const void* dy, const void* w_crsk, void* dx, const iit
         }
       }
       tp.ntaps = nt;
+      if (nt == 0) continue;     // zeroed above
       int rc = conv_tc_launch(dy, d->k, d->q, d->p, w_crsk, d->r * d->s * d->k, dx, tp, st, name);
       if (rc) return rc;
     }
