@@ -233,31 +233,8 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
           __syncwarp();
           if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[acc])) : "memory");
         }
-        tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c);
-        if (bn_sum != nullptr) {
-          // BatchNorm statistics of the values as stored (bf16-rounded), for the BN that follows this conv.
-          // Each lane holds one pixel x 32 channels; a butterfly that halves the channel set per step leaves
-          // lane l with the warp total of channel c+l after 31 shuffles (instead of 32 x 5).
-          float a[32], b[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            float f = ok ? __bfloat162float(__float2bfloat16_rn(__uint_as_float(v[j]))) : 0.f;
-            a[j] = f; b[j] = f * f;
-          }
-#pragma unroll
-          for (int h = 16; h >= 1; h >>= 1) {
-            const bool up = (lane & h) != 0;
-#pragma unroll
-            for (int i = 0; i < h; ++i) {
-              float sa = up ? a[i] : a[i + h], ka = up ? a[i + h] : a[i];
-              float sb = up ? b[i] : b[i + h], kb = up ? b[i + h] : b[i];
-              a[i] = ka + __shfl_xor_sync(0xffffffffu, sa, h);
-              b[i] = kb + __shfl_xor_sync(0xffffffffu, sb, h);
-            }
-          }
-          atomicAdd(&s_stat[c + lane], a[0]);
-          atomicAdd(&s_stat[BN + c + lane], b[0]);
-        }
+        // store (64 contiguous bytes per pixel) and, for the BatchNorm that follows, per-channel sums of the values as stored
+        tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c, ok, bn_sum != nullptr ? s_stat + c : nullptr, s_stat + BN + c);
       }
      }  // mt
       if (bn_sum != nullptr) {
@@ -470,28 +447,7 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
           __syncwarp();
           if (lane == 0) mbar_arrive_cluster(lead_empty);
         }
-        tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c);
-        if (bn_sum != nullptr) {   // statistics of the stored (bf16-rounded) values; same butterfly as the single-CTA kernel
-          float a[32], b[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            float f = ok ? __bfloat162float(__float2bfloat16_rn(__uint_as_float(v[j]))) : 0.f;
-            a[j] = f; b[j] = f * f;
-          }
-#pragma unroll
-          for (int h = 16; h >= 1; h >>= 1) {
-            const bool up = (lane & h) != 0;
-#pragma unroll
-            for (int i = 0; i < h; ++i) {
-              float sa = up ? a[i] : a[i + h], ka = up ? a[i + h] : a[i];
-              float sb = up ? b[i] : b[i + h], kb = up ? b[i + h] : b[i];
-              a[i] = ka + __shfl_xor_sync(0xffffffffu, sa, h);
-              b[i] = kb + __shfl_xor_sync(0xffffffffu, sb, h);
-            }
-          }
-          atomicAdd(&s_stat[c + lane], a[0]);
-          atomicAdd(&s_stat[BN + c + lane], b[0]);
-        }
+        tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c, ok, bn_sum != nullptr ? s_stat + c : nullptr, s_stat + BN + c);
       }
       if (bn_sum != nullptr) {
         asm volatile("bar.sync 1, 256;" ::: "memory");

@@ -164,8 +164,13 @@ constexpr int TC_STAGE_PITCH = 80;   // bytes per staged pixel row: 64 of data, 
 
 // pk = this lane's 32 channels as 16 packed bf16 pairs; sdst[i] points at piece `piece` of pixel sub + 8i, channel 0 of the
 // filter block (nullptr: pixel outside the tensor); c = first channel of the chunk.
+// `sum` / `sq` (shared memory, 32 floats each, or nullptr): per-channel sum and sum of squares of the staged values are
+// added to them, for the BatchNorm that follows. The staged rows make this a column sum: lane (row parity, channel pair)
+// reads 16 words, against a 31-shuffle butterfly over registers (~450 instructions per chunk, which bounded the
+// small-reduction layers). Rows outside the tensor must be staged as zeros when statistics are taken.
 __device__ __forceinline__ void tc_store_packed(const uint32_t (&pk)[16], uint8_t* stage, int lane, int sub, int piece,
-                                                __nv_bfloat16* const (&sdst)[4], int c) {
+                                                __nv_bfloat16* const (&sdst)[4], int c, float* sum = nullptr,
+                                                float* sq = nullptr) {
 #pragma unroll
   for (int j = 0; j < 16; j += 4)
     *reinterpret_cast<uint4*>(stage + lane * TC_STAGE_PITCH + j * 4) = make_uint4(pk[j], pk[j + 1], pk[j + 2], pk[j + 3]);
@@ -175,18 +180,35 @@ __device__ __forceinline__ void tc_store_packed(const uint32_t (&pk)[16], uint8_
     const uint4 o = *reinterpret_cast<const uint4*>(stage + (sub + 8 * i) * TC_STAGE_PITCH + piece * 16);
     if (sdst[i] != nullptr) *reinterpret_cast<uint4*>(sdst[i] + c) = o;
   }
+  if (sum != nullptr) {
+    const int cp = lane & 15, par = lane >> 4;       // channels 2cp, 2cp+1 of rows par, par+2, ...
+    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+      const uint32_t w = *reinterpret_cast<const uint32_t*>(stage + (2 * r + par) * TC_STAGE_PITCH + cp * 4);
+      const float f0 = __uint_as_float(w << 16), f1 = __uint_as_float(w & 0xffff0000u);
+      s0 += f0; s1 += f1; q0 = fmaf(f0, f0, q0); q1 = fmaf(f1, f1, q1);
+    }
+    s0 += __shfl_xor_sync(0xffffffffu, s0, 16); s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+    q0 += __shfl_xor_sync(0xffffffffu, q0, 16); q1 += __shfl_xor_sync(0xffffffffu, q1, 16);
+    if (par == 0) {
+      atomicAdd(&sum[2 * cp], s0); atomicAdd(&sum[2 * cp + 1], s1);
+      atomicAdd(&sq[2 * cp], q0); atomicAdd(&sq[2 * cp + 1], q1);
+    }
+  }
   __syncwarp();   // the rows are rewritten by the next chunk
 }
-// the same from the fp32 accumulator values
+// the same from the fp32 accumulator values; `keep` = this lane's pixel lies inside the tensor
 __device__ __forceinline__ void tc_store_chunk(const uint32_t (&v)[32], uint8_t* stage, int lane, int sub, int piece,
-                                               __nv_bfloat16* const (&sdst)[4], int c) {
+                                               __nv_bfloat16* const (&sdst)[4], int c, bool keep = true, float* sum = nullptr,
+                                               float* sq = nullptr) {
   uint32_t pk[16];
 #pragma unroll
   for (int j = 0; j < 16; ++j) {
     __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
-    pk[j] = *reinterpret_cast<uint32_t*>(&h);
+    pk[j] = keep ? *reinterpret_cast<uint32_t*>(&h) : 0u;
   }
-  tc_store_packed(pk, stage, lane, sub, piece, sdst, c);
+  tc_store_packed(pk, stage, lane, sub, piece, sdst, c, sum, sq);
 }
 
 // ---- host side -----------------------------------------------------------------------------------
