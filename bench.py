@@ -222,12 +222,13 @@ def hbm_bytes(name, a):
     every tensor the arithmetic needs is read once and every result written once)."""
     def ptr(v):
         return v is not None and getattr(v, "value", v) not in (None, 0)
-    if name == "iit_bn_act_fwd":            # x, residual, y, dtype, rows, c, ...
-        return a[4] * a[5] * _es(a[3]) * (2 + ptr(a[1]))
-    if name == "iit_bn_act_bwd_reduce":     # dy, y, x, dtype, rows, c, mean, invstd, relu, ...
-        return a[4] * a[5] * _es(a[3]) * (2 + (1 if a[8] else 0))
-    if name == "iit_bn_act_bwd_apply":      # dy, y, x, dx, dres, dtype, rows, c, ..., relu, stream
-        return a[6] * a[7] * _es(a[5]) * (3 + (1 if a[-2] else 0) + ptr(a[4]))
+    # a ReLU mask (one bit per element) stands in for y in the backward: 1/8 byte per element instead of _es
+    if name == "iit_bn_act_fwd":            # x, residual, y, dtype, rows, c, ..., relu, relu_mask, stream
+        return a[4] * a[5] * (_es(a[3]) * (2 + ptr(a[1])) + (0.125 if ptr(a[-2]) else 0))
+    if name == "iit_bn_act_bwd_reduce":     # dy, y, x, dtype, rows, c, mean, invstd, relu, dgamma, dbeta, relu_mask, stream
+        return a[4] * a[5] * (_es(a[3]) * 2 + ((0.125 if ptr(a[-2]) else _es(a[3])) if a[8] else 0))
+    if name == "iit_bn_act_bwd_apply":      # dy, y, x, dx, dres, dtype, rows, c, ..., relu, relu_mask, stream
+        return a[6] * a[7] * (_es(a[5]) * (3 + ptr(a[4])) + ((0.125 if ptr(a[-2]) else _es(a[5])) if a[-3] else 0))
     if name == "iit_bn_relu_maxpool_fwd":   # x, y, idx, xwin, dtype, n, h, w, c: read x, write y (+ xwin) (1/4 each) + idx (1 B)
         n, h, w, c = a[5:9]
         pooled = n * ((h + 1) // 2) * ((w + 1) // 2) * c

@@ -71,9 +71,9 @@ SIGNATURES = {
     "iit_bn_stats": [_vp, _i, _i64, _i, _vp, _vp, _vp],
     "iit_bn_finalize": [_vp, _vp, _i64, _i, _f, _f, _vp, _vp, _vp, _vp, _vp, _i, _vp],
     "iit_bn_eval_invstd": [_vp, _i, _f, _vp, _vp],
-    "iit_bn_act_fwd": [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _i, _vp],
-    "iit_bn_act_bwd_reduce": [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _i, _vp, _vp, _vp],
-    "iit_bn_act_bwd_apply": [_vp, _vp, _vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp],
+    "iit_bn_act_fwd": [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp],
+    "iit_bn_act_bwd_reduce": [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp],
+    "iit_bn_act_bwd_apply": [_vp, _vp, _vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp],
     "iit_relu_fwd": [_vp, _vp, _i, _i64, _vp],
     "iit_relu_bwd": [_vp, _vp, _vp, _i, _i64, _vp],
     "iit_add_relu_fwd": [_vp, _vp, _vp, _i, _i64, _i, _vp],

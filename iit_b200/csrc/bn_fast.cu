@@ -65,7 +65,8 @@ template <typename T>
 __global__ void __launch_bounds__(256) bn_act_fwd_fast_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y,
                                                               int64_t npacks, int C, const float* __restrict__ mean,
                                                               const float* __restrict__ invstd, const float* __restrict__ gamma,
-                                                              const float* __restrict__ beta, int relu) {
+                                                              const float* __restrict__ beta, int relu,
+                                                              uint8_t* __restrict__ mask) {
   constexpr int NP = Pack<T>::N;
   const int64_t tid = (int64_t)blockIdx.x * 256 + threadIdx.x, stride = (int64_t)gridDim.x * 256;
   const int c0 = (int)((tid * NP) % C);   // invariant: stride * NP is a multiple of C
@@ -85,8 +86,28 @@ __global__ void __launch_bounds__(256) bn_act_fwd_fast_kernel(const T* __restric
     if (relu) {
 #pragma unroll
       for (int j = 0; j < NP; ++j) o[j] = fmaxf(o[j], 0.f);
+      if (mask != nullptr) {   // one byte per pack: bit j = the STORED value of element j is > 0 (what the backward tests)
+        uint32_t bits = 0;
+#pragma unroll
+        for (int j = 0; j < NP; ++j) bits |= (round_to<T>(o[j]) > 0.f ? 1u : 0u) << j;
+        mask[i] = (uint8_t)bits;
+      }
     }
     Pack<T>::store(y + i * NP, o);
+  }
+}
+
+// ReLU mask of an activation tensor (for forwards that did not take the kernel above)
+template <typename T>
+__global__ void __launch_bounds__(256) relu_mask_kernel(const T* __restrict__ y, int64_t npacks, uint8_t* __restrict__ mask) {
+  constexpr int NP = Pack<T>::N;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < npacks; i += (int64_t)gridDim.x * 256) {
+    float v[NP];
+    Pack<T>::load(y + i * NP, v);
+    uint32_t bits = 0;
+#pragma unroll
+    for (int j = 0; j < NP; ++j) bits |= (v[j] > 0.f ? 1u : 0u) << j;
+    mask[i] = (uint8_t)bits;
   }
 }
 
@@ -145,12 +166,13 @@ template <typename T>
 __global__ void __launch_bounds__(256) bn_bwd_reduce_fast_kernel(const T* __restrict__ dy, const T* __restrict__ y,
                                                                  const T* __restrict__ x, int64_t rows, int C, int CGB,
                                                                  const float* __restrict__ mean, const float* __restrict__ invstd,
-                                                                 int relu, Red2 o) {
+                                                                 int relu, Red2 o, const uint8_t* __restrict__ mask) {
   extern __shared__ float smem[];
   constexpr int NP = Pack<T>::N;
   const int RL = 256 / CGB;
   const int cg = threadIdx.x % CGB, rl = threadIdx.x / CGB;
   const int cbase = blockIdx.y * CGB * NP, c = cbase + cg * NP;
+  const int CP = C / NP, cpk = c / NP;           // packs per row, this thread's pack within a row (mask index)
   float mu[NP], is[NP], acc[2][NP];
   load_consts<NP>(mean, c, mu); load_consts<NP>(invstd, c, is);
 #pragma unroll
@@ -159,18 +181,23 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_fast_kernel(const T* __rest
   int64_t r = (int64_t)blockIdx.x * RL + rl;
   for (; r + step < rows; r += 2 * step) {      // two rows (six 16-byte loads) in flight per thread
     uint4 rg[2], rx[2], ry[2];
+    uint32_t mb[2];
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
       rg[u] = *reinterpret_cast<const uint4*>(dy + (r + u * step) * C + c);
       rx[u] = *reinterpret_cast<const uint4*>(x + (r + u * step) * C + c);
-      if (relu) ry[u] = *reinterpret_cast<const uint4*>(y + (r + u * step) * C + c);
+      if (relu && mask != nullptr) mb[u] = mask[(r + u * step) * CP + cpk];
+      else if (relu) ry[u] = *reinterpret_cast<const uint4*>(y + (r + u * step) * C + c);
     }
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
       float g[NP], xv[NP];
       Pack<T>::unpack(rg[u], g);
       Pack<T>::unpack(rx[u], xv);
-      if (relu) {
+      if (relu && mask != nullptr) {
+#pragma unroll
+        for (int j = 0; j < NP; ++j) g[j] = (mb[u] >> j) & 1u ? g[j] : 0.f;
+      } else if (relu) {
         float yv[NP];
         Pack<T>::unpack(ry[u], yv);
 #pragma unroll
@@ -184,7 +211,11 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_fast_kernel(const T* __rest
     float g[NP], xv[NP];
     Pack<T>::load(dy + r * C + c, g);
     Pack<T>::load(x + r * C + c, xv);
-    if (relu) {
+    if (relu && mask != nullptr) {
+      const uint32_t m = mask[r * CP + cpk];
+#pragma unroll
+      for (int j = 0; j < NP; ++j) g[j] = (m >> j) & 1u ? g[j] : 0.f;
+    } else if (relu) {
       float yv[NP];
       Pack<T>::load(y + r * C + c, yv);
 #pragma unroll
@@ -204,7 +235,7 @@ __global__ void __launch_bounds__(256, 4) bn_bwd_apply_fast_kernel(const T* __re
                                                                 int64_t npacks, int C, float inv_rows, const float* __restrict__ mean,
                                                                 const float* __restrict__ invstd, const float* __restrict__ gamma,
                                                                 const double* __restrict__ dgamma, const double* __restrict__ dbeta,
-                                                                int relu) {
+                                                                int relu, const uint8_t* __restrict__ mask) {
   constexpr int NP = Pack<T>::N;
   const int64_t tid = (int64_t)blockIdx.x * 256 + threadIdx.x, stride = (int64_t)gridDim.x * 256;
   const int c0 = (int)((tid * NP) % C);
@@ -220,7 +251,11 @@ __global__ void __launch_bounds__(256, 4) bn_bwd_apply_fast_kernel(const T* __re
     float g[NP], xv[NP], o[NP];
     Pack<T>::load(dy + i * NP, g);
     Pack<T>::load(x + i * NP, xv);
-    if (relu) {
+    if (relu && mask != nullptr) {
+      const uint32_t m = mask[i];
+#pragma unroll
+      for (int j = 0; j < NP; ++j) g[j] = (m >> j) & 1u ? g[j] : 0.f;
+    } else if (relu) {
       float yv[NP];
       Pack<T>::load(y + i * NP, yv);
 #pragma unroll
@@ -502,23 +537,31 @@ int bn_stats_fast(const void* x, int dtype, int64_t rows, int C, double* sum, do
 }
 
 int bn_act_fwd_fast(const void* x, const void* res, void* y, int dtype, int64_t rows, int C, const float* mean, const float* invstd,
-                    const float* gamma, const float* beta, int relu, cudaStream_t st) {
+                    const float* gamma, const float* beta, int relu, uint8_t* mask, cudaStream_t st) {
   const int64_t npacks = rows * C / pack_n(dtype);
   IIT_DISPATCH_DTYPE(dtype, T, {
     bn_act_fwd_fast_kernel<T><<<grid_for(npacks, 256 * 2), 256, 0, st>>>((const T*)x, (const T*)res, (T*)y, npacks, C, mean, invstd,
-                                                                        gamma, beta, relu);
+                                                                        gamma, beta, relu, mask);
   })
   IIT_LAUNCH_CHECK("iit_bn_act_fwd");
   return 0;
 }
 
+int relu_mask_fast(const void* y, int dtype, int64_t rows, int C, uint8_t* mask, cudaStream_t st) {
+  const int64_t npacks = rows * C / pack_n(dtype);
+  IIT_DISPATCH_DTYPE(dtype, T, { relu_mask_kernel<T><<<grid_for(npacks, 256 * 2), 256, 0, st>>>((const T*)y, npacks, mask); })
+  IIT_LAUNCH_CHECK("iit_bn_act_fwd(mask)");
+  return 0;
+}
+
 int bn_bwd_reduce_fast(const void* dy, const void* y, const void* x, int dtype, int64_t rows, int C, const float* mean,
-                       const float* invstd, int relu, double* dgamma, double* dbeta, cudaStream_t st) {
+                       const float* invstd, int relu, double* dgamma, double* dbeta, const uint8_t* mask, cudaStream_t st) {
   int CGB; dim3 grid; size_t smem;
   red_geometry(rows, C, pack_n(dtype), &CGB, &grid, &smem);
   Red2 o{{dgamma, dbeta}};
   IIT_DISPATCH_DTYPE(dtype, T, {
-    bn_bwd_reduce_fast_kernel<T><<<grid, 256, smem, st>>>((const T*)dy, (const T*)y, (const T*)x, rows, C, CGB, mean, invstd, relu, o);
+    bn_bwd_reduce_fast_kernel<T><<<grid, 256, smem, st>>>((const T*)dy, (const T*)y, (const T*)x, rows, C, CGB, mean, invstd, relu, o,
+                                                          mask);
   })
   IIT_LAUNCH_CHECK("iit_bn_act_bwd_reduce");
   return 0;
@@ -526,12 +569,12 @@ int bn_bwd_reduce_fast(const void* dy, const void* y, const void* x, int dtype, 
 
 int bn_bwd_apply_fast(const void* dy, const void* y, const void* x, void* dx, void* dres, int dtype, int64_t rows, int C,
                       const float* mean, const float* invstd, const float* gamma, const double* dgamma, const double* dbeta,
-                      int relu, cudaStream_t st) {
+                      int relu, const uint8_t* mask, cudaStream_t st) {
   const int64_t npacks = rows * C / pack_n(dtype);
   IIT_DISPATCH_DTYPE(dtype, T, {
     bn_bwd_apply_fast_kernel<T><<<grid_for(npacks, 256 * 2), 256, 0, st>>>((const T*)dy, (const T*)y, (const T*)x, (T*)dx, (T*)dres,
                                                                           npacks, C, 1.f / (float)rows, mean, invstd, gamma, dgamma,
-                                                                          dbeta, relu);
+                                                                          dbeta, relu, mask);
   })
   IIT_LAUNCH_CHECK("iit_bn_act_bwd_apply");
   return 0;
@@ -587,7 +630,8 @@ extern "C" int iit_bn_relu_maxpool_bwd(const void* dy, const int8_t* idx, const 
     red_geometry(prows, c, np, &CGB, &grid, &smem);
     Red2 o{{dgamma, dbeta}};
     IIT_DISPATCH_DTYPE(dtype, T, {
-      bn_bwd_reduce_fast_kernel<T><<<grid, 256, smem, st>>>((const T*)dy, (const T*)y, (const T*)xwin, prows, c, CGB, mean, invstd, 1, o);
+      bn_bwd_reduce_fast_kernel<T><<<grid, 256, smem, st>>>((const T*)dy, (const T*)y, (const T*)xwin, prows, c, CGB, mean, invstd, 1, o,
+                                                            nullptr);
     })
     IIT_LAUNCH_CHECK("iit_bn_relu_maxpool_bwd(reduce)");
   }

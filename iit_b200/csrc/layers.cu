@@ -462,12 +462,26 @@ __global__ void __launch_bounds__(256) adam_dev_kernel(float* __restrict__ p, co
 bool bn_fast_ok(int dtype, int C, const void* a, const void* b, const void* c, const void* d, const void* e);
 int bn_stats_fast(const void* x, int dtype, int64_t rows, int C, double* sum, double* sq, cudaStream_t st);
 int bn_act_fwd_fast(const void* x, const void* res, void* y, int dtype, int64_t rows, int C, const float* mean, const float* invstd,
-                    const float* gamma, const float* beta, int relu, cudaStream_t st);
+                    const float* gamma, const float* beta, int relu, uint8_t* mask, cudaStream_t st);
+int relu_mask_fast(const void* y, int dtype, int64_t rows, int C, uint8_t* mask, cudaStream_t st);
 int bn_bwd_reduce_fast(const void* dy, const void* y, const void* x, int dtype, int64_t rows, int C, const float* mean,
-                       const float* invstd, int relu, double* dgamma, double* dbeta, cudaStream_t st);
+                       const float* invstd, int relu, double* dgamma, double* dbeta, const uint8_t* mask, cudaStream_t st);
 int bn_bwd_apply_fast(const void* dy, const void* y, const void* x, void* dx, void* dres, int dtype, int64_t rows, int C,
                       const float* mean, const float* invstd, const float* gamma, const double* dgamma, const double* dbeta,
-                      int relu, cudaStream_t st);
+                      int relu, const uint8_t* mask, cudaStream_t st);
+
+// fp64 per-channel sums of a BatchNorm backward -> fp32 parameter gradients, written or accumulated in place (the
+// optimizer's flat gradient buffer), and the layer's persistent accumulator cleared for its next backward: one launch
+// instead of a fill, two casts and two accumulation kernels per layer
+__global__ void bn_param_grads_kernel(double* __restrict__ sums, int c, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                      int accumulate, int clear) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= c) return;
+  const float dg = (float)sums[i], db = (float)sums[c + i];
+  dgamma[i] = accumulate ? dgamma[i] + dg : dg;
+  dbeta[i] = accumulate ? dbeta[i] + db : db;
+  if (clear) { sums[i] = 0.0; sums[c + i] = 0.0; }
+}
 
 }  // namespace iit
 
@@ -512,19 +526,6 @@ extern "C" int iit_bn_finalize(double* sum, double* sqsum, int64_t rows, int c, 
   return 0;
 }
 
-// fp64 per-channel sums of a BatchNorm backward -> fp32 parameter gradients, written or accumulated in place (the
-// optimizer's flat gradient buffer), and the layer's persistent accumulator cleared for its next backward: one launch
-// instead of a fill, two casts and two accumulation kernels per layer
-__global__ void bn_param_grads_kernel(double* __restrict__ sums, int c, float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                      int accumulate, int clear) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= c) return;
-  const float dg = (float)sums[i], db = (float)sums[c + i];
-  dgamma[i] = accumulate ? dgamma[i] + dg : dg;
-  dbeta[i] = accumulate ? dbeta[i] + db : db;
-  if (clear) { sums[i] = 0.0; sums[c + i] = 0.0; }
-}
-
 extern "C" int iit_bn_param_grads(double* sums, int c, float* dgamma, float* dbeta, int accumulate, int clear_sums, void* stream) {
   IIT_REQUIRE(sums && dgamma && dbeta && c >= 1, "iit_bn_param_grads: bad arguments");
   bn_param_grads_kernel<<<(c + 127) / 128, 128, 0, as_stream(stream)>>>(sums, c, dgamma, dbeta, accumulate, clear_sums);
@@ -540,10 +541,12 @@ extern "C" int iit_bn_eval_invstd(const float* running_var, int c, float eps, fl
 }
 
 extern "C" int iit_bn_act_fwd(const void* x, const void* residual, void* y, int dtype, int64_t rows, int c, const float* mean,
-                              const float* invstd, const float* gamma, const float* beta, int relu, void* stream) {
+                              const float* invstd, const float* gamma, const float* beta, int relu, uint8_t* relu_mask,
+                              void* stream) {
   IIT_REQUIRE(x && y && mean && invstd && gamma && beta, "iit_bn_act_fwd: null pointer");
+  if (!relu) relu_mask = nullptr;
   if (bn_fast_ok(dtype, c, x, residual, y, mean, invstd) && bn_fast_ok(dtype, c, gamma, beta, nullptr, nullptr, nullptr))
-    return bn_act_fwd_fast(x, residual, y, dtype, rows, c, mean, invstd, gamma, beta, relu, as_stream(stream));
+    return bn_act_fwd_fast(x, residual, y, dtype, rows, c, mean, invstd, gamma, beta, relu, relu_mask, as_stream(stream));
   IIT_REQUIRE(c % 4 == 0, "iit_bn_act_fwd: channels must be a multiple of 4");
   int64_t n4 = rows * c / 4;
   IIT_DISPATCH_DTYPE(dtype, T, {
@@ -551,15 +554,18 @@ extern "C" int iit_bn_act_fwd(const void* x, const void* residual, void* y, int 
                                                                                mean, invstd, gamma, beta, relu);
   })
   IIT_LAUNCH_CHECK("iit_bn_act_fwd");
+  // the generic kernel does not write the mask: derive it from y where the 16-byte backward kernels could ask for it
+  if (relu_mask && bn_fast_ok(dtype, c, y, nullptr, nullptr, nullptr, nullptr))
+    return relu_mask_fast(y, dtype, rows, c, relu_mask, as_stream(stream));
   return 0;
 }
 
 extern "C" int iit_bn_act_bwd_reduce(const void* dy, const void* y, const void* x, int dtype, int64_t rows, int c,
                                      const float* mean, const float* invstd, int relu, double* dgamma, double* dbeta,
-                                     void* stream) {
+                                     const uint8_t* relu_mask, void* stream) {
   IIT_REQUIRE(dy && x && mean && invstd && dgamma && dbeta && (!relu || y), "iit_bn_act_bwd_reduce: null pointer");
   if (bn_fast_ok(dtype, c, dy, y, x, mean, invstd))
-    return bn_bwd_reduce_fast(dy, y, x, dtype, rows, c, mean, invstd, relu, dgamma, dbeta, as_stream(stream));
+    return bn_bwd_reduce_fast(dy, y, x, dtype, rows, c, mean, invstd, relu, dgamma, dbeta, relu_mask, as_stream(stream));
   IIT_REQUIRE(c % 4 == 0 && (c / 4 <= 64 ? 256 % (c / 4) == 0 : (c / 4) % 64 == 0), "iit_bn_act_bwd_reduce: unsupported channel count %d", c);
   RedPtrs2 o{{dgamma, dbeta}};
   IIT_DISPATCH_DTYPE(dtype, T, {
@@ -572,10 +578,11 @@ extern "C" int iit_bn_act_bwd_reduce(const void* dy, const void* y, const void* 
 
 extern "C" int iit_bn_act_bwd_apply(const void* dy, const void* y, const void* x, void* dx, void* dres, int dtype, int64_t rows,
                                     int c, const float* mean, const float* invstd, const float* gamma, const double* dgamma,
-                                    const double* dbeta, int relu, void* stream) {
+                                    const double* dbeta, int relu, const uint8_t* relu_mask, void* stream) {
   IIT_REQUIRE(dy && x && dx && mean && invstd && gamma && dgamma && dbeta && (!relu || y), "iit_bn_act_bwd_apply: null pointer");
   if (bn_fast_ok(dtype, c, dy, y, x, dx, dres) && bn_fast_ok(dtype, c, mean, invstd, gamma, nullptr, nullptr))
-    return bn_bwd_apply_fast(dy, y, x, dx, dres, dtype, rows, c, mean, invstd, gamma, dgamma, dbeta, relu, as_stream(stream));
+    return bn_bwd_apply_fast(dy, y, x, dx, dres, dtype, rows, c, mean, invstd, gamma, dgamma, dbeta, relu, relu_mask,
+                             as_stream(stream));
   IIT_REQUIRE(c % 4 == 0, "iit_bn_act_bwd_apply: channels must be a multiple of 4");
   int64_t n4 = rows * c / 4;
   IIT_DISPATCH_DTYPE(dtype, T, {

@@ -525,6 +525,9 @@ def new_bn_sums(c: int, device) -> torch.Tensor:
     return torch.zeros((2, c), dtype=torch.float64, device=device)
 
 
+BN_RELU_MASK = True     # BatchNorm+ReLU forward keeps a bit mask of the positive outputs for its backward (tests flip it)
+
+
 class _BNActFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums, acc, tracked,
@@ -553,16 +556,20 @@ class _BNActFn(torch.autograd.Function):
             invstd = torch.empty(c, dtype=torch.float32, device=x.device)
             call("iit_bn_eval_invstd", _p(running_var), c, float(eps), _p(invstd), st)
         y = torch.empty_like(x)
+        # ReLU mask for the backward, one bit per element (it then reads 1/16 of what y would cost): only when one follows
+        mask = None
+        if BN_RELU_MASK and relu and any(ctx.needs_input_grad[:4]):
+            mask = torch.empty(rows * c // (8 if x.dtype == torch.bfloat16 else 4), dtype=torch.uint8, device=x.device)
         call("iit_bn_act_fwd", _p(x), _p(residual), _p(y), _dt(x), rows, c, _p(mean), _p(invstd), _p(gamma), _p(beta),
-             int(relu), st)
-        ctx.save_for_backward(x, y if relu else None, gamma, mean, invstd)
+             int(relu), _p(mask), st)
+        ctx.save_for_backward(x, y if relu else None, gamma, mean, invstd, mask)
         ctx.relu, ctx.training, ctx.has_res = relu, training, residual is not None
         ctx.bacc, ctx.pgrads = bacc, pgrads
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, y, gamma, mean, invstd = ctx.saved_tensors
+        x, y, gamma, mean, invstd, mask = ctx.saved_tensors
         dy = _cl(dy)
         n, c, h, w = x.shape
         rows = n * h * w
@@ -571,13 +578,13 @@ class _BNActFn(torch.autograd.Function):
         red = ctx.bacc if ctx.bacc is not None else torch.zeros((2, c), dtype=torch.float64, device=x.device)
         try:
             call("iit_bn_act_bwd_reduce", _p(dy), _p(y), _p(x), _dt(x), rows, c, _p(mean), _p(invstd), int(ctx.relu),
-                 _p(red[0]), _p(red[1]), st)
+                 _p(red[0]), _p(red[1]), _p(mask), st)
             dx = torch.empty_like(x)
             dres = torch.empty_like(x) if ctx.has_res else None
             # eval mode: statistics are constants, so the two correction terms vanish
             corr = red if ctx.training else torch.zeros_like(red)
             call("iit_bn_act_bwd_apply", _p(dy), _p(y), _p(x), _p(dx), _p(dres), _dt(x), rows, c, _p(mean), _p(invstd),
-                 _p(gamma), _p(corr[0]), _p(corr[1]), int(ctx.relu), st)
+                 _p(gamma), _p(corr[0]), _p(corr[1]), int(ctx.relu), _p(mask), st)
             dgamma, dbeta = _bn_param_grads(red, c, ctx.pgrads, ctx.bacc is not None, st)
         except Exception:
             if ctx.bacc is not None:

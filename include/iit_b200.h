@@ -237,20 +237,23 @@ int iit_bn_finalize(double* sum, double* sqsum, int64_t rows, int c, float eps, 
                     float* mean, float* invstd, float* running_mean, float* running_var,
                     int64_t* num_batches_tracked, int clear_sums, void* stream);
 /* y = act((x-mean)*invstd*gamma+beta (+ residual)); act = relu if relu!=0. In eval mode pass
- * mean=running_mean and invstd=1/sqrt(running_var+eps) (iit_bn_eval_invstd). */
+ * mean=running_mean and invstd=1/sqrt(running_var+eps) (iit_bn_eval_invstd).
+ * relu_mask (may be NULL): one byte per pack of 8 (bf16) or 4 (fp32) consecutive elements, bit j = element j of y is
+ * > 0. The backward reads it instead of y (1/16 of the bytes); rows*c/8 (rows*c/4) bytes. */
 int iit_bn_eval_invstd(const float* running_var, int c, float eps, float* invstd, void* stream);
 int iit_bn_act_fwd(const void* x, const void* residual, void* y, int dtype, int64_t rows, int c,
                    const float* mean, const float* invstd, const float* gamma, const float* beta,
-                   int relu, void* stream);
+                   int relu, uint8_t* relu_mask, void* stream);
 /* Backward of the above in training mode. Pass 1 reduces dgamma = sum(g*xhat), dbeta = sum(g)
  * with g = dy * [y>0 if relu]; pass 2 writes dx (and dresidual = g when dres != NULL).
- * dgamma/dbeta fp64 [c] zeroed by the caller. */
+ * dgamma/dbeta fp64 [c] zeroed by the caller. relu_mask: the mask iit_bn_act_fwd wrote, or NULL (y is read). */
 int iit_bn_act_bwd_reduce(const void* dy, const void* y, const void* x, int dtype, int64_t rows, int c,
                           const float* mean, const float* invstd, int relu,
-                          double* dgamma, double* dbeta, void* stream);
+                          double* dgamma, double* dbeta, const uint8_t* relu_mask, void* stream);
 int iit_bn_act_bwd_apply(const void* dy, const void* y, const void* x, void* dx, void* dres, int dtype,
                          int64_t rows, int c, const float* mean, const float* invstd, const float* gamma,
-                         const double* dgamma, const double* dbeta, int relu, void* stream);
+                         const double* dgamma, const double* dbeta, int relu, const uint8_t* relu_mask,
+                         void* stream);
 int iit_relu_fwd(const void* x, void* y, int dtype, int64_t n, void* stream);
 int iit_relu_bwd(const void* dy, const void* y, void* dx, int dtype, int64_t n, void* stream);
 int iit_add_relu_fwd(const void* a, const void* b, void* y, int dtype, int64_t n, int relu, void* stream);

@@ -21,7 +21,7 @@ def to_bytes(v, unit):
 launches = []
 for r in rows[2:]:
     name = r[col["Kernel Name"]]
-    if "conv3x3_tc_kernel" not in name and "conv_win_kernel" not in name:
+    if "conv3x3_tc" not in name and "conv_win_kernel" not in name:
         continue
     rd = to_bytes(r[col["dram__bytes_read.sum"]], units[col["dram__bytes_read.sum"]])
     wr = to_bytes(r[col["dram__bytes_write.sum"]], units[col["dram__bytes_write.sum"]])

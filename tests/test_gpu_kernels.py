@@ -734,3 +734,34 @@ def test_backward_adds_parameter_gradients_into_marked_buffers(ops):
     gn2, _ = run(False, 2)
     for a, b in zip(gd2, gn2):      # (g + p1) + p2 + ... against g + (p1 + p2 + ...): fp32 rounding order only
         torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("dtype,c", [(torch.bfloat16, 64), (torch.bfloat16, 256), (torch.float32, 64), (torch.bfloat16, 4)])
+def test_bn_relu_bitmask_backward_equals_reading_y(ops, dtype, c):
+    """BatchNorm(+residual)+ReLU keeps one bit per output element (y > 0) for its backward instead of having it re-read y:
+    same dx, dresidual, dgamma, dbeta bit for bit (c = 4 takes the generic kernels, which ignore the mask)."""
+    g = torch.Generator().manual_seed(31)
+    x = (torch.randn(5, c, 6, 6, generator=g) * 2).to(DEV).to(dtype).contiguous(memory_format=torch.channels_last)
+    r = torch.randn(5, c, 6, 6, generator=g).to(DEV).to(dtype).contiguous(memory_format=torch.channels_last)
+    gy = torch.randn(5, c, 6, 6, generator=g).to(DEV).to(dtype).contiguous(memory_format=torch.channels_last)
+    gamma, beta = (torch.rand(c, generator=g) + 0.5).to(DEV), torch.randn(c, generator=g).to(DEV)
+
+    def run(use_mask, with_res):
+        was = ops.BN_RELU_MASK
+        ops.BN_RELU_MASK = use_mask
+        try:
+            xd, rd = x.clone().requires_grad_(True), r.clone().requires_grad_(True)
+            gd, bd = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+            y = ops.bn_act(xd, gd, bd, rd if with_res else None, torch.zeros(c, device=DEV), torch.ones(c, device=DEV), True, 0.1,
+                           1e-5, True)
+            y.backward(gy)
+            return y.detach(), xd.grad, rd.grad, gd.grad, bd.grad
+        finally:
+            ops.BN_RELU_MASK = was
+
+    for with_res in (False, True):
+        a, b = run(True, with_res), run(False, with_res)
+        for u, v in zip(a, b):
+            assert (u is None) == (v is None)
+            if u is not None:
+                assert torch.equal(u, v)
