@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(256) bn_stats_fast_kernel(const T* __restrict_
   reduce_finish<2, NP>(acc, cg, rl, CGB, RL, cbase, outs, smem);
 }
 
-template <typename T>
+template <typename T, int RU>
 __global__ void __launch_bounds__(256) bn_bwd_reduce_fast_kernel(const T* __restrict__ dy, const T* __restrict__ y,
                                                                  const T* __restrict__ x, int64_t rows, int C, int CGB,
                                                                  const float* __restrict__ mean, const float* __restrict__ invstd,
@@ -198,18 +198,18 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_fast_kernel(const T* __rest
   for (int j = 0; j < NP; ++j) { acc[0][j] = 0.f; acc[1][j] = 0.f; }
   const int64_t step = (int64_t)gridDim.x * RL;
   int64_t r = (int64_t)blockIdx.x * RL + rl;
-  for (; r + step < rows; r += 2 * step) {      // two rows (six 16-byte loads) in flight per thread
-    uint4 rg[2], rx[2], ry[2];
-    uint32_t mb[2];
+  for (; r + (RU - 1) * step < rows; r += RU * step) {      // RU rows in flight per thread
+    uint4 rg[RU], rx[RU], ry[RU];
+    uint32_t mb[RU];
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < RU; ++u) {
       rg[u] = *reinterpret_cast<const uint4*>(dy + (r + u * step) * C + c);
       rx[u] = *reinterpret_cast<const uint4*>(x + (r + u * step) * C + c);
       if (relu && mask != nullptr) mb[u] = mask[(r + u * step) * CP + cpk];
       else if (relu) ry[u] = *reinterpret_cast<const uint4*>(y + (r + u * step) * C + c);
     }
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < RU; ++u) {
       float g[NP], xv[NP];
       Pack<T>::unpack(rg[u], g);
       Pack<T>::unpack(rx[u], xv);
@@ -605,9 +605,9 @@ int bn_bwd_reduce_fast(const void* dy, const void* y, const void* x, int dtype, 
   int CGB; dim3 grid; size_t smem;
   red_geometry(rows, C, pack_n(dtype), &CGB, &grid, &smem);
   Red2 o{{dgamma, dbeta}};
-  IIT_DISPATCH_DTYPE(dtype, T, {
-    bn_bwd_reduce_fast_kernel<T><<<grid, 256, smem, st>>>((const T*)dy, (const T*)y, (const T*)x, rows, C, CGB, mean, invstd, relu, o,
-                                                          mask);
+  IIT_DISPATCH_DTYPE(dtype, T, {   // four rows in flight per thread (two: +0.1 ms per step)
+    bn_bwd_reduce_fast_kernel<T, 4><<<grid, 256, smem, st>>>((const T*)dy, (const T*)y, (const T*)x, rows, C, CGB, mean, invstd, relu, o,
+                                                             mask);
   })
   IIT_LAUNCH_CHECK("iit_bn_act_bwd_reduce");
   return 0;
@@ -676,7 +676,7 @@ extern "C" int iit_bn_relu_maxpool_bwd(const void* dy, const int8_t* idx, const 
     red_geometry(prows, c, np, &CGB, &grid, &smem);
     Red2 o{{dgamma, dbeta}};
     IIT_DISPATCH_DTYPE(dtype, T, {
-      bn_bwd_reduce_fast_kernel<T><<<grid, 256, smem, st>>>((const T*)dy, (const T*)y, (const T*)xwin, prows, c, CGB, mean, invstd, 1, o,
+      bn_bwd_reduce_fast_kernel<T, 2><<<grid, 256, smem, st>>>((const T*)dy, (const T*)y, (const T*)xwin, prows, c, CGB, mean, invstd, 1, o,
                                                             nullptr);
     })
     IIT_LAUNCH_CHECK("iit_bn_relu_maxpool_bwd(reduce)");
