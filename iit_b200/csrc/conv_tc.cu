@@ -855,25 +855,46 @@ __global__ void __launch_bounds__(TC_THREADS) wgrad3x3_tc_kernel(const __grid_co
   }
 }
 
-// out[i] (+)= sum over splits of part[z][i], in fixed order (deterministic); four partials in flight per thread
+// out[i] (+)= sum over splits of part[z][i], in a fixed order (deterministic). A block is 64 float4 columns x 4 groups of
+// splits: the small filters (layer1: 9216 float4 columns, 148 splits) otherwise leave 36 blocks walking 148 partials each.
+// Four partials in flight per thread; the four group sums are added in order by the first group.
 __global__ void __launch_bounds__(256) tc_splitk_reduce_kernel(const float* __restrict__ part, float* __restrict__ out,
                                                                int64_t n, int splits, int accumulate) {
+  __shared__ float4 s_part[3][64];
   const int64_t n4 = n >> 2;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
-    float4 s = accumulate ? reinterpret_cast<const float4*>(out)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
-    int z = 0;
-    for (; z + 4 <= splits; z += 4) {
-      float4 v[4];
+  const int lane_col = threadIdx.x & 63, zg = threadIdx.x >> 6;
+  const int per = (splits + 3) >> 2;
+  const int z0 = zg * per, z1 = min(splits, z0 + per);
+  for (int64_t base = (int64_t)blockIdx.x * 64; base < n4; base += (int64_t)gridDim.x * 64) {   // block-uniform trip count
+    const int64_t i = base + lane_col;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < n4) {
+      int z = z0;
+      for (; z + 4 <= z1; z += 4) {
+        float4 v[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) v[u] = reinterpret_cast<const float4*>(part + (int64_t)(z + u) * n)[i];
+        for (int u = 0; u < 4; ++u) v[u] = reinterpret_cast<const float4*>(part + (int64_t)(z + u) * n)[i];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+        for (int u = 0; u < 4; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+      }
+      for (; z < z1; ++z) {
+        float4 v = reinterpret_cast<const float4*>(part + (int64_t)z * n)[i];
+        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+      }
     }
-    for (; z < splits; ++z) {
-      float4 v = reinterpret_cast<const float4*>(part + (int64_t)z * n)[i];
-      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    if (zg > 0) s_part[zg - 1][lane_col] = s;
+    __syncthreads();
+    if (zg == 0 && i < n4) {
+      float4 t = accumulate ? reinterpret_cast<const float4*>(out)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+      t.x += s.x; t.y += s.y; t.z += s.z; t.w += s.w;
+#pragma unroll
+      for (int g = 0; g < 3; ++g) {
+        const float4 v = s_part[g][lane_col];
+        t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
+      }
+      reinterpret_cast<float4*>(out)[i] = t;
     }
-    reinterpret_cast<float4*>(out)[i] = s;
+    __syncthreads();
   }
 }
 
@@ -995,7 +1016,7 @@ static int wgrad_tc_impl(const void* dy, const void* x, float* dw, const iit_con
     int rc = wgrad_win(dy, x, (float*)scratch, d, &nsplit, as_stream(stream), "iit_conv2d_wgrad_tc");
     if (rc) return rc;
     const int64_t n = (int64_t)d->k * d->r * d->s * d->c;
-    tc_splitk_reduce_kernel<<<grid_for(n / 4, 256), 256, 0, as_stream(stream)>>>((const float*)scratch, dw, n, nsplit, accumulate);
+    tc_splitk_reduce_kernel<<<grid_for(n / 4, 64), 256, 0, as_stream(stream)>>>((const float*)scratch, dw, n, nsplit, accumulate);
     IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc(reduce)");
     return 0;
   }
@@ -1017,7 +1038,7 @@ static int wgrad_tc_impl(const void* dy, const void* x, float* dw, const iit_con
   if (rc) return rc;
   IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc");
   int64_t n = (int64_t)d->k * d->r * d->s * d->c;
-  tc_splitk_reduce_kernel<<<grid_for(n / 4, 256), 256, 0, st>>>((const float*)scratch, dw, n, splits, accumulate);
+  tc_splitk_reduce_kernel<<<grid_for(n / 4, 64), 256, 0, st>>>((const float*)scratch, dw, n, splits, accumulate);
   IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc(reduce)");
   return 0;
 }
