@@ -765,3 +765,31 @@ def test_bn_relu_bitmask_backward_equals_reading_y(ops, dtype, c):
             assert (u is None) == (v is None)
             if u is not None:
                 assert torch.equal(u, v)
+
+
+def test_batched_filter_relayout_matches_single(ops):
+    """iit_filter_relayout_batched (one launch for every filter copy of the model; CRSK copies of channels-last filters go
+    through a shared-memory transposition) against iit_filter_relayout entry by entry, ragged sizes included."""
+    from iit_b200._lib import IIT_BF16, Relayout
+    g = torch.Generator().manual_seed(41)
+    filters = [torch.randn(k, c, r, r, generator=g).to(DEV).contiguous(memory_format=torch.channels_last)
+               for k, c, r in [(64, 64, 3), (128, 64, 1), (70, 40, 3), (33, 7, 1)]]
+    filters.append(torch.randn(48, 24, 3, 3, generator=g).to(DEV))           # NCHW-contiguous: the generic path
+    table = (Relayout * (2 * len(filters)))()
+    outs = []
+    for i, w in enumerate(filters):
+        for j in range(2):
+            o = torch.full((w.numel(),), 7.0, dtype=torch.bfloat16, device=DEV)
+            outs.append(o)
+            e = table[2 * i + j]
+            e.w, e.out = w.data_ptr(), o.data_ptr()
+            for d in range(4):
+                e.stride[d] = w.stride(d)
+            e.k, e.c, e.r, e.s = w.shape
+            e.to_crsk, e.dtype = j, IIT_BF16
+    dev_table = torch.frombuffer(bytearray(bytes(table)), dtype=torch.uint8).clone().to(DEV)
+    ops.filter_relayout_batched(dev_table, len(outs), max(w.numel() for w in filters))
+    for i, w in enumerate(filters):
+        for j in range(2):
+            ref = ops.filter_relayout(w, bool(j), torch.bfloat16)
+            assert torch.equal(outs[2 * i + j], ref), (tuple(w.shape), j)
