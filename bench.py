@@ -304,6 +304,35 @@ def run_ioi_extra(rank, world, dev, dp, batch=1024, steps=3, warmup=2):
             "steps": steps, "warmup": warmup, "dtype": "bf16", "last_step_metrics": m}
 
 
+def run_pvr84_extra(rank, world, dev, dp, batch=2048, steps=3, warmup=2):
+    """The headline step at the reference's DEFAULT image size (pad 7: 84x84, task_loader.py:10,43); the contract size is 56.
+    Odd spatial sizes downstream (21, 11, 6, 3); 11 * F84 = 6.51 GFLOP per pair."""
+    from iit_b200.model_pairs import StrictIITModelPair
+    from iit_b200.tasks.mnist_pvr.get_alignment import get_alignment
+    from oracle import restate as R
+    ll, hl, corr = get_alignment("mnist_pvr", {"input_shape": (1, 3, 84, 84)}, device=dev, dtype=torch.bfloat16)
+    ll.load_state_dict(R.resnet18_state_dict(0))
+    pair = StrictIITModelPair(hl, ll, corr, training_args={"lr": 1e-3, "cuda_graphs": True})
+    if world > 1:
+        pair.dp = dp
+    opt = pair.make_optimizer()
+    ll.train()
+
+    def gen(seed):
+        parts = [R.synthetic_pvr(min(512, batch - i), seed * 1000 + i, size=84) for i in range(0, batch, 512)]
+        return tuple(torch.cat([p[j] for p in parts]).to(dev) for j in range(3))
+    base, src = gen(51 + 2 * rank), gen(52 + 2 * rank)
+    pair.prepare_graphs(base, src, pair.loss_fn, opt)
+    for _ in range(warmup):
+        pair.run_train_step(base, src, pair.loss_fn, opt)
+    sec, m = _timed_region(dp, dev, lambda: pair.run_train_step(base, src, pair.loss_fn, opt), steps)
+    return {"metric": "iit_train_pairs_per_sec", "value": batch * world * steps / sec, "unit": UNIT, "ms_per_step": 1e3 * sec / steps,
+            "step_tflops": 11 * 592_125_440 * batch * world * steps / sec / 1e12,
+            "config": {"workload": f"MNIST-PVR IIT+behaviour+strict train step at 84x84 (the reference's default pad), batch {batch} "
+                                   f"pairs/GPU, bf16, CUDA-graph replay", "image": "3x84x84", "parallelism": f"dp{world}"},
+            "steps": steps, "warmup": warmup, "dtype": "bf16", "last_step_metrics": m}
+
+
 def run_sweep_extra(rank, world, dev, dp, batch=4096, batches_per_rank=2):
     """BASELINE.json configs[4]: the causality sweep of eval_causality.py -- 17 hook points x 4 HL nodes, counterfactuals
     generated on the device, batches sharded over ranks, counts gathered at the end. One "pair" = one (base,
@@ -453,7 +482,7 @@ def run_ours(args, rank, world, local):
         pair._static = None
         ops_mod._batch_cache.clear()
         torch.cuda.empty_cache()
-        for name, fn in (("iia_eval_sweep", run_sweep_extra), ("ioi_train", run_ioi_extra)):
+        for name, fn in (("iia_eval_sweep", run_sweep_extra), ("ioi_train", run_ioi_extra), ("pvr_train_84px", run_pvr84_extra)):
             try:
                 extras[name] = fn(rank, world, dev, dp)
             except Exception as e:  # the headline line must survive a failure here; the failure is reported, not hidden
