@@ -35,7 +35,7 @@ class Relayout(C.Structure):
     """iit_relayout_t"""
     _fields_ = [("w", C.c_void_p), ("out", C.c_void_p), ("stride", C.c_int64 * 4),
                 ("k", C.c_int32), ("c", C.c_int32), ("r", C.c_int32), ("s", C.c_int32),
-                ("to_crsk", C.c_int32), ("dtype", C.c_int32)]
+                ("to_crsk", C.c_int32), ("dtype", C.c_int32), ("out_pitch", C.c_int64)]
 
 
 _vp, _i, _i64, _f, _d, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_double, C.c_size_t

@@ -362,7 +362,7 @@ __global__ void __launch_bounds__(256) filter_relayout_batched_kernel(const iit_
   const uint32_t n = (uint32_t)e.k * e.c * e.r * e.s;            // 32-bit index arithmetic (host checks n < 2^31)
   const float* __restrict__ w = static_cast<const float*>(e.w);
   const uint32_t C = e.c, K = e.k, R = e.r, S = e.s;
-  if (e.to_crsk && e.stride[1] == 1 && e.dtype == IIT_BF16) {
+  if (e.to_crsk && e.stride[1] == 1 && e.dtype == IIT_BF16 && e.out_pitch == 0) {
     // channels-last master filter -> CRSK: a [k][c] -> [c][k] transposition per tap. Through a 32 x 33 shared tile both the
     // fp32 reads (32 consecutive c) and the bf16 writes (32 consecutive k) are contiguous; element by element the reads were
     // R*S*C floats apart (157 us per refresh of all ResNet-18 filters).
@@ -394,8 +394,13 @@ __global__ void __launch_bounds__(256) filter_relayout_batched_kernel(const iit_
     if (!e.to_crsk) { c = rem % C; rem /= C; s = rem % S; rem /= S; r = rem % R; k = rem / R; }
     else { k = rem % K; rem /= K; s = rem % S; rem /= S; r = rem % R; c = rem / R; }
     const float v = w[(int64_t)k * e.stride[0] + (int64_t)c * e.stride[1] + (int64_t)r * e.stride[2] + (int64_t)s * e.stride[3]];
-    if (e.dtype == IIT_BF16) static_cast<__nv_bfloat16*>(e.out)[i] = __float2bfloat16_rn(v);
-    else static_cast<float*>(e.out)[i] = v;
+    int64_t o = i;
+    if (e.out_pitch != 0) {   // rows of the output (outer index) are out_pitch elements apart
+      const uint32_t inner = e.to_crsk ? R * S * K : R * S * C, outer = e.to_crsk ? c : k;
+      o = (int64_t)outer * e.out_pitch + (i - outer * inner);
+    }
+    if (e.dtype == IIT_BF16) static_cast<__nv_bfloat16*>(e.out)[o] = __float2bfloat16_rn(v);
+    else static_cast<float*>(e.out)[o] = v;
   }
 }
 

@@ -122,6 +122,101 @@ class HookedTransformerLL(HookedRootModule):
                 sd[k] = own[k]
         return super().load_state_dict(sd, strict=strict, assign=assign)
 
+    # --- bf16 GEMM operands of every linear map, refreshed by ONE kernel launch ----------------------------------
+    # Each GEMM reads a bf16 [out][in] copy of its weight in the forward and a [in][out] copy in dgrad. Making them per
+    # GEMM and pass costs ~200 re-layout launches per train step (11 % of it); here they live in persistent buffers
+    # described by a device-resident iit_relayout_t table that one iit_filter_relayout_batched launch rewrites after
+    # every optimizer update (FlatAdam.post_step, also inside captured graphs) -- the ResNet's scheme. The fused QKV
+    # matrix is assembled by six entries straight from the per-head parameters; the unembedding keeps its zero padding
+    # to a multiple of 64 columns because the entries never write it.
+    def _linear_sites(self):
+        c = self.cfg
+        D, H, dh, F_, V = c.d_model, c.n_heads, c.d_head, c.d_mlp, c.d_vocab_out
+        sites = []
+        for i, blk in enumerate(self.blocks):
+            a, m = blk.attn, blk.mlp
+            hd = H * dh
+            # QKV: W_p[h, d, e] -> oi[(p*hd + h*dh + e)][d] (KRSC with K=H, R=dh, C=D) and io[d][p*hd + h*dh + e] (CRSK
+            # with C=D, R=H, S=dh, K=1, rows 3*hd apart)
+            ent = []
+            for j, w in enumerate((a.W_Q, a.W_K, a.W_V)):
+                ent.append((w, (H, D, dh, 1), (D * dh, dh, 1, 0), 0, j * hd * D, 0))
+                ent.append((w, (1, D, H, dh), (0, dh, D * dh, 1), 1, j * hd, 3 * hd))
+            specs = tuple(((H, D, dh), (dh * D, 1, D), j * hd * D) for j in range(3))
+            sites.append(dict(key=("qkv", i), n_in=D, n_out=3 * hd, n_out_pad=3 * hd, params=(a.W_Q, a.W_K, a.W_V), entries=ent,
+                              specs=specs))
+            # [in][out] row-major matrices: filter view [K=out, C=in] with strides (1, out)
+            for key, w, n_in, n_out, size, stride in (
+                    (("o", i), a.W_O, hd, D, (H, dh, D), (dh, 1, hd)),
+                    (("in", i), m.W_in, D, F_, (D, F_), (1, D)),
+                    (("out", i), m.W_out, F_, D, (F_, D), (1, F_))):
+                ent = [(w, (n_out, n_in, 1, 1), (1, n_out, 0, 0), 0, 0, 0), (w, (n_out, n_in, 1, 1), (1, n_out, 0, 0), 1, 0, 0)]
+                sites.append(dict(key=key, n_in=n_in, n_out=n_out, n_out_pad=n_out, params=(w,), entries=ent,
+                                  specs=((size, stride, 0),)))
+        Vp = V + (-V) % 64
+        w = self.unembed.W_U
+        ent = [(w, (V, D, 1, 1), (1, V, 0, 0), 0, 0, 0), (w, (V, D, 1, 1), (1, V, 0, 0), 1, 0, Vp)]
+        sites.append(dict(key=("unembed",), n_in=D, n_out=V, n_out_pad=Vp, params=(w,), entries=ent, specs=(((D, V), (1, D), 0),)))
+        return sites
+
+    def _shadow_usable(self):
+        c = self.cfg
+        return (self.act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES and c.d_model % 64 == 0 and c.d_mlp % 64 == 0
+                and (c.n_heads * c.d_head) % 64 == 0 and self.unembed.W_U.is_cuda)
+
+    def _build_filter_shadow(self):
+        from .._lib import IIT_BF16, Relayout
+        sites = self._linear_sites()
+        dev = self.unembed.W_U.device
+        n_ent = sum(len(st["entries"]) for st in sites)
+        table = (Relayout * n_ent)()
+        bufs, k, biggest = {}, 0, 1
+        for st in sites:
+            oi = torch.zeros(st["n_out_pad"] * st["n_in"], dtype=torch.bfloat16, device=dev)
+            io = torch.zeros(st["n_in"] * st["n_out_pad"], dtype=torch.bfloat16, device=dev)
+            bufs[st["key"]] = (oi, io, st)
+            for w, dims, strides, to_crsk, off, pitch in st["entries"]:
+                e = table[k]; k += 1
+                e.w, e.out = w.data_ptr(), (io if to_crsk else oi).data_ptr() + 2 * off
+                for d in range(4):
+                    e.stride[d] = strides[d]
+                e.k, e.c, e.r, e.s = dims
+                e.to_crsk, e.dtype, e.out_pitch = to_crsk, IIT_BF16, pitch
+                biggest = max(biggest, dims[0] * dims[1] * dims[2] * dims[3])
+        raw = torch.frombuffer(bytearray(bytes(table)), dtype=torch.uint8).clone()
+        params = [p for st in sites for p in st["params"]]
+        self._shadow = {"bufs": bufs, "table": raw.to(dev), "entries": n_ent, "max": biggest, "params": params,
+                        "ptrs": [p.data_ptr() for p in params], "versions": None}
+        b_U = self.unembed.b_U
+        self._shadow["b_U_pad"] = (-self.cfg.d_vocab_out) % 64
+
+    def refresh_filter_shadow(self):
+        if not self._shadow_usable():
+            return
+        sh = getattr(self, "_shadow", None)
+        if sh is None or sh["ptrs"] != [p.data_ptr() for p in sh["params"]]:
+            if ops.capturing():
+                return                       # never (re)allocate inside a capture: forward falls back to per-GEMM copies
+            self._build_filter_shadow()
+            sh = self._shadow
+        ops.filter_relayout_batched(sh["table"], sh["entries"], sh["max"])
+        sh["versions"] = [p._version for p in sh["params"]]
+
+    def _filter_shadow_stale(self):
+        if not self._shadow_usable():
+            return False
+        sh = getattr(self, "_shadow", None)
+        return (sh is None or sh["versions"] != [p._version for p in sh["params"]]
+                or sh["ptrs"] != [p.data_ptr() for p in sh["params"]])
+
+    def _linear(self, key, x):
+        """x @ W of site `key` from the prepared operands, or None when they are not in use."""
+        sh = getattr(self, "_shadow", None)
+        if sh is None or sh["versions"] is None:
+            return None
+        oi, io, st = sh["bufs"][key]
+        return ops.linear_prepared(x, oi, io, st["n_in"], st["n_out_pad"], st["specs"], st["params"])
+
     # ------------------------------------------------------------------------------------------
     def _check_hooks(self):
         for n in self._unsupported:
@@ -131,21 +226,34 @@ class HookedTransformerLL(HookedRootModule):
 
     def forward(self, tokens, last_pos_only=False, return_type="logits"):
         self._check_hooks()
+        if self._shadow_usable():
+            if self._filter_shadow_stale() and not ops.capturing():
+                self.refresh_filter_shadow()
+            use_shadow = not self._filter_shadow_stale()
+        else:
+            use_shadow = False
         c = self.cfg
         B, S = tokens.shape
         D, H, dh = c.d_model, c.n_heads, c.d_head
         T = B * S
         resid = ops.embed(tokens, self.embed.W_E, self.pos_embed.W_pos, self.act_dtype).view(T, D)
+        blocks_seen = []
         for blk in self.blocks:
             a, m = blk.attn, blk.mlp
             resid = blk.hook_resid_pre(resid.view(B, S, D)).reshape(T, D)
             x = ops.lnpre(resid, c.eps)
             # fused QKV projection: [D, (3,H,dh)] assembled from the per-head parameters (tiny; autograd routes grads)
-            w_qkv = torch.cat([w.permute(1, 0, 2).reshape(D, H * dh) for w in (a.W_Q, a.W_K, a.W_V)], dim=1)
             b_qkv = torch.cat([b.reshape(-1) for b in (a.b_Q, a.b_K, a.b_V)])
-            qkv = ops.bias_add(ops.linear_tokens(x, w_qkv), b_qkv).view(B, S, 3, H, dh)
+            if use_shadow:
+                li = len(blocks_seen); blocks_seen.append(blk)
+                qkv_lin = self._linear(("qkv", li), x)
+            else:
+                w_qkv = torch.cat([w.permute(1, 0, 2).reshape(D, H * dh) for w in (a.W_Q, a.W_K, a.W_V)], dim=1)
+                qkv_lin = ops.linear_tokens(x, w_qkv)
+            qkv = ops.bias_add(qkv_lin, b_qkv).view(B, S, 3, H, dh)
             z = a.hook_z(ops.attention(qkv))
-            proj = ops.linear_tokens(z.reshape(T, H * dh), a.W_O.reshape(H * dh, D))
+            zr = z.reshape(T, H * dh)
+            proj = self._linear(("o", li), zr) if use_shadow else ops.linear_tokens(zr, a.W_O.reshape(H * dh, D))
             if blk.hook_attn_out.has_hooks():
                 attn_out = blk.hook_attn_out(ops.bias_add(proj, a.b_O).view(B, S, D)).reshape(T, D)
                 resid = ops.bias_add(attn_out, None, resid)
@@ -153,13 +261,13 @@ class HookedTransformerLL(HookedRootModule):
                 resid = ops.bias_add(proj, a.b_O, resid)
             resid = blk.hook_resid_mid(resid.view(B, S, D)).reshape(T, D)
             x = ops.lnpre(resid, c.eps)
-            h = ops.linear_tokens(x, m.W_in)
+            h = self._linear(("in", li), x) if use_shadow else ops.linear_tokens(x, m.W_in)
             if m.hook_pre.has_hooks():  # observers only: the activation below is computed from the unhooked value
                 pre = ops.bias_add(h, m.b_in).view(B, S, -1)
                 if m.hook_pre(pre) is not pre:
                     raise NotImplementedError("mlp.hook_pre is read-only here; hook mlp.hook_post to intervene")
             post = m.hook_post(ops.bias_gelu(h, m.b_in, (B, S, c.d_mlp))).reshape(T, -1)
-            out = ops.linear_tokens(post, m.W_out)
+            out = self._linear(("out", li), post) if use_shadow else ops.linear_tokens(post, m.W_out)
             if blk.hook_mlp_out.has_hooks():
                 mlp_out = blk.hook_mlp_out(ops.bias_add(out, m.b_out).view(B, S, D)).reshape(T, D)
                 resid = ops.bias_add(mlp_out, None, resid)
@@ -168,6 +276,11 @@ class HookedTransformerLL(HookedRootModule):
             resid = blk.hook_resid_post(resid.view(B, S, D)).reshape(T, D)
         W_U, b_U, V = self.unembed.W_U, self.unembed.b_U, c.d_vocab_out
         pad = (-V) % 64
+        if use_shadow:
+            b_U = torch.nn.functional.pad(b_U, (0, pad)) if pad else b_U
+            xin = resid.view(B, S, D)[:, -1, :].contiguous() if last_pos_only else resid
+            logits = ops.bias_add(self._linear(("unembed",), ops.lnpre(xin, c.eps)), b_U)[:, :V]
+            return logits if last_pos_only else logits.reshape(B, S, -1)
         if pad and self.act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES:
             # the tensor-core GEMMs want widths that are multiples of 64: unembed into V + pad columns (zero weights and
             # bias) and slice them off again; autograd routes the gradient (50257 -> 50304 for GPT-2's vocabulary)

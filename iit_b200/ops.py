@@ -879,6 +879,51 @@ def linear_tokens(x2d: torch.Tensor, W_in_out: torch.Tensor) -> torch.Tensor:
     return _LinearTokensFn.apply(x2d, W_in_out)
 
 
+class _LinearPreparedFn(torch.autograd.Function):
+    """y[T, out_pad] = x[T, in] @ W on the tensor-core GEMMs from PREPARED bf16 operands: `w_oi` [out_pad][in] for the
+    forward, `w_io` [in][out_pad] for dgrad -- persistent copies the model refreshes in one launch after every weight
+    update (HookedTransformerLL.refresh_filter_shadow), instead of one re-layout launch per GEMM and pass. The weight
+    gradient [out_pad][in] is handed to each of `params` as the strided view its `spec` (size, stride, offset) names, so
+    fused / padded matrices (QKV from three per-head parameters, the padded unembedding) need no cat / pad in the graph."""
+
+    @staticmethod
+    def forward(ctx, x, w_oi, w_io, n_in, n_out_pad, specs, *params):
+        _require_cuda(x, w_oi, w_io)
+        x = x.contiguous()
+        T = x.shape[0]
+        d = Conv()
+        d.n, d.h, d.w, d.c, d.k, d.r, d.s, d.stride, d.pad, d.p, d.q = T, 1, 1, n_in, n_out_pad, 1, 1, 1, 0, 1, 1
+        if not (x.dtype == torch.bfloat16 and _lib.lib.iit_conv2d_tc_supported(C.byref(d), _dt(x))):
+            raise RuntimeError("linear_prepared: bf16 activations and widths that are multiples of 64 only")
+        y = torch.empty((T, n_out_pad), dtype=x.dtype, device=x.device)
+        call("iit_conv2d_fprop_tc", _p(x), _p(w_oi), _p(y), C.byref(d), None, None, _stream())
+        ctx.save_for_backward(x, w_io)
+        ctx.d, ctx.specs = d, specs
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w_io = ctx.saved_tensors
+        d = ctx.d
+        dy = dy.contiguous()
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            call("iit_conv2d_dgrad_tc", _p(dy), _p(w_io), _p(dx), C.byref(d), _stream())
+        grads = [None] * len(ctx.specs)
+        if any(ctx.needs_input_grad[6:]):
+            dwb = torch.empty(d.k * d.c, dtype=torch.float32, device=x.device)   # [out_pad][in]
+            need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
+            scratch = torch.empty(need, dtype=torch.uint8, device=x.device)
+            call("iit_conv2d_wgrad_tc", _p(dy), _p(x), _p(dwb), C.byref(d), _p(scratch), need, _stream())
+            grads = [torch.as_strided(dwb, size, stride, offset) for size, stride, offset in ctx.specs]
+        return (dx, None, None, None, None, None, *grads)
+
+
+def linear_prepared(x2d, w_oi, w_io, n_in, n_out_pad, specs, params):
+    return _LinearPreparedFn.apply(x2d, w_oi, w_io, n_in, n_out_pad, specs, *params)
+
+
 def colsum(x2d: torch.Tensor) -> torch.Tensor:
     out = torch.zeros(x2d.shape[1], dtype=torch.float32, device=x2d.device)
     call("iit_colsum", _p(x2d), _dt(x2d), _p(out), x2d.shape[0], x2d.shape[1], _stream())

@@ -223,6 +223,8 @@ typedef struct {
   int64_t stride[4];
   int32_t k, c, r, s;
   int32_t to_crsk, dtype;
+  int64_t out_pitch;   /* elements between consecutive OUTER indices of the output (k for KRSC, c for CRSK); 0 = dense.
+                          Lets several entries fill column blocks of one wider matrix, or leave zero padding per row. */
 } iit_relayout_t;
 int iit_filter_relayout_batched(const iit_relayout_t* table_dev, int entries, int64_t max_elements, void* stream);
 

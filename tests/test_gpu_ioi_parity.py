@@ -288,3 +288,34 @@ def test_ioi_cuda_graph_step_equals_eager_step():
     for e, g in zip(res["eager"], res["graphs"]):
         for k in e:
             assert rel(g[k], e[k]) < 1e-4, (k, e, g)
+
+
+def test_prepared_gemm_operands_equal_per_gemm_copies_and_follow_weight_edits():
+    """bf16 path: the persistent [out][in] / [in][out] copies of every linear map (one batched re-layout launch; fused QKV
+    assembled from the per-head parameters, unembedding padded to 64 columns) give the same logits and parameter gradients,
+    bit for bit, as the per-GEMM copies, and are rebuilt when a weight changes outside the optimizer."""
+    from iit_b200 import ops
+    from iit_b200.tasks.ioi import make_ll_model
+    x = batch(7)[0].to(DEV)
+
+    def run(use_shadow, scale=None):
+        ll = make_ll_model(device=DEV, d_mlp=DM, d_vocab=V, n_ctx=32, dtype=torch.bfloat16)
+        ll.load_state_dict(small_sd())
+        if not use_shadow:
+            ll._shadow_usable = lambda: False
+        if scale is not None:
+            ll(x)                                   # copies made from the original weights ...
+            with torch.no_grad():                   # ... then a weight edited in place
+                ll.blocks[2].mlp.W_in.mul_(scale)
+                ll.blocks[0].attn.W_K.mul_(scale)
+        out = ll(x)
+        out.float().square().mean().backward()
+        return out.detach(), {n: p.grad.clone() for n, p in ll.named_parameters() if p.grad is not None}
+
+    for scale in (None, 1.5):
+        (a, ga), (b, gb) = run(True, scale), run(False, scale)
+        assert torch.equal(a, b)
+        assert ga.keys() == gb.keys()
+        for n in ga:
+            assert torch.equal(ga[n], gb[n]), n
+    assert not torch.equal(run(True, 1.5)[0], run(True)[0])
