@@ -130,6 +130,78 @@ __global__ void __launch_bounds__(256) bias_act_kernel(const T* __restrict__ x, 
     Vec4<T>::store(out + e, v);
   }
 }
+// bf16 fast path: 16 bytes per thread and access, 32-bit index arithmetic (the 64-bit `e % N` of the kernel above costs
+// more than the rest of the loop), tanh.approx (2^-11 relative, below bf16's 2^-9 rounding)
+__device__ __forceinline__ float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ void unpack_bf16x8(const uint4& t, float (&v)[8]) {
+  const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { v[2 * i] = __uint_as_float(w[i] << 16); v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u); }
+}
+__device__ __forceinline__ uint4 pack_bf16x8(const float (&v)[8]) {
+  uint32_t w[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    w[i] = *reinterpret_cast<uint32_t*>(&h);
+  }
+  return make_uint4(w[0], w[1], w[2], w[3]);
+}
+__global__ void __launch_bounds__(256) bias_act_bf16x8_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ bias,
+                                                              const __nv_bfloat16* __restrict__ resid,
+                                                              __nv_bfloat16* __restrict__ pre_out, __nv_bfloat16* __restrict__ out,
+                                                              uint32_t n8, uint32_t N, int act) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += gridDim.x * blockDim.x) {
+    const int64_t e = (int64_t)i * 8;
+    float v[8];
+    unpack_bf16x8(*reinterpret_cast<const uint4*>(x + e), v);
+    if (bias) {
+      const uint32_t c = (i * 8u) % N;        // n8 * 8 < 2^32 (host-checked)
+      const float4 b0 = *reinterpret_cast<const float4*>(bias + c), b1 = *reinterpret_cast<const float4*>(bias + c + 4);
+      v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w; v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+    }
+    if (resid) {
+      float r[8];
+      unpack_bf16x8(*reinterpret_cast<const uint4*>(resid + e), r);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] += r[j];
+    }
+    if (pre_out) *reinterpret_cast<uint4*>(pre_out + e) = pack_bf16x8(v);
+    if (act == 1) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float u = 0.7978845608028654f * (v[j] + 0.044715f * v[j] * v[j] * v[j]);
+        v[j] = 0.5f * v[j] * (1.f + tanh_fast(u));
+      }
+    }
+    *reinterpret_cast<uint4*>(out + e) = pack_bf16x8(v);
+  }
+}
+__global__ void __launch_bounds__(256) gelu_bwd_bf16x8_kernel(const __nv_bfloat16* __restrict__ dpost,
+                                                              const __nv_bfloat16* __restrict__ pre, __nv_bfloat16* __restrict__ dpre,
+                                                              uint32_t n8) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += gridDim.x * blockDim.x) {
+    const int64_t e = (int64_t)i * 8;
+    float g[8], p[8];
+    unpack_bf16x8(*reinterpret_cast<const uint4*>(dpost + e), g);
+    unpack_bf16x8(*reinterpret_cast<const uint4*>(pre + e), p);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float k = 0.7978845608028654f, x = p[j];
+      const float th = tanh_fast(k * (x + 0.044715f * x * x * x));
+      g[j] *= 0.5f * (1.f + th) + 0.5f * x * (1.f - th * th) * k * (1.f + 3.f * 0.044715f * x * x);
+    }
+    *reinterpret_cast<uint4*>(dpre + e) = pack_bf16x8(g);
+  }
+}
+static bool aligned16(const void* a, const void* b = nullptr, const void* c = nullptr, const void* d = nullptr) {
+  return ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(c) |
+           reinterpret_cast<uintptr_t>(d)) & 15) == 0;
+}
 // same, element by element, for widths that are not a multiple of 4 (the 50257-wide unembed bias)
 template <typename T>
 __global__ void __launch_bounds__(256) bias_act_scalar_kernel(const T* __restrict__ x, const float* __restrict__ bias,
@@ -359,6 +431,14 @@ extern "C" int iit_bias_act_fwd(const void* x, const float* bias, const void* re
     IIT_LAUNCH_CHECK("iit_bias_act_fwd");
     return 0;
   }
+  if (dtype == IIT_BF16 && n % 8 == 0 && rows * n < (1ll << 32) && aligned16(x, resid, pre_out, out) && aligned16(bias)) {
+    const int64_t n8 = rows * n / 8;
+    bias_act_bf16x8_kernel<<<grid_for(n8, 512), 256, 0, as_stream(stream)>>>(
+        (const __nv_bfloat16*)x, bias, (const __nv_bfloat16*)resid, (__nv_bfloat16*)pre_out, (__nv_bfloat16*)out, (uint32_t)n8,
+        (uint32_t)n, act);
+    IIT_LAUNCH_CHECK("iit_bias_act_fwd");
+    return 0;
+  }
   int64_t n4 = rows * n / 4;
   IIT_DISPATCH_DTYPE(dtype, T, {
     bias_act_kernel<T><<<grid_for(n4, 512), 256, 0, as_stream(stream)>>>((const T*)x, bias, (const T*)resid, (T*)pre_out, (T*)out,
@@ -369,6 +449,12 @@ extern "C" int iit_bias_act_fwd(const void* x, const float* bias, const void* re
 }
 extern "C" int iit_gelu_bwd(const void* dpost, const void* pre, void* dpre, int dtype, int64_t n, void* stream) {
   IIT_REQUIRE(dpost && pre && dpre && n % 4 == 0, "iit_gelu_bwd: bad arguments");
+  if (dtype == IIT_BF16 && n % 8 == 0 && n < (1ll << 32) && aligned16(dpost, pre, dpre)) {
+    gelu_bwd_bf16x8_kernel<<<grid_for(n / 8, 512), 256, 0, as_stream(stream)>>>((const __nv_bfloat16*)dpost, (const __nv_bfloat16*)pre,
+                                                                              (__nv_bfloat16*)dpre, (uint32_t)(n / 8));
+    IIT_LAUNCH_CHECK("iit_gelu_bwd");
+    return 0;
+  }
   IIT_DISPATCH_DTYPE(dtype, T, {
     gelu_bwd_kernel<T><<<grid_for(n / 4, 512), 256, 0, as_stream(stream)>>>((const T*)dpost, (const T*)pre, (T*)dpre, n / 4);
   })
