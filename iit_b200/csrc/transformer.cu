@@ -4,6 +4,8 @@
 // bias (+GELU) (+residual) epilogues, column sums for bias gradients and the causal attention core.
 // With d_model = 64 every one of these is HBM/latency bound: rows are short, so one warp owns one row
 // (coalesced 256-byte row accesses), and attention keeps a whole (sequence, head) in shared memory.
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace iit {
@@ -248,6 +250,52 @@ __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x, fl
   }
 }
 
+// bf16, N % 8 == 0: a thread owns 8 consecutive columns (16-byte loads, four rows in flight); block = 16 column packs x 16 row
+// lanes, shared-memory reduction over the row lanes, one atomic per column and block
+__global__ void __launch_bounds__(256) colsum_bf16x8_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out,
+                                                            int64_t rows, int N) {
+  __shared__ float s[16][16 * 8 + 1];
+  const int cp = threadIdx.x & 15, ry = threadIdx.x >> 4;
+  const int c = (blockIdx.x * 16 + cp) * 8;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (c < N) {
+    const int64_t step = (int64_t)gridDim.y * 16;
+    int64_t r = (int64_t)blockIdx.y * 16 + ry;
+    for (; r + 3 * step < rows; r += 4 * step) {
+      uint4 t[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) t[u] = *reinterpret_cast<const uint4*>(x + (r + u * step) * N + c);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float v[8];
+        unpack_bf16x8(t[u], v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += v[j];
+      }
+    }
+    for (; r < rows; r += step) {
+      float v[8];
+      unpack_bf16x8(*reinterpret_cast<const uint4*>(x + r * N + c), v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += v[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[ry][cp * 8 + j] = acc[j];
+  __syncthreads();
+  if (threadIdx.x < 128) {
+    const int col = blockIdx.x * 128 + threadIdx.x;
+    if (col < N) {
+      float t = 0.f;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) t += s[j][threadIdx.x];
+      atomicAdd(out + col, t);
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------- attention core
 // qkv: [B, S, 3, H, DH] (one fused projection), z: [B, S, H, DH]. Causal, scores / sqrt(DH).
 // One warp per (batch, head); lane i < S owns query row i. S <= 32, DH <= 32.
@@ -463,6 +511,15 @@ extern "C" int iit_gelu_bwd(const void* dpost, const void* pre, void* dpre, int 
 }
 extern "C" int iit_colsum(const void* x, int dtype, float* out, int64_t rows, int64_t n, void* stream) {
   IIT_REQUIRE(x && out, "iit_colsum: null pointer");
+  if (dtype == IIT_BF16 && n % 8 == 0 && n < (1ll << 31) && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+    int64_t gy = (rows + 16 * 8 - 1) / (16 * 8);          // >= 8 rows per thread
+    const int64_t gx = (n + 127) / 128, cap = std::max<int64_t>(1, (int64_t)kNumSMs * 8 / gx);
+    if (gy > cap) gy = cap;
+    if (gy < 1) gy = 1;
+    colsum_bf16x8_kernel<<<dim3((unsigned)gx, (unsigned)gy), 256, 0, as_stream(stream)>>>((const __nv_bfloat16*)x, out, rows, (int)n);
+    IIT_LAUNCH_CHECK("iit_colsum");
+    return 0;
+  }
   int64_t by = (rows + 255) / 256;
   if (by > 64) by = 64;
   if (by < 1) by = 1;
