@@ -302,30 +302,33 @@ __global__ void __launch_bounds__(256) colsum_bf16x8_kernel(const __nv_bfloat16*
 template <typename T, int S_MAX, int DH_MAX>
 __global__ void __launch_bounds__(128) attn_fwd_kernel(const T* __restrict__ qkv, T* __restrict__ z, int64_t BH, int S, int H,
                                                        int DH, float scale) {
-  __shared__ float sk[4][S_MAX][DH_MAX + 1], sv[4][S_MAX][DH_MAX + 1];
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int64_t bh0 = (int64_t)blockIdx.x * 4; bh0 < BH; bh0 += (int64_t)gridDim.x * 4) {
+  // a (batch, head) unit needs S lanes: with S_MAX = 16 a warp serves two units (lanes 0-15 and 16-31)
+  constexpr int UPW = 32 / S_MAX, UPB = 4 * UPW;
+  __shared__ float sk[UPB][S_MAX][DH_MAX + 1], sv[UPB][S_MAX][DH_MAX + 1];
+  const int lane = threadIdx.x & 31, row = lane % S_MAX;
+  const int w = (threadIdx.x >> 5) * UPW + lane / S_MAX;       // unit slot within the block
+  for (int64_t bh0 = (int64_t)blockIdx.x * UPB; bh0 < BH; bh0 += (int64_t)gridDim.x * UPB) {
     const int64_t bh = bh0 + w;
     const bool live = bh < BH;
     const int64_t b = live ? bh / H : 0;
     const int h = live ? (int)(bh - b * H) : 0;
     const T* base = qkv + b * (int64_t)S * 3 * H * DH;
     if (live)
-      for (int i = lane; i < S * DH; i += 32) {
+      for (int i = row; i < S * DH; i += S_MAX) {
         const int s = i / DH, d = i - s * DH;
         sk[w][s][d] = to_f<T>(base[((int64_t)s * 3 + 1) * H * DH + h * DH + d]);
         sv[w][s][d] = to_f<T>(base[((int64_t)s * 3 + 2) * H * DH + h * DH + d]);
       }
     __syncwarp();
-    if (live && lane < S) {
+    if (live && row < S) {
       float q[DH_MAX], o[DH_MAX];
 #pragma unroll
       for (int d = 0; d < DH_MAX; ++d) {
-        q[d] = d < DH ? to_f<T>(base[((int64_t)lane * 3) * H * DH + h * DH + d]) : 0.f;
+        q[d] = d < DH ? to_f<T>(base[((int64_t)row * 3) * H * DH + h * DH + d]) : 0.f;
         o[d] = 0.f;
       }
       float m = -INFINITY, l = 0.f;
-      for (int j = 0; j <= lane; ++j) {
+      for (int j = 0; j <= row; ++j) {
         float sc = 0.f;
 #pragma unroll
         for (int d = 0; d < DH_MAX; ++d) if (d < DH) sc = fmaf(q[d], sk[w][j][d], sc);
@@ -337,7 +340,7 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const T* __restrict__ qkv
         for (int d = 0; d < DH_MAX; ++d) if (d < DH) o[d] = o[d] * corr + p * sv[w][j][d];
         m = mn;
       }
-      T* zo = z + ((b * S + lane) * H + h) * DH;
+      T* zo = z + ((b * S + row) * H + h) * DH;
 #pragma unroll
       for (int d = 0; d < DH_MAX; ++d) if (d < DH) zo[d] = from_f<T>(o[d] / l);
     }
@@ -347,12 +350,14 @@ __global__ void __launch_bounds__(128) attn_fwd_kernel(const T* __restrict__ qkv
 
 // dqkv [B,S,3,H,DH] from dz, recomputing the pattern.
 template <typename T, int S_MAX, int DH_MAX>
-__global__ void __launch_bounds__(128) attn_bwd_kernel(const T* __restrict__ qkv, const T* __restrict__ dz, T* __restrict__ dqkv,
+__global__ void __launch_bounds__(64) attn_bwd_kernel(const T* __restrict__ qkv, const T* __restrict__ dz, T* __restrict__ dqkv,
                                                        int64_t BH, int S, int H, int DH, float scale) {
-  __shared__ float sq[4][S_MAX][DH_MAX + 1], sk[4][S_MAX][DH_MAX + 1], sv[4][S_MAX][DH_MAX + 1], sdz[4][S_MAX][DH_MAX + 1];
-  __shared__ float sp[4][S_MAX][S_MAX + 1], sds[4][S_MAX][S_MAX + 1];
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int64_t bh0 = (int64_t)blockIdx.x * 4; bh0 < BH; bh0 += (int64_t)gridDim.x * 4) {
+  constexpr int UPW = 32 / S_MAX, UPB = 2 * UPW;     // units per warp as in the forward; two warps per block (shared memory)
+  __shared__ float sq[UPB][S_MAX][DH_MAX + 1], sk[UPB][S_MAX][DH_MAX + 1], sv[UPB][S_MAX][DH_MAX + 1], sdz[UPB][S_MAX][DH_MAX + 1];
+  __shared__ float sp[UPB][S_MAX][S_MAX + 1], sds[UPB][S_MAX][S_MAX + 1];
+  const int lane = threadIdx.x & 31, row = lane % S_MAX;
+  const int w = (threadIdx.x >> 5) * UPW + lane / S_MAX;
+  for (int64_t bh0 = (int64_t)blockIdx.x * UPB; bh0 < BH; bh0 += (int64_t)gridDim.x * UPB) {
     const int64_t bh = bh0 + w;
     const bool live = bh < BH;
     const int64_t b = live ? bh / H : 0;
@@ -360,7 +365,7 @@ __global__ void __launch_bounds__(128) attn_bwd_kernel(const T* __restrict__ qkv
     const T* base = qkv + b * (int64_t)S * 3 * H * DH;
     T* dbase = dqkv + b * (int64_t)S * 3 * H * DH;
     if (live)
-      for (int i = lane; i < S * DH; i += 32) {
+      for (int i = row; i < S * DH; i += S_MAX) {
         const int s = i / DH, d = i - s * DH;
         sq[w][s][d] = to_f<T>(base[((int64_t)s * 3 + 0) * H * DH + h * DH + d]);
         sk[w][s][d] = to_f<T>(base[((int64_t)s * 3 + 1) * H * DH + h * DH + d]);
@@ -368,8 +373,8 @@ __global__ void __launch_bounds__(128) attn_bwd_kernel(const T* __restrict__ qkv
         sdz[w][s][d] = to_f<T>(dz[((b * S + s) * H + h) * DH + d]);
       }
     __syncwarp();
-    if (live && lane < S) {  // phase 1: row i of the pattern P and of dS
-      const int i = lane;
+    if (live && row < S) {  // phase 1: row i of the pattern P and of dS
+      const int i = row;
       // scores -> pattern row (kept in shared memory: sp), dP row (kept in sds until rescaled)
       float m = -INFINITY;
       for (int j = 0; j <= i; ++j) {
@@ -402,8 +407,8 @@ __global__ void __launch_bounds__(128) attn_bwd_kernel(const T* __restrict__ qkv
       }
     }
     __syncwarp();
-    if (live && lane < S) {  // phase 2: column j: dk_j = sum_i dS_ij q_i, dv_j = sum_i P_ij dz_i
-      const int j = lane;
+    if (live && row < S) {  // phase 2: column j: dk_j = sum_i dS_ij q_i, dv_j = sum_i P_ij dz_i
+      const int j = row;
       for (int d = 0; d < DH; ++d) {
         float a = 0.f, c = 0.f;
         for (int i = j; i < S; ++i) { a = fmaf(sds[w][i][j], sq[w][i][d], a); c = fmaf(sp[w][i][j], sdz[w][i][d], c); }
@@ -534,7 +539,10 @@ extern "C" int iit_attn_fwd(const void* qkv, void* z, int dtype, int64_t batch, 
   const float scale = 1.0f / sqrtf((float)d_head);
   int64_t BH = batch * heads;
   IIT_DISPATCH_DTYPE(dtype, T, {
-    attn_fwd_kernel<T, 32, 32><<<grid_for(BH, 4), 128, 0, as_stream(stream)>>>((const T*)qkv, (T*)z, BH, seq, heads, d_head, scale);
+    if (seq <= 16 && d_head <= 16)   // the IOI model: half the unrolled work, registers and shared memory of the general instance
+      attn_fwd_kernel<T, 16, 16><<<grid_for(BH, 8, 16), 128, 0, as_stream(stream)>>>((const T*)qkv, (T*)z, BH, seq, heads, d_head, scale);
+    else
+      attn_fwd_kernel<T, 32, 32><<<grid_for(BH, 4), 128, 0, as_stream(stream)>>>((const T*)qkv, (T*)z, BH, seq, heads, d_head, scale);
   })
   IIT_LAUNCH_CHECK("iit_attn_fwd");
   return 0;
@@ -546,7 +554,7 @@ extern "C" int iit_attn_bwd(const void* qkv, const void* dz, void* dqkv, int dty
   const float scale = 1.0f / sqrtf((float)d_head);
   int64_t BH = batch * heads;
   IIT_DISPATCH_DTYPE(dtype, T, {
-    attn_bwd_kernel<T, 16, 16><<<grid_for(BH, 4), 128, 0, as_stream(stream)>>>((const T*)qkv, (const T*)dz, (T*)dqkv, BH, seq, heads,
+    attn_bwd_kernel<T, 16, 16><<<grid_for(BH, 4, 32), 64, 0, as_stream(stream)>>>((const T*)qkv, (const T*)dz, (T*)dqkv, BH, seq, heads,
                                                                                d_head, scale);
   })
   IIT_LAUNCH_CHECK("iit_attn_bwd");
