@@ -543,11 +543,20 @@ static int launch_tc2(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat1
   return 0;
 }
 
+// Pixel box of a tile: BW x BH x BNI = `pixels` rows (powers of two; TMA enumerates w fastest, then h, then the image).
+// The box that wastes the fewest rows on positions outside the P x Q grid wins; among equals the one with the largest
+// spatial extent (longer contiguous runs). A 7 x 7 or 11 x 11 grid is covered exactly by 1 x 1 x 128 (the same pixel of
+// 128 images) where 8 x 8 x 2 / 16 x 8 x 1 used 77 % / 47 % of the rows.
 static void plan_box(int P, int Q, int pixels, int* BW, int* BH, int* BNI) {
-  *BW = pow2_ge(Q) < 16 ? pow2_ge(Q) : 16;
-  int rem = pixels / *BW;
-  *BH = pow2_ge(P) < rem ? pow2_ge(P) : rem;
-  *BNI = rem / *BH;
+  double best = -1.0;
+  for (int bw = 1; bw <= pixels && bw <= 256; bw <<= 1)
+    for (int bh = 1; bw * bh <= pixels && bh <= 256; bh <<= 1) {
+      const int bn = pixels / (bw * bh);
+      if (bn > 256) continue;
+      const double covered = (double)(((Q + bw - 1) / bw) * bw) * (((P + bh - 1) / bh) * bh);
+      const double score = (double)P * Q / covered + 1e-6 * (bw * bh) + 1e-9 * bw;
+      if (score > best) { best = score; *BW = bw; *BH = bh; *BNI = bn; }
+    }
 }
 
 static int encode_nhwc_strided(CUtensorMap* m, const void* ptr, int C, int W, int H, int N, int bw, int bh, int bn, int es_hw,
@@ -898,6 +907,33 @@ __global__ void __launch_bounds__(256) tc_splitk_reduce_kernel(const float* __re
   }
 }
 
+// few splits, many weights (layers 3-4): one thread per float4 column, four partials in flight
+__global__ void __launch_bounds__(256) tc_splitk_reduce_flat_kernel(const float* __restrict__ part, float* __restrict__ out,
+                                                                    int64_t n, int splits, int accumulate) {
+  const int64_t n4 = n >> 2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 s = accumulate ? reinterpret_cast<const float4*>(out)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    int z = 0;
+    for (; z + 4 <= splits; z += 4) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = reinterpret_cast<const float4*>(part + (int64_t)(z + u) * n)[i];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+    }
+    for (; z < splits; ++z) {
+      float4 v = reinterpret_cast<const float4*>(part + (int64_t)z * n)[i];
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    reinterpret_cast<float4*>(out)[i] = s;
+  }
+}
+
+static void launch_splitk_reduce(const float* part, float* out, int64_t n, int splits, int accumulate, cudaStream_t st) {
+  if (splits >= 16) tc_splitk_reduce_kernel<<<grid_for(n / 4, 64), 256, 0, st>>>(part, out, n, splits, accumulate);
+  else tc_splitk_reduce_flat_kernel<<<grid_for(n / 4, 256), 256, 0, st>>>(part, out, n, splits, accumulate);
+}
+
 static void wgrad_tc_plan(const iit_conv_t* d, TcWgradParams* p, int* splits, int* CB) {
   p->N = d->n; p->P = d->p; p->Q = d->q; p->Cin = d->c; p->Cout = d->k; p->pad = d->pad;
   p->stride = d->stride; p->R = d->r; p->S = d->s;
@@ -1016,7 +1052,7 @@ static int wgrad_tc_impl(const void* dy, const void* x, float* dw, const iit_con
     int rc = wgrad_win(dy, x, (float*)scratch, d, &nsplit, as_stream(stream), "iit_conv2d_wgrad_tc");
     if (rc) return rc;
     const int64_t n = (int64_t)d->k * d->r * d->s * d->c;
-    tc_splitk_reduce_kernel<<<grid_for(n / 4, 64), 256, 0, as_stream(stream)>>>((const float*)scratch, dw, n, nsplit, accumulate);
+    launch_splitk_reduce((const float*)scratch, dw, n, nsplit, accumulate, as_stream(stream));
     IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc(reduce)");
     return 0;
   }
@@ -1038,7 +1074,7 @@ static int wgrad_tc_impl(const void* dy, const void* x, float* dw, const iit_con
   if (rc) return rc;
   IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc");
   int64_t n = (int64_t)d->k * d->r * d->s * d->c;
-  tc_splitk_reduce_kernel<<<grid_for(n / 4, 64), 256, 0, st>>>((const float*)scratch, dw, n, splits, accumulate);
+  launch_splitk_reduce((const float*)scratch, dw, n, splits, accumulate, st);
   IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc(reduce)");
   return 0;
 }
