@@ -362,6 +362,18 @@ __global__ void __launch_bounds__(256) filter_relayout_batched_kernel(const iit_
   const uint32_t n = (uint32_t)e.k * e.c * e.r * e.s;            // 32-bit index arithmetic (host checks n < 2^31)
   const float* __restrict__ w = static_cast<const float*>(e.w);
   const uint32_t C = e.c, K = e.k, R = e.r, S = e.s;
+  if (!e.to_crsk && e.dtype == IIT_BF16 && e.out_pitch == 0 && e.stride[1] == 1 && e.stride[3] == (int64_t)C &&
+      e.stride[2] == (int64_t)S * C && e.stride[0] == (int64_t)R * S * C && (n & 3) == 0 &&
+      ((reinterpret_cast<uintptr_t>(e.w) | reinterpret_cast<uintptr_t>(e.out)) & 15) == 0) {
+    // channels-last master filter -> KRSC: the same order, a pure fp32 -> bf16 conversion (no index arithmetic)
+    uint2* __restrict__ out = static_cast<uint2*>(e.out);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n / 4; i += gridDim.x * blockDim.x) {
+      const float4 v = reinterpret_cast<const float4*>(w)[i];
+      __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+      out[i] = make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
+    }
+    return;
+  }
   if (e.to_crsk && e.stride[1] == 1 && e.dtype == IIT_BF16 && e.out_pitch == 0) {
     // channels-last master filter -> CRSK: a [k][c] -> [c][k] transposition per tap. Through a 32 x 33 shared tile both the
     // fp32 reads (32 consecutive c) and the bf16 writes (32 consecutive k) are contiguous; element by element the reads were
@@ -526,7 +538,7 @@ extern "C" int iit_filter_relayout(const float* w, const int64_t* strides_kcrs, 
 extern "C" int iit_filter_relayout_batched(const iit_relayout_t* table_dev, int entries, int64_t max_elements, void* stream) {
   IIT_REQUIRE(table_dev && entries >= 1 && max_elements >= 1 && max_elements < (1ll << 31), "iit_filter_relayout_batched: bad arguments");
   int bx = (int)((max_elements + 256 * 8 - 1) / (256 * 8));
-  if (bx > 64) bx = 64;
+  if (bx > 256) bx = 256;
   if (bx < 1) bx = 1;
   filter_relayout_batched_kernel<<<dim3((unsigned)bx, (unsigned)entries), 256, 0, as_stream(stream)>>>(table_dev);
   IIT_LAUNCH_CHECK("iit_filter_relayout_batched");
