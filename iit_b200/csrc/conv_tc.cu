@@ -602,7 +602,10 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
   CUtensorMap ma, mb;
   if (encode_nhwc_strided(&ma, gathered, gC, gW, gH, tp.N, tp.BW, tp.BH, tp.BNI, tp.in_mul, name)) return 1;
   const int64_t mtiles = (int64_t)tp.tiles_w * tp.tiles_h * tp.tiles_n;
-  if (g_pair_mode && tp.Cout % 256 == 0 && tp.ntaps > 0 && mtiles >= kNumSMs) {
+  // CTA pairs: whenever every SM gets a tile; with fewer boxes (layer4 at batch 4096: 128) only for long reductions, where
+  // the halved filter traffic outweighs the pair's start-up (measured: +3 % on 4608-deep, -8 % on 256-deep reductions)
+  if (g_pair_mode && tp.Cout % 256 == 0 && tp.ntaps > 0 &&
+      (mtiles >= kNumSMs || (mtiles >= kNumSMs / 2 && tp.ntaps * tp.Cin >= 2304))) {
     // 256-filter tiles unless mode 3 asks for 128 (measured: half-width tiles fill the last wave better, 7 waves of 74
     // clusters instead of 4 on layer3, but pay the pixel box twice and end up slower: 76.6 vs 70.5 us)
     const int64_t pairs = (mtiles + 1) / 2;
