@@ -187,8 +187,6 @@ class HookedTransformerLL(HookedRootModule):
         params = [p for st in sites for p in st["params"]]
         self._shadow = {"bufs": bufs, "table": raw.to(dev), "entries": n_ent, "max": biggest, "params": params,
                         "ptrs": [p.data_ptr() for p in params], "versions": None}
-        b_U = self.unembed.b_U
-        self._shadow["b_U_pad"] = (-self.cfg.d_vocab_out) % 64
 
     def refresh_filter_shadow(self):
         if not self._shadow_usable():
