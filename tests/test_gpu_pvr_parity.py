@@ -304,3 +304,38 @@ def test_cuda_graph_step_equals_eager_step():
         for k in e:  # bf16 free-running trajectories with atomically ordered BN sums (see the chaos note above)
             assert rel(g[k], e[k]) < (5e-2 if i == 0 else 2e-1), (i, k, e, g)
     assert rel(res["graphs"][0]["train/iit_loss"], res["eager"][0]["train/iit_loss"]) < 1e-3
+
+
+@pytest.mark.parametrize("dtype,bar", [(torch.float32, 1e-3), (torch.bfloat16, 5e-2)])
+def test_84px_default_image_size_matches_oracle(dtype, bar):
+    """The reference's DEFAULT image size (pad 7: 84x84, task_loader.py:10,43; the contract size is 56): odd spatial sizes
+    21 / 11 / 6 / 3 downstream, the hooked layer is [B,256,6,6] with 3x3 quadrant boxes. IIT and behaviour terms from
+    synchronised weights against the oracle: losses within the bar (1e-3 fp32, 5e-2 bf16), fp32 gradients within 1e-2 in
+    relative L2 over all parameters."""
+    from iit_b200.model_pairs import IITBehaviorModelPair
+    from iit_b200.tasks.mnist_pvr.get_alignment import get_alignment
+    ll, hl, corr = get_alignment("mnist_pvr", {"mode": "q", "hook_point": HOOK, "input_shape": (1, 3, 84, 84)}, dtype=dtype)
+    ll.load_state_dict(R.resnet18_state_dict(0))
+    pair = IITBehaviorModelPair(hl, ll, corr, training_args={"lr": 1e-3})
+    oll = R.ResNet18Oracle(R.resnet18_state_dict(0))
+    opair = R.OraclePair(oll, "pvr", R.pvr_corr("q", HOOK, 256, 6), lr=1e-3)
+    opt = pair.make_optimizer()
+    ll.train()
+    b, s = R.synthetic_pvr(B, 100, size=84), R.synthetic_pvr(B, 200, size=84)
+    bd, sd_ = dev(b), dev(s)
+    hl_node = pair.sample_hl_name()
+    assert str(hl_node) == opair.sample_hl_name()
+    for name, mine_fn, oracle_fn in [
+            ("iit", lambda: pair.get_IIT_loss_over_batch(bd, sd_, hl_node, pair.loss_fn), lambda: opair.iit_loss(b, s, str(hl_node))),
+            ("behaviour", lambda: pair.get_behaviour_loss_over_batch(bd, pair.loss_fn), lambda: opair.loss_fn(oll(b[0]), b[1]))]:
+        ll.load_state_dict(oll.state_dict())
+        opt.zero_grad()
+        lm = mine_fn()
+        lm.backward()
+        opair.opt.zero_grad()
+        lo = oracle_fn()
+        lo.backward()
+        assert rel(lm.item(), lo.item()) < bar, (name, lm.item(), lo.item())
+        if dtype == torch.float32:
+            e = _grad_rel_l2(ll, oll)
+            assert e < 1e-2, (name, e)
