@@ -621,7 +621,8 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
   }
   if (encode_filter(&mb, wmat, Kg, tp.Cout, BN, name)) return 1;
   // two pixel boxes per filter block whenever that still leaves a tile for every SM
-  const int MT = (BN == 128 && g_tile_pairs && ((mtiles + 1) / 2) * (tp.Cout / BN) >= kNumSMs) ? 2 : 1;
+  // ... and the reduction is long enough to pay for the doubled epilogue per tile (measured: 1152-deep gains, 576-deep loses)
+  const int MT = (BN == 128 && g_tile_pairs && ((mtiles + 1) / 2) * (tp.Cout / BN) >= kNumSMs && tp.ntaps * tp.Cin >= 1024) ? 2 : 1;
   const int64_t total = ((mtiles + MT - 1) / MT) * (tp.Cout / BN);
   IIT_REQUIRE(total < (1ll << 31), "%s: too many tiles", name);
   int rc = BN == 256 ? launch_tc<256, 1>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq)
