@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libiit_b200.so")
+# IIT_B200_LIB: another build of the same library (e.g. a kernel variant for a same-machine A/B measurement)
+LIB_PATH = os.environ.get("IIT_B200_LIB") or os.path.join(_HERE, "libiit_b200.so")
 
 IIT_MAX_RANK = 6
 IIT_F32, IIT_BF16 = 0, 1
