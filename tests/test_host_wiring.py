@@ -207,3 +207,42 @@ def test_data_parallel_plumbing_world2_gloo():
         assert all(g == [1.5] * len(g) for g in grads)          # mean of 1 and 2 on both ranks
         assert counts == [3, 20]
         assert shard == [list(range(rank * 5, rank * 5 + 5)), [2 * i for i in range(rank * 5, rank * 5 + 5)]]
+
+
+def test_ctypes_structs_match_the_header(tmp_path):
+    """The ctypes mirrors of the POD descriptors (iit_box_t, iit_conv_t, iit_relayout_t) have the size and field offsets the
+    C compiler gives the structs of include/iit_b200.h: a field added on one side only would shift every later argument."""
+    import ctypes as C
+    import shutil
+    import subprocess
+    from iit_b200 import _lib
+    if shutil.which("gcc") is None:
+        pytest.skip("no C compiler")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "iit_b200.h"\nint main(void) {\n'
+                   '  printf("%zu %zu %zu\\n", sizeof(iit_box_t), sizeof(iit_conv_t), sizeof(iit_relayout_t));\n'
+                   '  printf("%zu %zu %zu %zu\\n", offsetof(iit_relayout_t, stride), offsetof(iit_relayout_t, k),\n'
+                   '         offsetof(iit_relayout_t, dtype), offsetof(iit_relayout_t, out_pitch));\n  return 0;\n}\n')
+    exe = tmp_path / "sizes"
+    subprocess.check_call(["gcc", "-I", os.path.join(root, "include"), str(src), "-o", str(exe)])
+    out = subprocess.check_output([str(exe)], text=True).split()
+    sizes, offs = [int(v) for v in out[:3]], [int(v) for v in out[3:]]
+    assert sizes == [C.sizeof(_lib.Box), C.sizeof(_lib.Conv), C.sizeof(_lib.Relayout)]
+    assert offs == [_lib.Relayout.stride.offset, _lib.Relayout.k.offset, _lib.Relayout.dtype.offset, _lib.Relayout.out_pitch.offset]
+
+
+def test_direct_grad_only_for_the_marked_flat_view():
+    """ops.direct_grad: backward kernels may add into p.grad only while it is the very tensor the flat optimizer installed
+    and marked; any other gradient tensor (or none) takes the ordinary autograd path."""
+    from iit_b200 import ops
+    p = torch.nn.Parameter(torch.zeros(8, 4))
+    assert ops.direct_grad(p) is None
+    p.grad = torch.zeros(8, 4)
+    assert ops.direct_grad(p) is None                      # not marked
+    p._iit_direct_grad = p.grad
+    assert ops.direct_grad(p) is p.grad
+    p.grad = torch.zeros(8, 4)                             # replaced (e.g. by another optimizer): mark is stale
+    assert ops.direct_grad(p) is None
+    p.grad = None
+    assert ops.direct_grad(p) is None
