@@ -47,7 +47,7 @@ SIGNATURES = {
     "iit_patch_fwd": [_vp, _vp, _BoxP, _vp],
     "iit_patch_bwd": [_vp, _BoxP, _vp],
     "iit_capture_box": [_vp, _vp, _BoxP, _vp],
-    "iit_hl_pvr": [_vp, _vp, _i, _i64, _vp, _vp],
+    "iit_hl_pvr": [_vp, _vp, _i, _i64, _vp, _vp, _vp],
     "iit_hl_ioi_last_argmax": [_vp, _vp, _i, _vp, _i, _i64, _i, _i64, _vp, _vp],
     "iit_hl_ioi_dense": [_vp, _vp, _i, _vp, _i, _i64, _i, _i64, _vp, _vp],
     "iit_ce_index_fwd": [_vp, _i, _i64, _i64, _i64, _vp, _vp, _vp, _vp],
@@ -113,11 +113,15 @@ SIGNATURES = {
     "iit_last_error": [],
     "iit_version": [],
     "iit_launch_count": [],
+    "iit_kernel_variant_slots": [],
+    "iit_kernel_variant_name": [_i],
+    "iit_kernel_variant_count": [_i],
 }
 _RESTYPES = {"iit_last_error": C.c_char_p, "iit_launch_count": C.c_ulonglong,
+             "iit_kernel_variant_name": C.c_char_p, "iit_kernel_variant_count": C.c_ulonglong,
              "iit_conv2d_wgrad_scratch_bytes": C.c_size_t, "iit_conv2d_wgrad_tc_scratch_bytes": C.c_size_t,
              "iit_stem_wgrad_s2d_scratch_bytes": C.c_size_t}
-_NO_STATUS = set(_RESTYPES) | {"iit_version", "iit_conv2d_tc_supported", "iit_conv_win_enable", "iit_conv_pair_enable"}
+_NO_STATUS = set(_RESTYPES) | {"iit_version", "iit_kernel_variant_slots", "iit_conv2d_tc_supported", "iit_conv_win_enable", "iit_conv_pair_enable"}
 
 
 def _load():
@@ -149,3 +153,9 @@ def call(name: str, *args):
 
 def launch_count() -> int:
     return int(lib.iit_launch_count())
+
+
+def kernel_variant_counts() -> dict:
+    """{kernel instantiation name: launches since load} for the tensor-core convolution dispatchers."""
+    return {lib.iit_kernel_variant_name(i).decode(): int(lib.iit_kernel_variant_count(i))
+            for i in range(int(lib.iit_kernel_variant_slots()))}

@@ -13,6 +13,12 @@ constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs; grids are sized in multi
 
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
+// which tensor-core kernel instantiation a dispatcher picked (diagnostic counters behind iit_kernel_variant_count)
+enum KernelVariant {
+  KV_TC_64 = 0, KV_TC_128, KV_TC_128_MT2, KV_TC_256, KV_TC2_256, KV_TC2_128, KV_WIN_3X3, KV_WIN_STEM, KV_WGRAD_TC,
+  KV_WGRAD_WIN, KV_WGRAD_WIN_STEM, KV_COUNT
+};
+void count_variant(int id);
 
 #define IIT_REQUIRE(cond, ...)            \
   do {                                    \
@@ -43,6 +49,15 @@ void count_launch(int n = 1);
   } while (0)
 
 inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// Function attributes (opt-in dynamic shared memory) and occupancy answers are per DEVICE: one-time set-up is keyed
+// by the current device ordinal, so a process that drives several GPUs sets every one of them up.
+constexpr int kMaxDevices = 64;
+inline int current_device_slot() {
+  int d = 0;
+  if (cudaGetDevice(&d) != cudaSuccess || d < 0) d = 0;
+  return d % kMaxDevices;
+}
 
 inline int grid_for(int64_t work_items, int per_block, int max_waves = 8) {
   int64_t b = (work_items + per_block - 1) / per_block;

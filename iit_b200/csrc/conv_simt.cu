@@ -559,7 +559,6 @@ extern "C" int iit_filter_relayout_batched(const iit_relayout_t* table_dev, int 
 namespace iit {
 constexpr size_t kStaticScratchBytes = 8u << 20;  // 8 MiB
 static __device__ __align__(256) unsigned char g_wgrad_static_scratch[kStaticScratchBytes];
-constexpr int kMaxDevices = 64;
 static void* g_static_scratch_addr[kMaxDevices] = {nullptr};  // device address of the array, per device
 }  // namespace iit
 

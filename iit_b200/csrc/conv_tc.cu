@@ -498,7 +498,8 @@ static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16
   constexpr int STAGES = 4;
   constexpr size_t smem = STAGES * (MT * TC_BM * TC_BK * 2 + BN * TC_BK * 2) + (2 * STAGES + 4) * 8 + 16 + 2 * BN * 4 +
                           16 + 8 * 32 * TC_STAGE_PITCH + 1024;
-  static int ctas_per_sm = 0;
+  static int ctas_per_sm_dev[kMaxDevices] = {};
+  int& ctas_per_sm = ctas_per_sm_dev[current_device_slot()];
   if (!ctas_per_sm) {
     IIT_CUDA(cudaFuncSetAttribute(conv3x3_tc_kernel<BN, STAGES, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int occ = 0;
@@ -509,6 +510,7 @@ static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16
   int grid = kNumSMs * ctas_per_sm;
   if (grid > total_tiles) grid = total_tiles;
   conv3x3_tc_kernel<BN, STAGES, MT><<<grid, TC_CONV_THREADS, smem, st>>>(ma, mb, out, p, bn_sum, bn_sq);
+  count_variant(BN == 64 ? KV_TC_64 : BN == 256 ? KV_TC_256 : MT == 2 ? KV_TC_128_MT2 : KV_TC_128);
   return 0;
 }
 
@@ -520,7 +522,8 @@ static int launch_tc2(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat1
   constexpr int STAGES = BN == 256 ? 6 : 8;
   constexpr size_t smem = STAGES * (TC_BM * TC_BK * 2 + (BN / 2) * TC_BK * 2) + (2 * STAGES + 4) * 8 + 16 + 2 * BN * 4 + 16 +
                           8 * 32 * TC_STAGE_PITCH + 1024;
-  static int max_clusters = 0;
+  static int max_clusters_dev[kMaxDevices] = {};
+  int& max_clusters = max_clusters_dev[current_device_slot()];
   cudaLaunchConfig_t cfg = {};
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -540,6 +543,7 @@ static int launch_tc2(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat1
   const int clusters = total_tiles < max_clusters ? total_tiles : max_clusters;
   cfg.gridDim = dim3(2 * clusters);
   IIT_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_tc2_kernel<BN, STAGES>, ma, mb, out, p, bn_sum, bn_sq));
+  count_variant(BN == 256 ? KV_TC2_256 : KV_TC2_128);
   return 0;
 }
 
@@ -964,12 +968,14 @@ static int launch_wgrad_tc(const CUtensorMap& mdy, const CUtensorMap& mx, float*
                            cudaStream_t st) {
   constexpr int STAGES = (S == 3 && CB == 128) ? 3 : 4;
   constexpr size_t smem = STAGES * (2 + S * (CB / 64)) * 8192 + (2 * STAGES + 1) * 8 + 16 + 1024;
-  static bool attr_set = false;
+  static bool attr_set_dev[kMaxDevices] = {};
+  bool& attr_set = attr_set_dev[current_device_slot()];
   if (!attr_set) {
     IIT_CUDA(cudaFuncSetAttribute(wgrad3x3_tc_kernel<CB, S, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
   wgrad3x3_tc_kernel<CB, S, STAGES><<<grid, TC_THREADS, smem, st>>>(mdy, mx, part, p);
+  count_variant(KV_WGRAD_TC);
   return 0;
 }
 

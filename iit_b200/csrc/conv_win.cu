@@ -313,14 +313,16 @@ static int win_launch(const CUtensorMap& ma, const CUtensorMap& mb, void* out, c
   IIT_REQUIRE(smem <= WIN_SMEM_MAX, "%s: tile does not fit shared memory", name);
   int grid = kNumSMs;
   if (grid > p.N * p.bands) grid = p.N * p.bands;
-  static bool attr_set[5] = {false, false, false, false, false};
+  static bool attr_set[kMaxDevices][5] = {};
+  const int dev = current_device_slot();
 #define IIT_WIN_LAUNCH(S)                                                                                              \
   case S:                                                                                                              \
-    if (!attr_set[S]) {                                                                                                \
+    if (!attr_set[dev][S]) {                                                                                           \
       IIT_CUDA(cudaFuncSetAttribute(conv_win_kernel<RB, NTAPS, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WIN_SMEM_MAX)); \
-      attr_set[S] = true;                                                                                              \
+      attr_set[dev][S] = true;                                                                                         \
     }                                                                                                                  \
     conv_win_kernel<RB, NTAPS, S><<<grid, WIN_THREADS, smem, st>>>(ma, mb, (__nv_bfloat16*)out, p, bn_sum, bn_sq);            \
+    count_variant(RB == 128 ? KV_WIN_3X3 : KV_WIN_STEM);                                                               \
     break;
   switch (stages) {
     IIT_WIN_LAUNCH(2)
@@ -555,12 +557,14 @@ int wgrad_win(const void* dy, const void* x, float* part, const iit_conv_t* d, i
   CUtensorMap mdy, mx;
   if (win_encode_a(&mdy, dy, 64, d->q, d->p, d->n, p.PW, p.box_h, 128, name)) return 1;
   if (win_encode_a(&mx, x, 64, d->w, d->h, d->n, p.PW, p.box_h, 128, name)) return 1;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static bool attr_set[kMaxDevices] = {};
+  const int dev = current_device_slot();
+  if (!attr_set[dev]) {
     IIT_CUDA(cudaFuncSetAttribute(wgrad_win_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WIN_SMEM_MAX));
-    attr_set = true;
+    attr_set[dev] = true;
   }
   wgrad_win_kernel<STAGES><<<grid, WIN_THREADS, smem, st>>>(mdy, mx, part, p);
+  count_variant(KV_WGRAD_WIN);
   IIT_LAUNCH_CHECK(name);
   *splits = grid;
   return 0;
@@ -778,13 +782,15 @@ extern "C" int iit_stem_wgrad_s2d(const void* dy, const void* s2d, float* dw, co
   // dy [n, OH, OW, 64] read on the PW-wide raster: the box is wider than the tensor, the excess columns are zero-filled
   if (win_encode_a(&mdy, dy, 64, p.OW, p.OH, n, p.PW, p.BH, 128, name)) return 1;
   if (win_encode_a(&mx, s2d, 16, sw, sh, n, p.PW, p.BH + 3, 32, name)) return 1;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static bool attr_set[kMaxDevices] = {};
+  const int dev = current_device_slot();
+  if (!attr_set[dev]) {
     IIT_CUDA(cudaFuncSetAttribute(stem_wgrad_win_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WIN_SMEM_MAX));
-    attr_set = true;
+    attr_set[dev] = true;
   }
   cudaStream_t st = as_stream(stream);
   stem_wgrad_win_kernel<STAGES><<<grid, WIN_THREADS, smem, st>>>(mdy, mx, (float*)scratch, p);
+  count_variant(KV_WGRAD_WIN_STEM);
   IIT_LAUNCH_CHECK(name);
   stem_wgrad_finish_kernel<<<64, 256, 0, st>>>((const float*)scratch, grid, dw, dw_strides_kcrs[0], dw_strides_kcrs[1],
                                                dw_strides_kcrs[2], dw_strides_kcrs[3]);

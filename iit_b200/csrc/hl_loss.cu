@@ -10,17 +10,26 @@ namespace iit {
 __constant__ int c_class_map[10] = {1, 1, 1, 1, 2, 2, 2, 3, 3, 3};  // iit/tasks/mnist_pvr/utils.py:10
 
 // ---------------------------------------------------------------- PVR HL
+// (tr, bl, br)[class_map[tl] - 1] for one pair's variables; tl outside [-10, 9] (what torch's indexing accepts) returns
+// false and leaves *out = -1 -- the reference would raise IndexError there (pvr_hl.py:50-53)
+__device__ __forceinline__ bool pvr_hl_eval(const int64_t (&v)[4], int64_t* out) {
+  int64_t tl = v[0];
+  tl = tl < 0 ? tl + 10 : tl;  // python-style negative index
+  if (tl < 0 || tl > 9) { *out = -1; return false; }
+  *out = v[c_class_map[(int)tl]];  // 1..3 -> tr, bl, br
+  return true;
+}
+
 __global__ void hl_pvr_kernel(const int64_t* __restrict__ bv, const int64_t* __restrict__ sv, int var,
-                              int64_t batch, int64_t* __restrict__ out) {
+                              int64_t batch, int64_t* __restrict__ out, int* __restrict__ err_flag) {
   int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= batch) return;
   int64_t v[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) v[i] = (i == var && sv != nullptr) ? sv[b * 4 + i] : bv[b * 4 + i];
-  int64_t tl = v[0];
-  tl = tl < 0 ? tl + 10 : tl;  // python-style negative index; caller guarantees 0..9
-  int ptr = c_class_map[(int)tl];  // 1..3 -> tr, bl, br
-  out[b] = v[ptr];
+  int64_t o;
+  if (!pvr_hl_eval(v, &o) && err_flag != nullptr) *err_flag = 1;
+  out[b] = o;
 }
 
 // ---------------------------------------------------------------- IOI HL (sparse, last position)
@@ -353,11 +362,12 @@ __global__ void __launch_bounds__(256) ce_prob_bwd_kernel(const T* __restrict__ 
 using namespace iit;
 
 extern "C" int iit_hl_pvr(const int64_t* base_vars, const int64_t* src_vars, int var, int64_t batch, int64_t* hl_out,
-                          void* stream) {
+                          int32_t* err_flag, void* stream) {
   IIT_REQUIRE(base_vars && hl_out && batch >= 0, "iit_hl_pvr: bad arguments");
   IIT_REQUIRE(var < 4, "iit_hl_pvr: var must be < 4 (got %d)", var);
   if (batch == 0) return 0;
-  hl_pvr_kernel<<<(unsigned)((batch + 255) / 256), 256, 0, as_stream(stream)>>>(base_vars, src_vars, var, batch, hl_out);
+  hl_pvr_kernel<<<(unsigned)((batch + 255) / 256), 256, 0, as_stream(stream)>>>(base_vars, src_vars, var, batch, hl_out,
+                                                                                  err_flag);
   IIT_LAUNCH_CHECK("iit_hl_pvr");
   return 0;
 }

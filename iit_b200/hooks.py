@@ -19,8 +19,13 @@ NamesFilter = Optional[Union[Callable[[str], bool], Sequence[str], str]]
 
 
 class HookPoint(nn.Module):
-    def __init__(self):
+    def __init__(self, inplace_ok: bool = False):
+        """`inplace_ok`: the model promises that no operator saved the tensor passing through here for its backward, so
+        a patch hook may overwrite it in place. False (the default) makes the patch clone first, as the reference always
+        does (iit/model_pairs/base_model_pair.py:157): e.g. a ReLU output is kept by its producer for the backward, and
+        overwriting it would trip autograd's version check."""
         super().__init__()
+        self.inplace_ok = bool(inplace_ok)
         self.name: Optional[str] = None
         self._fwd: list = []   # (fn, is_permanent, level)
         self._bwd: list = []
@@ -158,12 +163,16 @@ class HookedRootModule(nn.Module):
             if names_filter is None or callable(names_filter):
                 raise ValueError("stop_when_cached needs an explicit list of hook-point names")
             wanted = {names_filter} if isinstance(names_filter, str) else set(names_filter)
+            # A hook point that fires several times per forward (a BasicBlock's shared ReLU) ends up cached at its LAST
+            # firing, in transformer_lens and here; stopping at the first would keep the wrong activation. The model
+            # lists such hook points in `multi_fire_hook_points`: wanting one of them means running the whole forward.
+            if not wanted & set(getattr(self, "multi_fire_hook_points", ())):
 
-            def stop_hook(tensor, hook):
-                if wanted.issubset(cache.keys()):
-                    raise _StopForward()
+                def stop_hook(tensor, hook):
+                    if wanted.issubset(cache.keys()):
+                        raise _StopForward()
 
-            fwd = fwd + [(n, stop_hook) for n in wanted]
+                fwd = fwd + [(n, stop_hook) for n in wanted]
         with self.hooks(fwd_hooks=fwd, bwd_hooks=bwd, reset_hooks_end=reset_hooks_end, clear_contexts=clear_contexts):
             try:
                 out = self(*model_args, **model_kwargs)

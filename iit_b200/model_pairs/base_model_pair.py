@@ -25,6 +25,52 @@ from iit_b200.utils.index import Ix
 from iit_b200.utils.metric import MetricStoreCollection, MetricType
 
 
+class _LazyCache(dict):
+    """A cache dict filled by `fill()` the first time anything is read from it."""
+
+    def __init__(self, fill):
+        super().__init__()
+        self._fill = fill
+
+    def _load(self):
+        if self._fill is not None:
+            fill, self._fill = self._fill, None
+            with t.no_grad():
+                self.update(fill())
+
+    def __getitem__(self, k):
+        self._load()
+        return super().__getitem__(k)
+
+    def __contains__(self, k):
+        self._load()
+        return super().__contains__(k)
+
+    def __iter__(self):
+        self._load()
+        return super().__iter__()
+
+    def __len__(self):
+        self._load()
+        return super().__len__()
+
+    def keys(self):
+        self._load()
+        return super().keys()
+
+    def items(self):
+        self._load()
+        return super().items()
+
+    def values(self):
+        self._load()
+        return super().values()
+
+    def get(self, k, default=None):
+        self._load()
+        return super().get(k, default)
+
+
 class BaseModelPair(ABC):
     hl_model: Any
     ll_model: Any
@@ -100,6 +146,9 @@ class BaseModelPair(ABC):
     def hl_intervention(self, base_input, ablation_input, hl_node: HLNode) -> Tensor:
         """HL source run + HL base run with the node's value swapped (reference :80,89-91)."""
         if hasattr(self.hl_model, "interchange"):
+            # the kernel needs no HL cache; callers that read `pair.hl_cache` after an intervention (reference :80) get
+            # the source run's cache on first access
+            self.hl_cache = _LazyCache(lambda: self.hl_model.run_with_cache(ablation_input)[1])
             return self.hl_model.interchange(base_input, ablation_input, hl_node)
         _, self.hl_cache = self.hl_model.run_with_cache(ablation_input)
         return self.hl_model.run_with_hooks(
@@ -128,11 +177,7 @@ class BaseModelPair(ABC):
             cached = self.hl_cache[hook.name]
             if not isinstance(hook_point_out, Tensor):
                 return cached
-            if hook_point_out.is_cuda and hook_point_out.shape == cached.shape:
-                return ops.patch(hook_point_out, cached, hl_node.index, inplace=False)
-            out = hook_point_out.clone()
-            out[hl_node.index.as_index] = cached[hl_node.index.as_index]
-            return out
+            return ops.patch(hook_point_out, cached, hl_node.index, inplace=False)   # CUDA tensors only, like every operator
 
         return hl_ablation_hook
 
@@ -142,7 +187,10 @@ class BaseModelPair(ABC):
 
         def ll_ablation_hook(hook_point_out: Tensor, hook) -> Tensor:
             index = ll_node.index if ll_node.index is not None else Ix[[None]]
-            return ops.patch(hook_point_out, self.ll_cache[hook.name], index, inplace=True)
+            # in place only where the model vouches for it (HookPoint.inplace_ok: nothing saved this tensor for its
+            # backward) or no backward will follow; everywhere else clone first, like the reference (:157-161)
+            inplace = bool(getattr(hook, "inplace_ok", False)) or not (t.is_grad_enabled() and hook_point_out.requires_grad)
+            return ops.patch(hook_point_out, self.ll_cache[hook.name], index, inplace=inplace)
 
         return ll_ablation_hook
 

@@ -30,6 +30,7 @@ class IITBehaviorModelPair(IITModelPair):
         except AttributeError:
             print("WARNING: using default categorical loss function.")
             categorical = True
+        # regression HL models: torch's MSELoss on CUDA tensors (no reference task here has one; not a kernel of this library)
         return ops.cross_entropy if categorical else t.nn.MSELoss()
 
     @staticmethod

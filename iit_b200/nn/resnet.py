@@ -167,7 +167,10 @@ class Wrapped(nn.Module):
     def __init__(self, mod):
         super().__init__()
         self.mod = mod
-        self.hook_point = HookPoint()
+        # a convolution's output is saved by nobody (the conv keeps its INPUT, BatchNorm keeps whatever tensor it is
+        # handed after the hook), so patch hooks may overwrite it in place; BN / ReLU / pool / block outputs are kept by
+        # their producers for the backward and must be cloned first
+        self.hook_point = HookPoint(inplace_ok=isinstance(mod, Conv2d))
 
 
 class _Seq(nn.Module):
@@ -236,6 +239,9 @@ class ResNet18LL(HookedRootModule):
         self.mod = _Body(num_classes)
         self.act_dtype = dtype
         self.setup()
+        # each BasicBlock applies its one ReLU module twice (after bn1 and after the residual add), as torchvision does:
+        # its hook point fires twice per forward and a cache keeps the second value (hooks.run_with_cache)
+        self.multi_fire_hook_points = frozenset(n for n in self.hook_dict if ".mod.relu.hook_point" in n and "layer" in n)
 
     # --- forward ----------------------------------------------------------------------------
     def _block(self, wb: Wrapped, x):

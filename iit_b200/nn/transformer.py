@@ -59,7 +59,10 @@ class _Holder(nn.Module):
 
 
 def _hp():
-    return HookPoint()
+    # every hook point this model lets a hook modify (hook_z, mlp.hook_post, the residual-stream points, hook_attn_out /
+    # hook_mlp_out) carries a tensor whose producer kept its INPUTS for the backward (attention keeps qkv, bias+GELU keeps
+    # the pre-activation, bias+residual keeps nothing), so a patch may overwrite it in place
+    return HookPoint(inplace_ok=True)
 
 
 class HookedTransformerLL(HookedRootModule):
@@ -109,9 +112,13 @@ class HookedTransformerLL(HookedRootModule):
                 if "W_" in name:
                     nn.init.normal_(p, std=c.initializer_range)
         self.setup()
+        # attn.hook_result is not in this list: with use_attn_result=False (the only configuration this model accepts)
+        # transformer_lens never calls that hook point, so a hook attached there is legal and never fires -- which is
+        # what the reference's `check_causal_effect(node_type="a")` relies on (iit/utils/node_picker.py:11-14 default
+        # suffix); the same holds here.
         self._unsupported = [n for n in self.hook_dict if n.split(".")[-1] in (
             "hook_embed", "hook_pos_embed", "hook_scale", "hook_normalized", "hook_k", "hook_q", "hook_v",
-            "hook_attn_scores", "hook_pattern", "hook_result", "hook_attn_in", "hook_q_input", "hook_k_input",
+            "hook_attn_scores", "hook_pattern", "hook_attn_in", "hook_q_input", "hook_k_input",
             "hook_v_input", "hook_mlp_in")]
 
     def load_state_dict(self, state_dict, strict=True, assign=False):

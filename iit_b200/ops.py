@@ -166,7 +166,9 @@ def hl_pvr(base_vars: torch.Tensor, src_vars: Optional[torch.Tensor], var: int) 
     if bv.dtype != torch.int64 or bv.dim() != 2 or bv.shape[1] != 4:
         raise ValueError("hl_pvr: intermediate vars must be int64 [B,4]")
     out = torch.empty(bv.shape[0], dtype=torch.int64, device=bv.device)
-    call("iit_hl_pvr", _p(bv), _p(sv), int(var), bv.shape[0], _p(out), _stream())
+    # a top-left variable outside [-10, 9] (bad data, a user hook on hook_tl) sets the device error flag and yields -1;
+    # raise_on_index_error() turns it into the IndexError the reference's indexing raises
+    call("iit_hl_pvr", _p(bv), _p(sv), int(var), bv.shape[0], _p(out), _p(_err_flag(bv.device)), _stream())
     return out
 
 

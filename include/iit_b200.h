@@ -32,6 +32,12 @@ const char* iit_last_error(void);
 int iit_version(void);
 /* number of kernels this library has enqueued since load (bench.py's gpu_launches) */
 unsigned long long iit_launch_count(void);
+/* Which tensor-core kernel instantiation the convolution dispatchers picked, counted per launch since load: slot ids
+ * 0 .. iit_kernel_variant_slots()-1, each with the kernel's name. Diagnostics for tests and profiles (they assert that a
+ * configuration really ran on, e.g., the CTA-pair kernel); no reference counterpart. */
+int iit_kernel_variant_slots(void);
+const char* iit_kernel_variant_name(int slot);
+unsigned long long iit_kernel_variant_count(int slot);
 
 /* ------------------------------------------------------------------------------------------ */
 /* (a) patch: TorchIndex box gather/scatter                                                     */
@@ -67,9 +73,11 @@ int iit_capture_box(void* dst_compact, const void* src, const iit_box_t* box, vo
 /* MNIST-PVR HL with one variable interchanged: v = base_vars; v[:, var] = src_vars[:, var]
  * (var < 0: no interchange); hl_out[b] = (tr,bl,br)[class_map[tl]-1].
  * Replaces MNIST_PVR_HL.forward + hl_ablation_hook (iit/tasks/mnist_pvr/pvr_hl.py:44-56,
- * base_model_pair.py:80,89-91,120-142) and the leaky variant (pvr_check_leaky_hl.py:45-66). */
+ * base_model_pair.py:80,89-91,120-142) and the leaky variant (pvr_check_leaky_hl.py:45-66).
+ * A top-left variable outside [-10, 9] (where the reference's indexing raises IndexError) gives hl_out[b] = -1 and
+ * sets *err_flag (device int32, may be NULL) to 1. */
 int iit_hl_pvr(const int64_t* base_vars, const int64_t* src_vars, int var, int64_t batch,
-               int64_t* hl_out, void* stream);
+               int64_t* hl_out, int32_t* err_flag, void* stream);
 
 enum { IIT_IOI_NONE = 0, IIT_IOI_ALL_NODES = 1, IIT_IOI_DUPLICATE = 2, IIT_IOI_S_INHIBITION = 3,
        IIT_IOI_NAME_MOVER = 4 };

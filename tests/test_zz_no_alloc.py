@@ -33,26 +33,31 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("cfg", [(64, 64, 7, 3, 1, 1, 64), (64, 128, 14, 3, 2, 1, 33)])
-def test_noalloc_wgrad_matches_scratch_entry_point_twice(cfg):
+def test_noalloc_wgrad_matches_scratch_entry_point_twice(cfg, dtype):
+    """Both input types the entry point takes (fp32 and bf16 activations / output gradients; the weight gradient and the
+    partial sums are fp32 either way)."""
     from iit_b200 import _lib
     c, k, hw, ks, stride, pad, n = cfg
     d = _desc(n, c, hw, k, ks, stride, pad)
     need = int(_lib.lib.iit_conv2d_wgrad_scratch_bytes(C.byref(d)))
     assert need > 0, "the case must exercise the split-K scratch"
+    code = _lib.IIT_F32 if dtype == torch.float32 else _lib.IIT_BF16
     g = torch.Generator().manual_seed(21)
     for call_no in range(2):  # second call: the built-in buffer still holds the first call's partial sums
-        x = torch.randn(n, hw, hw, c, generator=g).cuda()                      # NHWC fp32
-        dy = torch.randn(n, d.p, d.q, k, generator=g).cuda() / math.sqrt(n * d.p * d.q)
+        x = torch.randn(n, hw, hw, c, generator=g).cuda().to(dtype)            # NHWC
+        dy = (torch.randn(n, d.p, d.q, k, generator=g).cuda() / math.sqrt(n * d.p * d.q)).to(dtype)
         want = torch.empty(k, ks, ks, c, device="cuda")
         scratch = torch.empty(need, dtype=torch.uint8, device="cuda")
-        _lib.call("iit_conv2d_wgrad", _ptr(dy), _ptr(x), _ptr(want), C.byref(d), _lib.IIT_F32, _ptr(scratch), need, _stream())
+        _lib.call("iit_conv2d_wgrad", _ptr(dy), _ptr(x), _ptr(want), C.byref(d), code, _ptr(scratch), need, _stream())
         got = torch.full((k, ks, ks, c), float("nan"), device="cuda")
-        _lib.call("iit_conv2d_wgrad_noalloc", _ptr(dy), _ptr(x), _ptr(got), C.byref(d), _lib.IIT_F32, _stream())
+        _lib.call("iit_conv2d_wgrad_noalloc", _ptr(dy), _ptr(x), _ptr(got), C.byref(d), code, _stream())
         torch.cuda.synchronize()
         scale = want.abs().max().item()
-        # same tolerance as the convolution tests of this suite (2e-4 of the output scale, fp32 path)
-        assert (got - want).abs().max().item() <= 2e-4 * scale, (cfg, call_no)
+        # same tolerance as the convolution tests of this suite (2e-4 of the output scale; both entry points read the
+        # same inputs and accumulate in fp32, so the bf16 case meets it too)
+        assert (got - want).abs().max().item() <= 2e-4 * scale, (cfg, dtype, call_no)
 
 
 def test_noalloc_wgrad_rejects_oversized_problems():
