@@ -93,9 +93,12 @@ def test_counterfactual_generator(node, quad):
     ops.raise_on_index_error(DEV)
 
 
-def test_causality_sweep_matches_oracle_on_the_same_counterfactuals():
-    """eval_causality.py:14-101 at two hook points, four HL nodes, two batches: the library's sweep (kernels, truncated
-    source run, integer counts) against the oracle's restatement fed the very counterfactual tensors the sweep drew."""
+@pytest.mark.parametrize("task,n_nodes", [("mnist_pvr", 4), ("pvr_leaky", 12)])
+def test_causality_sweep_matches_oracle_on_the_same_counterfactuals(task, n_nodes):
+    """eval_causality.py:14-101 at two hook points, two batches, for the 4-node correspondence and for the 12-node LEAKY one
+    the reference's script sweeps (eval_causality.py:102,138; pvr_check_leaky_hl.py:72-109: HL variable i interchanged while
+    LL quadrant j is patched): the library's sweep (kernels, truncated source run, integer counts) against the oracle's
+    restatement fed the very counterfactual tensors the sweep drew."""
     from iit_b200 import eval_causality
     from iit_b200.tasks.mnist_pvr.get_alignment import get_alignment
     from iit_b200.tasks.mnist_pvr.counterfactual import DigitBank
@@ -116,14 +119,15 @@ def test_causality_sweep_matches_oracle_on_the_same_counterfactuals():
         return out
 
     bank.patch_batch_at_hl = recording
-    stats = eval_causality.evaluate_model_on_ablations(ll, "mnist_pvr", batches, {"batch_size": 24, "count_pairs": True}, bank,
+    stats = eval_causality.evaluate_model_on_ablations(ll, task, batches, {"batch_size": 24, "count_pairs": True}, bank,
                                                        hook_points=hooks)
-    assert stats.pop("_pairs") == 2 * 4 * 2 * 24
+    assert stats.pop("_pairs") == 2 * n_nodes * 2 * 24
     k = 0
     for hp in hooks:
         dim = {hooks[0]: 14, HOOK: 4}[hp]
         ch = {hooks[0]: 64, HOOK: 256}[hp]
-        corr = R.pvr_corr("q", hp, ch, dim)
+        corr = R.pvr_corr("q", hp, ch, dim) if task == "mnist_pvr" else R.pvr_leaky_corr(hp, dim)
+        assert len(corr) == n_nodes
         assert [str(n) for n in stats[hp].keys()] == list(corr.keys())
         for node_name, ll_nodes in corr.items():
             ratios = []
