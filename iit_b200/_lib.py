@@ -75,6 +75,7 @@ SIGNATURES = {
     "iit_bn_act_fwd": [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp],
     "iit_bn_act_bwd_reduce": [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp],
     "iit_bn_act_bwd_apply": [_vp, _vp, _vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp],
+    "iit_div_scalar": [_vp, _vp, _i, _i64, _f, _vp],
     "iit_relu_fwd": [_vp, _vp, _i, _i64, _vp],
     "iit_relu_bwd": [_vp, _vp, _vp, _i, _i64, _vp],
     "iit_add_relu_fwd": [_vp, _vp, _vp, _i, _i64, _i, _vp],

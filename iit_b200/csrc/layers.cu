@@ -193,6 +193,17 @@ __global__ void __launch_bounds__(256) relu_fwd_kernel(const T* __restrict__ x, 
     Vec4<T>::store(y + i * 4, v);
   }
 }
+// y = x / scale (IEEE division in fp32, rounded to T: what torch's `tensor / scalar` gives)
+template <typename T>
+__global__ void __launch_bounds__(256) div_scalar_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t n4, float scale) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float v[4];
+    Vec4<T>::load(x + i * 4, v);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = v[j] / scale;
+    Vec4<T>::store(y + i * 4, v);
+  }
+}
 template <typename T>
 __global__ void __launch_bounds__(256) relu_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ y, T* __restrict__ dx,
                                                        int64_t n4) {
@@ -598,6 +609,15 @@ extern "C" int iit_relu_fwd(const void* x, void* y, int dtype, int64_t n, void* 
   IIT_REQUIRE(x && y && n % 4 == 0, "iit_relu_fwd: bad arguments (n must be a multiple of 4)");
   IIT_DISPATCH_DTYPE(dtype, T, { relu_fwd_kernel<T><<<grid_for(n / 4, 512), 256, 0, as_stream(stream)>>>((const T*)x, (T*)y, n / 4); })
   IIT_LAUNCH_CHECK("iit_relu_fwd");
+  return 0;
+}
+extern "C" int iit_div_scalar(const void* x, void* y, int dtype, int64_t n, float scale, void* stream) {
+  IIT_REQUIRE(x && y && n % 4 == 0 && scale != 0.f, "iit_div_scalar: bad arguments (n must be a multiple of 4, scale non-zero)");
+  if (n == 0) return 0;
+  IIT_DISPATCH_DTYPE(dtype, T, {
+    div_scalar_kernel<T><<<grid_for(n / 4, 512), 256, 0, as_stream(stream)>>>((const T*)x, (T*)y, n / 4, scale);
+  })
+  IIT_LAUNCH_CHECK("iit_div_scalar");
   return 0;
 }
 extern "C" int iit_relu_bwd(const void* dy, const void* y, void* dx, int dtype, int64_t n, void* stream) {

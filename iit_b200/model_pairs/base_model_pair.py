@@ -119,7 +119,11 @@ class BaseModelPair(ABC):
         names = list({n.name for n in ll_nodes})
         # in eval mode nothing after the last cached hook point matters (no BatchNorm statistics move): the sweep
         # sets `stop_source_run_at_hook` and saves that part of the source forward
-        stop = bool(getattr(self, "stop_source_run_at_hook", False)) and not self.ll_model.training
+        # ... and a model whose forward has no side effect in ANY mode (the transformer: no BatchNorm, no dropout) says so
+        # with `forward_is_pure`: its source run always stops at the last cached hook point -- for IOI that skips the
+        # rest of the blocks and the 16-position unembedding of a run whose logits nobody reads
+        stop = ((bool(getattr(self, "stop_source_run_at_hook", False)) and not self.ll_model.training)
+                or bool(getattr(self.ll_model, "forward_is_pure", False)))
         with t.no_grad():
             if stop:
                 out, cache = self.ll_model.run_with_cache(ablation_x, names_filter=names, stop_when_cached=True)

@@ -67,6 +67,7 @@ def _hp():
 
 class HookedTransformerLL(HookedRootModule):
     supports_last_pos = True
+    forward_is_pure = True      # no statistics, no dropout: abandoning a forward early changes nothing (base_model_pair.ll_source_run)
 
     def __init__(self, cfg, dtype=None):
         super().__init__()

@@ -254,6 +254,17 @@ class _CEProbFn(torch.autograd.Function):
 def cross_entropy(logits: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
     """F.cross_entropy(logits, target) with mean reduction for 2-D logits; `target` is class indices
     (int64 [rows]) or probabilities (float [rows, classes])."""
+    if logits.dim() == 3:
+        # torch's convention for [N, C, d1] inputs: the CLASS dimension is dim 1 (this is what the reference's
+        # IITBehaviorModelPair.loss_fn does to [B, S, V] transformer logits, iit_behavior_model_pair.py:20-30); the mean
+        # runs over N * d1 rows
+        n, c, d1 = logits.shape
+        rows = logits.permute(0, 2, 1).reshape(n * d1, c)
+        if target.dtype == torch.int64 and target.shape == (n, d1):
+            return _CEIndexFn.apply(rows, target.reshape(n * d1))
+        if target.is_floating_point() and target.shape == logits.shape:
+            return _CEProbFn.apply(rows, target.permute(0, 2, 1).reshape(n * d1, c))
+        raise ValueError(f"cross_entropy: unsupported target {target.dtype} {tuple(target.shape)} for logits {tuple(logits.shape)}")
     if target.dtype == torch.int64 and target.dim() == 1:
         return _CEIndexFn.apply(logits, target)
     if target.is_floating_point() and target.shape == logits.shape:
@@ -270,7 +281,12 @@ def iia_count(logits: torch.Tensor, hl: Optional[torch.Tensor], changed: Optiona
     """Accumulates (hits, denominator) into `counts` (int64[2], created if None); optionally returns
     top-1 indices. No host sync."""
     _require_cuda(logits, hl, changed, counts)
-    lg, rs = _rows_view(logits.detach())
+    logits = logits.detach()
+    if logits.dim() > 2:        # [..., classes] (e.g. [B, S, V] transformer logits): one row per leading index
+        logits = logits.reshape(-1, logits.shape[-1])
+        hl = hl.reshape(-1) if hl is not None else None
+        changed = changed.reshape(-1) if changed is not None else None
+    lg, rs = _rows_view(logits)
     rows, classes = lg.shape
     if counts is None and hl is not None:
         counts = torch.zeros(2, dtype=torch.int64, device=lg.device)
@@ -679,6 +695,29 @@ def bn_relu_maxpool(x, gamma, beta, running_mean, running_var, training, momentu
                     bacc=None, pgrads=None):
     return _BNReluPoolFn.apply(x, gamma, beta, running_mean, running_var, training, momentum, eps, sums, acc, tracked, bacc,
                                pgrads)
+
+
+class _DivScalarFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, scale):
+        _require_cuda(x)
+        xc = x if (x.is_contiguous() or _is_cl(x)) else x.contiguous()
+        y = torch.empty_like(xc)
+        call("iit_div_scalar", _p(xc), _p(y), _dt(xc), xc.numel(), float(scale), _stream())
+        ctx.scale = float(scale)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        dy = dy if (dy.is_contiguous() or _is_cl(dy)) else dy.contiguous()
+        dx = torch.empty_like(dy)
+        call("iit_div_scalar", _p(dy), _p(dx), _dt(dy), dy.numel(), ctx.scale, _stream())
+        return dx, None
+
+
+def div_scalar(x, scale: float):
+    """x / scale with autograd (the stop-gradient pair's forward hook, stop_grad_pair.py:37-44)."""
+    return _DivScalarFn.apply(x, scale)
 
 
 class _ReluFn(torch.autograd.Function):

@@ -264,6 +264,9 @@ int iit_bn_act_bwd_apply(const void* dy, const void* y, const void* x, void* dx,
                          int64_t rows, int c, const float* mean, const float* invstd, const float* gamma,
                          const double* dgamma, const double* dbeta, int relu, const uint8_t* relu_mask,
                          void* stream);
+/* y = x / scale, element-wise (n a multiple of 4; y may alias x). The forward hook of the stop-gradient pair
+ * (`hook_point_out / scale`, iit/model_pairs/stop_grad_pair.py:37-44); its backward is the same call on the gradient. */
+int iit_div_scalar(const void* x, void* y, int dtype, int64_t n, float scale, void* stream);
 int iit_relu_fwd(const void* x, void* y, int dtype, int64_t n, void* stream);
 int iit_relu_bwd(const void* dy, const void* y, void* dx, int dtype, int64_t n, void* stream);
 int iit_add_relu_fwd(const void* a, const void* b, void* y, int dtype, int64_t n, int relu, void* stream);

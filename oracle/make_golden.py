@@ -201,6 +201,53 @@ def golden_ioi():
     print("wrote ioi.npz", len(res), "arrays")
 
 
+def golden_freeze_stopgrad():
+    """FreezedModelPair / StopGradModelPair (iit/model_pairs/freeze_model_pair.py, stop_grad_pair.py), unmodified, on the
+    small IOI fixture: three train steps and one eval step each, plus the node / parameter lists they build."""
+    import transformer_lens
+    from iit.model_pairs.freeze_model_pair import FreezedModelPair
+    from iit.model_pairs.stop_grad_pair import StopGradModelPair
+    from iit.tasks.ioi import corr, ioi_cfg, IOI_HL
+
+    V, B = 101, 8
+    cfg = dict(n_layers=ioi_cfg["n_layers"], n_heads=ioi_cfg["n_heads"], d_model=ioi_cfg["d_model"],
+               d_head=ioi_cfg["d_head"], d_mlp=128, d_vocab=V, n_ctx=32, act_fn="gelu_new",
+               normalization_type="LNPre", init_weights=True, device="cpu")
+    res = {}
+    for tag, cls in (("freeze", FreezedModelPair), ("stopgrad", StopGradModelPair)):
+        ll = transformer_lens.HookedTransformer(cfg)
+        ll.load_state_dict(restate.transformer_state_dict(0, d_mlp=128, d_vocab=V, n_ctx=32), strict=False)
+        _, names = restate.synthetic_ioi(B, 100, d_vocab=V, n_names=20)
+        hl = IOI_HL(d_vocab=V, names=names)
+        pair = cls(hl, ll, corr, training_args={"lr": 1e-3, "lr_scheduler": None})
+        res[f"{tag}/params_not_in_circuit"] = np.array([f"{p.name}|{p.index}" for p in pair.params_not_in_circuit])
+        if tag == "stopgrad":
+            res["stopgrad/nodes_not_in_circuit"] = np.array([f"{n.name}|{n.index}" for n in pair.ll_model.nodes_not_in_circuit])
+            res["stopgrad/post_nodes_not_in_circuit"] = np.array([f"{n.name}|{n.index}" for n in pair.ll_model.post_nodes_not_in_circuit])
+        opt = torch.optim.Adam(ll.parameters(), lr=1e-3)
+        ll.train()
+        iit, beh = [], []
+        for step in range(3):
+            base, _ = restate.synthetic_ioi(B, 100 + step, d_vocab=V, n_names=20)
+            src, _ = restate.synthetic_ioi(B, 200 + step, d_vocab=V, n_names=20)
+            m = pair.run_train_step(base, src, pair.loss_fn, opt)
+            iit.append(m["train/iit_loss"]); beh.append(m["train/behavior_loss"])
+            if step == 0:
+                res[f"{tag}/after_step0/b2_W_in"] = ll.state_dict()["blocks.2.mlp.W_in"][:4, :8].clone()
+                res[f"{tag}/after_step0/b0_W_in"] = ll.state_dict()["blocks.0.mlp.W_in"][:4, :8].clone()
+        res[f"{tag}/train/iit_loss"] = np.array(iit, dtype=np.float64)
+        res[f"{tag}/train/behavior_loss"] = np.array(beh, dtype=np.float64)
+        ll.eval()
+        with torch.no_grad():
+            base, _ = restate.synthetic_ioi(B, 300, d_vocab=V, n_names=20)
+            src, _ = restate.synthetic_ioi(B, 301, d_vocab=V, n_names=20)
+            ev = pair.run_eval_step(base, src, pair.loss_fn)
+        for k, v in ev.items():
+            res[f"{tag}/eval/{k}"] = np.asarray(v, dtype=np.float64)
+    np.savez_compressed(os.path.join(OUT, "ioi_freeze_stopgrad.npz"), **to_np(res))
+    print("wrote ioi_freeze_stopgrad.npz", len(res), "arrays")
+
+
 def _ioi_ablation_setup(bias):
     """Small IOI pair (as golden_ioi) on 48 prompts with 4 names; `bias` is added to one name's unembed bias so that the
     accuracy-based statistics are not trivially zero."""
@@ -280,7 +327,12 @@ if __name__ == "__main__":
     import iit.model_pairs  # noqa: F401  (import first: the reference has an import cycle otherwise)
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(4)
-    if "ablations" not in sys.argv[1:]:
+    only = sys.argv[1:]
+    if not only or "pvr" in only:
         golden_pvr()
+    if not only or "ioi" in only:
         golden_ioi()
-    golden_ioi_ablations()
+    if not only or "ablations" in only:
+        golden_ioi_ablations()
+    if not only or "freeze" in only:
+        golden_freeze_stopgrad()

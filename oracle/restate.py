@@ -535,6 +535,107 @@ class OraclePair:
 
 
 # --------------------------------------------------------------------------------------------
+# Freeze / stop-gradient pairs AS WRITTEN in the reference
+# --------------------------------------------------------------------------------------------
+class _StopGradSite(torch.autograd.Function):
+    """One hook point under StopGradHookedModel (stop_grad_pair.py:37-44,63-77,79-103): forward `act / scale`; backward:
+    the incoming gradient with every listed index zeroed, handed on WITHOUT the 1/scale factor -- transformer_lens wires a
+    backward hook as a full backward hook of the HookPoint module, whose return value (`[grad]`, the hook's edited copy of
+    the gradient w.r.t. the module OUTPUT) replaces the gradient w.r.t. the module INPUT, skipping the division. [TL-knowledge]"""
+
+    @staticmethod
+    def forward(ctx, act, scale, specs):
+        ctx.specs = specs
+        return act / scale if scale else act.clone()
+
+    @staticmethod
+    def backward(ctx, g):
+        g = g.clone()
+        for spec in ctx.specs:
+            g[as_index(spec)] = 0
+        return g, None, None
+
+
+class OracleFreezePair:
+    """FreezedModelPair (stop_grad=False) and StopGradModelPair (stop_grad=True) over a TransformerOracle, restating what
+    the reference code does as written:
+      * both are IITBehaviorModelPair steps (iit_behavior_model_pair.py:66-141): IIT term then behaviour term, one
+        clip + Adam update each; the loss is CrossEntropyLoss on the full [B,S,V] logits, i.e. over torch's class
+        dimension 1, against the dense HL logits / the one-hot labels as probability targets;
+      * freeze_model_pair.py:23-38: the "zeroing" assigns .grad on a temporary and changes nothing;
+      * stop_grad_pair.py:79-103: `ll_model(x)` (the behaviour forward, the accuracy forward of eval) attaches the
+        scale / zero-gradient hooks and LEAVES them attached; they act once more, on the next run_with_cache (the source
+        run of the next intervention), which removes them when it ends."""
+
+    def __init__(self, ll, corr, names, d_vocab, stop_grad, n_layers=6, n_heads=4, scale=1e6, seed=0, lr=1e-3, clip=1.0,
+                 use_ln_hooks=True):
+        self.ll, self.corr, self.names, self.d_vocab = ll, corr, names, d_vocab
+        self.rng = np.random.default_rng(seed)
+        self.opt = torch.optim.Adam(ll.parameters(), lr=lr)
+        self.clip, self.stop_grad, self.scale, self.use_ln_hooks = clip, stop_grad, scale, use_ln_hooks
+        self.keys = list(corr.keys())
+        outside = nodes_not_in_circuit(n_layers, n_heads, corr, {"attn": "attn.hook_z", "mlp": "mlp.hook_post"})
+        self.sites = {}                       # hook name -> index specs zeroed there (node_picker.py:57-79 post nodes)
+        for name, spec in outside:
+            self.sites.setdefault(name, []).append(spec)
+        self.leftover = False
+
+    def _site_hooks(self):
+        sc = self.scale if self.use_ln_hooks else None
+        return {name: (lambda act, specs=tuple(specs): _StopGradSite.apply(act, sc, specs)) for name, specs in self.sites.items()}
+
+    def model_call(self, x):
+        """`self.ll_model(x)`: StopGradHookedModel.forward, or the plain model for the freeze pair."""
+        if not self.stop_grad:
+            return self.ll(x)
+        self.leftover = True
+        return self.ll(x, hooks=self._site_hooks())
+
+    def do_intervention(self, base, src, node):
+        hooks = self._site_hooks() if self.leftover else None
+        self.leftover = False                 # run_with_cache's exit clears the level the leftovers live on
+        cache = {}
+        ll_nodes = self.corr[node]
+        self.ll(src[0], hooks=hooks, cache=cache, cache_filter={n for n, _ in ll_nodes})
+        patches = {n: (lambda act, n=n, sp=sp: patch(act, cache[n], sp)) for n, sp in ll_nodes}
+        return ioi_hl_intervened(base[0], src[0], self.names, self.d_vocab, node), self.ll(base[0], hooks=patches)
+
+    def step_on_loss(self, loss):
+        self.opt.zero_grad()
+        loss.backward()
+        if self.clip:
+            torch.nn.utils.clip_grad_norm_(self.ll.parameters(), self.clip)
+        self.opt.step()
+
+    def iit_loss(self, base, src, node):
+        hl, ll_out = self.do_intervention(base, src, node)
+        return F.cross_entropy(ll_out, hl)
+
+    def behaviour_loss(self, base):
+        return F.cross_entropy(self.model_call(base[0]).squeeze(), base[1])
+
+    def train_step(self, base, src):
+        self.ll.train()
+        node = str(self.rng.choice(self.keys))
+        iit = self.iit_loss(base, src, node)
+        self.step_on_loss(iit)
+        beh = self.behaviour_loss(base)
+        self.step_on_loss(beh)
+        return {"train/iit_loss": iit.item(), "train/behavior_loss": beh.item(), "hl_node": node}
+
+    @torch.no_grad()
+    def eval_step(self, base, src):
+        self.ll.eval()
+        node = str(self.rng.choice(self.keys))
+        hl, ll_out = self.do_intervention(base, src, node)
+        loss = F.cross_entropy(ll_out, hl)
+        iia = (torch.argmax(ll_out, dim=-1) == torch.argmax(hl, dim=-1)).float().mean().item()
+        out = self.model_call(base[0])
+        acc = (torch.argmax(out, dim=-1) == torch.argmax(base[1], dim=-1)).float().mean().item()
+        return {"val/iit_loss": loss.item(), "val/IIA": iia, "val/accuracy": acc, "hl_node": node}
+
+
+# --------------------------------------------------------------------------------------------
 # Synthetic inputs (SURVEY.md section 8(d)); shared by tests, smoke and bench so both arms see the
 # same pairs. Pure torch-CPU generators: deterministic for a given torch build.
 # --------------------------------------------------------------------------------------------

@@ -11,10 +11,8 @@ if ROOT not in sys.path:
 def _ensure_built():
     """The CPU suite checks that the C-ABI library loads and exports every declared symbol, so it
     has to exist: nvcc cross-compiles it here when the tree is fresh (no GPU needed)."""
-    lib = os.path.join(ROOT, "iit_b200", "libiit_b200.so")
-    if not os.path.exists(lib):
-        import __graft_entry__
-        __graft_entry__.build()
+    import __graft_entry__
+    __graft_entry__.build()      # no-op when the .so is newer than every source (iit_b200/build.py:needs_build)
 
 
 def pytest_configure(config):
