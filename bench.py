@@ -739,6 +739,19 @@ def run_ours(args, rank, world, local):
     torch.cuda.synchronize()
     up.restart()   # the timed region starts with its own first upload (K uploads + 1 prefetch inside it)
     sec_e2e, _ = _timed_region(dp, dev, step_e2e, args.steps)
+    # the other end-to-end path: the dataset lives on the device (DeviceIITDataset); a step uploads
+    # only the pair indices of its batch (2 x B int64), gathers the batch with the gather kernels and reads the losses back
+    from iit_b200.utils.iit_dataset import DeviceIITDataset
+    ds = DeviceIITDataset(base_d, src_d, seed=rank)
+    ds.pair_table()
+    perm_rng = np.random.default_rng(1234 + rank)
+
+    def step_dataset():
+        base, abl = ds.gather_batch(perm_rng.permutation(B))
+        return pair.run_train_step(base, abl, pair.loss_fn, opt)
+
+    step_dataset()
+    sec_ds, _ = _timed_region(dp, dev, step_dataset, args.steps)
     # data-parallel consistency: every rank must hold the same parameters after the same updates
     chk = opt.flat_p.double().sum().reshape(1)
     if world > 1:
@@ -787,6 +800,9 @@ def run_ours(args, rank, world, local):
         "dtype": args.dtype, "data": "synthetic", "config": workload_config(args, world),
         "e2e": {"value": B * world * args.steps / sec_e2e, "unit": UNIT, "h2d_bytes_per_step": up.bytes,
                 "d2h_bytes_per_step": 3 * 4},
+        "e2e_device_dataset": {"value": B * world * args.steps / sec_ds, "unit": UNIT, "h2d_bytes_per_step": 2 * B * 8,
+                               "d2h_bytes_per_step": 3 * 4,
+                               "note": "DeviceIITDataset: samples resident in HBM, per step the pair indices go up and six gather kernels build the batch"},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "kernels": timer.by_entry(pk),
         "kernel_instantiations": timer.by_kernel(pk),
         "step_tflops": 11 * F56 * B * args.steps / sec / 1e12, "dp_check": dp_check,

@@ -44,20 +44,59 @@ class DataParallel:
         n = inputs[0].shape[0] // self.world
         return tuple(t[self.rank * n:(self.rank + 1) * n] for t in inputs)
 
+    # ---- gradient averaging ---------------------------------------------------------------------------------------
+    # The flat gradient buffer is ordered like the parameters (stem first, head last) while the backward fills it from
+    # the END. A model may name a "tap": a hook point whose gradient is computed only after every parameter from
+    # `first_tail_param` on has received its gradient (ResNet-18: the output of layer3, behind which sit layer4 and the
+    # head = 75 % of the parameters). When the tap's gradient arrives, the tail of the buffer is all-reduced at once on
+    # NCCL's stream, under the rest of the backward; only the (small) head part is reduced after it. Two messages, the
+    # larger one hidden. NCCL averages in the collective (ReduceOp.AVG): no separate scaling kernel.
+    def _average(self, t, async_op=False):
+        if dist.get_backend(self.group) == "nccl":
+            return dist.all_reduce(t, op=dist.ReduceOp.AVG, group=self.group, async_op=async_op)
+        w = dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group, async_op=False)   # gloo has no AVG
+        t.mul_(1.0 / self.world)
+        return None if async_op else w
+
+    def _attach(self, optimizer, ll_model):
+        self._attached = (optimizer, ll_model)
+        self._tail = None          # (offset of the tail bucket, pending Work or None)
+        tap = getattr(ll_model, "dp_bucket_tap", None)
+        offset_of = getattr(optimizer, "offset_of", None)
+        if tap is None or offset_of is None or getattr(optimizer, "flat_g", None) is None:
+            return
+        hook_name, first_tail_param = tap
+        off = offset_of(dict(ll_model.named_parameters())[first_tail_param])
+        flat = optimizer.flat_g
+
+        def tail_ready(grad, hook):
+            if self._tail is None:      # once per backward: every gradient from `off` on is final
+                self._tail = (off, self._average(flat[off:], async_op=True))
+            return None
+
+        ll_model.hook_dict[hook_name].add_hook(tail_ready, dir="bwd", is_permanent=True)
+
     def allreduce_grads(self, optimizer, ll_model):
         """Average gradients across ranks, before clip_grad_norm_ so the clip sees the global norm
         (reference order: backward -> clip -> step, iit_behavior_model_pair.py:60-64)."""
         if self.world == 1:
             return
+        if getattr(self, "_attached", None) is None or self._attached[0] is not optimizer:
+            self._attach(optimizer, ll_model)
         flat = getattr(optimizer, "flat_g", None)
-        if flat is not None:  # FlatAdam: one message
-            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
-            flat.mul_(1.0 / self.world)
+        if flat is not None:  # FlatAdam: one message, or two when the tail bucket left early
+            tail, self._tail = getattr(self, "_tail", None), None
+            if tail is None:
+                self._average(flat)
+                return
+            off, work = tail
+            self._average(flat[:off])
+            if work is not None:
+                work.wait()       # the current stream waits for the tail's collective
             return
         for p in ll_model.parameters():
             if p.grad is not None:
-                dist.all_reduce(p.grad, op=dist.ReduceOp.SUM, group=self.group)
-                p.grad.mul_(1.0 / self.world)
+                self._average(p.grad)
 
     def allreduce_counts(self, counts: torch.Tensor) -> torch.Tensor:
         """Sum int64 (hits, denominator) counts over ranks: reduce counts, then divide."""

@@ -23,6 +23,7 @@ class FlatAdam(torch.optim.Optimizer):
         if dev.type != "cuda":
             raise RuntimeError("FlatAdam runs on CUDA parameters only (no CPU fallback)")
         self._params = params
+        self._offsets = {}
         # 16-byte aligned segments so every view can be read with vector loads
         offs, total = [], 0
         for p in params:
@@ -42,6 +43,7 @@ class FlatAdam(torch.optim.Optimizer):
         self.post_step = []   # callables run after every update (e.g. the model's refresh of its bf16 filter copies)
         with torch.no_grad():
             for p, o in zip(params, offs):
+                self._offsets[id(p)] = o
                 pv = self._view_like(self.flat_p, o, p)
                 pv.copy_(p)
                 p.data = pv
@@ -52,6 +54,10 @@ class FlatAdam(torch.optim.Optimizer):
     def _view_like(flat, off, p):
         """View of flat[off: off+numel] with p's shape and (dense) strides, e.g. channels-last filters."""
         return torch.as_strided(flat, p.shape, p.stride(), off) if _dense(p) else flat[off: off + p.numel()].view(p.shape)
+
+    def offset_of(self, p) -> int:
+        """Element offset of parameter `p` (and of its gradient) in the flat buffers; segments follow parameter order."""
+        return self._offsets[id(p)]
 
     def zero_grad(self, set_to_none: bool = False):
         self.flat_g.zero_()

@@ -241,6 +241,9 @@ class ResNet18LL(HookedRootModule):
         self.setup()
         # each BasicBlock applies its one ReLU module twice (after bn1 and after the residual add), as torchvision does:
         # its hook point fires twice per forward and a cache keeps the second value (hooks.run_with_cache)
+        # data-parallel gradient buckets (iit_b200/dist.py): once the gradient w.r.t. layer3's output exists, every
+        # parameter of layer4 and the head (75 % of all) has its gradient
+        self.dp_bucket_tap = ("mod.layer3.hook_point", "mod.layer4.mod.0.mod.conv1.mod.weight")
         self.multi_fire_hook_points = frozenset(n for n in self.hook_dict if ".mod.relu.hook_point" in n and "layer" in n)
 
     # --- forward ----------------------------------------------------------------------------

@@ -113,6 +113,10 @@ class HookedTransformerLL(HookedRootModule):
                 if "W_" in name:
                     nn.init.normal_(p, std=c.initializer_range)
         self.setup()
+        # data-parallel gradient buckets (iit_b200/dist.py): the gradient w.r.t. the residual stream entering the middle
+        # block exists once the later blocks and the unembedding have theirs
+        if c.n_layers >= 2:
+            self.dp_bucket_tap = (f"blocks.{c.n_layers // 2}.hook_resid_pre", f"blocks.{c.n_layers // 2}.attn.W_Q")
         # attn.hook_result is not in this list: with use_attn_result=False (the only configuration this model accepts)
         # transformer_lens never calls that hook point, so a hook attached there is legal and never fires -- which is
         # what the reference's `check_causal_effect(node_type="a")` relies on (iit/utils/node_picker.py:11-14 default

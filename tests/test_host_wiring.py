@@ -180,6 +180,48 @@ def _gather_worker(rank, world, port, q):
             p_.grad = torch.full_like(p_, float(rank + 1))
         dp.allreduce_grads(torch.optim.SGD(lin.parameters(), lr=0.1), lin)
         grads = [p_.grad.flatten().tolist() for p_ in lin.parameters()]
+        # two-bucket path: a model that names a tap, an optimizer with one flat gradient buffer; the tail bucket is
+        # all-reduced from inside the backward (when the tap's gradient arrives), the head after it
+        from iit_b200.hooks import HookedRootModule, HookPoint
+
+        class Two(HookedRootModule):
+            def __init__(self):
+                super().__init__()
+                self.a, self.b, self.mid = torch.nn.Linear(3, 3), torch.nn.Linear(3, 2), HookPoint()
+                self.setup()
+                self.dp_bucket_tap = ("mid", "b.weight")
+
+            def forward(self, x):
+                return self.b(self.mid(self.a(x)))
+
+        class FlatOpt:
+            def __init__(self, model):
+                ps = list(model.parameters())
+                self.flat_g = torch.zeros(sum(p_.numel() for p_ in ps))
+                self.offs, o = {}, 0
+                for p_ in ps:
+                    self.offs[id(p_)] = o
+                    p_.grad = self.flat_g[o:o + p_.numel()].view_as(p_)
+                    o += p_.numel()
+
+            def offset_of(self, p_):
+                return self.offs[id(p_)]
+
+        torch.manual_seed(0)
+        two = Two()
+        fo = FlatOpt(two)
+        dp2 = DataParallel()
+        fired = []
+        for it in range(2):           # the first call attaches the tap (one message), the second uses both buckets
+            fo.flat_g.zero_()
+            two(torch.full((4, 3), float(rank + 1))).sum().backward()
+            local = fo.flat_g.clone()
+            fired.append(getattr(dp2, "_tail", None) is not None)
+            dp2.allreduce_grads(fo, two)
+            both = [torch.zeros_like(local) for _ in range(world)]
+            dist.all_gather(both, local)
+            assert torch.allclose(fo.flat_g, torch.stack(both).mean(0)), (it, fo.flat_g, both)
+        assert fired == [False, True], fired
         counts = dp.allreduce_counts(torch.tensor([rank + 1, 10], dtype=torch.int64)).tolist()
         shard = dp.shard((torch.arange(10), torch.arange(10) * 2))
         q.put((rank, out.shape, out[:, :, 0].tolist(), grads, counts, [t_.tolist() for t_ in shard]))
