@@ -852,12 +852,17 @@ def main():
         return
     from iit_b200 import dist as idist
     rank, world, local = idist.init_from_env()
-    try:
-        run_ours(args, rank, world, local)
-    finally:
-        if world > 1:
-            import torch.distributed as dist
-            dist.destroy_process_group()
+    run_ours(args, rank, world, local)
+    if world > 1:
+        # leave together, then end without tearing the communicator down: captured graphs still hold its collectives and
+        # destroying it under them can block at exit (seen in tests/dp_grad_check.py)
+        import torch.distributed as dist
+        done = torch.ones(1, device=torch.device("cuda", local))
+        dist.all_reduce(done)
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":

@@ -24,7 +24,13 @@ def flat_grad(ll):
     return torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).detach().flatten().double() for p in ll.parameters()])
 
 
+def say(msg):
+    print(f"[rank {os.environ.get('RANK', '0')}] {msg}", file=sys.stderr, flush=True)
+
+
 def main():
+    import faulthandler
+    faulthandler.dump_traceback_later(120, exit=True)      # a hang prints every thread's stack and ends the process
     from iit_b200 import dist as idist
     from iit_b200.model_pairs import IOI_ModelPair, StrictIITModelPair
     from iit_b200.tasks.ioi import IOI_HL, corr, make_ll_model
@@ -65,15 +71,16 @@ def main():
         fn(pair, lb, ls).backward()
         dp.allreduce_grads(opt, ll)
         dp_grads[name] = flat_grad(ll)
-    if rank == 0:
-        single, sll, sopt = make_ioi(False)
-        errs = {}
-        for name, fn in terms.items():
-            sopt.zero_grad()
-            fn(single, gb, gs).backward()
-            g1 = flat_grad(sll)
-            errs[name] = float((dp_grads[name] - g1).norm() / g1.norm())
-        out["ioi_grad_rel_l2_vs_1gpu"] = errs
+    say("ioi: data-parallel gradients done")
+    single, sll, sopt = make_ioi(False)        # every rank: the whole global batch on its own GPU, no collective
+    errs = {}
+    for name, fn in terms.items():
+        sopt.zero_grad()
+        fn(single, gb, gs).backward()
+        g1 = flat_grad(sll)
+        errs[name] = float((dp_grads[name] - g1).norm() / g1.norm())
+    out["ioi_grad_rel_l2_vs_1gpu"] = errs
+    say(f"ioi: single-GPU comparison done {errs}")
     # K free-running strict steps with graphs: identical parameters on every rank
     pair2, ll2, opt2 = make_ioi(True)
     pair2.training_args["cuda_graphs"] = True
@@ -83,6 +90,7 @@ def main():
     allc = [torch.empty_like(chk) for _ in range(world)]
     dist.all_gather(allc, chk)
     out["ioi_param_checksum_max_diff"] = float(max(abs(float(c) - float(allc[0])) for c in allc))
+    say("ioi: free-running graph steps done")
 
     # ---- ResNet: averaged gradient == mean of the shards' single-GPU gradients (BatchNorm statistics are per rank) ---
     hook = "mod.layer3.mod.1.mod.conv2.hook_point"
@@ -105,6 +113,7 @@ def main():
     dist.all_gather(parts, local_g)
     want = torch.stack(parts).mean(0)
     out["resnet_avg_grad_rel_l2_vs_mean_of_shards"] = float((avg_g - want).norm() / want.norm())
+    say("resnet: averaged gradient done")
     for _ in range(3):
         rpair.run_train_step(base, src, rpair.loss_fn, ropt)
     chk = ropt.flat_p.double().sum().reshape(1)
@@ -116,8 +125,16 @@ def main():
         assert all(v <= 1e-6 for v in out["ioi_grad_rel_l2_vs_1gpu"].values()), out
         assert out["ioi_param_checksum_max_diff"] == 0.0 and out["resnet_param_checksum_max_diff"] == 0.0, out
         assert out["resnet_avg_grad_rel_l2_vs_mean_of_shards"] <= 1e-6, out
-    dist.barrier()
-    dist.destroy_process_group()
+    faulthandler.cancel_dump_traceback_later()
+    # leave together (a tiny all-reduce the host waits for), then end the process without tearing NCCL down: the captured
+    # graphs above still hold collectives of this communicator, and destroying it under them blocked at exit
+    done = torch.ones(1, device=dev)
+    dist.all_reduce(done)
+    torch.cuda.synchronize()
+    say("done")
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(0)
 
 
 if __name__ == "__main__":
