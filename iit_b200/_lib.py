@@ -60,6 +60,7 @@ SIGNATURES = {
     "iit_conv2d_tc_supported": [_ConvP, _i],
     "iit_conv2d_fprop_tc": [_vp, _vp, _vp, _ConvP, _vp, _vp, _vp],
     "iit_conv2d_dgrad_tc": [_vp, _vp, _vp, _ConvP, _vp],
+    "iit_conv2d_dgrad_tc_accumulate": [_vp, _vp, _vp, _ConvP, _vp],
     "iit_conv2d_wgrad_tc_scratch_bytes": [_ConvP],
     "iit_conv2d_wgrad_tc": [_vp, _vp, _vp, _ConvP, _vp, _sz, _vp],
     "iit_conv2d_wgrad_tc_accumulate": [_vp, _vp, _vp, _ConvP, _vp, _sz, _vp],

@@ -40,6 +40,7 @@ struct TcParams {
   int BW, BH, BNI;        // pixel box
   int tiles_w, tiles_h;   // boxes per image row / column
   int tiles_n;            // image blocks
+  int accumulate;         // != 0: the produced values are ADDED to what `out` holds (st_or_add_bf16x8)
 };
 
 // Persistent: gridDim.x CTAs walk the tile list (tile = pixel box x filter block; filter block fastest so that CTAs
@@ -234,7 +235,8 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
           if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[acc])) : "memory");
         }
         // store (64 contiguous bytes per pixel) and, for the BatchNorm that follows, per-channel sums of the values as stored
-        tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c, ok, bn_sum != nullptr ? s_stat + c : nullptr, s_stat + BN + c);
+        tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c, ok, bn_sum != nullptr ? s_stat + c : nullptr, s_stat + BN + c,
+                       p.accumulate != 0);
       }
      }  // mt
       if (bn_sum != nullptr) {
@@ -447,7 +449,8 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
           __syncwarp();
           if (lane == 0) mbar_arrive_cluster(lead_empty);
         }
-        tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c, ok, bn_sum != nullptr ? s_stat + c : nullptr, s_stat + BN + c);
+        tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c, ok, bn_sum != nullptr ? s_stat + c : nullptr, s_stat + BN + c,
+                       p.accumulate != 0);
       }
       if (bn_sum != nullptr) {
         asm volatile("bar.sync 1, 256;" ::: "memory");
@@ -664,8 +667,10 @@ static int conv_tc_fprop(const void* x, const void* w_krsc, void* y, const iit_c
 
 // dx[n,h,w,c] = sum_{r,s,k} dy[n,(h+pad-r)/stride,(w+pad-s)/stride,k] * w[k,r,s,c]  over exact divisions.
 // For stride 2 the output splits into four parity classes, each a stride-1 gather of dy with its own taps.
-static int conv_tc_dgrad(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, cudaStream_t st) {
-  const char* name = "iit_conv2d_dgrad_tc";
+// `accumulate`: dx += the result (one reduction per element; classes no tap reaches then need no launch and no memset).
+static int conv_tc_dgrad(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, cudaStream_t st,
+                         bool accumulate = false) {
+  const char* name = accumulate ? "iit_conv2d_dgrad_tc_accumulate" : "iit_conv2d_dgrad_tc";
   if (check_tc_ptrs(dy, w_crsk, dx, name)) return 1;
   const int st_ = d->stride;
   // Parity classes of dx that no filter tap reaches (three of the four for a 1x1 stride-2 convolution) are zeros: one memset
@@ -678,7 +683,8 @@ static int conv_tc_dgrad(const void* dy, const void* w_crsk, void* dx, const iit
         for (int s = 0; s < d->s; ++s) any = any || ((a + d->pad - r) % st_ == 0 && (b + d->pad - s) % st_ == 0);
       zero_class = zero_class || !any;
     }
-  if (zero_class) IIT_CUDA(cudaMemsetAsync(dx, 0, (size_t)d->n * d->h * d->w * d->c * sizeof(__nv_bfloat16), st));
+  if (zero_class && !accumulate)
+    IIT_CUDA(cudaMemsetAsync(dx, 0, (size_t)d->n * d->h * d->w * d->c * sizeof(__nv_bfloat16), st));
   for (int a = 0; a < st_; ++a)
     for (int b = 0; b < st_; ++b) {
       TcParams tp{};
@@ -687,6 +693,7 @@ static int conv_tc_dgrad(const void* dy, const void* w_crsk, void* dx, const iit
       if (tp.P <= 0 || tp.Q <= 0) continue;
       tp.out_mul = st_; tp.out_oh = a; tp.out_ow = b; tp.in_mul = 1;
       tp.Cin = d->k; tp.Cout = d->c;
+      tp.accumulate = accumulate ? 1 : 0;
       int nt = 0;
       for (int r = 0; r < d->r; ++r) {
         if ((a + d->pad - r) % st_ != 0) continue;
@@ -982,7 +989,7 @@ static int launch_wgrad_tc(const CUtensorMap& mdy, const CUtensorMap& mx, float*
 // conv_win.cu: shifted-window kernel for 3x3 / stride-1 / 64 -> 64 convolutions on small images
 bool conv_win_3x3_supported(const iit_conv_t* d);
 int conv_win_3x3(const void* in, const void* wmat, void* out, const iit_conv_t* d, bool flip, cudaStream_t st, double* bn_sum,
-                 double* bn_sq, const char* name);
+                 double* bn_sq, const char* name, bool accumulate = false);
 bool wgrad_win_supported(const iit_conv_t* d);
 size_t wgrad_win_scratch_bytes(const iit_conv_t* d);
 int wgrad_win(const void* dy, const void* x, float* part, const iit_conv_t* d, int* splits, cudaStream_t st, const char* name);
@@ -1024,15 +1031,24 @@ extern "C" int iit_conv2d_fprop_tc(const void* x, const void* w_krsc, void* y, c
   return conv_tc_fprop(x, w_krsc, y, d, as_stream(stream), bn_sum, bn_sqsum);
 }
 
-extern "C" int iit_conv2d_dgrad_tc(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream) {
-  IIT_REQUIRE(dy && w_crsk && dx && d, "iit_conv2d_dgrad_tc: null pointer");
-  IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "iit_conv2d_dgrad_tc: only bf16 3x3/pad-1 or 1x1/pad-0 convolutions, stride 1 "
-              "or 2, with channel counts that are multiples of 64");
+static int dgrad_tc_entry(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream, bool accumulate,
+                          const char* name) {
+  IIT_REQUIRE(dy && w_crsk && dx && d, "%s: null pointer", name);
+  IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "%s: only bf16 3x3/pad-1 or 1x1/pad-0 convolutions, stride 1 "
+              "or 2, with channel counts that are multiples of 64", name);
   if (g_use_win && conv_win_3x3_supported(d)) {
-    if (check_tc_ptrs(dy, w_crsk, dx, "iit_conv2d_dgrad_tc")) return 1;
-    return conv_win_3x3(dy, w_crsk, dx, d, true, as_stream(stream), nullptr, nullptr, "iit_conv2d_dgrad_tc");
+    if (check_tc_ptrs(dy, w_crsk, dx, name)) return 1;
+    return conv_win_3x3(dy, w_crsk, dx, d, true, as_stream(stream), nullptr, nullptr, name, accumulate);
   }
-  return conv_tc_dgrad(dy, w_crsk, dx, d, as_stream(stream));
+  return conv_tc_dgrad(dy, w_crsk, dx, d, as_stream(stream), accumulate);
+}
+
+extern "C" int iit_conv2d_dgrad_tc(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream) {
+  return dgrad_tc_entry(dy, w_crsk, dx, d, stream, false, "iit_conv2d_dgrad_tc");
+}
+
+extern "C" int iit_conv2d_dgrad_tc_accumulate(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream) {
+  return dgrad_tc_entry(dy, w_crsk, dx, d, stream, true, "iit_conv2d_dgrad_tc_accumulate");
 }
 
 extern "C" size_t iit_conv2d_wgrad_tc_scratch_bytes(const iit_conv_t* d) {

@@ -37,6 +37,7 @@ struct WinParams {
   int tile_bytes;           // bytes TMA delivers per tile
   int16_t doff[WIN_MAX_TAPS];  // tap -> row offset dh*PW + dw (relative to the output position)
   int8_t wk[WIN_MAX_TAPS];     // tap -> block column of the filter matrix
+  int accumulate;              // != 0: results are added to `out` (one 16-byte reduction per piece) instead of stored
 };
 
 // K-major operand descriptor for rows of RB bytes: SWIZZLE_128B (RB = 128) or SWIZZLE_32B (RB = 32)
@@ -193,7 +194,7 @@ __global__ void __launch_bounds__(WIN_THREADS) conv_win_kernel(const __grid_cons
           if (ok) {
 #pragma unroll
             for (int j = 0; j < 16; j += 4)
-              *reinterpret_cast<uint4*>(dst + c + 2 * j) = make_uint4(pk[j], pk[j + 1], pk[j + 2], pk[j + 3]);
+              st_or_add_bf16x8(dst + c + 2 * j, make_uint4(pk[j], pk[j + 1], pk[j + 2], pk[j + 3]), p.accumulate != 0);
             if (bn_sum != nullptr) {
 #pragma unroll
               for (int j = 0; j < 16; ++j) {
@@ -343,9 +344,10 @@ bool conv_win_3x3_supported(const iit_conv_t* d) {
 }
 
 int conv_win_3x3(const void* in, const void* wmat, void* out, const iit_conv_t* d, bool flip, cudaStream_t st, double* bn_sum,
-                 double* bn_sq, const char* name) {
+                 double* bn_sq, const char* name, bool accumulate) {
   WinParams p{};
   p.N = d->n; p.ntaps = 9;
+  p.accumulate = accumulate ? 1 : 0;
   const int PW = d->w + 2;
   IIT_REQUIRE(win_plan(&p, 128, d->p, d->q, PW, 2, 1, 1, PW + 1, -(PW + 1)), "%s: image does not fit the shifted-window kernel", name);
   p.x0 = -1; p.y0 = -1; p.y_step = p.band_h;

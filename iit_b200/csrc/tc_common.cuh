@@ -168,9 +168,21 @@ constexpr int TC_STAGE_PITCH = 80;   // bytes per staged pixel row: 64 of data, 
 // added to them, for the BatchNorm that follows. The staged rows make this a column sum: lane (row parity, channel pair)
 // reads 16 words, against a 31-shuffle butterfly over registers (~450 instructions per chunk, which bounded the
 // small-reduction layers). Rows outside the tensor must be staged as zeros when statistics are taken.
+// 8 bf16 values: dst[0..7] = v (plain 16-byte store) or dst[0..7] += v (ONE 16-byte reduction instruction,
+// red.global.add.noftz.v4.bf16x2 = REDG.E.ADD.BF16x8: the addition happens in L2, the SM neither loads the old values nor
+// waits for them). Every element receives exactly one addend per launch, so the result does not depend on any order.
+__device__ __forceinline__ void st_or_add_bf16x8(__nv_bfloat16* dst, const uint4& v, bool accumulate) {
+  if (accumulate) {
+    asm volatile("red.global.add.noftz.v4.bf16x2 [%0], {%1, %2, %3, %4};"
+                 ::"l"(dst), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+  } else {
+    *reinterpret_cast<uint4*>(dst) = v;
+  }
+}
+
 __device__ __forceinline__ void tc_store_packed(const uint32_t (&pk)[16], uint8_t* stage, int lane, int sub, int piece,
                                                 __nv_bfloat16* const (&sdst)[4], int c, float* sum = nullptr,
-                                                float* sq = nullptr) {
+                                                float* sq = nullptr, bool accumulate = false) {
 #pragma unroll
   for (int j = 0; j < 16; j += 4)
     *reinterpret_cast<uint4*>(stage + lane * TC_STAGE_PITCH + j * 4) = make_uint4(pk[j], pk[j + 1], pk[j + 2], pk[j + 3]);
@@ -178,7 +190,7 @@ __device__ __forceinline__ void tc_store_packed(const uint32_t (&pk)[16], uint8_
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const uint4 o = *reinterpret_cast<const uint4*>(stage + (sub + 8 * i) * TC_STAGE_PITCH + piece * 16);
-    if (sdst[i] != nullptr) *reinterpret_cast<uint4*>(sdst[i] + c) = o;
+    if (sdst[i] != nullptr) st_or_add_bf16x8(sdst[i] + c, o, accumulate);
   }
   if (sum != nullptr) {
     const int cp = lane & 15, par = lane >> 4;       // channels 2cp, 2cp+1 of rows par, par+2, ...
@@ -201,14 +213,14 @@ __device__ __forceinline__ void tc_store_packed(const uint32_t (&pk)[16], uint8_
 // the same from the fp32 accumulator values; `keep` = this lane's pixel lies inside the tensor
 __device__ __forceinline__ void tc_store_chunk(const uint32_t (&v)[32], uint8_t* stage, int lane, int sub, int piece,
                                                __nv_bfloat16* const (&sdst)[4], int c, bool keep = true, float* sum = nullptr,
-                                               float* sq = nullptr) {
+                                               float* sq = nullptr, bool accumulate = false) {
   uint32_t pk[16];
 #pragma unroll
   for (int j = 0; j < 16; ++j) {
     __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
     pk[j] = keep ? *reinterpret_cast<uint32_t*>(&h) : 0u;
   }
-  tc_store_packed(pk, stage, lane, sub, piece, sdst, c, sum, sq);
+  tc_store_packed(pk, stage, lane, sub, piece, sdst, c, sum, sq, accumulate);
 }
 
 // ---- host side -----------------------------------------------------------------------------------

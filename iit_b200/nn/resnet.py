@@ -77,13 +77,13 @@ class Conv2d(nn.Module):
             self._prep["stem"] = ent
         return ent[1]
 
-    def forward(self, x, bn_sums=None, act_dtype=None):
+    def forward(self, x, bn_sums=None, act_dtype=None, slot=None):
         if act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES and self.is_stem():
             s2d = self.weight.shape[0] == 64 and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0
             return ops.stem_conv(x, self.weight, self.stem_filter(s2d), bn_sums)
         krsc, crsk = self.prepared(x.dtype)
         wgrad_buf = ops.direct_grad(self.weight) if torch.is_grad_enabled() else None
-        return ops.conv2d(x, self.weight, krsc, crsk, self.stride, self.pad, bn_sums, wgrad_buf)
+        return ops.conv2d(x, self.weight, krsc, crsk, self.stride, self.pad, bn_sums, wgrad_buf, slot)
 
 
 class BatchNorm2d(nn.Module):
@@ -120,13 +120,13 @@ class BatchNorm2d(nn.Module):
         gg, gb = ops.direct_grad(self.weight), ops.direct_grad(self.bias)
         return self.grad_accumulator(x.device), ((gg, gb) if gg is not None and gb is not None else None)
 
-    def forward(self, x, residual=None, relu=False, sums=None):
+    def forward(self, x, residual=None, relu=False, sums=None, slot=None):
         acc = self.accumulator(x.device) if (self.training and x.is_cuda) else None
         bacc, pgrads = self.backward_buffers(x)
         try:
             return ops.bn_act(x, self.weight, self.bias, residual, self.running_mean, self.running_var, self.training,
                               self.momentum, self.eps, relu, sums, acc, self.num_batches_tracked if self.training else None,
-                              bacc, pgrads)
+                              bacc, pgrads, slot)
         except Exception:
             if acc is not None:
                 acc.zero_()      # a failed launch sequence must not leave partial sums behind
@@ -198,7 +198,8 @@ class BasicBlock(nn.Module):
             self.downsample = Wrapped(_Seq(Wrapped(Conv2d(cin, cout, 1, stride, 0)), Wrapped(BatchNorm2d(cout))))
 
 
-def _conv_bn(conv: Wrapped, bn: Wrapped, x, residual=None, relu=False, fuse_stats=True, act_dtype=None):
+def _conv_bn(conv: Wrapped, bn: Wrapped, x, residual=None, relu=False, fuse_stats=True, act_dtype=None, in_slot=None,
+             res_slot=None):
     """conv -> hook -> bn(+residual)(+relu). BN statistics come from the conv epilogue unless a hook
     can modify the conv output first (the patch site): then they are taken from the hooked tensor."""
     bnm = bn.mod
@@ -206,12 +207,12 @@ def _conv_bn(conv: Wrapped, bn: Wrapped, x, residual=None, relu=False, fuse_stat
     if bnm.training and fuse_stats and not conv.hook_point.has_hooks():
         sums = bnm.accumulator(x.device) if x.is_cuda else ops.new_bn_sums(bnm.c, x.device)
     try:
-        y = conv.hook_point(conv.mod(x, sums) if act_dtype is None else conv.mod(x, sums, act_dtype))
+        y = conv.hook_point(conv.mod(x, sums, slot=in_slot) if act_dtype is None else conv.mod(x, sums, act_dtype))
     except Exception:
         if sums is not None:
             sums.zero_()         # the accumulator is persistent: never leave partial sums in it
         raise
-    return bnm(y, residual=residual, relu=relu, sums=sums)
+    return bnm(y, residual=residual, relu=relu, sums=sums, slot=res_slot)
 
 
 class _Body(nn.Module):
@@ -249,24 +250,28 @@ class ResNet18LL(HookedRootModule):
     # --- forward ----------------------------------------------------------------------------
     def _block(self, wb: Wrapped, x):
         b: BasicBlock = wb.mod
+        # the block input feeds conv1 and the skip path: their two gradients meet in a GradSlot (the second is added onto
+        # the first inside its kernel) instead of in an element-wise addition by autograd
+        slot = ops.GradSlot() if (torch.is_grad_enabled() and x.requires_grad) else None
         # conv1 -> bn1 -> relu
         if b.bn1.hook_point.has_hooks():
-            out = b.bn1.hook_point(_conv_bn(b.conv1, b.bn1, x))
+            out = b.bn1.hook_point(_conv_bn(b.conv1, b.bn1, x, in_slot=slot))
             out = b.relu.hook_point(b.relu.mod(out))
         else:
-            out = b.relu.hook_point(_conv_bn(b.conv1, b.bn1, x, relu=True))
+            out = b.relu.hook_point(_conv_bn(b.conv1, b.bn1, x, relu=True, in_slot=slot))
         # identity path
         identity = x
         if b.downsample is not None:
             ds = b.downsample
-            identity = ds.mod[1].hook_point(_conv_bn(ds.mod[0], ds.mod[1], x))
+            identity = ds.mod[1].hook_point(_conv_bn(ds.mod[0], ds.mod[1], x, in_slot=slot))
             identity = ds.hook_point(identity)
         # conv2 -> bn2 -> (+identity) -> relu
         if b.bn2.hook_point.has_hooks():
             out = b.bn2.hook_point(_conv_bn(b.conv2, b.bn2, out))
             out = ops.add_relu(out, identity, True)
         else:
-            out = _conv_bn(b.conv2, b.bn2, out, residual=identity, relu=True)
+            out = _conv_bn(b.conv2, b.bn2, out, residual=identity, relu=True,
+                           res_slot=slot if b.downsample is None else None)
         out = b.relu.hook_point(out)
         return wb.hook_point(out)
 

@@ -342,9 +342,39 @@ def direct_grad(p: torch.Tensor) -> Optional[torch.Tensor]:
     return g
 
 
+USE_GRAD_SLOTS = True     # tests flip it to compare with autograd's own addition
+
+
+class GradSlot:
+    """Meeting point for the two gradients of a tensor that feeds two consumers inside one residual block (conv1 and the
+    skip path). Whichever backward runs first writes its gradient as usual, returns it to autograd and leaves the buffer
+    here; the one that runs second ADDS its result onto that buffer inside its own kernel (iit_conv2d_dgrad_tc_accumulate)
+    and returns None -- so autograd, which holds the first tensor by reference until both are done, never launches an
+    element-wise addition. A consumer that cannot accumulate (another dtype / kernel family) ignores the slot and returns
+    its gradient normally; autograd then adds, as before."""
+    __slots__ = ("_buf", "_task")
+
+    def __init__(self):
+        self._buf, self._task = None, -1
+
+    @staticmethod
+    def _current_task() -> int:
+        return int(torch._C._current_graph_task_id())      # identifies the backward pass that is running (-1: none)
+
+    def put(self, t: torch.Tensor):
+        self._buf, self._task = t, self._current_task()
+
+    def take(self):
+        """The gradient the other consumer left during THIS backward pass (a leftover of an earlier, incomplete pass is
+        dropped), or None."""
+        buf, task = self._buf, self._task
+        self._buf, self._task = None, -1
+        return buf if (buf is not None and task == self._current_task() and task != -1) else None
+
+
 class _ConvFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums, wgrad_buf):
+    def forward(ctx, x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums, wgrad_buf, slot=None):
         _require_cuda(x, weight)
         x = _cl(x)
         k, c, r, s = weight.shape
@@ -360,6 +390,7 @@ class _ConvFn(torch.autograd.Function):
             call("iit_conv2d_fprop", _p(x), _p(w_krsc), _p(y), C.byref(d), _dt(x), _p(s0), _p(s1), _stream())
         ctx.save_for_backward(x, weight)
         ctx.d, ctx.w_crsk_fn, ctx.tc = d, w_crsk_fn, tc
+        ctx.slot = slot if tc else None
         # physical KRSC (channels-last filter) gradient buffer the weight-gradient reduction may add into directly
         ctx.wgrad_buf = wgrad_buf if (tc and wgrad_buf is not None and wgrad_buf.shape == weight.shape
                                       and wgrad_buf.permute(0, 2, 3, 1).is_contiguous()) else None
@@ -372,11 +403,19 @@ class _ConvFn(torch.autograd.Function):
         dy = _cl(dy)
         dx = dw = None
         if ctx.needs_input_grad[0]:
-            dx = empty_cl(d.n, d.c, d.h, d.w, x.dtype, x.device)
-            if ctx.tc:
-                call("iit_conv2d_dgrad_tc", _p(dy), _p(ctx.w_crsk_fn()), _p(dx), C.byref(d), _stream())
+            slot = ctx.slot if USE_GRAD_SLOTS else None
+            first = slot.take() if slot is not None else None
+            if first is not None and first.shape == x.shape and first.dtype == x.dtype and _is_cl(first):
+                # the other consumer's gradient is already there: add this one onto it, hand autograd nothing
+                call("iit_conv2d_dgrad_tc_accumulate", _p(dy), _p(ctx.w_crsk_fn()), _p(first), C.byref(d), _stream())
             else:
-                call("iit_conv2d_dgrad", _p(dy), _p(ctx.w_crsk_fn()), _p(dx), C.byref(d), _dt(x), _stream())
+                dx = empty_cl(d.n, d.c, d.h, d.w, x.dtype, x.device)
+                if ctx.tc:
+                    call("iit_conv2d_dgrad_tc", _p(dy), _p(ctx.w_crsk_fn()), _p(dx), C.byref(d), _stream())
+                    if slot is not None:
+                        slot.put(dx)
+                else:
+                    call("iit_conv2d_dgrad", _p(dy), _p(ctx.w_crsk_fn()), _p(dx), C.byref(d), _dt(x), _stream())
         if ctx.needs_input_grad[1] and ctx.wgrad_buf is not None:
             need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
             scratch = torch.empty(need, dtype=torch.uint8, device=x.device)
@@ -392,12 +431,13 @@ class _ConvFn(torch.autograd.Function):
                 scratch = torch.empty(need, dtype=torch.uint8, device=x.device) if need else None
                 call("iit_conv2d_wgrad", _p(dy), _p(x), _p(dwb), C.byref(d), _dt(x), _p(scratch), need, _stream())
             dw = dwb.permute(0, 3, 1, 2)  # [K,C,R,S] view with channels-last strides, like the parameter
-        return dx, dw, None, None, None, None, None, None
+        return dx, dw, None, None, None, None, None, None, None
 
 
-def conv2d(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums=None, wgrad_buf=None):
-    """`wgrad_buf`: see direct_grad -- the weight gradient is added into it and autograd receives None."""
-    return _ConvFn.apply(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums, wgrad_buf)
+def conv2d(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums=None, wgrad_buf=None, slot=None):
+    """`wgrad_buf`: see direct_grad -- the weight gradient is added into it and autograd receives None.
+    `slot`: see GradSlot -- shared with the other consumer of `x` in the same residual block."""
+    return _ConvFn.apply(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums, wgrad_buf, slot)
 
 
 STEM_K = 192
@@ -549,7 +589,7 @@ BN_RELU_MASK = True     # BatchNorm+ReLU forward keeps a bit mask of the positiv
 class _BNActFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums, acc, tracked,
-                bacc, pgrads):
+                bacc, pgrads, slot=None):
         _require_cuda(x, gamma, beta, residual)
         x = _cl(x)
         n, c, h, w = x.shape
@@ -583,6 +623,7 @@ class _BNActFn(torch.autograd.Function):
         ctx.save_for_backward(x, y if relu else None, gamma, mean, invstd, mask)
         ctx.relu, ctx.training, ctx.has_res = relu, training, residual is not None
         ctx.bacc, ctx.pgrads = bacc, pgrads
+        ctx.slot = slot if residual is not None else None
         return y
 
     @staticmethod
@@ -608,7 +649,9 @@ class _BNActFn(torch.autograd.Function):
             if ctx.bacc is not None:
                 ctx.bacc.zero_()
             raise
-        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None, None, None, None, None
+        if ctx.slot is not None and dres is not None and USE_GRAD_SLOTS:
+            ctx.slot.put(dres)       # the block input's other consumer (conv1) adds its gradient onto this (GradSlot)
+        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None, None, None, None, None, None
 
 
 def _bn_param_grads(red, c, pgrads, clear, st):
@@ -623,13 +666,13 @@ def _bn_param_grads(red, c, pgrads, clear, st):
 
 
 def bn_act(x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums=None, acc=None,
-           tracked=None, bacc=None, pgrads=None):
+           tracked=None, bacc=None, pgrads=None, slot=None):
     """`sums`: statistics already accumulated by the producing convolution's epilogue; `acc`: the layer's persistent
     fp64 accumulator [2, C] (kept zero between uses; `sums` may be it); `tracked`: num_batches_tracked, incremented by the
     finalize kernel; `bacc`: the same kind of accumulator for the backward's sums; `pgrads`: (gamma, beta) gradient buffers
     to add into (direct_grad)."""
     return _BNActFn.apply(x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums, acc, tracked,
-                          bacc, pgrads)
+                          bacc, pgrads, slot)
 
 
 class _BNReluPoolFn(torch.autograd.Function):

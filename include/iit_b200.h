@@ -175,6 +175,12 @@ int iit_conv2d_tc_supported(const iit_conv_t* d, int dtype);
 int iit_conv2d_fprop_tc(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, double* bn_sum,
                         double* bn_sqsum, void* stream);
 int iit_conv2d_dgrad_tc(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream);
+/* dx += dgrad(dy): the same kernels with their epilogue's stores replaced by 16-byte bf16 reductions (the addition is done
+ * in L2; every element receives exactly one addend, so the result is order-independent and equals a bf16 tensor addition).
+ * Where a tensor feeds two consumers -- a residual block's input goes to conv1 and to the skip path -- the second gradient
+ * is added straight onto the first: the sum autograd would otherwise make with a separate element-wise kernel
+ * (torchvision BasicBlock.forward `out += identity`, its backward). */
+int iit_conv2d_dgrad_tc_accumulate(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream);
 /* 3x3 / stride-1 / pad-1 convolutions with 64 -> 64 channels on images whose padded form fits shared memory
  * (layer1 of the ResNet) run on a "shifted-window" kernel inside the two entry points above: the padded image
  * is loaded once and every filter tap addresses it at a row offset. Same results bit for bit; this switch

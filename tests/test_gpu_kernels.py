@@ -793,3 +793,59 @@ def test_batched_filter_relayout_matches_single(ops):
         for j in range(2):
             ref = ops.filter_relayout(w, bool(j), torch.bfloat16)
             assert torch.equal(outs[2 * i + j], ref), (tuple(w.shape), j)
+
+
+def test_dgrad_accumulate_and_grad_slots():
+    """iit_conv2d_dgrad_tc_accumulate (epilogue stores replaced by 16-byte bf16 reductions) against dgrad + a tensor
+    addition, for the three kernel families (shifted-window 64->64, tiled, stride-2 parity classes / 1x1), bit for bit; and
+    the whole ResNet's gradients with the residual blocks' GradSlots on and off (no element-wise addition by autograd
+    against autograd's own)."""
+    import ctypes as C
+    from iit_b200 import _lib, ops
+    from iit_b200.nn.resnet import ResNet18LL
+    g = torch.Generator().manual_seed(3)
+
+    def desc(n, c, hw, k, ks, stride, pad):
+        d = _lib.Conv()
+        d.n, d.h, d.w, d.c, d.k, d.r, d.s, d.stride, d.pad = n, hw, hw, c, k, ks, ks, stride, pad
+        d.p = d.q = (hw + 2 * pad - ks) // stride + 1
+        return d
+
+    def ptr(t):
+        return C.c_void_p(t.data_ptr())
+
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for (n, c, hw, k, ks, stride, pad) in [(37, 64, 14, 64, 3, 1, 1), (50, 128, 7, 128, 3, 1, 1), (33, 64, 14, 128, 3, 2, 1),
+                                            (33, 64, 14, 128, 1, 2, 0), (300, 256, 4, 256, 3, 1, 1), (1200, 256, 4, 256, 3, 1, 1)]:
+        d = desc(n, c, hw, k, ks, stride, pad)
+        dy = (torch.randn(n, d.p, d.q, k, generator=g) * 0.5).to(DEV).bfloat16()
+        w = (torch.randn(c, ks, ks, k, generator=g) / (k * ks * ks) ** 0.5).to(DEV).bfloat16()     # CRSK
+        base = torch.randn(n, hw, hw, c, generator=g).to(DEV).bfloat16()
+        dx = torch.empty_like(base)
+        _lib.call("iit_conv2d_dgrad_tc", ptr(dy), ptr(w), ptr(dx), C.byref(d), st)
+        acc = base.clone()
+        _lib.call("iit_conv2d_dgrad_tc_accumulate", ptr(dy), ptr(w), ptr(acc), C.byref(d), st)
+        assert torch.equal(acc, base + dx), (n, c, hw, k, ks, stride)
+
+    grads = {}
+    x = R.synthetic_pvr(64, 5)[0].to(DEV)
+    for use in (True, False):
+        ops.USE_GRAD_SLOTS = use
+        try:
+            ll = ResNet18LL(dtype=torch.bfloat16).to(DEV)
+            ll.load_state_dict(R.resnet18_state_dict(0))
+            ll.train()
+            seen = []
+            inner = ops.call
+            ops.call = lambda name, *a: (seen.append(name), inner(name, *a))[1]
+            try:
+                ll(x).float().square().mean().backward()
+            finally:
+                ops.call = inner
+            grads[use] = {k: p.grad.detach().double().clone() for k, p in ll.named_parameters()}
+            assert (seen.count("iit_conv2d_dgrad_tc_accumulate") == 8) == use, seen.count("iit_conv2d_dgrad_tc_accumulate")
+        finally:
+            ops.USE_GRAD_SLOTS = True
+    num = sum(float((grads[True][k] - grads[False][k]).norm() ** 2) for k in grads[True])
+    den = sum(float(grads[False][k].norm() ** 2) for k in grads[False])
+    assert (num / den) ** 0.5 < 1e-3, (num / den) ** 0.5
