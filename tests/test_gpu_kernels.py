@@ -834,7 +834,10 @@ def test_dgrad_accumulate_and_grad_slots():
         try:
             ll = ResNet18LL(dtype=torch.bfloat16).to(DEV)
             ll.load_state_dict(R.resnet18_state_dict(0))
-            ll.train()
+            # running statistics: nothing in this forward / backward depends on the order of atomic additions, so the two
+            # modes must agree BIT FOR BIT on every convolution's weight gradient (batch statistics would add run-to-run
+            # rounding noise of their own, which this random-init network amplifies -- tests/test_bf16_rounding_model.py)
+            ll.eval()
             seen = []
             inner = ops.call
             ops.call = lambda name, *a: (seen.append(name), inner(name, *a))[1]
@@ -846,6 +849,8 @@ def test_dgrad_accumulate_and_grad_slots():
             assert (seen.count("iit_conv2d_dgrad_tc_accumulate") == 8) == use, seen.count("iit_conv2d_dgrad_tc_accumulate")
         finally:
             ops.USE_GRAD_SLOTS = True
-    num = sum(float((grads[True][k] - grads[False][k]).norm() ** 2) for k in grads[True])
-    den = sum(float(grads[False][k].norm() ** 2) for k in grads[False])
-    assert (num / den) ** 0.5 < 1e-3, (num / den) ** 0.5
+    for k in grads[True]:
+        if k.endswith("conv1.mod.weight") or k.endswith("conv2.mod.weight") or k.endswith("downsample.mod.0.mod.weight"):
+            assert torch.equal(grads[True][k], grads[False][k]), k
+        else:   # BatchNorm / head parameters: fp64 atomic sums, equal to rounding
+            torch.testing.assert_close(grads[True][k], grads[False][k], rtol=1e-5, atol=1e-7)
