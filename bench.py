@@ -327,6 +327,12 @@ def hbm_bytes(name, a):
         return a[4] * a[5] * 2 * _es(a[3])
     if name == "iit_lnpre_bwd":             # dy, y, rstd, dx, dtype, rows, d
         return a[5] * a[6] * 3 * _es(a[4])
+    if name == "iit_gemm_bias_act_tc":     # x, w_oi, bias, resid, y, pre_out, rows, n_in, n_out, act: operands once, results once
+        rows, n_in, n_out = a[6], a[7], a[8]
+        return 2 * (rows * n_in + n_in * n_out + rows * n_out * (1 + _ptr(a[3]) + _ptr(a[5]))) + 4 * n_out * _ptr(a[2])
+    if name == "iit_gemm_dgrad_gelu_tc":   # dy, w_io, pre, dpre, col_sum, col_sq, rows, n_in, n_out
+        rows, n_in, n_out = a[6], a[7], a[8]
+        return 2 * (rows * n_out + n_in * n_out + 2 * rows * n_in)
     if name in ("iit_ce_index_fwd", "iit_ce_index_bwd"):   # logits, dtype, rows, classes, ...: one pass over the logits (+ the gradient)
         return a[2] * a[3] * _es(a[1]) * (2 if name.endswith("bwd") else 1)
     return 0
@@ -334,7 +340,7 @@ def hbm_bytes(name, a):
 
 PVR_HBM = ["iit_bn_act_fwd", "iit_bn_act_bwd_reduce", "iit_bn_act_bwd_apply", "iit_bn_relu_maxpool_fwd",
            "iit_bn_relu_maxpool_bwd", "iit_patch_fwd"]
-IOI_HBM = ["iit_bias_act_fwd", "iit_gelu_bwd", "iit_colsum", "iit_attn_fwd", "iit_attn_bwd", "iit_lnpre_fwd", "iit_lnpre_bwd",
+IOI_HBM = ["iit_gemm_bias_act_tc", "iit_gemm_dgrad_gelu_tc", "iit_bias_act_fwd", "iit_gelu_bwd", "iit_colsum", "iit_attn_fwd", "iit_attn_bwd", "iit_lnpre_fwd", "iit_lnpre_bwd",
            "iit_ce_index_fwd", "iit_ce_index_bwd"]
 CONV_ENTRIES = ["iit_conv2d_fprop", "iit_conv2d_dgrad", "iit_conv2d_wgrad", "iit_conv2d_fprop_tc", "iit_conv2d_dgrad_tc",
                 "iit_conv2d_wgrad_tc", "iit_conv2d_wgrad_tc_accumulate", "iit_stem_conv_s2d", "iit_stem_wgrad_s2d"]

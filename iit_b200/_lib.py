@@ -61,6 +61,8 @@ SIGNATURES = {
     "iit_conv2d_fprop_tc": [_vp, _vp, _vp, _ConvP, _vp, _vp, _vp],
     "iit_conv2d_dgrad_tc": [_vp, _vp, _vp, _ConvP, _vp],
     "iit_conv2d_dgrad_tc_accumulate": [_vp, _vp, _vp, _ConvP, _vp],
+    "iit_gemm_bias_act_tc": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp],
+    "iit_gemm_dgrad_gelu_tc": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _vp],
     "iit_conv2d_wgrad_tc_scratch_bytes": [_ConvP],
     "iit_conv2d_wgrad_tc": [_vp, _vp, _vp, _ConvP, _vp, _sz, _vp],
     "iit_conv2d_wgrad_tc_accumulate": [_vp, _vp, _vp, _ConvP, _vp, _sz, _vp],

@@ -41,7 +41,30 @@ struct TcParams {
   int tiles_w, tiles_h;   // boxes per image row / column
   int tiles_n;            // image blocks
   int accumulate;         // != 0: the produced values are ADDED to what `out` holds (st_or_add_bf16x8)
+  // GEMM epilogues (the transformer's linear maps; single-CTA kernel only): applied to the fp32 accumulator before rounding
+  int epi;                        // TC_EPI_*
+  const float* bias;              // [Cout] fp32, added to every row (TC_EPI_BIAS / TC_EPI_GELU); may be null
+  const __nv_bfloat16* aux;       // laid out like `out`: the residual added (TC_EPI_BIAS, may be null) or the pre-activation
+                                  // whose GELU derivative multiplies the result (TC_EPI_GELU_BWD)
+  __nv_bfloat16* out2;            // TC_EPI_GELU: receives the pre-activation (may be null: not kept)
 };
+enum { TC_EPI_NONE = 0, TC_EPI_BIAS = 1, TC_EPI_GELU = 2, TC_EPI_GELU_BWD = 3 };
+
+// gelu_new and its derivative with tanh.approx (2^-11 relative, below bf16's 2^-9 rounding): the same arithmetic as the
+// element-wise kernels of transformer.cu
+__device__ __forceinline__ float tc_tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float tc_gelu(float x) {
+  return 0.5f * x * (1.f + tc_tanh_fast(0.7978845608028654f * (x + 0.044715f * x * x * x)));
+}
+__device__ __forceinline__ float tc_gelu_grad(float x) {
+  const float k = 0.7978845608028654f;
+  const float th = tc_tanh_fast(k * (x + 0.044715f * x * x * x));
+  return 0.5f * (1.f + th) + 0.5f * x * (1.f - th * th) * k * (1.f + 3.f * 0.044715f * x * x);
+}
 
 // Persistent: gridDim.x CTAs walk the tile list (tile = pixel box x filter block; filter block fastest so that CTAs
 // working at the same time share the pixel box through L2). The shared-memory ring runs across tile boundaries, and
@@ -233,6 +256,46 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
           __syncwarp();
           if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[acc])) : "memory");
+        }
+        if (p.epi != TC_EPI_NONE) {
+          // this lane's own row (pixel n, pp, qq), channels co0 + c .. + 31, still fp32
+          if (p.bias != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 b4 = *reinterpret_cast<const float4*>(p.bias + co0 + c + j);
+              v[j] = __float_as_uint(__uint_as_float(v[j]) + b4.x); v[j + 1] = __float_as_uint(__uint_as_float(v[j + 1]) + b4.y);
+              v[j + 2] = __float_as_uint(__uint_as_float(v[j + 2]) + b4.z); v[j + 3] = __float_as_uint(__uint_as_float(v[j + 3]) + b4.w);
+            }
+          }
+          const int64_t own = (((int64_t)n * p.OH + (pp * p.out_mul + p.out_oh)) * p.OW + (qq * p.out_mul + p.out_ow)) * p.Cout + co0 + c;
+          if (p.aux != nullptr && ok) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              const uint4 a4 = *reinterpret_cast<const uint4*>(p.aux + own + j);
+              const uint32_t w4[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+              for (int h2 = 0; h2 < 4; ++h2) {
+                const float a0 = __uint_as_float(w4[h2] << 16), a1 = __uint_as_float(w4[h2] & 0xffff0000u);
+                if (p.epi == TC_EPI_GELU_BWD) {
+                  v[j + 2 * h2] = __float_as_uint(__uint_as_float(v[j + 2 * h2]) * tc_gelu_grad(a0));
+                  v[j + 2 * h2 + 1] = __float_as_uint(__uint_as_float(v[j + 2 * h2 + 1]) * tc_gelu_grad(a1));
+                } else {
+                  v[j + 2 * h2] = __float_as_uint(__uint_as_float(v[j + 2 * h2]) + a0);
+                  v[j + 2 * h2 + 1] = __float_as_uint(__uint_as_float(v[j + 2 * h2 + 1]) + a1);
+                }
+              }
+            }
+          }
+          if (p.epi == TC_EPI_GELU) {
+            if (p.out2 != nullptr) {     // the pre-activation, kept for the backward
+              __nv_bfloat16* sdst2[4];
+#pragma unroll
+              for (int i = 0; i < 4; ++i) sdst2[i] = sdst[i] != nullptr ? p.out2 + (sdst[i] - out) : nullptr;
+              tc_store_chunk(v, my_stage, lane, sub, piece, sdst2, c, ok);
+            }
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(tc_gelu(__uint_as_float(v[j])));
+          }
         }
         // store (64 contiguous bytes per pixel) and, for the BatchNorm that follows, per-channel sums of the values as stored
         tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c, ok, bn_sum != nullptr ? s_stat + c : nullptr, s_stat + BN + c,
@@ -611,7 +674,7 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
   const int64_t mtiles = (int64_t)tp.tiles_w * tp.tiles_h * tp.tiles_n;
   // CTA pairs: whenever every SM gets a tile; with fewer boxes (layer4 at batch 4096: 128) only for long reductions, where
   // the halved filter traffic outweighs the pair's start-up (measured: +3 % on 4608-deep, -8 % on 256-deep reductions)
-  if (g_pair_mode && tp.Cout % 256 == 0 && tp.ntaps > 0 &&
+  if (g_pair_mode && tp.epi == TC_EPI_NONE && tp.Cout % 256 == 0 && tp.ntaps > 0 &&
       (mtiles >= kNumSMs || (mtiles >= kNumSMs / 2 && tp.ntaps * tp.Cin >= 2304))) {
     // 256-filter tiles unless mode 3 asks for 128 (measured: half-width tiles fill the last wave better, 7 waves of 74
     // clusters instead of 4 on layer3, but pay the pixel box twice and end up slower: 76.6 vs 70.5 us)
@@ -649,10 +712,10 @@ static int check_tc_ptrs(const void* a, const void* b, const void* c, const char
 
 // y[n,p,q,k] = sum_{r,s,c} x[n, p*stride - pad + r, q*stride - pad + s, c] * w[k,r,s,c]
 static int conv_tc_fprop(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, cudaStream_t st, double* bn_sum,
-                         double* bn_sq) {
-  const char* name = "iit_conv2d_fprop_tc";
+                         double* bn_sq, const TcParams* epi = nullptr, const char* name = "iit_conv2d_fprop_tc") {
   if (check_tc_ptrs(x, w_krsc, y, name)) return 1;
   TcParams tp{};
+  if (epi != nullptr) { tp.epi = epi->epi; tp.bias = epi->bias; tp.aux = epi->aux; tp.out2 = epi->out2; }
   tp.N = d->n; tp.P = d->p; tp.Q = d->q; tp.OH = d->p; tp.OW = d->q;
   tp.out_mul = 1; tp.out_oh = 0; tp.out_ow = 0; tp.in_mul = d->stride;
   tp.Cin = d->c; tp.Cout = d->k;
@@ -669,8 +732,9 @@ static int conv_tc_fprop(const void* x, const void* w_krsc, void* y, const iit_c
 // For stride 2 the output splits into four parity classes, each a stride-1 gather of dy with its own taps.
 // `accumulate`: dx += the result (one reduction per element; classes no tap reaches then need no launch and no memset).
 static int conv_tc_dgrad(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, cudaStream_t st,
-                         bool accumulate = false) {
-  const char* name = accumulate ? "iit_conv2d_dgrad_tc_accumulate" : "iit_conv2d_dgrad_tc";
+                         bool accumulate = false, const TcParams* epi = nullptr, double* col_sum = nullptr,
+                         double* col_sq = nullptr, const char* name_override = nullptr) {
+  const char* name = name_override ? name_override : accumulate ? "iit_conv2d_dgrad_tc_accumulate" : "iit_conv2d_dgrad_tc";
   if (check_tc_ptrs(dy, w_crsk, dx, name)) return 1;
   const int st_ = d->stride;
   // Parity classes of dx that no filter tap reaches (three of the four for a 1x1 stride-2 convolution) are zeros: one memset
@@ -694,6 +758,7 @@ static int conv_tc_dgrad(const void* dy, const void* w_crsk, void* dx, const iit
       tp.out_mul = st_; tp.out_oh = a; tp.out_ow = b; tp.in_mul = 1;
       tp.Cin = d->k; tp.Cout = d->c;
       tp.accumulate = accumulate ? 1 : 0;
+      if (epi != nullptr) { tp.epi = epi->epi; tp.bias = epi->bias; tp.aux = epi->aux; tp.out2 = epi->out2; }
       int nt = 0;
       for (int r = 0; r < d->r; ++r) {
         if ((a + d->pad - r) % st_ != 0) continue;
@@ -707,7 +772,7 @@ static int conv_tc_dgrad(const void* dy, const void* w_crsk, void* dx, const iit
       }
       tp.ntaps = nt;
       if (nt == 0) continue;     // zeroed above
-      int rc = conv_tc_launch(dy, d->k, d->q, d->p, w_crsk, d->r * d->s * d->k, dx, tp, st, name);
+      int rc = conv_tc_launch(dy, d->k, d->q, d->p, w_crsk, d->r * d->s * d->k, dx, tp, st, name, col_sum, col_sq);
       if (rc) return rc;
     }
   return 0;
@@ -1049,6 +1114,43 @@ extern "C" int iit_conv2d_dgrad_tc(const void* dy, const void* w_crsk, void* dx,
 
 extern "C" int iit_conv2d_dgrad_tc_accumulate(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream) {
   return dgrad_tc_entry(dy, w_crsk, dx, d, stream, true, "iit_conv2d_dgrad_tc_accumulate");
+}
+
+// ---- the transformer's linear maps with their element-wise neighbours in the GEMM epilogue ------------------------------
+static void gemm_desc(iit_conv_t* d, int64_t rows, int n_in, int n_out) {
+  d->n = (int)rows; d->h = 1; d->w = 1; d->c = n_in; d->k = n_out; d->r = 1; d->s = 1; d->stride = 1; d->pad = 0; d->p = 1; d->q = 1;
+}
+
+extern "C" int iit_gemm_bias_act_tc(const void* x, const void* w_oi, const float* bias, const void* resid, void* y, void* pre_out,
+                                    int64_t rows, int n_in, int n_out, int act, void* stream) {
+  const char* name = "iit_gemm_bias_act_tc";
+  IIT_REQUIRE(x && w_oi && y && rows > 0 && rows < (1ll << 31), "%s: bad arguments", name);
+  IIT_REQUIRE(n_in % 64 == 0 && n_out % 64 == 0, "%s: widths must be multiples of 64 (got %d -> %d)", name, n_in, n_out);
+  IIT_REQUIRE(act == 0 || act == 1, "%s: act must be 0 (identity) or 1 (gelu_new)", name);
+  IIT_REQUIRE(!(act == 1 && resid != nullptr), "%s: a residual cannot be combined with the activation", name);
+  IIT_REQUIRE(((reinterpret_cast<uintptr_t>(bias) | reinterpret_cast<uintptr_t>(resid) | reinterpret_cast<uintptr_t>(pre_out)) & 15) == 0,
+              "%s: pointers must be 16-byte aligned", name);
+  iit_conv_t d;
+  gemm_desc(&d, rows, n_in, n_out);
+  TcParams e{};
+  e.epi = act == 1 ? TC_EPI_GELU : TC_EPI_BIAS;
+  e.bias = bias; e.aux = (const __nv_bfloat16*)resid; e.out2 = (__nv_bfloat16*)pre_out;
+  return conv_tc_fprop(x, w_oi, y, &d, as_stream(stream), nullptr, nullptr, &e, name);
+}
+
+extern "C" int iit_gemm_dgrad_gelu_tc(const void* dy, const void* w_io, const void* pre, void* dpre, double* col_sum,
+                                      double* col_sq, int64_t rows, int n_in, int n_out, void* stream) {
+  const char* name = "iit_gemm_dgrad_gelu_tc";
+  IIT_REQUIRE(dy && w_io && pre && dpre && rows > 0 && rows < (1ll << 31), "%s: bad arguments", name);
+  IIT_REQUIRE(n_in % 64 == 0 && n_out % 64 == 0, "%s: widths must be multiples of 64 (got %d -> %d)", name, n_in, n_out);
+  IIT_REQUIRE((col_sum == nullptr) == (col_sq == nullptr), "%s: col_sum and col_sq come together", name);
+  IIT_REQUIRE((reinterpret_cast<uintptr_t>(pre) & 15) == 0, "%s: pointers must be 16-byte aligned", name);
+  iit_conv_t d;
+  gemm_desc(&d, rows, n_in, n_out);
+  TcParams e{};
+  e.epi = TC_EPI_GELU_BWD;
+  e.aux = (const __nv_bfloat16*)pre;
+  return conv_tc_dgrad(dy, w_io, dpre, &d, as_stream(stream), false, &e, col_sum, col_sq, name);
 }
 
 extern "C" size_t iit_conv2d_wgrad_tc_scratch_bytes(const iit_conv_t* d) {

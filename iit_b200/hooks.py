@@ -50,6 +50,12 @@ class HookPoint(nn.Module):
     def has_hooks(self) -> bool:
         return bool(self._fwd or self._bwd)
 
+    def only_patch_hooks(self) -> bool:
+        """True when nothing but interchange patches (base_model_pair.make_ll_ablation_hook marks them `_iit_patch`) is
+        attached: their effect on the gradient is to zero a box, which commutes with an element-wise factor, so a model may
+        keep a fused backward across this hook point."""
+        return not self._bwd and all(getattr(fn, "_iit_patch", False) for fn, _, _ in self._fwd)
+
     def clear_context(self):
         self.ctx = {}
 

@@ -211,13 +211,44 @@ class HookedTransformerLL(HookedRootModule):
             sh = self._shadow
         ops.filter_relayout_batched(sh["table"], sh["entries"], sh["max"])
         sh["versions"] = [p._version for p in sh["params"]]
+        # the unembedding bias padded to the GEMM's width (fp32: the epilogue adds it to the accumulator)
+        V = self.cfg.d_vocab_out
+        bu = sh.get("b_U_pad")
+        if bu is None:
+            bu = sh["b_U_pad"] = torch.zeros(V + (-V) % 64, dtype=torch.float32, device=self.unembed.b_U.device)
+        with torch.no_grad():
+            bu[:V].copy_(self.unembed.b_U)
+        sh["b_U_version"] = self.unembed.b_U._version
 
     def _filter_shadow_stale(self):
         if not self._shadow_usable():
             return False
         sh = getattr(self, "_shadow", None)
         return (sh is None or sh["versions"] != [p._version for p in sh["params"]]
-                or sh["ptrs"] != [p.data_ptr() for p in sh["params"]])
+                or sh["ptrs"] != [p.data_ptr() for p in sh["params"]] or sh.get("b_U_version") != self.unembed.b_U._version)
+
+    # ---- fused epilogues (bf16 prepared path): bias / residual / gelu_new in the GEMM, GELU backward in the output map's dgrad
+    def _qkv_bias(self, a):
+        """b_Q | b_K | b_V as one fp32 [3*H*dh] vector: a view when the three parameters are adjacent in memory (they are
+        under FlatAdam, whose flat buffer follows parameter order), a concatenation otherwise."""
+        n = a.b_Q.numel()
+        if (a.b_Q.is_contiguous() and a.b_K.data_ptr() == a.b_Q.data_ptr() + 4 * n and a.b_V.data_ptr() == a.b_Q.data_ptr() + 8 * n
+                and a.b_Q.untyped_storage().data_ptr() == a.b_V.untyped_storage().data_ptr()):
+            return torch.as_strided(a.b_Q.detach(), (3 * n,), (1,), a.b_Q.storage_offset())
+        return torch.cat([b.detach().reshape(-1) for b in (a.b_Q, a.b_K, a.b_V)])
+
+    def _epi(self, key, x, bias, bias_specs, bias_params, resid=None, act=0, link_out=None, link_in=None):
+        oi, io, st = self._shadow["bufs"][key]
+        return ops.linear_epi(x, oi, io, st["n_in"], st["n_out_pad"], st["specs"], st["params"], bias=bias, bias_specs=bias_specs,
+                              bias_params=bias_params, resid=resid, act=act, link_out=link_out, link_in=link_in)
+
+    def _mlp_link(self, li):
+        sites = self.__dict__.setdefault("_mlp_sites", {})
+        ent = sites.get(li)
+        dev = self.unembed.W_U.device
+        if ent is None or ent[0].device != dev:
+            ent = sites[li] = (torch.zeros((2, self.cfg.d_mlp), dtype=torch.float64, device=dev), {"dirty": False})
+        return ops.GeluLink(ent[0], ent[1])
 
     def _linear(self, key, x):
         """x @ W of site `key` from the prepared operands, or None when they are not in use."""
@@ -252,6 +283,22 @@ class HookedTransformerLL(HookedRootModule):
             a, m = blk.attn, blk.mlp
             resid = blk.hook_resid_pre(resid.view(B, S, D)).reshape(T, D)
             x = ops.lnpre(resid, c.eps)
+            if use_shadow and not (blk.hook_attn_out.has_hooks() or blk.hook_mlp_out.has_hooks() or m.hook_pre.has_hooks()):
+                # every element-wise neighbour of the four linear maps runs in their GEMM epilogues
+                li = len(blocks_seen); blocks_seen.append(blk)
+                hd = H * dh
+                qkv = self._epi(("qkv", li), x, self._qkv_bias(a), tuple(((H, dh), (dh, 1), j * hd) for j in range(3)),
+                                (a.b_Q, a.b_K, a.b_V)).view(B, S, 3, H, dh)
+                z = a.hook_z(ops.attention(qkv))
+                resid = self._epi(("o", li), z.reshape(T, hd), a.b_O.detach(), (((D,), (1,), 0),), (a.b_O,), resid=resid)
+                resid = blk.hook_resid_mid(resid.view(B, S, D)).reshape(T, D)
+                x = ops.lnpre(resid, c.eps)
+                link = self._mlp_link(li) if (torch.is_grad_enabled() and m.hook_post.only_patch_hooks()) else None
+                post = self._epi(("in", li), x, m.b_in.detach(), (((c.d_mlp,), (1,), 0),), (m.b_in,), act=1, link_out=link)
+                post = m.hook_post(post.view(B, S, c.d_mlp)).reshape(T, -1)
+                resid = self._epi(("out", li), post, m.b_out.detach(), (((D,), (1,), 0),), (m.b_out,), resid=resid, link_in=link)
+                resid = blk.hook_resid_post(resid.view(B, S, D)).reshape(T, D)
+                continue
             # fused QKV projection: [D, (3,H,dh)] assembled from the per-head parameters (tiny; autograd routes grads)
             b_qkv = torch.cat([b.reshape(-1) for b in (a.b_Q, a.b_K, a.b_V)])
             if use_shadow:
@@ -287,9 +334,8 @@ class HookedTransformerLL(HookedRootModule):
         W_U, b_U, V = self.unembed.W_U, self.unembed.b_U, c.d_vocab_out
         pad = (-V) % 64
         if use_shadow:
-            b_U = torch.nn.functional.pad(b_U, (0, pad)) if pad else b_U
             xin = resid.view(B, S, D)[:, -1, :].contiguous() if last_pos_only else resid
-            logits = ops.bias_add(self._linear(("unembed",), ops.lnpre(xin, c.eps)), b_U)[:, :V]
+            logits = self._epi(("unembed",), ops.lnpre(xin, c.eps), self._shadow["b_U_pad"], (((V,), (1,), 0),), (b_U,))[:, :V]
             return logits if last_pos_only else logits.reshape(B, S, -1)
         if pad and self.act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES:
             # the tensor-core GEMMs want widths that are multiples of 64: unembed into V + pad columns (zero weights and

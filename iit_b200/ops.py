@@ -1008,6 +1008,124 @@ def linear_prepared(x2d, w_oi, w_io, n_in, n_out_pad, specs, params):
     return _LinearPreparedFn.apply(x2d, w_oi, w_io, n_in, n_out_pad, specs, *params)
 
 
+class GeluLink:
+    """Couples the MLP's two linear maps across `mlp.hook_post` so that the GELU's backward runs in a GEMM epilogue:
+    the input map (`act=1`) leaves its pre-activation here; the output map's backward then computes
+    `dpre = (dy @ W_out^T) * gelu'(pre)` in one kernel (iit_gemm_dgrad_gelu_tc, with the column sums of dpre = the
+    input bias's gradient), hands it on as the gradient of `post`, and marks the link; the input map's backward sees the
+    mark (same backward pass) and takes the gradient as dpre instead of applying gelu' itself. Anything between the two
+    that only zeroes parts of the gradient (a patch hook's backward) commutes with that. `sums` is the site's persistent
+    fp64 [2, d_mlp] accumulator (zero between uses)."""
+    __slots__ = ("pre", "sums", "state", "_task")
+
+    def __init__(self, sums: torch.Tensor, state: dict):
+        """One link per forward; `sums` and `state` ({"dirty": bool}) belong to the site and persist."""
+        self.pre, self.sums, self.state, self._task = None, sums, state, -1
+
+    def begin_accumulate(self):
+        if self.state.get("dirty"):      # sums left behind by a backward whose gradient never reached the input map
+            self.sums.zero_()
+        self.state["dirty"] = True
+
+    def mark(self):
+        self._task = GradSlot._current_task()
+
+    def marked(self) -> bool:
+        t = GradSlot._current_task()
+        ok = t != -1 and t == self._task
+        self._task = -1
+        return ok
+
+    def consumed(self):
+        self.state["dirty"] = False
+
+
+class _LinearEpiFn(torch.autograd.Function):
+    """y = act(x @ W + bias (+ resid)) with bias / residual / gelu_new applied to the fp32 accumulator in the GEMM epilogue
+    (iit_gemm_bias_act_tc), from the model's PREPARED bf16 operands (see _LinearPreparedFn). `bias`: fp32 [n_out_pad] or
+    None, its gradient (the column sums of dy) is returned for each of `bias_params` as the view its spec names.
+    `link_out`: this is the MLP's input map (act must be 1); `link_in`: this map consumes that activation (GeluLink)."""
+
+    @staticmethod
+    def forward(ctx, x, w_oi, w_io, n_in, n_out_pad, specs, bias, bias_specs, resid, act, link_out, link_in, n_w, *params):
+        _require_cuda(x, w_oi, w_io, bias, resid)
+        x = x.contiguous()
+        T = x.shape[0]
+        if x.dtype != torch.bfloat16 or n_in % 64 or n_out_pad % 64:
+            raise RuntimeError("linear_epi: bf16 activations and widths that are multiples of 64 only")
+        y = torch.empty((T, n_out_pad), dtype=x.dtype, device=x.device)
+        want_grad = any(ctx.needs_input_grad)
+        pre = torch.empty_like(y) if (act == 1 and want_grad) else None
+        if resid is not None:
+            resid = resid.contiguous()
+        call("iit_gemm_bias_act_tc", _p(x), _p(w_oi), _p(bias), _p(resid), _p(y), _p(pre), T, n_in, n_out_pad, int(act), _stream())
+        if link_out is not None:
+            link_out.pre = pre
+        ctx.save_for_backward(x, w_io, pre)
+        ctx.geom = (T, n_in, n_out_pad)
+        ctx.specs, ctx.bias_specs, ctx.act, ctx.has_res = specs, bias_specs, act, resid is not None
+        ctx.link_out, ctx.link_in, ctx.n_w = link_out, link_in, n_w
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w_io, pre = ctx.saved_tensors
+        T, n_in, n_out = ctx.geom
+        dy = dy.contiguous()
+        st = _stream()
+        d = Conv()
+        d.n, d.h, d.w, d.c, d.k, d.r, d.s, d.stride, d.pad, d.p, d.q = T, 1, 1, n_in, n_out, 1, 1, 1, 0, 1, 1
+        db = None
+        want_db = ctx.bias_specs is not None and any(ctx.needs_input_grad[13 + ctx.n_w:])
+        if ctx.act == 1:
+            link = ctx.link_out
+            if link is not None and link.marked():
+                g = dy                                       # already dpre: the output map's backward applied gelu'
+                if want_db:
+                    db = torch.empty(n_out, dtype=torch.float32, device=dy.device)
+                    scratch = torch.empty(n_out, dtype=torch.float32, device=dy.device)
+                    call("iit_bn_param_grads", _p(link.sums), n_out, _p(db), _p(scratch), 0, 1, st)   # fp64 sums -> fp32, cleared
+                else:
+                    link.sums.zero_()
+                link.consumed()
+            else:
+                g = torch.empty_like(dy)
+                call("iit_gelu_bwd", _p(dy), _p(pre), _p(g), _dt(dy), dy.numel(), st)
+                if want_db:
+                    db = colsum(g)
+        else:
+            g = dy
+            if want_db:
+                db = colsum(g)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            lin = ctx.link_in
+            if lin is not None and lin.pre is not None and lin.pre.shape == x.shape:
+                lin.begin_accumulate()
+                call("iit_gemm_dgrad_gelu_tc", _p(g), _p(w_io), _p(lin.pre), _p(dx), _p(lin.sums[0]), _p(lin.sums[1]), T, n_in, n_out, st)
+                lin.mark()
+            else:
+                call("iit_conv2d_dgrad_tc", _p(g), _p(w_io), _p(dx), C.byref(d), st)
+        grads = [None] * ctx.n_w
+        if any(ctx.needs_input_grad[13:13 + ctx.n_w]):
+            dwb = torch.empty(n_out * n_in, dtype=torch.float32, device=x.device)   # [out_pad][in]
+            need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
+            scratch = torch.empty(need, dtype=torch.uint8, device=x.device)
+            call("iit_conv2d_wgrad_tc", _p(g), _p(x), _p(dwb), C.byref(d), _p(scratch), need, st)
+            grads = [torch.as_strided(dwb, size, stride, offset) for size, stride, offset in ctx.specs]
+        bgrads = []
+        if ctx.bias_specs is not None:
+            bgrads = [torch.as_strided(db, size, stride, offset) if db is not None else None for size, stride, offset in ctx.bias_specs]
+        return (dx, None, None, None, None, None, None, None, (g if ctx.has_res else None), None, None, None, None, *grads, *bgrads)
+
+
+def linear_epi(x2d, w_oi, w_io, n_in, n_out_pad, specs, params, bias=None, bias_specs=None, bias_params=(), resid=None, act=0,
+               link_out=None, link_in=None):
+    return _LinearEpiFn.apply(x2d, w_oi, w_io, n_in, n_out_pad, specs, bias, bias_specs, resid, act, link_out, link_in,
+                              len(params), *params, *bias_params)
+
+
 def colsum(x2d: torch.Tensor) -> torch.Tensor:
     out = torch.zeros(x2d.shape[1], dtype=torch.float32, device=x2d.device)
     call("iit_colsum", _p(x2d), _dt(x2d), _p(out), x2d.shape[0], x2d.shape[1], _stream())

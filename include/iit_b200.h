@@ -181,6 +181,21 @@ int iit_conv2d_dgrad_tc(const void* dy, const void* w_crsk, void* dx, const iit_
  * is added straight onto the first: the sum autograd would otherwise make with a separate element-wise kernel
  * (torchvision BasicBlock.forward `out += identity`, its backward). */
 int iit_conv2d_dgrad_tc_accumulate(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream);
+/* The transformer's linear maps (transformer_lens HookedTransformer: attention projections, MLP, unembedding; reference
+ * train_ioi.py:30-34) on the same tensor-core GEMM with their element-wise neighbours applied to the fp32 accumulator in the
+ * epilogue, before the one rounding to bf16:
+ *   iit_gemm_bias_act_tc:   y[rows, n_out] = act(x[rows, n_in] @ w_oi[n_out, n_in]^T + bias (+ resid)), act 0 identity /
+ *                           1 gelu_new. With act 1, pre_out (may be NULL) receives the pre-activation for the backward
+ *                           (mlp.hook_pre's value); resid must then be NULL. bias fp32 [n_out] (may be NULL).
+ *   iit_gemm_dgrad_gelu_tc: dpre[rows, n_in] = (dy[rows, n_out] @ w_io[n_in, n_out]^T) * gelu_new'(pre[rows, n_in]) -- the
+ *                           input gradient of the MLP's output map already taken through the activation; col_sum / col_sq
+ *                           (fp64 [n_in], both or neither; ADDED to) receive the column sums of dpre (= the gradient of
+ *                           the MLP's input bias) and of its squares (a by-product of the shared epilogue).
+ * Widths are multiples of 64, tensors bf16, 16-byte aligned. */
+int iit_gemm_bias_act_tc(const void* x, const void* w_oi, const float* bias, const void* resid, void* y, void* pre_out,
+                         int64_t rows, int n_in, int n_out, int act, void* stream);
+int iit_gemm_dgrad_gelu_tc(const void* dy, const void* w_io, const void* pre, void* dpre, double* col_sum, double* col_sq,
+                           int64_t rows, int n_in, int n_out, void* stream);
 /* 3x3 / stride-1 / pad-1 convolutions with 64 -> 64 channels on images whose padded form fits shared memory
  * (layer1 of the ResNet) run on a "shifted-window" kernel inside the two entry points above: the padded image
  * is loaded once and every filter tap addresses it at a row offset. Same results bit for bit; this switch

@@ -292,8 +292,9 @@ def test_ioi_cuda_graph_step_equals_eager_step():
 
 def test_prepared_gemm_operands_equal_per_gemm_copies_and_follow_weight_edits():
     """bf16 path: the persistent [out][in] / [in][out] copies of every linear map (one batched re-layout launch; fused QKV
-    assembled from the per-head parameters, unembedding padded to 64 columns) give the same logits and parameter gradients,
-    bit for bit, as the per-GEMM copies, and are rebuilt when a weight changes outside the optimizer."""
+    assembled from the per-head parameters, unembedding padded to 64 columns) with the fused GEMM epilogues give the same
+    logits and parameter gradients as the per-GEMM copies with separate element-wise kernels (to bf16 rounding), and are
+    rebuilt when a weight changes outside the optimizer."""
     from iit_b200 import ops
     from iit_b200.tasks.ioi import make_ll_model
     x = batch(7)[0].to(DEV)
@@ -312,10 +313,16 @@ def test_prepared_gemm_operands_equal_per_gemm_copies_and_follow_weight_edits():
         out.float().square().mean().backward()
         return out.detach(), {n: p.grad.clone() for n, p in ll.named_parameters() if p.grad is not None}
 
+    def close(u, v, what):
+        # the prepared path applies bias / residual / GELU to the fp32 accumulator in the GEMM epilogue, the per-GEMM path
+        # rounds the GEMM result to bf16 first: equal to bf16 rounding, not bit for bit
+        err = float((u.float() - v.float()).norm() / (v.float().norm() + 1e-30))
+        assert err < 2e-2, (what, err)
+
     for scale in (None, 1.5):
         (a, ga), (b, gb) = run(True, scale), run(False, scale)
-        assert torch.equal(a, b)
+        close(a, b, "logits")
         assert ga.keys() == gb.keys()
         for n in ga:
-            assert torch.equal(ga[n], gb[n]), n
+            close(ga[n], gb[n], n)
     assert not torch.equal(run(True, 1.5)[0], run(True)[0])

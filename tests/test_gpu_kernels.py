@@ -854,3 +854,45 @@ def test_dgrad_accumulate_and_grad_slots():
             assert torch.equal(grads[True][k], grads[False][k]), k
         else:   # BatchNorm / head parameters: fp64 atomic sums, equal to rounding
             torch.testing.assert_close(grads[True][k], grads[False][k], rtol=1e-5, atol=1e-7)
+
+
+def test_gemm_epilogues_match_separate_kernels():
+    """iit_gemm_bias_act_tc / iit_gemm_dgrad_gelu_tc against torch fp32 on the same bf16 operands: bias, residual and
+    gelu_new applied to the fp32 accumulator (one rounding), pre-activation output, GELU backward with column sums."""
+    import ctypes as C
+    from iit_b200 import _lib
+    g = torch.Generator().manual_seed(11)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def ptr(t):
+        return None if t is None else C.c_void_p(t.data_ptr())
+
+    for rows, n_in, n_out in [(300, 64, 192), (1000, 64, 3072), (777, 3072, 64), (130, 64, 64)]:
+        x = torch.randn(rows, n_in, generator=g).to(DEV).bfloat16()
+        w = (torch.randn(n_out, n_in, generator=g) / n_in ** 0.5).to(DEV).bfloat16()          # [out][in]
+        bias = torch.randn(n_out, generator=g).to(DEV)
+        resid = torch.randn(rows, n_out, generator=g).to(DEV).bfloat16()
+        lin = x.float() @ w.float().t()
+        # bias + residual
+        y = torch.empty(rows, n_out, device=DEV, dtype=torch.bfloat16)
+        _lib.call("iit_gemm_bias_act_tc", ptr(x), ptr(w), ptr(bias), ptr(resid), ptr(y), None, rows, n_in, n_out, 0, st)
+        torch.testing.assert_close(y.float(), lin + bias + resid.float(), rtol=1e-2, atol=2e-2)
+        # bias only, no bias
+        _lib.call("iit_gemm_bias_act_tc", ptr(x), ptr(w), None, None, ptr(y), None, rows, n_in, n_out, 0, st)
+        torch.testing.assert_close(y.float(), lin, rtol=1e-2, atol=2e-2)
+        # bias + gelu_new with the pre-activation kept
+        pre = torch.empty_like(y)
+        _lib.call("iit_gemm_bias_act_tc", ptr(x), ptr(w), ptr(bias), None, ptr(y), ptr(pre), rows, n_in, n_out, 1, st)
+        torch.testing.assert_close(pre.float(), lin + bias, rtol=1e-2, atol=2e-2)
+        torch.testing.assert_close(y.float(), R.gelu_new(lin + bias), rtol=1e-2, atol=2e-2)
+        # GELU backward in the dgrad epilogue: dpre[rows, n_in] = (dy[rows, n_out] @ w_io[n_in, n_out]^T) * gelu'(pre_in)
+        dy = (torch.randn(rows, n_out, generator=g) / n_out ** 0.5).to(DEV).bfloat16()
+        w_io = w.t().contiguous()                                                            # [in][out]
+        pre_in = torch.randn(rows, n_in, generator=g).to(DEV).bfloat16()
+        dpre = torch.empty(rows, n_in, device=DEV, dtype=torch.bfloat16)
+        sums = torch.zeros(2, n_in, device=DEV, dtype=torch.float64)
+        _lib.call("iit_gemm_dgrad_gelu_tc", ptr(dy), ptr(w_io), ptr(pre_in), ptr(dpre), ptr(sums[0]), ptr(sums[1]), rows, n_in, n_out, st)
+        p32 = pre_in.float().requires_grad_(True)
+        R.gelu_new(p32).backward(dy.float() @ w.float())
+        torch.testing.assert_close(dpre.float(), p32.grad, rtol=2e-2, atol=2e-2)
+        torch.testing.assert_close(sums[0].float(), dpre.float().sum(0), rtol=1e-3, atol=1e-2)
