@@ -317,6 +317,8 @@ def hbm_bytes(name, a):
         return a[6] * a[7] * _es(a[5]) * (2 + _ptr(a[2]) + _ptr(a[3]))
     if name == "iit_gelu_bwd":              # dpost, pre, dpre, dtype, n
         return 3 * a[4] * _es(a[3])
+    if name == "iit_gelu_bwd_bias_colsum":  # dpost, h, bias, dpre, colsum, rows, n (bf16)
+        return 3 * a[5] * a[6] * 2
     if name == "iit_colsum":                # x, dtype, out, rows, n
         return a[3] * a[4] * _es(a[1])
     if name == "iit_attn_fwd":              # qkv, z, dtype, batch, seq, heads, d_head
@@ -340,7 +342,7 @@ def hbm_bytes(name, a):
 
 PVR_HBM = ["iit_bn_act_fwd", "iit_bn_act_bwd_reduce", "iit_bn_act_bwd_apply", "iit_bn_relu_maxpool_fwd",
            "iit_bn_relu_maxpool_bwd", "iit_patch_fwd"]
-IOI_HBM = ["iit_gemm_bias_act_tc", "iit_gemm_dgrad_gelu_tc", "iit_bias_act_fwd", "iit_gelu_bwd", "iit_colsum", "iit_attn_fwd", "iit_attn_bwd", "iit_lnpre_fwd", "iit_lnpre_bwd",
+IOI_HBM = ["iit_gemm_bias_act_tc", "iit_gemm_dgrad_gelu_tc", "iit_gelu_bwd_bias_colsum", "iit_bias_act_fwd", "iit_gelu_bwd", "iit_colsum", "iit_attn_fwd", "iit_attn_bwd", "iit_lnpre_fwd", "iit_lnpre_bwd",
            "iit_ce_index_fwd", "iit_ce_index_bwd"]
 CONV_ENTRIES = ["iit_conv2d_fprop", "iit_conv2d_dgrad", "iit_conv2d_wgrad", "iit_conv2d_fprop_tc", "iit_conv2d_dgrad_tc",
                 "iit_conv2d_wgrad_tc", "iit_conv2d_wgrad_tc_accumulate", "iit_stem_conv_s2d", "iit_stem_wgrad_s2d"]
@@ -378,7 +380,13 @@ class KernelTimer:
             inner(name, *a)
             e.record()
             if name in self.hbm:
-                self.records.append((name, s, e, hbm_bytes(name, a), "hbm", None, ()))
+                layer = None
+                if name == "iit_gemm_bias_act_tc":
+                    layer = (f"gemm [{a[6]} x {a[7]}] x [{a[7]} x {a[8]}] + bias{' + residual' if _ptr(a[3]) else ''}"
+                             f"{' + gelu_new' if a[9] else ''}{' (pre kept)' if _ptr(a[5]) else ''}")
+                elif name == "iit_gemm_dgrad_gelu_tc":
+                    layer = f"gemm [{a[6]} x {a[8]}] x [{a[8]} x {a[7]}] * gelu'(pre) + column sums"
+                self.records.append((name, s, e, hbm_bytes(name, a), "hbm", layer, ()))
                 return
             after = _lib.kernel_variant_counts()
             variants = tuple(k for k in after if after[k] > before[k])

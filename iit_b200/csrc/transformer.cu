@@ -514,6 +514,82 @@ extern "C" int iit_gelu_bwd(const void* dpost, const void* pre, void* dpre, int 
   IIT_LAUNCH_CHECK("iit_gelu_bwd");
   return 0;
 }
+// dpre = dpost * gelu_new'(h + bias) and, in the same pass, colsum[c] += sum_r dpre[r, c] (the input bias's gradient): the
+// geometry of colsum_bf16x8_kernel (a thread owns 8 columns; 16 column packs x 16 row lanes per block; two rows in flight).
+// `h` is the MLP input map's raw GEMM result: the pre-activation h + bias is never stored.
+__global__ void __launch_bounds__(256) gelu_bwd_bias_colsum_kernel(const __nv_bfloat16* __restrict__ dpost,
+                                                                   const __nv_bfloat16* __restrict__ h, const float* __restrict__ bias,
+                                                                   __nv_bfloat16* __restrict__ dpre, float* __restrict__ colsum,
+                                                                   int64_t rows, int N) {
+  __shared__ float s[16][16 * 8 + 1];
+  const int cp = threadIdx.x & 15, ry = threadIdx.x >> 4;
+  const int c = (blockIdx.x * 16 + cp) * 8;
+  float acc[8], b[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { acc[j] = 0.f; b[j] = 0.f; }
+  if (c < N) {
+    if (bias != nullptr) {
+      const float4 b0 = *reinterpret_cast<const float4*>(bias + c), b1 = *reinterpret_cast<const float4*>(bias + c + 4);
+      b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+    }
+    const int64_t step = (int64_t)gridDim.y * 16;
+    auto one = [&](const uint4& tg, const uint4& th, int64_t r) {
+      float g[8], x[8];
+      unpack_bf16x8(tg, g);
+      unpack_bf16x8(th, x);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float k = 0.7978845608028654f, v = x[j] + b[j];
+        const float t = tanh_fast(k * (v + 0.044715f * v * v * v));
+        g[j] *= 0.5f * (1.f + t) + 0.5f * v * (1.f - t * t) * k * (1.f + 3.f * 0.044715f * v * v);
+      }
+      const uint4 o = pack_bf16x8(g);
+      *reinterpret_cast<uint4*>(dpre + r * N + c) = o;
+      unpack_bf16x8(o, g);          // the sums are of the values as stored
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += g[j];
+    };
+    int64_t r = (int64_t)blockIdx.y * 16 + ry;
+    for (; r + step < rows; r += 2 * step) {
+      const uint4 g0 = *reinterpret_cast<const uint4*>(dpost + r * N + c), h0 = *reinterpret_cast<const uint4*>(h + r * N + c);
+      const uint4 g1 = *reinterpret_cast<const uint4*>(dpost + (r + step) * N + c), h1 = *reinterpret_cast<const uint4*>(h + (r + step) * N + c);
+      one(g0, h0, r);
+      one(g1, h1, r + step);
+    }
+    for (; r < rows; r += step)
+      one(*reinterpret_cast<const uint4*>(dpost + r * N + c), *reinterpret_cast<const uint4*>(h + r * N + c), r);
+  }
+  if (colsum == nullptr) return;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[ry][cp * 8 + j] = acc[j];
+  __syncthreads();
+  if (threadIdx.x < 128) {
+    const int col = blockIdx.x * 128 + threadIdx.x;
+    if (col < N) {
+      float t = 0.f;
+#pragma unroll
+      for (int l = 0; l < 16; ++l) t += s[l][threadIdx.x];
+      atomicAdd(&colsum[col], t);
+    }
+  }
+}
+
+extern "C" int iit_gelu_bwd_bias_colsum(const void* dpost, const void* h, const float* bias, void* dpre, float* colsum,
+                                        int64_t rows, int64_t n, void* stream) {
+  IIT_REQUIRE(dpost && h && dpre && rows >= 0 && n > 0 && n % 8 == 0 && n < (1ll << 31), "iit_gelu_bwd_bias_colsum: bad arguments "
+              "(bf16 tensors, width a multiple of 8)");
+  IIT_REQUIRE(aligned16(dpost, h, dpre, bias), "iit_gelu_bwd_bias_colsum: pointers must be 16-byte aligned");
+  if (rows == 0) return 0;
+  int64_t gy = (rows + 16 * 4 - 1) / (16 * 4);
+  const int64_t gx = (n + 127) / 128, cap = std::max<int64_t>(1, (int64_t)kNumSMs * 8 / gx);
+  if (gy > cap) gy = cap;
+  if (gy < 1) gy = 1;
+  gelu_bwd_bias_colsum_kernel<<<dim3((unsigned)gx, (unsigned)gy), 256, 0, as_stream(stream)>>>(
+      (const __nv_bfloat16*)dpost, (const __nv_bfloat16*)h, bias, (__nv_bfloat16*)dpre, colsum, rows, (int)n);
+  IIT_LAUNCH_CHECK("iit_gelu_bwd_bias_colsum");
+  return 0;
+}
+
 extern "C" int iit_colsum(const void* x, int dtype, float* out, int64_t rows, int64_t n, void* stream) {
   IIT_REQUIRE(x && out, "iit_colsum: null pointer");
   if (dtype == IIT_BF16 && n % 8 == 0 && n < (1ll << 31) && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {

@@ -58,6 +58,9 @@ class _Holder(nn.Module):
     """Namespace module so that parameters / hook points get transformer_lens' dotted names."""
 
 
+FUSE_GELU_IN_GEMM = False   # True: gelu_new / its backward in the GEMM epilogues (iit_gemm_bias_act_tc act=1, iit_gemm_dgrad_gelu_tc)
+
+
 def _hp():
     # every hook point this model lets a hook modify (hook_z, mlp.hook_post, the residual-stream points, hook_attn_out /
     # hook_mlp_out) carries a tensor whose producer kept its INPUTS for the backward (attention keeps qkv, bias+GELU keeps
@@ -293,9 +296,16 @@ class HookedTransformerLL(HookedRootModule):
                 resid = self._epi(("o", li), z.reshape(T, hd), a.b_O.detach(), (((D,), (1,), 0),), (a.b_O,), resid=resid)
                 resid = blk.hook_resid_mid(resid.view(B, S, D)).reshape(T, D)
                 x = ops.lnpre(resid, c.eps)
-                link = self._mlp_link(li) if (torch.is_grad_enabled() and m.hook_post.only_patch_hooks()) else None
-                post = self._epi(("in", li), x, m.b_in.detach(), (((c.d_mlp,), (1,), 0),), (m.b_in,), act=1, link_out=link)
-                post = m.hook_post(post.view(B, S, c.d_mlp)).reshape(T, -1)
+                if FUSE_GELU_IN_GEMM:      # measured slower: the tiled kernel's eight epilogue warps are ALU-bound on the GELU
+                    link = self._mlp_link(li) if (torch.is_grad_enabled() and m.hook_post.only_patch_hooks()) else None
+                    post = self._epi(("in", li), x, m.b_in.detach(), (((c.d_mlp,), (1,), 0),), (m.b_in,), act=1, link_out=link)
+                    post = post.view(B, S, c.d_mlp)
+                else:
+                    # the MLP's input map stays a plain GEMM; bias + gelu_new read its result once and write `post` only
+                    # (the backward recomputes h + bias and takes the bias gradient in the same pass)
+                    link = None
+                    post = ops.bias_gelu_lean(self._linear(("in", li), x), m.b_in, (B, S, c.d_mlp))
+                post = m.hook_post(post).reshape(T, -1)
                 resid = self._epi(("out", li), post, m.b_out.detach(), (((D,), (1,), 0),), (m.b_out,), resid=resid, link_in=link)
                 resid = blk.hook_resid_post(resid.view(B, S, D)).reshape(T, D)
                 continue

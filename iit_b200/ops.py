@@ -1187,6 +1187,39 @@ def bias_gelu(x2d, bias, out_shape):
     return _BiasGeluFn.apply(x2d, bias, tuple(out_shape))
 
 
+class _BiasGeluLeanFn(torch.autograd.Function):
+    """post = gelu_new(h + bias) for bf16 activations, keeping `h` (the GEMM's raw result, alive anyway) instead of writing
+    the pre-activation: the forward moves two tensors instead of three, and the backward computes
+    dpre = dpost * gelu'(h + bias) together with the bias gradient (column sums of dpre) in ONE pass
+    (iit_gelu_bwd_bias_colsum) instead of a GELU-backward kernel plus a column-sum kernel."""
+
+    @staticmethod
+    def forward(ctx, h, bias, out_shape):
+        _require_cuda(h, bias)
+        h = h.contiguous()
+        if h.dtype != torch.bfloat16 or h.shape[1] % 8:
+            raise RuntimeError("bias_gelu_lean: bf16 activations with a width that is a multiple of 8 only")
+        post = torch.empty(out_shape, dtype=h.dtype, device=h.device)
+        rows, n = h.shape
+        call("iit_bias_act_fwd", _p(h), _p(bias), None, None, _p(post), _dt(h), rows, n, 1, _stream())
+        ctx.save_for_backward(h, bias)
+        return post
+
+    @staticmethod
+    def backward(ctx, dpost):
+        h, bias = ctx.saved_tensors
+        dpost = dpost.contiguous()
+        rows, n = h.shape
+        dpre = torch.empty_like(h)
+        db = torch.zeros(n, dtype=torch.float32, device=h.device) if ctx.needs_input_grad[1] else None
+        call("iit_gelu_bwd_bias_colsum", _p(dpost), _p(h), _p(bias), _p(dpre), _p(db), rows, n, _stream())
+        return dpre, db, None
+
+
+def bias_gelu_lean(h2d, bias, out_shape):
+    return _BiasGeluLeanFn.apply(h2d, bias, tuple(out_shape))
+
+
 class _LNPreFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, eps):

@@ -371,6 +371,11 @@ int iit_lnpre_bwd(const void* dy, const void* y, const float* rstd, void* dx, in
 int iit_bias_act_fwd(const void* x, const float* bias, const void* resid, void* pre_out, void* out, int dtype,
                      int64_t rows, int n, int act, void* stream);
 int iit_gelu_bwd(const void* dpost, const void* pre, void* dpre, int dtype, int64_t n, void* stream);
+/* The MLP activation's backward with the input bias folded in and its gradient taken in the same pass (bf16, n % 8 == 0):
+ * dpre[r,c] = dpost[r,c] * gelu_new'(h[r,c] + bias[c]); colsum[c] += sum_r dpre[r,c] (fp32, caller zeroes; may be NULL).
+ * `h` is the raw result of the MLP's input map: the forward keeps it instead of the pre-activation h + bias. */
+int iit_gelu_bwd_bias_colsum(const void* dpost, const void* h, const float* bias, void* dpre, float* colsum, int64_t rows,
+                             int64_t n, void* stream);
 /* out[c] += sum_r x[r,c] (bias gradients; fp32, caller zeroes) */
 int iit_colsum(const void* x, int dtype, float* out, int64_t rows, int64_t n, void* stream);
 /* Causal attention core on the fused projection qkv [B,S,3,H,DH] -> z [B,S,H,DH] (blocks.i.attn.hook_z),

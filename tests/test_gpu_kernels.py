@@ -896,3 +896,45 @@ def test_gemm_epilogues_match_separate_kernels():
         R.gelu_new(p32).backward(dy.float() @ w.float())
         torch.testing.assert_close(dpre.float(), p32.grad, rtol=2e-2, atol=2e-2)
         torch.testing.assert_close(sums[0].float(), dpre.float().sum(0), rtol=1e-3, atol=1e-2)
+
+
+def test_gelu_backward_with_bias_and_column_sums():
+    """iit_gelu_bwd_bias_colsum: dpre = dpost * gelu_new'(h + bias) and the bias gradient in one pass, against torch fp32."""
+    from iit_b200 import ops
+    g = torch.Generator().manual_seed(4)
+    for rows, n in [(37, 128), (1000, 3072), (5, 8)]:
+        h = torch.randn(rows, n, generator=g).to(DEV).bfloat16()
+        b = torch.randn(n, generator=g).to(DEV)
+        dpost = torch.randn(rows, n, generator=g).to(DEV).bfloat16()
+        hd, bd = h.clone().requires_grad_(True), b.clone().requires_grad_(True)
+        post = ops.bias_gelu_lean(hd, bd, (rows, n))
+        post.backward(dpost)
+        h32, b32 = h.float().requires_grad_(True), b.clone().requires_grad_(True)
+        ref = R.gelu_new(h32 + b32)
+        ref.backward(dpost.float())
+        torch.testing.assert_close(post.float(), ref.detach(), rtol=1e-2, atol=1e-2)
+        torch.testing.assert_close(hd.grad.float(), h32.grad, rtol=2e-2, atol=2e-2)
+        torch.testing.assert_close(bd.grad, b32.grad, rtol=2e-2, atol=2e-2 * rows ** 0.5)
+
+
+def test_transformer_with_gelu_in_the_gemm_epilogues_matches_the_default_path():
+    """nn.transformer.FUSE_GELU_IN_GEMM (off by default: slower) keeps working: same logits and gradients to bf16 rounding."""
+    from iit_b200.nn import transformer as T
+    from iit_b200.tasks.ioi import make_ll_model
+    x = R.synthetic_ioi(8, 7, d_vocab=101, n_names=20)[0][0].to(DEV)
+    out = {}
+    for flag in (False, True):
+        T.FUSE_GELU_IN_GEMM = flag
+        try:
+            ll = make_ll_model(device=DEV, d_mlp=128, d_vocab=101, n_ctx=32, dtype=torch.bfloat16)
+            ll.load_state_dict(R.transformer_state_dict(0, d_mlp=128, d_vocab=101, n_ctx=32))
+            y = ll(x)
+            y.float().square().mean().backward()
+            out[flag] = (y.detach().float(), {n: p.grad.float().clone() for n, p in ll.named_parameters() if p.grad is not None})
+        finally:
+            T.FUSE_GELU_IN_GEMM = False
+    assert float((out[True][0] - out[False][0]).norm() / out[False][0].norm()) < 2e-2
+    top = max(float(v.norm()) for v in out[False][1].values())
+    for n, gref in out[False][1].items():
+        if float(gref.norm()) > 1e-3 * top:
+            assert float((out[True][1][n] - gref).norm() / gref.norm()) < 5e-2, n
