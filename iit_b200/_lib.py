@@ -39,6 +39,12 @@ class Relayout(C.Structure):
                 ("to_crsk", C.c_int32), ("dtype", C.c_int32), ("out_pitch", C.c_int64)]
 
 
+class HlSpec(C.Structure):
+    """iit_hl_spec_t"""
+    _fields_ = [("mode", C.c_int32), ("node", C.c_int32), ("base", C.c_void_p), ("src", C.c_void_p), ("names", C.c_void_p),
+                ("n_names", C.c_int32), ("seq", C.c_int32), ("d_vocab", C.c_int64)]
+
+
 _vp, _i, _i64, _f, _d, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_double, C.c_size_t
 _BoxP, _ConvP = C.POINTER(Box), C.POINTER(Conv)
 
@@ -50,6 +56,7 @@ SIGNATURES = {
     "iit_hl_pvr": [_vp, _vp, _i, _i64, _vp, _vp, _vp],
     "iit_hl_ioi_last_argmax": [_vp, _vp, _i, _vp, _i, _i64, _i, _i64, _vp, _vp],
     "iit_hl_ioi_dense": [_vp, _vp, _i, _vp, _i, _i64, _i, _i64, _vp, _vp],
+    "iit_hl_ce_fwd": [_vp, _i, _i64, _i64, _i64, C.POINTER(HlSpec), _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "iit_ce_index_fwd": [_vp, _i, _i64, _i64, _i64, _vp, _vp, _vp, _vp],
     "iit_ce_index_bwd": [_vp, _i, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _i64, _vp],
     "iit_ce_prob_fwd": [_vp, _i, _i64, _i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp],

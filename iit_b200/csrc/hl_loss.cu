@@ -76,11 +76,9 @@ __device__ void ioi_sparse(const int64_t* bt, const int64_t* st, int node, int s
   }
 }
 
-__global__ void hl_ioi_last_argmax_kernel(const int64_t* __restrict__ base_tok, const int64_t* __restrict__ src_tok,
-                                          int node, const int64_t* __restrict__ names, int n_names, int64_t batch,
-                                          int seq, int64_t V, int64_t* __restrict__ out) {
-  int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= batch) return;
+// argmax over the vocabulary of the IOI HL model's last-position logits for sample b, one hook interchanged
+__device__ int64_t ioi_last_argmax_row(const int64_t* __restrict__ base_tok, const int64_t* __restrict__ src_tok, int node,
+                                       const int64_t* __restrict__ names, int n_names, int64_t b, int seq, int64_t V) {
   int64_t bt[kMaxSeq], st[kMaxSeq], mt[kMaxSeq], sh[kMaxSeq];
   for (int j = 0; j < seq; ++j) { bt[j] = base_tok[b * seq + j]; st[j] = src_tok ? src_tok[b * seq + j] : bt[j]; }
   ioi_sparse(bt, st, node, seq, mt, sh);
@@ -113,7 +111,15 @@ __global__ void hl_ioi_last_argmax_kernel(const int64_t* __restrict__ base_tok, 
       if (!nz) { arg = c; break; }
     }
   }
-  out[b] = arg;
+  return arg;
+}
+
+__global__ void hl_ioi_last_argmax_kernel(const int64_t* __restrict__ base_tok, const int64_t* __restrict__ src_tok,
+                                          int node, const int64_t* __restrict__ names, int n_names, int64_t batch,
+                                          int seq, int64_t V, int64_t* __restrict__ out) {
+  int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= batch) return;
+  out[b] = ioi_last_argmax_row(base_tok, src_tok, node, names, n_names, b, seq, V);
 }
 
 // dense [B,S,V] fp32: zero fill is done by the caller-visible kernel below (grid-stride), then the
@@ -255,6 +261,162 @@ __device__ __forceinline__ float row_lse(const T* __restrict__ row, int64_t clas
     __syncthreads();
   }
   return m + __logf(s);
+}
+
+// the same for a bf16 row whose start is 16-byte aligned: 8 values per load, one rescale per pack instead of per element
+template <int GROUP>
+__device__ __forceinline__ float row_lse_bf16x8(const __nv_bfloat16* __restrict__ row, int64_t classes, int t, float* s_m, float* s_s) {
+  float m = -INFINITY, s = 0.f;
+  const int packs = (int)(classes >> 3);
+  for (int pk = t; pk < packs; pk += GROUP) {
+    const uint4 w = *reinterpret_cast<const uint4*>(row + (int64_t)pk * 8);
+    const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { v[2 * i] = __uint_as_float(ww[i] << 16); v[2 * i + 1] = __uint_as_float(ww[i] & 0xffff0000u); }
+    float pm = v[0];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) pm = fmaxf(pm, v[i]);
+    if (pm == -INFINITY) continue;
+    const float nm = fmaxf(m, pm);
+    float acc = (m == -INFINITY) ? 0.f : s * __expf(m - nm);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc += __expf(v[i] - nm);        // exp(-inf) = 0
+    m = nm; s = acc;
+  }
+  for (int64_t c = (int64_t)packs * 8 + t; c < classes; c += GROUP) {      // tail of fewer than 8 elements
+    const float v = __bfloat162float(row[c]);
+    if (v > m) { s = s * __expf(m - v) + 1.f; m = v; }
+    else if (v != -INFINITY) s += __expf(v - m);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    float om = __shfl_xor_sync(0xffffffffu, m, o), os = __shfl_xor_sync(0xffffffffu, s, o);
+    float nm = fmaxf(m, om);
+    float a = (m == -INFINITY) ? 0.f : s * __expf(m - nm);
+    float b = (om == -INFINITY) ? 0.f : os * __expf(om - nm);
+    m = nm; s = a + b;
+  }
+  if (GROUP == 256) {
+    int w = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) { s_m[w] = m; s_s[w] = s; }
+    __syncthreads();
+    m = threadIdx.x < 8 ? s_m[threadIdx.x & 7] : -INFINITY;
+    s = threadIdx.x < 8 ? s_s[threadIdx.x & 7] : 0.f;
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) {
+      float om = __shfl_xor_sync(0xffffffffu, m, o), os = __shfl_xor_sync(0xffffffffu, s, o);
+      float nm = fmaxf(m, om);
+      float a = (m == -INFINITY) ? 0.f : s * __expf(m - nm);
+      float b = (om == -INFINITY) ? 0.f : os * __expf(om - nm);
+      m = nm; s = a + b;
+    }
+    __syncthreads();
+  }
+  return m + __logf(s);
+}
+
+// (c) ONE launch for an IIT loss term's high-level side and its loss: per row the HL model's intervened output (the class
+// index the LL logits are scored against), the row's logsumexp, its negative log-likelihood; the block that finishes last
+// adds the rows' values in a fixed order (deterministic) and writes the mean. mode 0 takes the targets as given.
+template <typename T, int GROUP>
+__global__ void __launch_bounds__(256) hl_ce_fwd_kernel(const T* __restrict__ logits, int64_t rows, int64_t classes,
+                                                        int64_t row_stride, iit_hl_spec_t hl, int64_t* __restrict__ target,
+                                                        float* __restrict__ out_lse, float* __restrict__ row_nll,
+                                                        float* __restrict__ loss, unsigned int* __restrict__ ticket,
+                                                        int* __restrict__ err_flag, int vec_ok) {
+  constexpr int RPB = 256 / GROUP;
+  __shared__ float s_m[8], s_s[8], s_red[8];
+  __shared__ int s_last;
+  const int g = threadIdx.x / GROUP, t = threadIdx.x % GROUP;
+  for (int64_t r0 = (int64_t)blockIdx.x * RPB; r0 < rows; r0 += (int64_t)gridDim.x * RPB) {
+    const int64_t r = r0 + g;
+    int64_t tgt = -1;
+    if (t == 0 && r < rows) {
+      if (hl.mode == 1) {            // MNIST-PVR: (tr, bl, br)[class_map[tl] - 1] with variable `node` taken from the source run
+        int64_t v[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) v[i] = (i == hl.node && hl.src != nullptr) ? hl.src[r * 4 + i] : hl.base[r * 4 + i];
+        if (!pvr_hl_eval(v, &tgt) && err_flag != nullptr) *err_flag = 1;
+        target[r] = tgt;
+      } else if (hl.mode == 2) {     // IOI: argmax of the HL logits at the last position
+        tgt = ioi_last_argmax_row(hl.base, hl.src, hl.node, hl.names, hl.n_names, r, hl.seq, hl.d_vocab);
+        target[r] = tgt;
+      } else {
+        tgt = target[r];
+      }
+    }
+    float l = 0.f;
+    if (GROUP == 256 || r < rows) {
+      const T* row = logits + (r < rows ? r : 0) * row_stride;
+      if (sizeof(T) == 2 && vec_ok) l = row_lse_bf16x8<GROUP>(reinterpret_cast<const __nv_bfloat16*>(row), classes, t, s_m, s_s);
+      else l = row_lse<T, GROUP>(row, classes, t, s_m, s_s);
+    }
+    if (r < rows && t == 0) {
+      out_lse[r] = l;
+      float nll = l;
+      if (tgt >= 0 && tgt < classes) nll -= to_f<T>(logits[r * row_stride + tgt]);
+      else { nll = NAN; if (err_flag != nullptr) *err_flag = 1; }      // torch raises for a target outside [0, classes)
+      row_nll[r] = nll;
+    }
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(ticket, 1u) == gridDim.x - 1) ? 1 : 0;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  float acc = 0.f;
+  for (int64_t r = threadIdx.x; r < rows; r += 256) acc += __ldcg(row_nll + r);
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float v = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v += s_red[i];
+    *loss = v / (float)rows;
+    *ticket = 0u;                    // ready for the next launch
+  }
+}
+
+// d[r, c] = (softmax(logits[r])[c] - [c == target[r]]) * g / rows for c < classes, 0 for classes <= c < d_cols: bf16 rows whose
+// starts are 16-byte aligned, 8 columns per thread
+__global__ void __launch_bounds__(256) ce_index_bwd_bf16x8_kernel(const __nv_bfloat16* __restrict__ logits, int rows, int classes,
+                                                                  int64_t row_stride, const int64_t* __restrict__ target,
+                                                                  const float* __restrict__ lse, const float* __restrict__ gout,
+                                                                  __nv_bfloat16* __restrict__ dl, int64_t d_row_stride, int d_cols) {
+  const int r = blockIdx.y;
+  const int c0 = (blockIdx.x * 256 + threadIdx.x) * 8;
+  if (c0 >= d_cols) return;
+  const float g = (gout ? *gout : 1.f) / (float)rows;
+  const float l = lse[r];
+  const int tg = (int)target[r];
+  float v[8];
+  if (c0 + 8 <= classes) {
+    const uint4 w = *reinterpret_cast<const uint4*>(logits + (int64_t)r * row_stride + c0);
+    const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { v[2 * i] = __uint_as_float(ww[i] << 16); v[2 * i + 1] = __uint_as_float(ww[i] & 0xffff0000u); }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = c0 + i < classes ? __bfloat162float(logits[(int64_t)r * row_stride + c0 + i]) : -INFINITY;
+  }
+  uint32_t o[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float p0 = __expf(v[2 * i] - l), p1 = __expf(v[2 * i + 1] - l);
+    if (c0 + 2 * i == tg) p0 -= 1.f;
+    if (c0 + 2 * i + 1 == tg) p1 -= 1.f;
+    __nv_bfloat162 h = __floats2bfloat162_rn(p0 * g, p1 * g);
+    o[i] = *reinterpret_cast<uint32_t*>(&h);
+  }
+  if (c0 + 8 <= d_cols) {
+    *reinterpret_cast<uint4*>(dl + (int64_t)r * d_row_stride + c0) = make_uint4(o[0], o[1], o[2], o[3]);
+  } else {
+    const __nv_bfloat16* ob = reinterpret_cast<const __nv_bfloat16*>(o);
+    for (int i = 0; c0 + i < d_cols; ++i) dl[(int64_t)r * d_row_stride + c0 + i] = ob[i];
+  }
 }
 
 template <typename T, int GROUP>
@@ -435,11 +597,46 @@ extern "C" int iit_ce_index_fwd(const void* logits, int dtype, int64_t rows, int
   return 0;
 }
 
+extern "C" int iit_hl_ce_fwd(const void* logits, int dtype, int64_t rows, int64_t classes, int64_t row_stride,
+                             const iit_hl_spec_t* hl, int64_t* target, float* row_lse_out, float* row_nll, float* loss,
+                             unsigned int* ticket, int32_t* err_flag, void* stream) {
+  IIT_REQUIRE(logits && hl && target && row_lse_out && row_nll && loss && ticket && rows >= 1 && classes >= 1,
+              "iit_hl_ce_fwd: bad arguments");
+  IIT_REQUIRE(hl->mode >= 0 && hl->mode <= 2, "iit_hl_ce_fwd: mode must be 0 (targets given), 1 (MNIST-PVR HL) or 2 (IOI HL)");
+  IIT_REQUIRE(hl->mode == 0 || hl->base != nullptr, "iit_hl_ce_fwd: the HL model needs the base run's variables / tokens");
+  IIT_REQUIRE(hl->mode != 1 || hl->node < 4, "iit_hl_ce_fwd: PVR variable index must be < 4 (got %d)", hl->node);
+  IIT_REQUIRE(hl->mode != 2 || (hl->seq >= 1 && hl->seq <= kMaxSeq && hl->names != nullptr), "iit_hl_ce_fwd: IOI needs 1 <= seq <= %d "
+              "and the sorted name ids", kMaxSeq);
+  cudaStream_t st = as_stream(stream);
+  const int vec_ok = dtype == IIT_BF16 && (reinterpret_cast<uintptr_t>(logits) & 15) == 0 && row_stride % 8 == 0;
+  IIT_DISPATCH_DTYPE(dtype, T, {
+    if (classes <= 1024)
+      hl_ce_fwd_kernel<T, 32><<<grid_for(rows, 8), 256, 0, st>>>((const T*)logits, rows, classes, row_stride, *hl, target, row_lse_out,
+                                                                 row_nll, loss, ticket, err_flag, vec_ok);
+    else
+      hl_ce_fwd_kernel<T, 256><<<grid_for(rows, 1), 256, 0, st>>>((const T*)logits, rows, classes, row_stride, *hl, target, row_lse_out,
+                                                                  row_nll, loss, ticket, err_flag, vec_ok);
+  })
+  IIT_LAUNCH_CHECK("iit_hl_ce_fwd");
+  return 0;
+}
+
 extern "C" int iit_ce_index_bwd(const void* logits, int dtype, int64_t rows, int64_t classes, int64_t row_stride,
                                 const int64_t* target, const float* row_lse_in, const float* grad_out, void* dlogits,
                                 int64_t d_row_stride, void* stream) {
   IIT_REQUIRE(logits && target && row_lse_in && dlogits && rows >= 1, "iit_ce_index_bwd: bad arguments");
   cudaStream_t st = as_stream(stream);
+  // bf16 rows with 16-byte aligned starts: 8 columns per thread; every column up to the row pitch is written (the gradient of
+  // padding columns is zero), so a padded logits buffer gets a padded gradient with no slicing by the caller
+  if (dtype == IIT_BF16 && ((reinterpret_cast<uintptr_t>(logits) | reinterpret_cast<uintptr_t>(dlogits)) & 15) == 0 &&
+      row_stride % 8 == 0 && d_row_stride % 8 == 0 && rows < 65536 && d_row_stride < (1ll << 31) && d_row_stride >= classes) {
+    const int d_cols = (int)d_row_stride;
+    dim3 grid((unsigned)((d_cols / 8 + 255) / 256), (unsigned)rows);
+    ce_index_bwd_bf16x8_kernel<<<grid, 256, 0, st>>>((const __nv_bfloat16*)logits, (int)rows, (int)classes, row_stride, target,
+                                                     row_lse_in, grad_out, (__nv_bfloat16*)dlogits, d_row_stride, d_cols);
+    IIT_LAUNCH_CHECK("iit_ce_index_bwd");
+    return 0;
+  }
   IIT_DISPATCH_DTYPE(dtype, T, {
     ce_index_bwd_kernel<T><<<grid_for(rows * classes, 256 * 4), 256, 0, st>>>((const T*)logits, rows, classes, row_stride,
                                                                              target, row_lse_in, grad_out, (T*)dlogits,

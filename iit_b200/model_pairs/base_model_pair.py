@@ -200,6 +200,19 @@ class BaseModelPair(ABC):
         return ll_ablation_hook
 
     def get_IIT_loss_over_batch(self, base_input, ablation_input, hl_node, loss_fn):
+        if loss_fn is ops.cross_entropy and hasattr(self.hl_model, "interchange_ce"):
+            # the same four runs as do_intervention (reference :75-105, :165-174), with the HL base run and the loss as ONE
+            # kernel: the intervened HL output is the class index each row of the LL logits is scored against
+            hl_node = self._resolve_hl_node(hl_node)
+            ll_nodes = self.corr[hl_node]
+            self.hl_cache = _LazyCache(lambda: self.hl_model.run_with_cache(ablation_input)[1])
+            self.ll_source_run(ablation_input[0], ll_nodes)
+            ll_output = self.ll_model.run_with_hooks(
+                base_input[0], fwd_hooks=[(n.name, self.make_ll_ablation_hook(n)) for n in ll_nodes])
+            if ll_output.dim() == 2:
+                loss, self.last_hl_output = self.hl_model.interchange_ce(base_input, ablation_input, hl_node, ll_output)
+                return loss
+            return loss_fn(ll_output, self.hl_intervention(base_input, ablation_input, hl_node))
         hl_output, ll_output = self.do_intervention(base_input, ablation_input, hl_node)
         return loss_fn(ll_output, hl_output)
 

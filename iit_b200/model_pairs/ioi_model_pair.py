@@ -72,38 +72,45 @@ class IOI_ModelPair(StrictIITModelPair):
         return ids
 
     def _last_logits(self, fwd_hooks, x):
-        """LL run returning last-position logits [B,V] (unembeds one position when the model can)."""
+        """LL run returning last-position logits (unembeds one position when the model can) and the number of real classes:
+        the tensor may carry padding columns beyond it (HookedTransformerLL return_padded), which the loss ignores."""
         if getattr(self.ll_model, "supports_last_pos", False):
-            return self.ll_model.run_with_hooks(x, fwd_hooks=fwd_hooks, last_pos_only=True)
-        return self.ll_model.run_with_hooks(x, fwd_hooks=fwd_hooks)[:, -1, :]
+            out = self.ll_model.run_with_hooks(x, fwd_hooks=fwd_hooks, last_pos_only=True, return_padded=True)
+            return out, int(self.ll_model.cfg.d_vocab_out)
+        out = self.ll_model.run_with_hooks(x, fwd_hooks=fwd_hooks)[:, -1, :]
+        return out, int(out.shape[-1])
 
-    def _label_loss(self, logits_last, base_y):
+    def _label_loss(self, logits_last, classes, base_y):
         if self.training_args["labels_are_one_hot"] or base_y.dtype == t.int64:
-            return ops.cross_entropy(logits_last, self.label_ids(base_y)[:, -1].contiguous())
-        return ops.cross_entropy(logits_last, base_y[:, -1, :])
+            return ops.cross_entropy(logits_last, self.label_ids(base_y)[:, -1].contiguous(), classes=classes)
+        return ops.cross_entropy(logits_last[:, :classes], base_y[:, -1, :])
 
     # ---- losses ------------------------------------------------------------------------------
     def get_IIT_loss_over_batch(self, base_input, ablation_input, hl_node, loss_fn):
         hl_node = self._resolve_hl_node(hl_node)
         ll_nodes = self.corr[hl_node]
+        self.ll_source_run(ablation_input[0], ll_nodes)
+        last, classes = self._last_logits([(n.name, self.make_ll_ablation_hook(n)) for n in ll_nodes], base_input[0])
+        # CE against one_hot(argmax(hl)).float() == CE against the index (reference :64-68)
+        if hasattr(self.hl_model, "interchange_last_ce"):
+            # the HL model's intervened last-position argmax and the loss against it in ONE launch
+            loss, self.last_hl_argmax = self.hl_model.interchange_last_ce(base_input, ablation_input, hl_node, last, classes)
+            return loss
         if hasattr(self.hl_model, "interchange_last_argmax"):
             hl_argmax = self.hl_model.interchange_last_argmax(base_input, ablation_input, hl_node)
         else:
             hl_output = self.hl_intervention(base_input, ablation_input, hl_node)
             hl_argmax = ops.argmax_rows(hl_output[:, -1, :])
-        self.ll_source_run(ablation_input[0], ll_nodes)
-        last = self._last_logits([(n.name, self.make_ll_ablation_hook(n)) for n in ll_nodes], base_input[0])
-        # CE against one_hot(argmax).float() == CE against the index (reference :64-68)
-        return ops.cross_entropy(last, hl_argmax)
+        return ops.cross_entropy(last, hl_argmax, classes=classes)
 
     def get_strict_loss_over_batch(self, base_input, ablation_input, ll_node, loss_fn):
         self.ll_source_run(ablation_input[0], [ll_node])
-        last = self._last_logits([(ll_node.name, self.make_ll_ablation_hook(ll_node))], base_input[0])
-        return self._label_loss(last, base_input[1])
+        last, classes = self._last_logits([(ll_node.name, self.make_ll_ablation_hook(ll_node))], base_input[0])
+        return self._label_loss(last, classes, base_input[1])
 
     def get_behaviour_loss_over_batch(self, base_input, loss_fn):
-        last = self._last_logits([], base_input[0])
-        return self._label_loss(last, base_input[1])
+        last, classes = self._last_logits([], base_input[0])
+        return self._label_loss(last, classes, base_input[1])
 
     def run_eval_step(self, base_input, ablation_input, loss_fn):
         hl_node = self._resolve_hl_node(self.sample_hl_name())
@@ -113,10 +120,10 @@ class IOI_ModelPair(StrictIITModelPair):
         else:
             hl_argmax = ops.argmax_rows(self.hl_intervention(base_input, ablation_input, hl_node)[:, -1, :])
         self.ll_source_run(ablation_input[0], ll_nodes)
-        last = self._last_logits([(n.name, self.make_ll_ablation_hook(n)) for n in ll_nodes], base_input[0])
+        last, classes = self._last_logits([(n.name, self.make_ll_ablation_hook(n)) for n in ll_nodes], base_input[0])
         assert self.hl_model.is_categorical()
-        loss = ops.cross_entropy(last, hl_argmax)
-        counts, _ = ops.iia_count(last, hl_argmax)
+        loss = ops.cross_entropy(last, hl_argmax, classes=classes)
+        counts, _ = ops.iia_count(last[:, :classes], hl_argmax)
         # behavioural accuracy at every position (reference :94-102)
         base_x, base_y, _ = base_input
         output = self.ll_model(base_x)

@@ -268,7 +268,10 @@ class HookedTransformerLL(HookedRootModule):
                 raise NotImplementedError(f"hook point {n} lives inside a fused kernel; hook hook_z / hook_post / "
                                           "the residual-stream hook points instead")
 
-    def forward(self, tokens, last_pos_only=False, return_type="logits"):
+    def forward(self, tokens, last_pos_only=False, return_type="logits", return_padded=False):
+        """`return_padded` (with last_pos_only): the last-position logits as the unembedding GEMM wrote them, [B, V rounded up
+        to 64 columns] -- the caller scores columns < d_vocab_out only (ops.cross_entropy(..., classes=V)) and no slice sits
+        in the autograd graph (its backward would rebuild the padded gradient with a fill and a copy)."""
         self._check_hooks()
         if self._shadow_usable():
             if self._filter_shadow_stale() and not ops.capturing():
@@ -345,7 +348,10 @@ class HookedTransformerLL(HookedRootModule):
         pad = (-V) % 64
         if use_shadow:
             xin = resid.view(B, S, D)[:, -1, :].contiguous() if last_pos_only else resid
-            logits = self._epi(("unembed",), ops.lnpre(xin, c.eps), self._shadow["b_U_pad"], (((V,), (1,), 0),), (b_U,))[:, :V]
+            logits = self._epi(("unembed",), ops.lnpre(xin, c.eps), self._shadow["b_U_pad"], (((V,), (1,), 0),), (b_U,))
+            if last_pos_only and return_padded:
+                return logits
+            logits = logits[:, :V]
             return logits if last_pos_only else logits.reshape(B, S, -1)
         if pad and self.act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES:
             # the tensor-core GEMMs want widths that are multiples of 64: unembed into V + pad columns (zero weights and

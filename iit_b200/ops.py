@@ -201,28 +201,89 @@ def _rows_view(logits: torch.Tensor):
     return logits, logits.stride(0)
 
 
-class _CEIndexFn(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, logits, target):
-        _require_cuda(logits, target)
-        lg, rs = _rows_view(logits)
-        tgt = target.contiguous()
-        rows, classes = lg.shape
-        lse = torch.empty(rows, dtype=torch.float32, device=lg.device)
-        loss = torch.zeros((), dtype=torch.float32, device=lg.device)
-        call("iit_ce_index_fwd", _p(lg), _dt(lg), rows, classes, rs, _p(tgt), _p(lse), _p(loss), _stream())
-        ctx.save_for_backward(lg, tgt, lse)
-        return loss
+_tickets: dict = {}
+
+
+def _ticket(device) -> torch.Tensor:
+    """One zeroed uint32 per device for iit_hl_ce_fwd's last-block reduction (the kernel leaves it zero)."""
+    dev = torch.device(device)
+    if dev.type == "cuda" and dev.index is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+    t = _tickets.get(dev)
+    if t is None:
+        t = _tickets[dev] = torch.zeros(1, dtype=torch.int32, device=dev)
+    return t
+
+
+class _HLCEFn(torch.autograd.Function):
+    """Mean cross-entropy of `logits[:, :classes]` against a class index per row that comes from a high-level model, all in
+    one launch (iit_hl_ce_fwd): `hl` = None (targets given), ("pvr", base_vars, src_vars, var) or
+    ("ioi", base_tok, src_tok, node, names, d_vocab). `logits` may be wider than `classes` (padded columns): the gradient is
+    then as wide, zero in the padding. Returns (loss, target)."""
 
     @staticmethod
-    def backward(ctx, g):
+    def forward(ctx, logits, target, classes, hl):
+        _require_cuda(logits, target)
+        lg, rs = _rows_view(logits)
+        rows = lg.shape[0]
+        classes = lg.shape[1] if classes is None else int(classes)
+        spec = _lib.HlSpec()
+        keep = []
+        if hl is None:
+            spec.mode = 0
+            tgt = target.contiguous()
+        else:
+            tgt = torch.empty(rows, dtype=torch.int64, device=lg.device)
+            if hl[0] == "pvr":
+                _, bv, sv, var = hl
+                bv = bv.contiguous()
+                sv = sv.contiguous() if sv is not None else None
+                if bv.dtype != torch.int64 or bv.dim() != 2 or bv.shape[1] != 4 or bv.shape[0] != rows:
+                    raise ValueError("PVR HL: intermediate vars must be int64 [rows,4]")
+                spec.mode, spec.node, spec.base, spec.src = 1, int(var), bv.data_ptr(), (sv.data_ptr() if sv is not None else None)
+                keep += [bv, sv]
+            else:
+                _, bt, st_, node, names, d_vocab = hl
+                bt = bt.contiguous()
+                st_ = st_.contiguous() if st_ is not None else None
+                if bt.shape[0] != rows:
+                    raise ValueError("IOI HL: one prompt per row of logits expected")
+                spec.mode, spec.node, spec.base = 2, _lib.IOI_NODE_IDS[node], bt.data_ptr()
+                spec.src = st_.data_ptr() if st_ is not None else None
+                spec.names, spec.n_names, spec.seq, spec.d_vocab = names.data_ptr(), int(names.numel()), int(bt.shape[1]), int(d_vocab)
+                keep += [bt, st_, names]
+        lse = torch.empty(rows, dtype=torch.float32, device=lg.device)
+        nll = torch.empty(rows, dtype=torch.float32, device=lg.device)
+        loss = torch.empty((), dtype=torch.float32, device=lg.device)
+        call("iit_hl_ce_fwd", _p(lg), _dt(lg), rows, classes, rs, C.byref(spec), _p(tgt), _p(lse), _p(nll), _p(loss),
+             _p(_ticket(lg.device)), _p(_err_flag(lg.device)), _stream())
+        ctx.save_for_backward(lg, tgt, lse)
+        ctx.classes = classes
+        ctx.mark_non_differentiable(tgt)
+        return loss, tgt
+
+    @staticmethod
+    def backward(ctx, g, _g_tgt):
         lg, tgt, lse = ctx.saved_tensors
-        rows, classes = lg.shape
-        d = torch.empty((rows, classes), dtype=lg.dtype, device=lg.device)
+        rows, width = lg.shape
+        d = torch.empty((rows, width), dtype=lg.dtype, device=lg.device)
+        if width > ctx.classes and not (lg.dtype == torch.bfloat16 and width % 8 == 0):
+            d[:, ctx.classes:] = 0          # the vector path writes the padding columns itself
         g = g.to(torch.float32).contiguous()
-        call("iit_ce_index_bwd", _p(lg), _dt(lg), rows, classes, lg.stride(0), _p(tgt), _p(lse), _p(g), _p(d), classes,
+        call("iit_ce_index_bwd", _p(lg), _dt(lg), rows, ctx.classes, lg.stride(0), _p(tgt), _p(lse), _p(g), _p(d), width,
              _stream())
-        return d, None
+        return d, None, None, None
+
+
+class _CEIndexFn:
+    @staticmethod
+    def apply(logits, target):
+        return _HLCEFn.apply(logits, target, None, None)[0]
+
+
+def hl_cross_entropy(logits, hl, classes=None):
+    """(loss, hl_target): see _HLCEFn."""
+    return _HLCEFn.apply(logits, None, classes, hl)
 
 
 class _CEProbFn(torch.autograd.Function):
@@ -251,9 +312,12 @@ class _CEProbFn(torch.autograd.Function):
         return d, None
 
 
-def cross_entropy(logits: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+def cross_entropy(logits: torch.Tensor, target: torch.Tensor, classes: Optional[int] = None) -> torch.Tensor:
     """F.cross_entropy(logits, target) with mean reduction for 2-D logits; `target` is class indices
-    (int64 [rows]) or probabilities (float [rows, classes])."""
+    (int64 [rows]) or probabilities (float [rows, classes]). `classes` < logits.shape[1] (index targets): the remaining
+    columns are padding -- ignored, and given a zero gradient."""
+    if classes is not None and logits.dim() == 2 and target.dtype == torch.int64 and target.dim() == 1:
+        return _HLCEFn.apply(logits, target, classes, None)[0]
     if logits.dim() == 3:
         # torch's convention for [N, C, d1] inputs: the CLASS dimension is dim 1 (this is what the reference's
         # IITBehaviorModelPair.loss_fn does to [B, S, V] transformer logits, iit_behavior_model_pair.py:20-30); the mean

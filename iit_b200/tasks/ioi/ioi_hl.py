@@ -59,6 +59,13 @@ class IOI_HL(HookedRootModule, HLModel):
         return ops.hl_ioi_dense(self._tokens(base_input), self._tokens(ablation_input), self._node_name(hl_node),
                                 self.names, self.d_vocab)
 
+    def interchange_last_ce(self, base_input, ablation_input, hl_node, last_logits, classes):
+        """(loss, hl_argmax): the intervened HL run's last-position argmax and the mean cross-entropy of `last_logits[:, :classes]`
+        against it, in one launch (ops.hl_cross_entropy)."""
+        self._no_hooks()
+        return ops.hl_cross_entropy(last_logits, ("ioi", self._tokens(base_input), self._tokens(ablation_input),
+                                                  self._node_name(hl_node), self.names, self.d_vocab), classes=classes)
+
     def interchange_last_argmax(self, base_input, ablation_input, hl_node) -> t.Tensor:
         self._no_hooks()
         return ops.hl_ioi_last_argmax(self._tokens(base_input), self._tokens(ablation_input), self._node_name(hl_node),

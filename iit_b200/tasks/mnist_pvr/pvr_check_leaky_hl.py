@@ -50,6 +50,9 @@ class MNIST_PVR_Leaky_HL(HookedRootModule):
     def interchange(self, base_input, ablation_input, hl_node) -> t.Tensor:
         return ops.hl_pvr(base_input[2], ablation_input[2], var_index(hl_node.name))
 
+    def interchange_ce(self, base_input, ablation_input, hl_node, ll_output):
+        return ops.hl_cross_entropy(ll_output, ("pvr", base_input[2], ablation_input[2], var_index(hl_node.name)))
+
 
 def get_corr(mode, hook_point, model, input_shape):
     if mode != "q":

@@ -59,6 +59,13 @@ class MNIST_PVR_HL(HookedRootModule, HLModel):
         return ops.hl_pvr(base_input[2], ablation_input[2], var_index(hl_node.name))
 
 
+    def interchange_ce(self, base_input, ablation_input, hl_node, ll_output):
+        """(loss, hl_output): the intervened HL output and the mean cross-entropy of `ll_output` against it in one launch."""
+        if hl_node.index is not None and not hl_node.index.is_whole():
+            raise NotImplementedError("PVR HL nodes are interchanged whole (pvr_hl.py:60-65)")
+        return ops.hl_cross_entropy(ll_output, ("pvr", base_input[2], ablation_input[2], var_index(hl_node.name)))
+
+
 hl_nodes = {h: HLNode(h, 10, None) for h in _HOOKS}
 
 

@@ -82,6 +82,18 @@ int iit_hl_pvr(const int64_t* base_vars, const int64_t* src_vars, int var, int64
 enum { IIT_IOI_NONE = 0, IIT_IOI_ALL_NODES = 1, IIT_IOI_DUPLICATE = 2, IIT_IOI_S_INHIBITION = 3,
        IIT_IOI_NAME_MOVER = 4 };
 
+/* Which high-level model produces the class index a row of LL logits is scored against (iit_hl_ce_fwd). */
+typedef struct {
+  int32_t mode;          /* 0: targets are given; 1: MNIST-PVR HL (pvr_hl.py:44-56); 2: IOI HL, last position (ioi_hl.py:102-130) */
+  int32_t node;          /* mode 1: index of the interchanged variable (-1: none); mode 2: IIT_IOI_* */
+  const int64_t* base;   /* mode 1: base run's intermediate variables [rows,4]; mode 2: base tokens [rows,seq] */
+  const int64_t* src;    /* the same from the source run (NULL: no interchange) */
+  const int64_t* names;  /* mode 2: sorted name token ids */
+  int32_t n_names;
+  int32_t seq;           /* mode 2: tokens per prompt (<= 64) */
+  int64_t d_vocab;       /* mode 2 */
+} iit_hl_spec_t;
+
 /* IOI HL with one hook interchanged, evaluated sparsely at the LAST position:
  * out_argmax[b] = argmax_v logits[b, S-1, v] with first-index tie-breaking (torch.argmax).
  * Replaces IOI_HL.forward + heads (iit/tasks/ioi/ioi_hl.py:16-24,37-46,54-68,102-130) and the
@@ -103,7 +115,20 @@ int iit_hl_ioi_dense(const int64_t* base_tok, const int64_t* src_tok, int node,
 int iit_ce_index_fwd(const void* logits, int dtype, int64_t rows, int64_t classes, int64_t row_stride,
                      const int64_t* target, float* row_lse, float* loss, void* stream);
 
-/* dlogits[r,c] = (exp(logits[r,c]-row_lse[r]) - [c==target[r]]) * (*grad_out) / rows */
+/* The high-level side of a loss term and the loss in ONE launch (north_star (c): "the HL model's intervened evaluation fused
+ * with the losses"): per row the class index comes from `hl` -- given (mode 0), MNIST_PVR_HL with one variable interchanged
+ * (mode 1; replaces pvr_hl.py:44-56 + base_model_pair.py:80,89-91), or the argmax of IOI_HL's last-position logits with one
+ * hook interchanged (mode 2; ioi_hl.py:102-130 + ioi_model_pair.py:64-66) -- and is written to target[] (modes 1, 2); then
+ * row_lse[r] = logsumexp(logits[r, :classes]), and *loss = mean_r (row_lse[r] - logits[r, target[r]]) (written, not added;
+ * fixed summation order). row_nll: fp32 [rows] scratch. ticket: one device uint32 that is zero before the first call (the
+ * kernel leaves it zero). A PVR pointer variable outside [-10, 9] or a target outside [0, classes) sets *err_flag (may be
+ * NULL) and gives NaN, where torch raises. Replaces CrossEntropyLoss (iit_behavior_model_pair.py:20-30, base_model_pair.py:173). */
+int iit_hl_ce_fwd(const void* logits, int dtype, int64_t rows, int64_t classes, int64_t row_stride, const iit_hl_spec_t* hl,
+                  int64_t* target, float* row_lse, float* row_nll, float* loss, unsigned int* ticket, int32_t* err_flag,
+                  void* stream);
+
+/* dlogits[r,c] = (exp(logits[r,c]-row_lse[r]) - [c==target[r]]) * (*grad_out) / rows for c < classes; when d_row_stride >
+ * classes the columns classes .. d_row_stride-1 of every row are written too, as zeros (padded logits get a padded gradient). */
 int iit_ce_index_bwd(const void* logits, int dtype, int64_t rows, int64_t classes, int64_t row_stride,
                      const int64_t* target, const float* row_lse, const float* grad_out,
                      void* dlogits, int64_t d_row_stride, void* stream);

@@ -317,7 +317,7 @@ def test_prepared_gemm_operands_equal_per_gemm_copies_and_follow_weight_edits():
         # the prepared path applies bias / residual / GELU to the fp32 accumulator in the GEMM epilogue, the per-GEMM path
         # rounds the GEMM result to bf16 first: equal to bf16 rounding, not bit for bit
         err = float((u.float() - v.float()).norm() / (v.float().norm() + 1e-30))
-        assert err < 2e-2, (what, err)
+        assert err < 4e-2, (what, err)
 
     for scale in (None, 1.5):
         (a, ga), (b, gb) = run(True, scale), run(False, scale)

@@ -938,3 +938,55 @@ def test_transformer_with_gelu_in_the_gemm_epilogues_matches_the_default_path():
     for n, gref in out[False][1].items():
         if float(gref.norm()) > 1e-3 * top:
             assert float((out[True][1][n] - gref).norm() / gref.norm()) < 5e-2, n
+
+
+def test_fused_hl_and_cross_entropy_kernel():
+    """iit_hl_ce_fwd: the HL model's intervened output and the loss against it in one launch, for explicit targets, the
+    MNIST-PVR HL and the IOI HL (padded bf16 logits included), against the separate kernels / torch; gradients too."""
+    from iit_b200 import ops
+    g = torch.Generator().manual_seed(9)
+    # explicit targets, fp32 and bf16, narrow and wide rows
+    for rows, classes, dtype in [(37, 10, torch.float32), (4096, 10, torch.bfloat16), (9, 50257, torch.float32), (33, 1000, torch.bfloat16)]:
+        lg = (torch.randn(rows, classes, generator=g) * 3).to(DEV).to(dtype)
+        tgt = torch.randint(0, classes, (rows,), generator=g).to(DEV)
+        want = F.cross_entropy(lg.float().requires_grad_(False), tgt)
+        l2 = lg.clone().requires_grad_(True)
+        got = ops.cross_entropy(l2, tgt)
+        assert abs(got.item() - want.item()) <= 1e-5 * abs(want.item()) + 1e-6, (rows, classes, dtype)
+        got.backward()
+        ref = lg.float().requires_grad_(True)
+        F.cross_entropy(ref, tgt).backward()
+        torch.testing.assert_close(l2.grad.float(), ref.grad, rtol=2e-2 if dtype == torch.bfloat16 else 1e-4, atol=1e-6)
+    # MNIST-PVR HL fused with the loss
+    bv, sv = torch.randint(0, 10, (300, 4), generator=g).to(DEV), torch.randint(0, 10, (300, 4), generator=g).to(DEV)
+    lg = torch.randn(300, 10, generator=g).to(DEV)
+    for var in (-1, 0, 2):
+        loss, hl = ops.hl_cross_entropy(lg, ("pvr", bv, sv if var >= 0 else None, var))
+        want_hl = ops.hl_pvr(bv, sv if var >= 0 else None, var)
+        assert torch.equal(hl, want_hl)
+        assert abs(loss.item() - F.cross_entropy(lg, want_hl).item()) < 1e-5
+    ops.raise_on_index_error(DEV)
+    # IOI HL fused with the loss on padded bf16 logits: columns >= V are ignored and get a zero gradient
+    V, Vp = 50257, 50304
+    (bx, _, _), names = R.synthetic_ioi(16, 3, one_hot=False)
+    (sx, _, _), _ = R.synthetic_ioi(16, 4, one_hot=False)
+    bx, sx, names_d = bx.to(DEV), sx.to(DEV), names.to(DEV)
+    lg = (torch.randn(16, Vp, generator=g) * 2).to(DEV).bfloat16()
+    lg[:, V:] = 50.0                                     # garbage in the padding must not matter
+    for node in ("hook_duplicate", "hook_s_inhibition", "hook_name_mover", "all_nodes_hook"):
+        l2 = lg.clone().requires_grad_(True)
+        loss, am = ops.hl_cross_entropy(l2, ("ioi", bx, sx, node, names_d, V), classes=V)
+        want_am = ops.hl_ioi_last_argmax(bx, sx, node, names_d, V)
+        assert torch.equal(am, want_am)
+        ref = lg[:, :V].float().requires_grad_(True)
+        want = F.cross_entropy(ref, want_am)
+        assert abs(loss.item() - want.item()) <= 2e-5 * abs(want.item())
+        loss.backward()
+        want.backward()
+        assert float(l2.grad[:, V:].abs().max()) == 0.0
+        torch.testing.assert_close(l2.grad[:, :V].float(), ref.grad, rtol=2e-2, atol=1e-7)
+    # a target outside [0, classes) sets the error flag (torch raises there)
+    bad = torch.tensor([3, 11, 2], device=DEV)
+    ops.cross_entropy(torch.randn(3, 10, device=DEV), bad)
+    with pytest.raises(IndexError):
+        ops.raise_on_index_error(DEV)

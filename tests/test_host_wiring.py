@@ -264,13 +264,16 @@ def test_ctypes_structs_match_the_header(tmp_path):
     src = tmp_path / "sizes.c"
     src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "iit_b200.h"\nint main(void) {\n'
                    '  printf("%zu %zu %zu\\n", sizeof(iit_box_t), sizeof(iit_conv_t), sizeof(iit_relayout_t));\n'
+                   '  printf("%zu %zu %zu %zu\\n", sizeof(iit_hl_spec_t), offsetof(iit_hl_spec_t, base), offsetof(iit_hl_spec_t, n_names),\n'
+                   '         offsetof(iit_hl_spec_t, d_vocab));\n'
                    '  printf("%zu %zu %zu %zu\\n", offsetof(iit_relayout_t, stride), offsetof(iit_relayout_t, k),\n'
                    '         offsetof(iit_relayout_t, dtype), offsetof(iit_relayout_t, out_pitch));\n  return 0;\n}\n')
     exe = tmp_path / "sizes"
     subprocess.check_call(["gcc", "-I", os.path.join(root, "include"), str(src), "-o", str(exe)])
     out = subprocess.check_output([str(exe)], text=True).split()
-    sizes, offs = [int(v) for v in out[:3]], [int(v) for v in out[3:]]
+    sizes, hl, offs = [int(v) for v in out[:3]], [int(v) for v in out[3:7]], [int(v) for v in out[7:]]
     assert sizes == [C.sizeof(_lib.Box), C.sizeof(_lib.Conv), C.sizeof(_lib.Relayout)]
+    assert hl == [C.sizeof(_lib.HlSpec), _lib.HlSpec.base.offset, _lib.HlSpec.n_names.offset, _lib.HlSpec.d_vocab.offset]
     assert offs == [_lib.Relayout.stride.offset, _lib.Relayout.k.offset, _lib.Relayout.dtype.offset, _lib.Relayout.out_pitch.offset]
 
 
