@@ -68,6 +68,9 @@ SIGNATURES = {
     "iit_conv2d_fprop_tc": [_vp, _vp, _vp, _ConvP, _vp, _vp, _vp],
     "iit_conv2d_dgrad_tc": [_vp, _vp, _vp, _ConvP, _vp],
     "iit_conv2d_dgrad_tc_accumulate": [_vp, _vp, _vp, _ConvP, _vp],
+    "iit_conv2d_patch_fusable": [_ConvP],
+    "iit_conv2d_fprop_tc_patch": [_vp, _vp, _vp, _ConvP, _vp, _vp, _vp, C.POINTER(C.c_int32), _vp],
+    "iit_bn_act_bwd_apply_box": [_vp, _vp, _vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, C.POINTER(C.c_int32), _vp],
     "iit_gemm_bias_act_tc": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp],
     "iit_gemm_dgrad_gelu_tc": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _vp],
     "iit_conv2d_wgrad_tc_scratch_bytes": [_ConvP],
@@ -133,7 +136,8 @@ _RESTYPES = {"iit_last_error": C.c_char_p, "iit_launch_count": C.c_ulonglong,
              "iit_kernel_variant_name": C.c_char_p, "iit_kernel_variant_count": C.c_ulonglong,
              "iit_conv2d_wgrad_scratch_bytes": C.c_size_t, "iit_conv2d_wgrad_tc_scratch_bytes": C.c_size_t,
              "iit_stem_wgrad_s2d_scratch_bytes": C.c_size_t}
-_NO_STATUS = set(_RESTYPES) | {"iit_version", "iit_kernel_variant_slots", "iit_conv2d_tc_supported", "iit_conv_win_enable", "iit_conv_pair_enable"}
+_NO_STATUS = set(_RESTYPES) | {"iit_version", "iit_kernel_variant_slots", "iit_conv2d_tc_supported", "iit_conv_win_enable", "iit_conv_pair_enable",
+                               "iit_conv2d_patch_fusable"}
 
 
 def _load():

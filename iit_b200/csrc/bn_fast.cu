@@ -250,12 +250,17 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_fast_kernel(const T* __rest
 // dx = gamma * invstd * (g - dbeta/rows - xhat * dgamma/rows),  g = relu'(y) * dy;  dres = g
 // Two packs per thread and iteration are loaded before either is used (48 KB of loads in flight per SM at 3 blocks; with one
 // pack and 4 blocks the kernel was latency-bound: 24.4 -> 24.1 ms per step).
+// `zb`: the box of x (rows p, columns q of the hw x w image, channels) that an interchange patch overwrote in the forward
+// pass: its gradient is zero (the patched values are constants; CopySlices backward), written here instead of by a
+// separate zeroing kernel on dx.
+struct ZeroBox { int on, hw, w, p0, p1, q0, q1, c0, c1; };
+
 template <typename T>
 __global__ void __launch_bounds__(256, 3)
 bn_bwd_apply_fast_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x, T* __restrict__ dx,
                          T* __restrict__ dres, int64_t npacks, int C, float inv_rows, const float* __restrict__ mean,
                          const float* __restrict__ invstd, const float* __restrict__ gamma, const double* __restrict__ dgamma,
-                         const double* __restrict__ dbeta, int relu, const uint8_t* __restrict__ mask) {
+                         const double* __restrict__ dbeta, int relu, const uint8_t* __restrict__ mask, ZeroBox zb) {
   constexpr int NP = Pack<T>::N;
   constexpr int U = 2;
   const int64_t tid = (int64_t)blockIdx.x * 256 + threadIdx.x, stride = (int64_t)gridDim.x * 256;
@@ -287,6 +292,13 @@ bn_bwd_apply_fast_kernel(const T* __restrict__ dy, const T* __restrict__ y, cons
     if (dres) Pack<T>::store(dres + i * NP, g);
 #pragma unroll
     for (int j = 0; j < NP; ++j) o[j] = k[j] * (g[j] - dbn[j] - (xv[j] - mu[j]) * c1[j]);
+    if (zb.on && c0 >= zb.c0 && c0 < zb.c1) {       // channel ranges are multiples of the pack width (host-checked)
+      const int pix = (int)(((i * NP) / C) % zb.hw), pp = pix / zb.w, qq = pix - pp * zb.w;
+      if (pp >= zb.p0 && pp < zb.p1 && qq >= zb.q0 && qq < zb.q1) {
+#pragma unroll
+        for (int j = 0; j < NP; ++j) o[j] = 0.f;
+      }
+    }
     Pack<T>::store(dx + i * NP, o);
   };
   int64_t i = tid;
@@ -615,12 +627,18 @@ int bn_bwd_reduce_fast(const void* dy, const void* y, const void* x, int dtype, 
 
 int bn_bwd_apply_fast(const void* dy, const void* y, const void* x, void* dx, void* dres, int dtype, int64_t rows, int C,
                       const float* mean, const float* invstd, const float* gamma, const double* dgamma, const double* dbeta,
-                      int relu, const uint8_t* mask, cudaStream_t st) {
+                      int relu, const uint8_t* mask, cudaStream_t st, const int* zero_box_hw) {
   const int64_t npacks = rows * C / pack_n(dtype);
+  ZeroBox zb{};
+  if (zero_box_hw != nullptr) {     // h, w, p0, p1, q0, q1, c0, c1
+    zb.on = 1; zb.hw = zero_box_hw[0] * zero_box_hw[1]; zb.w = zero_box_hw[1];
+    zb.p0 = zero_box_hw[2]; zb.p1 = zero_box_hw[3]; zb.q0 = zero_box_hw[4]; zb.q1 = zero_box_hw[5];
+    zb.c0 = zero_box_hw[6]; zb.c1 = zero_box_hw[7];
+  }
   IIT_DISPATCH_DTYPE(dtype, T, {
     bn_bwd_apply_fast_kernel<T><<<grid_for(npacks, 256 * 2, 6), 256, 0, st>>>((const T*)dy, (const T*)y, (const T*)x, (T*)dx, (T*)dres,
                                                                           npacks, C, 1.f / (float)rows, mean, invstd, gamma, dgamma,
-                                                                          dbeta, relu, mask);
+                                                                          dbeta, relu, mask, zb);
   })
   IIT_LAUNCH_CHECK("iit_bn_act_bwd_apply");
   return 0;

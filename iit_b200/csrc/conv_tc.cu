@@ -47,8 +47,10 @@ struct TcParams {
   const __nv_bfloat16* aux;       // laid out like `out`: the residual added (TC_EPI_BIAS, may be null) or the pre-activation
                                   // whose GELU derivative multiplies the result (TC_EPI_GELU_BWD)
   __nv_bfloat16* out2;            // TC_EPI_GELU: receives the pre-activation (may be null: not kept)
+  int box[6];                     // TC_EPI_PATCH: output rows p in [box0, box1), columns q in [box2, box3), channels in [box4, box5)
+                                  // take their value from `aux` (the cached source activation) instead of the convolution
 };
-enum { TC_EPI_NONE = 0, TC_EPI_BIAS = 1, TC_EPI_GELU = 2, TC_EPI_GELU_BWD = 3 };
+enum { TC_EPI_NONE = 0, TC_EPI_BIAS = 1, TC_EPI_GELU = 2, TC_EPI_GELU_BWD = 3, TC_EPI_PATCH = 4 };
 
 // gelu_new and its derivative with tanh.approx (2^-11 relative, below bf16's 2^-9 rounding): the same arithmetic as the
 // element-wise kernels of transformer.cu
@@ -268,7 +270,9 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
             }
           }
           const int64_t own = (((int64_t)n * p.OH + (pp * p.out_mul + p.out_oh)) * p.OW + (qq * p.out_mul + p.out_ow)) * p.Cout + co0 + c;
-          if (p.aux != nullptr && ok) {
+          const bool in_pq = p.epi != TC_EPI_PATCH || (pp >= p.box[0] && pp < p.box[1] && qq >= p.box[2] && qq < p.box[3] &&
+                                                       co0 + c < p.box[5] && co0 + c + 32 > p.box[4]);
+          if (p.aux != nullptr && ok && in_pq) {
 #pragma unroll
             for (int j = 0; j < 32; j += 8) {
               const uint4 a4 = *reinterpret_cast<const uint4*>(p.aux + own + j);
@@ -276,7 +280,11 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
 #pragma unroll
               for (int h2 = 0; h2 < 4; ++h2) {
                 const float a0 = __uint_as_float(w4[h2] << 16), a1 = __uint_as_float(w4[h2] & 0xffff0000u);
-                if (p.epi == TC_EPI_GELU_BWD) {
+                if (p.epi == TC_EPI_PATCH) {      // the interchange: dst[box] = src[box], inside the producing layer
+                  const int ch = co0 + c + j + 2 * h2;
+                  if (ch >= p.box[4] && ch < p.box[5]) v[j + 2 * h2] = __float_as_uint(a0);
+                  if (ch + 1 >= p.box[4] && ch + 1 < p.box[5]) v[j + 2 * h2 + 1] = __float_as_uint(a1);
+                } else if (p.epi == TC_EPI_GELU_BWD) {
                   v[j + 2 * h2] = __float_as_uint(__uint_as_float(v[j + 2 * h2]) * tc_gelu_grad(a0));
                   v[j + 2 * h2 + 1] = __float_as_uint(__uint_as_float(v[j + 2 * h2 + 1]) * tc_gelu_grad(a1));
                 } else {
@@ -715,7 +723,10 @@ static int conv_tc_fprop(const void* x, const void* w_krsc, void* y, const iit_c
                          double* bn_sq, const TcParams* epi = nullptr, const char* name = "iit_conv2d_fprop_tc") {
   if (check_tc_ptrs(x, w_krsc, y, name)) return 1;
   TcParams tp{};
-  if (epi != nullptr) { tp.epi = epi->epi; tp.bias = epi->bias; tp.aux = epi->aux; tp.out2 = epi->out2; }
+  if (epi != nullptr) {
+    tp.epi = epi->epi; tp.bias = epi->bias; tp.aux = epi->aux; tp.out2 = epi->out2;
+    for (int i = 0; i < 6; ++i) tp.box[i] = epi->box[i];
+  }
   tp.N = d->n; tp.P = d->p; tp.Q = d->q; tp.OH = d->p; tp.OW = d->q;
   tp.out_mul = 1; tp.out_oh = 0; tp.out_ow = 0; tp.in_mul = d->stride;
   tp.Cin = d->c; tp.Cout = d->k;
@@ -1114,6 +1125,28 @@ extern "C" int iit_conv2d_dgrad_tc(const void* dy, const void* w_crsk, void* dx,
 
 extern "C" int iit_conv2d_dgrad_tc_accumulate(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream) {
   return dgrad_tc_entry(dy, w_crsk, dx, d, stream, true, "iit_conv2d_dgrad_tc_accumulate");
+}
+
+// ---- the interchange patch inside the producing convolution (north_star (a)) ---------------------------------------------
+extern "C" int iit_conv2d_patch_fusable(const iit_conv_t* d) {
+  // the tiled kernel carries the epilogue; the shifted-window kernel (64 -> 64 on small images, the stem) does not
+  return d && iit_conv2d_tc_supported(d, IIT_BF16) && !(g_use_win && conv_win_3x3_supported(d)) ? 1 : 0;
+}
+
+extern "C" int iit_conv2d_fprop_tc_patch(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, double* bn_sum,
+                                         double* bn_sqsum, const void* src, const int32_t* box6, void* stream) {
+  const char* name = "iit_conv2d_fprop_tc_patch";
+  IIT_REQUIRE(x && w_krsc && y && d && src && box6, "%s: null pointer", name);
+  IIT_REQUIRE((bn_sum == nullptr) == (bn_sqsum == nullptr), "%s: bn_sum and bn_sqsum come together", name);
+  IIT_REQUIRE(iit_conv2d_patch_fusable(d), "%s: this convolution runs on a kernel without the patch epilogue", name);
+  IIT_REQUIRE(box6[0] >= 0 && box6[1] <= d->p && box6[2] >= 0 && box6[3] <= d->q && box6[4] >= 0 && box6[5] <= d->k &&
+              box6[0] <= box6[1] && box6[2] <= box6[3] && box6[4] <= box6[5], "%s: box outside the output tensor", name);
+  IIT_REQUIRE((reinterpret_cast<uintptr_t>(src) & 15) == 0, "%s: pointers must be 16-byte aligned", name);
+  TcParams e{};
+  e.epi = TC_EPI_PATCH;
+  e.aux = (const __nv_bfloat16*)src;
+  for (int i = 0; i < 6; ++i) e.box[i] = box6[i];
+  return conv_tc_fprop(x, w_krsc, y, d, as_stream(stream), bn_sum, bn_sqsum, &e, name);
 }
 
 // ---- the transformer's linear maps with their element-wise neighbours in the GEMM epilogue ------------------------------

@@ -479,7 +479,7 @@ int bn_bwd_reduce_fast(const void* dy, const void* y, const void* x, int dtype, 
                        const float* invstd, int relu, double* dgamma, double* dbeta, const uint8_t* mask, cudaStream_t st);
 int bn_bwd_apply_fast(const void* dy, const void* y, const void* x, void* dx, void* dres, int dtype, int64_t rows, int C,
                       const float* mean, const float* invstd, const float* gamma, const double* dgamma, const double* dbeta,
-                      int relu, const uint8_t* mask, cudaStream_t st);
+                      int relu, const uint8_t* mask, cudaStream_t st, const int* zero_box_hw = nullptr);
 
 // fp64 per-channel sums of a BatchNorm backward -> fp32 parameter gradients, written or accumulated in place (the
 // optimizer's flat gradient buffer), and the layer's persistent accumulator cleared for its next backward: one launch
@@ -603,6 +603,22 @@ extern "C" int iit_bn_act_bwd_apply(const void* dy, const void* y, const void* x
   })
   IIT_LAUNCH_CHECK("iit_bn_act_bwd_apply");
   return 0;
+}
+
+extern "C" int iit_bn_act_bwd_apply_box(const void* dy, const void* y, const void* x, void* dx, void* dres, int dtype, int64_t rows,
+                                        int c, const float* mean, const float* invstd, const float* gamma, const double* dgamma,
+                                        const double* dbeta, int relu, const uint8_t* relu_mask, int h, int w, const int32_t* box6,
+                                        void* stream) {
+  const char* name = "iit_bn_act_bwd_apply_box";
+  IIT_REQUIRE(dy && x && dx && mean && invstd && gamma && dgamma && dbeta && (!relu || y) && box6, "%s: null pointer", name);
+  IIT_REQUIRE(h >= 1 && w >= 1 && rows % ((int64_t)h * w) == 0, "%s: rows must be whole %d x %d images", name, h, w);
+  const int np = dtype == IIT_BF16 ? 8 : 4;
+  IIT_REQUIRE(box6[4] % np == 0 && box6[5] % np == 0, "%s: the channel range must be a multiple of %d", name, np);
+  IIT_REQUIRE(bn_fast_ok(dtype, c, dy, y, x, dx, dres) && bn_fast_ok(dtype, c, mean, invstd, gamma, nullptr, nullptr),
+              "%s: 16-byte aligned tensors with a channel count the vector kernels take only", name);
+  const int zb[8] = {h, w, box6[0], box6[1], box6[2], box6[3], box6[4], box6[5]};
+  return bn_bwd_apply_fast(dy, y, x, dx, dres, dtype, rows, c, mean, invstd, gamma, dgamma, dbeta, relu, relu_mask,
+                           as_stream(stream), zb);
 }
 
 extern "C" int iit_relu_fwd(const void* x, void* y, int dtype, int64_t n, void* stream) {

@@ -56,6 +56,21 @@ class HookPoint(nn.Module):
         keep a fused backward across this hook point."""
         return not self._bwd and all(getattr(fn, "_iit_patch", False) for fn, _, _ in self._fwd)
 
+    def fusable_patch(self):
+        """(cached source activation, TorchIndex) when the ONLY thing attached here is one interchange patch of a model pair
+        (base_model_pair.make_ll_ablation_hook) whose source run has cached this hook point -- the producing layer may then
+        apply the patch itself and skip the hook call; None otherwise."""
+        if self._bwd or len(self._fwd) != 1:
+            return None
+        tag = getattr(self._fwd[0][0], "_iit_patch", None)
+        if not isinstance(tag, tuple):
+            return None
+        pair, node = tag
+        cache = getattr(pair, "ll_cache", None)
+        if node.subspace is not None or cache is None or self.name not in cache:
+            return None
+        return cache[self.name], node.index
+
     def clear_context(self):
         self.ctx = {}
 

@@ -196,7 +196,9 @@ class BaseModelPair(ABC):
             inplace = bool(getattr(hook, "inplace_ok", False)) or not (t.is_grad_enabled() and hook_point_out.requires_grad)
             return ops.patch(hook_point_out, self.ll_cache[hook.name], index, inplace=inplace)
 
-        ll_ablation_hook._iit_patch = True      # HookPoint.only_patch_hooks
+        # (pair, node): lets a layer that can apply the patch itself find its source and index (HookPoint.fusable_patch), and
+        # marks the hook as a pure interchange (HookPoint.only_patch_hooks)
+        ll_ablation_hook._iit_patch = (self, ll_node)
         return ll_ablation_hook
 
     def get_IIT_loss_over_batch(self, base_input, ablation_input, hl_node, loss_fn):

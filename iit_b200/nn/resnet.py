@@ -77,13 +77,43 @@ class Conv2d(nn.Module):
             self._prep["stem"] = ent
         return ent[1]
 
-    def forward(self, x, bn_sums=None, act_dtype=None, slot=None):
+    def forward(self, x, bn_sums=None, act_dtype=None, slot=None, patch=None):
         if act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES and self.is_stem():
             s2d = self.weight.shape[0] == 64 and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0
             return ops.stem_conv(x, self.weight, self.stem_filter(s2d), bn_sums)
         krsc, crsk = self.prepared(x.dtype)
         wgrad_buf = ops.direct_grad(self.weight) if torch.is_grad_enabled() else None
-        return ops.conv2d(x, self.weight, krsc, crsk, self.stride, self.pad, bn_sums, wgrad_buf, slot)
+        return ops.conv2d(x, self.weight, krsc, crsk, self.stride, self.pad, bn_sums, wgrad_buf, slot, patch)
+
+    def plan_patch(self, x, hook_point):
+        """How an interchange patch attached to this convolution's hook point can be applied without the hook call:
+        ("whole", src): the whole output is replaced -- the convolution need not run; ("box", src, box6): in the convolution's
+        epilogue; None: call the hook (PATCH_IN_LAYER off, other hooks attached, an index with no box form, a kernel without
+        the epilogue, fp32 activations)."""
+        if not PATCH_IN_LAYER:
+            return None
+        fp = hook_point.fusable_patch()
+        if fp is None:
+            return None
+        src, index = fp
+        shape = ops.conv_out_shape(x, self.weight, self.stride, self.pad)
+        if tuple(src.shape) != shape or not ops._is_cl(src):
+            return None
+        spans = index.box(shape)
+        if spans is None:
+            return None
+        if all(st == 0 and ext == dim for (st, ext), dim in zip(spans, shape)):
+            return ("whole", src)
+        (n0, ne), (c0, ce), (h0, he), (w0, we) = spans
+        if n0 != 0 or ne != shape[0] or c0 % 8 or ce % 8 or src.dtype != torch.bfloat16 or self.is_stem():
+            return None
+        xin = x if x.dtype == torch.bfloat16 else None
+        if xin is None or not ops.conv_patch_fusable(xin, self.weight, self.stride, self.pad):
+            return None
+        return ("box", src, (h0, h0 + he, w0, w0 + we, c0, c0 + ce))
+
+
+PATCH_IN_LAYER = True    # interchange patches on convolution hook points run inside the convolution (tests flip it to compare)
 
 
 class BatchNorm2d(nn.Module):
@@ -120,13 +150,13 @@ class BatchNorm2d(nn.Module):
         gg, gb = ops.direct_grad(self.weight), ops.direct_grad(self.bias)
         return self.grad_accumulator(x.device), ((gg, gb) if gg is not None and gb is not None else None)
 
-    def forward(self, x, residual=None, relu=False, sums=None, slot=None):
+    def forward(self, x, residual=None, relu=False, sums=None, slot=None, zero_box=None):
         acc = self.accumulator(x.device) if (self.training and x.is_cuda) else None
         bacc, pgrads = self.backward_buffers(x)
         try:
             return ops.bn_act(x, self.weight, self.bias, residual, self.running_mean, self.running_var, self.training,
                               self.momentum, self.eps, relu, sums, acc, self.num_batches_tracked if self.training else None,
-                              bacc, pgrads, slot)
+                              bacc, pgrads, slot, zero_box)
         except Exception:
             if acc is not None:
                 acc.zero_()      # a failed launch sequence must not leave partial sums behind
@@ -204,9 +234,18 @@ def _conv_bn(conv: Wrapped, bn: Wrapped, x, residual=None, relu=False, fuse_stat
     can modify the conv output first (the patch site): then they are taken from the hooked tensor."""
     bnm = bn.mod
     sums = None
-    if bnm.training and fuse_stats and not conv.hook_point.has_hooks():
+    plan = conv.mod.plan_patch(x, conv.hook_point) if (act_dtype is None and conv.hook_point.has_hooks()) else None
+    if plan is not None and plan[0] == "whole":
+        # the whole output is replaced by the cached source activation: the convolution's result (and its gradient) would be
+        # discarded, so it does not run; the BatchNorm takes its statistics from the patched tensor
+        return bnm(plan[1], residual=residual, relu=relu, sums=None, slot=res_slot)
+    if bnm.training and fuse_stats and (plan is not None or not conv.hook_point.has_hooks()):
         sums = bnm.accumulator(x.device) if x.is_cuda else ops.new_bn_sums(bnm.c, x.device)
     try:
+        if plan is not None:     # the patch runs in the convolution's epilogue; the statistics are of the patched values
+            y = conv.mod(x, sums, slot=in_slot, patch=(plan[1], plan[2]))
+            zero_box = plan[2] if (torch.is_grad_enabled() and y.requires_grad) else None
+            return bnm(y, residual=residual, relu=relu, sums=sums, slot=res_slot, zero_box=zero_box)
         y = conv.hook_point(conv.mod(x, sums, slot=in_slot) if act_dtype is None else conv.mod(x, sums, act_dtype))
     except Exception:
         if sums is not None:

@@ -438,7 +438,7 @@ class GradSlot:
 
 class _ConvFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums, wgrad_buf, slot=None):
+    def forward(ctx, x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums, wgrad_buf, slot=None, patch=None):
         _require_cuda(x, weight)
         x = _cl(x)
         k, c, r, s = weight.shape
@@ -448,7 +448,13 @@ class _ConvFn(torch.autograd.Function):
         if bn_sums is not None:
             s0, s1 = bn_sums[0], bn_sums[1]
         tc = USE_TENSOR_CORES and bool(_lib.lib.iit_conv2d_tc_supported(C.byref(d), _dt(x)))
-        if tc:  # tcgen05 + TMA implicit GEMM; BN statistics (if wanted) by the statistics kernel
+        if patch is not None:   # (cached source activation, box6): the interchange runs in this convolution's epilogue
+            src, box6 = patch
+            if not tc or src.shape != y.shape or src.dtype != y.dtype or not _is_cl(src):
+                raise RuntimeError("conv2d: a fused patch needs the tensor-core path and a source activation laid out like the output")
+            call("iit_conv2d_fprop_tc_patch", _p(x), _p(w_krsc), _p(y), C.byref(d), _p(s0), _p(s1), _p(src),
+                 (C.c_int32 * 6)(*box6), _stream())
+        elif tc:  # tcgen05 + TMA implicit GEMM; BN statistics (if wanted) by the statistics kernel
             call("iit_conv2d_fprop_tc", _p(x), _p(w_krsc), _p(y), C.byref(d), _p(s0), _p(s1), _stream())
         else:
             call("iit_conv2d_fprop", _p(x), _p(w_krsc), _p(y), C.byref(d), _dt(x), _p(s0), _p(s1), _stream())
@@ -495,13 +501,29 @@ class _ConvFn(torch.autograd.Function):
                 scratch = torch.empty(need, dtype=torch.uint8, device=x.device) if need else None
                 call("iit_conv2d_wgrad", _p(dy), _p(x), _p(dwb), C.byref(d), _dt(x), _p(scratch), need, _stream())
             dw = dwb.permute(0, 3, 1, 2)  # [K,C,R,S] view with channels-last strides, like the parameter
-        return dx, dw, None, None, None, None, None, None, None
+        return dx, dw, None, None, None, None, None, None, None, None
 
 
-def conv2d(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums=None, wgrad_buf=None, slot=None):
+def conv2d(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums=None, wgrad_buf=None, slot=None, patch=None):
     """`wgrad_buf`: see direct_grad -- the weight gradient is added into it and autograd receives None.
-    `slot`: see GradSlot -- shared with the other consumer of `x` in the same residual block."""
-    return _ConvFn.apply(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums, wgrad_buf, slot)
+    `slot`: see GradSlot -- shared with the other consumer of `x` in the same residual block.
+    `patch`: (src, (p0, p1, q0, q1, c0, c1)) -- output rows / columns / channels inside the box take src's values, in the
+    kernel's epilogue (iit_conv2d_fprop_tc_patch). The caller must see to it that the gradient reaching this convolution is
+    zero inside the box (bn_act(..., zero_box=...) does it in the BatchNorm backward's dx store)."""
+    return _ConvFn.apply(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums, wgrad_buf, slot, patch)
+
+
+def conv_out_shape(x, weight, stride, pad):
+    n, _, h, w = x.shape
+    k, _, r, s_ = weight.shape
+    return (n, k, (h + 2 * pad - r) // stride + 1, (w + 2 * pad - s_) // stride + 1)
+
+
+def conv_patch_fusable(x, weight, stride, pad) -> bool:
+    if not (USE_TENSOR_CORES and x.is_cuda and x.dtype == torch.bfloat16):
+        return False
+    d = _conv_desc(x, weight.shape[0], weight.shape[2], weight.shape[3], stride, pad)
+    return bool(_lib.lib.iit_conv2d_patch_fusable(C.byref(d)))
 
 
 STEM_K = 192
@@ -653,7 +675,7 @@ BN_RELU_MASK = True     # BatchNorm+ReLU forward keeps a bit mask of the positiv
 class _BNActFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums, acc, tracked,
-                bacc, pgrads, slot=None):
+                bacc, pgrads, slot=None, zero_box=None):
         _require_cuda(x, gamma, beta, residual)
         x = _cl(x)
         n, c, h, w = x.shape
@@ -688,6 +710,7 @@ class _BNActFn(torch.autograd.Function):
         ctx.relu, ctx.training, ctx.has_res = relu, training, residual is not None
         ctx.bacc, ctx.pgrads = bacc, pgrads
         ctx.slot = slot if residual is not None else None
+        ctx.zero_box = zero_box
         return y
 
     @staticmethod
@@ -706,8 +729,12 @@ class _BNActFn(torch.autograd.Function):
             dres = torch.empty_like(x) if ctx.has_res else None
             # eval mode: statistics are constants, so the two correction terms vanish
             corr = red if ctx.training else torch.zeros_like(red)
-            call("iit_bn_act_bwd_apply", _p(dy), _p(y), _p(x), _p(dx), _p(dres), _dt(x), rows, c, _p(mean), _p(invstd),
-                 _p(gamma), _p(corr[0]), _p(corr[1]), int(ctx.relu), _p(mask), st)
+            if ctx.zero_box is not None:    # x was patched inside its convolution: zero gradient inside the box, written here
+                call("iit_bn_act_bwd_apply_box", _p(dy), _p(y), _p(x), _p(dx), _p(dres), _dt(x), rows, c, _p(mean), _p(invstd),
+                     _p(gamma), _p(corr[0]), _p(corr[1]), int(ctx.relu), _p(mask), h, w, (C.c_int32 * 6)(*ctx.zero_box), st)
+            else:
+                call("iit_bn_act_bwd_apply", _p(dy), _p(y), _p(x), _p(dx), _p(dres), _dt(x), rows, c, _p(mean), _p(invstd),
+                     _p(gamma), _p(corr[0]), _p(corr[1]), int(ctx.relu), _p(mask), st)
             dgamma, dbeta = _bn_param_grads(red, c, ctx.pgrads, ctx.bacc is not None, st)
         except Exception:
             if ctx.bacc is not None:
@@ -715,7 +742,7 @@ class _BNActFn(torch.autograd.Function):
             raise
         if ctx.slot is not None and dres is not None and USE_GRAD_SLOTS:
             ctx.slot.put(dres)       # the block input's other consumer (conv1) adds its gradient onto this (GradSlot)
-        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None, None, None, None, None, None
+        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None, None, None, None, None, None, None
 
 
 def _bn_param_grads(red, c, pgrads, clear, st):
@@ -730,13 +757,13 @@ def _bn_param_grads(red, c, pgrads, clear, st):
 
 
 def bn_act(x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums=None, acc=None,
-           tracked=None, bacc=None, pgrads=None, slot=None):
+           tracked=None, bacc=None, pgrads=None, slot=None, zero_box=None):
     """`sums`: statistics already accumulated by the producing convolution's epilogue; `acc`: the layer's persistent
     fp64 accumulator [2, C] (kept zero between uses; `sums` may be it); `tracked`: num_batches_tracked, incremented by the
     finalize kernel; `bacc`: the same kind of accumulator for the backward's sums; `pgrads`: (gamma, beta) gradient buffers
     to add into (direct_grad)."""
     return _BNActFn.apply(x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums, acc, tracked,
-                          bacc, pgrads, slot)
+                          bacc, pgrads, slot, zero_box)
 
 
 class _BNReluPoolFn(torch.autograd.Function):

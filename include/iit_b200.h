@@ -206,6 +206,15 @@ int iit_conv2d_dgrad_tc(const void* dy, const void* w_crsk, void* dx, const iit_
  * is added straight onto the first: the sum autograd would otherwise make with a separate element-wise kernel
  * (torchvision BasicBlock.forward `out += identity`, its backward). */
 int iit_conv2d_dgrad_tc_accumulate(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream);
+/* The interchange patch INSIDE the hooked layer (north_star (a); replaces the Python forward hook of
+ * base_model_pair.py:151-163 for a convolution's hook point): iit_conv2d_fprop_tc whose epilogue, for output rows p in
+ * [box6[0], box6[1]), columns q in [box6[2], box6[3]) and channels in [box6[4], box6[5]) of every image, stores src's value
+ * (the cached source-run activation, laid out like y) instead of the convolution's; the BatchNorm sums are taken from the
+ * patched values, as a BatchNorm after the hook would see them. iit_conv2d_patch_fusable: 1 when the descriptor runs on the
+ * kernel that carries this epilogue. */
+int iit_conv2d_patch_fusable(const iit_conv_t* d);
+int iit_conv2d_fprop_tc_patch(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, double* bn_sum, double* bn_sqsum,
+                              const void* src, const int32_t* box6, void* stream);
 /* The transformer's linear maps (transformer_lens HookedTransformer: attention projections, MLP, unembedding; reference
  * train_ioi.py:30-34) on the same tensor-core GEMM with their element-wise neighbours applied to the fp32 accumulator in the
  * epilogue, before the one rounding to bf16:
@@ -313,6 +322,14 @@ int iit_bn_act_bwd_apply(const void* dy, const void* y, const void* x, void* dx,
 /* y = x / scale, element-wise (n a multiple of 4; y may alias x). The forward hook of the stop-gradient pair
  * (`hook_point_out / scale`, iit/model_pairs/stop_grad_pair.py:37-44); its backward is the same call on the gradient. */
 int iit_div_scalar(const void* x, void* y, int dtype, int64_t n, float scale, void* stream);
+/* iit_bn_act_bwd_apply for a BatchNorm whose input was interchange-patched inside the producing convolution
+ * (iit_conv2d_fprop_tc_patch): dx is written as ZERO for rows p in [box6[0], box6[1]), columns q in [box6[2], box6[3]) of every
+ * h x w image and channels in [box6[4], box6[5]) -- the CopySlices backward of `out[idx] = cache[idx]`
+ * (base_model_pair.py:157-161) without a separate zeroing kernel. Vector path only (16-byte aligned, bf16 c % 8 / fp32 c % 4). */
+int iit_bn_act_bwd_apply_box(const void* dy, const void* y, const void* x, void* dx, void* dres, int dtype, int64_t rows, int c,
+                             const float* mean, const float* invstd, const float* gamma, const double* dgamma,
+                             const double* dbeta, int relu, const uint8_t* relu_mask, int h, int w, const int32_t* box6,
+                             void* stream);
 int iit_relu_fwd(const void* x, void* y, int dtype, int64_t n, void* stream);
 int iit_relu_bwd(const void* dy, const void* y, void* dx, int dtype, int64_t n, void* stream);
 int iit_add_relu_fwd(const void* a, const void* b, void* y, int dtype, int64_t n, int relu, void* stream);

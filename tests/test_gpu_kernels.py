@@ -991,3 +991,69 @@ def test_fused_hl_and_cross_entropy_kernel():
     ops.cross_entropy(torch.randn(3, 10, device=DEV), bad)
     with pytest.raises(IndexError):
         ops.raise_on_index_error(DEV)
+
+
+def test_patch_inside_the_convolution_matches_the_hook():
+    """north_star (a): the interchange on a convolution's hook point applied in that convolution's epilogue
+    (iit_conv2d_fprop_tc_patch; BatchNorm sums of the patched values fused; zero gradient inside the box written by the
+    BatchNorm backward) against the Python hook calling the standalone patch kernel. Whole-tensor patches skip the convolution.
+    Eval mode (no batch statistics): outputs equal bit for bit. Train mode: loss and gradients agree to bf16 rounding, and the
+    fused step launches no patch / zeroing / statistics kernel."""
+    from iit_b200 import ops
+    from iit_b200.model_pairs import StrictIITModelPair
+    from iit_b200.model_pairs.nodes import LLNode
+    from iit_b200.nn import resnet
+    from iit_b200.tasks.mnist_pvr.get_alignment import get_alignment
+    from iit_b200.utils.index import Ix
+    hook = "mod.layer3.mod.1.mod.conv2.hook_point"
+    Bn = 64
+    base = tuple(t.to(DEV) for t in R.synthetic_pvr(Bn, 100))
+    src = tuple(t.to(DEV) for t in R.synthetic_pvr(Bn, 200))
+    res = {}
+    for fused in (True, False):
+        resnet.PATCH_IN_LAYER = fused
+        try:
+            out = {}
+            for mode in ("q", "c"):
+                ll, hl, corr = get_alignment("mnist_pvr", {"mode": mode, "hook_point": hook, "input_shape": (1, 3, 56, 56)}, dtype=torch.bfloat16)
+                ll.load_state_dict(R.resnet18_state_dict(0))
+                whole = [LLNode("mod.layer2.mod.0.mod.conv2.hook_point", Ix[[None]]), LLNode("mod.layer4.mod.1.mod.conv1.hook_point", Ix[[None]])]
+                pair = StrictIITModelPair(hl, ll, corr, training_args={"lr": 1e-3, "nodes_not_in_circuit": whole})
+                opt = pair.make_optimizer()
+                ll.eval()
+                with torch.no_grad():
+                    out[mode, "eval"] = [pair.do_intervention(base, src, k)[1].clone() for k in corr] + \
+                                        [pair.get_strict_loss_over_batch(base, src, n, pair.loss_fn).clone() for n in whole]
+                ll.train()
+                seen = []
+                inner = ops.call
+                ops.call = lambda name, *a: (seen.append(name), inner(name, *a))[1]
+                try:
+                    node = list(corr.keys())[1]
+                    opt.zero_grad()
+                    loss = pair.get_IIT_loss_over_batch(base, src, node, pair.loss_fn)
+                    loss.backward()
+                    g_iit = torch.cat([p.grad.flatten().double() for p in ll.parameters()])
+                    opt.zero_grad()
+                    sl = pair.get_strict_loss_over_batch(base, src, whole[0], pair.loss_fn)
+                    sl.backward()
+                    g_strict = torch.cat([p.grad.flatten().double() for p in ll.parameters()])
+                finally:
+                    ops.call = inner
+                out[mode, "train"] = (loss.item(), g_iit, sl.item(), g_strict, seen)
+            res[fused] = out
+        finally:
+            resnet.PATCH_IN_LAYER = True
+    for mode in ("q", "c"):
+        for a, b in zip(res[True][mode, "eval"], res[False][mode, "eval"]):
+            assert torch.equal(a, b), mode
+        lf, gf, sf, gsf, seen_f = res[True][mode, "train"]
+        lh, gh, sh, gsh, seen_h = res[False][mode, "train"]
+        assert abs(lf - lh) <= 2e-3 * abs(lh) and abs(sf - sh) <= 2e-3 * abs(sh), (mode, lf, lh, sf, sh)
+        assert float((gf - gh).norm() / gh.norm()) < 5e-2 and float((gsf - gsh).norm() / gsh.norm()) < 5e-2
+        assert "iit_conv2d_fprop_tc_patch" in seen_f and "iit_bn_act_bwd_apply_box" in seen_f
+        assert not {"iit_patch_fwd", "iit_patch_bwd"} & set(seen_f), set(seen_f) & {"iit_patch_fwd", "iit_patch_bwd"}
+        assert "iit_patch_fwd" in seen_h and "iit_conv2d_fprop_tc_patch" not in seen_h
+        # the fused IIT term takes no separate statistics pass; the whole-tensor strict patch skips one convolution
+        assert seen_f.count("iit_bn_stats") < seen_h.count("iit_bn_stats") or seen_h.count("iit_bn_stats") == 0
+        assert seen_f.count("iit_conv2d_fprop_tc") == seen_h.count("iit_conv2d_fprop_tc") - 2
