@@ -1010,8 +1010,8 @@ def test_patch_inside_the_convolution_matches_the_hook():
     base = tuple(t.to(DEV) for t in R.synthetic_pvr(Bn, 100))
     src = tuple(t.to(DEV) for t in R.synthetic_pvr(Bn, 200))
     res = {}
-    for fused in (True, False):
-        resnet.PATCH_IN_LAYER = fused
+    for fused in (True, False, "again"):      # "again": the hook path a second time -- the run-to-run noise of batch statistics
+        resnet.PATCH_IN_LAYER = fused is True
         try:
             out = {}
             for mode in ("q", "c"):
@@ -1049,8 +1049,18 @@ def test_patch_inside_the_convolution_matches_the_hook():
             assert torch.equal(a, b), mode
         lf, gf, sf, gsf, seen_f = res[True][mode, "train"]
         lh, gh, sh, gsh, seen_h = res[False][mode, "train"]
-        assert abs(lf - lh) <= 2e-3 * abs(lh) and abs(sf - sh) <= 2e-3 * abs(sh), (mode, lf, lh, sf, sh)
-        assert float((gf - gh).norm() / gh.norm()) < 5e-2 and float((gsf - gsh).norm() / gsh.norm()) < 5e-2
+        # Train mode: the BatchNorm sums are accumulated with fp64 atomics in an order that differs from run to run; their
+        # last-bit differences, re-rounded to bf16, move this random-init network's loss by ~1e-3 and its gradient by
+        # several percent between two runs of the SAME path (tests/test_bf16_rounding_model.py). The fused path must sit
+        # inside that noise.
+        l2, g2, s2, gs2, _ = res["again"][mode, "train"]
+        noise_g = max(float((g2 - gh).norm() / gh.norm()), float((gs2 - gsh).norm() / gsh.norm()))
+        noise_l = max(abs(l2 - lh) / abs(lh), abs(s2 - sh) / abs(sh))
+        print(f"patch in layer, mode {mode}: fused-vs-hook loss {abs(lf - lh) / abs(lh):.2e} / grad {float((gf - gh).norm() / gh.norm()):.2e}; "
+              f"hook run-to-run loss {noise_l:.2e} / grad {noise_g:.2e}")
+        assert abs(lf - lh) <= max(3 * noise_l, 2e-3) * abs(lh) and abs(sf - sh) <= max(3 * noise_l, 2e-3) * abs(sh), (mode, lf, lh, sf, sh)
+        assert float((gf - gh).norm() / gh.norm()) < max(3 * noise_g, 5e-2), (mode, noise_g)
+        assert float((gsf - gsh).norm() / gsh.norm()) < max(3 * noise_g, 5e-2), (mode, noise_g)
         assert "iit_conv2d_fprop_tc_patch" in seen_f and "iit_bn_act_bwd_apply_box" in seen_f
         assert not {"iit_patch_fwd", "iit_patch_bwd"} & set(seen_f), set(seen_f) & {"iit_patch_fwd", "iit_patch_bwd"}
         assert "iit_patch_fwd" in seen_h and "iit_conv2d_fprop_tc_patch" not in seen_h
