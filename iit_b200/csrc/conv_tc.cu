@@ -47,6 +47,9 @@ struct TcParams {
   const __nv_bfloat16* aux;       // laid out like `out`: the residual added (TC_EPI_BIAS, may be null) or the pre-activation
                                   // whose GELU derivative multiplies the result (TC_EPI_GELU_BWD)
   __nv_bfloat16* out2;            // TC_EPI_GELU: receives the pre-activation (may be null: not kept)
+  int ksplit, kper;               // ksplit > 1: the reduction (one tap) is cut into ksplit ranges of kper 64-deep blocks, each
+                                  // a tile of its own whose result is ADDED to `out` (zeroed by the host): few-tile, very deep
+                                  // GEMMs (the unembedding's input gradient: 8 tiles x 786 blocks) then fill the machine
   int box[6];                     // TC_EPI_PATCH: output rows p in [box0, box1), columns q in [box2, box3), channels in [box4, box5)
                                   // take their value from `aux` (the cached source activation) instead of the convolution
 };
@@ -102,7 +105,10 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
   const int nk = p.ntaps * kchunks;
   const int nblk = p.Cout / BN;
   const int mtiles = p.tiles_w * p.tiles_h * p.tiles_n;            // pixel boxes
-  const int total_tiles = ((mtiles + MT - 1) / MT) * nblk;
+  const int real_tiles = ((mtiles + MT - 1) / MT) * nblk;
+  const int ksplit = p.ksplit > 1 ? p.ksplit : 1;
+  const int kper = p.ksplit > 1 ? p.kper : kchunks;                // k-blocks per tile and tap
+  const int total_tiles = real_tiles * ksplit;                     // tile = split * real_tiles + (pixel box, filter block)
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
@@ -128,11 +134,13 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int co0 = (tile % nblk) * BN;
+        const int sp = tile / real_tiles, rt = tile - sp * real_tiles;
+        const int kc_lo = sp * kper * TC_BK, kc_hi = min(p.Cin, (sp + 1) * kper * TC_BK);
+        const int co0 = (rt % nblk) * BN;
         int n0[MT], p0[MT], q0[MT];
 #pragma unroll
         for (int mt = 0; mt < MT; ++mt) {
-          int t = (tile / nblk) * MT + mt;
+          int t = (rt / nblk) * MT + mt;
           if (t >= mtiles) t = mtiles - 1;            // odd tail: the box is loaded twice, its second copy never stored
           const int tw = t % p.tiles_w; t /= p.tiles_w;
           const int th = t % p.tiles_h; t /= p.tiles_h;
@@ -140,7 +148,7 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
         }
         for (int tap = 0; tap < p.ntaps; ++tap) {
           const int dh = p.dh[tap], dw = p.dw[tap], wk0 = p.wk[tap] * p.Cin;
-          for (int kc = 0; kc < p.Cin; kc += TC_BK) {
+          for (int kc = kc_lo; kc < kc_hi; kc += TC_BK) {
             mbar_wait(&empty[stage], phase ^ 1);
             if (issuer) {
               mbar_expect_tx(&full[stage], MT * A_BYTES + B_BYTES);
@@ -172,7 +180,9 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);   // the epilogue has drained this accumulator
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t tmem_d = tmem_base + acc * (MT * BN);
-        for (int kb = 0; kb < nk; ++kb) {
+        const int sp = tile / real_tiles;
+        const int nk_t = p.ntaps * (min(kchunks, (sp + 1) * kper) - sp * kper);     // k-blocks of this tile's reduction range
+        for (int kb = 0; kb < nk_t; ++kb) {
           mbar_wait(&full[stage], phase);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t a_lo = a_lo0 + stage * (MT * A_BYTES >> 4), b_lo = b_lo0 + stage * (B_BYTES >> 4);
@@ -221,7 +231,8 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
     int run_co = -1;
     uint32_t it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      const int co0 = (tile % nblk) * BN;
+      const int rt = tile % real_tiles;
+      const int co0 = (rt % nblk) * BN;
       const uint32_t acc = it & 1, acc_phase = (it >> 1) & 1;
       if (nk > 0) {
         mbar_wait(&tmem_full[acc], acc_phase);
@@ -229,7 +240,7 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
       }
 #pragma unroll 1
      for (int mt = 0; mt < MT; ++mt) {
-      int t = (tile / nblk) * MT + mt;
+      int t = (rt / nblk) * MT + mt;
       const bool box_ok = t < mtiles;
       const int tw = t % p.tiles_w; t /= p.tiles_w;
       const int th = t % p.tiles_h; t /= p.tiles_h;
@@ -698,10 +709,25 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
     return 0;
   }
   if (encode_filter(&mb, wmat, Kg, tp.Cout, BN, name)) return 1;
+  // few tiles and a very deep single-tap reduction: cut the reduction so that every SM gets a tile; the partial results are
+  // added onto the zeroed output by the accumulate epilogue (bf16 reductions: at most a few dozen addends per element)
+  const int kchunks_all = tp.Cin / TC_BK;
+  const int64_t base_tiles = mtiles * (tp.Cout / BN);
+  if (tp.ntaps == 1 && tp.epi == TC_EPI_NONE && !tp.accumulate && bn_sum == nullptr && base_tiles * 2 <= kNumSMs && kchunks_all >= 64 &&
+      tp.out_mul == 1) {
+    int want = (int)(kNumSMs / base_tiles);
+    if (want > kchunks_all / 8) want = kchunks_all / 8;
+    if (want > 1) {
+      tp.kper = (kchunks_all + want - 1) / want;
+      tp.ksplit = (kchunks_all + tp.kper - 1) / tp.kper;
+      tp.accumulate = 1;
+      IIT_CUDA(cudaMemsetAsync(out, 0, (size_t)tp.N * tp.OH * tp.OW * tp.Cout * sizeof(__nv_bfloat16), st));
+    }
+  }
   // two pixel boxes per filter block whenever that still leaves a tile for every SM
   // ... and the reduction is long enough to pay for the doubled epilogue per tile (measured: 1152-deep gains, 576-deep loses)
   const int MT = (BN == 128 && g_tile_pairs && ((mtiles + 1) / 2) * (tp.Cout / BN) >= kNumSMs && tp.ntaps * tp.Cin >= 1024) ? 2 : 1;
-  const int64_t total = ((mtiles + MT - 1) / MT) * (tp.Cout / BN);
+  const int64_t total = ((mtiles + MT - 1) / MT) * (tp.Cout / BN) * (tp.ksplit > 1 ? tp.ksplit : 1);
   IIT_REQUIRE(total < (1ll << 31), "%s: too many tiles", name);
   int rc = BN == 256 ? launch_tc<256, 1>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq)
          : BN == 128 ? (MT == 2 ? launch_tc<128, 2>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq)

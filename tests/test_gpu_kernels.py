@@ -1067,3 +1067,24 @@ def test_patch_inside_the_convolution_matches_the_hook():
         # the fused IIT term takes no separate statistics pass; the whole-tensor strict patch skips one convolution
         assert seen_f.count("iit_bn_stats") < seen_h.count("iit_bn_stats") or seen_h.count("iit_bn_stats") == 0
         assert seen_f.count("iit_conv2d_fprop_tc") == seen_h.count("iit_conv2d_fprop_tc") - 2
+
+
+def test_deep_few_tile_gemm_is_split_over_the_reduction():
+    """The unembedding's input gradient: dx[1024, 64] = dy[1024, 50304] @ W^T -- 8 output tiles, 786 k-blocks. The tiled
+    kernel cuts the reduction into ranges that run as tiles of their own and add their results (bf16 reductions) onto the
+    zeroed output; against torch fp32 on the same bf16 operands."""
+    import ctypes as C
+    from iit_b200 import _lib
+    g = torch.Generator().manual_seed(2)
+    rows, n_in, n_out = 1024, 64, 50304
+    d = _lib.Conv()
+    d.n, d.h, d.w, d.c, d.k, d.r, d.s, d.stride, d.pad, d.p, d.q = rows, 1, 1, n_in, n_out, 1, 1, 1, 0, 1, 1
+    dy = (torch.randn(rows, n_out, generator=g) * 0.05).to(DEV).bfloat16()
+    w_io = (torch.randn(n_in, n_out, generator=g) * 0.1).to(DEV).bfloat16()       # [in][out]
+    dx = torch.full((rows, n_in), float("nan"), device=DEV, dtype=torch.bfloat16)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    _lib.call("iit_conv2d_dgrad_tc", C.c_void_p(dy.data_ptr()), C.c_void_p(w_io.data_ptr()), C.c_void_p(dx.data_ptr()), C.byref(d), st)
+    want = dy.float() @ w_io.float().t()
+    err = float((dx.float() - want).norm() / want.norm())
+    assert err < 1e-2, err
+    assert float((dx.float() - want).abs().max()) < 3e-2 * float(want.abs().max())
