@@ -335,6 +335,8 @@ def hbm_bytes(name, a):
     if name == "iit_gemm_dgrad_gelu_tc":   # dy, w_io, pre, dpre, col_sum, col_sq, rows, n_in, n_out
         rows, n_in, n_out = a[6], a[7], a[8]
         return 2 * (rows * n_out + n_in * n_out + 2 * rows * n_in)
+    if name == "iit_hl_ce_fwd":             # logits, dtype, rows, classes, row_stride, ...: one pass over the scored columns
+        return a[2] * a[3] * _es(a[1])
     if name in ("iit_ce_index_fwd", "iit_ce_index_bwd"):   # logits, dtype, rows, classes, ...: one pass over the logits (+ the gradient)
         return a[2] * a[3] * _es(a[1]) * (2 if name.endswith("bwd") else 1)
     return 0
@@ -343,7 +345,7 @@ def hbm_bytes(name, a):
 PVR_HBM = ["iit_bn_act_fwd", "iit_bn_act_bwd_reduce", "iit_bn_act_bwd_apply", "iit_bn_relu_maxpool_fwd",
            "iit_bn_relu_maxpool_bwd", "iit_patch_fwd"]
 IOI_HBM = ["iit_gemm_bias_act_tc", "iit_gemm_dgrad_gelu_tc", "iit_gelu_bwd_bias_colsum", "iit_bias_act_fwd", "iit_gelu_bwd", "iit_colsum", "iit_attn_fwd", "iit_attn_bwd", "iit_lnpre_fwd", "iit_lnpre_bwd",
-           "iit_ce_index_fwd", "iit_ce_index_bwd"]
+           "iit_hl_ce_fwd", "iit_ce_index_fwd", "iit_ce_index_bwd"]
 CONV_ENTRIES = ["iit_conv2d_fprop", "iit_conv2d_dgrad", "iit_conv2d_wgrad", "iit_conv2d_fprop_tc", "iit_conv2d_dgrad_tc",
                 "iit_conv2d_wgrad_tc", "iit_conv2d_wgrad_tc_accumulate", "iit_stem_conv_s2d", "iit_stem_wgrad_s2d"]
 

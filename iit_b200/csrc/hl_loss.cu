@@ -77,7 +77,7 @@ __device__ void ioi_sparse(const int64_t* bt, const int64_t* st, int node, int s
 }
 
 // argmax over the vocabulary of the IOI HL model's last-position logits for sample b, one hook interchanged
-__device__ int64_t ioi_last_argmax_row(const int64_t* __restrict__ base_tok, const int64_t* __restrict__ src_tok, int node,
+__device__ __noinline__ int64_t ioi_last_argmax_row(const int64_t* __restrict__ base_tok, const int64_t* __restrict__ src_tok, int node,
                                        const int64_t* __restrict__ names, int n_names, int64_t b, int seq, int64_t V) {
   int64_t bt[kMaxSeq], st[kMaxSeq], mt[kMaxSeq], sh[kMaxSeq];
   for (int j = 0; j < seq; ++j) { bt[j] = base_tok[b * seq + j]; st[j] = src_tok ? src_tok[b * seq + j] : bt[j]; }
@@ -268,21 +268,33 @@ template <int GROUP>
 __device__ __forceinline__ float row_lse_bf16x8(const __nv_bfloat16* __restrict__ row, int64_t classes, int t, float* s_m, float* s_s) {
   float m = -INFINITY, s = 0.f;
   const int packs = (int)(classes >> 3);
-  for (int pk = t; pk < packs; pk += GROUP) {
-    const uint4 w = *reinterpret_cast<const uint4*>(row + (int64_t)pk * 8);
-    const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
-    float v[8];
+  auto fold = [&](const uint4* w, int n) {           // n packs: one running-maximum update and one rescale for all of them
+    float pm = -INFINITY;
+    for (int u = 0; u < n; ++u) {
+      const uint32_t ww[4] = {w[u].x, w[u].y, w[u].z, w[u].w};
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { v[2 * i] = __uint_as_float(ww[i] << 16); v[2 * i + 1] = __uint_as_float(ww[i] & 0xffff0000u); }
-    float pm = v[0];
-#pragma unroll
-    for (int i = 1; i < 8; ++i) pm = fmaxf(pm, v[i]);
-    if (pm == -INFINITY) continue;
+      for (int i = 0; i < 4; ++i) pm = fmaxf(pm, fmaxf(__uint_as_float(ww[i] << 16), __uint_as_float(ww[i] & 0xffff0000u)));
+    }
+    if (pm == -INFINITY) return;
     const float nm = fmaxf(m, pm);
     float acc = (m == -INFINITY) ? 0.f : s * __expf(m - nm);
+    for (int u = 0; u < n; ++u) {
+      const uint32_t ww[4] = {w[u].x, w[u].y, w[u].z, w[u].w};
 #pragma unroll
-    for (int i = 0; i < 8; ++i) acc += __expf(v[i] - nm);        // exp(-inf) = 0
-    m = nm; s = acc;
+      for (int i = 0; i < 4; ++i) acc += __expf(__uint_as_float(ww[i] << 16) - nm) + __expf(__uint_as_float(ww[i] & 0xffff0000u) - nm);
+    }
+    m = nm; s = acc;                                 // exp(-inf) = 0 for masked entries
+  };
+  int pk = t;
+  for (; pk + 3 * GROUP < packs; pk += 4 * GROUP) {  // four 16-byte loads in flight per thread
+    uint4 w[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) w[u] = *reinterpret_cast<const uint4*>(row + (int64_t)(pk + u * GROUP) * 8);
+    fold(w, 4);
+  }
+  for (; pk < packs; pk += GROUP) {
+    const uint4 w = *reinterpret_cast<const uint4*>(row + (int64_t)pk * 8);
+    fold(&w, 1);
   }
   for (int64_t c = (int64_t)packs * 8 + t; c < classes; c += GROUP) {      // tail of fewer than 8 elements
     const float v = __bfloat162float(row[c]);
@@ -386,36 +398,46 @@ __global__ void __launch_bounds__(256) ce_index_bwd_bf16x8_kernel(const __nv_bfl
                                                                   int64_t row_stride, const int64_t* __restrict__ target,
                                                                   const float* __restrict__ lse, const float* __restrict__ gout,
                                                                   __nv_bfloat16* __restrict__ dl, int64_t d_row_stride, int d_cols) {
-  const int r = blockIdx.y;
-  const int c0 = (blockIdx.x * 256 + threadIdx.x) * 8;
-  if (c0 >= d_cols) return;
+  // one block per row (grid-stride over rows), four 16-byte loads in flight per thread: a block streams its row
   const float g = (gout ? *gout : 1.f) / (float)rows;
-  const float l = lse[r];
-  const int tg = (int)target[r];
-  float v[8];
-  if (c0 + 8 <= classes) {
-    const uint4 w = *reinterpret_cast<const uint4*>(logits + (int64_t)r * row_stride + c0);
-    const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+  const int packs = (d_cols + 7) >> 3, full = classes >> 3;       // packs that lie wholly inside the classes
+  for (int r = blockIdx.x; r < rows; r += gridDim.x) {
+    const float l = lse[r];
+    const int tg = (int)target[r];
+    const __nv_bfloat16* lrow = logits + (int64_t)r * row_stride;
+    __nv_bfloat16* drow = dl + (int64_t)r * d_row_stride;
+    auto emit = [&](int pk, const uint4& w) {
+      const int c0 = pk * 8;
+      const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+      uint32_t o[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { v[2 * i] = __uint_as_float(ww[i] << 16); v[2 * i + 1] = __uint_as_float(ww[i] & 0xffff0000u); }
-  } else {
+      for (int i = 0; i < 4; ++i) {
+        float p0 = __expf(__uint_as_float(ww[i] << 16) - l), p1 = __expf(__uint_as_float(ww[i] & 0xffff0000u) - l);
+        if (c0 + 2 * i == tg) p0 -= 1.f;
+        if (c0 + 2 * i + 1 == tg) p1 -= 1.f;
+        __nv_bfloat162 h = __floats2bfloat162_rn(p0 * g, p1 * g);
+        o[i] = *reinterpret_cast<uint32_t*>(&h);
+      }
+      *reinterpret_cast<uint4*>(drow + c0) = make_uint4(o[0], o[1], o[2], o[3]);
+    };
+    int pk = threadIdx.x;
+    for (; pk + 3 * 256 < full; pk += 4 * 256) {
+      uint4 w[4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] = c0 + i < classes ? __bfloat162float(logits[(int64_t)r * row_stride + c0 + i]) : -INFINITY;
-  }
-  uint32_t o[4];
+      for (int u = 0; u < 4; ++u) w[u] = *reinterpret_cast<const uint4*>(lrow + (int64_t)(pk + u * 256) * 8);
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    float p0 = __expf(v[2 * i] - l), p1 = __expf(v[2 * i + 1] - l);
-    if (c0 + 2 * i == tg) p0 -= 1.f;
-    if (c0 + 2 * i + 1 == tg) p1 -= 1.f;
-    __nv_bfloat162 h = __floats2bfloat162_rn(p0 * g, p1 * g);
-    o[i] = *reinterpret_cast<uint32_t*>(&h);
-  }
-  if (c0 + 8 <= d_cols) {
-    *reinterpret_cast<uint4*>(dl + (int64_t)r * d_row_stride + c0) = make_uint4(o[0], o[1], o[2], o[3]);
-  } else {
-    const __nv_bfloat16* ob = reinterpret_cast<const __nv_bfloat16*>(o);
-    for (int i = 0; c0 + i < d_cols; ++i) dl[(int64_t)r * d_row_stride + c0 + i] = ob[i];
+      for (int u = 0; u < 4; ++u) emit(pk + u * 256, w[u]);
+    }
+    for (; pk < full; pk += 256) emit(pk, *reinterpret_cast<const uint4*>(lrow + (int64_t)pk * 8));
+    // the pack that straddles `classes` and the padding packs: element by element (exp(-inf) = 0 gives the zero gradient)
+    for (pk = full + threadIdx.x; pk < packs; pk += 256) {
+      const int c0 = pk * 8;
+      for (int i = 0; i < 8 && c0 + i < d_cols; ++i) {
+        float pv = 0.f;
+        if (c0 + i < classes) { pv = __expf(__bfloat162float(lrow[c0 + i]) - l); if (c0 + i == tg) pv -= 1.f; }
+        drow[c0 + i] = __float2bfloat16_rn(pv * g);
+      }
+    }
   }
 }
 
@@ -631,7 +653,7 @@ extern "C" int iit_ce_index_bwd(const void* logits, int dtype, int64_t rows, int
   if (dtype == IIT_BF16 && ((reinterpret_cast<uintptr_t>(logits) | reinterpret_cast<uintptr_t>(dlogits)) & 15) == 0 &&
       row_stride % 8 == 0 && d_row_stride % 8 == 0 && rows < 65536 && d_row_stride < (1ll << 31) && d_row_stride >= classes) {
     const int d_cols = (int)d_row_stride;
-    dim3 grid((unsigned)((d_cols / 8 + 255) / 256), (unsigned)rows);
+    const unsigned grid = (unsigned)(rows < (int64_t)kNumSMs * 8 ? rows : (int64_t)kNumSMs * 8);
     ce_index_bwd_bf16x8_kernel<<<grid, 256, 0, st>>>((const __nv_bfloat16*)logits, (int)rows, (int)classes, row_stride, target,
                                                      row_lse_in, grad_out, (__nv_bfloat16*)dlogits, d_row_stride, d_cols);
     IIT_LAUNCH_CHECK("iit_ce_index_bwd");

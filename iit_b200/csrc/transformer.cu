@@ -420,6 +420,217 @@ __global__ void __launch_bounds__(64) attn_bwd_kernel(const T* __restrict__ qkv,
   }
 }
 
+// ---- the IOI model's attention (16 tokens, d_head 16, bf16): the same arithmetic with 16-byte loads and stores ------------
+// A token's q / k / v row of one head is 32 contiguous bytes of qkv [B, S, 3, H, 16]; lane `row` of a half-warp owns token
+// `row` of its (batch, head) unit: it loads its own rows with two 16-byte loads each (the general kernels issue sixteen 2-byte
+// loads per row) and writes its 16 outputs with two 16-byte stores.
+__device__ __forceinline__ void ld_row16(const __nv_bfloat16* p, float (&v)[16]) {
+  float a[8], b[8];
+  unpack_bf16x8(*reinterpret_cast<const uint4*>(p), a);
+  unpack_bf16x8(*reinterpret_cast<const uint4*>(p + 8), b);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { v[i] = a[i]; v[8 + i] = b[i]; }
+}
+__device__ __forceinline__ void st_row16(__nv_bfloat16* p, const float (&v)[16]) {
+  float a[8], b[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { a[i] = v[i]; b[i] = v[8 + i]; }
+  *reinterpret_cast<uint4*>(p) = pack_bf16x8(a);
+  *reinterpret_cast<uint4*>(p + 8) = pack_bf16x8(b);
+}
+
+__global__ void __launch_bounds__(128) attn_fwd_s16_bf16_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ z,
+                                                                int64_t BH, int H, float scale) {
+  constexpr int S = 16, DH = 16, UPB = 8, PITCH = 20;      // two units per warp, four warps; rows padded to 80 bytes
+  __shared__ __align__(16) float sk[UPB][S][PITCH], sv[UPB][S][PITCH];
+  const int lane = threadIdx.x & 31, row = lane & 15;
+  const int w = (threadIdx.x >> 5) * 2 + (lane >> 4);
+  for (int64_t bh0 = (int64_t)blockIdx.x * UPB; bh0 < BH; bh0 += (int64_t)gridDim.x * UPB) {
+    const int64_t bh = bh0 + w;
+    const bool live = bh < BH;
+    const int64_t b = live ? bh / H : 0;
+    const int h = live ? (int)(bh - b * H) : 0;
+    const __nv_bfloat16* tok = qkv + ((b * S + row) * 3) * (int64_t)H * DH + h * DH;     // this lane's token: q row
+    float q[DH], o[DH];
+    if (live) {
+      float kv[DH];
+      ld_row16(tok, q);
+      ld_row16(tok + (int64_t)H * DH, kv);
+#pragma unroll
+      for (int d = 0; d < DH; d += 4) *reinterpret_cast<float4*>(&sk[w][row][d]) = make_float4(kv[d], kv[d + 1], kv[d + 2], kv[d + 3]);
+      ld_row16(tok + 2 * (int64_t)H * DH, kv);
+#pragma unroll
+      for (int d = 0; d < DH; d += 4) *reinterpret_cast<float4*>(&sv[w][row][d]) = make_float4(kv[d], kv[d + 1], kv[d + 2], kv[d + 3]);
+    }
+    __syncwarp();
+    if (live) {
+#pragma unroll
+      for (int d = 0; d < DH; ++d) o[d] = 0.f;
+      float m = -INFINITY, l = 0.f;
+      for (int j = 0; j <= row; ++j) {
+        float sc = 0.f;
+#pragma unroll
+        for (int d = 0; d < DH; ++d) sc = fmaf(q[d], sk[w][j][d], sc);
+        sc *= scale;
+        const float mn = fmaxf(m, sc);
+        const float corr = __expf(m - mn), pr = __expf(sc - mn);
+        l = l * corr + pr;
+#pragma unroll
+        for (int d = 0; d < DH; ++d) o[d] = o[d] * corr + pr * sv[w][j][d];
+        m = mn;
+      }
+      const float inv = 1.f / l;
+#pragma unroll
+      for (int d = 0; d < DH; ++d) o[d] *= inv;
+      st_row16(z + ((b * S + row) * H + h) * DH, o);
+    }
+    __syncwarp();
+  }
+}
+
+__global__ void __launch_bounds__(64) attn_bwd_s16_bf16_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dz,
+                                                               __nv_bfloat16* __restrict__ dqkv, int64_t BH, int H, float scale) {
+  constexpr int S = 16, DH = 16, UPB = 4, PITCH = 20;
+  __shared__ __align__(16) float sq[UPB][S][PITCH], sk[UPB][S][PITCH], sv[UPB][S][PITCH], sdz[UPB][S][PITCH];
+  __shared__ float sp[UPB][S][S + 1], sds[UPB][S][S + 1];
+  const int lane = threadIdx.x & 31, row = lane & 15;
+  const int w = (threadIdx.x >> 5) * 2 + (lane >> 4);
+  for (int64_t bh0 = (int64_t)blockIdx.x * UPB; bh0 < BH; bh0 += (int64_t)gridDim.x * UPB) {
+    const int64_t bh = bh0 + w;
+    const bool live = bh < BH;
+    const int64_t b = live ? bh / H : 0;
+    const int h = live ? (int)(bh - b * H) : 0;
+    const int64_t tok_off = ((b * S + row) * 3) * (int64_t)H * DH + h * DH;
+    float q[DH], g[DH];            // this lane's own query row and dz row
+    if (live) {
+      float t[DH];
+      ld_row16(qkv + tok_off, q);
+#pragma unroll
+      for (int d = 0; d < DH; d += 4) *reinterpret_cast<float4*>(&sq[w][row][d]) = make_float4(q[d], q[d + 1], q[d + 2], q[d + 3]);
+      ld_row16(qkv + tok_off + (int64_t)H * DH, t);
+#pragma unroll
+      for (int d = 0; d < DH; d += 4) *reinterpret_cast<float4*>(&sk[w][row][d]) = make_float4(t[d], t[d + 1], t[d + 2], t[d + 3]);
+      ld_row16(qkv + tok_off + 2 * (int64_t)H * DH, t);
+#pragma unroll
+      for (int d = 0; d < DH; d += 4) *reinterpret_cast<float4*>(&sv[w][row][d]) = make_float4(t[d], t[d + 1], t[d + 2], t[d + 3]);
+      ld_row16(dz + ((b * S + row) * H + h) * DH, g);
+#pragma unroll
+      for (int d = 0; d < DH; d += 4) *reinterpret_cast<float4*>(&sdz[w][row][d]) = make_float4(g[d], g[d + 1], g[d + 2], g[d + 3]);
+    }
+    __syncwarp();
+    if (live) {   // phase 1: row i of the pattern P and of dS; dq_i
+      const int i = row;
+      float m = -INFINITY;
+      for (int j = 0; j <= i; ++j) {
+        float a = 0.f;
+#pragma unroll
+        for (int d = 0; d < DH; ++d) a = fmaf(q[d], sk[w][j][d], a);
+        a *= scale;
+        sp[w][i][j] = a;
+        m = fmaxf(m, a);
+      }
+      float l = 0.f;
+      for (int j = 0; j <= i; ++j) { const float e = __expf(sp[w][i][j] - m); sp[w][i][j] = e; l += e; }
+      const float inv = 1.f / l;
+      float dot = 0.f;
+      for (int j = 0; j <= i; ++j) {
+        const float pr = sp[w][i][j] * inv;
+        float a = 0.f;
+#pragma unroll
+        for (int d = 0; d < DH; ++d) a = fmaf(g[d], sv[w][j][d], a);
+        sds[w][i][j] = a;
+        dot += pr * a;
+        sp[w][i][j] = pr;
+      }
+      float dq[DH];
+#pragma unroll
+      for (int d = 0; d < DH; ++d) dq[d] = 0.f;
+      for (int j = 0; j < S; ++j) {
+        if (j <= i) {
+          const float ds = sp[w][i][j] * (sds[w][i][j] - dot) * scale;
+          sds[w][i][j] = ds;
+#pragma unroll
+          for (int d = 0; d < DH; ++d) dq[d] = fmaf(ds, sk[w][j][d], dq[d]);
+        } else { sds[w][i][j] = 0.f; sp[w][i][j] = 0.f; }
+      }
+      st_row16(dqkv + tok_off, dq);
+    }
+    __syncwarp();
+    if (live) {   // phase 2: column j: dk_j = sum_i dS_ij q_i, dv_j = sum_i P_ij dz_i
+      const int j = row;
+      float dk[DH], dv[DH];
+#pragma unroll
+      for (int d = 0; d < DH; ++d) { dk[d] = 0.f; dv[d] = 0.f; }
+      for (int i = j; i < S; ++i) {
+        const float ds = sds[w][i][j], pr = sp[w][i][j];
+#pragma unroll
+        for (int d = 0; d < DH; ++d) { dk[d] = fmaf(ds, sq[w][i][d], dk[d]); dv[d] = fmaf(pr, sdz[w][i][d], dv[d]); }
+      }
+      st_row16(dqkv + tok_off + (int64_t)H * DH, dk);
+      st_row16(dqkv + tok_off + 2 * (int64_t)H * DH, dv);
+    }
+    __syncwarp();
+  }
+}
+
+// ---- LayerNormPre for d_model = 64 in bf16: eight lanes per row (16-byte accesses), four rows per warp ----------------------
+__device__ __forceinline__ float sum8(float v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  return v;
+}
+__global__ void __launch_bounds__(256) lnpre_fwd_d64_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                                                                 float* __restrict__ rstd, int64_t rows, float eps) {
+  const int64_t r = ((int64_t)blockIdx.x * 256 + threadIdx.x) >> 3;      // grid covers ceil(rows / 32) blocks exactly
+  const int part = threadIdx.x & 7;
+  const bool live = r < rows;
+  float v[8];
+  if (live) unpack_bf16x8(*reinterpret_cast<const uint4*>(x + r * 64 + part * 8), v);
+  else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = 0.f;
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s += v[j];
+  const float mean = sum8(s) * (1.f / 64.f);
+  float q = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { v[j] -= mean; q += v[j] * v[j]; }
+  const float scale = sqrtf(sum8(q) * (1.f / 64.f) + eps);
+  if (!live) return;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] = v[j] / scale;
+  *reinterpret_cast<uint4*>(y + r * 64 + part * 8) = pack_bf16x8(v);
+  if (part == 0 && rstd) rstd[r] = 1.f / scale;
+}
+__global__ void __launch_bounds__(256) lnpre_bwd_d64_bf16_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
+                                                                 const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx,
+                                                                 int64_t rows) {
+  const int64_t r = ((int64_t)blockIdx.x * 256 + threadIdx.x) >> 3;
+  const int part = threadIdx.x & 7;
+  const bool live = r < rows;
+  float g[8], yy[8];
+  if (live) {
+    unpack_bf16x8(*reinterpret_cast<const uint4*>(dy + r * 64 + part * 8), g);
+    unpack_bf16x8(*reinterpret_cast<const uint4*>(y + r * 64 + part * 8), yy);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { g[j] = 0.f; yy[j] = 0.f; }
+  }
+  float a = 0.f, b = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { a += g[j]; b += g[j] * yy[j]; }
+  a = sum8(a) * (1.f / 64.f);
+  b = sum8(b) * (1.f / 64.f);
+  if (!live) return;
+  const float rs = rstd[r];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) g[j] = rs * (g[j] - a - yy[j] * b);
+  *reinterpret_cast<uint4*>(dx + r * 64 + part * 8) = pack_bf16x8(g);
+}
+
 }  // namespace iit
 
 using namespace iit;
@@ -460,6 +671,11 @@ extern "C" int iit_embed_bwd(const int64_t* tokens, const void* dresid, int dtyp
 extern "C" int iit_lnpre_fwd(const void* x, void* y, float* rstd, int dtype, int64_t rows, int d, float eps, void* stream) {
   IIT_REQUIRE(x && y && d % 32 == 0, "iit_lnpre_fwd: bad arguments (width must be a multiple of 32)");
   cudaStream_t st = as_stream(stream);
+  if (dtype == IIT_BF16 && d == 64 && aligned16(x, y) && rows > 0) {
+    lnpre_fwd_d64_bf16_kernel<<<(unsigned)((rows + 31) / 32), 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, rstd, rows, eps);
+    IIT_LAUNCH_CHECK("iit_lnpre_fwd");
+    return 0;
+  }
   IIT_DISPATCH_DTYPE(dtype, T, { IIT_LN_DISPATCH(lnpre_fwd_kernel, (const T*)x, (T*)y, rstd, rows, d, eps) })
   IIT_LAUNCH_CHECK("iit_lnpre_fwd");
   return 0;
@@ -468,6 +684,12 @@ extern "C" int iit_lnpre_bwd(const void* dy, const void* y, const float* rstd, v
                              void* stream) {
   IIT_REQUIRE(dy && y && rstd && dx && d % 32 == 0, "iit_lnpre_bwd: bad arguments");
   cudaStream_t st = as_stream(stream);
+  if (dtype == IIT_BF16 && d == 64 && aligned16(dy, y, dx) && rows > 0) {
+    lnpre_bwd_d64_bf16_kernel<<<(unsigned)((rows + 31) / 32), 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, rstd,
+                                                                          (__nv_bfloat16*)dx, rows);
+    IIT_LAUNCH_CHECK("iit_lnpre_bwd");
+    return 0;
+  }
   IIT_DISPATCH_DTYPE(dtype, T, { IIT_LN_DISPATCH(lnpre_bwd_kernel, (const T*)dy, (const T*)y, rstd, (T*)dx, rows, d) })
   IIT_LAUNCH_CHECK("iit_lnpre_bwd");
   return 0;
@@ -614,6 +836,11 @@ extern "C" int iit_attn_fwd(const void* qkv, void* z, int dtype, int64_t batch, 
   IIT_REQUIRE(qkv && z && seq >= 1 && seq <= 32 && d_head >= 1 && d_head <= 32, "iit_attn_fwd: seq and d_head must be <= 32");
   const float scale = 1.0f / sqrtf((float)d_head);
   int64_t BH = batch * heads;
+  if (dtype == IIT_BF16 && seq == 16 && d_head == 16 && aligned16(qkv, z)) {     // the IOI model: 16-byte loads and stores
+    attn_fwd_s16_bf16_kernel<<<grid_for(BH, 8, 16), 128, 0, as_stream(stream)>>>((const __nv_bfloat16*)qkv, (__nv_bfloat16*)z, BH, heads, scale);
+    IIT_LAUNCH_CHECK("iit_attn_fwd");
+    return 0;
+  }
   IIT_DISPATCH_DTYPE(dtype, T, {
     if (seq <= 16 && d_head <= 16)   // the IOI model: half the unrolled work, registers and shared memory of the general instance
       attn_fwd_kernel<T, 16, 16><<<grid_for(BH, 8, 16), 128, 0, as_stream(stream)>>>((const T*)qkv, (T*)z, BH, seq, heads, d_head, scale);
@@ -629,6 +856,12 @@ extern "C" int iit_attn_bwd(const void* qkv, const void* dz, void* dqkv, int dty
               "iit_attn_bwd: seq and d_head must be <= 16");
   const float scale = 1.0f / sqrtf((float)d_head);
   int64_t BH = batch * heads;
+  if (dtype == IIT_BF16 && seq == 16 && d_head == 16 && aligned16(qkv, dz, dqkv)) {
+    attn_bwd_s16_bf16_kernel<<<grid_for(BH, 4, 32), 64, 0, as_stream(stream)>>>((const __nv_bfloat16*)qkv, (const __nv_bfloat16*)dz,
+                                                                              (__nv_bfloat16*)dqkv, BH, heads, scale);
+    IIT_LAUNCH_CHECK("iit_attn_bwd");
+    return 0;
+  }
   IIT_DISPATCH_DTYPE(dtype, T, {
     attn_bwd_kernel<T, 16, 16><<<grid_for(BH, 4, 32), 64, 0, as_stream(stream)>>>((const T*)qkv, (const T*)dz, (T*)dqkv, BH, seq, heads,
                                                                                d_head, scale);

@@ -1088,3 +1088,32 @@ def test_deep_few_tile_gemm_is_split_over_the_reduction():
     err = float((dx.float() - want).norm() / want.norm())
     assert err < 1e-2, err
     assert float((dx.float() - want).abs().max()) < 3e-2 * float(want.abs().max())
+
+
+def test_bf16_attention_and_lnpre_vector_kernels_match_the_fp32_kernels():
+    """The IOI model's shapes in bf16 (16 tokens, d_head 16, d_model 64) run on kernels with 16-byte loads / stores; same
+    arithmetic as the general kernels: compared with those in fp32 on the same (bf16-representable) inputs."""
+    from iit_b200 import ops
+    g = torch.Generator().manual_seed(6)
+    for B in (1, 5, 130):
+        qkv = torch.randn(B, 16, 3, 4, 16, generator=g).bfloat16()
+        gz = torch.randn(B, 16, 4, 16, generator=g).bfloat16()
+        a = qkv.to(DEV).requires_grad_(True)
+        za = ops.attention(a)
+        za.backward(gz.to(DEV))
+        b = qkv.float().to(DEV).requires_grad_(True)
+        zb = ops.attention(b)
+        zb.backward(gz.float().to(DEV))
+        torch.testing.assert_close(za.float(), zb, rtol=1e-2, atol=1e-2)
+        torch.testing.assert_close(a.grad.float(), b.grad, rtol=2e-2, atol=2e-2)
+    for rows in (1, 33, 16384):
+        x = (torch.randn(rows, 64, generator=g) * 2 + 0.5).bfloat16()
+        gy = torch.randn(rows, 64, generator=g).bfloat16()
+        a = x.to(DEV).requires_grad_(True)
+        ya = ops.lnpre(a, 1e-5)
+        ya.backward(gy.to(DEV))
+        b = x.float().to(DEV).requires_grad_(True)
+        yb = ops.lnpre(b, 1e-5)
+        yb.backward(gy.float().to(DEV))
+        torch.testing.assert_close(ya.float(), yb, rtol=1e-2, atol=1e-2)
+        torch.testing.assert_close(a.grad.float(), b.grad, rtol=3e-2, atol=3e-2)
