@@ -13,6 +13,8 @@
 // NHWC, so when the channel count is a multiple of 16 every 16-wide K slice of A is one contiguous
 // 64 B run per pixel and is fetched with 16 B vector loads; otherwise (the 3-channel stem) a scalar
 // gather with full index decode is used.
+#include <atomic>
+
 #include "common.cuh"
 
 namespace iit {
@@ -559,7 +561,9 @@ extern "C" int iit_filter_relayout_batched(const iit_relayout_t* table_dev, int 
 namespace iit {
 constexpr size_t kStaticScratchBytes = 8u << 20;  // 8 MiB
 static __device__ __align__(256) unsigned char g_wgrad_static_scratch[kStaticScratchBytes];
-static void* g_static_scratch_addr[kMaxDevices] = {nullptr};  // device address of the array, per device
+// device address of the array, per device; atomic because two host threads may make their first call at the same time (both
+// then resolve the same address: the look-up is idempotent)
+static std::atomic<void*> g_static_scratch_addr[kMaxDevices];
 }  // namespace iit
 
 extern "C" int iit_conv2d_wgrad_noalloc(const void* dy, const void* x, float* dw, const iit_conv_t* d, int dtype,
@@ -573,15 +577,17 @@ extern "C" int iit_conv2d_wgrad_noalloc(const void* dy, const void* x, float* dw
   int dev = -1;
   IIT_CUDA(cudaGetDevice(&dev));
   IIT_REQUIRE(dev >= 0 && dev < kMaxDevices, "iit_conv2d_wgrad_noalloc: device ordinal %d out of range", dev);
-  if (g_static_scratch_addr[dev] == nullptr) {
+  void* scratch = g_static_scratch_addr[dev].load(std::memory_order_acquire);
+  if (scratch == nullptr) {
     // One-time set-up for the current device: in host code the array's name is only a handle, the
     // address the kernels must be given comes from the runtime. Nothing is allocated here.
     void* p = nullptr;
     IIT_CUDA(cudaGetSymbolAddress(&p, g_wgrad_static_scratch));
     IIT_REQUIRE(p != nullptr, "iit_conv2d_wgrad_noalloc: could not resolve the built-in scratch buffer");
-    g_static_scratch_addr[dev] = p;
+    g_static_scratch_addr[dev].store(p, std::memory_order_release);
+    scratch = p;
   }
   // The partial sums need no clearing: every cell of the region a launch uses is written by the
   // gradient kernel before the reduction reads it.
-  return iit_conv2d_wgrad(dy, x, dw, d, dtype, g_static_scratch_addr[dev], kStaticScratchBytes, stream);
+  return iit_conv2d_wgrad(dy, x, dw, d, dtype, scratch, kStaticScratchBytes, stream);
 }
