@@ -103,6 +103,7 @@ SIGNATURES = {
     "iit_embed_bwd": [_vp, _vp, _i, _vp, _vp, _i64, _i, _i, _i64, _vp],
     "iit_lnpre_fwd": [_vp, _vp, _vp, _i, _i64, _i, _f, _vp],
     "iit_lnpre_bwd": [_vp, _vp, _vp, _vp, _i, _i64, _i, _vp],
+    "iit_lnpre_bwd_accumulate": [_vp, _vp, _vp, _vp, _i, _i64, _i, _vp],
     "iit_bias_act_fwd": [_vp, _vp, _vp, _vp, _vp, _i, _i64, _i, _i, _vp],
     "iit_gelu_bwd": [_vp, _vp, _vp, _i, _i64, _vp],
     "iit_gelu_bwd_bias_colsum": [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _vp],

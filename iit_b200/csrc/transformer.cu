@@ -71,7 +71,8 @@ __global__ void __launch_bounds__(256) lnpre_fwd_kernel(const T* __restrict__ x,
 // dx = rstd * (dy - mean(dy) - y * mean(dy * y))
 template <typename T, int PER>
 __global__ void __launch_bounds__(256) lnpre_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ y,
-                                                        const float* __restrict__ rstd, T* __restrict__ dx, int64_t rows, int D) {
+                                                        const float* __restrict__ rstd, T* __restrict__ dx, int64_t rows, int D,
+                                                        int accumulate) {
   const int lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -88,7 +89,11 @@ __global__ void __launch_bounds__(256) lnpre_bwd_kernel(const T* __restrict__ dy
     b = warp_sum(b) / (float)D;
     const float rs = rstd[r];
 #pragma unroll
-    for (int j = 0; j < PER; ++j) dx[r * D + lane + 32 * j] = from_f<T>(rs * (g[j] - a - yy[j] * b));
+    for (int j = 0; j < PER; ++j) {
+      float o = rs * (g[j] - a - yy[j] * b);
+      if (accumulate) o += to_f<T>(dx[r * D + lane + 32 * j]);
+      dx[r * D + lane + 32 * j] = from_f<T>(o);
+    }
   }
 }
 
@@ -607,14 +612,17 @@ __global__ void __launch_bounds__(256) lnpre_fwd_d64_bf16_kernel(const __nv_bflo
 }
 __global__ void __launch_bounds__(256) lnpre_bwd_d64_bf16_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
                                                                  const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx,
-                                                                 int64_t rows) {
+                                                                 int64_t rows, int accumulate) {
   const int64_t r = ((int64_t)blockIdx.x * 256 + threadIdx.x) >> 3;
   const int part = threadIdx.x & 7;
   const bool live = r < rows;
-  float g[8], yy[8];
+  float g[8], yy[8], old[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) old[j] = 0.f;
   if (live) {
     unpack_bf16x8(*reinterpret_cast<const uint4*>(dy + r * 64 + part * 8), g);
     unpack_bf16x8(*reinterpret_cast<const uint4*>(y + r * 64 + part * 8), yy);
+    if (accumulate) unpack_bf16x8(*reinterpret_cast<const uint4*>(dx + r * 64 + part * 8), old);
   } else {
 #pragma unroll
     for (int j = 0; j < 8; ++j) { g[j] = 0.f; yy[j] = 0.f; }
@@ -627,7 +635,7 @@ __global__ void __launch_bounds__(256) lnpre_bwd_d64_bf16_kernel(const __nv_bflo
   if (!live) return;
   const float rs = rstd[r];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) g[j] = rs * (g[j] - a - yy[j] * b);
+  for (int j = 0; j < 8; ++j) g[j] = rs * (g[j] - a - yy[j] * b) + old[j];
   *reinterpret_cast<uint4*>(dx + r * 64 + part * 8) = pack_bf16x8(g);
 }
 
@@ -680,19 +688,27 @@ extern "C" int iit_lnpre_fwd(const void* x, void* y, float* rstd, int dtype, int
   IIT_LAUNCH_CHECK("iit_lnpre_fwd");
   return 0;
 }
-extern "C" int iit_lnpre_bwd(const void* dy, const void* y, const float* rstd, void* dx, int dtype, int64_t rows, int d,
-                             void* stream) {
-  IIT_REQUIRE(dy && y && rstd && dx && d % 32 == 0, "iit_lnpre_bwd: bad arguments");
+static int lnpre_bwd_impl(const void* dy, const void* y, const float* rstd, void* dx, int dtype, int64_t rows, int d, void* stream,
+                          int accumulate, const char* name) {
+  IIT_REQUIRE(dy && y && rstd && dx && d % 32 == 0, "%s: bad arguments", name);
   cudaStream_t st = as_stream(stream);
   if (dtype == IIT_BF16 && d == 64 && aligned16(dy, y, dx) && rows > 0) {
     lnpre_bwd_d64_bf16_kernel<<<(unsigned)((rows + 31) / 32), 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, rstd,
-                                                                          (__nv_bfloat16*)dx, rows);
-    IIT_LAUNCH_CHECK("iit_lnpre_bwd");
+                                                                          (__nv_bfloat16*)dx, rows, accumulate);
+    IIT_LAUNCH_CHECK(name);
     return 0;
   }
-  IIT_DISPATCH_DTYPE(dtype, T, { IIT_LN_DISPATCH(lnpre_bwd_kernel, (const T*)dy, (const T*)y, rstd, (T*)dx, rows, d) })
-  IIT_LAUNCH_CHECK("iit_lnpre_bwd");
+  IIT_DISPATCH_DTYPE(dtype, T, { IIT_LN_DISPATCH(lnpre_bwd_kernel, (const T*)dy, (const T*)y, rstd, (T*)dx, rows, d, accumulate) })
+  IIT_LAUNCH_CHECK(name);
   return 0;
+}
+extern "C" int iit_lnpre_bwd(const void* dy, const void* y, const float* rstd, void* dx, int dtype, int64_t rows, int d,
+                             void* stream) {
+  return lnpre_bwd_impl(dy, y, rstd, dx, dtype, rows, d, stream, 0, "iit_lnpre_bwd");
+}
+extern "C" int iit_lnpre_bwd_accumulate(const void* dy, const void* y, const float* rstd, void* dx, int dtype, int64_t rows, int d,
+                                        void* stream) {
+  return lnpre_bwd_impl(dy, y, rstd, dx, dtype, rows, d, stream, 1, "iit_lnpre_bwd_accumulate");
 }
 
 extern "C" int iit_bias_act_fwd(const void* x, const float* bias, const void* resid, void* pre_out, void* out, int dtype,

@@ -240,10 +240,30 @@ class HookedTransformerLL(HookedRootModule):
             return torch.as_strided(a.b_Q.detach(), (3 * n,), (1,), a.b_Q.storage_offset())
         return torch.cat([b.detach().reshape(-1) for b in (a.b_Q, a.b_K, a.b_V)])
 
-    def _epi(self, key, x, bias, bias_specs, bias_params, resid=None, act=0, link_out=None, link_in=None):
+    @staticmethod
+    def _direct_bias_grad(params):
+        """The optimizer's fp32 gradient buffer behind one bias parameter -- or behind several that lie back to back in it
+        (b_Q | b_K | b_V under FlatAdam) -- when backward kernels may add into it (ops.direct_grad); None otherwise."""
+        if not torch.is_grad_enabled():
+            return None
+        gs = [ops.direct_grad(p) for p in params]
+        if any(g is None or not g.is_contiguous() for g in gs):
+            return None
+        n = gs[0].numel()
+        for j, g in enumerate(gs):
+            if g.numel() != n or g.data_ptr() != gs[0].data_ptr() + 4 * n * j:
+                return None
+        return gs[0].reshape(-1) if len(gs) == 1 else torch.as_strided(gs[0], (n * len(gs),), (1,), gs[0].storage_offset())
+
+    def _epi(self, key, x, bias, bias_specs, bias_params, resid=None, act=0, link_out=None, link_in=None, direct_bias=True,
+             res_slot=None):
+        if direct_bias and act == 0:
+            buf = self._direct_bias_grad(bias_params)
+            if buf is not None:
+                bias_specs = (*bias_specs, ("direct", buf))
         oi, io, st = self._shadow["bufs"][key]
         return ops.linear_epi(x, oi, io, st["n_in"], st["n_out_pad"], st["specs"], st["params"], bias=bias, bias_specs=bias_specs,
-                              bias_params=bias_params, resid=resid, act=act, link_out=link_out, link_in=link_in)
+                              bias_params=bias_params, resid=resid, act=act, link_out=link_out, link_in=link_in, res_slot=res_slot)
 
     def _mlp_link(self, li):
         sites = self.__dict__.setdefault("_mlp_sites", {})
@@ -288,17 +308,21 @@ class HookedTransformerLL(HookedRootModule):
         for blk in self.blocks:
             a, m = blk.attn, blk.mlp
             resid = blk.hook_resid_pre(resid.view(B, S, D)).reshape(T, D)
-            x = ops.lnpre(resid, c.eps)
-            if use_shadow and not (blk.hook_attn_out.has_hooks() or blk.hook_mlp_out.has_hooks() or m.hook_pre.has_hooks()):
+            fused = use_shadow and not (blk.hook_attn_out.has_hooks() or blk.hook_mlp_out.has_hooks() or m.hook_pre.has_hooks())
+            # the residual stream feeds a LayerNorm and a skip connection: their two gradients meet in a GradSlot
+            slot_a = ops.GradSlot() if (fused and torch.is_grad_enabled() and resid.requires_grad) else None
+            x = ops.lnpre(resid, c.eps, slot_a)
+            if fused:
                 # every element-wise neighbour of the four linear maps runs in their GEMM epilogues
                 li = len(blocks_seen); blocks_seen.append(blk)
                 hd = H * dh
                 qkv = self._epi(("qkv", li), x, self._qkv_bias(a), tuple(((H, dh), (dh, 1), j * hd) for j in range(3)),
                                 (a.b_Q, a.b_K, a.b_V)).view(B, S, 3, H, dh)
                 z = a.hook_z(ops.attention(qkv))
-                resid = self._epi(("o", li), z.reshape(T, hd), a.b_O.detach(), (((D,), (1,), 0),), (a.b_O,), resid=resid)
+                resid = self._epi(("o", li), z.reshape(T, hd), a.b_O.detach(), (((D,), (1,), 0),), (a.b_O,), resid=resid, res_slot=slot_a)
                 resid = blk.hook_resid_mid(resid.view(B, S, D)).reshape(T, D)
-                x = ops.lnpre(resid, c.eps)
+                slot_m = ops.GradSlot() if (torch.is_grad_enabled() and resid.requires_grad) else None
+                x = ops.lnpre(resid, c.eps, slot_m)
                 if FUSE_GELU_IN_GEMM:      # measured slower: the tiled kernel's eight epilogue warps are ALU-bound on the GELU
                     link = self._mlp_link(li) if (torch.is_grad_enabled() and m.hook_post.only_patch_hooks()) else None
                     post = self._epi(("in", li), x, m.b_in.detach(), (((c.d_mlp,), (1,), 0),), (m.b_in,), act=1, link_out=link)
@@ -307,9 +331,10 @@ class HookedTransformerLL(HookedRootModule):
                     # the MLP's input map stays a plain GEMM; bias + gelu_new read its result once and write `post` only
                     # (the backward recomputes h + bias and takes the bias gradient in the same pass)
                     link = None
-                    post = ops.bias_gelu_lean(self._linear(("in", li), x), m.b_in, (B, S, c.d_mlp))
+                    post = ops.bias_gelu_lean(self._linear(("in", li), x), m.b_in, (B, S, c.d_mlp), self._direct_bias_grad((m.b_in,)))
                 post = m.hook_post(post).reshape(T, -1)
-                resid = self._epi(("out", li), post, m.b_out.detach(), (((D,), (1,), 0),), (m.b_out,), resid=resid, link_in=link)
+                resid = self._epi(("out", li), post, m.b_out.detach(), (((D,), (1,), 0),), (m.b_out,), resid=resid, link_in=link,
+                                  res_slot=slot_m)
                 resid = blk.hook_resid_post(resid.view(B, S, D)).reshape(T, D)
                 continue
             # fused QKV projection: [D, (3,H,dh)] assembled from the per-head parameters (tiny; autograd routes grads)
@@ -348,7 +373,8 @@ class HookedTransformerLL(HookedRootModule):
         pad = (-V) % 64
         if use_shadow:
             xin = resid.view(B, S, D)[:, -1, :].contiguous() if last_pos_only else resid
-            logits = self._epi(("unembed",), ops.lnpre(xin, c.eps), self._shadow["b_U_pad"], (((V,), (1,), 0),), (b_U,))
+            # (the padded width is wider than b_U's gradient: its column sums go through autograd)
+            logits = self._epi(("unembed",), ops.lnpre(xin, c.eps), self._shadow["b_U_pad"], (((V,), (1,), 0),), (b_U,), direct_bias=False)
             if last_pos_only and return_padded:
                 return logits
             logits = logits[:, :V]

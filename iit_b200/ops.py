@@ -1149,6 +1149,17 @@ class _LinearEpiFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, w_oi, w_io, n_in, n_out_pad, specs, bias, bias_specs, resid, act, link_out, link_in, n_w, *params):
+        # `link_in` may be a (GeluLink or None, GradSlot) pair: the slot receives this map's residual gradient (the skip
+        # connection's share of the residual stream's gradient) for the LayerNorm backward to add onto
+        ctx.res_slot = None
+        if isinstance(link_in, tuple):
+            link_in, ctx.res_slot = link_in
+        # bias_specs may end with the string key "direct": (specs..., ("direct", buffer)) -- the bias gradient (column sums of
+        # dy) is then ADDED straight into `buffer`, the optimizer's fp32 gradient view (direct_grad), and autograd gets None
+        ctx.bias_direct = None
+        if bias_specs is not None and len(bias_specs) and isinstance(bias_specs[-1], tuple) and bias_specs[-1][0] == "direct":
+            ctx.bias_direct = bias_specs[-1][1]
+            bias_specs = bias_specs[:-1]
         _require_cuda(x, w_oi, w_io, bias, resid)
         x = x.contiguous()
         T = x.shape[0]
@@ -1178,6 +1189,9 @@ class _LinearEpiFn(torch.autograd.Function):
         d.n, d.h, d.w, d.c, d.k, d.r, d.s, d.stride, d.pad, d.p, d.q = T, 1, 1, n_in, n_out, 1, 1, 1, 0, 1, 1
         db = None
         want_db = ctx.bias_specs is not None and any(ctx.needs_input_grad[13 + ctx.n_w:])
+        direct = ctx.bias_direct if (want_db and ctx.act != 1) else None
+        if direct is not None:      # column sums added into the optimizer's gradient buffer: no zero fill, no AccumulateGrad
+            want_db = False
         if ctx.act == 1:
             link = ctx.link_out
             if link is not None and link.marked():
@@ -1196,7 +1210,9 @@ class _LinearEpiFn(torch.autograd.Function):
                     db = colsum(g)
         else:
             g = dy
-            if want_db:
+            if direct is not None:
+                call("iit_colsum", _p(g), _dt(g), _p(direct), g.shape[0], n_out, st)
+            elif want_db:
                 db = colsum(g)
         dx = None
         if ctx.needs_input_grad[0]:
@@ -1215,6 +1231,8 @@ class _LinearEpiFn(torch.autograd.Function):
             scratch = torch.empty(need, dtype=torch.uint8, device=x.device)
             call("iit_conv2d_wgrad_tc", _p(g), _p(x), _p(dwb), C.byref(d), _p(scratch), need, st)
             grads = [torch.as_strided(dwb, size, stride, offset) for size, stride, offset in ctx.specs]
+        if ctx.has_res and ctx.res_slot is not None and USE_GRAD_SLOTS:
+            ctx.res_slot.put(g)
         bgrads = []
         if ctx.bias_specs is not None:
             bgrads = [torch.as_strided(db, size, stride, offset) if db is not None else None for size, stride, offset in ctx.bias_specs]
@@ -1222,7 +1240,9 @@ class _LinearEpiFn(torch.autograd.Function):
 
 
 def linear_epi(x2d, w_oi, w_io, n_in, n_out_pad, specs, params, bias=None, bias_specs=None, bias_params=(), resid=None, act=0,
-               link_out=None, link_in=None):
+               link_out=None, link_in=None, res_slot=None):
+    if res_slot is not None:
+        link_in = (link_in, res_slot)
     return _LinearEpiFn.apply(x2d, w_oi, w_io, n_in, n_out_pad, specs, bias, bias_specs, resid, act, link_out, link_in,
                               len(params), *params, *bias_params)
 
@@ -1295,9 +1315,10 @@ class _BiasGeluLeanFn(torch.autograd.Function):
     (iit_gelu_bwd_bias_colsum) instead of a GELU-backward kernel plus a column-sum kernel."""
 
     @staticmethod
-    def forward(ctx, h, bias, out_shape):
+    def forward(ctx, h, bias, out_shape, bias_grad=None):
         _require_cuda(h, bias)
         h = h.contiguous()
+        ctx.bias_grad = bias_grad       # the optimizer's gradient view of `bias` (direct_grad): the column sums are added into it
         if h.dtype != torch.bfloat16 or h.shape[1] % 8:
             raise RuntimeError("bias_gelu_lean: bf16 activations with a width that is a multiple of 8 only")
         post = torch.empty(out_shape, dtype=h.dtype, device=h.device)
@@ -1312,18 +1333,21 @@ class _BiasGeluLeanFn(torch.autograd.Function):
         dpost = dpost.contiguous()
         rows, n = h.shape
         dpre = torch.empty_like(h)
+        if ctx.needs_input_grad[1] and ctx.bias_grad is not None:
+            call("iit_gelu_bwd_bias_colsum", _p(dpost), _p(h), _p(bias), _p(dpre), _p(ctx.bias_grad), rows, n, _stream())
+            return dpre, None, None, None
         db = torch.zeros(n, dtype=torch.float32, device=h.device) if ctx.needs_input_grad[1] else None
         call("iit_gelu_bwd_bias_colsum", _p(dpost), _p(h), _p(bias), _p(dpre), _p(db), rows, n, _stream())
-        return dpre, db, None
+        return dpre, db, None, None
 
 
-def bias_gelu_lean(h2d, bias, out_shape):
-    return _BiasGeluLeanFn.apply(h2d, bias, tuple(out_shape))
+def bias_gelu_lean(h2d, bias, out_shape, bias_grad=None):
+    return _BiasGeluLeanFn.apply(h2d, bias, tuple(out_shape), bias_grad)
 
 
 class _LNPreFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, eps):
+    def forward(ctx, x, eps, slot):
         _require_cuda(x)
         x = x.contiguous()
         rows, d = x.shape
@@ -1331,19 +1355,26 @@ class _LNPreFn(torch.autograd.Function):
         rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
         call("iit_lnpre_fwd", _p(x), _p(y), _p(rstd), _dt(x), rows, d, float(eps), _stream())
         ctx.save_for_backward(y, rstd)
+        ctx.slot = slot
         return y
 
     @staticmethod
     def backward(ctx, dy):
         y, rstd = ctx.saved_tensors
         dy = dy.contiguous()
+        first = ctx.slot.take() if (ctx.slot is not None and USE_GRAD_SLOTS) else None
+        if first is not None and first.shape == y.shape and first.dtype == y.dtype and first.is_contiguous():
+            # the skip connection's gradient of the same residual-stream tensor is already there: add onto it (GradSlot)
+            call("iit_lnpre_bwd_accumulate", _p(dy), _p(y), _p(rstd), _p(first), _dt(y), y.shape[0], y.shape[1], _stream())
+            return None, None, None
         dx = torch.empty_like(y)
         call("iit_lnpre_bwd", _p(dy), _p(y), _p(rstd), _p(dx), _dt(y), y.shape[0], y.shape[1], _stream())
-        return dx, None
+        return dx, None, None
 
 
-def lnpre(x2d, eps):
-    return _LNPreFn.apply(x2d, eps)
+def lnpre(x2d, eps, slot=None):
+    """`slot`: a GradSlot shared with the skip connection that consumes the same tensor (linear_epi(..., res_slot=slot))."""
+    return _LNPreFn.apply(x2d, eps, slot)
 
 
 class _AttnFn(torch.autograd.Function):
@@ -1375,8 +1406,9 @@ def attention(qkv):
 
 class _EmbedFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, tokens, W_E, W_pos, dtype):
+    def forward(ctx, tokens, W_E, W_pos, dtype, direct=None):
         _require_cuda(tokens, W_E, W_pos)
+        ctx.direct = direct     # (W_E.grad, W_pos.grad) views of the optimizer's buffer: the scatter-add goes straight into them
         tokens = tokens.contiguous()
         b, s = tokens.shape
         v, dm = W_E.shape
@@ -1392,15 +1424,24 @@ class _EmbedFn(torch.autograd.Function):
         (tokens,) = ctx.saved_tensors
         dres = dres.contiguous()
         (v, dm), pshape = ctx.shapes
+        b, s = tokens.shape
+        if ctx.direct is not None:
+            call("iit_embed_bwd", _p(tokens), _p(dres), _dt(dres), _p(ctx.direct[0]), _p(ctx.direct[1]), b * s, s, dm, v, _stream())
+            return None, None, None, None, None
         dWE = torch.zeros((v, dm), dtype=torch.float32, device=dres.device)
         dWpos = torch.zeros(pshape, dtype=torch.float32, device=dres.device)
         b, s = tokens.shape
         call("iit_embed_bwd", _p(tokens), _p(dres), _dt(dres), _p(dWE), _p(dWpos), b * s, s, dm, v, _stream())
-        return None, dWE, dWpos, None
+        return None, dWE, dWpos, None, None
 
 
 def embed(tokens, W_E, W_pos, dtype):
-    return _EmbedFn.apply(tokens, W_E, W_pos, dtype)
+    direct = None
+    if torch.is_grad_enabled():
+        gE, gP = direct_grad(W_E), direct_grad(W_pos)
+        if gE is not None and gP is not None and gE.is_contiguous() and gP.is_contiguous() and W_E.is_contiguous() and W_pos.is_contiguous():
+            direct = (gE, gP)
+    return _EmbedFn.apply(tokens, W_E, W_pos, dtype, direct)
 
 
 # =================================================================================================

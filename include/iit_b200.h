@@ -417,6 +417,10 @@ int iit_embed_bwd(const int64_t* tokens, const void* dresid, int dtype, float* d
 int iit_lnpre_fwd(const void* x, void* y, float* rstd, int dtype, int64_t rows, int d, float eps, void* stream);
 int iit_lnpre_bwd(const void* dy, const void* y, const float* rstd, void* dx, int dtype, int64_t rows, int d,
                   void* stream);
+/* dx += the same: the residual stream feeds the LayerNorm and the skip connection, and the LayerNorm's input gradient is added
+ * onto the skip path's (which is already there) instead of being summed by a separate element-wise kernel. */
+int iit_lnpre_bwd_accumulate(const void* dy, const void* y, const float* rstd, void* dx, int dtype, int64_t rows, int d,
+                             void* stream);
 /* pre = x + bias (+ resid); out = act(pre), act 0: identity, 1: gelu_new. pre_out optional (hook_pre). */
 int iit_bias_act_fwd(const void* x, const float* bias, const void* resid, void* pre_out, void* out, int dtype,
                      int64_t rows, int n, int act, void* stream);
