@@ -70,7 +70,6 @@ SIGNATURES = {
     "iit_conv2d_dgrad_tc_accumulate": [_vp, _vp, _vp, _ConvP, _vp],
     "iit_conv2d_patch_fusable": [_ConvP],
     "iit_conv2d_fprop_tc_patch": [_vp, _vp, _vp, _ConvP, _vp, _vp, _vp, C.POINTER(C.c_int32), _vp],
-    "iit_bn_act_fwd_stats": [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp],
     "iit_bn_act_bwd_apply_box": [_vp, _vp, _vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, C.POINTER(C.c_int32), _vp],
     "iit_gemm_bias_act_tc": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp],
     "iit_gemm_dgrad_gelu_tc": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _vp],

@@ -61,50 +61,18 @@ __device__ __forceinline__ void load_consts(const float* __restrict__ a, int c0,
 }
 
 // ---- forward: y = [relu]((x - mean) * invstd * gamma + beta [+ res]) ---------------------------------------
-// Batch statistics finalised INSIDE the forward kernel (`fin.sum != nullptr`): every thread derives mean / invstd of its own
-// channels from the fp64 sums (two fp64 multiplies and one fma per channel, then fp32: no fp64 division or square root on the
-// way), and the block that finishes LAST publishes mean / invstd for the backward, moves the running statistics, clears the
-// sums for their next use and bumps num_batches_tracked -- what iit_bn_finalize did in a launch of its own (95 per step).
-struct BnFinalize {
-  const double* sum; const double* sq;        // [C] each; cleared by the last block when `clear`
-  double inv_rows, unbias;                    // 1 / rows, rows / (rows - 1)
-  float eps, momentum;
-  float* mean_out; float* invstd_out;         // [C] fp32, for the backward
-  float* rmean; float* rvar;                  // running statistics (may be null)
-  long long* tracked;                         // num_batches_tracked (may be null)
-  unsigned int* ticket;                       // zero between launches
-  int clear;
-};
-__device__ __forceinline__ void bn_channel_stats(double s, double q, const BnFinalize& fin, float* m_out, float* is_out, double* var_out) {
-  const double m = s * fin.inv_rows;
-  double var = q * fin.inv_rows - m * m;
-  if (var < 0) var = 0;
-  *m_out = (float)m;
-  *is_out = 1.0f / sqrtf((float)var + fin.eps);
-  *var_out = var;
-}
-
 template <typename T>
 __global__ void __launch_bounds__(256) bn_act_fwd_fast_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y,
                                                               int64_t npacks, int C, const float* __restrict__ mean,
                                                               const float* __restrict__ invstd, const float* __restrict__ gamma,
                                                               const float* __restrict__ beta, int relu,
-                                                              uint8_t* __restrict__ mask, BnFinalize fin) {
+                                                              uint8_t* __restrict__ mask) {
   constexpr int NP = Pack<T>::N;
   constexpr int U = 2;                    // packs (and their residuals) in flight per thread: 23.7 -> 23.4 ms per step against one
   const int64_t tid = (int64_t)blockIdx.x * 256 + threadIdx.x, stride = (int64_t)gridDim.x * 256;
   const int c0 = (int)((tid * NP) % C);   // invariant: stride * NP is a multiple of C
   float mu[NP], is[NP], g[NP], b[NP];
-  if (fin.sum != nullptr) {
-#pragma unroll
-    for (int j = 0; j < NP; ++j) {
-      double var;
-      bn_channel_stats(fin.sum[c0 + j], fin.sq[c0 + j], fin, &mu[j], &is[j], &var);
-    }
-  } else {
-    load_consts<NP>(mean, c0, mu); load_consts<NP>(invstd, c0, is);
-  }
-  load_consts<NP>(gamma, c0, g); load_consts<NP>(beta, c0, b);
+  load_consts<NP>(mean, c0, mu); load_consts<NP>(invstd, c0, is); load_consts<NP>(gamma, c0, g); load_consts<NP>(beta, c0, b);
   auto finish = [&](int64_t i, const uint4& rx, const uint4& rr) {
     float v[NP], o[NP];
     Pack<T>::unpack(rx, v);
@@ -145,31 +113,6 @@ __global__ void __launch_bounds__(256) bn_act_fwd_fast_kernel(const T* __restric
     uint4 rr = make_uint4(0, 0, 0, 0);
     if (res) rr = *reinterpret_cast<const uint4*>(res + i * NP);
     finish(i, rx, rr);
-  }
-  if (fin.sum == nullptr) return;
-  // every block has read the sums before it gets here; the one that arrives last owns them
-  __shared__ int s_last;
-  __syncthreads();
-  if (threadIdx.x == 0) s_last = (atomicAdd(fin.ticket, 1u) == gridDim.x - 1) ? 1 : 0;
-  __syncthreads();
-  if (!s_last) return;
-  for (int c = threadIdx.x; c < C; c += 256) {
-    float m, isd;
-    double var;
-    bn_channel_stats(fin.sum[c], fin.sq[c], fin, &m, &isd, &var);
-    fin.mean_out[c] = m;
-    fin.invstd_out[c] = isd;
-    if (fin.rmean != nullptr) {
-      fin.rmean[c] = (float)((1.0 - fin.momentum) * fin.rmean[c] + fin.momentum * (fin.sum[c] * fin.inv_rows));
-      fin.rvar[c] = (float)((1.0 - fin.momentum) * fin.rvar[c] + fin.momentum * (var * fin.unbias));
-    }
-  }
-  __syncthreads();
-  if (fin.clear)
-    for (int c = threadIdx.x; c < C; c += 256) { const_cast<double*>(fin.sum)[c] = 0.0; const_cast<double*>(fin.sq)[c] = 0.0; }
-  if (threadIdx.x == 0) {
-    if (fin.tracked != nullptr) *fin.tracked += 1;
-    *fin.ticket = 0u;
   }
 }
 
@@ -654,30 +597,11 @@ int bn_stats_fast(const void* x, int dtype, int64_t rows, int C, double* sum, do
 int bn_act_fwd_fast(const void* x, const void* res, void* y, int dtype, int64_t rows, int C, const float* mean, const float* invstd,
                     const float* gamma, const float* beta, int relu, uint8_t* mask, cudaStream_t st) {
   const int64_t npacks = rows * C / pack_n(dtype);
-  BnFinalize fin{};
   IIT_DISPATCH_DTYPE(dtype, T, {
     bn_act_fwd_fast_kernel<T><<<grid_for(npacks, 256 * 2), 256, 0, st>>>((const T*)x, (const T*)res, (T*)y, npacks, C, mean, invstd,
-                                                                        gamma, beta, relu, mask, fin);
+                                                                        gamma, beta, relu, mask);
   })
   IIT_LAUNCH_CHECK("iit_bn_act_fwd");
-  return 0;
-}
-
-// the forward with the statistics finalised inside it (BnFinalize)
-int bn_act_fwd_stats_fast(const void* x, const void* res, void* y, int dtype, int64_t rows, int C, double* sum, double* sq, float eps,
-                          float momentum, float* mean_out, float* invstd_out, float* rmean, float* rvar, long long* tracked,
-                          unsigned int* ticket, int clear, const float* gamma, const float* beta, int relu, uint8_t* mask,
-                          cudaStream_t st) {
-  const int64_t npacks = rows * C / pack_n(dtype);
-  BnFinalize fin{};
-  fin.sum = sum; fin.sq = sq; fin.inv_rows = 1.0 / (double)rows; fin.unbias = rows > 1 ? (double)rows / (double)(rows - 1) : 1.0;
-  fin.eps = eps; fin.momentum = momentum; fin.mean_out = mean_out; fin.invstd_out = invstd_out; fin.rmean = rmean; fin.rvar = rvar;
-  fin.tracked = tracked; fin.ticket = ticket; fin.clear = clear;
-  IIT_DISPATCH_DTYPE(dtype, T, {
-    bn_act_fwd_fast_kernel<T><<<grid_for(npacks, 256 * 2), 256, 0, st>>>((const T*)x, (const T*)res, (T*)y, npacks, C, nullptr, nullptr,
-                                                                        gamma, beta, relu, mask, fin);
-  })
-  IIT_LAUNCH_CHECK("iit_bn_act_fwd_stats");
   return 0;
 }
 

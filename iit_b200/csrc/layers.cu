@@ -605,33 +605,6 @@ extern "C" int iit_bn_act_bwd_apply(const void* dy, const void* y, const void* x
   return 0;
 }
 
-namespace iit {
-int bn_act_fwd_stats_fast(const void* x, const void* res, void* y, int dtype, int64_t rows, int C, double* sum, double* sq, float eps,
-                          float momentum, float* mean_out, float* invstd_out, float* rmean, float* rvar, long long* tracked,
-                          unsigned int* ticket, int clear, const float* gamma, const float* beta, int relu, uint8_t* mask,
-                          cudaStream_t st);
-}
-
-extern "C" int iit_bn_act_fwd_stats(const void* x, const void* residual, void* y, int dtype, int64_t rows, int c, double* sum,
-                                    double* sqsum, float eps, float momentum, float* mean_out, float* invstd_out,
-                                    float* running_mean, float* running_var, int64_t* num_batches_tracked, unsigned int* ticket,
-                                    int clear_sums, const float* gamma, const float* beta, int relu, uint8_t* relu_mask,
-                                    void* stream) {
-  const char* name = "iit_bn_act_fwd_stats";
-  IIT_REQUIRE(x && y && sum && sqsum && mean_out && invstd_out && gamma && beta && ticket && rows >= 1, "%s: bad arguments", name);
-  IIT_REQUIRE((running_mean == nullptr) == (running_var == nullptr), "%s: running stats go together", name);
-  if (!relu) relu_mask = nullptr;
-  if (bn_fast_ok(dtype, c, x, residual, y, mean_out, invstd_out) && bn_fast_ok(dtype, c, gamma, beta, nullptr, nullptr, nullptr))
-    return bn_act_fwd_stats_fast(x, residual, y, dtype, rows, c, sum, sqsum, eps, momentum, mean_out, invstd_out, running_mean,
-                                 running_var, reinterpret_cast<long long*>(num_batches_tracked), ticket, clear_sums, gamma, beta,
-                                 relu, relu_mask, as_stream(stream));
-  // shapes the vector kernel does not take: the two launches it replaces
-  if (iit_bn_finalize(sum, sqsum, rows, c, eps, momentum, mean_out, invstd_out, running_mean, running_var, num_batches_tracked,
-                      clear_sums, stream))
-    return 1;
-  return iit_bn_act_fwd(x, residual, y, dtype, rows, c, mean_out, invstd_out, gamma, beta, relu, relu_mask, stream);
-}
-
 extern "C" int iit_bn_act_bwd_apply_box(const void* dy, const void* y, const void* x, void* dx, void* dres, int dtype, int64_t rows,
                                         int c, const float* mean, const float* invstd, const float* gamma, const double* dgamma,
                                         const double* dbeta, int relu, const uint8_t* relu_mask, int h, int w, const int32_t* box6,

@@ -143,14 +143,6 @@ class BatchNorm2d(nn.Module):
             self.__dict__["_bacc"] = acc
         return acc
 
-    def ticket(self, device):
-        """One zeroed device uint32 for the forward kernel's last-block hand-over (it leaves it zero)."""
-        tk = self.__dict__.get("_ticket")
-        if tk is None or tk.device != device:
-            tk = torch.zeros(1, dtype=torch.int32, device=device)
-            self.__dict__["_ticket"] = tk
-        return tk
-
     def backward_buffers(self, x):
         """(persistent backward accumulator, (gamma.grad, beta.grad) when kernels may add into them) -- ops.direct_grad."""
         if not (x.is_cuda and torch.is_grad_enabled()):
@@ -164,7 +156,7 @@ class BatchNorm2d(nn.Module):
         try:
             return ops.bn_act(x, self.weight, self.bias, residual, self.running_mean, self.running_var, self.training,
                               self.momentum, self.eps, relu, sums, acc, self.num_batches_tracked if self.training else None,
-                              bacc, pgrads, slot, zero_box, self.ticket(x.device) if (self.training and x.is_cuda) else None)
+                              bacc, pgrads, slot, zero_box)
         except Exception:
             if acc is not None:
                 acc.zero_()      # a failed launch sequence must not leave partial sums behind

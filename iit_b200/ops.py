@@ -669,14 +669,13 @@ def new_bn_sums(c: int, device) -> torch.Tensor:
     return torch.zeros((2, c), dtype=torch.float64, device=device)
 
 
-FUSE_BN_FINALIZE = True  # batch statistics are finalised inside the BatchNorm forward kernel (iit_bn_act_fwd_stats; tests flip it)
 BN_RELU_MASK = True     # BatchNorm+ReLU forward keeps a bit mask of the positive outputs for its backward (tests flip it)
 
 
 class _BNActFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums, acc, tracked,
-                bacc, pgrads, slot=None, zero_box=None, ticket=None):
+                bacc, pgrads, slot=None, zero_box=None):
         _require_cuda(x, gamma, beta, residual)
         x = _cl(x)
         n, c, h, w = x.shape
@@ -684,7 +683,6 @@ class _BNActFn(torch.autograd.Function):
         st = _stream()
         if residual is not None:
             residual = _cl(residual)
-        fin = None       # (sums, clear): statistics to be finalised inside the forward kernel
         if training:
             clear = 0
             if sums is None:
@@ -695,11 +693,8 @@ class _BNActFn(torch.autograd.Function):
                 clear = 1
             mean = torch.empty(c, dtype=torch.float32, device=x.device)
             invstd = torch.empty(c, dtype=torch.float32, device=x.device)
-            if ticket is not None and FUSE_BN_FINALIZE:
-                fin = (sums, clear)
-            else:
-                call("iit_bn_finalize", _p(sums[0]), _p(sums[1]), rows, c, float(eps), float(momentum), _p(mean), _p(invstd),
-                     _p(running_mean), _p(running_var), _p(tracked), clear, st)
+            call("iit_bn_finalize", _p(sums[0]), _p(sums[1]), rows, c, float(eps), float(momentum), _p(mean), _p(invstd),
+                 _p(running_mean), _p(running_var), _p(tracked), clear, st)
         else:
             mean = running_mean
             invstd = torch.empty(c, dtype=torch.float32, device=x.device)
@@ -709,13 +704,8 @@ class _BNActFn(torch.autograd.Function):
         mask = None
         if BN_RELU_MASK and relu and any(ctx.needs_input_grad[:4]):
             mask = torch.empty(rows * c // (8 if x.dtype == torch.bfloat16 else 4), dtype=torch.uint8, device=x.device)
-        if fin is not None:     # statistics finalised inside the forward kernel: one launch instead of two
-            call("iit_bn_act_fwd_stats", _p(x), _p(residual), _p(y), _dt(x), rows, c, _p(fin[0][0]), _p(fin[0][1]), float(eps),
-                 float(momentum), _p(mean), _p(invstd), _p(running_mean), _p(running_var), _p(tracked), _p(ticket), fin[1],
-                 _p(gamma), _p(beta), int(relu), _p(mask), st)
-        else:
-            call("iit_bn_act_fwd", _p(x), _p(residual), _p(y), _dt(x), rows, c, _p(mean), _p(invstd), _p(gamma), _p(beta),
-                 int(relu), _p(mask), st)
+        call("iit_bn_act_fwd", _p(x), _p(residual), _p(y), _dt(x), rows, c, _p(mean), _p(invstd), _p(gamma), _p(beta),
+             int(relu), _p(mask), st)
         ctx.save_for_backward(x, y if relu else None, gamma, mean, invstd, mask)
         ctx.relu, ctx.training, ctx.has_res = relu, training, residual is not None
         ctx.bacc, ctx.pgrads = bacc, pgrads
@@ -752,7 +742,7 @@ class _BNActFn(torch.autograd.Function):
             raise
         if ctx.slot is not None and dres is not None and USE_GRAD_SLOTS:
             ctx.slot.put(dres)       # the block input's other consumer (conv1) adds its gradient onto this (GradSlot)
-        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None, None, None, None, None, None, None, None
+        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None, None, None, None, None, None, None
 
 
 def _bn_param_grads(red, c, pgrads, clear, st):
@@ -767,13 +757,13 @@ def _bn_param_grads(red, c, pgrads, clear, st):
 
 
 def bn_act(x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums=None, acc=None,
-           tracked=None, bacc=None, pgrads=None, slot=None, zero_box=None, ticket=None):
+           tracked=None, bacc=None, pgrads=None, slot=None, zero_box=None):
     """`sums`: statistics already accumulated by the producing convolution's epilogue; `acc`: the layer's persistent
     fp64 accumulator [2, C] (kept zero between uses; `sums` may be it); `tracked`: num_batches_tracked, incremented by the
     finalize kernel; `bacc`: the same kind of accumulator for the backward's sums; `pgrads`: (gamma, beta) gradient buffers
     to add into (direct_grad)."""
     return _BNActFn.apply(x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu, sums, acc, tracked,
-                          bacc, pgrads, slot, zero_box, ticket)
+                          bacc, pgrads, slot, zero_box)
 
 
 class _BNReluPoolFn(torch.autograd.Function):

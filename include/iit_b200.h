@@ -322,14 +322,6 @@ int iit_bn_act_bwd_apply(const void* dy, const void* y, const void* x, void* dx,
 /* y = x / scale, element-wise (n a multiple of 4; y may alias x). The forward hook of the stop-gradient pair
  * (`hook_point_out / scale`, iit/model_pairs/stop_grad_pair.py:37-44); its backward is the same call on the gradient. */
 int iit_div_scalar(const void* x, void* y, int dtype, int64_t n, float scale, void* stream);
-/* iit_bn_finalize + iit_bn_act_fwd as ONE launch: every thread derives mean / invstd of its channels from the fp64 sums, the
- * block that finishes last publishes them (mean_out / invstd_out, for the backward), updates the running statistics and
- * num_batches_tracked and, with clear_sums, zeroes the sums. ticket: one device uint32, zero before the first call (the kernel
- * leaves it zero). invstd is computed in fp32 (1 / sqrtf(var + eps)) from the fp64 variance. */
-int iit_bn_act_fwd_stats(const void* x, const void* residual, void* y, int dtype, int64_t rows, int c, double* sum, double* sqsum,
-                         float eps, float momentum, float* mean_out, float* invstd_out, float* running_mean, float* running_var,
-                         int64_t* num_batches_tracked, unsigned int* ticket, int clear_sums, const float* gamma, const float* beta,
-                         int relu, uint8_t* relu_mask, void* stream);
 /* iit_bn_act_bwd_apply for a BatchNorm whose input was interchange-patched inside the producing convolution
  * (iit_conv2d_fprop_tc_patch): dx is written as ZERO for rows p in [box6[0], box6[1]), columns q in [box6[2], box6[3]) of every
  * h x w image and channels in [box6[4], box6[5]) -- the CopySlices backward of `out[idx] = cache[idx]`

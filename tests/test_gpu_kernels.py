@@ -1117,42 +1117,3 @@ def test_bf16_attention_and_lnpre_vector_kernels_match_the_fp32_kernels():
         yb.backward(gy.float().to(DEV))
         torch.testing.assert_close(ya.float(), yb, rtol=1e-2, atol=1e-2)
         torch.testing.assert_close(a.grad.float(), b.grad, rtol=3e-2, atol=3e-2)
-
-
-def test_bn_forward_with_fused_finalize_matches_the_two_launch_path():
-    """iit_bn_act_fwd_stats (statistics finalised inside the forward kernel, the last block publishing mean / invstd, moving
-    the running statistics and clearing the sums) against iit_bn_finalize + iit_bn_act_fwd: outputs, saved statistics,
-    running statistics, num_batches_tracked, cleared accumulator, gradients -- over several calls on one layer."""
-    from iit_b200 import ops
-    from iit_b200.nn.resnet import BatchNorm2d
-    g = torch.Generator().manual_seed(8)
-    for dtype, tol in ((torch.float32, 1e-5), (torch.bfloat16, 1e-2)):
-        for (n, c, hw, relu, with_res) in [(37, 64, 7, True, True), (512, 256, 4, True, False), (9, 512, 2, False, False)]:
-            outs = {}
-            for fused in (True, False):
-                ops.FUSE_BN_FINALIZE = fused
-                try:
-                    bn = BatchNorm2d(c).to(DEV)
-                    bn.train()
-                    rec = []
-                    for it in range(3):
-                        gi = torch.Generator().manual_seed(100 + it)
-                        x = (torch.randn(n, c, hw, hw, generator=gi) * 2 + 0.3).to(DEV).to(dtype).contiguous(memory_format=torch.channels_last).requires_grad_(True)
-                        r = torch.randn(n, c, hw, hw, generator=gi).to(DEV).to(dtype).contiguous(memory_format=torch.channels_last) if with_res else None
-                        y = bn(x, residual=r, relu=relu)
-                        y.float().square().mean().backward()
-                        rec.append((y.detach().float().clone(), x.grad.float().clone(), bn.weight.grad.clone()))
-                        bn.weight.grad = None
-                        bn.bias.grad = None
-                    outs[fused] = (rec, bn.running_mean.clone(), bn.running_var.clone(), int(bn.num_batches_tracked),
-                                   bn.accumulator(torch.device(DEV, 0)).clone())
-                finally:
-                    ops.FUSE_BN_FINALIZE = True
-            (ra, rma, rva, ta, acca), (rb, rmb, rvb, tb, accb) = outs[True], outs[False]
-            assert ta == tb == 3 and float(acca.abs().max()) == 0.0 and float(accb.abs().max()) == 0.0
-            torch.testing.assert_close(rma, rmb, rtol=1e-6, atol=1e-7)
-            torch.testing.assert_close(rva, rvb, rtol=1e-6, atol=1e-7)
-            for (ya, ga, wa), (yb, gb, wb) in zip(ra, rb):
-                torch.testing.assert_close(ya, yb, rtol=tol, atol=tol)
-                torch.testing.assert_close(ga, gb, rtol=10 * tol, atol=tol)
-                torch.testing.assert_close(wa, wb, rtol=10 * tol, atol=10 * tol)
