@@ -19,7 +19,8 @@ from iit_b200.tasks.mnist_pvr.get_alignment import get_alignment
 from iit_b200.utils.wrapper import get_hook_points
 
 
-def evaluate_model_on_ablations(ll_model, task, test_batches, eval_args, bank, verbose=False, dp=None, hook_points=None):
+def evaluate_model_on_ablations(ll_model, task, test_batches, eval_args, bank, verbose=False, dp=None, hook_points=None,
+                                share_base_prefix=True):
     """`test_batches`: list of base inputs `(x, y, intermediate_vars)` already on the device (this rank's share);
     `bank`: DigitBank. Returns {hook_point: {hl_node: float}} like the reference, plus the evaluated pair count under
     the key "_pairs" when eval_args.get("count_pairs")."""
@@ -39,10 +40,18 @@ def evaluate_model_on_ablations(ll_model, task, test_batches, eval_args, bank, v
                                                   ll_model=ll_model)
                 pair = IITModelPair(hl_model, ll_model, corr=corr)
                 pair.stop_source_run_at_hook = True
+                # the base run is the same for every node up to the residual block that holds the hook point: compute that
+                # prefix once per batch and let each node's base run resume there (ResNet18LL.resume_point)
+                rp = ll_model.resume_point(hook_point) if (share_base_prefix and hasattr(ll_model, "resume_point")) else None
+                prefixes = None
+                if rp is not None:
+                    prefixes = [ll_model.run_with_cache(b[0], names_filter=[rp[1]], stop_when_cached=True)[1][rp[1]]
+                                for b in test_batches]
                 for hl_node in corr.keys():
                     per_batch = t.zeros((len(test_batches), 2), dtype=t.int64, device=test_batches[0][0].device)
                     for bi, base_input in enumerate(test_batches):
                         ablated = bank.patch_batch_at_hl(base_input[0], base_input[2], hl_node, base_input[1])
+                        pair.base_resume = (rp[0], prefixes[bi]) if rp is not None else None
                         hl_output, ll_output = pair.do_intervention(base_input, ablated, hl_node)
                         changed = ablated[1] != base_input[1]
                         ops.iia_count(ll_output, hl_output, changed=changed, counts=per_batch[bi])

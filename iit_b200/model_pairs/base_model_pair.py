@@ -141,8 +141,12 @@ class BaseModelPair(ABC):
         ll_nodes = self.corr[hl_node]
         hl_output = self.hl_intervention(base_input, ablation_input, hl_node)
         self.ll_source_run(ablation_x, ll_nodes)
+        # `base_resume` (set by the causality sweep): the base run's prefix up to the hooked block was computed once for all
+        # the nodes interchanged at this hook point; the run resumes from that block's cached input
+        resume = getattr(self, "base_resume", None)
+        kw = {"resume": resume} if resume is not None else {}
         ll_output = self.ll_model.run_with_hooks(
-            base_x, fwd_hooks=[(n.name, self.make_ll_ablation_hook(n)) for n in ll_nodes])
+            base_x, fwd_hooks=[(n.name, self.make_ll_ablation_hook(n)) for n in ll_nodes], **kw)
         if verbose:
             print(f"{hl_node=}, {ll_nodes=}\n{hl_output=}")
         return hl_output, ll_output

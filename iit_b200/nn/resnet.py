@@ -376,10 +376,40 @@ class ResNet18LL(HookedRootModule):
         model pairs call this before replaying captured graphs (ops.stem_cols)."""
         ops.refresh_batch_operands(x)
 
-    def forward(self, x):
+    # --- resuming a forward pass at a residual block -----------------------------------------------------------
+    # The causality sweep interchanges, at ONE hook point, every HL node in turn: the base run is identical up to the
+    # residual block that holds the hook point, so its prefix is computed once per batch (cached block input) and each node's
+    # base run resumes there (`forward(x, resume=(block, tensor))`). Legal in eval mode only (nothing upstream has a side effect).
+    _BLOCK_INPUTS = ["mod.maxpool.hook_point", "mod.layer1.mod.0.hook_point", "mod.layer1.hook_point", "mod.layer2.mod.0.hook_point",
+                     "mod.layer2.hook_point", "mod.layer3.mod.0.hook_point", "mod.layer3.hook_point", "mod.layer4.mod.0.hook_point"]
+
+    def resume_point(self, hook_name: str):
+        """(block number 0..7, name of the hook point that carries that block's input) for a hook point inside a residual
+        block; None for the stem's hook points and everything after the last block."""
+        parts = hook_name.split(".")
+        if len(parts) >= 5 and parts[0] == "mod" and parts[1].startswith("layer") and parts[2] == "mod" and parts[3] in ("0", "1"):
+            layer = int(parts[1][5:])
+            if 1 <= layer <= 4 and len(parts) > 5:        # strictly inside the block (not the block's own output hook point)
+                b = 2 * (layer - 1) + int(parts[3])
+                return b, self._BLOCK_INPUTS[b]
+        return None
+
+    def forward(self, x, resume=None):
         m = self.mod
         if self.act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES and x.is_cuda and self._filter_shadow_stale():
             self.refresh_filter_shadow()
+        if resume is not None:
+            if self.training or torch.is_grad_enabled():
+                raise RuntimeError("resume= skips the layers before a block: eval mode under no_grad only")
+            first, x = resume
+            for b in range(first, 8):
+                layer: Wrapped = getattr(m, f"layer{b // 2 + 1}")
+                x = self._block(layer.mod[b % 2], x)
+                if b % 2 == 1:
+                    x = layer.hook_point(x)
+            x = m.avgpool.hook_point(m.avgpool.mod(x))
+            x = torch.flatten(x, 1)
+            return m.fc.hook_point(m.fc.mod(x))
         stem_tc = self.act_dtype == torch.bfloat16 and ops.USE_TENSOR_CORES and m.conv1.mod.is_stem()
         if not stem_tc and (x.dtype != self.act_dtype or not ops._is_cl(x)):
             # the tensor-core stem reads the caller's tensor (fp32 NCHW included) directly; otherwise convert

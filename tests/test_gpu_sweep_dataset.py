@@ -142,3 +142,26 @@ def test_causality_sweep_matches_oracle_on_the_same_counterfactuals(task, n_node
             want = float(torch.stack(ratios).sum() / len(ratios))
             got = [v for n, v in stats[hp].items() if str(n) == node_name][0]
             assert abs(got - want) <= 1e-6, (hp, node_name, got, want)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_sweep_with_shared_base_prefix_equals_full_base_runs(dtype):
+    """The sweep computes the base run's prefix (everything before the residual block that holds the hook point) once per
+    batch and resumes each node's base run there: same statistics, bit for bit, as full base runs (eval mode)."""
+    from iit_b200 import eval_causality
+    from iit_b200.tasks.mnist_pvr.get_alignment import get_alignment
+    ll, _, _ = get_alignment("mnist_pvr", {"input_shape": (1, 3, 56, 56)}, device=DEV, dtype=dtype)
+    ll.load_state_dict(R.resnet18_state_dict(0))
+    batches = [tuple(t.to(DEV) for t in R.synthetic_pvr(32, 60 + i)) for i in range(2)]
+    hooks = ["mod.conv1.hook_point", "mod.layer1.mod.0.mod.conv1.hook_point", "mod.layer2.mod.0.mod.conv2.hook_point",
+             "mod.layer3.mod.1.mod.conv2.hook_point", "mod.layer4.mod.1.mod.conv1.hook_point"]
+    assert ll.resume_point(hooks[0]) is None
+    assert ll.resume_point(hooks[3]) == (5, "mod.layer3.mod.0.hook_point")
+    assert ll.resume_point("mod.layer2.mod.0.mod.conv1.hook_point") == (2, "mod.layer1.hook_point")
+    res = []
+    for share in (True, False):
+        bank, _, _ = _bank(seed=9)
+        res.append(eval_causality.evaluate_model_on_ablations(ll, "pvr_leaky", batches, {"batch_size": 32}, bank, hook_points=hooks,
+                                                              share_base_prefix=share))
+    for hp in hooks:
+        assert {str(k): v for k, v in res[0][hp].items()} == {str(k): v for k, v in res[1][hp].items()}, hp
