@@ -39,6 +39,11 @@ class Relayout(C.Structure):
                 ("to_crsk", C.c_int32), ("dtype", C.c_int32), ("out_pitch", C.c_int64)]
 
 
+class WgradMap(C.Structure):
+    """iit_wgrad_map_t"""
+    _fields_ = [("dst", C.c_void_p), ("size", C.c_int32 * 3), ("reserved", C.c_int32), ("stride", C.c_int64 * 3), ("offset", C.c_int64)]
+
+
 class HlSpec(C.Structure):
     """iit_hl_spec_t"""
     _fields_ = [("mode", C.c_int32), ("node", C.c_int32), ("base", C.c_void_p), ("src", C.c_void_p), ("names", C.c_void_p),
@@ -76,6 +81,7 @@ SIGNATURES = {
     "iit_conv2d_wgrad_tc_scratch_bytes": [_ConvP],
     "iit_conv2d_wgrad_tc": [_vp, _vp, _vp, _ConvP, _vp, _sz, _vp],
     "iit_conv2d_wgrad_tc_accumulate": [_vp, _vp, _vp, _ConvP, _vp, _sz, _vp],
+    "iit_conv2d_wgrad_tc_scatter": [_vp, _vp, _ConvP, _vp, _sz, _vp, _i, _i64, _vp],
     "iit_bn_param_grads": [_vp, _i, _vp, _vp, _i, _i, _vp],
     "iit_conv2d_wgrad_scratch_bytes": [_ConvP],
     "iit_conv2d_wgrad": [_vp, _vp, _vp, _ConvP, _i, _vp, _sz, _vp],

@@ -1046,6 +1046,25 @@ __global__ void __launch_bounds__(256) tc_splitk_reduce_flat_kernel(const float*
   }
 }
 
+// The reduction written straight into parameter gradients whose layout differs from the [k][r][s][c] weight-gradient matrix
+// (the transformer's per-head [H, d_model, d_head] and [in][out] matrices): destination element idx of map m, decomposed by
+// the map's shape, reads the matrix at offset + a*stride0 + b*stride1 + c*stride2 from every partial and ADDS the sum to
+// dst[idx] (the optimizer's gradient buffer): no intermediate matrix, no strided addition by autograd.
+__global__ void __launch_bounds__(256) tc_splitk_reduce_map_kernel(const float* __restrict__ part, int64_t n, int splits,
+                                                                   const iit_wgrad_map_t* __restrict__ maps) {
+  const iit_wgrad_map_t mp = maps[blockIdx.y];
+  const int64_t numel = (int64_t)mp.size[0] * mp.size[1] * mp.size[2];
+  for (int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x; idx < numel; idx += (int64_t)gridDim.x * 256) {
+    const int c = (int)(idx % mp.size[2]);
+    const int64_t t = idx / mp.size[2];
+    const int b = (int)(t % mp.size[1]), a = (int)(t / mp.size[1]);
+    const int64_t src = mp.offset + a * mp.stride[0] + b * mp.stride[1] + c * mp.stride[2];
+    float s = 0.f;
+    for (int z = 0; z < splits; ++z) s += part[(int64_t)z * n + src];
+    mp.dst[idx] += s;
+  }
+}
+
 static void launch_splitk_reduce(const float* part, float* out, int64_t n, int splits, int accumulate, cudaStream_t st) {
   if (splits >= 16) tc_splitk_reduce_kernel<<<grid_for(n / 4, 64), 256, 0, st>>>(part, out, n, splits, accumulate);
   else tc_splitk_reduce_flat_kernel<<<grid_for(n / 4, 256), 256, 0, st>>>(part, out, n, splits, accumulate);
@@ -1223,7 +1242,9 @@ extern "C" size_t iit_conv2d_wgrad_tc_scratch_bytes(const iit_conv_t* d) {
 }
 
 static int wgrad_tc_impl(const void* dy, const void* x, float* dw, const iit_conv_t* d, void* scratch, size_t scratch_bytes,
-                         void* stream, int accumulate) {
+                         void* stream, int accumulate, const iit_wgrad_map_t* maps = nullptr, int n_maps = 0,
+                         int64_t max_map_numel = 0) {
+  if (maps != nullptr) dw = reinterpret_cast<float*>(scratch);     // unused placeholder that passes the pointer checks
   IIT_REQUIRE(dy && x && dw && d, "iit_conv2d_wgrad_tc: null pointer");
   IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "iit_conv2d_wgrad_tc: only bf16 3x3/pad-1 or 1x1/pad-0 convolutions, stride 1 "
               "or 2, with channel counts that are multiples of 64");
@@ -1239,7 +1260,11 @@ static int wgrad_tc_impl(const void* dy, const void* x, float* dw, const iit_con
     int rc = wgrad_win(dy, x, (float*)scratch, d, &nsplit, as_stream(stream), "iit_conv2d_wgrad_tc");
     if (rc) return rc;
     const int64_t n = (int64_t)d->k * d->r * d->s * d->c;
-    launch_splitk_reduce((const float*)scratch, dw, n, nsplit, accumulate, as_stream(stream));
+    if (maps != nullptr)
+      tc_splitk_reduce_map_kernel<<<dim3((unsigned)grid_for(max_map_numel, 256, 2), (unsigned)n_maps), 256, 0, as_stream(stream)>>>(
+          (const float*)scratch, n, nsplit, maps);
+    else
+      launch_splitk_reduce((const float*)scratch, dw, n, nsplit, accumulate, as_stream(stream));
     IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc(reduce)");
     return 0;
   }
@@ -1261,9 +1286,19 @@ static int wgrad_tc_impl(const void* dy, const void* x, float* dw, const iit_con
   if (rc) return rc;
   IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc");
   int64_t n = (int64_t)d->k * d->r * d->s * d->c;
-  launch_splitk_reduce((const float*)scratch, dw, n, splits, accumulate, st);
+  if (maps != nullptr)
+    tc_splitk_reduce_map_kernel<<<dim3((unsigned)grid_for(max_map_numel, 256, 2), (unsigned)n_maps), 256, 0, st>>>(
+        (const float*)scratch, n, splits, maps);
+  else
+    launch_splitk_reduce((const float*)scratch, dw, n, splits, accumulate, st);
   IIT_LAUNCH_CHECK("iit_conv2d_wgrad_tc(reduce)");
   return 0;
+}
+
+extern "C" int iit_conv2d_wgrad_tc_scatter(const void* dy, const void* x, const iit_conv_t* d, void* scratch, size_t scratch_bytes,
+                                           const iit_wgrad_map_t* maps_dev, int n_maps, int64_t max_map_numel, void* stream) {
+  IIT_REQUIRE(maps_dev && n_maps >= 1 && n_maps <= 16 && max_map_numel >= 1, "iit_conv2d_wgrad_tc_scatter: 1..16 maps (device array) expected");
+  return wgrad_tc_impl(dy, x, nullptr, d, scratch, scratch_bytes, stream, 1, maps_dev, n_maps, max_map_numel);
 }
 
 extern "C" int iit_conv2d_wgrad_tc(const void* dy, const void* x, float* dw, const iit_conv_t* d, void* scratch,

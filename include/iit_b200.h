@@ -230,6 +230,20 @@ int iit_gemm_bias_act_tc(const void* x, const void* w_oi, const float* bias, con
                          int64_t rows, int n_in, int n_out, int act, void* stream);
 int iit_gemm_dgrad_gelu_tc(const void* dy, const void* w_io, const void* pre, void* dpre, double* col_sum, double* col_sq,
                            int64_t rows, int n_in, int n_out, void* stream);
+/* iit_conv2d_wgrad_tc with the split-K reduction written straight INTO parameter gradients whose layout is not the
+ * [k][r][s][c] matrix (the transformer's per-head [H, d_model, d_head] tensors and [in][out] matrices): for every map m and
+ * destination element idx (decomposed by size[] in row-major order), dst[idx] += sum over partials of the matrix element at
+ * offset + a*stride[0] + b*stride[1] + c*stride[2]. maps_dev: DEVICE array of n_maps (<= 16) descriptors; max_map_numel: the
+ * largest destination. Replaces the strided additions autograd would otherwise make per parameter. */
+typedef struct {
+  float* dst;
+  int32_t size[3];
+  int32_t reserved;
+  int64_t stride[3];
+  int64_t offset;
+} iit_wgrad_map_t;
+int iit_conv2d_wgrad_tc_scatter(const void* dy, const void* x, const iit_conv_t* d, void* scratch, size_t scratch_bytes,
+                                const iit_wgrad_map_t* maps_dev, int n_maps, int64_t max_map_numel, void* stream);
 /* 3x3 / stride-1 / pad-1 convolutions with 64 -> 64 channels on images whose padded form fits shared memory
  * (layer1 of the ResNet) run on a "shifted-window" kernel inside the two entry points above: the padded image
  * is loaded once and every filter tap addresses it at a row offset. Same results bit for bit; this switch
