@@ -94,11 +94,9 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
   uint64_t* tmem_full = empty + STAGES;      // [2]
   uint64_t* tmem_empty = tmem_full + 2;      // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [2][BN] per-channel sum / sum of squares of one tile
+  float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [4 lane quarters][2][BN]: tc_flush_stats
   // [8 warps][32 rows][TC_STAGE_PITCH], 16-byte aligned: output transposition
-  uint8_t* s_stage = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(s_stat + 2 * BN) + 15) & ~uintptr_t(15));
-  if (bn_sum != nullptr)
-    for (int i = threadIdx.x; i < 2 * BN; i += TC_CONV_THREADS) s_stat[i] = 0.f;
+  uint8_t* s_stage = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(s_stat + 8 * BN) + 15) & ~uintptr_t(15));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kchunks = p.Cin / TC_BK;
@@ -212,27 +210,37 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
     const int wl = m % p.BW;
     const int hl = (m / p.BW) % p.BH;
     const int nl = m / (p.BW * p.BH);
-    const int e = threadIdx.x - 64;     // 0..255: owner of channel e of the current filter block's statistics
-    constexpr int NCH = (BN + 255) / 256;   // channels of the filter block owned by each of the 256 epilogue threads
-    double run_s[NCH], run_q[NCH];          // this CTA's running totals for channels run_co + e + 256*i
+    const int e = threadIdx.x - 64;     // 0..255: index among the epilogue threads
+    // BatchNorm statistics: running sums in registers (tc_store_packed), flushed when the filter block changes
+    float rstat[BN / 64][4];
 #pragma unroll
-    for (int i = 0; i < NCH; ++i) { run_s[i] = 0.0; run_q[i] = 0.0; }
+    for (int cc = 0; cc < BN / 64; ++cc) { rstat[cc][0] = 0.f; rstat[cc][1] = 0.f; rstat[cc][2] = 0.f; rstat[cc][3] = 0.f; }
+    int stat_tiles = 0;                 // tiles summed since the last flush (fp32 running sums are kept short)
     // Stores: a lane holds one pixel x 32 channels (64 bytes). Written as such, a warp store touches 32 lines with 16 bytes
     // each (half a sector): 10-15 % of the kernel. Each warp instead passes the chunk through its own staging rows and
     // stores 64 contiguous bytes per pixel: four lanes per pixel, pixels (lane/4) + 8i of the warp's 32.
     uint8_t* my_stage = s_stage + (warp - 2) * (32 * TC_STAGE_PITCH);
     const int sub = lane >> 2, piece = lane & 3;
     int swl[4], shl[4], snl[4];
+    int64_t soff[4];                    // offset of pixel (snl, shl, swl) from the box's first output pixel, plus this lane's piece
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int mm = quarter * 32 + sub + 8 * i;
       swl[i] = mm % p.BW; shl[i] = (mm / p.BW) % p.BH; snl[i] = mm / (p.BW * p.BH);
+      soff[i] = (((int64_t)snl[i] * p.OH + shl[i] * p.out_mul) * p.OW + swl[i] * p.out_mul) * p.Cout + piece * 8;
     }
+    const bool one_box = p.tiles_w == 1 && p.tiles_h == 1;     // the box covers whole images: no division per tile
     int run_co = -1;
     uint32_t it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      const int rt = tile % real_tiles;
+      const int rt = ksplit > 1 ? tile % real_tiles : tile;
       const int co0 = (rt % nblk) * BN;
+      if (bn_sum != nullptr && run_co >= 0 && (run_co != co0 || stat_tiles >= 16)) {
+        tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, run_co, bn_sum, bn_sq);
+        stat_tiles = 0;
+      }
+      run_co = co0;
+      ++stat_tiles;
       const uint32_t acc = it & 1, acc_phase = (it >> 1) & 1;
       if (nk > 0) {
         mbar_wait(&tmem_full[acc], acc_phase);
@@ -240,20 +248,19 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
       }
 #pragma unroll 1
      for (int mt = 0; mt < MT; ++mt) {
-      int t = (rt / nblk) * MT + mt;
+      int t = (nblk > 1 ? rt / nblk : rt) * MT + mt;
       const bool box_ok = t < mtiles;
-      const int tw = t % p.tiles_w; t /= p.tiles_w;
-      const int th = t % p.tiles_h; t /= p.tiles_h;
-      const int n = t * p.BNI + nl, pp = th * p.BH + hl, qq = tw * p.BW + wl;
+      int tw = 0, th = 0;
+      if (!one_box) { tw = t % p.tiles_w; t /= p.tiles_w; th = t % p.tiles_h; t /= p.tiles_h; }
+      const int n_box = t * p.BNI, p_box = th * p.BH, q_box = tw * p.BW;
+      const int n = n_box + nl, pp = p_box + hl, qq = q_box + wl;
       const bool ok = box_ok && n < p.N && pp < p.P && qq < p.Q;
+      __nv_bfloat16* const box_out =
+          out + (((int64_t)n_box * p.OH + (p_box * p.out_mul + p.out_oh)) * p.OW + (q_box * p.out_mul + p.out_ow)) * p.Cout + co0;
       __nv_bfloat16* sdst[4];      // the four pixels this lane stores a 16-byte piece of (nullptr: outside the tensor)
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int sn = t * p.BNI + snl[i], sp = th * p.BH + shl[i], sq = tw * p.BW + swl[i];
-        sdst[i] = (box_ok && sn < p.N && sp < p.P && sq < p.Q)
-                      ? out + (((int64_t)sn * p.OH + (sp * p.out_mul + p.out_oh)) * p.OW + (sq * p.out_mul + p.out_ow)) * p.Cout + co0 + piece * 8
-                      : nullptr;
-      }
+      for (int i = 0; i < 4; ++i)
+        sdst[i] = (box_ok && n_box + snl[i] < p.N && p_box + shl[i] < p.P && q_box + swl[i] < p.Q) ? box_out + soff[i] : nullptr;
 #pragma unroll
       for (int cc = 0; cc < BN / 64; ++cc) {
         const int c = cc * 64 + half * 32;
@@ -317,39 +324,11 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
           }
         }
         // store (64 contiguous bytes per pixel) and, for the BatchNorm that follows, per-channel sums of the values as stored
-        tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c, ok, bn_sum != nullptr ? s_stat + c : nullptr, s_stat + BN + c,
-                       p.accumulate != 0);
+        tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c, ok, rstat[cc], bn_sum != nullptr, p.accumulate != 0);
       }
      }  // mt
-      if (bn_sum != nullptr) {
-        asm volatile("bar.sync 1, 256;" ::: "memory");   // the eight epilogue warps only: the tile's sums are complete
-        if (run_co != co0) {
-#pragma unroll
-          for (int i = 0; i < NCH; ++i) {
-            const int ch = e + 256 * i;
-            if (run_co >= 0 && ch < BN) { atomicAdd(&bn_sum[run_co + ch], run_s[i]); atomicAdd(&bn_sq[run_co + ch], run_q[i]); }
-            run_s[i] = 0.0; run_q[i] = 0.0;
-          }
-          run_co = co0;
-        }
-#pragma unroll
-        for (int i = 0; i < NCH; ++i) {
-          const int ch = e + 256 * i;
-          if (ch < BN) {
-            run_s[i] += (double)s_stat[ch]; run_q[i] += (double)s_stat[BN + ch];
-            s_stat[ch] = 0.f; s_stat[BN + ch] = 0.f;
-          }
-        }
-        asm volatile("bar.sync 1, 256;" ::: "memory");   // zeroed before the next tile adds to it
-      }
     }
-    if (bn_sum != nullptr && run_co >= 0) {
-#pragma unroll
-      for (int i = 0; i < NCH; ++i) {
-        const int ch = e + 256 * i;
-        if (ch < BN) { atomicAdd(&bn_sum[run_co + ch], run_s[i]); atomicAdd(&bn_sq[run_co + ch], run_q[i]); }
-      }
-    }
+    if (bn_sum != nullptr && run_co >= 0) tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, run_co, bn_sum, bn_sq);
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -385,10 +364,8 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
   uint64_t* tmem_full = empty + STAGES;      // [2]
   uint64_t* tmem_empty = tmem_full + 2;      // [2] (the leader's are used)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [2][BN]
-  uint8_t* s_stage = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(s_stat + 2 * BN) + 15) & ~uintptr_t(15));
-  if (bn_sum != nullptr)
-    for (int i = threadIdx.x; i < 2 * BN; i += TC_CONV_THREADS) s_stat[i] = 0.f;
+  float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [4 lane quarters][2][BN]: tc_flush_stats
+  uint8_t* s_stage = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(s_stat + 8 * BN) + 15) & ~uintptr_t(15));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -487,40 +464,48 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
     const int hl = (m / p.BW) % p.BH;
     const int nl = m / (p.BW * p.BH);
     const int e = threadIdx.x - 64;                        // 0..255
-    constexpr int NCH = (BN + 255) / 256;
-    double run_s[NCH], run_q[NCH];                         // channels run_co + e + 256 * i
+    float rstat[BN / 64][4];                               // running BatchNorm statistics (tc_store_packed / tc_flush_stats)
 #pragma unroll
-    for (int i = 0; i < NCH; ++i) { run_s[i] = 0.0; run_q[i] = 0.0; }
+    for (int cc = 0; cc < BN / 64; ++cc) { rstat[cc][0] = 0.f; rstat[cc][1] = 0.f; rstat[cc][2] = 0.f; rstat[cc][3] = 0.f; }
+    int stat_tiles = 0;
     uint8_t* my_stage = s_stage + (warp - 2) * (32 * TC_STAGE_PITCH);
     const int sub = lane >> 2, piece = lane & 3;
     int swl[4], shl[4], snl[4];
+    int64_t soff[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int mm = quarter * 32 + sub + 8 * i;
       swl[i] = mm % p.BW; shl[i] = (mm / p.BW) % p.BH; snl[i] = mm / (p.BW * p.BH);
+      soff[i] = (((int64_t)snl[i] * p.OH + shl[i] * p.out_mul) * p.OW + swl[i] * p.out_mul) * p.Cout + piece * 8;
     }
+    const bool one_box = p.tiles_w == 1 && p.tiles_h == 1;
     int run_co = -1;
     uint32_t it = 0;
     for (int tile = pair; tile < total_tiles; tile += npairs, ++it) {
       const int co0 = (tile % nblk) * BN;
+      if (bn_sum != nullptr && run_co >= 0 && (run_co != co0 || stat_tiles >= 16)) {
+        tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, run_co, bn_sum, bn_sq);
+        stat_tiles = 0;
+      }
+      run_co = co0;
+      ++stat_tiles;
       const uint32_t acc = it & 1, acc_phase = (it >> 1) & 1;
       const uint32_t lead_empty = mapa_u32(smem_u32(&tmem_empty[acc]), 0);
       mbar_wait(&tmem_full[acc], acc_phase);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       int t = (tile / nblk) * 2 + (int)rank;
       const bool box_ok = t < mtiles;
-      const int tw = t % p.tiles_w; t /= p.tiles_w;
-      const int th = t % p.tiles_h; t /= p.tiles_h;
-      const int n = t * p.BNI + nl, pp = th * p.BH + hl, qq = tw * p.BW + wl;
+      int tw = 0, th = 0;
+      if (!one_box) { tw = t % p.tiles_w; t /= p.tiles_w; th = t % p.tiles_h; t /= p.tiles_h; }
+      const int n_box = t * p.BNI, p_box = th * p.BH, q_box = tw * p.BW;
+      const int n = n_box + nl, pp = p_box + hl, qq = q_box + wl;
       const bool ok = box_ok && n < p.N && pp < p.P && qq < p.Q;
+      __nv_bfloat16* const box_out =
+          out + (((int64_t)n_box * p.OH + (p_box * p.out_mul + p.out_oh)) * p.OW + (q_box * p.out_mul + p.out_ow)) * p.Cout + co0;
       __nv_bfloat16* sdst[4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int sn = t * p.BNI + snl[i], sp = th * p.BH + shl[i], sq = tw * p.BW + swl[i];
-        sdst[i] = (box_ok && sn < p.N && sp < p.P && sq < p.Q)
-                      ? out + (((int64_t)sn * p.OH + (sp * p.out_mul + p.out_oh)) * p.OW + (sq * p.out_mul + p.out_ow)) * p.Cout + co0 + piece * 8
-                      : nullptr;
-      }
+      for (int i = 0; i < 4; ++i)
+        sdst[i] = (box_ok && n_box + snl[i] < p.N && p_box + shl[i] < p.P && q_box + swl[i] < p.Q) ? box_out + soff[i] : nullptr;
 #pragma unroll
       for (int cc = 0; cc < BN / 64; ++cc) {
         const int c = cc * 64 + half * 32;
@@ -531,35 +516,10 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
           __syncwarp();
           if (lane == 0) mbar_arrive_cluster(lead_empty);
         }
-        tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c, ok, bn_sum != nullptr ? s_stat + c : nullptr, s_stat + BN + c,
-                       p.accumulate != 0);
-      }
-      if (bn_sum != nullptr) {
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        if (run_co != co0) {
-#pragma unroll
-          for (int i = 0; i < NCH; ++i) {
-            if (run_co >= 0 && e + 256 * i < BN) { atomicAdd(&bn_sum[run_co + e + 256 * i], run_s[i]); atomicAdd(&bn_sq[run_co + e + 256 * i], run_q[i]); }
-            run_s[i] = 0.0; run_q[i] = 0.0;
-          }
-          run_co = co0;
-        }
-#pragma unroll
-        for (int i = 0; i < NCH; ++i) {
-          const int ch = e + 256 * i;
-          if (ch < BN) {
-            run_s[i] += (double)s_stat[ch]; run_q[i] += (double)s_stat[BN + ch];
-            s_stat[ch] = 0.f; s_stat[BN + ch] = 0.f;
-          }
-        }
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c, ok, rstat[cc], bn_sum != nullptr, p.accumulate != 0);
       }
     }
-    if (bn_sum != nullptr && run_co >= 0) {
-#pragma unroll
-      for (int i = 0; i < NCH; ++i)
-        if (e + 256 * i < BN) { atomicAdd(&bn_sum[run_co + e + 256 * i], run_s[i]); atomicAdd(&bn_sq[run_co + e + 256 * i], run_q[i]); }
-    }
+    if (bn_sum != nullptr && run_co >= 0) tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, run_co, bn_sum, bn_sq);
   }
   // neither CTA may leave (or free the pair's TMEM) while its peer can still signal its barriers or read its operands
   __syncwarp();
@@ -581,7 +541,7 @@ template <int BN, int MT>
 static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16* out, const TcParams& p, int total_tiles,
                      cudaStream_t st, double* bn_sum, double* bn_sq) {
   constexpr int STAGES = 4;
-  constexpr size_t smem = STAGES * (MT * TC_BM * TC_BK * 2 + BN * TC_BK * 2) + (2 * STAGES + 4) * 8 + 16 + 2 * BN * 4 +
+  constexpr size_t smem = STAGES * (MT * TC_BM * TC_BK * 2 + BN * TC_BK * 2) + (2 * STAGES + 4) * 8 + 16 + 8 * BN * 4 +
                           16 + 8 * 32 * TC_STAGE_PITCH + 1024;
   static int ctas_per_sm_dev[kMaxDevices] = {};
   int& ctas_per_sm = ctas_per_sm_dev[current_device_slot()];
@@ -605,7 +565,7 @@ template <int BN>
 static int launch_tc2(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16* out, const TcParams& p, int total_tiles,
                       cudaStream_t st, double* bn_sum, double* bn_sq) {
   constexpr int STAGES = BN == 256 ? 6 : 8;
-  constexpr size_t smem = STAGES * (TC_BM * TC_BK * 2 + (BN / 2) * TC_BK * 2) + (2 * STAGES + 4) * 8 + 16 + 2 * BN * 4 + 16 +
+  constexpr size_t smem = STAGES * (TC_BM * TC_BK * 2 + (BN / 2) * TC_BK * 2) + (2 * STAGES + 4) * 8 + 16 + 8 * BN * 4 + 16 +
                           8 * 32 * TC_STAGE_PITCH + 1024;
   static int max_clusters_dev[kMaxDevices] = {};
   int& max_clusters = max_clusters_dev[current_device_slot()];

@@ -164,10 +164,13 @@ constexpr int TC_STAGE_PITCH = 80;   // bytes per staged pixel row: 64 of data, 
 
 // pk = this lane's 32 channels as 16 packed bf16 pairs; sdst[i] points at piece `piece` of pixel sub + 8i, channel 0 of the
 // filter block (nullptr: pixel outside the tensor); c = first channel of the chunk.
-// `sum` / `sq` (shared memory, 32 floats each, or nullptr): per-channel sum and sum of squares of the staged values are
-// added to them, for the BatchNorm that follows. The staged rows make this a column sum: lane (row parity, channel pair)
-// reads 16 words, against a 31-shuffle butterfly over registers (~450 instructions per chunk, which bounded the
-// small-reduction layers). Rows outside the tensor must be staged as zeros when statistics are taken.
+// `rs` (four registers of the calling lane, used when `stats`): running per-channel sum and sum of squares of the staged values,
+// for the BatchNorm that follows. The staged rows make this a column sum: lane (row parity `lane >> 4`, channel pair
+// `lane & 15`) reads 16 words and keeps {sum, sum, squares, squares} of its two channels over its 16 rows IN REGISTERS, across
+// chunks of the same columns and across tiles; tc_flush_stats combines parities, warps and CTAs when the filter block
+// changes. (Per chunk this used to end in 4 shuffles and 4 shared-memory atomics per lane -- compare-and-swap loops that
+// four warps fought over -- and two CTA barriers per tile: 40 % of a short-reduction layer's time.) Rows outside the
+// tensor must be staged as zeros when statistics are taken.
 // 8 bf16 values: dst[0..7] = v (plain 16-byte store) or dst[0..7] += v (ONE 16-byte reduction instruction,
 // red.global.add.noftz.v4.bf16x2 = REDG.E.ADD.BF16x8: the addition happens in L2, the SM neither loads the old values nor
 // waits for them). Every element receives exactly one addend per launch, so the result does not depend on any order.
@@ -181,8 +184,8 @@ __device__ __forceinline__ void st_or_add_bf16x8(__nv_bfloat16* dst, const uint4
 }
 
 __device__ __forceinline__ void tc_store_packed(const uint32_t (&pk)[16], uint8_t* stage, int lane, int sub, int piece,
-                                                __nv_bfloat16* const (&sdst)[4], int c, float* sum = nullptr,
-                                                float* sq = nullptr, bool accumulate = false) {
+                                                __nv_bfloat16* const (&sdst)[4], int c, float (&rs)[4], bool stats,
+                                                bool accumulate = false) {
 #pragma unroll
   for (int j = 0; j < 16; j += 4)
     *reinterpret_cast<uint4*>(stage + lane * TC_STAGE_PITCH + j * 4) = make_uint4(pk[j], pk[j + 1], pk[j + 2], pk[j + 3]);
@@ -192,35 +195,65 @@ __device__ __forceinline__ void tc_store_packed(const uint32_t (&pk)[16], uint8_
     const uint4 o = *reinterpret_cast<const uint4*>(stage + (sub + 8 * i) * TC_STAGE_PITCH + piece * 16);
     if (sdst[i] != nullptr) st_or_add_bf16x8(sdst[i] + c, o, accumulate);
   }
-  if (sum != nullptr) {
-    const int cp = lane & 15, par = lane >> 4;       // channels 2cp, 2cp+1 of rows par, par+2, ...
-    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+  if (stats) {
+    const uint8_t* col = stage + (lane >> 4) * TC_STAGE_PITCH + (lane & 15) * 4;       // channels 2cp, 2cp+1 of rows par, par+2, ...
+    float s0 = rs[0], s1 = rs[1], q0 = rs[2], q1 = rs[3];
 #pragma unroll
     for (int r = 0; r < 16; ++r) {
-      const uint32_t w = *reinterpret_cast<const uint32_t*>(stage + (2 * r + par) * TC_STAGE_PITCH + cp * 4);
+      const uint32_t w = *reinterpret_cast<const uint32_t*>(col + 2 * r * TC_STAGE_PITCH);
       const float f0 = __uint_as_float(w << 16), f1 = __uint_as_float(w & 0xffff0000u);
       s0 += f0; s1 += f1; q0 = fmaf(f0, f0, q0); q1 = fmaf(f1, f1, q1);
     }
-    s0 += __shfl_xor_sync(0xffffffffu, s0, 16); s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
-    q0 += __shfl_xor_sync(0xffffffffu, q0, 16); q1 += __shfl_xor_sync(0xffffffffu, q1, 16);
-    if (par == 0) {
-      atomicAdd(&sum[2 * cp], s0); atomicAdd(&sum[2 * cp + 1], s1);
-      atomicAdd(&sq[2 * cp], q0); atomicAdd(&sq[2 * cp + 1], q1);
-    }
+    rs[0] = s0; rs[1] = s1; rs[2] = q0; rs[3] = q1;
   }
   __syncwarp();   // the rows are rewritten by the next chunk
 }
 // the same from the fp32 accumulator values; `keep` = this lane's pixel lies inside the tensor
 __device__ __forceinline__ void tc_store_chunk(const uint32_t (&v)[32], uint8_t* stage, int lane, int sub, int piece,
-                                               __nv_bfloat16* const (&sdst)[4], int c, bool keep = true, float* sum = nullptr,
-                                               float* sq = nullptr, bool accumulate = false) {
+                                               __nv_bfloat16* const (&sdst)[4], int c, bool keep, float (&rs)[4], bool stats,
+                                               bool accumulate = false) {
   uint32_t pk[16];
 #pragma unroll
   for (int j = 0; j < 16; ++j) {
     __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
     pk[j] = keep ? *reinterpret_cast<uint32_t*>(&h) : 0u;
   }
-  tc_store_packed(pk, stage, lane, sub, piece, sdst, c, sum, sq, accumulate);
+  tc_store_packed(pk, stage, lane, sub, piece, sdst, c, rs, stats, accumulate);
+}
+__device__ __forceinline__ void tc_store_chunk(const uint32_t (&v)[32], uint8_t* stage, int lane, int sub, int piece,
+                                               __nv_bfloat16* const (&sdst)[4], int c, bool keep = true) {
+  float none[4] = {0.f, 0.f, 0.f, 0.f};
+  tc_store_chunk(v, stage, lane, sub, piece, sdst, c, keep, none, false, false);
+}
+
+// The running statistics of the eight epilogue warps (tc_store_packed: rs[cc] = chunk cc * 64 + half * 32 of the filter block
+// at channel `co`) added to the global fp64 sums: row parities by one shuffle, the four lane quarters through s_stat
+// ([4 quarters][2][BN] floats), one fp64 atomic per channel and CTA; the registers restart at zero. Every epilogue thread
+// calls it (two named barriers over the 256 of them); e = its index among them.
+template <int BN>
+__device__ __forceinline__ void tc_flush_stats(float (&rs)[BN / 64][4], float* s_stat, int quarter, int half, int lane, int e,
+                                               int co, double* bn_sum, double* bn_sq) {
+#pragma unroll
+  for (int cc = 0; cc < BN / 64; ++cc) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) rs[cc][k] += __shfl_xor_sync(0xffffffffu, rs[cc][k], 16);
+    if (lane < 16) {
+      const int ch = cc * 64 + half * 32 + 2 * lane;
+      *reinterpret_cast<float2*>(s_stat + (quarter * 2 + 0) * BN + ch) = make_float2(rs[cc][0], rs[cc][1]);
+      *reinterpret_cast<float2*>(s_stat + (quarter * 2 + 1) * BN + ch) = make_float2(rs[cc][2], rs[cc][3]);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) rs[cc][k] = 0.f;
+  }
+  asm volatile("bar.sync 1, 256;" ::: "memory");
+  for (int ch = e; ch < BN; ch += 256) {
+    double s = 0.0, q = 0.0;
+#pragma unroll
+    for (int qd = 0; qd < 4; ++qd) { s += (double)s_stat[(qd * 2 + 0) * BN + ch]; q += (double)s_stat[(qd * 2 + 1) * BN + ch]; }
+    atomicAdd(&bn_sum[co + ch], s);
+    atomicAdd(&bn_sq[co + ch], q);
+  }
+  asm volatile("bar.sync 1, 256;" ::: "memory");   // s_stat may be rewritten
 }
 
 // ---- host side -----------------------------------------------------------------------------------

@@ -58,6 +58,7 @@ class _Holder(nn.Module):
     """Namespace module so that parameters / hook points get transformer_lens' dotted names."""
 
 
+DIRECT_WEIGHT_GRADS = True    # weight-gradient GEMMs add into the optimizer's gradient views (tests flip it to compare)
 FUSE_GELU_IN_GEMM = False   # True: gelu_new / its backward in the GEMM epilogues (iit_gemm_bias_act_tc act=1, iit_gemm_dgrad_gelu_tc)
 
 
@@ -262,7 +263,8 @@ class HookedTransformerLL(HookedRootModule):
             if buf is not None:
                 bias_specs = (*bias_specs, ("direct", buf))
         oi, io, st = self._shadow["bufs"][key]
-        return ops.linear_epi(x, oi, io, st["n_in"], st["n_out_pad"], st["specs"], st["params"], bias=bias, bias_specs=bias_specs,
+        specs = (ops.wgrad_direct_maps(st["specs"], st["params"], st) if DIRECT_WEIGHT_GRADS else None) or st["specs"]
+        return ops.linear_epi(x, oi, io, st["n_in"], st["n_out_pad"], specs, st["params"], bias=bias, bias_specs=bias_specs,
                               bias_params=bias_params, resid=resid, act=act, link_out=link_out, link_in=link_in, res_slot=res_slot)
 
     def _mlp_link(self, li):
@@ -279,7 +281,8 @@ class HookedTransformerLL(HookedRootModule):
         if sh is None or sh["versions"] is None:
             return None
         oi, io, st = sh["bufs"][key]
-        return ops.linear_prepared(x, oi, io, st["n_in"], st["n_out_pad"], st["specs"], st["params"])
+        specs = (ops.wgrad_direct_maps(st["specs"], st["params"], st) if DIRECT_WEIGHT_GRADS else None) or st["specs"]
+        return ops.linear_prepared(x, oi, io, st["n_in"], st["n_out_pad"], specs, st["params"])
 
     # ------------------------------------------------------------------------------------------
     def _check_hooks(self):

@@ -1054,6 +1054,43 @@ def linear_tokens(x2d: torch.Tensor, W_in_out: torch.Tensor) -> torch.Tensor:
     return _LinearTokensFn.apply(x2d, W_in_out)
 
 
+def wgrad_direct_maps(specs, params, cache: dict):
+    """Device table of iit_wgrad_map_t that lets the weight-gradient GEMM's split-K reduction add straight into the
+    optimizer's gradient views of `params` (direct_grad), each laid out as its `spec` (size, stride, offset) of the
+    [out_pad][in] matrix says -- or None when any of them may not be written in place. Returned as ("direct", specs,
+    table, n, max_numel), the form _LinearPreparedFn / _LinearEpiFn take in place of `specs`. `cache` belongs to the call
+    site: the table is rebuilt only when a gradient buffer moved."""
+    if not torch.is_grad_enabled():
+        return None
+    gs = [direct_grad(p) if p.requires_grad else None for p in params]
+    if any(g is None or not g.is_contiguous() for g in gs):
+        return None
+    key = tuple(g.data_ptr() for g in gs)
+    ent = cache.get("wgrad_maps")
+    if ent is None or ent[0] != key:
+        arr = (_lib.WgradMap * len(gs))()
+        biggest = 0
+        for m, g, (size, stride, offset) in zip(arr, gs, specs):
+            if tuple(g.shape) != tuple(size) or len(size) > 3:
+                return None
+            pad = 3 - len(size)
+            m.dst = g.data_ptr()
+            for i in range(3):
+                m.size[i] = 1 if i < pad else int(size[i - pad])
+                m.stride[i] = 0 if i < pad else int(stride[i - pad])
+            m.offset = int(offset)
+            biggest = max(biggest, g.numel())
+        host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+        ent = cache["wgrad_maps"] = (key, host.to(gs[0].device), len(gs), biggest)
+    return ("direct", specs, ent[1], ent[2], ent[3])
+
+
+def _split_direct(specs):
+    if isinstance(specs, tuple) and len(specs) == 5 and isinstance(specs[0], str) and specs[0] == "direct":
+        return specs[1], specs[2:]
+    return specs, None
+
+
 class _LinearPreparedFn(torch.autograd.Function):
     """y[T, out_pad] = x[T, in] @ W on the tensor-core GEMMs from PREPARED bf16 operands: `w_oi` [out_pad][in] for the
     forward, `w_io` [in][out_pad] for dgrad -- persistent copies the model refreshes in one launch after every weight
@@ -1073,7 +1110,8 @@ class _LinearPreparedFn(torch.autograd.Function):
         y = torch.empty((T, n_out_pad), dtype=x.dtype, device=x.device)
         call("iit_conv2d_fprop_tc", _p(x), _p(w_oi), _p(y), C.byref(d), None, None, _stream())
         ctx.save_for_backward(x, w_io)
-        ctx.d, ctx.specs = d, specs
+        ctx.specs, ctx.w_direct = _split_direct(specs)
+        ctx.d = d
         return y
 
     @staticmethod
@@ -1087,12 +1125,22 @@ class _LinearPreparedFn(torch.autograd.Function):
             call("iit_conv2d_dgrad_tc", _p(dy), _p(w_io), _p(dx), C.byref(d), _stream())
         grads = [None] * len(ctx.specs)
         if any(ctx.needs_input_grad[6:]):
-            dwb = torch.empty(d.k * d.c, dtype=torch.float32, device=x.device)   # [out_pad][in]
-            need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
-            scratch = torch.empty(need, dtype=torch.uint8, device=x.device)
-            call("iit_conv2d_wgrad_tc", _p(dy), _p(x), _p(dwb), C.byref(d), _p(scratch), need, _stream())
-            grads = [torch.as_strided(dwb, size, stride, offset) for size, stride, offset in ctx.specs]
+            grads = _wgrad_into(dy, x, d, ctx.specs, ctx.w_direct)
         return (dx, None, None, None, None, None, *grads)
+
+
+def _wgrad_into(g, x, d, specs, w_direct):
+    """The [out_pad][in] weight gradient of a token GEMM: added in place into the parameters' gradient buffers
+    (iit_conv2d_wgrad_tc_scatter; autograd gets None) when `w_direct` holds their table, else returned as strided views."""
+    need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
+    scratch = torch.empty(max(need, 16), dtype=torch.uint8, device=x.device)
+    if w_direct is not None:
+        table, n_maps, biggest = w_direct
+        call("iit_conv2d_wgrad_tc_scatter", _p(g), _p(x), C.byref(d), _p(scratch), need, _p(table), n_maps, biggest, _stream())
+        return [None] * len(specs)
+    dwb = torch.empty(d.k * d.c, dtype=torch.float32, device=x.device)   # [out_pad][in]
+    call("iit_conv2d_wgrad_tc", _p(g), _p(x), _p(dwb), C.byref(d), _p(scratch), need, _stream())
+    return [torch.as_strided(dwb, size, stride, offset) for size, stride, offset in specs]
 
 
 def linear_prepared(x2d, w_oi, w_io, n_in, n_out_pad, specs, params):
@@ -1165,7 +1213,8 @@ class _LinearEpiFn(torch.autograd.Function):
             link_out.pre = pre
         ctx.save_for_backward(x, w_io, pre)
         ctx.geom = (T, n_in, n_out_pad)
-        ctx.specs, ctx.bias_specs, ctx.act, ctx.has_res = specs, bias_specs, act, resid is not None
+        ctx.specs, ctx.w_direct = _split_direct(specs)
+        ctx.bias_specs, ctx.act, ctx.has_res = bias_specs, act, resid is not None
         ctx.link_out, ctx.link_in, ctx.n_w = link_out, link_in, n_w
         return y
 
@@ -1216,11 +1265,7 @@ class _LinearEpiFn(torch.autograd.Function):
                 call("iit_conv2d_dgrad_tc", _p(g), _p(w_io), _p(dx), C.byref(d), st)
         grads = [None] * ctx.n_w
         if any(ctx.needs_input_grad[13:13 + ctx.n_w]):
-            dwb = torch.empty(n_out * n_in, dtype=torch.float32, device=x.device)   # [out_pad][in]
-            need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
-            scratch = torch.empty(need, dtype=torch.uint8, device=x.device)
-            call("iit_conv2d_wgrad_tc", _p(g), _p(x), _p(dwb), C.byref(d), _p(scratch), need, st)
-            grads = [torch.as_strided(dwb, size, stride, offset) for size, stride, offset in ctx.specs]
+            grads = _wgrad_into(g, x, d, ctx.specs, ctx.w_direct)
         if ctx.has_res and ctx.res_slot is not None and USE_GRAD_SLOTS:
             ctx.res_slot.put(g)
         bgrads = []

@@ -941,6 +941,68 @@ def test_transformer_with_gelu_in_the_gemm_epilogues_matches_the_default_path():
             assert float((out[True][1][n] - gref).norm() / gref.norm()) < 5e-2, n
 
 
+def test_weight_gradients_added_straight_into_the_optimizer_buffers():
+    """iit_conv2d_wgrad_tc_scatter: with FlatAdam's gradient views in place, the transformer's weight-gradient GEMMs add their
+    split-K sums into those views (per-head / transposed layouts through the map table) and hand autograd None. Two
+    backward passes (so the second ADDS) against the strided-view path: same numbers to fp32 summation order."""
+    from iit_b200.nn import transformer as T
+    from iit_b200.nn.optim import FlatAdam
+    from iit_b200.tasks.ioi import make_ll_model
+    from iit_b200 import _lib
+    x = R.synthetic_ioi(8, 7, d_vocab=101, n_names=20)[0][0].to(DEV)
+    out = {}
+    for flag in (False, True):
+        T.DIRECT_WEIGHT_GRADS = flag
+        try:
+            ll = make_ll_model(device=DEV, d_mlp=128, d_vocab=101, n_ctx=32, dtype=torch.bfloat16)
+            ll.load_state_dict(R.transformer_state_dict(0, d_mlp=128, d_vocab=101, n_ctx=32))
+            opt = FlatAdam(list(ll.parameters()), lr=1e-3)
+            opt.zero_grad()
+            before = _lib.kernel_variant_counts()
+            for rep in range(2):
+                y = ll(x)
+                (y.float().square().mean() * (1 + rep)).backward()
+            torch.cuda.synchronize()
+            out[flag] = {n: p.grad.float().clone() for n, p in ll.named_parameters() if p.grad is not None}
+        finally:
+            T.DIRECT_WEIGHT_GRADS = True
+    top = max(float(v.norm()) for v in out[False].values())
+    assert top > 0
+    checked = 0
+    for n, gref in out[False].items():
+        if float(gref.norm()) > 1e-4 * top:
+            assert float((out[True][n] - gref).norm() / gref.norm()) < 1e-5, n
+            checked += 1
+    assert checked >= 10
+    # the raw entry point, one map that transposes and one per-head map, against iit_conv2d_wgrad_tc
+    from iit_b200 import ops
+    g = torch.Generator().manual_seed(3)
+    Tn, n_in, n_out = 300, 64, 192
+    xx = torch.randn(Tn, n_in, generator=g).to(DEV).bfloat16()
+    dy = torch.randn(Tn, n_out, generator=g).to(DEV).bfloat16()
+    d = _lib.Conv()
+    d.n, d.h, d.w, d.c, d.k, d.r, d.s, d.stride, d.pad, d.p, d.q = Tn, 1, 1, n_in, n_out, 1, 1, 1, 0, 1, 1
+    import ctypes as C
+    need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
+    scratch = torch.empty(need, dtype=torch.uint8, device=DEV)
+    dwb = torch.empty(n_out * n_in, dtype=torch.float32, device=DEV)
+    ops.call("iit_conv2d_wgrad_tc", ops._p(dy), ops._p(xx), ops._p(dwb), C.byref(d), ops._p(scratch), need, ops._stream())
+    H, dh = 3, 32                                     # W[h][in][dh] <- dwb[(h*dh + e)*n_in + i], over the first 96 outputs
+    specs = [((H, n_in, dh), (dh * n_in, 1, n_in), 0), ((n_in, 96), (1, n_in), 96 * n_in)]
+    params = [torch.nn.Parameter(torch.zeros(sz, device=DEV)) for sz, _, _ in specs]
+    for prm in params:
+        prm.grad = torch.full_like(prm, 0.5)
+        prm._iit_direct_grad = prm.grad
+    cache = {}
+    direct = ops.wgrad_direct_maps(specs, params, cache)
+    assert direct is not None and direct[0] == "direct" and ops.wgrad_direct_maps(specs, params, cache)[2] is direct[2]
+    ops.call("iit_conv2d_wgrad_tc_scatter", ops._p(dy), ops._p(xx), C.byref(d), ops._p(scratch), need, ops._p(direct[2]), direct[3],
+             direct[4], ops._stream())
+    for prm, (sz, st, off) in zip(params, specs):
+        want = torch.as_strided(dwb, sz, st, off) + 0.5
+        torch.testing.assert_close(prm.grad, want, rtol=1e-6, atol=1e-6)
+
+
 def test_fused_hl_and_cross_entropy_kernel():
     """iit_hl_ce_fwd: the HL model's intervened output and the loss against it in one launch, for explicit targets, the
     MNIST-PVR HL and the IOI HL (padded bf16 logits included), against the separate kernels / torch; gradients too."""

@@ -267,11 +267,14 @@ def test_ctypes_structs_match_the_header(tmp_path):
                    '  printf("%zu %zu %zu %zu\\n", sizeof(iit_hl_spec_t), offsetof(iit_hl_spec_t, base), offsetof(iit_hl_spec_t, n_names),\n'
                    '         offsetof(iit_hl_spec_t, d_vocab));\n'
                    '  printf("%zu %zu %zu %zu\\n", offsetof(iit_relayout_t, stride), offsetof(iit_relayout_t, k),\n'
-                   '         offsetof(iit_relayout_t, dtype), offsetof(iit_relayout_t, out_pitch));\n  return 0;\n}\n')
+                   '         offsetof(iit_relayout_t, dtype), offsetof(iit_relayout_t, out_pitch));\n'
+                   '  printf("%zu %zu %zu %zu\\n", sizeof(iit_wgrad_map_t), offsetof(iit_wgrad_map_t, size), offsetof(iit_wgrad_map_t, stride),\n'
+                   '         offsetof(iit_wgrad_map_t, offset));\n  return 0;\n}\n')
     exe = tmp_path / "sizes"
     subprocess.check_call(["gcc", "-I", os.path.join(root, "include"), str(src), "-o", str(exe)])
     out = subprocess.check_output([str(exe)], text=True).split()
-    sizes, hl, offs = [int(v) for v in out[:3]], [int(v) for v in out[3:7]], [int(v) for v in out[7:]]
+    sizes, hl, offs, wm = [int(v) for v in out[:3]], [int(v) for v in out[3:7]], [int(v) for v in out[7:11]], [int(v) for v in out[11:]]
+    assert wm == [C.sizeof(_lib.WgradMap), _lib.WgradMap.size.offset, _lib.WgradMap.stride.offset, _lib.WgradMap.offset.offset]
     assert sizes == [C.sizeof(_lib.Box), C.sizeof(_lib.Conv), C.sizeof(_lib.Relayout)]
     assert hl == [C.sizeof(_lib.HlSpec), _lib.HlSpec.base.offset, _lib.HlSpec.n_names.offset, _lib.HlSpec.d_vocab.offset]
     assert offs == [_lib.Relayout.stride.offset, _lib.Relayout.k.offset, _lib.Relayout.dtype.offset, _lib.Relayout.out_pitch.offset]
