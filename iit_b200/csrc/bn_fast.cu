@@ -149,6 +149,7 @@ __device__ __forceinline__ void reduce_finish(float (&acc)[NRED][NP], int cg, in
 }
 
 struct Red2 { double* p[2]; };
+constexpr int RED_THREADS = 1024;     // bn_bwd_reduce_fast_kernel: one block per SM
 
 template <typename T>
 __global__ void __launch_bounds__(256) bn_stats_fast_kernel(const T* __restrict__ x, int64_t rows, int C, int CGB, Red2 o) {
@@ -181,21 +182,43 @@ __global__ void __launch_bounds__(256) bn_stats_fast_kernel(const T* __restrict_
   reduce_finish<2, NP>(acc, cg, rl, CGB, RL, cbase, outs, smem);
 }
 
-template <typename T, int RU>
-__global__ void __launch_bounds__(256) bn_bwd_reduce_fast_kernel(const T* __restrict__ dy, const T* __restrict__ y,
-                                                                 const T* __restrict__ x, int64_t rows, int C, int CGB,
-                                                                 const float* __restrict__ mean, const float* __restrict__ invstd,
-                                                                 int relu, Red2 o, const uint8_t* __restrict__ mask) {
+// dgamma[c] = sum g * xhat,  dbeta[c] = sum g,  g = relu'(y) * dy,  xhat = (x - mean) * invstd.
+// The loop accumulates sum(g * (x - mean)) and sum(g) -- the mean stays in the loop (the uncentred form sum(g x) - mean * sum(g)
+// cancels badly in fp32), invstd is applied once per block and channel before the atomics. The kernel fits 64 registers: four blocks of 256 threads per SM with RU rows (2 x 16 bytes + the mask byte each) in
+// flight per thread, launched as ONE wave (red_geometry). The previous form (xhat in the loop, 121 registers, two blocks
+// per SM, 1.7 waves on the 2 x 2 layers) reached 42 % of HBM bandwidth.
+// MODE: 0 = no ReLU, 1 = ReLU through the bit mask the forward kept, 2 = ReLU through the stored activation y.
+template <typename T, int RU, int MODE>
+__global__ void __launch_bounds__(RED_THREADS, 1) bn_bwd_reduce_fast_kernel(const T* __restrict__ dy, const T* __restrict__ y,
+                                                                    const T* __restrict__ x, int64_t rows, int C, int CGB,
+                                                                    const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                                    Red2 o, const uint8_t* __restrict__ mask) {
   extern __shared__ float smem[];
   constexpr int NP = Pack<T>::N;
-  const int RL = 256 / CGB;
+  const int RL = RED_THREADS / CGB;
   const int cg = threadIdx.x % CGB, rl = threadIdx.x / CGB;
   const int cbase = blockIdx.y * CGB * NP, c = cbase + cg * NP;
   const int CP = C / NP, cpk = c / NP;           // packs per row, this thread's pack within a row (mask index)
-  float mu[NP], is[NP], acc[2][NP];
-  load_consts<NP>(mean, c, mu); load_consts<NP>(invstd, c, is);
+  float acc[2][NP], mu[NP];                      // [0] = sum g * (x - mean), [1] = sum g
+  load_consts<NP>(mean, c, mu);
 #pragma unroll
   for (int j = 0; j < NP; ++j) { acc[0][j] = 0.f; acc[1][j] = 0.f; }
+  auto add = [&](const uint4& rg, const uint4& rx, const uint4& ry, uint32_t mb) {
+    float g[NP], xv[NP];
+    Pack<T>::unpack(rg, g);
+    Pack<T>::unpack(rx, xv);
+    if (MODE == 1) {
+#pragma unroll
+      for (int j = 0; j < NP; ++j) g[j] = (mb >> j) & 1u ? g[j] : 0.f;
+    } else if (MODE == 2) {
+      float yv[NP];
+      Pack<T>::unpack(ry, yv);
+#pragma unroll
+      for (int j = 0; j < NP; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < NP; ++j) { acc[0][j] = fmaf(g[j], xv[j] - mu[j], acc[0][j]); acc[1][j] += g[j]; }
+  };
   const int64_t step = (int64_t)gridDim.x * RL;
   int64_t r = (int64_t)blockIdx.x * RL + rl;
   for (; r + (RU - 1) * step < rows; r += RU * step) {      // RU rows in flight per thread
@@ -205,46 +228,44 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_fast_kernel(const T* __rest
     for (int u = 0; u < RU; ++u) {
       rg[u] = *reinterpret_cast<const uint4*>(dy + (r + u * step) * C + c);
       rx[u] = *reinterpret_cast<const uint4*>(x + (r + u * step) * C + c);
-      if (relu && mask != nullptr) mb[u] = mask[(r + u * step) * CP + cpk];
-      else if (relu) ry[u] = *reinterpret_cast<const uint4*>(y + (r + u * step) * C + c);
+      ry[u] = make_uint4(0, 0, 0, 0); mb[u] = 0;
+      if (MODE == 1) mb[u] = mask[(r + u * step) * CP + cpk];
+      else if (MODE == 2) ry[u] = *reinterpret_cast<const uint4*>(y + (r + u * step) * C + c);
     }
 #pragma unroll
-    for (int u = 0; u < RU; ++u) {
-      float g[NP], xv[NP];
-      Pack<T>::unpack(rg[u], g);
-      Pack<T>::unpack(rx[u], xv);
-      if (relu && mask != nullptr) {
-#pragma unroll
-        for (int j = 0; j < NP; ++j) g[j] = (mb[u] >> j) & 1u ? g[j] : 0.f;
-      } else if (relu) {
-        float yv[NP];
-        Pack<T>::unpack(ry[u], yv);
-#pragma unroll
-        for (int j = 0; j < NP; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
-      }
-#pragma unroll
-      for (int j = 0; j < NP; ++j) { acc[0][j] += g[j] * (xv[j] - mu[j]) * is[j]; acc[1][j] += g[j]; }
-    }
+    for (int u = 0; u < RU; ++u) add(rg[u], rx[u], ry[u], mb[u]);
   }
   for (; r < rows; r += step) {
-    float g[NP], xv[NP];
-    Pack<T>::load(dy + r * C + c, g);
-    Pack<T>::load(x + r * C + c, xv);
-    if (relu && mask != nullptr) {
-      const uint32_t m = mask[r * CP + cpk];
-#pragma unroll
-      for (int j = 0; j < NP; ++j) g[j] = (m >> j) & 1u ? g[j] : 0.f;
-    } else if (relu) {
-      float yv[NP];
-      Pack<T>::load(y + r * C + c, yv);
-#pragma unroll
-      for (int j = 0; j < NP; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
-    }
-#pragma unroll
-    for (int j = 0; j < NP; ++j) { acc[0][j] += g[j] * (xv[j] - mu[j]) * is[j]; acc[1][j] += g[j]; }
+    const uint4 rg = *reinterpret_cast<const uint4*>(dy + r * C + c), rx = *reinterpret_cast<const uint4*>(x + r * C + c);
+    uint4 ry = make_uint4(0, 0, 0, 0);
+    uint32_t mb = 0;
+    if (MODE == 1) mb = mask[r * CP + cpk];
+    else if (MODE == 2) ry = *reinterpret_cast<const uint4*>(y + r * C + c);
+    add(rg, rx, ry, mb);
   }
-  double* outs[2] = {o.p[0], o.p[1]};
-  reduce_finish<2, NP>(acc, cg, rl, CGB, RL, cbase, outs, smem);
+  // block totals through shared memory ([2][RL][W]); `parts` threads per (sum, channel) add RL / parts rows each and meet in
+  // a shuffle; the block's share goes to the fp64 totals with one conversion each (fp64 arithmetic runs at 1/64 rate)
+  const int W = CGB * NP;
+#pragma unroll
+  for (int q = 0; q < 2; ++q)
+#pragma unroll
+    for (int j = 0; j < NP; ++j) smem[(q * RL + rl) * W + cg * NP + j] = acc[q][j];
+  __syncthreads();
+  const int parts = RED_THREADS / (2 * W) > 32 ? 32 : RED_THREADS / (2 * W);     // 1 ... 8 for W = 512 ... 64; a power of two
+  const int outi = threadIdx.x / parts, part = threadIdx.x % parts;     // outi = q * W + ch
+  float v = 0.f;
+  if (outi < 2 * W) {
+    const int q = outi / W, ch = outi - q * W;
+    for (int l = part; l < RL; l += parts) v += smem[(q * RL + l) * W + ch];
+  }
+  for (int o2 = parts >> 1; o2 > 0; o2 >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o2);
+  __syncthreads();
+  if (part == 0 && outi < 2 * W) smem[outi] = v;           // [0..W) = sum g (x - mean), [W..2W) = sum g
+  __syncthreads();
+  for (int ch = threadIdx.x; ch < W; ch += blockDim.x) {
+    atomicAdd(&o.p[0][cbase + ch], (double)(invstd[cbase + ch] * smem[ch]));
+    atomicAdd(&o.p[1][cbase + ch], (double)smem[W + ch]);
+  }
 }
 
 // dx = gamma * invstd * (g - dbeta/rows - xhat * dgamma/rows),  g = relu'(y) * dy;  dres = g
@@ -265,17 +286,19 @@ bn_bwd_apply_fast_kernel(const T* __restrict__ dy, const T* __restrict__ y, cons
   constexpr int U = 2;
   const int64_t tid = (int64_t)blockIdx.x * 256 + threadIdx.x, stride = (int64_t)gridDim.x * 256;
   const int c0 = (int)((tid * NP) % C);
-  float mu[NP], k[NP], dbn[NP], c1[NP];     // o = k * (g - dbn - (x - mu) * c1),  c1 = invstd * dgamma / rows
-  {
-    float is[NP];
-    load_consts<NP>(mean, c0, mu); load_consts<NP>(invstd, c0, is); load_consts<NP>(gamma, c0, k);
-#pragma unroll
-    for (int j = 0; j < NP; ++j) {
-      k[j] *= is[j];
-      dbn[j] = (float)dbeta[c0 + j] * inv_rows;
-      c1[j] = is[j] * ((float)dgamma[c0 + j] * inv_rows);
-    }
+  // o = k * (g - dbn - (x - mu) * c1),  k = gamma * invstd,  dbn = dbeta / rows,  c1 = invstd * dgamma / rows. The fp64 sums
+  // are converted ONCE per block into shared memory: every thread converting its own 16 values (fp64 conversions issue at
+  // 1/64 rate) was a fixed ~9 us per launch, more than the 2 x 2 layers' whole pass.
+  extern __shared__ float s_c[];           // [3][C]
+  for (int ch = threadIdx.x; ch < C; ch += 256) {
+    const float is = invstd[ch];
+    s_c[ch] = gamma[ch] * is;
+    s_c[C + ch] = (float)dbeta[ch] * inv_rows;
+    s_c[2 * C + ch] = is * ((float)dgamma[ch] * inv_rows);
   }
+  __syncthreads();
+  float mu[NP], k[NP], dbn[NP], c1[NP];
+  load_consts<NP>(mean, c0, mu); load_consts<NP>(s_c, c0, k); load_consts<NP>(s_c + C, c0, dbn); load_consts<NP>(s_c + 2 * C, c0, c1);
   auto finish = [&](int64_t i, const uint4& rg, const uint4& rx, const uint4& ry, uint32_t mb) {
     float g[NP], xv[NP], o[NP];
     Pack<T>::unpack(rg, g);
@@ -469,12 +492,15 @@ __global__ void __launch_bounds__(256, 2) bn_relu_pool_bwd_apply_kernel(const T*
   // four constants per channel (two blocks of 2 x 2 pixels in flight leave no registers for six):
   //   activation = x * A + B0 (its sign is the ReLU mask);  dx = A * g + K0 + K1 * x
   float A[NP], B0[NP], K0[NP], K1[NP];
+  extern __shared__ float s_d[];            // [2][C]: dbeta / rows, dgamma / rows, converted from fp64 once per block
+  for (int ch = threadIdx.x; ch < C; ch += 256) { s_d[ch] = (float)dbeta[ch] * inv_rows; s_d[C + ch] = (float)dgamma[ch] * inv_rows; }
+  __syncthreads();
   {
     float mu[NP], is[NP], gm[NP], bt[NP];
     load_consts<NP>(mean, c, mu); load_consts<NP>(invstd, c, is); load_consts<NP>(gamma, c, gm); load_consts<NP>(beta, c, bt);
 #pragma unroll
     for (int j = 0; j < NP; ++j) {
-      const float dbn = (float)dbeta[c + j] * inv_rows, dgn = (float)dgamma[c + j] * inv_rows;
+      const float dbn = s_d[c + j], dgn = s_d[C + c + j];
       A[j] = gm[j] * is[j];
       B0[j] = bt[j] - mu[j] * A[j];
       K1[j] = -A[j] * dgn * is[j];
@@ -585,6 +611,27 @@ static inline void red_geometry(int64_t rows, int C, int np, int* CGB, dim3* gri
   *smem = (size_t)2 * RL * *CGB * np * sizeof(float);
 }
 
+// one wave of 1024-thread blocks (bn_bwd_reduce_fast_kernel): block = CGB channel groups x RL row lanes
+static inline void red_geometry_1024(int64_t rows, int C, int np, int* CGB, dim3* grid, size_t* smem) {
+  const int CG = C / np;
+  *CGB = CG < 64 ? CG : 64;
+  const int RL = RED_THREADS / *CGB;
+  const int chunks = CG / *CGB;
+  int64_t bx = (rows + (int64_t)RL * 4 - 1) / ((int64_t)RL * 4);
+  int64_t cap = kNumSMs / chunks;
+  if (cap < 1) cap = 1;
+  if (bx > cap) bx = cap;
+  if (bx < 1) bx = 1;
+  *grid = dim3((unsigned)bx, (unsigned)chunks);
+  *smem = (size_t)2 * RL * *CGB * np * sizeof(float);      // 64 KB (bf16) / 32 KB (fp32)
+}
+
+template <typename K>
+static int red_opt_in(K kernel, size_t smem) {
+  IIT_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  return 0;
+}
+
 int bn_stats_fast(const void* x, int dtype, int64_t rows, int C, double* sum, double* sq, cudaStream_t st) {
   int CGB; dim3 grid; size_t smem;
   red_geometry(rows, C, pack_n(dtype), &CGB, &grid, &smem);
@@ -615,11 +662,13 @@ int relu_mask_fast(const void* y, int dtype, int64_t rows, int C, uint8_t* mask,
 int bn_bwd_reduce_fast(const void* dy, const void* y, const void* x, int dtype, int64_t rows, int C, const float* mean,
                        const float* invstd, int relu, double* dgamma, double* dbeta, const uint8_t* mask, cudaStream_t st) {
   int CGB; dim3 grid; size_t smem;
-  red_geometry(rows, C, pack_n(dtype), &CGB, &grid, &smem);
+  red_geometry_1024(rows, C, pack_n(dtype), &CGB, &grid, &smem);
   Red2 o{{dgamma, dbeta}};
-  IIT_DISPATCH_DTYPE(dtype, T, {   // four rows in flight per thread (two: +0.1 ms per step)
-    bn_bwd_reduce_fast_kernel<T, 4><<<grid, 256, smem, st>>>((const T*)dy, (const T*)y, (const T*)x, rows, C, CGB, mean, invstd, relu, o,
-                                                             mask);
+  IIT_DISPATCH_DTYPE(dtype, T, {   // four rows in flight per thread (three when the stored activation is read as well)
+    auto k0 = bn_bwd_reduce_fast_kernel<T, 4, 0>; auto k1 = bn_bwd_reduce_fast_kernel<T, 4, 1>; auto k2 = bn_bwd_reduce_fast_kernel<T, 3, 2>;
+    auto k = !relu ? k0 : (mask != nullptr ? k1 : k2);
+    if (red_opt_in(k, smem)) return 3;
+    k<<<grid, RED_THREADS, smem, st>>>((const T*)dy, (const T*)y, (const T*)x, rows, C, CGB, mean, invstd, o, mask);
   })
   IIT_LAUNCH_CHECK("iit_bn_act_bwd_reduce");
   return 0;
@@ -636,7 +685,7 @@ int bn_bwd_apply_fast(const void* dy, const void* y, const void* x, void* dx, vo
     zb.c0 = zero_box_hw[6]; zb.c1 = zero_box_hw[7];
   }
   IIT_DISPATCH_DTYPE(dtype, T, {
-    bn_bwd_apply_fast_kernel<T><<<grid_for(npacks, 256 * 2, 6), 256, 0, st>>>((const T*)dy, (const T*)y, (const T*)x, (T*)dx, (T*)dres,
+    bn_bwd_apply_fast_kernel<T><<<grid_for(npacks, 256 * 2, 6), 256, (size_t)3 * C * sizeof(float), st>>>((const T*)dy, (const T*)y, (const T*)x, (T*)dx, (T*)dres,
                                                                           npacks, C, 1.f / (float)rows, mean, invstd, gamma, dgamma,
                                                                           dbeta, relu, mask, zb);
   })
@@ -691,17 +740,18 @@ extern "C" int iit_bn_relu_maxpool_bwd(const void* dy, const int8_t* idx, const 
   // per-channel sums over the pooled tensors: mask = y > 0, normalised value from the winner's raw value
   {
     int CGB; dim3 grid; size_t smem;
-    red_geometry(prows, c, np, &CGB, &grid, &smem);
+    red_geometry_1024(prows, c, np, &CGB, &grid, &smem);
     Red2 o{{dgamma, dbeta}};
     IIT_DISPATCH_DTYPE(dtype, T, {
-      bn_bwd_reduce_fast_kernel<T, 2><<<grid, 256, smem, st>>>((const T*)dy, (const T*)y, (const T*)xwin, prows, c, CGB, mean, invstd, 1, o,
-                                                            nullptr);
+      if (red_opt_in(bn_bwd_reduce_fast_kernel<T, 3, 2>, smem)) return 3;
+      bn_bwd_reduce_fast_kernel<T, 3, 2><<<grid, RED_THREADS, smem, st>>>((const T*)dy, (const T*)y, (const T*)xwin, prows, c, CGB, mean,
+                                                                       invstd, o, nullptr);
     })
     IIT_LAUNCH_CHECK("iit_bn_relu_maxpool_bwd(reduce)");
   }
   const int64_t total = (int64_t)n * ((h + 1) / 2) * ((w + 1) / 2) * (c / np);
   IIT_DISPATCH_DTYPE(dtype, T, {
-    bn_relu_pool_bwd_apply_kernel<T><<<grid_for(total, 256, 12), 256, 0, st>>>((const T*)dy, idx, (const T*)x, (T*)dx, n, h, w, c, P, Q,
+    bn_relu_pool_bwd_apply_kernel<T><<<grid_for(total, 256, 12), 256, (size_t)2 * c * sizeof(float), st>>>((const T*)dy, idx, (const T*)x, (T*)dx, n, h, w, c, P, Q,
                                                                           1.f / (float)rows, mean, invstd, gamma, beta, dgamma, dbeta);
   })
   IIT_LAUNCH_CHECK("iit_bn_relu_maxpool_bwd(apply)");
