@@ -21,6 +21,7 @@
 namespace iit {
 
 constexpr int WIN_THREADS = 192;
+constexpr int WIN_CONV_THREADS = 320;   // conv_win_kernel: TMA warp, MMA warp, eight epilogue warps
 constexpr int WIN_BN = 64;        // filters per tile (all of them: these layers have 64)
 constexpr int WIN_NACC = 4;       // TMEM accumulators in the ring
 constexpr int WIN_MAX_TAPS = 16;
@@ -48,7 +49,7 @@ __device__ __forceinline__ uint64_t win_desc(uint32_t smem_addr) {
 }
 
 template <int RB, int NTAPS, int STAGES>
-__global__ void __launch_bounds__(WIN_THREADS) conv_win_kernel(const __grid_constant__ CUtensorMap map_a,
+__global__ void __launch_bounds__(WIN_CONV_THREADS) conv_win_kernel(const __grid_constant__ CUtensorMap map_a,
                                                                const __grid_constant__ CUtensorMap map_b,
                                                                __nv_bfloat16* __restrict__ out, WinParams p,
                                                                double* __restrict__ bn_sum, double* __restrict__ bn_sq) {
@@ -73,7 +74,7 @@ __global__ void __launch_bounds__(WIN_THREADS) conv_win_kernel(const __grid_cons
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < WIN_NACC; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+    for (int i = 0; i < WIN_NACC; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 8); }
     mbar_init(b_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -154,12 +155,18 @@ __global__ void __launch_bounds__(WIN_THREADS) conv_win_kernel(const __grid_cons
       }
     }
   } else {
+    // Epilogue, eight warps: warp w reads TMEM lanes [32 (w % 4), +32), so two warps share each lane quarter and each takes
+    // one 32-column half of the 64 filters (four warps doing both halves, with 128 statistics registers per lane: layer1
+    // 80 -> 77.5 us; the stem did not move -- and routing the stores through staging rows as conv_tc.cu does made both slower:
+    // 224 and 80.6 us).
     const int quarter = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int c = half * 32;              // this warp's filters
     const int m = quarter * 32 + lane;
-    const int e = threadIdx.x - 64;
-    float st_s[BN], st_q[BN];
+    const int e = threadIdx.x - 64;       // 0..255
+    float st_s[32], st_q[32];
 #pragma unroll
-    for (int j = 0; j < BN; ++j) { st_s[j] = 0.f; st_q[j] = 0.f; }
+    for (int j = 0; j < 32; ++j) { st_s[j] = 0.f; st_q[j] = 0.f; }
     uint32_t it = 0;
     const int j0 = p.pad_top * p.PW + p.pad_left;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -169,72 +176,56 @@ __global__ void __launch_bounds__(WIN_THREADS) conv_win_kernel(const __grid_cons
         const int hh = jj / p.PW - p.pad_top, ww = jj % p.PW - p.pad_left;
         const int oh = band * p.band_h + hh;
         const bool ok = ww >= 0 && ww < p.OW && hh >= 0 && hh < p.band_h && oh < p.OH;
-        __nv_bfloat16* dst = out + (((int64_t)n * p.OH + oh) * p.OW + ww) * BN;
+        __nv_bfloat16* dst = out + (((int64_t)n * p.OH + oh) * p.OW + ww) * BN + c;
         const uint32_t acc = it % WIN_NACC, acc_phase = (it / WIN_NACC) & 1;
         mbar_wait(&tmem_full[acc], acc_phase);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        uint32_t v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c), v);
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[acc])) : "memory");
+        // bf16 pairs as stored; the BatchNorm statistics are taken from these rounded values. Each lane keeps running sums
+        // for its own accumulator row across all the tiles of this CTA (2 x 32 fp32 registers); the cross-lane reduction
+        // happens once, after the tile loop.
+        uint32_t pk[16];
 #pragma unroll
-        for (int c = 0; c < BN; c += 32) {
-          uint32_t v[32];
-          tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c), v);
-          if (c + 32 >= BN) {
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            __syncwarp();
-            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[acc])) : "memory");
-          }
-          // bf16 pairs as stored; the BatchNorm statistics are taken from these rounded values. Each lane keeps
-          // running sums for its own accumulator row across all the tiles of this CTA (2 x 64 fp32 registers); the
-          // cross-lane reduction happens once, after the tile loop.
-          uint32_t pk[16];
+        for (int j = 0; j < 16; ++j) {
+          __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+          pk[j] = *reinterpret_cast<uint32_t*>(&h);
+        }
+        if (ok) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
-            pk[j] = *reinterpret_cast<uint32_t*>(&h);
-          }
-          if (ok) {
+          for (int j = 0; j < 16; j += 4)
+            st_or_add_bf16x8(dst + 2 * j, make_uint4(pk[j], pk[j + 1], pk[j + 2], pk[j + 3]), p.accumulate != 0);
+          if (bn_sum != nullptr) {
 #pragma unroll
-            for (int j = 0; j < 16; j += 4)
-              st_or_add_bf16x8(dst + c + 2 * j, make_uint4(pk[j], pk[j + 1], pk[j + 2], pk[j + 3]), p.accumulate != 0);
-            if (bn_sum != nullptr) {
-#pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                const float f0 = __uint_as_float(pk[j] << 16), f1 = __uint_as_float(pk[j] & 0xffff0000u);
-                if (c == 0) {
-                  st_s[2 * j] += f0; st_q[2 * j] = fmaf(f0, f0, st_q[2 * j]);
-                  st_s[2 * j + 1] += f1; st_q[2 * j + 1] = fmaf(f1, f1, st_q[2 * j + 1]);
-                } else {
-                  st_s[32 + 2 * j] += f0; st_q[32 + 2 * j] = fmaf(f0, f0, st_q[32 + 2 * j]);
-                  st_s[32 + 2 * j + 1] += f1; st_q[32 + 2 * j + 1] = fmaf(f1, f1, st_q[32 + 2 * j + 1]);
-                }
-              }
+            for (int j = 0; j < 16; ++j) {
+              const float f0 = __uint_as_float(pk[j] << 16), f1 = __uint_as_float(pk[j] & 0xffff0000u);
+              st_s[2 * j] += f0; st_q[2 * j] = fmaf(f0, f0, st_q[2 * j]);
+              st_s[2 * j + 1] += f1; st_q[2 * j + 1] = fmaf(f1, f1, st_q[2 * j + 1]);
             }
           }
         }
       }
     }
     if (bn_sum != nullptr) {
-      // once per CTA: butterfly over the 32 lanes (lane l ends with the warp total of channel c+l), shared-memory
-      // atomics over the four warps, one fp64 atomic per channel
+      // once per CTA: butterfly over the 32 lanes (lane l ends with the warp total of channel c + l), shared-memory
+      // atomics over the four warps of a half, one fp64 atomic per channel
 #pragma unroll
-      for (int c = 0; c < BN; c += 32) {
-        float a[32], b[32];
+      for (int h = 16; h >= 1; h >>= 1) {
+        const bool up = (lane & h) != 0;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) { a[j] = st_s[c + j]; b[j] = st_q[c + j]; }
-#pragma unroll
-        for (int h = 16; h >= 1; h >>= 1) {
-          const bool up = (lane & h) != 0;
-#pragma unroll
-          for (int i = 0; i < h; ++i) {
-            float sa = up ? a[i] : a[i + h], ka = up ? a[i + h] : a[i];
-            float sb = up ? b[i] : b[i + h], kb = up ? b[i + h] : b[i];
-            a[i] = ka + __shfl_xor_sync(0xffffffffu, sa, h);
-            b[i] = kb + __shfl_xor_sync(0xffffffffu, sb, h);
-          }
+        for (int i = 0; i < h; ++i) {
+          float sa = up ? st_s[i] : st_s[i + h], ka = up ? st_s[i + h] : st_s[i];
+          float sb = up ? st_q[i] : st_q[i + h], kb = up ? st_q[i + h] : st_q[i];
+          st_s[i] = ka + __shfl_xor_sync(0xffffffffu, sa, h);
+          st_q[i] = kb + __shfl_xor_sync(0xffffffffu, sb, h);
         }
-        atomicAdd(&s_stat[c + lane], a[0]);
-        atomicAdd(&s_stat[BN + c + lane], b[0]);
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      atomicAdd(&s_stat[c + lane], st_s[0]);
+      atomicAdd(&s_stat[BN + c + lane], st_q[0]);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       if (e < BN) { atomicAdd(&bn_sum[e], (double)s_stat[e]); atomicAdd(&bn_sq[e], (double)s_stat[BN + e]); }
     }
   }
@@ -322,7 +313,7 @@ static int win_launch(const CUtensorMap& ma, const CUtensorMap& mb, void* out, c
       IIT_CUDA(cudaFuncSetAttribute(conv_win_kernel<RB, NTAPS, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WIN_SMEM_MAX)); \
       attr_set[dev][S] = true;                                                                                         \
     }                                                                                                                  \
-    conv_win_kernel<RB, NTAPS, S><<<grid, WIN_THREADS, smem, st>>>(ma, mb, (__nv_bfloat16*)out, p, bn_sum, bn_sq);            \
+    conv_win_kernel<RB, NTAPS, S><<<grid, WIN_CONV_THREADS, smem, st>>>(ma, mb, (__nv_bfloat16*)out, p, bn_sum, bn_sq);            \
     count_variant(RB == 128 ? KV_WIN_3X3 : KV_WIN_STEM);                                                               \
     break;
   switch (stages) {

@@ -53,6 +53,21 @@ def case(n, h, c, k, r, stride, stats, which="fprop"):
 
 if __name__ == "__main__":
     N = 4096
+    if len(sys.argv) > 1 and sys.argv[1] == "win":        # layer1's shifted-window kernel
+        for stats in (True, False):
+            case(N, 14, 64, 64, 3, 1, stats)
+        case(N, 14, 64, 64, 3, 1, False, "dgrad")
+        sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "stem":       # the stem through the model's own module (space-to-depth window kernel)
+        from iit_b200.nn.resnet import Conv2d
+        conv = Conv2d(3, 64, 7, 2, 3).to(dev)
+        img = torch.randn(N, 3, 56, 56, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+        with torch.no_grad():
+            before = _lib.kernel_variant_counts()
+            us = t(lambda: conv(img))
+            after = _lib.kernel_variant_counts()
+        print(f"stem forward (module call, includes its relayout launches): {us:.1f} us", [k_ for k_ in after if after[k_] != before.get(k_, 0)])
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "short":      # the two launches an ncu capture wants
         case(N, 14, 64, 128, 1, 2, True)
         case(N, 14, 64, 128, 1, 2, False)
