@@ -51,6 +51,27 @@ def case(n, h, c, k, r, stride, stats, which="fprop"):
           f"{flops / us / 1e6:7.1f} TF  {kern}", flush=True)
 
 
+def wcase(n, h, c, k, r, stride):
+    pad = 1 if r == 3 else 0
+    p = (h + 2 * pad - r) // stride + 1
+    d = _lib.Conv()
+    d.n, d.h, d.w, d.c, d.k, d.r, d.s, d.stride, d.pad, d.p, d.q = n, h, h, c, k, r, r, stride, pad, p, p
+    x = torch.randn(n, h, h, c, device=dev).bfloat16()
+    dy = torch.randn(n, p, p, k, device=dev).bfloat16()
+    dw = torch.zeros(k * r * r * c, device=dev)
+    need = int(_lib.lib.iit_conv2d_wgrad_tc_scratch_bytes(C.byref(d)))
+    scratch = torch.empty(need, dtype=torch.uint8, device=dev)
+    st = ops._stream()
+    fn = lambda: ops.call("iit_conv2d_wgrad_tc_accumulate", ops._p(dy), ops._p(x), ops._p(dw), C.byref(d), ops._p(scratch), need, st)
+    before = _lib.kernel_variant_counts()
+    us = t(fn)
+    after = _lib.kernel_variant_counts()
+    kern = [k_ for k_ in after if after[k_] != before.get(k_, 0)]
+    flops = 2.0 * n * p * p * k * r * r * c
+    print(f"wgrad  n={n} {h}x{h} {c}->{k} {r}x{r}/{stride}: {us:7.1f} us  in {(x.numel() + dy.numel()) * 2 / us / 1e3:7.0f} GB/s  "
+          f"{flops / us / 1e6:7.1f} TF  scratch {need / 1e6:.1f} MB {kern}", flush=True)
+
+
 if __name__ == "__main__":
     N = 4096
     if len(sys.argv) > 1 and sys.argv[1] == "win":        # layer1's shifted-window kernel
@@ -67,6 +88,11 @@ if __name__ == "__main__":
             us = t(lambda: conv(img))
             after = _lib.kernel_variant_counts()
         print(f"stem forward (module call, includes its relayout launches): {us:.1f} us", [k_ for k_ in after if after[k_] != before.get(k_, 0)])
+        sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "wgrad":
+        for (h, c, k, r, stride) in [(7, 128, 128, 3, 1), (4, 256, 256, 3, 1), (2, 512, 512, 3, 1), (14, 64, 64, 3, 1), (14, 64, 128, 3, 2),
+                                     (7, 128, 256, 3, 2), (4, 256, 512, 3, 2), (14, 64, 128, 1, 2), (7, 128, 256, 1, 2), (4, 256, 512, 1, 2)]:
+            wcase(N, h, c, k, r, stride)
         sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "short":      # the two launches an ncu capture wants
         case(N, 14, 64, 128, 1, 2, True)
