@@ -78,9 +78,11 @@ __device__ __forceinline__ float tc_gelu_grad(float x) {
 // MT pixel boxes share one filter block per tile (MT = 2: 256 pixels x 128 filters). The kernel is bound by L2 -> shared
 // memory traffic (ncu: ~11 TB/s through the crossbar at 36-42 % tensor-pipe activity with 128 x 128 tiles); a filter block
 // that serves two pixel boxes cuts the bytes per FLOP by a quarter.
-template <int BN, int STAGES, int MT>
+template <int BN, int STAGES, int MT, int OBUF>
 __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __grid_constant__ CUtensorMap map_a,
                                                                 const __grid_constant__ CUtensorMap map_b,
+                                                                const __grid_constant__ CUtensorMap map_o,
+                                                                const __grid_constant__ CUtensorMap map_o2,
                                                                 __nv_bfloat16* __restrict__ out, TcParams p,
                                                                 double* __restrict__ bn_sum, double* __restrict__ bn_sq) {
   extern __shared__ uint8_t smem_raw[];
@@ -89,14 +91,13 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
   constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2, B_BYTES = BN * TC_BK * 2;
   uint8_t* sA = smem;                         // [STAGES][MT] pixel boxes
   uint8_t* sB = smem + STAGES * MT * A_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * B_BYTES);
+  uint8_t* s_out = sB + STAGES * B_BYTES;     // [OBUF][128 rows][128 bytes], SWIZZLE_128B: output tiles of the rounds (tc_round_store)
+  uint64_t* full = reinterpret_cast<uint64_t*>(s_out + OBUF * TC_OUT_TILE_BYTES);
   uint64_t* empty = full + STAGES;
   uint64_t* tmem_full = empty + STAGES;      // [2]
   uint64_t* tmem_empty = tmem_full + 2;      // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
   float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [4 lane quarters][2][BN]: tc_flush_stats
-  // [8 warps][32 rows][TC_STAGE_PITCH], 16-byte aligned: output transposition
-  uint8_t* s_stage = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(s_stat + 8 * BN) + 15) & ~uintptr_t(15));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kchunks = p.Cin / TC_BK;
@@ -128,6 +129,7 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
       if (issuer) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_o)) : "memory");
       }
       int stage = 0;
       uint32_t phase = 0;
@@ -202,8 +204,9 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
     }
   } else {
     // epilogue, eight warps: warp w may read TMEM lanes [32*(w%4), 32*(w%4)+32), so two warps share each lane quarter and
-    // take alternate 32-column chunks. With small reductions (1x1 and 64-channel layers) the tile time IS the epilogue time:
-    // one warp per scheduler ran a dependent chain of ~350 instructions per chunk with nothing to overlap it with.
+    // take the two 32-column halves of every 64-channel round; the round's [128 x 64] tile goes out through one TMA store
+    // (tc_round_store). With small reductions (1x1 and 64-channel layers, the d_model-64 GEMMs) the tile time IS the
+    // epilogue time.
     const int quarter = warp & 3;
     const int half = (warp - 2) >> 2;   // which of the two warps of this lane quarter
     const int m = quarter * 32 + lane;  // accumulator row == pixel of the box
@@ -211,30 +214,18 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
     const int hl = (m / p.BW) % p.BH;
     const int nl = m / (p.BW * p.BH);
     const int e = threadIdx.x - 64;     // 0..255: index among the epilogue threads
-    // BatchNorm statistics: running sums in registers (tc_store_packed), flushed when the filter block changes
+    const bool leader = e == 0;         // issues the TMA stores
+    // BatchNorm statistics: running sums in registers (tc_round_store), flushed when the filter block changes
     float rstat[BN / 64][4];
 #pragma unroll
     for (int cc = 0; cc < BN / 64; ++cc) { rstat[cc][0] = 0.f; rstat[cc][1] = 0.f; rstat[cc][2] = 0.f; rstat[cc][3] = 0.f; }
     int stat_tiles = 0;                 // tiles summed since the last flush (fp32 running sums are kept short)
-    // Stores: a lane holds one pixel x 32 channels (64 bytes). Written as such, a warp store touches 32 lines with 16 bytes
-    // each (half a sector): 10-15 % of the kernel. Each warp instead passes the chunk through its own staging rows and
-    // stores 64 contiguous bytes per pixel: four lanes per pixel, pixels (lane/4) + 8i of the warp's 32.
-    uint8_t* my_stage = s_stage + (warp - 2) * (32 * TC_STAGE_PITCH);
-    const int sub = lane >> 2, piece = lane & 3;
-    int swl[4], shl[4], snl[4];
-    int64_t soff[4];                    // offset of pixel (snl, shl, swl) from the box's first output pixel, plus this lane's piece
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int mm = quarter * 32 + sub + 8 * i;
-      swl[i] = mm % p.BW; shl[i] = (mm / p.BW) % p.BH; snl[i] = mm / (p.BW * p.BH);
-      soff[i] = (((int64_t)snl[i] * p.OH + shl[i] * p.out_mul) * p.OW + swl[i] * p.out_mul) * p.Cout + piece * 8;
-    }
     const bool one_box = p.tiles_w == 1 && p.tiles_h == 1;     // the box covers whole images: no division per tile
     int run_co = -1;
-    uint32_t it = 0;
+    uint32_t it = 0, round = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
       const int rt = ksplit > 1 ? tile % real_tiles : tile;
-      const int co0 = (rt % nblk) * BN;
+      const int co0 = (nblk > 1 ? rt % nblk : 0) * BN;
       if (bn_sum != nullptr && run_co >= 0 && (run_co != co0 || stat_tiles >= 16)) {
         tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, run_co, bn_sum, bn_sq);
         stat_tiles = 0;
@@ -242,10 +233,8 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
       run_co = co0;
       ++stat_tiles;
       const uint32_t acc = it & 1, acc_phase = (it >> 1) & 1;
-      if (nk > 0) {
-        mbar_wait(&tmem_full[acc], acc_phase);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      }
+      mbar_wait(&tmem_full[acc], acc_phase);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll 1
      for (int mt = 0; mt < MT; ++mt) {
       int t = (nblk > 1 ? rt / nblk : rt) * MT + mt;
@@ -255,23 +244,12 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
       const int n_box = t * p.BNI, p_box = th * p.BH, q_box = tw * p.BW;
       const int n = n_box + nl, pp = p_box + hl, qq = q_box + wl;
       const bool ok = box_ok && n < p.N && pp < p.P && qq < p.Q;
-      __nv_bfloat16* const box_out =
-          out + (((int64_t)n_box * p.OH + (p_box * p.out_mul + p.out_oh)) * p.OW + (q_box * p.out_mul + p.out_ow)) * p.Cout + co0;
-      __nv_bfloat16* sdst[4];      // the four pixels this lane stores a 16-byte piece of (nullptr: outside the tensor)
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-        sdst[i] = (box_ok && n_box + snl[i] < p.N && p_box + shl[i] < p.P && q_box + swl[i] < p.Q) ? box_out + soff[i] : nullptr;
 #pragma unroll
       for (int cc = 0; cc < BN / 64; ++cc) {
         const int c = cc * 64 + half * 32;
         uint32_t v[32];
-        if (nk > 0) {
-          tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * (MT * BN) + mt * BN + c), v);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = 0u;
-        }
-        if (cc == BN / 64 - 1 && mt == MT - 1 && nk > 0) {
+        tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * (MT * BN) + mt * BN + c), v);
+        if (cc == BN / 64 - 1 && mt == MT - 1) {
           // all of this warp's TMEM reads of the accumulator are complete: hand it back to the MMA warp
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
           __syncwarp();
@@ -313,21 +291,22 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
             }
           }
           if (p.epi == TC_EPI_GELU) {
-            if (p.out2 != nullptr) {     // the pre-activation, kept for the backward
-              __nv_bfloat16* sdst2[4];
-#pragma unroll
-              for (int i = 0; i < 4; ++i) sdst2[i] = sdst[i] != nullptr ? p.out2 + (sdst[i] - out) : nullptr;
-              tc_store_chunk(v, my_stage, lane, sub, piece, sdst2, c, ok);
+            if (p.out2 != nullptr) {     // the pre-activation, kept for the backward: a round of its own through the same tile
+              float none[4] = {0.f, 0.f, 0.f, 0.f};
+              tc_round_store<OBUF>(v, ok, s_out + (round++ % OBUF) * TC_OUT_TILE_BYTES, quarter, half, lane, leader, box_ok, &map_o2,
+                                   co0 + cc * 64, q_box, p_box, n_box, false, none, false);
             }
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(tc_gelu(__uint_as_float(v[j])));
           }
         }
-        // store (64 contiguous bytes per pixel) and, for the BatchNorm that follows, per-channel sums of the values as stored
-        tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c, ok, rstat[cc], bn_sum != nullptr, p.accumulate != 0);
+        // the round's tile: staged, stored by TMA, and -- for the BatchNorm that follows -- its per-channel sums as stored
+        tc_round_store<OBUF>(v, ok, s_out + (round++ % OBUF) * TC_OUT_TILE_BYTES, quarter, half, lane, leader, box_ok, &map_o,
+                             co0 + cc * 64, q_box, p_box, n_box, p.accumulate != 0, rstat[cc], bn_sum != nullptr);
       }
      }  // mt
     }
+    if (leader) tma_store_wait_all();    // every store of this CTA has been written before it may exit
     if (bn_sum != nullptr && run_co >= 0) tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, run_co, bn_sum, bn_sq);
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -352,20 +331,21 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
 template <int BN, int STAGES>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC_CONV_THREADS, 1)
 conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                   __nv_bfloat16* __restrict__ out, TcParams p, double* __restrict__ bn_sum, double* __restrict__ bn_sq) {
+                   const __grid_constant__ CUtensorMap map_o, __nv_bfloat16* __restrict__ out, TcParams p,
+                   double* __restrict__ bn_sum, double* __restrict__ bn_sq) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   constexpr int BHALF = BN / 2;
   constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2, B_BYTES = BHALF * TC_BK * 2;
   uint8_t* sA = smem;
   uint8_t* sB = smem + STAGES * A_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(sB + STAGES * B_BYTES);
+  uint8_t* s_out = sB + STAGES * B_BYTES;     // this CTA's [128 rows][128 bytes] output tile of one round (tc_round_store)
+  uint64_t* full = reinterpret_cast<uint64_t*>(s_out + TC_OUT_TILE_BYTES);
   uint64_t* empty = full + STAGES;
   uint64_t* tmem_full = empty + STAGES;      // [2]
   uint64_t* tmem_empty = tmem_full + 2;      // [2] (the leader's are used)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
   float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [4 lane quarters][2][BN]: tc_flush_stats
-  uint8_t* s_stage = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(s_stat + 8 * BN) + 15) & ~uintptr_t(15));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -456,7 +436,8 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       }
     }
   } else {
-    // eight epilogue warps, two per TMEM lane quarter on alternate 32-column chunks; staged 64-byte stores (tc_store_chunk)
+    // eight epilogue warps per CTA, two per TMEM lane quarter on the two halves of each 64-channel round; each CTA stores
+    // ITS 128 pixels of the pair's tile by TMA (tc_round_store)
     const int quarter = warp & 3;
     const int half = (warp - 2) >> 2;
     const int m = quarter * 32 + lane;
@@ -464,20 +445,11 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
     const int hl = (m / p.BW) % p.BH;
     const int nl = m / (p.BW * p.BH);
     const int e = threadIdx.x - 64;                        // 0..255
-    float rstat[BN / 64][4];                               // running BatchNorm statistics (tc_store_packed / tc_flush_stats)
+    const bool leader = e == 0;
+    float rstat[BN / 64][4];                               // running BatchNorm statistics (tc_round_store / tc_flush_stats)
 #pragma unroll
     for (int cc = 0; cc < BN / 64; ++cc) { rstat[cc][0] = 0.f; rstat[cc][1] = 0.f; rstat[cc][2] = 0.f; rstat[cc][3] = 0.f; }
     int stat_tiles = 0;
-    uint8_t* my_stage = s_stage + (warp - 2) * (32 * TC_STAGE_PITCH);
-    const int sub = lane >> 2, piece = lane & 3;
-    int swl[4], shl[4], snl[4];
-    int64_t soff[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int mm = quarter * 32 + sub + 8 * i;
-      swl[i] = mm % p.BW; shl[i] = (mm / p.BW) % p.BH; snl[i] = mm / (p.BW * p.BH);
-      soff[i] = (((int64_t)snl[i] * p.OH + shl[i] * p.out_mul) * p.OW + swl[i] * p.out_mul) * p.Cout + piece * 8;
-    }
     const bool one_box = p.tiles_w == 1 && p.tiles_h == 1;
     int run_co = -1;
     uint32_t it = 0;
@@ -498,14 +470,7 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       int tw = 0, th = 0;
       if (!one_box) { tw = t % p.tiles_w; t /= p.tiles_w; th = t % p.tiles_h; t /= p.tiles_h; }
       const int n_box = t * p.BNI, p_box = th * p.BH, q_box = tw * p.BW;
-      const int n = n_box + nl, pp = p_box + hl, qq = q_box + wl;
-      const bool ok = box_ok && n < p.N && pp < p.P && qq < p.Q;
-      __nv_bfloat16* const box_out =
-          out + (((int64_t)n_box * p.OH + (p_box * p.out_mul + p.out_oh)) * p.OW + (q_box * p.out_mul + p.out_ow)) * p.Cout + co0;
-      __nv_bfloat16* sdst[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-        sdst[i] = (box_ok && n_box + snl[i] < p.N && p_box + shl[i] < p.P && q_box + swl[i] < p.Q) ? box_out + soff[i] : nullptr;
+      const bool ok = box_ok && n_box + nl < p.N && p_box + hl < p.P && q_box + wl < p.Q;
 #pragma unroll
       for (int cc = 0; cc < BN / 64; ++cc) {
         const int c = cc * 64 + half * 32;
@@ -516,9 +481,11 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
           __syncwarp();
           if (lane == 0) mbar_arrive_cluster(lead_empty);
         }
-        tc_store_chunk(v, my_stage, lane, sub, piece, sdst, c, ok, rstat[cc], bn_sum != nullptr, p.accumulate != 0);
+        tc_round_store<1>(v, ok, s_out, quarter, half, lane, leader, box_ok, &map_o, co0 + cc * 64, q_box, p_box, n_box,
+                          p.accumulate != 0, rstat[cc], bn_sum != nullptr);
       }
     }
+    if (leader) tma_store_wait_all();
     if (bn_sum != nullptr && run_co >= 0) tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, run_co, bn_sum, bn_sq);
   }
   // neither CTA may leave (or free the pair's TMEM) while its peer can still signal its barriers or read its operands
@@ -538,23 +505,30 @@ static bool g_bn256 = true;
 static int pow2_ge(int v) { int r = 1; while (r < v) r <<= 1; return r; }
 
 template <int BN, int MT>
-static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16* out, const TcParams& p, int total_tiles,
-                     cudaStream_t st, double* bn_sum, double* bn_sq) {
-  constexpr int STAGES = 4;
-  constexpr size_t smem = STAGES * (MT * TC_BM * TC_BK * 2 + BN * TC_BK * 2) + (2 * STAGES + 4) * 8 + 16 + 8 * BN * 4 +
-                          16 + 8 * 32 * TC_STAGE_PITCH + 1024;
+static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, const CUtensorMap& mo2, __nv_bfloat16* out,
+                     const TcParams& p, int total_tiles, cudaStream_t st, double* bn_sum, double* bn_sq) {
+  // Two output tiles (the TMA unit reads one while the warps fill the other) wherever shared memory has room for them next
+  // to the operand ring: 256-filter tiles keep them by running a three-stage ring (their MMAs take 128 cycles per k-block
+  // step, so three stages in flight cover the load latency as four do for the narrower tiles); 2 x 128 pixels x 128 filters
+  // (four stages of 48 KB) has room for one.
+  constexpr int STAGES = BN == 256 ? 3 : 4;
+  constexpr int OBUF = (BN == 128 && MT == 2) ? 1 : 2;     // (three stages and two tiles there: 60.6 -> 62.9 us on layer2)
+  constexpr size_t smem = STAGES * (MT * TC_BM * TC_BK * 2 + BN * TC_BK * 2) + OBUF * TC_OUT_TILE_BYTES + (2 * STAGES + 4) * 8 + 16 +
+                          8 * BN * 4 + 1024;
+  static_assert(smem <= 227 * 1024, "tile does not fit shared memory");
+  auto kernel = conv3x3_tc_kernel<BN, STAGES, MT, OBUF>;
   static int ctas_per_sm_dev[kMaxDevices] = {};
   int& ctas_per_sm = ctas_per_sm_dev[current_device_slot()];
   if (!ctas_per_sm) {
-    IIT_CUDA(cudaFuncSetAttribute(conv3x3_tc_kernel<BN, STAGES, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    IIT_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int occ = 0;
-    IIT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv3x3_tc_kernel<BN, STAGES, MT>, TC_CONV_THREADS, smem));
+    IIT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, TC_CONV_THREADS, smem));
     const int tmem_limit = 512 / (2 * MT * BN);   // every resident CTA holds 2*MT*BN TMEM columns for its whole life
     ctas_per_sm = occ < 1 ? 1 : (occ > tmem_limit ? tmem_limit : occ);
   }
   int grid = kNumSMs * ctas_per_sm;
   if (grid > total_tiles) grid = total_tiles;
-  conv3x3_tc_kernel<BN, STAGES, MT><<<grid, TC_CONV_THREADS, smem, st>>>(ma, mb, out, p, bn_sum, bn_sq);
+  kernel<<<grid, TC_CONV_THREADS, smem, st>>>(ma, mb, mo, mo2, out, p, bn_sum, bn_sq);
   count_variant(BN == 64 ? KV_TC_64 : BN == 256 ? KV_TC_256 : MT == 2 ? KV_TC_128_MT2 : KV_TC_128);
   return 0;
 }
@@ -562,11 +536,11 @@ static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16
 // CTA-pair launch (256 pixels x BN filters per cluster of two)
 static int g_pair_mode = 1;   // 0 off; 1 / 2 on for Cout % 256 == 0 with 256-filter tiles; 3 the same with 128-filter tiles
 template <int BN>
-static int launch_tc2(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat16* out, const TcParams& p, int total_tiles,
-                      cudaStream_t st, double* bn_sum, double* bn_sq) {
+static int launch_tc2(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, __nv_bfloat16* out, const TcParams& p,
+                      int total_tiles, cudaStream_t st, double* bn_sum, double* bn_sq) {
   constexpr int STAGES = BN == 256 ? 6 : 8;
-  constexpr size_t smem = STAGES * (TC_BM * TC_BK * 2 + (BN / 2) * TC_BK * 2) + (2 * STAGES + 4) * 8 + 16 + 8 * BN * 4 + 16 +
-                          8 * 32 * TC_STAGE_PITCH + 1024;
+  constexpr size_t smem = STAGES * (TC_BM * TC_BK * 2 + (BN / 2) * TC_BK * 2) + TC_OUT_TILE_BYTES + (2 * STAGES + 4) * 8 + 16 +
+                          8 * BN * 4 + 1024;
   static int max_clusters_dev[kMaxDevices] = {};
   int& max_clusters = max_clusters_dev[current_device_slot()];
   cudaLaunchConfig_t cfg = {};
@@ -587,7 +561,7 @@ static int launch_tc2(const CUtensorMap& ma, const CUtensorMap& mb, __nv_bfloat1
   }
   const int clusters = total_tiles < max_clusters ? total_tiles : max_clusters;
   cfg.gridDim = dim3(2 * clusters);
-  IIT_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_tc2_kernel<BN, STAGES>, ma, mb, out, p, bn_sum, bn_sq));
+  IIT_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_tc2_kernel<BN, STAGES>, ma, mb, mo, out, p, bn_sum, bn_sq));
   count_variant(BN == 256 ? KV_TC2_256 : KV_TC2_128);
   return 0;
 }
@@ -624,6 +598,24 @@ static int encode_nhwc_strided(CUtensorMap* m, const void* ptr, int C, int W, in
   return 0;
 }
 
+// The produced tensor as the epilogue's TMA stores see it: the pixel grid (p, q) of this launch -- the whole [N, OH, OW, Cout]
+// tensor, or one parity class of it for a strided dgrad (base shifted to the class's first pixel, pixel strides multiplied)
+// -- in boxes of 64 channels x BW x BH x BNI pixels, SWIZZLE_128B (tc_round_store).
+static int encode_out(CUtensorMap* m, void* out, const TcParams& tp, const char* name) {
+  EncodeTiledFn enc = get_encode();
+  IIT_REQUIRE(enc != nullptr, "%s: cuTensorMapEncodeTiled is unavailable in this driver", name);
+  uint8_t* base = reinterpret_cast<uint8_t*>(out) + ((size_t)tp.out_oh * tp.OW + tp.out_ow) * tp.Cout * 2;
+  cuuint64_t dims[4] = {(cuuint64_t)tp.Cout, (cuuint64_t)tp.Q, (cuuint64_t)tp.P, (cuuint64_t)tp.N};
+  cuuint64_t strides[3] = {(cuuint64_t)tp.out_mul * tp.Cout * 2, (cuuint64_t)tp.out_mul * tp.OW * tp.Cout * 2,
+                           (cuuint64_t)tp.OH * tp.OW * tp.Cout * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)tp.BW, (cuuint32_t)tp.BH, (cuuint32_t)tp.BNI};
+  cuuint32_t es[4] = {1, 1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  IIT_REQUIRE(r == CUDA_SUCCESS, "%s: output tensor map rejected (CUresult %d)", name, (int)r);
+  return 0;
+}
+
 static int encode_filter(CUtensorMap* m, const void* wmat, int Kg, int rows, int BN, const char* name) {
   EncodeTiledFn enc = get_encode();
   IIT_REQUIRE(enc != nullptr, "%s: cuTensorMapEncodeTiled is unavailable in this driver", name);
@@ -648,8 +640,12 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
   // 256 filters per tile where the layer has them: with N = 256 an MMA reads 12 KB of shared memory per 128 tensor cycles
   // (96 B/clk); with N = 128 it is 8 KB per 64 cycles, exactly the 128 B/clk shared memory delivers
   const int BN = (tp.Cout % 256 == 0 && g_bn256) ? 256 : (tp.Cout % 128 == 0) ? 128 : 64;
-  CUtensorMap ma, mb;
+  IIT_REQUIRE(tp.ntaps > 0 && tp.Cin >= TC_BK, "%s: empty reduction", name);
+  CUtensorMap ma, mb, mo, mo2;
   if (encode_nhwc_strided(&ma, gathered, gC, gW, gH, tp.N, tp.BW, tp.BH, tp.BNI, tp.in_mul, name)) return 1;
+  if (encode_out(&mo, out, tp, name)) return 1;
+  mo2 = mo;
+  if (tp.out2 != nullptr && encode_out(&mo2, tp.out2, tp, name)) return 1;
   const int64_t mtiles = (int64_t)tp.tiles_w * tp.tiles_h * tp.tiles_n;
   // CTA pairs: whenever every SM gets a tile; with fewer boxes (layer4 at batch 4096: 128) only for long reductions, where
   // the halved filter traffic outweighs the pair's start-up (measured: +3 % on 4608-deep, -8 % on 256-deep reductions)
@@ -663,8 +659,8 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
     if (encode_filter(&mb, wmat, Kg, tp.Cout, BN2 / 2, name)) return 1;
     const int64_t total2 = BN2 == 256 ? t256 : t128;
     IIT_REQUIRE(total2 < (1ll << 31), "%s: too many tiles", name);
-    if (BN2 == 256 ? launch_tc2<256>(ma, mb, (__nv_bfloat16*)out, tp, (int)total2, st, bn_sum, bn_sq)
-                   : launch_tc2<128>(ma, mb, (__nv_bfloat16*)out, tp, (int)total2, st, bn_sum, bn_sq)) return 1;
+    if (BN2 == 256 ? launch_tc2<256>(ma, mb, mo, (__nv_bfloat16*)out, tp, (int)total2, st, bn_sum, bn_sq)
+                   : launch_tc2<128>(ma, mb, mo, (__nv_bfloat16*)out, tp, (int)total2, st, bn_sum, bn_sq)) return 1;
     IIT_LAUNCH_CHECK(name);
     return 0;
   }
@@ -689,10 +685,10 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
   const int MT = (BN == 128 && g_tile_pairs && ((mtiles + 1) / 2) * (tp.Cout / BN) >= kNumSMs && tp.ntaps * tp.Cin >= 1024) ? 2 : 1;
   const int64_t total = ((mtiles + MT - 1) / MT) * (tp.Cout / BN) * (tp.ksplit > 1 ? tp.ksplit : 1);
   IIT_REQUIRE(total < (1ll << 31), "%s: too many tiles", name);
-  int rc = BN == 256 ? launch_tc<256, 1>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq)
-         : BN == 128 ? (MT == 2 ? launch_tc<128, 2>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq)
-                                : launch_tc<128, 1>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq))
-                     : launch_tc<64, 1>(ma, mb, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq);
+  int rc = BN == 256 ? launch_tc<256, 1>(ma, mb, mo, mo2, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq)
+         : BN == 128 ? (MT == 2 ? launch_tc<128, 2>(ma, mb, mo, mo2, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq)
+                                : launch_tc<128, 1>(ma, mb, mo, mo2, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq))
+                     : launch_tc<64, 1>(ma, mb, mo, mo2, (__nv_bfloat16*)out, tp, (int)total, st, bn_sum, bn_sq);
   if (rc) return rc;
   IIT_LAUNCH_CHECK(name);
   return 0;

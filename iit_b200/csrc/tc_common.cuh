@@ -156,21 +156,6 @@ __device__ __forceinline__ void umma2_commit_both(uint64_t* bar) {
 }
 
 // ---- epilogue stores -------------------------------------------------------------------------------
-// A lane of an epilogue warp holds one pixel x 32 channels (64 bytes of bf16). Stored as such, one warp store instruction
-// touches 32 lines with 16 bytes each - half a sector - and costs the tiled convolutions 10-15 % of their time. Each warp
-// passes the chunk through its own 32 staging rows instead and stores 64 contiguous bytes per pixel: four lanes per pixel
-// (`piece` = lane & 3), pixels `sub` + 8i (`sub` = lane >> 2) of the warp's 32.
-constexpr int TC_STAGE_PITCH = 80;   // bytes per staged pixel row: 64 of data, padded so that 16-byte accesses spread over the banks
-
-// pk = this lane's 32 channels as 16 packed bf16 pairs; sdst[i] points at piece `piece` of pixel sub + 8i, channel 0 of the
-// filter block (nullptr: pixel outside the tensor); c = first channel of the chunk.
-// `rs` (four registers of the calling lane, used when `stats`): running per-channel sum and sum of squares of the staged values,
-// for the BatchNorm that follows. The staged rows make this a column sum: lane (row parity `lane >> 4`, channel pair
-// `lane & 15`) reads 16 words and keeps {sum, sum, squares, squares} of its two channels over its 16 rows IN REGISTERS, across
-// chunks of the same columns and across tiles; tc_flush_stats combines parities, warps and CTAs when the filter block
-// changes. (Per chunk this used to end in 4 shuffles and 4 shared-memory atomics per lane -- compare-and-swap loops that
-// four warps fought over -- and two CTA barriers per tile: 40 % of a short-reduction layer's time.) Rows outside the
-// tensor must be staged as zeros when statistics are taken.
 // 8 bf16 values: dst[0..7] = v (plain 16-byte store) or dst[0..7] += v (ONE 16-byte reduction instruction,
 // red.global.add.noftz.v4.bf16x2 = REDG.E.ADD.BF16x8: the addition happens in L2, the SM neither loads the old values nor
 // waits for them). Every element receives exactly one addend per launch, so the result does not depend on any order.
@@ -183,50 +168,90 @@ __device__ __forceinline__ void st_or_add_bf16x8(__nv_bfloat16* dst, const uint4
   }
 }
 
-__device__ __forceinline__ void tc_store_packed(const uint32_t (&pk)[16], uint8_t* stage, int lane, int sub, int piece,
-                                                __nv_bfloat16* const (&sdst)[4], int c, float (&rs)[4], bool stats,
-                                                bool accumulate = false) {
+
+// The tiled kernels' output path: TMA stores from a staged tile.
+// A lane of an epilogue warp holds one pixel (accumulator row m) x 32 channels. The eight warps of a CTA -- two per TMEM lane
+// quarter, `half` = which 32 of a 64-channel round -- write their rows into ONE [128 rows][128 bytes] tile in the
+// SWIZZLE_128B layout (16-byte unit u of row m lives at unit u ^ (m & 7): conflict-free for a quarter-warp), and one thread
+// hands the tile to the TMA unit: cp.async.bulk.tensor.4d (UTMASTG) with the same (channels, BW, BH, BNI) box the loads
+// use, so rows outside the tensor are clipped by the hardware, or cp.reduce.async.bulk.tensor...add (UTMAREDG.ADD) when
+// the result is to be ADDED to the tensor (bf16 addition in L2, one addend per element and launch: order-independent).
+// This replaced per-lane stores through warp-private staging rows (64 contiguous bytes per pixel from four lanes): that
+// epilogue spent ~270 instructions per 32-column chunk on addresses, bounds and the transposition, ran at 1.3 IPC on a
+// dependent chain and WAS the tile time of every layer with a short reduction (ncu: profiles/r02_ncu_single_kernels.md).
+// Per round now: 16 conversions, 4 shared stores, a proxy fence and two named barriers per thread.
+constexpr uint32_t TC_OUT_TILE_BYTES = 128 * 128;
+
+__device__ __forceinline__ void tma_store_4d(const void* src, const CUtensorMap* map, int c0, int c1, int c2, int c3, bool add) {
+  if (add)
+    asm volatile("cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.tile.bulk_group [%0, {%1, %2, %3, %4}], [%5];"
+                 ::"l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(smem_u32(src)) : "memory");
+  else
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%1, %2, %3, %4}], [%5];"
+                 ::"l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(smem_u32(src)) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+// PENDING = 0: every store issued by this thread has read its shared-memory tile; 1: all but the most recent one
+template <int PENDING>
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(PENDING) : "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+// One 64-channel round of the CTA's eight epilogue warps (all 256 threads call it, in the same order).
+//   v          this lane's row m = quarter * 32 + lane, fp32 columns [half * 32, +32) of the round
+//   keep       the row lies inside the tensor (rows outside are staged as zeros: the statistics read them; TMA clips them)
+//   leader     exactly one of the 256 threads; it issues the store of the round when `do_store`
+//   (c0..c3)   tensor coordinates of the tile's box: first channel of the round, q, p, image
+//   rs, stats  running BatchNorm statistics of the staged (bf16-rounded) values: lane (par = lane >> 4, cp = lane & 15)
+//              owns channels half * 32 + 2cp, +1 and 16 of the warp's rows, chosen so that the two parities read different
+//              64-byte halves of the swizzled rows (no bank conflicts); sums stay in registers across rounds of the same
+//              columns and across tiles (tc_flush_stats)
+// OBUF = number of output tiles the caller alternates between (s_out is the one of THIS round): with two, the leader waits
+// only for the store before the one it just issued, so the TMA unit reads one tile while the warps fill the other; with one,
+// every round ends with the store's read latency on the critical path of all eight warps.
+template <int OBUF>
+__device__ __forceinline__ void tc_round_store(const uint32_t (&v)[32], bool keep, uint8_t* s_out, int quarter, int half, int lane,
+                                               bool leader, bool do_store, const CUtensorMap* map, int c0, int c1, int c2, int c3,
+                                               bool accumulate, float (&rs)[4], bool stats) {
+  uint32_t pk[16];
 #pragma unroll
-  for (int j = 0; j < 16; j += 4)
-    *reinterpret_cast<uint4*>(stage + lane * TC_STAGE_PITCH + j * 4) = make_uint4(pk[j], pk[j + 1], pk[j + 2], pk[j + 3]);
-  __syncwarp();
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const uint4 o = *reinterpret_cast<const uint4*>(stage + (sub + 8 * i) * TC_STAGE_PITCH + piece * 16);
-    if (sdst[i] != nullptr) st_or_add_bf16x8(sdst[i] + c, o, accumulate);
+  for (int j = 0; j < 16; ++j) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+    pk[j] = *reinterpret_cast<uint32_t*>(&h);
   }
+  if (stats && !keep) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) pk[j] = 0u;
+  }
+  const int m = quarter * 32 + lane;
+  const uint32_t row = smem_u32(s_out) + m * 128;
+  asm volatile("bar.sync 1, 256;" ::: "memory");      // the previous round's tile has been read (TMA and statistics)
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const uint32_t a = row + ((uint32_t)((half * 4 + j) ^ (m & 7)) << 4);
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pk[4 * j]), "r"(pk[4 * j + 1]), "r"(pk[4 * j + 2]),
+                 "r"(pk[4 * j + 3]) : "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the TMA unit
+  asm volatile("bar.sync 1, 256;" ::: "memory");      // the tile is complete
+  if (leader && do_store) tma_store_4d(s_out, map, c0, c1, c2, c3, accumulate);
   if (stats) {
-    const uint8_t* col = stage + (lane >> 4) * TC_STAGE_PITCH + (lane & 15) * 4;       // channels 2cp, 2cp+1 of rows par, par+2, ...
+    const int par = lane >> 4, cp = lane & 15;
+    const uint32_t u = (uint32_t)(half * 4 + (cp >> 2)), w4 = (uint32_t)(cp & 3) * 4;
     float s0 = rs[0], s1 = rs[1], q0 = rs[2], q1 = rs[3];
 #pragma unroll
     for (int r = 0; r < 16; ++r) {
-      const uint32_t w = *reinterpret_cast<const uint32_t*>(col + 2 * r * TC_STAGE_PITCH);
+      const int gr = quarter * 32 + (r >> 2) * 8 + par * 4 + (r & 3);
+      uint32_t w;
+      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(smem_u32(s_out) + gr * 128 + ((u ^ (uint32_t)(gr & 7)) << 4) + w4) : "memory");
       const float f0 = __uint_as_float(w << 16), f1 = __uint_as_float(w & 0xffff0000u);
       s0 += f0; s1 += f1; q0 = fmaf(f0, f0, q0); q1 = fmaf(f1, f1, q1);
     }
     rs[0] = s0; rs[1] = s1; rs[2] = q0; rs[3] = q1;
   }
-  __syncwarp();   // the rows are rewritten by the next chunk
-}
-// the same from the fp32 accumulator values; `keep` = this lane's pixel lies inside the tensor
-__device__ __forceinline__ void tc_store_chunk(const uint32_t (&v)[32], uint8_t* stage, int lane, int sub, int piece,
-                                               __nv_bfloat16* const (&sdst)[4], int c, bool keep, float (&rs)[4], bool stats,
-                                               bool accumulate = false) {
-  uint32_t pk[16];
-#pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
-    pk[j] = keep ? *reinterpret_cast<uint32_t*>(&h) : 0u;
-  }
-  tc_store_packed(pk, stage, lane, sub, piece, sdst, c, rs, stats, accumulate);
-}
-__device__ __forceinline__ void tc_store_chunk(const uint32_t (&v)[32], uint8_t* stage, int lane, int sub, int piece,
-                                               __nv_bfloat16* const (&sdst)[4], int c, bool keep = true) {
-  float none[4] = {0.f, 0.f, 0.f, 0.f};
-  tc_store_chunk(v, stage, lane, sub, piece, sdst, c, keep, none, false, false);
+  if (leader) tma_store_wait_read<OBUF - 1>();         // before this thread arrives at the next round's first barrier
 }
 
-// The running statistics of the eight epilogue warps (tc_store_packed: rs[cc] = chunk cc * 64 + half * 32 of the filter block
+// The running statistics of the eight epilogue warps (tc_round_store: rs[cc] = chunk cc * 64 + half * 32 of the filter block
 // at channel `co`) added to the global fp64 sums: row parities by one shuffle, the four lane quarters through s_stat
 // ([4 quarters][2][BN] floats), one fp64 atomic per channel and CTA; the registers restart at zero. Every epilogue thread
 // calls it (two named barriers over the 256 of them); e = its index among them.
