@@ -649,7 +649,9 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
   const int64_t mtiles = (int64_t)tp.tiles_w * tp.tiles_h * tp.tiles_n;
   // CTA pairs: whenever every SM gets a tile; with fewer boxes (layer4 at batch 4096: 128) only for long reductions, where
   // the halved filter traffic outweighs the pair's start-up (measured: +3 % on 4608-deep, -8 % on 256-deep reductions)
-  if (g_pair_mode && tp.epi == TC_EPI_NONE && tp.Cout % 256 == 0 && tp.ntaps > 0 &&
+  // ... and not for reductions of one or two k-blocks (the 1x1 downsample 128 -> 256: 24.6 us on pairs, 20.5 us on single
+  // CTAs, which keep two output tiles in flight)
+  if (g_pair_mode && tp.epi == TC_EPI_NONE && tp.Cout % 256 == 0 && tp.ntaps > 0 && tp.ntaps * tp.Cin >= 512 &&
       (mtiles >= kNumSMs || (mtiles >= kNumSMs / 2 && tp.ntaps * tp.Cin >= 2304))) {
     // 256-filter tiles unless mode 3 asks for 128 (measured: half-width tiles fill the last wave better, 7 waves of 74
     // clusters instead of 4 on layer3, but pay the pixel box twice and end up slower: 76.6 vs 70.5 us)

@@ -94,6 +94,16 @@ if __name__ == "__main__":
                                      (7, 128, 256, 3, 2), (4, 256, 512, 3, 2), (14, 64, 128, 1, 2), (7, 128, 256, 1, 2), (4, 256, 512, 1, 2)]:
             wcase(N, h, c, k, r, stride)
         sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "pair":       # short reductions with and without the CTA-pair kernel
+        for on in (1, 0):
+            _lib.lib.iit_conv_pair_enable(on)
+            print("pair kernel", on)
+            case(N, 7, 128, 256, 1, 2, True)
+            case(N, 7, 128, 256, 3, 2, True)
+            case(N, 4, 256, 512, 3, 2, True)
+            case(N, 4, 256, 256, 3, 1, True)
+            case(N, 7, 128, 256, 1, 2, False, "dgrad")
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "short":      # the two launches an ncu capture wants
         case(N, 14, 64, 128, 1, 2, True)
         case(N, 14, 64, 128, 1, 2, False)
