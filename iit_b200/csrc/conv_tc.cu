@@ -511,7 +511,9 @@ static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, const CUtenso
   // to the operand ring: 256-filter tiles keep them by running a three-stage ring (their MMAs take 128 cycles per k-block
   // step, so three stages in flight cover the load latency as four do for the narrower tiles); 2 x 128 pixels x 128 filters
   // (four stages of 48 KB) has room for one.
-  constexpr int STAGES = BN == 256 ? 3 : 4;
+  // 64-filter tiles stream long, narrow reductions (the transformer's [tokens x 3072] x [3072 x 64] maps: 24 KB per k-block and
+  // 192 cycles of MMAs): seven stages keep ~170 KB of loads in flight per SM, what HBM latency x bandwidth asks for
+  constexpr int STAGES = BN == 256 ? 3 : BN == 64 ? 7 : 4;
   constexpr int OBUF = (BN == 128 && MT == 2) ? 1 : 2;     // (three stages and two tiles there: 60.6 -> 62.9 us on layer2)
   constexpr size_t smem = STAGES * (MT * TC_BM * TC_BK * 2 + BN * TC_BK * 2) + OBUF * TC_OUT_TILE_BYTES + (2 * STAGES + 4) * 8 + 16 +
                           8 * BN * 4 + 1024;

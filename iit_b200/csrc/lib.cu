@@ -25,7 +25,7 @@ extern "C" int iit_version(void) { return 100; }
 extern "C" unsigned long long iit_launch_count(void) { return iit::g_launches.load(); }
 
 static const char* const kVariantNames[iit::KV_COUNT] = {
-    "conv3x3_tc_kernel<64,4,1>", "conv3x3_tc_kernel<128,4,1>", "conv3x3_tc_kernel<128,4,2>", "conv3x3_tc_kernel<256,3,1>",
+    "conv3x3_tc_kernel<64,7,1>", "conv3x3_tc_kernel<128,4,1>", "conv3x3_tc_kernel<128,4,2>", "conv3x3_tc_kernel<256,3,1>",
     "conv3x3_tc2_kernel<256,6>", "conv3x3_tc2_kernel<128,8>", "conv_win_kernel<128,9,4>", "conv_win_kernel<32,16,4>",
     "wgrad3x3_tc_kernel", "wgrad_win_kernel", "stem_wgrad_win_kernel"};
 extern "C" int iit_kernel_variant_slots(void) { return iit::KV_COUNT; }
