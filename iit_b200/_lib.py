@@ -119,6 +119,7 @@ SIGNATURES = {
     "iit_bn_relu_maxpool_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "iit_conv_win_enable": [_i],
     "iit_conv_pair_enable": [_i],
+    "iit_conv_win_tma_store": [_i],
     "iit_stem_s2d": [_vp, _i, _vp, _vp, _i, _i, _i, _vp],
     "iit_stem_filter_s2d": [_vp, _vp, _vp, _vp],
     "iit_stem_conv_s2d": [_vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp],
@@ -143,7 +144,7 @@ _RESTYPES = {"iit_last_error": C.c_char_p, "iit_launch_count": C.c_ulonglong,
              "iit_kernel_variant_name": C.c_char_p, "iit_kernel_variant_count": C.c_ulonglong,
              "iit_conv2d_wgrad_scratch_bytes": C.c_size_t, "iit_conv2d_wgrad_tc_scratch_bytes": C.c_size_t,
              "iit_stem_wgrad_s2d_scratch_bytes": C.c_size_t}
-_NO_STATUS = set(_RESTYPES) | {"iit_version", "iit_kernel_variant_slots", "iit_conv2d_tc_supported", "iit_conv_win_enable", "iit_conv_pair_enable",
+_NO_STATUS = set(_RESTYPES) | {"iit_version", "iit_kernel_variant_slots", "iit_conv2d_tc_supported", "iit_conv_win_enable", "iit_conv_pair_enable", "iit_conv_win_tma_store",
                                "iit_conv2d_patch_fusable"}
 
 

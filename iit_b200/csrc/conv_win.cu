@@ -16,6 +16,8 @@
 //
 // Persistent CTAs; all filter taps resident in shared memory; STAGES image tiles in flight; 4 TMEM accumulators of
 // 64 columns so that the epilogue (TMEM -> bf16 NHWC + BatchNorm statistics) overlaps the next tiles' MMAs.
+#include <stdlib.h>
+
 #include "tc_common.cuh"
 
 namespace iit {
@@ -48,9 +50,14 @@ __device__ __forceinline__ uint64_t win_desc(uint32_t smem_addr) {
   return (uint64_t)((smem_addr >> 4) & 0x3FFF) | (1ull << 16) | ((uint64_t)((8 * RB) >> 4) << 32) | (1ull << 46) | (swz << 61);
 }
 
-template <int RB, int NTAPS, int STAGES>
+// OBUF = 0: the epilogue stores from registers, one pixel row per lane. OBUF = 1 / 2: it stores by TMA from that many
+// [128 positions][64 filters] tiles (tc_round_store) -- possible when an M tile is a rectangle of the output, i.e. the padded
+// row length divides 128 and the image is one band: then the positions of the padding columns and of rows below the image
+// fall outside the tensor map and the hardware clips them.
+template <int RB, int NTAPS, int STAGES, int OBUF>
 __global__ void __launch_bounds__(WIN_CONV_THREADS) conv_win_kernel(const __grid_constant__ CUtensorMap map_a,
                                                                const __grid_constant__ CUtensorMap map_b,
+                                                               const __grid_constant__ CUtensorMap map_o,
                                                                __nv_bfloat16* __restrict__ out, WinParams p,
                                                                double* __restrict__ bn_sum, double* __restrict__ bn_sq) {
   extern __shared__ uint8_t smem_raw[];
@@ -60,14 +67,15 @@ __global__ void __launch_bounds__(WIN_CONV_THREADS) conv_win_kernel(const __grid
   constexpr int KSTEPS = RB / 32;                     // UMMA K = 16 bf16 = 32 bytes
   uint8_t* sB = smem;                                 // [ntaps][64][RB]
   uint8_t* sA = smem + ((p.ntaps * B_TAP + 1023) & ~1023u);
-  uint64_t* full = reinterpret_cast<uint64_t*>(sA + (size_t)STAGES * p.stage_bytes);
+  uint8_t* s_out = sA + (size_t)STAGES * p.stage_bytes;   // [OBUF][128][128 bytes], SWIZZLE_128B (1024-byte aligned: stage_bytes is)
+  uint64_t* full = reinterpret_cast<uint64_t*>(s_out + OBUF * TC_OUT_TILE_BYTES);
   uint64_t* empty = full + STAGES;
   uint64_t* tmem_full = empty + STAGES;               // [NACC]
   uint64_t* tmem_empty = tmem_full + WIN_NACC;        // [NACC]
   uint64_t* b_full = tmem_empty + WIN_NACC;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(b_full + 1);
-  float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [2][BN]
-  if (bn_sum != nullptr && threadIdx.x < BN) { s_stat[threadIdx.x] = 0.f; s_stat[threadIdx.x + BN] = 0.f; }
+  float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [2][BN]; with TMA stores [4 lane quarters][2][BN] (tc_flush_stats)
+  if (OBUF == 0 && bn_sum != nullptr && threadIdx.x < BN) { s_stat[threadIdx.x] = 0.f; s_stat[threadIdx.x + BN] = 0.f; }
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = p.N * p.bands;
@@ -164,6 +172,38 @@ __global__ void __launch_bounds__(WIN_CONV_THREADS) conv_win_kernel(const __grid
     const int c = half * 32;              // this warp's filters
     const int m = quarter * 32 + lane;
     const int e = threadIdx.x - 64;       // 0..255
+    if constexpr (OBUF > 0) {
+      // TMA-store epilogue. ncu on the register-store form (profiles/r02_ncu_single_kernels.md): its 16-byte stores to 32
+      // different lines per instruction are one L1 wavefront each -- 1024 per tile, 822 MB of half-filled sectors for the
+      // stem's 411 MB -- on the SAME data pipe the MMAs read their operands through: stem 54 % store + 44 % tensor-core
+      // wavefronts, layer1 69 % tensor-core. A TMA store reads the tile in 128 full-width wavefronts.
+      const bool leader = e == 0;
+      float rstat[1][4] = {{0.f, 0.f, 0.f, 0.f}};
+      uint32_t it = 0, round = 0;
+      const int j0 = p.pad_top * p.PW + p.pad_left;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int n = tile;                                    // one band per image
+        for (int t = 0; t < p.mtiles; ++t, ++it) {
+          const int jj = j0 + 128 * t + m;
+          const int hh = jj / p.PW - p.pad_top, ww = jj % p.PW - p.pad_left;
+          const bool ok = ww >= 0 && ww < p.OW && hh >= 0 && hh < p.OH;
+          const uint32_t acc = it % WIN_NACC, acc_phase = (it / WIN_NACC) & 1;
+          mbar_wait(&tmem_full[acc], acc_phase);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          uint32_t v[32];
+          tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + c), v);
+          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[acc])) : "memory");
+          // the tile's 128 positions are rows hh0 .. of the image, all PW columns from output column 0
+          const int hh0 = (j0 + 128 * t) / p.PW - p.pad_top;
+          tc_round_store<(OBUF > 0 ? OBUF : 1)>(v, ok, s_out + (round++ % (OBUF > 0 ? OBUF : 1)) * TC_OUT_TILE_BYTES, quarter, half, lane,
+                                                leader, true, &map_o, 0, 0, hh0, n, p.accumulate != 0, rstat[0], bn_sum != nullptr);
+        }
+      }
+      if (leader) tma_store_wait_all();
+      if (bn_sum != nullptr) tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, 0, bn_sum, bn_sq);
+    } else {
     float st_s[32], st_q[32];
 #pragma unroll
     for (int j = 0; j < 32; ++j) { st_s[j] = 0.f; st_q[j] = 0.f; }
@@ -228,6 +268,7 @@ __global__ void __launch_bounds__(WIN_CONV_THREADS) conv_win_kernel(const __grid
       asm volatile("bar.sync 1, 256;" ::: "memory");
       if (e < BN) { atomicAdd(&bn_sum[e], (double)s_stat[e]); atomicAdd(&bn_sq[e], (double)s_stat[BN + e]); }
     }
+    }  // OBUF == 0
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -240,9 +281,10 @@ __global__ void __launch_bounds__(WIN_CONV_THREADS) conv_win_kernel(const __grid
 // ---- host side -----------------------------------------------------------------------------------
 constexpr size_t WIN_SMEM_MAX = 227 * 1024;
 
-static size_t win_smem_bytes(const WinParams& p, int RB, int stages) {
+static size_t win_smem_bytes(const WinParams& p, int RB, int stages, int obuf = 0) {
   const size_t b = ((size_t)p.ntaps * WIN_BN * RB + 1023) & ~(size_t)1023;
-  return b + (size_t)stages * p.stage_bytes + (2 * stages + 2 * WIN_NACC + 1) * 8 + 16 + 2 * WIN_BN * 4 + 1024;
+  return b + (size_t)stages * p.stage_bytes + (size_t)obuf * TC_OUT_TILE_BYTES + (2 * stages + 2 * WIN_NACC + 1) * 8 + 16 +
+         (obuf ? 8 : 2) * WIN_BN * 4 + 1024;
 }
 
 // Fills the geometry for an image of IH x IW input pixels whose TMA box is (PW x box_h) pixels per band.
@@ -295,25 +337,77 @@ static int win_encode_b(CUtensorMap* m, const void* wmat, int Kg, int RB, const 
   return 0;
 }
 
+// the output as the TMA-store epilogue sees it: [N][OH][OW][64] in boxes of 64 filters x PW columns x 128 / PW rows
+static int win_encode_out(CUtensorMap* m, void* out, const WinParams& p, const char* name) {
+  EncodeTiledFn enc = get_encode();
+  IIT_REQUIRE(enc != nullptr, "%s: cuTensorMapEncodeTiled is unavailable in this driver", name);
+  cuuint64_t dims[4] = {(cuuint64_t)WIN_BN, (cuuint64_t)p.OW, (cuuint64_t)p.OH, (cuuint64_t)p.N};
+  cuuint64_t strides[3] = {(cuuint64_t)WIN_BN * 2, (cuuint64_t)p.OW * WIN_BN * 2, (cuuint64_t)p.OH * p.OW * WIN_BN * 2};
+  cuuint32_t box[4] = {(cuuint32_t)WIN_BN, (cuuint32_t)p.PW, (cuuint32_t)(128 / p.PW), 1};
+  cuuint32_t es[4] = {1, 1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, out, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  IIT_REQUIRE(r == CUDA_SUCCESS, "%s: output tensor map rejected (CUresult %d)", name, (int)r);
+  return 0;
+}
+
+static int win_tma_default() {
+  const char* e = getenv("IIT_WIN_TMA_STORE");
+  return (e != nullptr && e[0] == '0') ? 0 : 1;
+}
+static int g_win_tma_out = win_tma_default();     // iit_conv_win_tma_store(): 0 = always the register-store epilogue (A/B measurements)
+
 template <int RB, int NTAPS>
 static int win_launch(const CUtensorMap& ma, const CUtensorMap& mb, void* out, const WinParams& p, cudaStream_t st,
                       double* bn_sum, double* bn_sq, const char* name) {
+  int grid = kNumSMs;
+  if (grid > p.N * p.bands) grid = p.N * p.bands;
+  const int dev = current_device_slot();
+  // TMA stores when an M tile is a rectangle of the output (see the kernel): two output tiles and at least three operand
+  // stages if that fits, else one tile
+  const bool rect = g_win_tma_out && 128 % p.PW == 0 && p.bands == 1;
+  if (rect) {
+    int obuf = 0, stages = 0;
+    if (win_smem_bytes(p, RB, 4, 2) <= WIN_SMEM_MAX) { obuf = 2; stages = 4; }
+    else if (win_smem_bytes(p, RB, 3, 2) <= WIN_SMEM_MAX) { obuf = 2; stages = 3; }
+    else if (win_smem_bytes(p, RB, 4, 1) <= WIN_SMEM_MAX) { obuf = 1; stages = 4; }
+    else if (win_smem_bytes(p, RB, 3, 1) <= WIN_SMEM_MAX) { obuf = 1; stages = 3; }
+    if (obuf) {
+      CUtensorMap mo;
+      if (win_encode_out(&mo, out, p, name)) return 1;
+      const size_t smem = win_smem_bytes(p, RB, stages, obuf);
+      static bool attr_t[kMaxDevices][5][3] = {};
+#define IIT_WIN_LAUNCH_T(S, O)                                                                                           \
+  if (stages == S && obuf == O) {                                                                                        \
+    if (!attr_t[dev][S][O]) {                                                                                            \
+      IIT_CUDA(cudaFuncSetAttribute(conv_win_kernel<RB, NTAPS, S, O>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WIN_SMEM_MAX)); \
+      attr_t[dev][S][O] = true;                                                                                          \
+    }                                                                                                                    \
+    conv_win_kernel<RB, NTAPS, S, O><<<grid, WIN_CONV_THREADS, smem, st>>>(ma, mb, mo, (__nv_bfloat16*)out, p, bn_sum, bn_sq);       \
+  }
+      IIT_WIN_LAUNCH_T(4, 2)
+      IIT_WIN_LAUNCH_T(3, 2)
+      IIT_WIN_LAUNCH_T(4, 1)
+      IIT_WIN_LAUNCH_T(3, 1)
+#undef IIT_WIN_LAUNCH_T
+      count_variant(RB == 128 ? KV_WIN_3X3 : KV_WIN_STEM);
+      IIT_LAUNCH_CHECK(name);
+      return 0;
+    }
+  }
   // as many tiles in flight as the shared-memory budget allows, at most 4
   int stages = 4;
   while (stages > 2 && win_smem_bytes(p, RB, stages) > WIN_SMEM_MAX) --stages;
   const size_t smem = win_smem_bytes(p, RB, stages);
   IIT_REQUIRE(smem <= WIN_SMEM_MAX, "%s: tile does not fit shared memory", name);
-  int grid = kNumSMs;
-  if (grid > p.N * p.bands) grid = p.N * p.bands;
   static bool attr_set[kMaxDevices][5] = {};
-  const int dev = current_device_slot();
 #define IIT_WIN_LAUNCH(S)                                                                                              \
   case S:                                                                                                              \
     if (!attr_set[dev][S]) {                                                                                           \
-      IIT_CUDA(cudaFuncSetAttribute(conv_win_kernel<RB, NTAPS, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WIN_SMEM_MAX)); \
+      IIT_CUDA(cudaFuncSetAttribute(conv_win_kernel<RB, NTAPS, S, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WIN_SMEM_MAX)); \
       attr_set[dev][S] = true;                                                                                         \
     }                                                                                                                  \
-    conv_win_kernel<RB, NTAPS, S><<<grid, WIN_CONV_THREADS, smem, st>>>(ma, mb, (__nv_bfloat16*)out, p, bn_sum, bn_sq);            \
+    conv_win_kernel<RB, NTAPS, S, 0><<<grid, WIN_CONV_THREADS, smem, st>>>(ma, mb, ma, (__nv_bfloat16*)out, p, bn_sum, bn_sq);       \
     count_variant(RB == 128 ? KV_WIN_3X3 : KV_WIN_STEM);                                                               \
     break;
   switch (stages) {
@@ -720,7 +814,11 @@ __global__ void stem_wgrad_finish_kernel(const float* __restrict__ part, int spl
 }
 
 static bool stem_wgrad_plan(int n, int sh, int sw, StemWgradParams* p, int* grid, size_t* smem, int stages) {
-  const int OH = sh - 3, OW = sw - 3, PW = sw;
+  // padded row length: 32 for the 31-wide image of the 56-pixel input (TMA zero-fills the extra column; the M-tile count
+  // stays 7) so that an M tile is a 4 x 32 rectangle of the output and the epilogue can store by TMA
+  const int OH = sh - 3, OW = sw - 3;
+  int PW = sw;
+  if (sw > 16 && sw < 32 && ((OH - 1) * 32 + OW + 127) / 128 <= ((OH - 1) * sw + OW + 127) / 128) PW = 32;
   if (OH < 1 || OW < 1 || PW > STEM_LEAD) return false;      // one raster row of zeros must fit in front of the dy band
   const int a0 = STEM_LEAD - PW;                             // first tile row of M block 0 (block 1 starts at STEM_LEAD)
   for (int BH = OH; BH >= 1; --BH) {
@@ -794,6 +892,12 @@ extern "C" int iit_stem_wgrad_s2d(const void* dy, const void* s2d, float* dw, co
 // Stem: y[n,p,q,k] = sum_{R,S<4} sum_{c<16} s2d[n, p+R, q+S, c] * w2[k, R, S, c], where s2d is the zero-padded image
 // after a 2x2 space-to-depth ([N, (H+6)/2, (W+6)/2, 16] bf16, 12 real channels) and w2 the 7x7 filter regrouped
 // accordingly ([64, 4, 4, 16] bf16): exactly the 7x7 / stride-2 / pad-3 convolution.
+extern "C" int iit_conv_win_tma_store(int on) {
+  const int before = g_win_tma_out;
+  g_win_tma_out = on ? 1 : 0;
+  return before;
+}
+
 extern "C" int iit_stem_conv_s2d(const void* s2d, const void* w2, void* y, int n, int sh, int sw, double* bn_sum, double* bn_sqsum,
                                  void* stream) {
   const char* name = "iit_stem_conv_s2d";

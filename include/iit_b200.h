@@ -253,6 +253,9 @@ int iit_conv_win_enable(int on);
  * 256 pixel x 256 filter tile, each loading half of the filter block). Same results bit for bit as the single-CTA
  * kernel; this switch (returns the previous setting) lets tests and profiles compare the two. */
 int iit_conv_pair_enable(int on);
+/* The shifted-window kernels store by TMA where an M tile is a rectangle of the output (default on; 0 = always the
+ * register-store epilogue). Same results either way; for A/B measurements. Returns the previous setting. */
+int iit_conv_win_tma_store(int on);
 /* The 7x7 / stride-2 / pad-3 stem on 3 input channels (torchvision resnet18.conv1 under
  * iit/utils/wrapper.py:33-66) as a 4x4 stride-1 convolution over the 2x2 space-to-depth image:
  *   iit_stem_s2d:      x [n,3,h,w] (fp32 or bf16, any strides; h, w even) -> s2d [n,(h+6)/2,(w+6)/2,16] bf16,

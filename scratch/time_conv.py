@@ -79,20 +79,30 @@ if __name__ == "__main__":
             case(N, 14, 64, 64, 3, 1, stats)
         case(N, 14, 64, 64, 3, 1, False, "dgrad")
         sys.exit(0)
-    if len(sys.argv) > 1 and sys.argv[1] == "stem":       # the stem through the model's own module (space-to-depth window kernel)
-        from iit_b200.nn.resnet import Conv2d
-        conv = Conv2d(3, 64, 7, 2, 3).to(dev)
-        img = torch.randn(N, 3, 56, 56, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
-        with torch.no_grad():
-            before = _lib.kernel_variant_counts()
-            us = t(lambda: conv(img))
-            after = _lib.kernel_variant_counts()
-        print(f"stem forward (module call, includes its relayout launches): {us:.1f} us", [k_ for k_ in after if after[k_] != before.get(k_, 0)])
+    if len(sys.argv) > 1 and sys.argv[1] == "stem":       # the stem convolution on the space-to-depth window kernel
+        s2d = torch.randn(N, 31, 31, 16, device=dev).bfloat16()
+        w2 = torch.randn(64 * 4 * 4 * 16, device=dev).bfloat16()
+        y = torch.empty(N, 28, 28, 64, device=dev).bfloat16()
+        st = ops._stream()
+        for stats in (True, False):
+            s1 = torch.zeros(64, dtype=torch.float64, device=dev) if stats else None
+            s2 = torch.zeros(64, dtype=torch.float64, device=dev) if stats else None
+            us = t(lambda: ops.call("iit_stem_conv_s2d", ops._p(s2d), ops._p(w2), ops._p(y), N, 31, 31, ops._p(s1), ops._p(s2), st))
+            print(f"stem s2d conv n={N} stats={int(stats)}: {us:.1f} us  out {y.numel() * 2 / us / 1e3:.0f} GB/s", flush=True)
         sys.exit(0)
-    if len(sys.argv) > 1 and sys.argv[1] == "wgrad":
-        for (h, c, k, r, stride) in [(7, 128, 128, 3, 1), (4, 256, 256, 3, 1), (2, 512, 512, 3, 1), (14, 64, 64, 3, 1), (14, 64, 128, 3, 2),
-                                     (7, 128, 256, 3, 2), (4, 256, 512, 3, 2), (14, 64, 128, 1, 2), (7, 128, 256, 1, 2), (4, 256, 512, 1, 2)]:
-            wcase(N, h, c, k, r, stride)
+    if len(sys.argv) > 1 and sys.argv[1] == "wintma":     # shifted-window kernels with / without the TMA-store epilogue
+        s2d = torch.randn(N, 31, 31, 16, device=dev).bfloat16()
+        w2 = torch.randn(64 * 4 * 4 * 16, device=dev).bfloat16()
+        y = torch.empty(N, 28, 28, 64, device=dev).bfloat16()
+        st = ops._stream()
+        s1 = torch.zeros(64, dtype=torch.float64, device=dev); s2 = torch.zeros(64, dtype=torch.float64, device=dev)
+        for on in (1, 0, 1):
+            _lib.lib.iit_conv_win_tma_store(on)
+            print("TMA-store epilogue", on)
+            us = t(lambda: ops.call("iit_stem_conv_s2d", ops._p(s2d), ops._p(w2), ops._p(y), N, 31, 31, ops._p(s1), ops._p(s2), st))
+            print(f"stem s2d conv n={N} stats=1: {us:.1f} us  out {y.numel() * 2 / us / 1e3:.0f} GB/s", flush=True)
+            case(N, 14, 64, 64, 3, 1, True)
+            case(N, 14, 64, 64, 3, 1, False, "dgrad")
         sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "pair":       # short reductions with and without the CTA-pair kernel
         for on in (1, 0):
