@@ -814,11 +814,7 @@ __global__ void stem_wgrad_finish_kernel(const float* __restrict__ part, int spl
 }
 
 static bool stem_wgrad_plan(int n, int sh, int sw, StemWgradParams* p, int* grid, size_t* smem, int stages) {
-  // padded row length: 32 for the 31-wide image of the 56-pixel input (TMA zero-fills the extra column; the M-tile count
-  // stays 7) so that an M tile is a 4 x 32 rectangle of the output and the epilogue can store by TMA
-  const int OH = sh - 3, OW = sw - 3;
-  int PW = sw;
-  if (sw > 16 && sw < 32 && ((OH - 1) * 32 + OW + 127) / 128 <= ((OH - 1) * sw + OW + 127) / 128) PW = 32;
+  const int OH = sh - 3, OW = sw - 3, PW = sw;
   if (OH < 1 || OW < 1 || PW > STEM_LEAD) return false;      // one raster row of zeros must fit in front of the dy band
   const int a0 = STEM_LEAD - PW;                             // first tile row of M block 0 (block 1 starts at STEM_LEAD)
   for (int BH = OH; BH >= 1; --BH) {
@@ -907,7 +903,11 @@ extern "C" int iit_stem_conv_s2d(const void* s2d, const void* w2, void* y, int n
               "%s: pointers must be 16-byte aligned", name);
   WinParams p{};
   p.N = n; p.ntaps = 16;
-  const int OH = sh - 3, OW = sw - 3, PW = sw;
+  // padded row length: 32 for the 31-wide image of the 56-pixel input (TMA zero-fills the extra column; the M-tile count
+  // stays 7) so that an M tile is a 4 x 32 rectangle of the output and the epilogue can store by TMA
+  const int OH = sh - 3, OW = sw - 3;
+  int PW = sw;
+  if (sw > 16 && sw < 32 && ((OH - 1) * 32 + OW + 127) / 128 <= ((OH - 1) * sw + OW + 127) / 128) PW = 32;
   IIT_REQUIRE(win_plan(&p, 32, OH, OW, PW, 3, 0, 0, 3 * PW + 3, 0), "%s: image %dx%d does not fit the shifted-window kernel", name, sh, sw);
   p.x0 = 0; p.y0 = 0; p.y_step = p.band_h;
   for (int R = 0; R < 4; ++R)
