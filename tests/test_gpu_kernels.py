@@ -450,7 +450,13 @@ def test_tensor_core_path_is_taken_and_matches_cuda_core_path(ops):
             (64, 64, 21, 3, 3, 1, 1), (64, 128, 14, 4, 3, 1, 1),
             (64, 128, 14, 9, 3, 2, 1), (128, 256, 7, 5, 3, 2, 1), (256, 512, 4, 11, 3, 2, 1),      # strided 3x3
             (64, 128, 14, 9, 1, 2, 0), (128, 256, 7, 5, 1, 2, 0), (256, 512, 4, 11, 1, 2, 0),      # downsample 1x1
-            (64, 128, 21, 2, 3, 2, 1), (64, 128, 21, 2, 1, 2, 0)]:                                  # odd sizes (84 px)
+            (64, 128, 21, 2, 3, 2, 1), (64, 128, 21, 2, 1, 2, 0),                                   # odd sizes (84 px)
+            # the TMA-store epilogue clips what lies outside the tensor: image counts off the pixel box (1, 129, 257 images
+            # against boxes of 8 / 32 / 128 images), grids no power-of-two box tiles (11 x 11, 3 x 3, 6 x 6), token GEMMs
+            # whose row count is no multiple of 128, 64 / 192 / 320 filters (one, three, five 64-channel rounds)
+            (128, 128, 4, 1, 3, 1, 1), (256, 256, 2, 129, 3, 1, 1), (128, 256, 1, 257, 1, 1, 0), (128, 128, 11, 3, 3, 1, 1),
+            (256, 256, 3, 7, 3, 1, 1), (128, 128, 6, 10, 3, 1, 1), (64, 192, 1, 300, 1, 1, 0), (192, 64, 1, 300, 1, 1, 0),
+            (64, 320, 1, 77, 1, 1, 0), (64, 64, 14, 1, 3, 1, 1), (64, 64, 14, 150, 3, 1, 1)]:
         conv = Conv2d(c, k, ks, stride, pad).to(DEV)
         ohw = (hw + 2 * pad - ks) // stride + 1
         x = torch.randn(n, c, hw, hw, generator=g).to(DEV).bfloat16().contiguous(memory_format=torch.channels_last)
