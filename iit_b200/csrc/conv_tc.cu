@@ -97,7 +97,7 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
   uint64_t* tmem_full = empty + STAGES;      // [2]
   uint64_t* tmem_empty = tmem_full + 2;      // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [4 lane quarters][2][BN]: tc_flush_stats
+  float* s_stat = reinterpret_cast<float*>(s_out);           // [4 lane quarters][2][BN] (<= 8 KB) over the first output tile: tc_flush_stats
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kchunks = p.Cin / TC_BK;
@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
       const int rt = ksplit > 1 ? tile % real_tiles : tile;
       const int co0 = (nblk > 1 ? rt % nblk : 0) * BN;
       if (bn_sum != nullptr && run_co >= 0 && (run_co != co0 || stat_tiles >= 16)) {
-        tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, run_co, bn_sum, bn_sq);
+        tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, run_co, bn_sum, bn_sq, leader);
         stat_tiles = 0;
       }
       run_co = co0;
@@ -307,7 +307,7 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
      }  // mt
     }
     if (leader) tma_store_wait_all();    // every store of this CTA has been written before it may exit
-    if (bn_sum != nullptr && run_co >= 0) tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, run_co, bn_sum, bn_sq);
+    if (bn_sum != nullptr && run_co >= 0) tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, run_co, bn_sum, bn_sq, leader);
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -339,13 +339,13 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
   constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2, B_BYTES = BHALF * TC_BK * 2;
   uint8_t* sA = smem;
   uint8_t* sB = smem + STAGES * A_BYTES;
-  uint8_t* s_out = sB + STAGES * B_BYTES;     // this CTA's [128 rows][128 bytes] output tile of one round (tc_round_store)
-  uint64_t* full = reinterpret_cast<uint64_t*>(s_out + TC_OUT_TILE_BYTES);
+  uint8_t* s_out = sB + STAGES * B_BYTES;     // this CTA's two [128 rows][128 bytes] output tiles (tc_round_store)
+  uint64_t* full = reinterpret_cast<uint64_t*>(s_out + 2 * TC_OUT_TILE_BYTES);
   uint64_t* empty = full + STAGES;
   uint64_t* tmem_full = empty + STAGES;      // [2]
   uint64_t* tmem_empty = tmem_full + 2;      // [2] (the leader's are used)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  float* s_stat = reinterpret_cast<float*>(tmem_slot + 2);   // [4 lane quarters][2][BN]: tc_flush_stats
+  float* s_stat = reinterpret_cast<float*>(s_out);           // over the first output tile: tc_flush_stats
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -452,11 +452,11 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
     int stat_tiles = 0;
     const bool one_box = p.tiles_w == 1 && p.tiles_h == 1;
     int run_co = -1;
-    uint32_t it = 0;
+    uint32_t it = 0, round = 0;
     for (int tile = pair; tile < total_tiles; tile += npairs, ++it) {
       const int co0 = (tile % nblk) * BN;
       if (bn_sum != nullptr && run_co >= 0 && (run_co != co0 || stat_tiles >= 16)) {
-        tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, run_co, bn_sum, bn_sq);
+        tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, run_co, bn_sum, bn_sq, leader);
         stat_tiles = 0;
       }
       run_co = co0;
@@ -481,12 +481,12 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
           __syncwarp();
           if (lane == 0) mbar_arrive_cluster(lead_empty);
         }
-        tc_round_store<1>(v, ok, s_out, quarter, half, lane, leader, box_ok, &map_o, co0 + cc * 64, q_box, p_box, n_box,
-                          p.accumulate != 0, rstat[cc], bn_sum != nullptr);
+        tc_round_store<2>(v, ok, s_out + (round++ & 1) * TC_OUT_TILE_BYTES, quarter, half, lane, leader, box_ok, &map_o,
+                          co0 + cc * 64, q_box, p_box, n_box, p.accumulate != 0, rstat[cc], bn_sum != nullptr);
       }
     }
     if (leader) tma_store_wait_all();
-    if (bn_sum != nullptr && run_co >= 0) tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, run_co, bn_sum, bn_sq);
+    if (bn_sum != nullptr && run_co >= 0) tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, run_co, bn_sum, bn_sq, leader);
   }
   // neither CTA may leave (or free the pair's TMEM) while its peer can still signal its barriers or read its operands
   __syncwarp();
@@ -514,9 +514,9 @@ static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, const CUtenso
   // 64-filter tiles stream long, narrow reductions (the transformer's [tokens x 3072] x [3072 x 64] maps: 24 KB per k-block and
   // 192 cycles of MMAs): seven stages keep ~170 KB of loads in flight per SM, what HBM latency x bandwidth asks for
   constexpr int STAGES = BN == 256 ? 3 : BN == 64 ? 7 : 4;
-  constexpr int OBUF = (BN == 128 && MT == 2) ? 1 : 2;     // (three stages and two tiles there: 60.6 -> 62.9 us on layer2)
+  constexpr int OBUF = 2;                                   // the statistics scratch lives in the first tile (tc_flush_stats)
   constexpr size_t smem = STAGES * (MT * TC_BM * TC_BK * 2 + BN * TC_BK * 2) + OBUF * TC_OUT_TILE_BYTES + (2 * STAGES + 4) * 8 + 16 +
-                          8 * BN * 4 + 1024;
+                          1024;
   static_assert(smem <= 227 * 1024, "tile does not fit shared memory");
   auto kernel = conv3x3_tc_kernel<BN, STAGES, MT, OBUF>;
   static int ctas_per_sm_dev[kMaxDevices] = {};
@@ -541,8 +541,9 @@ template <int BN>
 static int launch_tc2(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, __nv_bfloat16* out, const TcParams& p,
                       int total_tiles, cudaStream_t st, double* bn_sum, double* bn_sq) {
   constexpr int STAGES = BN == 256 ? 6 : 8;
-  constexpr size_t smem = STAGES * (TC_BM * TC_BK * 2 + (BN / 2) * TC_BK * 2) + TC_OUT_TILE_BYTES + (2 * STAGES + 4) * 8 + 16 +
-                          8 * BN * 4 + 1024;
+  constexpr size_t smem = STAGES * (TC_BM * TC_BK * 2 + (BN / 2) * TC_BK * 2) + 2 * TC_OUT_TILE_BYTES + (2 * STAGES + 4) * 8 + 16 +
+                          1024;
+  static_assert(smem <= 227 * 1024, "pair tile does not fit shared memory");
   static int max_clusters_dev[kMaxDevices] = {};
   int& max_clusters = max_clusters_dev[current_device_slot()];
   cudaLaunchConfig_t cfg = {};

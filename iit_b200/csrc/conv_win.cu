@@ -202,7 +202,7 @@ __global__ void __launch_bounds__(WIN_CONV_THREADS) conv_win_kernel(const __grid
         }
       }
       if (leader) tma_store_wait_all();
-      if (bn_sum != nullptr) tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, 0, bn_sum, bn_sq);
+      if (bn_sum != nullptr) tc_flush_stats<BN>(rstat, s_stat, quarter, half, lane, e, 0, bn_sum, bn_sq, leader);
     } else {
     float st_s[32], st_q[32];
 #pragma unroll

@@ -254,10 +254,14 @@ __device__ __forceinline__ void tc_round_store(const uint32_t (&v)[32], bool kee
 // The running statistics of the eight epilogue warps (tc_round_store: rs[cc] = chunk cc * 64 + half * 32 of the filter block
 // at channel `co`) added to the global fp64 sums: row parities by one shuffle, the four lane quarters through s_stat
 // ([4 quarters][2][BN] floats), one fp64 atomic per channel and CTA; the registers restart at zero. Every epilogue thread
-// calls it (two named barriers over the 256 of them); e = its index among them.
+// calls it (named barriers over the 256 of them); e = its index among them.
+// s_stat may be the FIRST OUTPUT TILE of the CTA (the kernels alias it: a flush is rare and the 4-8 KB are what lets two
+// output tiles fit next to the operand ring): the leader first waits until the TMA unit has read every tile it was given.
 template <int BN>
 __device__ __forceinline__ void tc_flush_stats(float (&rs)[BN / 64][4], float* s_stat, int quarter, int half, int lane, int e,
-                                               int co, double* bn_sum, double* bn_sq) {
+                                               int co, double* bn_sum, double* bn_sq, bool leader) {
+  if (leader) tma_store_wait_read<0>();
+  asm volatile("bar.sync 1, 256;" ::: "memory");   // no tile is being read, every warp is past its statistics reads
 #pragma unroll
   for (int cc = 0; cc < BN / 64; ++cc) {
 #pragma unroll
@@ -278,7 +282,7 @@ __device__ __forceinline__ void tc_flush_stats(float (&rs)[BN / 64][4], float* s
     atomicAdd(&bn_sum[co + ch], s);
     atomicAdd(&bn_sq[co + ch], q);
   }
-  asm volatile("bar.sync 1, 256;" ::: "memory");   // s_stat may be rewritten
+  asm volatile("bar.sync 1, 256;" ::: "memory");   // s_stat may be rewritten (as an output tile)
 }
 
 // ---- host side -----------------------------------------------------------------------------------
