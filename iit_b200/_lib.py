@@ -81,6 +81,8 @@ SIGNATURES = {
     "iit_conv2d_wgrad_tc_scratch_bytes": [_ConvP],
     "iit_conv2d_wgrad_tc": [_vp, _vp, _vp, _ConvP, _vp, _sz, _vp],
     "iit_conv2d_wgrad_tc_accumulate": [_vp, _vp, _vp, _ConvP, _vp, _sz, _vp],
+    "iit_conv2d_fprop_tc_affine": [_vp, _vp, _vp, _ConvP, _vp, _vp, _vp, _i, _vp],
+    "iit_bn_eval_affine": [_vp, _vp, _vp, _vp, _i, _f, _vp, _vp, _vp],
     "iit_conv2d_wgrad_tc_scatter": [_vp, _vp, _ConvP, _vp, _sz, _vp, _i, _i64, _vp],
     "iit_bn_param_grads": [_vp, _i, _vp, _vp, _i, _i, _vp],
     "iit_conv2d_wgrad_scratch_bytes": [_ConvP],

@@ -44,6 +44,9 @@ struct TcParams {
   // GEMM epilogues (the transformer's linear maps; single-CTA kernel only): applied to the fp32 accumulator before rounding
   int epi;                        // TC_EPI_*
   const float* bias;              // [Cout] fp32, added to every row (TC_EPI_BIAS / TC_EPI_GELU); may be null
+  const float* scale;             // [Cout] fp32 or null: the accumulator is multiplied by it before `bias` is added (an
+                                  // eval-mode BatchNorm folded into the convolution: scale = gamma / std, bias = beta - mean * scale)
+  int relu;                       // != 0: max(0, .) after bias / residual
   const __nv_bfloat16* aux;       // laid out like `out`: the residual added (TC_EPI_BIAS, may be null) or the pre-activation
                                   // whose GELU derivative multiplies the result (TC_EPI_GELU_BWD)
   __nv_bfloat16* out2;            // TC_EPI_GELU: receives the pre-activation (may be null: not kept)
@@ -257,7 +260,8 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
         }
         if (p.epi != TC_EPI_NONE) {
           // this lane's own row (pixel n, pp, qq), channels co0 + c .. + 31, still fp32
-          if (p.bias != nullptr) {
+          if (p.scale != nullptr) tc_scale_shift(v, p.scale + co0 + c, p.bias + co0 + c);
+          else if (p.bias != nullptr) {
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
               const float4 b4 = *reinterpret_cast<const float4*>(p.bias + co0 + c + j);
@@ -290,6 +294,7 @@ __global__ void __launch_bounds__(TC_CONV_THREADS) conv3x3_tc_kernel(const __gri
               }
             }
           }
+          if (p.relu) tc_relu(v);
           if (p.epi == TC_EPI_GELU) {
             if (p.out2 != nullptr) {     // the pre-activation, kept for the backward: a round of its own through the same tile
               float none[4] = {0.f, 0.f, 0.f, 0.f};
@@ -481,6 +486,15 @@ conv3x3_tc2_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
           __syncwarp();
           if (lane == 0) mbar_arrive_cluster(lead_empty);
         }
+        if (p.epi == TC_EPI_BIAS) {     // folded eval-mode BatchNorm: scale / shift (+ residual) (+ ReLU) on the fp32 accumulator
+          if (p.scale != nullptr) tc_scale_shift(v, p.scale + co0 + c, p.bias + co0 + c);
+          if (p.aux != nullptr && ok) {
+            const int64_t own = (((int64_t)(n_box + nl) * p.OH + ((p_box + hl) * p.out_mul + p.out_oh)) * p.OW +
+                                 ((q_box + wl) * p.out_mul + p.out_ow)) * p.Cout + co0 + c;
+            tc_add_bf16_row(v, p.aux + own);
+          }
+          if (p.relu) tc_relu(v);
+        }
         tc_round_store<2>(v, ok, s_out + (round++ & 1) * TC_OUT_TILE_BYTES, quarter, half, lane, leader, box_ok, &map_o,
                           co0 + cc * 64, q_box, p_box, n_box, p.accumulate != 0, rstat[cc], bn_sum != nullptr);
       }
@@ -654,7 +668,8 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
   // the halved filter traffic outweighs the pair's start-up (measured: +3 % on 4608-deep, -8 % on 256-deep reductions)
   // ... and not for reductions of one or two k-blocks (the 1x1 downsample 128 -> 256: 24.6 us on pairs, 20.5 us on single
   // CTAs, which keep two output tiles in flight)
-  if (g_pair_mode && tp.epi == TC_EPI_NONE && tp.Cout % 256 == 0 && tp.ntaps > 0 && tp.ntaps * tp.Cin >= 512 &&
+  const bool pair_epi = tp.epi == TC_EPI_NONE || (tp.epi == TC_EPI_BIAS && tp.scale != nullptr && tp.out2 == nullptr);
+  if (g_pair_mode && pair_epi && tp.Cout % 256 == 0 && tp.ntaps > 0 && tp.ntaps * tp.Cin >= 512 &&
       (mtiles >= kNumSMs || (mtiles >= kNumSMs / 2 && tp.ntaps * tp.Cin >= 2304))) {
     // 256-filter tiles unless mode 3 asks for 128 (measured: half-width tiles fill the last wave better, 7 waves of 74
     // clusters instead of 4 on layer3, but pay the pixel box twice and end up slower: 76.6 vs 70.5 us)
@@ -711,7 +726,7 @@ static int conv_tc_fprop(const void* x, const void* w_krsc, void* y, const iit_c
   if (check_tc_ptrs(x, w_krsc, y, name)) return 1;
   TcParams tp{};
   if (epi != nullptr) {
-    tp.epi = epi->epi; tp.bias = epi->bias; tp.aux = epi->aux; tp.out2 = epi->out2;
+    tp.epi = epi->epi; tp.bias = epi->bias; tp.aux = epi->aux; tp.out2 = epi->out2; tp.scale = epi->scale; tp.relu = epi->relu;
     for (int i = 0; i < 6; ++i) tp.box[i] = epi->box[i];
   }
   tp.N = d->n; tp.P = d->p; tp.Q = d->q; tp.OH = d->p; tp.OW = d->q;
@@ -1071,7 +1086,8 @@ static int launch_wgrad_tc(const CUtensorMap& mdy, const CUtensorMap& mx, float*
 // conv_win.cu: shifted-window kernel for 3x3 / stride-1 / 64 -> 64 convolutions on small images
 bool conv_win_3x3_supported(const iit_conv_t* d);
 int conv_win_3x3(const void* in, const void* wmat, void* out, const iit_conv_t* d, bool flip, cudaStream_t st, double* bn_sum,
-                 double* bn_sq, const char* name, bool accumulate = false);
+                 double* bn_sq, const char* name, bool accumulate = false, const float* scale = nullptr,
+                 const float* shift = nullptr, const void* residual = nullptr, int relu = 0);
 bool wgrad_win_supported(const iit_conv_t* d);
 size_t wgrad_win_scratch_bytes(const iit_conv_t* d);
 int wgrad_win(const void* dy, const void* x, float* part, const iit_conv_t* d, int* splits, cudaStream_t st, const char* name);
@@ -1111,6 +1127,24 @@ extern "C" int iit_conv2d_fprop_tc(const void* x, const void* w_krsc, void* y, c
     return conv_win_3x3(x, w_krsc, y, d, false, as_stream(stream), bn_sum, bn_sqsum, "iit_conv2d_fprop_tc");
   }
   return conv_tc_fprop(x, w_krsc, y, d, as_stream(stream), bn_sum, bn_sqsum);
+}
+
+// y = act(conv(x, w) * scale[k] + shift[k] (+ residual)): an eval-mode BatchNorm (and the block's residual addition and
+// ReLU) folded into the convolution's epilogue, on the fp32 accumulator
+extern "C" int iit_conv2d_fprop_tc_affine(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, const float* scale,
+                                          const float* shift, const void* residual, int relu, void* stream) {
+  const char* name = "iit_conv2d_fprop_tc_affine";
+  IIT_REQUIRE(x && w_krsc && y && d && scale && shift, "%s: null pointer", name);
+  IIT_REQUIRE(iit_conv2d_tc_supported(d, IIT_BF16), "%s: only bf16 3x3/pad-1 or 1x1/pad-0 convolutions, stride 1 or 2, with channel "
+              "counts that are multiples of 64", name);
+  IIT_REQUIRE(((reinterpret_cast<uintptr_t>(scale) | reinterpret_cast<uintptr_t>(shift) | reinterpret_cast<uintptr_t>(residual)) & 15) == 0,
+              "%s: scale, shift and residual must be 16-byte aligned", name);
+  if (check_tc_ptrs(x, w_krsc, y, name)) return 1;
+  if (g_use_win && conv_win_3x3_supported(d))
+    return conv_win_3x3(x, w_krsc, y, d, false, as_stream(stream), nullptr, nullptr, name, false, scale, shift, residual, relu);
+  TcParams e{};
+  e.epi = TC_EPI_BIAS; e.scale = scale; e.bias = shift; e.aux = (const __nv_bfloat16*)residual; e.relu = relu;
+  return conv_tc_fprop(x, w_krsc, y, d, as_stream(stream), nullptr, nullptr, &e, name);
 }
 
 static int dgrad_tc_entry(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream, bool accumulate,

@@ -41,7 +41,19 @@ struct WinParams {
   int16_t doff[WIN_MAX_TAPS];  // tap -> row offset dh*PW + dw (relative to the output position)
   int8_t wk[WIN_MAX_TAPS];     // tap -> block column of the filter matrix
   int accumulate;              // != 0: results are added to `out` (one 16-byte reduction per piece) instead of stored
+  // folded eval-mode BatchNorm (iit_conv2d_fprop_tc_affine): y = act(acc * scale[k] + shift[k] (+ residual)); scale == null: off
+  const float* scale;
+  const float* shift;
+  const __nv_bfloat16* residual;   // laid out like `out`, or null
+  int relu;
 };
+
+// this lane's pixel (n, oh, ww), filters c .. c + 31 of the accumulator row, before rounding
+__device__ __forceinline__ void win_affine(uint32_t (&v)[32], const WinParams& p, int n, int oh, int ww, int c, bool ok) {
+  tc_scale_shift(v, p.scale + c, p.shift + c);
+  if (p.residual != nullptr && ok) tc_add_bf16_row(v, p.residual + (((int64_t)n * p.OH + oh) * p.OW + ww) * WIN_BN + c);
+  if (p.relu) tc_relu(v);
+}
 
 // K-major operand descriptor for rows of RB bytes: SWIZZLE_128B (RB = 128) or SWIZZLE_32B (RB = 32)
 template <int RB>
@@ -195,6 +207,7 @@ __global__ void __launch_bounds__(WIN_CONV_THREADS) conv_win_kernel(const __grid
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
           __syncwarp();
           if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[acc])) : "memory");
+          if (p.scale != nullptr) win_affine(v, p, n, hh, ww, c, ok);
           // the tile's 128 positions are rows hh0 .. of the image, all PW columns from output column 0
           const int hh0 = (j0 + 128 * t) / p.PW - p.pad_top;
           tc_round_store<(OBUF > 0 ? OBUF : 1)>(v, ok, s_out + (round++ % (OBUF > 0 ? OBUF : 1)) * TC_OUT_TILE_BYTES, quarter, half, lane,
@@ -225,6 +238,7 @@ __global__ void __launch_bounds__(WIN_CONV_THREADS) conv_win_kernel(const __grid
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncwarp();
         if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[acc])) : "memory");
+        if (p.scale != nullptr) win_affine(v, p, n, oh, ww, c, ok);
         // bf16 pairs as stored; the BatchNorm statistics are taken from these rounded values. Each lane keeps running sums
         // for its own accumulator row across all the tiles of this CTA (2 x 32 fp32 registers); the cross-lane reduction
         // happens once, after the tile loop.
@@ -429,10 +443,12 @@ bool conv_win_3x3_supported(const iit_conv_t* d) {
 }
 
 int conv_win_3x3(const void* in, const void* wmat, void* out, const iit_conv_t* d, bool flip, cudaStream_t st, double* bn_sum,
-                 double* bn_sq, const char* name, bool accumulate) {
+                 double* bn_sq, const char* name, bool accumulate, const float* scale, const float* shift, const void* residual,
+                 int relu) {
   WinParams p{};
   p.N = d->n; p.ntaps = 9;
   p.accumulate = accumulate ? 1 : 0;
+  p.scale = scale; p.shift = shift; p.residual = (const __nv_bfloat16*)residual; p.relu = relu;
   const int PW = d->w + 2;
   IIT_REQUIRE(win_plan(&p, 128, d->p, d->q, PW, 2, 1, 1, PW + 1, -(PW + 1)), "%s: image does not fit the shifted-window kernel", name);
   p.x0 = -1; p.y0 = -1; p.y_step = p.band_h;

@@ -81,6 +81,17 @@ __global__ void bn_finalize_kernel(double* __restrict__ sum, double* __restrict_
   }
 }
 
+__global__ void bn_eval_affine_kernel(const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ rmean,
+                                      const float* __restrict__ rvar, int C, float eps, float* __restrict__ scale,
+                                      float* __restrict__ shift) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float is = (float)(1.0 / sqrt((double)rvar[c] + (double)eps));      // as bn_eval_invstd_kernel
+  const float sc = gamma[c] * is;
+  scale[c] = sc;
+  shift[c] = beta[c] - rmean[c] * sc;
+}
+
 __global__ void bn_eval_invstd_kernel(const float* __restrict__ rvar, int C, float eps, float* __restrict__ invstd) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c < C) invstd[c] = 1.0f / sqrtf(rvar[c] + eps);
@@ -534,6 +545,14 @@ extern "C" int iit_bn_finalize(double* sum, double* sqsum, int64_t rows, int c, 
                                                                     running_mean, running_var,
                                                                     reinterpret_cast<long long*>(num_batches_tracked), clear_sums);
   IIT_LAUNCH_CHECK("iit_bn_finalize");
+  return 0;
+}
+
+extern "C" int iit_bn_eval_affine(const float* gamma, const float* beta, const float* running_mean, const float* running_var, int c,
+                                  float eps, float* scale, float* shift, void* stream) {
+  IIT_REQUIRE(gamma && beta && running_mean && running_var && scale && shift && c >= 1, "iit_bn_eval_affine: bad arguments");
+  bn_eval_affine_kernel<<<(c + 127) / 128, 128, 0, as_stream(stream)>>>(gamma, beta, running_mean, running_var, c, eps, scale, shift);
+  IIT_LAUNCH_CHECK("iit_bn_eval_affine");
   return 0;
 }
 

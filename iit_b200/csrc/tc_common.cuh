@@ -155,6 +155,32 @@ __device__ __forceinline__ void umma2_commit_both(uint64_t* bar) {
                ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
 }
 
+// ---- epilogue arithmetic on a lane's 32 fp32 accumulator columns -----------------------------------------------------
+__device__ __forceinline__ void tc_scale_shift(uint32_t (&v)[32], const float* __restrict__ scale, const float* __restrict__ shift) {
+#pragma unroll
+  for (int j = 0; j < 32; j += 4) {
+    const float4 a = *reinterpret_cast<const float4*>(scale + j), b = *reinterpret_cast<const float4*>(shift + j);
+    v[j] = __float_as_uint(fmaf(__uint_as_float(v[j]), a.x, b.x)); v[j + 1] = __float_as_uint(fmaf(__uint_as_float(v[j + 1]), a.y, b.y));
+    v[j + 2] = __float_as_uint(fmaf(__uint_as_float(v[j + 2]), a.z, b.z)); v[j + 3] = __float_as_uint(fmaf(__uint_as_float(v[j + 3]), a.w, b.w));
+  }
+}
+__device__ __forceinline__ void tc_add_bf16_row(uint32_t (&v)[32], const __nv_bfloat16* __restrict__ row) {
+#pragma unroll
+  for (int j = 0; j < 32; j += 8) {
+    const uint4 a4 = *reinterpret_cast<const uint4*>(row + j);
+    const uint32_t w4[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+    for (int h = 0; h < 4; ++h) {
+      v[j + 2 * h] = __float_as_uint(__uint_as_float(v[j + 2 * h]) + __uint_as_float(w4[h] << 16));
+      v[j + 2 * h + 1] = __float_as_uint(__uint_as_float(v[j + 2 * h + 1]) + __uint_as_float(w4[h] & 0xffff0000u));
+    }
+  }
+}
+__device__ __forceinline__ void tc_relu(uint32_t (&v)[32]) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(fmaxf(__uint_as_float(v[j]), 0.f));
+}
+
 // ---- epilogue stores -------------------------------------------------------------------------------
 // 8 bf16 values: dst[0..7] = v (plain 16-byte store) or dst[0..7] += v (ONE 16-byte reduction instruction,
 // red.global.add.noftz.v4.bf16x2 = REDG.E.ADD.BF16x8: the addition happens in L2, the SM neither loads the old values nor

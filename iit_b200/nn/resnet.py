@@ -135,6 +135,16 @@ class BatchNorm2d(nn.Module):
             self.__dict__["_acc"] = acc
         return acc
 
+    def eval_affine(self):
+        """(scale, shift) with y = x * scale + shift in evaluation mode, cached until a parameter or running statistic changes."""
+        key = (self.weight._version, self.bias._version, self.running_mean._version, self.running_var._version,
+               self.weight.data_ptr(), self.running_mean.data_ptr())
+        ent = self.__dict__.get("_affine")
+        if ent is None or ent[0] != key:
+            ent = self.__dict__["_affine"] = (key, ops.bn_eval_affine(self.weight.detach(), self.bias.detach(), self.running_mean,
+                                                                      self.running_var, self.eps))
+        return ent[1]
+
     def grad_accumulator(self, device):
         """The same for the backward's per-channel sums (cleared by iit_bn_param_grads)."""
         acc = self.__dict__.get("_bacc")
@@ -234,6 +244,12 @@ def _conv_bn(conv: Wrapped, bn: Wrapped, x, residual=None, relu=False, fuse_stat
     can modify the conv output first (the patch site): then they are taken from the hooked tensor."""
     bnm = bn.mod
     sums = None
+    if (not bnm.training and act_dtype is None and not conv.hook_point.has_hooks() and not conv.mod.is_stem()
+            and ops.conv_affine_ok(x, conv.mod.weight, conv.mod.stride, conv.mod.pad)):
+        # evaluation pass, nothing looks at the convolution's own output: conv + BatchNorm (+ residual) (+ ReLU) in one kernel
+        scale, shift = bnm.eval_affine()
+        return ops.conv2d_affine(x, conv.mod.weight.shape, conv.mod.prepared(x.dtype)[0], conv.mod.stride, conv.mod.pad, scale, shift,
+                                 residual, relu)
     plan = conv.mod.plan_patch(x, conv.hook_point) if (act_dtype is None and conv.hook_point.has_hooks()) else None
     if plan is not None and plan[0] == "whole":
         # the whole output is replaced by the cached source activation: the convolution's result (and its gradient) would be

@@ -504,6 +504,43 @@ class _ConvFn(torch.autograd.Function):
         return dx, dw, None, None, None, None, None, None, None, None
 
 
+FOLD_EVAL_BN = True     # evaluation passes run conv + BatchNorm (+ residual) (+ ReLU) as one kernel (tests flip it to compare)
+
+
+def conv_affine_ok(x, weight, stride, pad) -> bool:
+    """Whether conv2d_affine can take this convolution (the tensor-core path on bf16 activations, outside autograd)."""
+    if not (FOLD_EVAL_BN and USE_TENSOR_CORES and x.is_cuda and x.dtype == torch.bfloat16 and not torch.is_grad_enabled()):
+        return False
+    k, c, r, s = weight.shape
+    return bool(_lib.lib.iit_conv2d_tc_supported(C.byref(_conv_desc(_cl(x), k, r, s, stride, pad)), _dt(x)))
+
+
+def conv2d_affine(x, weight_shape, w_krsc, stride, pad, scale, shift, residual=None, relu=False):
+    """y = act(conv(x, w) * scale[k] + shift[k] (+ residual)) in one kernel (iit_conv2d_fprop_tc_affine): an evaluation-mode
+    BatchNorm, the block's residual addition and its ReLU folded into the convolution's epilogue. No autograd: evaluation
+    passes only (the causality sweep, run_eval_step)."""
+    _require_cuda(x, scale, shift, residual)
+    x = _cl(x)
+    k, c, r, s = weight_shape
+    d = _conv_desc(x, k, r, s, stride, pad)
+    y = empty_cl(d.n, k, d.p, d.q, x.dtype, x.device)
+    if residual is not None:
+        residual = _cl(residual)
+        if residual.shape != y.shape or residual.dtype != y.dtype:
+            raise RuntimeError("conv2d_affine: the residual must have the output's shape and dtype")
+    call("iit_conv2d_fprop_tc_affine", _p(x), _p(w_krsc), _p(y), C.byref(d), _p(scale), _p(shift), _p(residual), int(bool(relu)), _stream())
+    return y
+
+
+def bn_eval_affine(gamma, beta, running_mean, running_var, eps):
+    """(scale, shift) of an evaluation-mode BatchNorm as one per-channel affine map."""
+    c = gamma.numel()
+    scale = torch.empty(c, dtype=torch.float32, device=gamma.device)
+    shift = torch.empty(c, dtype=torch.float32, device=gamma.device)
+    call("iit_bn_eval_affine", _p(gamma), _p(beta), _p(running_mean), _p(running_var), c, float(eps), _p(scale), _p(shift), _stream())
+    return scale, shift
+
+
 def conv2d(x, weight, w_krsc, w_crsk_fn, stride, pad, bn_sums=None, wgrad_buf=None, slot=None, patch=None):
     """`wgrad_buf`: see direct_grad -- the weight gradient is added into it and autograd receives None.
     `slot`: see GradSlot -- shared with the other consumer of `x` in the same residual block.

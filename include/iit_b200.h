@@ -199,6 +199,14 @@ int iit_conv2d_wgrad_noalloc(const void* dy, const void* x, float* dw, const iit
 int iit_conv2d_tc_supported(const iit_conv_t* d, int dtype);
 int iit_conv2d_fprop_tc(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, double* bn_sum,
                         double* bn_sqsum, void* stream);
+/* Evaluation-mode convolution + BatchNorm (+ residual) (+ ReLU) in one kernel: y = act(conv(x, w) * scale[k] + shift[k]
+ * (+ residual)), scale = gamma / sqrt(running_var + eps), shift = beta - running_mean * scale (iit_bn_eval_affine), applied to
+ * the fp32 accumulator in the epilogue. residual (may be NULL) is laid out like y. The evaluation passes of the causality
+ * sweep and of run_eval_step use it wherever no hook sits between the convolution and its BatchNorm. */
+int iit_conv2d_fprop_tc_affine(const void* x, const void* w_krsc, void* y, const iit_conv_t* d, const float* scale,
+                               const float* shift, const void* residual, int relu, void* stream);
+int iit_bn_eval_affine(const float* gamma, const float* beta, const float* running_mean, const float* running_var, int c,
+                       float eps, float* scale, float* shift, void* stream);
 int iit_conv2d_dgrad_tc(const void* dy, const void* w_crsk, void* dx, const iit_conv_t* d, void* stream);
 /* dx += dgrad(dy): the same kernels with their epilogue's stores replaced by 16-byte bf16 reductions (the addition is done
  * in L2; every element receives exactly one addend, so the result is order-independent and equals a bf16 tensor addition).

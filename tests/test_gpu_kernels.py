@@ -947,6 +947,61 @@ def test_transformer_with_gelu_in_the_gemm_epilogues_matches_the_default_path():
             assert float((out[True][1][n] - gref).norm() / gref.norm()) < 5e-2, n
 
 
+def test_eval_batchnorm_folded_into_the_convolution(ops):
+    """iit_conv2d_fprop_tc_affine: conv + evaluation-mode BatchNorm (+ residual) (+ ReLU) in one kernel, on every kernel
+    family the ResNet uses, against convolution -> BatchNorm kernel (which rounds the convolution's output to bf16 in between:
+    hence 3 bf16 ulps of the output scale); then the whole network in eval mode with and without the fold."""
+    from iit_b200.nn import resnet
+    from iit_b200.nn.resnet import BatchNorm2d, Conv2d, Wrapped
+    g = torch.Generator().manual_seed(23)
+    for (c, k, hw, n, ks, stride, pad) in [(64, 64, 14, 150, 3, 1, 1), (128, 128, 7, 300, 3, 1, 1), (256, 256, 4, 1300, 3, 1, 1),
+                                           (64, 128, 14, 40, 1, 2, 0), (512, 512, 2, 2100, 3, 1, 1), (128, 256, 7, 600, 3, 2, 1),
+                                           (64, 64, 21, 5, 3, 1, 1)]:
+        x = torch.randn(n, c, hw, hw, generator=g).to(DEV).bfloat16().contiguous(memory_format=torch.channels_last)
+        conv, bn = Wrapped(Conv2d(c, k, ks, stride, pad)).to(DEV), Wrapped(BatchNorm2d(k)).to(DEV)
+        with torch.no_grad():
+            bn.mod.weight.copy_(torch.rand(k, generator=g) + 0.5)
+            bn.mod.bias.copy_(torch.randn(k, generator=g) * 0.3)
+            bn.mod.running_mean.copy_(torch.randn(k, generator=g) * 0.2)
+            bn.mod.running_var.copy_(torch.rand(k, generator=g) + 0.5)
+        bn.mod.eval()
+        ohw = (hw + 2 * pad - ks) // stride + 1
+        res = torch.randn(n, k, ohw, ohw, generator=g).to(DEV).bfloat16().contiguous(memory_format=torch.channels_last)
+        for residual, relu in ((None, False), (None, True), (res, True)):
+            out = {}
+            for fold in (True, False):
+                ops.FOLD_EVAL_BN = fold
+                seen = []
+                inner = ops.call
+                ops.call = lambda name, *a, inner=inner, seen=seen: (seen.append(name), inner(name, *a))[1]
+                try:
+                    with torch.no_grad():
+                        out[fold] = resnet._conv_bn(conv, bn, x, residual=residual, relu=relu).float()
+                finally:
+                    ops.call = inner
+                    ops.FOLD_EVAL_BN = True
+                assert ("iit_conv2d_fprop_tc_affine" in seen) == fold and ("iit_bn_act_fwd" in seen) == (not fold), seen
+            scale = out[False].abs().max().item()
+            assert (out[True] - out[False]).abs().max().item() <= 3 * 2 ** -8 * scale, (c, k, hw, ks, stride, relu, residual is not None)
+    # the network: eval-mode logits with and without the fold
+    from iit_b200.tasks.mnist_pvr.get_alignment import get_alignment
+    ll, _, _ = get_alignment("mnist_pvr", {"input_shape": (1, 3, 56, 56)}, device=DEV, dtype=torch.bfloat16)
+    ll.load_state_dict(R.resnet18_state_dict(0))
+    ll.eval()
+    img = R.synthetic_pvr(96, 31)[0].to(DEV)
+    logits = {}
+    for fold in (True, False):
+        ops.FOLD_EVAL_BN = fold
+        try:
+            with torch.no_grad():
+                logits[fold] = ll(img).float()
+        finally:
+            ops.FOLD_EVAL_BN = True
+    rel = float((logits[True] - logits[False]).norm() / logits[False].norm())
+    assert rel < 2e-2, rel
+    assert float((logits[True].argmax(1) == logits[False].argmax(1)).float().mean()) > 0.97
+
+
 def test_weight_gradients_added_straight_into_the_optimizer_buffers():
     """iit_conv2d_wgrad_tc_scatter: with FlatAdam's gradient views in place, the transformer's weight-gradient GEMMs add their
     split-K sums into those views (per-head / transposed layouts through the map table) and hand autograd None. Two
