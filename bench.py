@@ -347,7 +347,8 @@ PVR_HBM = ["iit_bn_act_fwd", "iit_bn_act_bwd_reduce", "iit_bn_act_bwd_apply", "i
 IOI_HBM = ["iit_gemm_bias_act_tc", "iit_gemm_dgrad_gelu_tc", "iit_gelu_bwd_bias_colsum", "iit_bias_act_fwd", "iit_gelu_bwd", "iit_colsum", "iit_attn_fwd", "iit_attn_bwd", "iit_lnpre_fwd", "iit_lnpre_bwd",
            "iit_hl_ce_fwd", "iit_ce_index_fwd", "iit_ce_index_bwd"]
 CONV_ENTRIES = ["iit_conv2d_fprop", "iit_conv2d_dgrad", "iit_conv2d_wgrad", "iit_conv2d_fprop_tc", "iit_conv2d_dgrad_tc",
-                "iit_conv2d_wgrad_tc", "iit_conv2d_wgrad_tc_accumulate", "iit_stem_conv_s2d", "iit_stem_wgrad_s2d"]
+                "iit_conv2d_wgrad_tc", "iit_conv2d_wgrad_tc_accumulate", "iit_stem_conv_s2d", "iit_stem_wgrad_s2d",
+                "iit_conv2d_fprop_tc_affine", "iit_conv2d_fprop_tc_patch", "iit_conv2d_dgrad_tc_accumulate", "iit_conv2d_wgrad_tc_scatter"]
 
 
 def stem_flops(name, a):
