@@ -550,7 +550,7 @@ static int launch_tc(const CUtensorMap& ma, const CUtensorMap& mb, const CUtenso
 }
 
 // CTA-pair launch (256 pixels x BN filters per cluster of two)
-static int g_pair_mode = 1;   // 0 off; 1 / 2 on for Cout % 256 == 0 with 256-filter tiles; 3 the same with 128-filter tiles
+static int g_pair_mode = 1;   // 0 off; 1 on (Cout % 256 == 0: 256-filter tiles; Cout == 128 with long reductions: 128); 2 without the 128-filter layers; 3 128-filter tiles everywhere
 template <int BN>
 static int launch_tc2(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, __nv_bfloat16* out, const TcParams& p,
                       int total_tiles, cudaStream_t st, double* bn_sum, double* bn_sq) {
@@ -669,13 +669,17 @@ static int conv_tc_launch(const void* gathered, int gC, int gW, int gH, const vo
   // ... and not for reductions of one or two k-blocks (the 1x1 downsample 128 -> 256: 24.6 us on pairs, 20.5 us on single
   // CTAs, which keep two output tiles in flight)
   const bool pair_epi = tp.epi == TC_EPI_NONE || (tp.epi == TC_EPI_BIAS && tp.scale != nullptr && tp.out2 == nullptr);
-  if (g_pair_mode && pair_epi && tp.Cout % 256 == 0 && tp.ntaps > 0 && tp.ntaps * tp.Cin >= 512 &&
+  // 128-filter layers with a long reduction (layer2's 3x3s) run on pairs too: 256 pixels x 128 filters per pair, each CTA
+  // loads half the filter block (layer2 fprop 61.0 -> 58.9 us, dgrad 59.9 -> 57.9 us against two pixel boxes per single CTA;
+  // mode 2 keeps them on single CTAs)
+  const bool pair_cout = tp.Cout % 256 == 0 || (g_pair_mode != 2 && tp.Cout == 128 && tp.ntaps * tp.Cin >= 1024);
+  if (g_pair_mode && pair_epi && pair_cout && tp.ntaps > 0 && tp.ntaps * tp.Cin >= 512 &&
       (mtiles >= kNumSMs || (mtiles >= kNumSMs / 2 && tp.ntaps * tp.Cin >= 2304))) {
     // 256-filter tiles unless mode 3 asks for 128 (measured: half-width tiles fill the last wave better, 7 waves of 74
     // clusters instead of 4 on layer3, but pay the pixel box twice and end up slower: 76.6 vs 70.5 us)
     const int64_t pairs = (mtiles + 1) / 2;
     const int64_t t256 = pairs * (tp.Cout / 256), t128 = pairs * (tp.Cout / 128);
-    const int BN2 = g_pair_mode == 3 ? 128 : 256;
+    const int BN2 = (g_pair_mode == 3 || tp.Cout % 256 != 0) ? 128 : 256;
     if (encode_filter(&mb, wmat, Kg, tp.Cout, BN2 / 2, name)) return 1;
     const int64_t total2 = BN2 == 256 ? t256 : t128;
     IIT_REQUIRE(total2 < (1ll << 31), "%s: too many tiles", name);

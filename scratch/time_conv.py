@@ -104,6 +104,13 @@ if __name__ == "__main__":
             case(N, 14, 64, 64, 3, 1, True)
             case(N, 14, 64, 64, 3, 1, False, "dgrad")
         sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "pair128":    # layer2 on CTA pairs (mode 4) against the two-box single-CTA tiles
+        for mode in (2, 1, 2, 1):
+            _lib.lib.iit_conv_pair_enable(mode)
+            print("pair mode", mode)
+            case(N, 7, 128, 128, 3, 1, True)
+            case(N, 7, 128, 128, 3, 1, False, "dgrad")
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "pair":       # short reductions with and without the CTA-pair kernel
         for on in (1, 0):
             _lib.lib.iit_conv_pair_enable(on)

@@ -134,9 +134,9 @@ def test_c2_batch4096_bf16_graphs_pair_kernel_teacher_forced():
         opair.opt.step()
     after = _lib.kernel_variant_counts()
     ran = {k for k in after if after[k] > before[k]}
-    # the kernels bench.py's headline runs on: CTA pair (layers 3-4), two pixel boxes per filter block (layer2),
+    # the kernels bench.py's headline runs on: CTA pairs (layers 3-4 with 256-filter tiles, layer2 with 128-filter tiles),
     # shifted-window layer1 / stem, tensor-core weight gradients
-    for k in ("conv3x3_tc2_kernel<256,6>", "conv3x3_tc_kernel<128,4,2>", "conv_win_kernel<128,9,4>", "conv_win_kernel<32,16,4>",
+    for k in ("conv3x3_tc2_kernel<256,6>", "conv3x3_tc2_kernel<128,8>", "conv_win_kernel<128,9,4>", "conv_win_kernel<32,16,4>",
               "wgrad3x3_tc_kernel", "wgrad_win_kernel", "stem_wgrad_win_kernel"):
         assert k in ran, (k, ran)
     # activations at the hooked layer, eager, same (oracle) weights, train-mode statistics
