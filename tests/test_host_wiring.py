@@ -294,3 +294,31 @@ def test_direct_grad_only_for_the_marked_flat_view():
     assert ops.direct_grad(p) is None
     p.grad = None
     assert ops.direct_grad(p) is None
+
+
+def test_wgrad_direct_maps_table_layout():
+    """ops.wgrad_direct_maps: the iit_wgrad_map_t table the scatter reduction reads -- one entry per parameter, shape padded to
+    three indices from the left, strides / offset of the [out][in] matrix, destination = the marked gradient view; None as soon
+    as one parameter's gradient may not be written in place; rebuilt only when a gradient buffer moved."""
+    import ctypes as C
+    from iit_b200 import _lib, ops
+    H, D, dh, n_in = 4, 64, 16, 64
+    specs = [((H, D, dh), (dh * n_in, 1, n_in), 0), ((D, 3072), (1, D), 64 * n_in)]
+    params = [torch.nn.Parameter(torch.zeros(sz)) for sz, _, _ in specs]
+    cache = {}
+    with torch.enable_grad():
+        assert ops.wgrad_direct_maps(specs, params, cache) is None          # no marked gradient views yet
+        for p in params:
+            p.grad = torch.zeros_like(p)
+            p._iit_direct_grad = p.grad
+        got = ops.wgrad_direct_maps(specs, params, cache)
+        assert got is not None and got[0] == "direct" and got[3] == 2 and got[4] == D * 3072
+        table = (_lib.WgradMap * 2).from_buffer_copy(bytes(got[2].numpy().tobytes()))
+        assert table[0].dst == params[0].grad.data_ptr() and list(table[0].size) == [H, D, dh]
+        assert list(table[0].stride) == [dh * n_in, 1, n_in] and table[0].offset == 0
+        assert list(table[1].size) == [1, D, 3072] and list(table[1].stride) == [0, 1, D] and table[1].offset == 64 * n_in
+        assert ops.wgrad_direct_maps(specs, params, cache)[2] is got[2]      # cached
+        params[1].grad = torch.zeros_like(params[1])                         # another tensor, not marked: no in-place writes
+        assert ops.wgrad_direct_maps(specs, params, cache) is None
+    with torch.no_grad():
+        assert ops.wgrad_direct_maps(specs, params, cache) is None
