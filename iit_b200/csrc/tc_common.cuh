@@ -263,16 +263,22 @@ __device__ __forceinline__ void tc_round_store(const uint32_t (&v)[32], bool kee
   if (stats) {
     const int par = lane >> 4, cp = lane & 15;
     const uint32_t u = (uint32_t)(half * 4 + (cp >> 2)), w4 = (uint32_t)(cp & 3) * 4;
-    float s0 = rs[0], s1 = rs[1], q0 = rs[2], q1 = rs[3];
+    // both channels of a word at once: add.rn.f32x2 / fma.rn.f32x2 (SASS FADD2 / FFMA2), the same roundings as the scalar forms
+    uint64_t s2, q2;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(s2) : "f"(rs[0]), "f"(rs[1]));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(q2) : "f"(rs[2]), "f"(rs[3]));
 #pragma unroll
     for (int r = 0; r < 16; ++r) {
       const int gr = quarter * 32 + (r >> 2) * 8 + par * 4 + (r & 3);
       uint32_t w;
       asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(smem_u32(s_out) + gr * 128 + ((u ^ (uint32_t)(gr & 7)) << 4) + w4) : "memory");
-      const float f0 = __uint_as_float(w << 16), f1 = __uint_as_float(w & 0xffff0000u);
-      s0 += f0; s1 += f1; q0 = fmaf(f0, f0, q0); q1 = fmaf(f1, f1, q1);
+      uint64_t f2;
+      asm("mov.b64 %0, {%1, %2};" : "=l"(f2) : "r"(w << 16), "r"(w & 0xffff0000u));
+      asm("add.rn.f32x2 %0, %0, %1;" : "+l"(s2) : "l"(f2));
+      asm("fma.rn.f32x2 %0, %1, %1, %0;" : "+l"(q2) : "l"(f2));
     }
-    rs[0] = s0; rs[1] = s1; rs[2] = q0; rs[3] = q1;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(rs[0]), "=f"(rs[1]) : "l"(s2));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(rs[2]), "=f"(rs[3]) : "l"(q2));
   }
   if (leader) tma_store_wait_read<OBUF - 1>();         // before this thread arrives at the next round's first barrier
 }
